@@ -1,0 +1,162 @@
+/*
+ * mpb.h -- C ABI of the B200 batched state-validity engine ("libmpb.so").
+ *
+ * The reference (KolinGuo/MPlib @ c647ab9) has no C ABI: its pybind11 module binds the C++
+ * classes directly (python/pybind.cpp:16-27).  This header is the boundary the replacement
+ * introduces: the host layer that mirrors the reference classes (mplib_b200/pymp) compiles a
+ * PlanningWorld into the flat `mpb_scene_desc` below and calls these entry points; each entry
+ * point names the reference function(s) whose per-state work it performs for a whole batch.
+ *
+ * Conventions: plain C structs, caller-owned memory, no exceptions across the boundary.  Every
+ * function returns MPB_OK (0) or a negative status; `mpb_last_error()` gives a thread-local
+ * message.  Matrices are row-major 3x4 ([R|p], 12 doubles).  Pose vectors are
+ * [x, y, z, qw, qx, qy, qz] (src/math_utils.cpp:12-18).
+ */
+#ifndef MPB_H_
+#define MPB_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPB_OK 0
+#define MPB_ERR_INVALID (-1)   /* bad argument / malformed description (reference: std::invalid_argument / ASSERT) */
+#define MPB_ERR_CUDA (-2)      /* CUDA runtime failure, or no usable device */
+#define MPB_ERR_CAPACITY (-3)  /* a static capacity of this build was exceeded */
+#define MPB_ERR_UNSUPPORTED (-4)
+
+/* joint types: Pinocchio JointModelR* / JointModelP* / JointModelRUB* (src/pinocchio_model.cpp:69-81) */
+#define MPB_JOINT_REVOLUTE 0
+#define MPB_JOINT_PRISMATIC 1
+#define MPB_JOINT_CONTINUOUS 2
+
+/* collision geometry types (python/pybind_fcl.hpp:59-239, the subset the hot path meets) */
+#define MPB_GEOM_CONVEX 0   /* fcl::Convex    : obj_geom = hull index                         */
+#define MPB_GEOM_SPHERE 1   /* fcl::Sphere    : param = {radius}                              */
+#define MPB_GEOM_BOX 2      /* fcl::Box       : param = {side x, side y, side z}              */
+#define MPB_GEOM_CAPSULE 3  /* fcl::Capsule   : param = {radius, lz}                          */
+#define MPB_GEOM_CYLINDER 4 /* fcl::Cylinder  : param = {radius, lz}                          */
+#define MPB_GEOM_MESH 5     /* fcl::BVHModel<OBBRSS> : obj_geom = mesh index                  */
+#define MPB_GEOM_OCTREE 6   /* fcl::OcTree    : obj_geom = octree index                       */
+
+/* pointer-space flags for batch calls */
+#define MPB_HOST 0    /* q / outputs are host pointers; copies happen inside the call */
+#define MPB_DEVICE 1  /* q / outputs are device pointers on the scene's device       */
+
+/*
+ * Flat description of one PlanningWorld (src/planning_world.h:138-141 holds the same content as
+ * maps of shared_ptr).  All articulations are merged into one kinematic forest; `q_full` is the
+ * concatenation of every articulation's full qpos; a batch *state* (length `state_dim`) writes
+ * the entries `state_map[k]` of `q_full` -- the move-group scatter of
+ * ArticulatedModelTpl::setQpos (src/articulated_model.cpp:108-113) composed with the name-ordered
+ * split of PlanningWorldTpl::setQposAll (src/planning_world.cpp:249-262); all other entries keep
+ * `q_base` (the articulations' current_qpos_).
+ */
+typedef struct mpb_scene_desc {
+  /* movable joints, topological order; model index 0 is the universe, joint i has model index i+1 */
+  int32_t n_joints;
+  const int32_t *joint_parent;    /* [n_joints] model index of the parent joint                */
+  const double *joint_placement;  /* [n_joints][12]                                            */
+  const int32_t *joint_type;      /* [n_joints] MPB_JOINT_*                                    */
+  const double *joint_axis;       /* [n_joints][3] unit axis in the joint frame                */
+  const int32_t *joint_qidx;      /* [n_joints] index into q_full                              */
+  int32_t nq_full;
+  const double *q_base;           /* [nq_full]                                                 */
+  int32_t state_dim;
+  const int32_t *state_map;       /* [state_dim]                                               */
+
+  /* link frames (Pinocchio BODY frames): oMf = oMi[link_joint] * link_placement */
+  int32_t n_links;
+  const int32_t *link_joint;      /* [n_links] model joint index (0 = universe)                */
+  const double *link_placement;   /* [n_links][12]                                             */
+
+  /* collision objects: pose = linkpose(obj_link) * obj_local, or obj_local if obj_link < 0 */
+  int32_t n_objects;
+  const int32_t *obj_type;        /* [n_objects] MPB_GEOM_*                                    */
+  const int32_t *obj_link;        /* [n_objects] link index or -1 (world-fixed)                */
+  const double *obj_local;        /* [n_objects][12]                                           */
+  const double *obj_param;        /* [n_objects][4]                                            */
+  const int32_t *obj_geom;        /* [n_objects] hull / mesh / octree index, else -1           */
+
+  /* convex hull pool */
+  int32_t n_hulls;
+  const int32_t *hull_vert_off;   /* [n_hulls+1] */
+  const double *hull_verts;       /* [.][3]      */
+  const int32_t *hull_face_off;   /* [n_hulls+1] */
+  const int32_t *hull_faces;      /* [.][3] vertex indices local to the hull */
+
+  /* triangle mesh pool */
+  int32_t n_meshes;
+  const int32_t *mesh_vert_off;   /* [n_meshes+1] */
+  const double *mesh_verts;       /* [.][3]       */
+  const int32_t *mesh_tri_off;    /* [n_meshes+1] */
+  const int32_t *mesh_tris;       /* [.][3]       */
+
+  /* octree pool: occupied finest-level voxels as integer cell coordinates floor(p/res) */
+  int32_t n_octrees;
+  const double *oct_res;          /* [n_octrees]   */
+  const int32_t *oct_cell_off;    /* [n_octrees+1] */
+  const int32_t *oct_cells;       /* [.][3]        */
+
+  /* ACM-admitted object pairs, argument order of ::fcl::collide(a, b) preserved */
+  int32_t n_pairs;
+  const int32_t *pair_a;
+  const int32_t *pair_b;
+} mpb_scene_desc;
+
+typedef struct mpb_scene mpb_scene; /* opaque: device image + work queues + streams */
+
+/* Per-call counters (SURVEY 5 "metrics": new; the reference has none). */
+typedef struct mpb_stats {
+  int64_t n_states;
+  int64_t pairs_admitted;    /* n_states * n_pairs                                   */
+  int64_t pairs_after_cull;  /* items that reached an exact narrowphase              */
+  int64_t narrow_iterations; /* support-mapping evaluations (MPR/GJK iterations)     */
+  int64_t narrow_capped;     /* items that hit the iteration cap (reported, not hidden) */
+  int64_t kernel_launches;   /* kernels launched by this call                        */
+  float gpu_ms;              /* device time of the call's kernels (CUDA events)      */
+  float gpu_ms_cull;         /* FK + broadphase kernels                              */
+  float gpu_ms_narrow;       /* narrowphase kernel(s)                                */
+} mpb_stats;
+
+/* Thread-local message of the last failing call on this thread. */
+const char *mpb_last_error(void);
+
+/* Number of CUDA devices visible (0 if none); never fails. */
+int mpb_device_count(void);
+
+/* Compile `desc` into a device image on CUDA device `device`.
+ * Replaces the per-state reads of PlanningWorldTpl's maps (src/planning_world.cpp:276-481). */
+int mpb_scene_create(const mpb_scene_desc *desc, int device, mpb_scene **out);
+void mpb_scene_destroy(mpb_scene *scene);
+
+/* Replace q_base (ArticulatedModelTpl::current_qpos_, src/articulated_model.cpp:104-113). */
+int mpb_scene_set_q_base(mpb_scene *scene, const double *q_base, int32_t nq_full);
+
+/* Replace the admitted pair list (after an ACM edit, src/collision_matrix.cpp:34-138). */
+int mpb_scene_set_pairs(mpb_scene *scene, int32_t n_pairs, const int32_t *pair_a, const int32_t *pair_b);
+
+/* Batched PinocchioModelTpl::computeForwardKinematics + getLinkPose for every link
+ * (src/pinocchio_model.cpp:271-312).  q: [n][state_dim] float32; poses: [n][n_links][7] float32. */
+int mpb_fk_batch(mpb_scene *scene, const float *q, int64_t n, float *poses, int space, void *stream);
+
+/* Batched ValidityCheckerTpl::isValid = setQposAll + collideFull (src/ompl_planner.h:59-62,
+ * src/planning_world.cpp:249-262, 483-490).
+ *   q            [n][state_dim] float32
+ *   verdict_bits [ceil(n/32)] uint32, bit (i&31) of word i>>5 set iff state i collides
+ *   pair_bits    nullable, [n][ceil(n_pairs/32)] uint32, bit p set iff admitted pair p collides
+ * `stream` is a cudaStream_t (NULL = the scene's own stream).  With MPB_HOST the call returns
+ * after the results are in the host buffers; with MPB_DEVICE it returns after enqueueing. */
+int mpb_collide_batch(mpb_scene *scene, const float *q, int64_t n, uint32_t *verdict_bits,
+                      uint32_t *pair_bits, mpb_stats *stats, int space, void *stream);
+
+/* Query geometry constants of the compiled scene (for tests / host layer). */
+int mpb_scene_info(const mpb_scene *scene, int32_t *n_pairs, int32_t *state_dim, int32_t *n_links,
+                   int32_t *n_objects, int32_t *device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPB_H_ */

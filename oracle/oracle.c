@@ -1,0 +1,879 @@
+/*
+ * oracle.c -- CPU restatement (double precision, plain C) of the reference's per-state algorithm
+ * for the hot path.  TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs; never by the product path.
+ *
+ * PARITY UNPINNED: the reference cannot be built or imported in this environment (Pinocchio,
+ * FCL, libccd, octomap, OMPL, Eigen, Boost, assimp, urdfdom are all absent) and its own tests
+ * hold no golden vectors (tests/test_basic.py:39-50 has no assertions).  MPlib-side logic below is
+ * restated from /root/reference and cited file:line.  Third-party arithmetic is restated from the
+ * published algorithms of the pinned versions (docker/Dockerfile:17-81): Pinocchio v2.6.21
+ * forwardKinematics, FCL 0.7.0 narrowphase dispatch (GJKSolver_libccd), libccd v2.1 mpr.c, octomap
+ * v1.9.8 -- marked [upstream] where they appear.  The oracle is pinned by hand-derived FK known
+ * answers, the reference's stated example outcomes (examples/detect_collision.py:22-65), analytic
+ * primitive cases and an independent exhaustive SAT (orc_sat_*), see tests/.
+ *
+ * Per-state order follows the reference: scatter state -> FK -> link pose as 7-vector
+ * -> matrix -> object transforms -> every admitted pair -> flags.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <float.h>
+
+#include "../include/mpb.h"
+
+#define ORC_EPS DBL_EPSILON /* libccd CCD_EPS for double builds [upstream] */
+#define ORC_MPR_TOL 1e-6    /* GJKSolver_libccd::collision_tolerance [upstream] */
+#define ORC_MAX_ITERS 500   /* GJKSolver_libccd::max_collision_iterations [upstream] */
+
+typedef struct { double R[9]; double p[3]; } xf_t; /* row-major rotation + translation */
+typedef struct { double v[3]; } v3_t;
+
+/* ------------------------------------------------------------------ small algebra */
+static inline double dot3(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+static inline void cross3(double *o, const double *a, const double *b) {
+  double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  o[0] = x; o[1] = y; o[2] = z;
+}
+static inline void sub3(double *o, const double *a, const double *b) { o[0] = a[0] - b[0]; o[1] = a[1] - b[1]; o[2] = a[2] - b[2]; }
+static inline void add3(double *o, const double *a, const double *b) { o[0] = a[0] + b[0]; o[1] = a[1] + b[1]; o[2] = a[2] + b[2]; }
+static inline void scale3(double *a, double s) { a[0] *= s; a[1] *= s; a[2] *= s; }
+static inline void copy3(double *o, const double *a) { o[0] = a[0]; o[1] = a[1]; o[2] = a[2]; }
+static inline double len2_3(const double *a) { return dot3(a, a); }
+static inline void normalize3(double *a) { double d = 1.0 / sqrt(len2_3(a)); scale3(a, d); } /* ccdVec3Normalize */
+static inline int is_zero(double v) { return fabs(v) < ORC_EPS; }                                /* ccdIsZero */
+static inline int eq_real(double a, double b) {                                                  /* ccdEq */
+  double ab = fabs(a - b);
+  if (ab < ORC_EPS) return 1;
+  a = fabs(a); b = fabs(b);
+  return (b > a) ? (ab < ORC_EPS * b) : (ab < ORC_EPS * a);
+}
+static inline int eq3(const double *a, const double *b) { return eq_real(a[0], b[0]) && eq_real(a[1], b[1]) && eq_real(a[2], b[2]); }
+static inline double sign_real(double v) { return is_zero(v) ? 0.0 : (v < 0 ? -1.0 : 1.0); }   /* ccdSign */
+
+static void xf_from12(xf_t *o, const double *m) {
+  for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) o->R[3 * r + c] = m[4 * r + c]; o->p[r] = m[4 * r + 3]; }
+}
+static void xf_identity(xf_t *o) { memset(o, 0, sizeof(*o)); o->R[0] = o->R[4] = o->R[8] = 1.0; }
+static void xf_mul(xf_t *o, const xf_t *a, const xf_t *b) {
+  xf_t t;
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 3; c++) t.R[3 * r + c] = a->R[3 * r] * b->R[c] + a->R[3 * r + 1] * b->R[3 + c] + a->R[3 * r + 2] * b->R[6 + c];
+    t.p[r] = a->R[3 * r] * b->p[0] + a->R[3 * r + 1] * b->p[1] + a->R[3 * r + 2] * b->p[2] + a->p[r];
+  }
+  *o = t;
+}
+static inline void xf_rot(double *o, const xf_t *t, const double *v) { /* o = R v */
+  double x = t->R[0] * v[0] + t->R[1] * v[1] + t->R[2] * v[2];
+  double y = t->R[3] * v[0] + t->R[4] * v[1] + t->R[5] * v[2];
+  double z = t->R[6] * v[0] + t->R[7] * v[1] + t->R[8] * v[2];
+  o[0] = x; o[1] = y; o[2] = z;
+}
+static inline void xf_rot_t(double *o, const xf_t *t, const double *v) { /* o = R^T v */
+  double x = t->R[0] * v[0] + t->R[3] * v[1] + t->R[6] * v[2];
+  double y = t->R[1] * v[0] + t->R[4] * v[1] + t->R[7] * v[2];
+  double z = t->R[2] * v[0] + t->R[5] * v[1] + t->R[8] * v[2];
+  o[0] = x; o[1] = y; o[2] = z;
+}
+static inline void xf_apply(double *o, const xf_t *t, const double *v) { xf_rot(o, t, v); add3(o, o, t->p); }
+static inline void xf_apply_inv(double *o, const xf_t *t, const double *v) { double d[3]; sub3(d, v, t->p); xf_rot_t(o, t, d); }
+
+/* Eigen Quaternion(Matrix3) -> (w,x,y,z); used by getLinkPose, src/pinocchio_model.cpp:276-312 */
+static void mat_to_quat(const double *R, double *q) {
+  double t = R[0] + R[4] + R[8];
+  if (t > 0) {
+    t = sqrt(t + 1.0);
+    q[0] = 0.5 * t;
+    t = 0.5 / t;
+    q[1] = (R[7] - R[5]) * t; q[2] = (R[2] - R[6]) * t; q[3] = (R[3] - R[1]) * t;
+  } else {
+    int i = 0;
+    if (R[4] > R[0]) i = 1;
+    if (R[8] > R[4 * i]) i = 2;
+    int j = (i + 1) % 3, k = (j + 1) % 3;
+    t = sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
+    q[1 + i] = 0.5 * t;
+    t = 0.5 / t;
+    q[0] = (R[3 * k + j] - R[3 * j + k]) * t;
+    q[1 + j] = (R[3 * j + i] + R[3 * i + j]) * t;
+    q[1 + k] = (R[3 * k + i] + R[3 * i + k]) * t;
+  }
+}
+/* Eigen Quaternion::toRotationMatrix; used by setQpos, src/articulated_model.cpp:118-125 */
+static void quat_to_mat(const double *q, double *R) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  double tx = 2 * x, ty = 2 * y, tz = 2 * z;
+  double twx = tx * w, twy = ty * w, twz = tz * w, txx = tx * x, txy = ty * x, txz = tz * x, tyy = ty * y, tyz = tz * y, tzz = tz * z;
+  R[0] = 1 - (tyy + tzz); R[1] = txy - twz; R[2] = txz + twy;
+  R[3] = txy + twz; R[4] = 1 - (txx + tzz); R[5] = tyz - twx;
+  R[6] = txz - twy; R[7] = tyz + twx; R[8] = 1 - (txx + tyy);
+}
+
+/* ------------------------------------------------------------------ forward kinematics */
+/* Joint motion J(q): [upstream Pinocchio] revolute = rotation about the axis by q (Rodrigues),
+ * prismatic = translation q*axis; continuous joints go through (cos q, sin q)
+ * (src/pinocchio_model.cpp:511-515) which is the same rotation. */
+static void joint_motion(xf_t *o, int type, const double *ax, double q) {
+  xf_identity(o);
+  if (type == MPB_JOINT_PRISMATIC) { o->p[0] = ax[0] * q; o->p[1] = ax[1] * q; o->p[2] = ax[2] * q; return; }
+  double c = cos(q), s = sin(q), v = 1.0 - c;
+  double x = ax[0], y = ax[1], z = ax[2];
+  o->R[0] = x * x * v + c;     o->R[1] = x * y * v - z * s; o->R[2] = x * z * v + y * s;
+  o->R[3] = x * y * v + z * s; o->R[4] = y * y * v + c;     o->R[5] = y * z * v - x * s;
+  o->R[6] = x * z * v - y * s; o->R[7] = y * z * v + x * s; o->R[8] = z * z * v + c;
+}
+
+/* oMi for every model joint (index 0 = universe).  [upstream] pinocchio::forwardKinematics:
+ * liMi = placement * J(q); oMi = oMi[parent] * liMi.   Called from src/pinocchio_model.cpp:271-274. */
+static void fk_joints(const mpb_scene_desc *d, const double *qfull, xf_t *oMi) {
+  xf_identity(&oMi[0]);
+  for (int j = 0; j < d->n_joints; j++) {
+    xf_t pl, jm, li;
+    xf_from12(&pl, d->joint_placement + 12 * j);
+    joint_motion(&jm, d->joint_type[j], d->joint_axis + 3 * j, qfull[d->joint_qidx[j]]);
+    xf_mul(&li, &pl, &jm);
+    xf_mul(&oMi[j + 1], &oMi[d->joint_parent[j]], &li);
+  }
+}
+
+/* getLinkPose (src/pinocchio_model.cpp:276-312): oMf = oMi[parent] * placement -> [p, quat] */
+static void link_pose7(const mpb_scene_desc *d, const xf_t *oMi, int link, double *pose7) {
+  xf_t pl, w;
+  xf_from12(&pl, d->link_placement + 12 * link);
+  xf_mul(&w, &oMi[d->link_joint[link]], &pl);
+  pose7[0] = w.p[0]; pose7[1] = w.p[1]; pose7[2] = w.p[2];
+  mat_to_quat(w.R, pose7 + 3);
+}
+
+/* scatter a state into q_full: src/articulated_model.cpp:108-113 + src/planning_world.cpp:249-262 */
+static void scatter_state(const mpb_scene_desc *d, const double *state, double *qfull) {
+  memcpy(qfull, d->q_base, sizeof(double) * (size_t)d->nq_full);
+  for (int k = 0; k < d->state_dim; k++) qfull[d->state_map[k]] = state[k];
+}
+
+/* Object transforms: link pose -> 7-vector -> matrix (src/articulated_model.cpp:116-125), then
+ * T_obj = T_link * origin2link (src/fcl_model.cpp:138-148); attached bodies use the same product
+ * with their attach pose (src/attached_body.h:48-54).  World-fixed objects keep obj_local. */
+static void object_transforms(const mpb_scene_desc *d, const xf_t *oMi, xf_t *objT, double *link_pose_out /*nullable [nl][7]*/) {
+  xf_t *linkT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_links > 0 ? d->n_links : 1));
+  for (int l = 0; l < d->n_links; l++) {
+    double p7[7];
+    link_pose7(d, oMi, l, p7);
+    if (link_pose_out) memcpy(link_pose_out + 7 * l, p7, sizeof(p7));
+    quat_to_mat(p7 + 3, linkT[l].R);
+    copy3(linkT[l].p, p7);
+  }
+  for (int o = 0; o < d->n_objects; o++) {
+    xf_t loc;
+    xf_from12(&loc, d->obj_local + 12 * o);
+    if (d->obj_link[o] >= 0) xf_mul(&objT[o], &linkT[d->obj_link[o]], &loc);
+    else objT[o] = loc;
+  }
+  free(linkT);
+}
+
+/* ------------------------------------------------------------------ shapes + libccd-style supports */
+typedef struct {
+  int type;          /* MPB_GEOM_* or ORC_TRI */
+  xf_t T;            /* world pose */
+  double a, b, c;    /* sphere r | box half sides | capsule/cylinder r, half height */
+  const double *verts; int nverts; /* convex */
+  double center_local[3];          /* convex interior point (vertex mean), fcl::Convex ctor [upstream] */
+  double tri[9];                   /* triangle vertices in the frame T */
+} shape_t;
+#define ORC_TRI 100
+
+static void shape_from_object(const mpb_scene_desc *d, int o, const xf_t *T, shape_t *s) {
+  memset(s, 0, sizeof(*s));
+  s->type = d->obj_type[o];
+  s->T = *T;
+  const double *p = d->obj_param + 4 * o;
+  switch (s->type) {
+    case MPB_GEOM_SPHERE: s->a = p[0]; break;
+    case MPB_GEOM_BOX: s->a = 0.5 * p[0]; s->b = 0.5 * p[1]; s->c = 0.5 * p[2]; break; /* ccd_box_t dim = side/2 [upstream] */
+    case MPB_GEOM_CAPSULE:
+    case MPB_GEOM_CYLINDER: s->a = p[0]; s->b = 0.5 * p[1]; break;                     /* height = lz/2 [upstream] */
+    case MPB_GEOM_CONVEX: {
+      int h = d->obj_geom[o];
+      int v0 = d->hull_vert_off[h], v1 = d->hull_vert_off[h + 1];
+      s->verts = d->hull_verts + 3 * v0; s->nverts = v1 - v0;
+      double c[3] = {0, 0, 0};
+      for (int i = 0; i < s->nverts; i++) add3(c, c, s->verts + 3 * i);
+      scale3(c, 1.0 / (double)s->nverts);
+      copy3(s->center_local, c);
+    } break;
+    default: break;
+  }
+}
+
+/* [upstream FCL 0.7.0 gjk_libccd-inl.h] support{Box,Sphere,Cap,Cyl,Convex,Triangle}: direction into
+ * the shape frame, extreme point there, back to the world.  Convex: argmax over the vertices (first
+ * maximum wins; FCL hill-climbs on hulls with >32 vertices, same point except on exact ties). */
+static void shape_support(const shape_t *s, const double *dir_w, double *out_w) {
+  double dir[3], v[3];
+  xf_rot_t(dir, &s->T, dir_w);
+  switch (s->type) {
+    case MPB_GEOM_BOX:
+      v[0] = sign_real(dir[0]) * s->a; v[1] = sign_real(dir[1]) * s->b; v[2] = sign_real(dir[2]) * s->c;
+      break;
+    case MPB_GEOM_SPHERE: {
+      double len = len2_3(dir);
+      if (len - ORC_EPS > 0) { copy3(v, dir); scale3(v, s->a / sqrt(len)); } else { v[0] = v[1] = v[2] = 0; }
+    } break;
+    case MPB_GEOM_CAPSULE: {
+      double n[3]; copy3(n, dir); normalize3(n); scale3(n, s->a);
+      v[0] = n[0]; v[1] = n[1]; v[2] = n[2] + (dir[2] > 0 ? s->b : -s->b);
+    } break;
+    case MPB_GEOM_CYLINDER: {
+      double zdist = sqrt(dir[0] * dir[0] + dir[1] * dir[1]);
+      if (is_zero(zdist)) { v[0] = 0; v[1] = 0; v[2] = sign_real(dir[2]) * s->b; }
+      else { double rad = s->a / zdist; v[0] = rad * dir[0]; v[1] = rad * dir[1]; v[2] = sign_real(dir[2]) * s->b; }
+    } break;
+    case MPB_GEOM_CONVEX: {
+      int best = 0; double bd = dot3(s->verts, dir);
+      for (int i = 1; i < s->nverts; i++) { double t = dot3(s->verts + 3 * i, dir); if (t > bd) { bd = t; best = i; } }
+      copy3(v, s->verts + 3 * best);
+    } break;
+    case ORC_TRI: {
+      int best = 0; double bd = dot3(s->tri, dir);
+      for (int i = 1; i < 3; i++) { double t = dot3(s->tri + 3 * i, dir); if (t > bd) { bd = t; best = i; } }
+      copy3(v, s->tri + 3 * best);
+    } break;
+    default: v[0] = v[1] = v[2] = 0; break;
+  }
+  xf_apply(out_w, &s->T, v);
+}
+/* [upstream] centerShape / centerConvex / centerTriangle */
+static void shape_center(const shape_t *s, double *c) {
+  if (s->type == MPB_GEOM_CONVEX) xf_apply(c, &s->T, s->center_local);
+  else if (s->type == ORC_TRI) {
+    double m[3] = {(s->tri[0] + s->tri[3] + s->tri[6]) / 3, (s->tri[1] + s->tri[4] + s->tri[7]) / 3, (s->tri[2] + s->tri[5] + s->tri[8]) / 3};
+    xf_apply(c, &s->T, m);
+  } else copy3(c, s->T.p);
+}
+/* [upstream libccd support.c] __ccdSupport: v = support1(dir) - support2(-dir) */
+static void mink_support(const shape_t *a, const shape_t *b, const double *dir, double *v) {
+  double p1[3], p2[3], nd[3] = {-dir[0], -dir[1], -dir[2]};
+  shape_support(a, dir, p1);
+  shape_support(b, nd, p2);
+  sub3(v, p1, p2);
+}
+
+/* ------------------------------------------------------------------ MPR  [upstream libccd v2.1 src/mpr.c] */
+typedef struct { double v[4][3]; int size; } portal_t;
+typedef struct { long iters; } orc_counter_t;
+static __thread orc_counter_t g_cnt;
+
+static void portal_dir(const portal_t *p, double *dir) {
+  double v2v1[3], v3v1[3];
+  sub3(v2v1, p->v[2], p->v[1]);
+  sub3(v3v1, p->v[3], p->v[1]);
+  cross3(dir, v2v1, v3v1);
+  normalize3(dir);
+}
+static int portal_encapsules_origin(const portal_t *p, const double *dir) { double d = dot3(dir, p->v[1]); return is_zero(d) || d > 0; }
+static int portal_can_encapsule_origin(const double *v4, const double *dir) { double d = dot3(v4, dir); return is_zero(d) || d > 0; }
+static int portal_reach_tolerance(const portal_t *p, const double *v4, const double *dir, double tol) {
+  double dv1 = dot3(p->v[1], dir), dv2 = dot3(p->v[2], dir), dv3 = dot3(p->v[3], dir), dv4 = dot3(v4, dir);
+  double d1 = dv4 - dv1, d2 = dv4 - dv2, d3 = dv4 - dv3;
+  double m = d1 < d2 ? d1 : d2; m = m < d3 ? m : d3;
+  return eq_real(m, tol) || m < tol;
+}
+static void expand_portal(portal_t *p, const double *v4) {
+  double v4v0[3];
+  cross3(v4v0, v4, p->v[0]);
+  double d = dot3(p->v[1], v4v0);
+  if (d > 0) {
+    d = dot3(p->v[2], v4v0);
+    if (d > 0) copy3(p->v[1], v4); else copy3(p->v[3], v4);
+  } else {
+    d = dot3(p->v[3], v4v0);
+    if (d > 0) copy3(p->v[2], v4); else copy3(p->v[1], v4);
+  }
+}
+/* discoverPortal: -1 no intersection, 0 portal found, 1 origin on v1, 2 origin on v0-v1 segment */
+static int discover_portal(const shape_t *A, const shape_t *B, portal_t *p) {
+  double dir[3], va[3], vb[3], c1[3], c2[3], dot;
+  static const double origin[3] = {0, 0, 0};
+  shape_center(A, c1); shape_center(B, c2);
+  sub3(p->v[0], c1, c2); /* findOrigin */
+  p->size = 1;
+  if (eq3(p->v[0], origin)) p->v[0][0] += ORC_EPS * 10.0;
+  copy3(dir, p->v[0]); scale3(dir, -1.0); normalize3(dir);
+  mink_support(A, B, dir, p->v[1]); g_cnt.iters++;
+  p->size = 2;
+  dot = dot3(p->v[1], dir);
+  if (is_zero(dot) || dot < 0) return -1;
+  cross3(dir, p->v[0], p->v[1]);
+  if (is_zero(len2_3(dir))) return eq3(p->v[1], origin) ? 1 : 2;
+  normalize3(dir);
+  mink_support(A, B, dir, p->v[2]); g_cnt.iters++;
+  dot = dot3(p->v[2], dir);
+  if (is_zero(dot) || dot < 0) return -1;
+  p->size = 3;
+  sub3(va, p->v[1], p->v[0]); sub3(vb, p->v[2], p->v[0]);
+  cross3(dir, va, vb); normalize3(dir);
+  dot = dot3(dir, p->v[0]);
+  if (dot > 0) { double t[3]; copy3(t, p->v[1]); copy3(p->v[1], p->v[2]); copy3(p->v[2], t); scale3(dir, -1.0); }
+  while (p->size < 4) {
+    mink_support(A, B, dir, p->v[3]); g_cnt.iters++;
+    dot = dot3(p->v[3], dir);
+    if (is_zero(dot) || dot < 0) return -1;
+    int cont = 0;
+    cross3(va, p->v[1], p->v[3]);
+    dot = dot3(va, p->v[0]);
+    if (dot < 0 && !is_zero(dot)) { copy3(p->v[2], p->v[3]); cont = 1; }
+    if (!cont) {
+      cross3(va, p->v[3], p->v[2]);
+      dot = dot3(va, p->v[0]);
+      if (dot < 0 && !is_zero(dot)) { copy3(p->v[1], p->v[3]); cont = 1; }
+    }
+    if (cont) {
+      sub3(va, p->v[1], p->v[0]); sub3(vb, p->v[2], p->v[0]);
+      cross3(dir, va, vb); normalize3(dir);
+    } else p->size = 4;
+  }
+  return 0;
+}
+static int refine_portal(const shape_t *A, const shape_t *B, portal_t *p) {
+  double dir[3], v4[3];
+  for (;;) {
+    portal_dir(p, dir);
+    if (portal_encapsules_origin(p, dir)) return 0;
+    mink_support(A, B, dir, v4); g_cnt.iters++;
+    if (!portal_can_encapsule_origin(v4, dir) || portal_reach_tolerance(p, v4, dir, ORC_MPR_TOL)) return -1;
+    expand_portal(p, v4);
+  }
+}
+/* ccdMPRIntersect */
+static int mpr_intersect(const shape_t *A, const shape_t *B) {
+  portal_t p;
+  int res = discover_portal(A, B, &p);
+  if (res < 0) return 0;
+  if (res > 0) return 1;
+  return refine_portal(A, B, &p) == 0 ? 1 : 0;
+}
+
+/* closest point on triangle to origin -> squared distance, witness (libccd ccdVec3PointTriDist2 role) */
+static double point_seg_dist2(const double *P, const double *a, const double *b, double *w) {
+  double d[3], ap[3]; sub3(d, b, a); sub3(ap, P, a);
+  double t = dot3(ap, d), dd = len2_3(d);
+  if (dd <= 0) t = 0; else { t /= dd; if (t < 0) t = 0; if (t > 1) t = 1; }
+  double q[3] = {a[0] + t * d[0], a[1] + t * d[1], a[2] + t * d[2]};
+  if (w) copy3(w, q);
+  double r[3]; sub3(r, P, q); return len2_3(r);
+}
+static double point_tri_dist2(const double *P, const double *a, const double *b, const double *c, double *w) {
+  /* Ericson, Real-Time Collision Detection 5.1.5 */
+  double ab[3], ac[3], ap[3]; sub3(ab, b, a); sub3(ac, c, a); sub3(ap, P, a);
+  double d1 = dot3(ab, ap), d2 = dot3(ac, ap), q[3];
+  if (d1 <= 0 && d2 <= 0) { copy3(q, a); goto done; }
+  { double bp[3]; sub3(bp, P, b);
+    double d3 = dot3(ab, bp), d4 = dot3(ac, bp);
+    if (d3 >= 0 && d4 <= d3) { copy3(q, b); goto done; }
+    double vc = d1 * d4 - d3 * d2;
+    if (vc <= 0 && d1 >= 0 && d3 <= 0) { double v = d1 / (d1 - d3); q[0] = a[0] + v * ab[0]; q[1] = a[1] + v * ab[1]; q[2] = a[2] + v * ab[2]; goto done; }
+    double cp[3]; sub3(cp, P, c);
+    double d5 = dot3(ab, cp), d6 = dot3(ac, cp);
+    if (d6 >= 0 && d5 <= d6) { copy3(q, c); goto done; }
+    double vb = d5 * d2 - d1 * d6;
+    if (vb <= 0 && d2 >= 0 && d6 <= 0) { double w2 = d2 / (d2 - d6); q[0] = a[0] + w2 * ac[0]; q[1] = a[1] + w2 * ac[1]; q[2] = a[2] + w2 * ac[2]; goto done; }
+    double va = d3 * d6 - d5 * d4;
+    if (va <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0) {
+      double w2 = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+      q[0] = b[0] + w2 * (c[0] - b[0]); q[1] = b[1] + w2 * (c[1] - b[1]); q[2] = b[2] + w2 * (c[2] - b[2]); goto done;
+    }
+    double den = 1.0 / (va + vb + vc), v = vb * den, w2 = vc * den;
+    q[0] = a[0] + ab[0] * v + ac[0] * w2; q[1] = a[1] + ab[1] * v + ac[1] * w2; q[2] = a[2] + ab[2] * v + ac[2] * w2;
+  }
+done:
+  if (w) copy3(w, q);
+  { double r[3]; sub3(r, P, q); return len2_3(r); }
+}
+
+/* ccdMPRPenetration depth (findPenetr): distance from the origin to the final portal triangle.
+ * An UPPER bound of the true penetration depth; used only to classify the 1e-4 m contact band. */
+static double mpr_penetration_depth(const shape_t *A, const shape_t *B) {
+  portal_t p;
+  static const double origin[3] = {0, 0, 0};
+  int res = discover_portal(A, B, &p);
+  if (res < 0) return -1.0; /* separated */
+  if (res == 1) return 0.0; /* touching */
+  if (res == 2) { /* findPenetrSegment: depth = |v1| */ return sqrt(len2_3(p.v[1])); }
+  if (refine_portal(A, B, &p) < 0) return -1.0;
+  double dir[3], v4[3];
+  for (long it = 0;; it++) {
+    portal_dir(&p, dir);
+    mink_support(A, B, dir, v4);
+    if (portal_reach_tolerance(&p, v4, dir, ORC_MPR_TOL) || it > ORC_MAX_ITERS)
+      return sqrt(point_tri_dist2(origin, p.v[1], p.v[2], p.v[3], NULL));
+    expand_portal(&p, v4);
+  }
+}
+
+/* ------------------------------------------------------------------ GJK distance
+ * Role of FCL GJKDistance / libccd-style GJK (tolerance 1e-6): returns the separation distance, or -1
+ * when the shapes touch or intersect (enable_signed_distance = false, python/pybind_fcl.hpp:311-315).
+ * Implemented as textbook GJK with closest-point-on-simplex; equal to the upstream result within its
+ * distance tolerance.  Witness points are not produced. */
+static double closest_on_simplex(double S[4][3], int *n, double *cp) {
+  static const double O[3] = {0, 0, 0};
+  if (*n == 1) { copy3(cp, S[0]); return len2_3(cp); }
+  if (*n == 2) {
+    double d2 = point_seg_dist2(O, S[0], S[1], cp);
+    /* reduce */
+    if (eq3(cp, S[0])) { *n = 1; } else if (eq3(cp, S[1])) { copy3(S[0], S[1]); *n = 1; }
+    return d2;
+  }
+  if (*n == 3) {
+    double best = point_tri_dist2(O, S[0], S[1], S[2], cp);
+    /* reduce to the supporting sub-simplex by testing edges/vertices */
+    double w[3]; int keep[3] = {1, 1, 1};
+    for (int e = 0; e < 3; e++) {
+      int a = e, b = (e + 1) % 3, c = (e + 2) % 3;
+      double d2 = point_seg_dist2(O, S[a], S[b], w);
+      if (d2 <= best * (1 + 1e-14) + 1e-300) { keep[c] = 0; (void)c; /* closest lies on edge ab */
+        double T[2][3]; copy3(T[0], S[a]); copy3(T[1], S[b]); copy3(S[0], T[0]); copy3(S[1], T[1]); *n = 2; copy3(cp, w);
+        return closest_on_simplex(S, n, cp);
+      }
+    }
+    (void)keep;
+    return best;
+  }
+  /* tetrahedron: inside test, else closest over the 4 faces */
+  {
+    double best = DBL_MAX, bcp[3] = {0, 0, 0}; int bf = -1;
+    static const int F[4][3] = {{0, 1, 2}, {0, 1, 3}, {0, 2, 3}, {1, 2, 3}};
+    static const int opp[4] = {3, 2, 1, 0};
+    int inside = 1;
+    for (int f = 0; f < 4; f++) {
+      double ab[3], ac[3], nrm[3], ao[3], ad[3];
+      sub3(ab, S[F[f][1]], S[F[f][0]]); sub3(ac, S[F[f][2]], S[F[f][0]]); cross3(nrm, ab, ac);
+      sub3(ad, S[opp[f]], S[F[f][0]]);
+      ao[0] = -S[F[f][0]][0]; ao[1] = -S[F[f][0]][1]; ao[2] = -S[F[f][0]][2];
+      double so = dot3(nrm, ao), sd = dot3(nrm, ad);
+      if (so * sd < 0 || sd == 0) { /* origin on the outer side of this face (or degenerate tetra) */
+        inside = 0;
+        double w[3]; double d2 = point_tri_dist2(O, S[F[f][0]], S[F[f][1]], S[F[f][2]], w);
+        if (d2 < best) { best = d2; copy3(bcp, w); bf = f; }
+      }
+    }
+    if (inside) { cp[0] = cp[1] = cp[2] = 0; return 0.0; }
+    double T[3][3]; copy3(T[0], S[F[bf][0]]); copy3(T[1], S[F[bf][1]]); copy3(T[2], S[F[bf][2]]);
+    copy3(S[0], T[0]); copy3(S[1], T[1]); copy3(S[2], T[2]); *n = 3;
+    copy3(cp, bcp);
+    return closest_on_simplex(S, n, cp);
+  }
+}
+static double gjk_distance(const shape_t *A, const shape_t *B) {
+  double S[4][3]; int n = 0;
+  double c1[3], c2[3], dir[3], cp[3], w[3];
+  shape_center(A, c1); shape_center(B, c2); sub3(dir, c2, c1); /* search towards B */
+  if (len2_3(dir) < 1e-24) { dir[0] = 1; dir[1] = 0; dir[2] = 0; }
+  normalize3(dir);
+  mink_support(A, B, dir, S[0]); n = 1;
+  copy3(cp, S[0]);
+  double d2 = len2_3(cp);
+  for (int it = 0; it < ORC_MAX_ITERS; it++) {
+    if (d2 < 1e-24) return -1.0;
+    double dist = sqrt(d2);
+    dir[0] = -cp[0] / dist; dir[1] = -cp[1] / dist; dir[2] = -cp[2] / dist;
+    mink_support(A, B, dir, w); g_cnt.iters++;
+    /* lower bound from the supporting plane: -w.dir ; converged when gap small */
+    double lb = -dot3(w, dir);
+    if (dist - lb <= 1e-10 * (dist > 1 ? dist : 1.0)) return dist;
+    int dup = 0;
+    for (int i = 0; i < n; i++) if (eq3(S[i], w)) dup = 1;
+    if (dup) return dist;
+    copy3(S[n], w); n++;
+    d2 = closest_on_simplex(S, &n, cp);
+    if (n == 4 && d2 == 0.0) return -1.0;
+  }
+  return sqrt(d2);
+}
+
+/* ------------------------------------------------------------------ closed-form primitives [upstream FCL 0.7.0
+ * narrowphase/detail/primitive_shape_algorithm/{sphere_sphere,sphere_box,sphere_capsule,sphere_cylinder,box_box}-inl.h] */
+static int sphere_sphere(const shape_t *s1, const shape_t *s2) {
+  double d[3]; sub3(d, s2->T.p, s1->T.p);
+  return !(sqrt(len2_3(d)) > s1->a + s2->a);
+}
+static int sphere_box(const shape_t *sp, const shape_t *bx) {
+  double c[3], n[3]; xf_apply_inv(c, &bx->T, sp->T.p);
+  const double h[3] = {bx->a, bx->b, bx->c};
+  int clamped = 0;
+  for (int i = 0; i < 3; i++) { n[i] = c[i]; if (c[i] < -h[i]) { n[i] = -h[i]; clamped = 1; } if (c[i] > h[i]) { n[i] = h[i]; clamped = 1; } }
+  if (!clamped) return 1;
+  double d[3]; sub3(d, c, n);
+  return !(len2_3(d) > sp->a * sp->a);
+}
+static int sphere_capsule(const shape_t *sp, const shape_t *cap) {
+  double c[3]; xf_apply_inv(c, &cap->T, sp->T.p);
+  double a[3] = {0, 0, cap->b}, b[3] = {0, 0, -cap->b}, w[3];
+  double d2 = point_seg_dist2(c, a, b, w);
+  double dist = sqrt(d2) - sp->a - cap->a;
+  return !(dist > 0);
+}
+static int sphere_cylinder(const shape_t *sp, const shape_t *cy) {
+  double c[3], n[3]; xf_apply_inv(c, &cy->T, sp->T.p);
+  int clamped = 0;
+  copy3(n, c);
+  double r2 = c[0] * c[0] + c[1] * c[1];
+  if (r2 > cy->a * cy->a) { double s = cy->a / sqrt(r2); n[0] = c[0] * s; n[1] = c[1] * s; clamped = 1; }
+  if (c[2] > cy->b) { n[2] = cy->b; clamped = 1; } else if (c[2] < -cy->b) { n[2] = -cy->b; clamped = 1; }
+  if (!clamped) return 1;
+  double d[3]; sub3(d, c, n);
+  return !(len2_3(d) > sp->a * sp->a);
+}
+/* boxBox2 as a boolean: 15-axis SAT, separated iff some axis has s > 0 (tested before normalisation) */
+static int box_box(const shape_t *b1, const shape_t *b2) {
+  double R[9], Q[9], p[3], pp[3];
+  sub3(p, b2->T.p, b1->T.p);
+  xf_rot_t(pp, &b1->T, p);
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    double s = 0; for (int k = 0; k < 3; k++) s += b1->T.R[3 * k + i] * b2->T.R[3 * k + j];
+    R[3 * i + j] = s; Q[3 * i + j] = fabs(s);
+  }
+  const double A[3] = {b1->a, b1->b, b1->c}, B[3] = {b2->a, b2->b, b2->c};
+  for (int i = 0; i < 3; i++) { double s2 = fabs(pp[i]) - (A[i] + B[0] * Q[3 * i] + B[1] * Q[3 * i + 1] + B[2] * Q[3 * i + 2]); if (s2 > 0) return 0; }
+  for (int j = 0; j < 3; j++) {
+    double t = R[j] * pp[0] + R[3 + j] * pp[1] + R[6 + j] * pp[2];
+    double s2 = fabs(t) - (B[j] + A[0] * Q[j] + A[1] * Q[3 + j] + A[2] * Q[6 + j]);
+    if (s2 > 0) return 0;
+  }
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    double expr1 = pp[i2] * R[3 * i1 + j] - pp[i1] * R[3 * i2 + j];
+    double expr2 = A[i1] * Q[3 * i2 + j] + A[i2] * Q[3 * i1 + j] + B[j1] * Q[3 * i + j2] + B[j2] * Q[3 * i + j1];
+    if (fabs(expr1) - expr2 > 0) return 0;
+  }
+  return 1;
+}
+
+/* GJKSolver_libccd::shapeIntersect dispatch [upstream]: specialised pairs, everything else -> MPR */
+static int shape_intersect(const shape_t *A, const shape_t *B) {
+  int ta = A->type, tb = B->type;
+  if (ta == MPB_GEOM_SPHERE && tb == MPB_GEOM_SPHERE) return sphere_sphere(A, B);
+  if (ta == MPB_GEOM_SPHERE && tb == MPB_GEOM_BOX) return sphere_box(A, B);
+  if (ta == MPB_GEOM_BOX && tb == MPB_GEOM_SPHERE) return sphere_box(B, A);
+  if (ta == MPB_GEOM_SPHERE && tb == MPB_GEOM_CAPSULE) return sphere_capsule(A, B);
+  if (ta == MPB_GEOM_CAPSULE && tb == MPB_GEOM_SPHERE) return sphere_capsule(B, A);
+  if (ta == MPB_GEOM_SPHERE && tb == MPB_GEOM_CYLINDER) return sphere_cylinder(A, B);
+  if (ta == MPB_GEOM_CYLINDER && tb == MPB_GEOM_SPHERE) return sphere_cylinder(B, A);
+  if (ta == MPB_GEOM_BOX && tb == MPB_GEOM_BOX) return box_box(A, B);
+  return mpr_intersect(A, B);
+}
+
+/* ------------------------------------------------------------------ mesh / octree (exhaustive leaves)
+ * FCL walks an OBBRSS hierarchy / the octree and tests leaves.  The hierarchy only prunes,
+ * so the verdict equals "some leaf intersects"; the oracle tests every leaf behind a conservative
+ * bounding-sphere reject. */
+static double shape_bound_radius(const mpb_scene_desc *d, int o, double *center_local) {
+  center_local[0] = center_local[1] = center_local[2] = 0;
+  const double *p = d->obj_param + 4 * o;
+  switch (d->obj_type[o]) {
+    case MPB_GEOM_SPHERE: return p[0];
+    case MPB_GEOM_BOX: return 0.5 * sqrt(p[0] * p[0] + p[1] * p[1] + p[2] * p[2]);
+    case MPB_GEOM_CAPSULE: return p[0] + 0.5 * p[1];
+    case MPB_GEOM_CYLINDER: return sqrt(p[0] * p[0] + 0.25 * p[1] * p[1]);
+    case MPB_GEOM_CONVEX: {
+      int h = d->obj_geom[o]; int v0 = d->hull_vert_off[h], v1 = d->hull_vert_off[h + 1];
+      double r = 0; for (int i = v0; i < v1; i++) { double l = sqrt(len2_3(d->hull_verts + 3 * i)); if (l > r) r = l; }
+      return r;
+    }
+    default: return 1e30;
+  }
+}
+/* [upstream] shapeTriangleIntersect: sphere-triangle closed form, else MPR with a triangle support */
+static int shape_triangle(const shape_t *S, const double *P0, const double *P1, const double *P2, const xf_t *Ttri) {
+  if (S->type == MPB_GEOM_SPHERE) {
+    double a[3], b[3], c[3]; xf_apply(a, Ttri, P0); xf_apply(b, Ttri, P1); xf_apply(c, Ttri, P2);
+    return !(point_tri_dist2(S->T.p, a, b, c, NULL) > S->a * S->a);
+  }
+  shape_t t; memset(&t, 0, sizeof(t)); t.type = ORC_TRI; t.T = *Ttri;
+  copy3(t.tri, P0); copy3(t.tri + 3, P1); copy3(t.tri + 6, P2);
+  return mpr_intersect(S, &t);
+}
+static int mesh_shape(const mpb_scene_desc *d, int om, const xf_t *Tm, int os, const xf_t *Ts, int mesh_first) {
+  int m = d->obj_geom[om];
+  const double *V = d->mesh_verts + 3 * d->mesh_vert_off[m];
+  const int32_t *Tr = d->mesh_tris + 3 * d->mesh_tri_off[m];
+  int nt = d->mesh_tri_off[m + 1] - d->mesh_tri_off[m];
+  shape_t S; shape_from_object(d, os, Ts, &S);
+  double cl[3]; double rad = shape_bound_radius(d, os, cl);
+  double cw[3]; copy3(cw, Ts->p);
+  (void)mesh_first;
+  for (int t = 0; t < nt; t++) {
+    const double *P0 = V + 3 * Tr[3 * t], *P1 = V + 3 * Tr[3 * t + 1], *P2 = V + 3 * Tr[3 * t + 2];
+    double a[3], b[3], c[3]; xf_apply(a, Tm, P0); xf_apply(b, Tm, P1); xf_apply(c, Tm, P2);
+    if (point_tri_dist2(cw, a, b, c, NULL) > rad * rad) continue;
+    if (shape_triangle(&S, P0, P1, P2, Tm)) return 1;
+  }
+  return 0;
+}
+/* triangle-triangle intersection (role of FCL Intersect::intersect_Triangle): exact segment/triangle
+ * piercing tests both ways plus the coplanar-overlap fallback via MPR on the two triangles. */
+static int seg_tri(const double *p, const double *q, const double *a, const double *b, const double *c) {
+  double ab[3], ac[3], n[3], pq[3], ap[3];
+  sub3(ab, b, a); sub3(ac, c, a); cross3(n, ab, ac); sub3(pq, q, p); sub3(ap, p, a);
+  double dn = dot3(n, pq), t = -dot3(n, ap);
+  if (dn == 0) return 0;
+  t /= dn; if (t < 0 || t > 1) return 0;
+  double x[3] = {p[0] + t * pq[0] - a[0], p[1] + t * pq[1] - a[1], p[2] + t * pq[2] - a[2]};
+  double d00 = dot3(ab, ab), d01 = dot3(ab, ac), d11 = dot3(ac, ac), d20 = dot3(x, ab), d21 = dot3(x, ac);
+  double den = d00 * d11 - d01 * d01; if (den == 0) return 0;
+  double v = (d11 * d20 - d01 * d21) / den, w = (d00 * d21 - d01 * d20) / den;
+  return v >= 0 && w >= 0 && v + w <= 1;
+}
+static int tri_tri(const double *A, const double *B) {
+  for (int e = 0; e < 3; e++) {
+    if (seg_tri(A + 3 * e, A + 3 * ((e + 1) % 3), B, B + 3, B + 6)) return 1;
+    if (seg_tri(B + 3 * e, B + 3 * ((e + 1) % 3), A, A + 3, A + 6)) return 1;
+  }
+  return 0;
+}
+static int mesh_mesh(const mpb_scene_desc *d, int oa, const xf_t *Ta, int ob, const xf_t *Tb) {
+  int ma = d->obj_geom[oa], mb = d->obj_geom[ob];
+  const double *Va = d->mesh_verts + 3 * d->mesh_vert_off[ma], *Vb = d->mesh_verts + 3 * d->mesh_vert_off[mb];
+  const int32_t *Ia = d->mesh_tris + 3 * d->mesh_tri_off[ma], *Ib = d->mesh_tris + 3 * d->mesh_tri_off[mb];
+  int na = d->mesh_tri_off[ma + 1] - d->mesh_tri_off[ma], nb = d->mesh_tri_off[mb + 1] - d->mesh_tri_off[mb];
+  double *WB = (double *)malloc(sizeof(double) * 9 * (size_t)nb);
+  for (int t = 0; t < nb; t++) for (int k = 0; k < 3; k++) xf_apply(WB + 9 * t + 3 * k, Tb, Vb + 3 * Ib[3 * t + k]);
+  int hit = 0;
+  for (int t = 0; t < na && !hit; t++) {
+    double A[9]; for (int k = 0; k < 3; k++) xf_apply(A + 3 * k, Ta, Va + 3 * Ia[3 * t + k]);
+    for (int u = 0; u < nb; u++) if (tri_tri(A, WB + 9 * u)) { hit = 1; break; }
+  }
+  free(WB);
+  return hit;
+}
+/* OcTreeShapeIntersectRecurse leaves [upstream]: Box(res) centred on the voxel vs the shape through
+ * shape_intersect(box, shape); octomap voxel centre = (cell + 0.5) * res (key - 32768 + 0.5). */
+static int octree_shape(const mpb_scene_desc *d, int oo, const xf_t *To, int os, const xf_t *Ts) {
+  int t = d->obj_geom[oo];
+  double res = d->oct_res[t];
+  const int32_t *C = d->oct_cells + 3 * d->oct_cell_off[t];
+  int nc = d->oct_cell_off[t + 1] - d->oct_cell_off[t];
+  shape_t S; shape_from_object(d, os, Ts, &S);
+  double cl[3]; double rad = shape_bound_radius(d, os, cl);
+  double cs[3]; xf_apply_inv(cs, To, Ts->p); /* shape origin in the octree frame */
+  double reach = rad + 0.5 * res * sqrt(3.0);
+  shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+  for (int i = 0; i < nc; i++) {
+    double c[3] = {(C[3 * i] + 0.5) * res, (C[3 * i + 1] + 0.5) * res, (C[3 * i + 2] + 0.5) * res};
+    double dd[3]; sub3(dd, c, cs);
+    if (len2_3(dd) > reach * reach) continue;
+    bx.T = *To; xf_apply(bx.T.p, To, c);
+    if (shape_intersect(&bx, &S)) return 1;
+  }
+  return 0;
+}
+static int octree_mesh(const mpb_scene_desc *d, int oo, const xf_t *To, int om, const xf_t *Tm) {
+  int t = d->obj_geom[oo]; double res = d->oct_res[t];
+  const int32_t *C = d->oct_cells + 3 * d->oct_cell_off[t];
+  int nc = d->oct_cell_off[t + 1] - d->oct_cell_off[t];
+  int m = d->obj_geom[om];
+  const double *V = d->mesh_verts + 3 * d->mesh_vert_off[m];
+  const int32_t *Tr = d->mesh_tris + 3 * d->mesh_tri_off[m];
+  int nt = d->mesh_tri_off[m + 1] - d->mesh_tri_off[m];
+  shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+  double reach = 0.5 * res * sqrt(3.0);
+  for (int u = 0; u < nt; u++) {
+    const double *P0 = V + 3 * Tr[3 * u], *P1 = V + 3 * Tr[3 * u + 1], *P2 = V + 3 * Tr[3 * u + 2];
+    double a[3], b[3], c[3]; xf_apply(a, Tm, P0); xf_apply(b, Tm, P1); xf_apply(c, Tm, P2);
+    double al[3], bl[3], cl2[3]; xf_apply_inv(al, To, a); xf_apply_inv(bl, To, b); xf_apply_inv(cl2, To, c);
+    for (int i = 0; i < nc; i++) {
+      double cc[3] = {(C[3 * i] + 0.5) * res, (C[3 * i + 1] + 0.5) * res, (C[3 * i + 2] + 0.5) * res};
+      if (point_tri_dist2(cc, al, bl, cl2, NULL) > reach * reach) continue;
+      bx.T = *To; xf_apply(bx.T.p, To, cc);
+      if (shape_triangle(&bx, P0, P1, P2, Tm)) return 1;
+    }
+  }
+  return 0;
+}
+
+/* ::fcl::collide(o1, o2) as a boolean for the geometry types on the hot path */
+static int object_collide(const mpb_scene_desc *d, int a, const xf_t *Ta, int b, const xf_t *Tb) {
+  int ta = d->obj_type[a], tb = d->obj_type[b];
+  if (ta == MPB_GEOM_OCTREE && tb == MPB_GEOM_OCTREE) return 0; /* not produced by the path */
+  if (ta == MPB_GEOM_OCTREE) return tb == MPB_GEOM_MESH ? octree_mesh(d, a, Ta, b, Tb) : octree_shape(d, a, Ta, b, Tb);
+  if (tb == MPB_GEOM_OCTREE) return ta == MPB_GEOM_MESH ? octree_mesh(d, b, Tb, a, Ta) : octree_shape(d, b, Tb, a, Ta);
+  if (ta == MPB_GEOM_MESH && tb == MPB_GEOM_MESH) return mesh_mesh(d, a, Ta, b, Tb);
+  if (ta == MPB_GEOM_MESH) return mesh_shape(d, a, Ta, b, Tb, 1);
+  if (tb == MPB_GEOM_MESH) return mesh_shape(d, b, Tb, a, Ta, 0);
+  shape_t A, B; shape_from_object(d, a, Ta, &A); shape_from_object(d, b, Tb, &B);
+  return shape_intersect(&A, &B);
+}
+
+/* ------------------------------------------------------------------ exported API */
+/* FK of a batch: link poses [n][n_links][7] (getLinkPose for every link). */
+int orc_fk_batch(const mpb_scene_desc *d, const double *states, int64_t n, double *poses) {
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  for (int64_t i = 0; i < n; i++) {
+    scatter_state(d, states + i * d->state_dim, qf);
+    fk_joints(d, qf, oMi);
+    for (int l = 0; l < d->n_links; l++) link_pose7(d, oMi, l, poses + (i * d->n_links + l) * 7);
+  }
+  free(oMi); free(qf);
+  return 0;
+}
+
+/* Object world transforms [n][n_objects][12] after setQposAll (for tests). */
+int orc_object_poses(const mpb_scene_desc *d, const double *states, int64_t n, double *out12) {
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
+  double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  for (int64_t i = 0; i < n; i++) {
+    scatter_state(d, states + i * d->state_dim, qf);
+    fk_joints(d, qf, oMi);
+    object_transforms(d, oMi, objT, NULL);
+    for (int o = 0; o < d->n_objects; o++) {
+      double *m = out12 + (i * d->n_objects + o) * 12;
+      for (int r = 0; r < 3; r++) { m[4 * r] = objT[o].R[3 * r]; m[4 * r + 1] = objT[o].R[3 * r + 1]; m[4 * r + 2] = objT[o].R[3 * r + 2]; m[4 * r + 3] = objT[o].p[r]; }
+    }
+  }
+  free(oMi); free(objT); free(qf);
+  return 0;
+}
+
+/* ValidityCheckerTpl::isValid for a batch (src/ompl_planner.h:59-62): per state, every admitted pair
+ * is tested (no early exit, src/planning_world.h:248-250).  pair_hit: [n][n_pairs] bytes (nullable),
+ * verdict: [n] bytes (nullable).  Returns total support evaluations through *iters (nullable). */
+int orc_collide_batch(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters) {
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
+  double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  g_cnt.iters = 0;
+  for (int64_t i = 0; i < n; i++) {
+    scatter_state(d, states + i * d->state_dim, qf);
+    fk_joints(d, qf, oMi);
+    object_transforms(d, oMi, objT, NULL);
+    int any = 0;
+    for (int p = 0; p < d->n_pairs; p++) {
+      int a = d->pair_a[p], b = d->pair_b[p];
+      int hit = object_collide(d, a, &objT[a], b, &objT[b]);
+      if (pair_hit) pair_hit[i * d->n_pairs + p] = (uint8_t)hit;
+      any |= hit;
+    }
+    if (verdict) verdict[i] = (uint8_t)any;
+  }
+  if (iters) *iters = g_cnt.iters;
+  free(oMi); free(objT); free(qf);
+  return 0;
+}
+
+/* Band classifier for one (state, pair): signed distance estimate.  > 0: GJK separation distance;
+ * < 0: -(MPR penetration depth) (an upper bound of the true depth => |value| >= true depth);
+ * mesh/octree pairs return NaN (callers treat those with the exhaustive-leaf margin test). */
+int orc_pair_signed_distance(const mpb_scene_desc *d, const double *state, int pair, double *out) {
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
+  double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  scatter_state(d, state, qf); fk_joints(d, qf, oMi); object_transforms(d, oMi, objT, NULL);
+  int a = d->pair_a[pair], b = d->pair_b[pair];
+  int ta = d->obj_type[a], tb = d->obj_type[b];
+  if (ta >= MPB_GEOM_MESH || tb >= MPB_GEOM_MESH) { *out = NAN; }
+  else {
+    shape_t A, B; shape_from_object(d, a, &objT[a], &A); shape_from_object(d, b, &objT[b], &B);
+    double g = gjk_distance(&A, &B);
+    if (g > 0) *out = g;
+    else { double pd = mpr_penetration_depth(&A, &B); *out = pd < 0 ? 0.0 : -pd; }
+  }
+  free(oMi); free(objT); free(qf);
+  return 0;
+}
+
+/* min over admitted pairs of ::fcl::distance (distanceFull, src/planning_world.cpp:714-720) for
+ * shape/shape pairs; -1 for touching/penetrating pairs as FCL returns with signed distance disabled. */
+int orc_distance_batch(const mpb_scene_desc *d, const double *states, int64_t n, double *min_dist, int32_t *argmin_pair) {
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
+  double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  int rc = 0;
+  for (int64_t i = 0; i < n; i++) {
+    scatter_state(d, states + i * d->state_dim, qf); fk_joints(d, qf, oMi); object_transforms(d, oMi, objT, NULL);
+    double best = DBL_MAX; int bi = -1; /* WorldDistanceResult::min_distance starts at max (src/planning_world.h:30-41) */
+    for (int p = 0; p < d->n_pairs; p++) {
+      int a = d->pair_a[p], b = d->pair_b[p];
+      if (d->obj_type[a] >= MPB_GEOM_MESH || d->obj_type[b] >= MPB_GEOM_MESH) { rc = MPB_ERR_UNSUPPORTED; continue; }
+      shape_t A, B; shape_from_object(d, a, &objT[a], &A); shape_from_object(d, b, &objT[b], &B);
+      double g = gjk_distance(&A, &B);
+      if (g < best) { best = g; bi = p; }
+    }
+    min_dist[i] = best; if (argmin_pair) argmin_pair[i] = bi;
+  }
+  free(oMi); free(objT); free(qf);
+  return rc;
+}
+
+/* ------------------------------------------------------------------ independent exact check: SAT on polytopes
+ * Signed separation of two convex polytopes (vertices + triangle faces) in world poses: the maximum over
+ * all candidate axes (face normals of A, of B, edge x edge) of the projection gap.  > 0 => separated by at
+ * least that much (a lower bound of the distance), < 0 => exact penetration depth.  Shares no code path
+ * with MPR/GJK above. */
+static void project_hull(const double *W, int nv, const double *ax, double *lo, double *hi) {
+  double l = DBL_MAX, h = -DBL_MAX;
+  for (int i = 0; i < nv; i++) { double t = dot3(W + 3 * i, ax); if (t < l) l = t; if (t > h) h = t; }
+  *lo = l; *hi = h;
+}
+static double sat_axis_gap(const double *WA, int na, const double *WB, int nb, double *ax) {
+  double l2 = len2_3(ax);
+  if (l2 < 1e-24) return -DBL_MAX;
+  scale3(ax, 1.0 / sqrt(l2));
+  double la, ha, lb, hb; project_hull(WA, na, ax, &la, &ha); project_hull(WB, nb, ax, &lb, &hb);
+  double g1 = lb - ha, g2 = la - hb;
+  return g1 > g2 ? g1 : g2;
+}
+int orc_sat_pair(const mpb_scene_desc *d, const double *state, int pair, double *gap_out) {
+  int a = d->pair_a[pair], b = d->pair_b[pair];
+  if (d->obj_type[a] != MPB_GEOM_CONVEX || d->obj_type[b] != MPB_GEOM_CONVEX) return MPB_ERR_UNSUPPORTED;
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)d->n_objects);
+  double *qf = (double *)malloc(sizeof(double) * (size_t)d->nq_full);
+  scatter_state(d, state, qf); fk_joints(d, qf, oMi); object_transforms(d, oMi, objT, NULL);
+  int ha = d->obj_geom[a], hb = d->obj_geom[b];
+  int na = d->hull_vert_off[ha + 1] - d->hull_vert_off[ha], nb = d->hull_vert_off[hb + 1] - d->hull_vert_off[hb];
+  int fa = d->hull_face_off[ha + 1] - d->hull_face_off[ha], fb = d->hull_face_off[hb + 1] - d->hull_face_off[hb];
+  const double *VA = d->hull_verts + 3 * d->hull_vert_off[ha], *VB = d->hull_verts + 3 * d->hull_vert_off[hb];
+  const int32_t *FA = d->hull_faces + 3 * d->hull_face_off[ha], *FB = d->hull_faces + 3 * d->hull_face_off[hb];
+  double *WA = (double *)malloc(sizeof(double) * 3 * (size_t)na), *WB = (double *)malloc(sizeof(double) * 3 * (size_t)nb);
+  for (int i = 0; i < na; i++) xf_apply(WA + 3 * i, &objT[a], VA + 3 * i);
+  for (int i = 0; i < nb; i++) xf_apply(WB + 3 * i, &objT[b], VB + 3 * i);
+  double best = -DBL_MAX;
+  for (int f = 0; f < fa; f++) {
+    double e1[3], e2[3], ax[3]; sub3(e1, WA + 3 * FA[3 * f + 1], WA + 3 * FA[3 * f]); sub3(e2, WA + 3 * FA[3 * f + 2], WA + 3 * FA[3 * f]);
+    cross3(ax, e1, e2); double g = sat_axis_gap(WA, na, WB, nb, ax); if (g > best) best = g;
+  }
+  for (int f = 0; f < fb; f++) {
+    double e1[3], e2[3], ax[3]; sub3(e1, WB + 3 * FB[3 * f + 1], WB + 3 * FB[3 * f]); sub3(e2, WB + 3 * FB[3 * f + 2], WB + 3 * FB[3 * f]);
+    cross3(ax, e1, e2); double g = sat_axis_gap(WA, na, WB, nb, ax); if (g > best) best = g;
+  }
+  for (int f = 0; f < fa; f++) for (int e = 0; e < 3; e++) {
+    int i0 = FA[3 * f + e], i1 = FA[3 * f + (e + 1) % 3];
+    if (i0 > i1) continue; /* each undirected edge once */
+    double ea[3]; sub3(ea, WA + 3 * i1, WA + 3 * i0);
+    for (int g2 = 0; g2 < fb; g2++) for (int e2 = 0; e2 < 3; e2++) {
+      int j0 = FB[3 * g2 + e2], j1 = FB[3 * g2 + (e2 + 1) % 3];
+      if (j0 > j1) continue;
+      double eb[3], ax[3]; sub3(eb, WB + 3 * j1, WB + 3 * j0); cross3(ax, ea, eb);
+      double g = sat_axis_gap(WA, na, WB, nb, ax); if (g > best) best = g;
+    }
+  }
+  *gap_out = best;
+  free(WA); free(WB); free(oMi); free(objT); free(qf);
+  return 0;
+}
+
+/* Standalone narrowphase on two primitive/convex objects given world poses [12] each (tests). */
+int orc_object_collide(const mpb_scene_desc *d, int a, const double *Ta12, int b, const double *Tb12) {
+  xf_t Ta, Tb; xf_from12(&Ta, Ta12); xf_from12(&Tb, Tb12);
+  return object_collide(d, a, &Ta, b, &Tb);
+}
+double orc_object_distance(const mpb_scene_desc *d, int a, const double *Ta12, int b, const double *Tb12) {
+  xf_t Ta, Tb; xf_from12(&Ta, Ta12); xf_from12(&Tb, Tb12);
+  shape_t A, B; shape_from_object(d, a, &Ta, &A); shape_from_object(d, b, &Tb, &B);
+  return gjk_distance(&A, &B);
+}
