@@ -1,0 +1,599 @@
+// mpb.cu -- host side of libmpb.so: scene image compiler (double -> fp32 device tables, bounding
+// volumes, bin classes), work-queue management, and the extern "C" entry points of include/mpb.h.
+// There is no CPU compute path here: every batch entry point launches the sm_100a kernels of
+// mpb_kernels.cuh or fails with MPB_ERR_CUDA.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "mpb_kernels.cuh"
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                                      \
+  do {                                                                                                \
+    cudaError_t e_ = (call);                                                                          \
+    if (e_ != cudaSuccess)                                                                            \
+      return fail(MPB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                  \
+  } while (0)
+
+struct mpb_scene {
+  int device = 0;
+  int num_sms = 0;
+  cudaStream_t stream = nullptr;
+  // host copies (double) kept for set_q_base / set_pairs
+  std::vector<DevJoint> h_joints;
+  std::vector<DevObject> h_objs;
+  std::vector<DevPair> h_pairs;
+  std::vector<int> joint_qidx;
+  std::vector<int> obj_key;
+  int nq_full = 0;
+  // device image
+  DevJoint *d_joints = nullptr;
+  DevObject *d_objs = nullptr;
+  DevPair *d_pairs = nullptr;
+  float4 *d_verts = nullptr;
+  float *d_linkL = nullptr;
+  int *d_linkJoint = nullptr;
+  SceneImg img{};
+  size_t pairs_cap = 0;
+  // work buffers
+  long long chunk = 0;
+  WorkQ wq{};
+  float *d_q = nullptr;
+  unsigned int *d_verdict = nullptr;
+  unsigned int *d_pairbits = nullptr;
+  float *d_poses = nullptr;
+  size_t d_q_cap = 0, d_verdict_cap = 0, d_pairbits_cap = 0, d_poses_cap = 0, bins_cap = 0;
+  bool smem_verts = true;
+  int narrow_blocks = 0;
+  std::vector<cudaEvent_t> events;
+};
+
+extern "C" const char *mpb_last_error(void) { return g_err.c_str(); }
+
+extern "C" int mpb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// ------------------------------------------------------------------------------------------ host geometry helpers
+static void mul12(const double *a, const double *b, double *o) {  // 3x4 * 3x4 (implicit last row)
+  double t[12];
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 3; c++) t[4 * r + c] = a[4 * r] * b[c] + a[4 * r + 1] * b[4 + c] + a[4 * r + 2] * b[8 + c];
+    t[4 * r + 3] = a[4 * r] * b[3] + a[4 * r + 1] * b[7] + a[4 * r + 2] * b[11] + a[4 * r + 3];
+  }
+  memcpy(o, t, sizeof(t));
+}
+
+// Jacobi eigen-decomposition of a symmetric 3x3; columns of V are eigenvectors.
+static void jacobi3(double A[3][3], double V[3][3]) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) V[i][j] = i == j;
+  for (int sweep = 0; sweep < 32; sweep++) {
+    double off = fabs(A[0][1]) + fabs(A[0][2]) + fabs(A[1][2]);
+    if (off < 1e-18) break;
+    for (int p = 0; p < 2; p++)
+      for (int q = p + 1; q < 3; q++) {
+        if (fabs(A[p][q]) < 1e-300) continue;
+        double th = (A[q][q] - A[p][p]) / (2 * A[p][q]);
+        double t = (th >= 0 ? 1.0 : -1.0) / (fabs(th) + sqrt(th * th + 1));
+        double c = 1 / sqrt(t * t + 1), s = t * c;
+        for (int k = 0; k < 3; k++) {
+          double akp = A[k][p], akq = A[k][q];
+          A[k][p] = c * akp - s * akq;
+          A[k][q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < 3; k++) {
+          double apk = A[p][k], aqk = A[q][k];
+          A[p][k] = c * apk - s * aqk;
+          A[q][k] = s * apk + c * aqk;
+        }
+        for (int k = 0; k < 3; k++) {
+          double vkp = V[k][p], vkq = V[k][q];
+          V[k][p] = c * vkp - s * vkq;
+          V[k][q] = s * vkp + c * vkq;
+        }
+      }
+  }
+}
+
+static void fit_box(const double *v, int n, const double R[3][3], double *c, double *h) {
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (int i = 0; i < n; i++)
+    for (int a = 0; a < 3; a++) {
+      double t = v[3 * i] * R[0][a] + v[3 * i + 1] * R[1][a] + v[3 * i + 2] * R[2][a];
+      lo[a] = std::min(lo[a], t);
+      hi[a] = std::max(hi[a], t);
+    }
+  double m[3];
+  for (int a = 0; a < 3; a++) {
+    m[a] = 0.5 * (lo[a] + hi[a]);
+    h[a] = 0.5 * (hi[a] - lo[a]);
+  }
+  for (int r = 0; r < 3; r++) c[r] = R[r][0] * m[0] + R[r][1] * m[1] + R[r][2] * m[2];
+}
+
+// bounding sphere + OBB of a vertex cloud (object frame)
+static void bound_points(const double *v, int n, DevObject &O) {
+  double mean[3] = {0, 0, 0};
+  for (int i = 0; i < n; i++)
+    for (int a = 0; a < 3; a++) mean[a] += v[3 * i + a];
+  for (int a = 0; a < 3; a++) mean[a] /= std::max(n, 1);
+  double C[3][3] = {{0}};
+  for (int i = 0; i < n; i++) {
+    double d[3] = {v[3 * i] - mean[0], v[3 * i + 1] - mean[1], v[3 * i + 2] - mean[2]};
+    for (int a = 0; a < 3; a++)
+      for (int b = 0; b < 3; b++) C[a][b] += d[a] * d[b];
+  }
+  double V[3][3];
+  jacobi3(C, V);
+  // make V a proper rotation
+  double det = V[0][0] * (V[1][1] * V[2][2] - V[1][2] * V[2][1]) - V[0][1] * (V[1][0] * V[2][2] - V[1][2] * V[2][0]) +
+               V[0][2] * (V[1][0] * V[2][1] - V[1][1] * V[2][0]);
+  if (det < 0)
+    for (int r = 0; r < 3; r++) V[r][2] = -V[r][2];
+  const double I[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  double c1[3], h1[3], c2[3], h2[3];
+  fit_box(v, n, V, c1, h1);
+  fit_box(v, n, I, c2, h2);
+  const bool use_pca = h1[0] * h1[1] * h1[2] <= h2[0] * h2[1] * h2[2];
+  const double(*R)[3] = use_pca ? V : I;
+  const double *c = use_pca ? c1 : c2, *h = use_pca ? h1 : h2;
+  const double pad = 1e-6;  // fp32 rounding of the stored box
+  for (int a = 0; a < 3; a++) {
+    O.oc[a] = (float)c[a];
+    O.oh[a] = (float)(h[a] + pad);
+    for (int b = 0; b < 3; b++) O.oR[3 * a + b] = (float)R[a][b];
+  }
+  // bounding sphere around the box centre
+  double r2 = 0;
+  for (int i = 0; i < n; i++) {
+    double d[3] = {v[3 * i] - c[0], v[3 * i + 1] - c[1], v[3 * i + 2] - c[2]};
+    r2 = std::max(r2, d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+  }
+  for (int a = 0; a < 3; a++) O.bc[a] = (float)c[a];
+  O.br = (float)(sqrt(r2) + pad);
+}
+
+static void bound_box(double hx, double hy, double hz, DevObject &O) {
+  const double pad = 1e-6;
+  for (int a = 0; a < 3; a++) O.oc[a] = O.bc[a] = 0.f;
+  O.oh[0] = (float)(hx + pad);
+  O.oh[1] = (float)(hy + pad);
+  O.oh[2] = (float)(hz + pad);
+  for (int a = 0; a < 9; a++) O.oR[a] = (a % 4 == 0) ? 1.f : 0.f;
+  O.br = (float)(sqrt(hx * hx + hy * hy + hz * hz) + pad);
+}
+
+static int geom_key(int type, int geom) { return type == MPB_GEOM_CONVEX ? 16 + geom : type; }
+
+static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32_t *pb) {
+  const int no = (int)s->h_objs.size();
+  std::map<std::pair<int, int>, int> bins;
+  s->h_pairs.resize(n_pairs);
+  for (int p = 0; p < n_pairs; p++) {
+    int a = pa[p], b = pb[p];
+    if (a < 0 || a >= no || b < 0 || b >= no) return fail(MPB_ERR_INVALID, "pair index out of range");
+    int ta = s->h_objs[a].type, tb = s->h_objs[b].type;
+    if (ta >= MPB_GEOM_MESH || tb >= MPB_GEOM_MESH)
+      return fail(MPB_ERR_UNSUPPORTED, "mesh / octree pairs are not supported by this build yet");
+    auto key = std::make_pair(s->obj_key[a], s->obj_key[b]);
+    auto it = bins.find(key);
+    int bin = it == bins.end() ? (bins[key] = (int)bins.size()) : it->second;
+    s->h_pairs[p] = DevPair{a, b, bin, 0};
+  }
+  s->img.n_pairs = n_pairs;
+  s->img.n_bins = (int)bins.size();
+  s->img.pair_words = (n_pairs + 31) / 32;
+  return MPB_OK;
+}
+
+static int upload_pairs(mpb_scene *s) {
+  const size_t n = s->h_pairs.size();
+  if (n > s->pairs_cap) {
+    if (s->d_pairs) cudaFree(s->d_pairs);
+    s->pairs_cap = std::max<size_t>(n, 64);
+    CU(cudaMalloc(&s->d_pairs, s->pairs_cap * sizeof(DevPair)));
+  }
+  if (n) CU(cudaMemcpy(s->d_pairs, s->h_pairs.data(), n * sizeof(DevPair), cudaMemcpyHostToDevice));
+  s->img.pairs = s->d_pairs;
+  s->chunk = 0;  // queue sizing depends on the pair count
+  return MPB_OK;
+}
+
+extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene **out) {
+  if (!d || !out) return fail(MPB_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (d->n_joints > MPB_MAX_JOINTS) return fail(MPB_ERR_CAPACITY, "too many movable joints (MPB_MAX_JOINTS)");
+  if (d->n_joints < 0 || d->n_objects < 0 || d->n_pairs < 0 || d->state_dim < 0 || d->n_links < 0)
+    return fail(MPB_ERR_INVALID, "negative count in scene description");
+  int ndev = mpb_device_count();
+  if (ndev == 0) return fail(MPB_ERR_CUDA, "no CUDA device visible: libmpb has no CPU path");
+  if (device < 0 || device >= ndev) return fail(MPB_ERR_INVALID, "device index out of range");
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  mpb_scene *s = new mpb_scene();
+  s->device = device;
+  s->num_sms = prop.multiProcessorCount;
+  s->nq_full = d->nq_full;
+
+  // joints
+  std::vector<int> slot_of_q(std::max(d->nq_full, 1), -1);
+  for (int k = 0; k < d->state_dim; k++) {
+    int qi = d->state_map[k];
+    if (qi < 0 || qi >= d->nq_full) { delete s; return fail(MPB_ERR_INVALID, "state_map entry out of range"); }
+    slot_of_q[qi] = k;
+  }
+  s->h_joints.resize(d->n_joints);
+  s->joint_qidx.assign(d->joint_qidx, d->joint_qidx + d->n_joints);
+  for (int j = 0; j < d->n_joints; j++) {
+    DevJoint &J = s->h_joints[j];
+    for (int k = 0; k < 12; k++) J.P[k] = (float)d->joint_placement[12 * j + k];
+    for (int k = 0; k < 3; k++) J.ax[k] = (float)d->joint_axis[3 * j + k];
+    J.type = d->joint_type[j];
+    J.parent = d->joint_parent[j];
+    if (J.parent < 0 || J.parent > j) { delete s; return fail(MPB_ERR_INVALID, "joint table is not topologically ordered"); }
+    int qi = d->joint_qidx[j];
+    if (qi < 0 || qi >= d->nq_full) { delete s; return fail(MPB_ERR_INVALID, "joint_qidx out of range"); }
+    J.slot = slot_of_q[qi];
+    J.qconst = (float)d->q_base[qi];
+    J.pad = 0;
+  }
+  // objects
+  s->h_objs.resize(d->n_objects);
+  s->obj_key.resize(d->n_objects);
+  int ndyn = 0;
+  std::vector<float4> verts;
+  std::vector<int> hull_off(d->n_hulls + 1, 0);
+  for (int h = 0; h < d->n_hulls; h++) {
+    hull_off[h] = (int)verts.size();
+    for (int i = d->hull_vert_off[h]; i < d->hull_vert_off[h + 1]; i++)
+      verts.push_back(make_float4((float)d->hull_verts[3 * i], (float)d->hull_verts[3 * i + 1], (float)d->hull_verts[3 * i + 2], 0.f));
+  }
+  hull_off[d->n_hulls] = (int)verts.size();
+  for (int o = 0; o < d->n_objects; o++) {
+    DevObject &O = s->h_objs[o];
+    memset(&O, 0, sizeof(O));
+    O.type = d->obj_type[o];
+    O.geom = d->obj_geom[o];
+    double L[12];
+    int link = d->obj_link[o];
+    if (link >= d->n_links) { delete s; return fail(MPB_ERR_INVALID, "obj_link out of range"); }
+    if (link >= 0) {
+      mul12(d->link_placement + 12 * link, d->obj_local + 12 * o, L);
+      O.joint = d->link_joint[link];
+    } else {
+      memcpy(L, d->obj_local + 12 * o, sizeof(L));
+      O.joint = 0;
+    }
+    for (int k = 0; k < 12; k++) O.L[k] = (float)L[k];
+    O.dyn = O.joint > 0 ? ndyn++ : -1;
+    const double *p = d->obj_param + 4 * o;
+    switch (O.type) {
+      case MPB_GEOM_SPHERE:
+        O.prm[0] = (float)p[0];
+        bound_box(p[0], p[0], p[0], O);
+        O.br = (float)(p[0] + 1e-6);
+        break;
+      case MPB_GEOM_BOX:
+        O.prm[0] = (float)(0.5 * p[0]); O.prm[1] = (float)(0.5 * p[1]); O.prm[2] = (float)(0.5 * p[2]);
+        bound_box(0.5 * p[0], 0.5 * p[1], 0.5 * p[2], O);
+        break;
+      case MPB_GEOM_CAPSULE:
+        O.prm[0] = (float)p[0]; O.prm[1] = (float)(0.5 * p[1]);
+        bound_box(p[0], p[0], 0.5 * p[1] + p[0], O);
+        O.br = (float)(p[0] + 0.5 * p[1] + 1e-6);
+        break;
+      case MPB_GEOM_CYLINDER:
+        O.prm[0] = (float)p[0]; O.prm[1] = (float)(0.5 * p[1]);
+        bound_box(p[0], p[0], 0.5 * p[1], O);
+        break;
+      case MPB_GEOM_CONVEX: {
+        int h = O.geom;
+        if (h < 0 || h >= d->n_hulls) { delete s; return fail(MPB_ERR_INVALID, "obj_geom (hull) out of range"); }
+        int v0 = d->hull_vert_off[h], nv = d->hull_vert_off[h + 1] - v0;
+        if (nv <= 0) { delete s; return fail(MPB_ERR_INVALID, "empty convex hull"); }
+        O.voff = hull_off[h];
+        O.vcnt = nv;
+        bound_points(d->hull_verts + 3 * v0, nv, O);
+        double c[3] = {0, 0, 0};
+        for (int i = 0; i < nv; i++)
+          for (int a = 0; a < 3; a++) c[a] += d->hull_verts[3 * (v0 + i) + a];
+        for (int a = 0; a < 3; a++) O.ctr[a] = (float)(c[a] / nv);
+      } break;
+      case MPB_GEOM_MESH:
+      case MPB_GEOM_OCTREE:
+        bound_box(1e3, 1e3, 1e3, O);
+        break;
+      default:
+        delete s;
+        return fail(MPB_ERR_INVALID, "unknown geometry type");
+    }
+    s->obj_key[o] = geom_key(O.type, O.geom);
+  }
+  if (ndyn > MPB_MAX_DYN) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (MPB_MAX_DYN)"); }
+
+  s->img.n_joints = d->n_joints;
+  s->img.n_objects = d->n_objects;
+  s->img.n_links = d->n_links;
+  s->img.n_verts = (int)verts.size();
+  s->img.state_dim = d->state_dim;
+  int rc = build_pairs(s, d->n_pairs, d->pair_a, d->pair_b);
+  if (rc != MPB_OK) { delete s; return rc; }
+
+  // upload
+  CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  auto up = [&](void **dst, const void *src, size_t bytes) -> cudaError_t {
+    cudaError_t e = cudaMalloc(dst, std::max<size_t>(bytes, 16));
+    if (e != cudaSuccess) return e;
+    return bytes ? cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice) : cudaSuccess;
+  };
+  CU(up((void **)&s->d_joints, s->h_joints.data(), s->h_joints.size() * sizeof(DevJoint)));
+  CU(up((void **)&s->d_objs, s->h_objs.data(), s->h_objs.size() * sizeof(DevObject)));
+  CU(up((void **)&s->d_verts, verts.data(), verts.size() * sizeof(float4)));
+  std::vector<float> linkL((size_t)d->n_links * 12);
+  for (size_t k = 0; k < linkL.size(); k++) linkL[k] = (float)d->link_placement[k];
+  CU(up((void **)&s->d_linkL, linkL.data(), linkL.size() * sizeof(float)));
+  CU(up((void **)&s->d_linkJoint, d->link_joint, (size_t)d->n_links * sizeof(int)));
+  s->img.joints = s->d_joints;
+  s->img.objs = s->d_objs;
+  s->img.verts = s->d_verts;
+  s->img.linkL = s->d_linkL;
+  s->img.linkJoint = s->d_linkJoint;
+  rc = upload_pairs(s);
+  if (rc != MPB_OK) { mpb_scene_destroy(s); return rc; }
+
+  // narrowphase launch shape: hull pool in shared memory when it fits
+  const size_t vbytes = verts.size() * sizeof(float4);
+  s->smem_verts = vbytes <= 200 * 1024;
+  int per_sm = 0;
+  if (s->smem_verts) {
+    CU(cudaFuncSetAttribute(narrow_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vbytes, 16)));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<true>, 256, vbytes));
+  } else {
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<false>, 256, 0));
+  }
+  s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
+  *out = s;
+  return MPB_OK;
+}
+
+extern "C" void mpb_scene_destroy(mpb_scene *s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  if (s->stream) cudaStreamSynchronize(s->stream);
+  void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q, s->d_verdict,
+                  s->d_pairbits, s->d_poses, s->wq.itf, s->wq.icfg, s->wq.ipair, s->wq.bin_count, s->wq.totals, s->wq.counters};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  for (auto e : s->events) cudaEventDestroy(e);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+}
+
+extern "C" int mpb_scene_info(const mpb_scene *s, int32_t *n_pairs, int32_t *state_dim, int32_t *n_links, int32_t *n_objects,
+                              int32_t *device) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n_pairs) *n_pairs = s->img.n_pairs;
+  if (state_dim) *state_dim = s->img.state_dim;
+  if (n_links) *n_links = s->img.n_links;
+  if (n_objects) *n_objects = s->img.n_objects;
+  if (device) *device = s->device;
+  return MPB_OK;
+}
+
+extern "C" int mpb_scene_set_q_base(mpb_scene *s, const double *q_base, int32_t nq_full) {
+  if (!s || !q_base) return fail(MPB_ERR_INVALID, "null argument");
+  if (nq_full != s->nq_full) return fail(MPB_ERR_INVALID, "q_base length does not match the scene");
+  CU(cudaSetDevice(s->device));
+  for (size_t j = 0; j < s->h_joints.size(); j++) s->h_joints[j].qconst = (float)q_base[s->joint_qidx[j]];
+  CU(cudaStreamSynchronize(s->stream));
+  if (!s->h_joints.empty())
+    CU(cudaMemcpy(s->d_joints, s->h_joints.data(), s->h_joints.size() * sizeof(DevJoint), cudaMemcpyHostToDevice));
+  return MPB_OK;
+}
+
+extern "C" int mpb_scene_set_pairs(mpb_scene *s, int32_t n_pairs, const int32_t *pa, const int32_t *pb) {
+  if (!s || n_pairs < 0 || (n_pairs && (!pa || !pb))) return fail(MPB_ERR_INVALID, "bad pair list");
+  CU(cudaSetDevice(s->device));
+  CU(cudaStreamSynchronize(s->stream));
+  int rc = build_pairs(s, n_pairs, pa, pb);
+  if (rc != MPB_OK) return rc;
+  return upload_pairs(s);
+}
+
+// ------------------------------------------------------------------------------------------ work buffers
+template <typename T>
+static cudaError_t ensure(T **p, size_t *cap, size_t need) {
+  if (need <= *cap && *p) return cudaSuccess;
+  if (*p) cudaFree(*p);
+  *p = nullptr;
+  *cap = 0;
+  cudaError_t e = cudaMalloc((void **)p, std::max<size_t>(need, 1) * sizeof(T));
+  if (e == cudaSuccess) *cap = need;
+  return e;
+}
+
+static const long long kMaxChunk = 1ll << 20;       // configurations per pass
+static const size_t kMaxItems = (size_t)48 << 20;   // work-queue capacity bound (x56 B = 2.6 GiB)
+
+static int prepare_work(mpb_scene *s, long long chunk) {
+  if (s->chunk == chunk && s->wq.itf) return MPB_OK;
+  const size_t P = (size_t)std::max(s->img.n_pairs, 1);
+  size_t cap = std::min((size_t)chunk * P, kMaxItems);
+  cap = std::max<size_t>(cap, 1024);
+  if (s->wq.itf) { cudaFree(s->wq.itf); cudaFree(s->wq.icfg); cudaFree(s->wq.ipair); s->wq.itf = nullptr; }
+  CU(cudaMalloc((void **)&s->wq.itf, cap * 12 * sizeof(float)));
+  CU(cudaMalloc((void **)&s->wq.icfg, cap * sizeof(int)));
+  CU(cudaMalloc((void **)&s->wq.ipair, cap * sizeof(int)));
+  s->wq.cap = (unsigned)cap;
+  const size_t nb = (size_t)std::max(s->img.n_bins, 1);
+  if (nb > s->bins_cap || !s->wq.bin_count) {
+    if (s->wq.bin_count) cudaFree(s->wq.bin_count);
+    CU(cudaMalloc((void **)&s->wq.bin_count, (4 * nb + 8) * sizeof(unsigned)));
+    s->bins_cap = nb;
+  }
+  s->wq.bin_cursor = s->wq.bin_count + nb;
+  s->wq.bin_start = s->wq.bin_cursor + nb;
+  s->wq.unit_start = s->wq.bin_start + nb + 1;
+  if (!s->wq.totals) CU(cudaMalloc((void **)&s->wq.totals, 4 * sizeof(unsigned)));
+  if (!s->wq.counters) CU(cudaMalloc((void **)&s->wq.counters, 4 * sizeof(unsigned long long)));
+  s->chunk = chunk;
+  return MPB_OK;
+}
+
+static cudaEvent_t get_event(mpb_scene *s, size_t i) {
+  while (s->events.size() <= i) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    s->events.push_back(e);
+  }
+  return s->events[i];
+}
+
+// One attempt over the whole batch with a given chunk size.  Returns MPB_OK and sets *overflow.
+static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *verdict, uint32_t *pair_bits, int space,
+                           cudaStream_t st, long long chunk, bool *overflow, mpb_stats *stats) {
+  int rc = prepare_work(s, chunk);
+  if (rc != MPB_OK) return rc;
+  const int D = s->img.state_dim, W = s->img.pair_words, nb = std::max(s->img.n_bins, 1);
+  const bool host = space == MPB_HOST;
+  if (host) {
+    CU(ensure(&s->d_q, &s->d_q_cap, (size_t)chunk * std::max(D, 1)));
+    CU(ensure(&s->d_verdict, &s->d_verdict_cap, (size_t)(chunk + 31) / 32));
+    if (pair_bits) CU(ensure(&s->d_pairbits, &s->d_pairbits_cap, (size_t)chunk * std::max(W, 1)));
+  }
+  CU(cudaMemsetAsync(s->wq.totals, 0, 4 * sizeof(unsigned), st));
+  CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
+  size_t ev = 0;
+  long long launches = 0;
+  for (long long off = 0; off < n; off += chunk) {
+    const long long m = std::min(chunk, n - off);
+    const size_t vwords = (size_t)(m + 31) / 32;
+    const float *dq = q + off * D;
+    uint32_t *dv = verdict + off / 32;
+    uint32_t *dp = pair_bits ? pair_bits + (size_t)off * W : nullptr;
+    if (host) {
+      if (D > 0) CU(cudaMemcpyAsync(s->d_q, q + off * D, (size_t)m * D * sizeof(float), cudaMemcpyHostToDevice, st));
+      dq = s->d_q;
+      dv = s->d_verdict;
+      dp = pair_bits ? s->d_pairbits : nullptr;
+    }
+    CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
+    if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
+    if (s->img.n_pairs > 0) {
+      const int blocks = (int)std::min<long long>((m + 127) / 128, (long long)s->num_sms * 16);
+      cudaEvent_t e0 = get_event(s, ev++), e1 = get_event(s, ev++), e2 = get_event(s, ev++);
+      CU(cudaEventRecord(e0, st));
+      fk_cull_kernel<0><<<blocks, 128, 0, st>>>(s->img, dq, m, s->wq);
+      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins);
+      fk_cull_kernel<1><<<blocks, 128, 0, st>>>(s->img, dq, m, s->wq);
+      CU(cudaEventRecord(e1, st));
+      if (s->smem_verts)
+        narrow_kernel<true><<<s->narrow_blocks, 256, (size_t)s->img.n_verts * sizeof(float4), st>>>(s->img, s->wq, dv, dp);
+      else
+        narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp);
+      CU(cudaEventRecord(e2, st));
+      CU(cudaGetLastError());
+      launches += 4;
+    }
+    if (host) {
+      CU(cudaMemcpyAsync(verdict + off / 32, dv, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+      if (pair_bits)
+        CU(cudaMemcpyAsync(pair_bits + (size_t)off * W, dp, (size_t)m * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    }
+  }
+  unsigned totals[4] = {0, 0, 0, 0};
+  unsigned long long counters[4] = {0, 0, 0, 0};
+  CU(cudaMemcpyAsync(totals, s->wq.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(counters, s->wq.counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  *overflow = totals[2] != 0;
+  if (stats) {
+    stats->n_states = n;
+    stats->pairs_admitted = n * (long long)s->img.n_pairs;
+    stats->pairs_after_cull = (long long)counters[0];
+    stats->narrow_iterations = (long long)counters[1];
+    stats->narrow_capped = (long long)counters[2];
+    stats->kernel_launches = launches;
+    float cull = 0.f, narrow = 0.f;
+    for (size_t i = 0; i + 2 < ev + 0 && i + 2 <= ev - 1; i += 3) {
+      float a = 0.f, b = 0.f;
+      cudaEventElapsedTime(&a, s->events[i], s->events[i + 1]);
+      cudaEventElapsedTime(&b, s->events[i + 1], s->events[i + 2]);
+      cull += a;
+      narrow += b;
+    }
+    stats->gpu_ms_cull = cull;
+    stats->gpu_ms_narrow = narrow;
+    stats->gpu_ms = cull + narrow;
+  }
+  return MPB_OK;
+}
+
+extern "C" int mpb_collide_batch(mpb_scene *s, const float *q, int64_t n, uint32_t *verdict_bits, uint32_t *pair_bits,
+                                 mpb_stats *stats, int space, void *stream) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!verdict_bits || (!q && s->img.state_dim > 0)))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (space != MPB_HOST && space != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
+  if (stats) memset(stats, 0, sizeof(*stats));
+  if (n == 0) return MPB_OK;
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  long long chunk = std::min<long long>(kMaxChunk, (n + 31) / 32 * 32);
+  for (int attempt = 0; attempt < 12; attempt++) {
+    bool overflow = false;
+    int rc = collide_attempt(s, q, n, verdict_bits, pair_bits, space, st, chunk, &overflow, stats);
+    if (rc != MPB_OK) return rc;
+    if (!overflow) return MPB_OK;
+    chunk = std::max<long long>(32, (chunk / 4 + 31) / 32 * 32);  // queue overflowed: smaller passes, exact redo
+  }
+  return fail(MPB_ERR_CAPACITY, "work queue overflow persists at the minimum chunk size");
+}
+
+extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *poses, int space, void *stream) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!poses || (!q && s->img.state_dim > 0)))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (space != MPB_HOST && space != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
+  if (n == 0 || s->img.n_links == 0) return MPB_OK;
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  const int D = s->img.state_dim, L = s->img.n_links;
+  const long long chunk = std::min<long long>(kMaxChunk, n);
+  if (space == MPB_HOST) {
+    CU(ensure(&s->d_q, &s->d_q_cap, (size_t)chunk * std::max(D, 1)));
+    CU(ensure(&s->d_poses, &s->d_poses_cap, (size_t)chunk * L * 7));
+  }
+  for (long long off = 0; off < n; off += chunk) {
+    const long long m = std::min(chunk, n - off);
+    const float *dq = q + off * D;
+    float *dp = poses + (size_t)off * L * 7;
+    if (space == MPB_HOST) {
+      if (D > 0) CU(cudaMemcpyAsync(s->d_q, dq, (size_t)m * D * sizeof(float), cudaMemcpyHostToDevice, st));
+      dq = s->d_q;
+      dp = s->d_poses;
+    }
+    const int blocks = (int)std::min<long long>((m + 127) / 128, (long long)s->num_sms * 16);
+    fk_pose_kernel<<<blocks, 128, 0, st>>>(s->img, dq, m, dp);
+    CU(cudaGetLastError());
+    if (space == MPB_HOST)
+      CU(cudaMemcpyAsync(poses + (size_t)off * L * 7, dp, (size_t)m * L * 7 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  }
+  if (space == MPB_HOST) CU(cudaStreamSynchronize(st));
+  return MPB_OK;
+}

@@ -1,0 +1,106 @@
+// mpb_device.cuh -- device-side scene image and small fp32 algebra shared by the kernels.
+//
+// HBM layout of the compiled scene (all read-only during a batch):
+//   DevJoint[n_joints]   placement (3x4), axis, type, parent, state slot / constant q
+//   DevObject[n_objects] pose relative to its owner joint (link placement folded in on the host in
+//                        double), geometry parameters, bounding sphere + OBB (object frame)
+//   float4 verts[]       hull vertex pool, one float4 per vertex (xyz + pad) -> one LDS.128/LDG.128
+//   DevPair[n_pairs]     (a, b, bin) admitted pairs; bin = index of the (geometry-key A, key B) class
+// Work queues are structure-of-arrays so that both the producer (ballot-compacted lanes) and the
+// consumer (lane = item) touch consecutive 4-byte words.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define MPB_MAX_JOINTS 32   // movable joints in the merged forest (two Pandas = 18)
+#define MPB_MAX_DYN 40      // objects that move with a joint
+#define MPB_ITEM_WORDS 14   // 12 floats relative transform + cfg + pair
+
+struct DevJoint {
+  float P[12];   // placement in the parent joint frame
+  float ax[3];
+  int type;      // MPB_JOINT_*
+  int parent;    // model index (0 = universe)
+  int slot;      // index into the batch state, or -1
+  float qconst;  // value when slot < 0 (q_base)
+  int pad;
+};
+
+struct DevObject {
+  float L[12];      // pose in the owner joint frame (joint == 0: world pose)
+  int joint;        // model joint index, 0 = world-fixed
+  int type;         // MPB_GEOM_*
+  int geom;         // hull / mesh / octree index
+  int dyn;          // slot in the per-thread dynamic-object table, -1 if world-fixed
+  float prm[4];     // sphere r | box half sides | capsule, cylinder: r, half height
+  float bc[3];      // bounding-sphere centre, object frame
+  float br;         // bounding-sphere radius
+  float oc[3];      // OBB centre, object frame
+  float oh[3];      // OBB half extents
+  float oR[9];      // OBB axes as columns of a rotation (object frame)
+  float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
+  int voff, vcnt;   // hull vertices in the pool
+  int pad;
+};
+
+struct DevPair {
+  int a, b, bin, pad;
+};
+
+struct Xf {  // rigid transform, row-major rotation
+  float r[9];
+  float p[3];
+};
+
+__device__ __forceinline__ Xf xf_mul(const Xf &a, const Xf &b) {
+  Xf o;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+      o.r[3 * i + j] = fmaf(a.r[3 * i], b.r[j], fmaf(a.r[3 * i + 1], b.r[3 + j], a.r[3 * i + 2] * b.r[6 + j]));
+    o.p[i] = fmaf(a.r[3 * i], b.p[0], fmaf(a.r[3 * i + 1], b.p[1], fmaf(a.r[3 * i + 2], b.p[2], a.p[i])));
+  }
+  return o;
+}
+// a^-1 * b
+__device__ __forceinline__ Xf xf_inv_mul(const Xf &a, const Xf &b) {
+  Xf o;
+  float d0 = b.p[0] - a.p[0], d1 = b.p[1] - a.p[1], d2 = b.p[2] - a.p[2];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+      o.r[3 * i + j] = fmaf(a.r[i], b.r[j], fmaf(a.r[3 + i], b.r[3 + j], a.r[6 + i] * b.r[6 + j]));
+    o.p[i] = fmaf(a.r[i], d0, fmaf(a.r[3 + i], d1, a.r[6 + i] * d2));
+  }
+  return o;
+}
+__device__ __forceinline__ Xf xf_from12(const float *m) {
+  Xf o;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    o.r[3 * i] = m[4 * i];
+    o.r[3 * i + 1] = m[4 * i + 1];
+    o.r[3 * i + 2] = m[4 * i + 2];
+    o.p[i] = m[4 * i + 3];
+  }
+  return o;
+}
+__device__ __forceinline__ void xf_point(const Xf &t, const float *v, float *o) {
+#pragma unroll
+  for (int i = 0; i < 3; i++) o[i] = fmaf(t.r[3 * i], v[0], fmaf(t.r[3 * i + 1], v[1], fmaf(t.r[3 * i + 2], v[2], t.p[i])));
+}
+
+struct V3 {
+  float x, y, z;
+};
+__device__ __forceinline__ V3 v3(float x, float y, float z) { return V3{x, y, z}; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return V3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return V3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return V3{a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+  return V3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ V3 normalized(V3 a) { return a * rsqrtf(dot(a, a)); }

@@ -1,0 +1,109 @@
+"""ctypes wrapper of the CPU oracle (oracle/oracle.c).  TEST INFRASTRUCTURE ONLY -- see the header of
+oracle.c.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+may import this module."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "liboracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        os.makedirs(os.path.dirname(_SO), exist_ok=True)
+        subprocess.check_call(["gcc", "-O3", "-fPIC", "-shared", "-o", _SO, src, "-lm"])
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_SO)
+        _lib.orc_object_distance.restype = C.c_double
+    return _lib
+
+
+def _states(desc, states):
+    s = np.ascontiguousarray(np.asarray(states, dtype=np.float64))
+    if s.ndim == 1:
+        s = s.reshape(1, -1)
+    assert s.shape[1] == desc.state_dim, (s.shape, desc.state_dim)
+    return s
+
+
+def fk_batch(desc, states):
+    s = _states(desc, states)
+    out = np.zeros((s.shape[0], desc.n_links, 7), dtype=np.float64)
+    lib().orc_fk_batch(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(s.shape[0]), C.c_void_p(out.ctypes.data))
+    return out
+
+
+def object_poses(desc, states):
+    s = _states(desc, states)
+    out = np.zeros((s.shape[0], desc.n_objects, 12), dtype=np.float64)
+    lib().orc_object_poses(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(s.shape[0]), C.c_void_p(out.ctypes.data))
+    return out.reshape(s.shape[0], desc.n_objects, 3, 4)
+
+
+def collide_batch(desc, states, return_iters=False):
+    s = _states(desc, states)
+    n = s.shape[0]
+    ph = np.zeros((n, max(desc.n_pairs, 1)), dtype=np.uint8)
+    vd = np.zeros(n, dtype=np.uint8)
+    it = C.c_int64(0)
+    lib().orc_collide_batch(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(ph.ctypes.data),
+                            C.c_void_p(vd.ctypes.data), C.byref(it))
+    ph = ph[:, : desc.n_pairs].astype(bool)
+    if return_iters:
+        return vd.astype(bool), ph, it.value
+    return vd.astype(bool), ph
+
+
+def pair_signed_distance(desc, state, pair):
+    s = _states(desc, state)
+    out = C.c_double(0)
+    lib().orc_pair_signed_distance(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int(pair), C.byref(out))
+    return out.value
+
+
+def sat_pair(desc, state, pair):
+    s = _states(desc, state)
+    out = C.c_double(0)
+    rc = lib().orc_sat_pair(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int(pair), C.byref(out))
+    if rc != 0:
+        raise ValueError("orc_sat_pair: pair is not convex/convex")
+    return out.value
+
+
+def distance_batch(desc, states):
+    s = _states(desc, states)
+    n = s.shape[0]
+    md = np.zeros(n, dtype=np.float64)
+    am = np.zeros(n, dtype=np.int32)
+    lib().orc_distance_batch(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(md.ctypes.data),
+                             C.c_void_p(am.ctypes.data))
+    return md, am
+
+
+def _T12(T):
+    return np.ascontiguousarray(np.asarray(T, dtype=np.float64)[:3, :4].reshape(12))
+
+
+def object_collide(desc, a, Ta, b, Tb):
+    ta, tb = _T12(Ta), _T12(Tb)
+    return bool(lib().orc_object_collide(C.byref(desc.as_struct()), C.c_int(a), C.c_void_p(ta.ctypes.data), C.c_int(b),
+                                         C.c_void_p(tb.ctypes.data)))
+
+
+def object_distance(desc, a, Ta, b, Tb):
+    ta, tb = _T12(Ta), _T12(Tb)
+    return float(lib().orc_object_distance(C.byref(desc.as_struct()), C.c_int(a), C.c_void_p(ta.ctypes.data), C.c_int(b),
+                                           C.c_void_p(tb.ctypes.data)))

@@ -1,0 +1,75 @@
+"""GPU parity: CUDA path (through the C-ABI) vs the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+from tests.common import compile_desc, make_panda_world, random_q
+
+pytestmark = pytest.mark.gpu
+
+BAND = 1e-4  # north_star: verdicts may differ only where |signed distance| < 1e-4 m
+
+
+def _check_pairs(desc, q, gpu_pairs, orc_pairs):
+    from oracle import oracle as O
+
+    mism = np.argwhere(gpu_pairs != orc_pairs)
+    in_band = 0
+    for i, p in mism:
+        sd = O.pair_signed_distance(desc, q[i], int(p))
+        if abs(sd) >= BAND:
+            sat = O.sat_pair(desc, q[i], int(p))
+            assert abs(sat) < BAND, f"state {i} pair {p}: gpu={gpu_pairs[i, p]} oracle={orc_pairs[i, p]} sd={sd} sat={sat}"
+        in_band += 1
+    return len(mism), in_band
+
+
+def test_fk_parity(panda_world):
+    from oracle import oracle as O
+
+    q = random_q(4096, 11)
+    c = panda_world._sync()
+    got = c["dev"].fk(q)
+    ref = O.fk_batch(c["dev"].desc, q.astype(np.float32).astype(np.float64))
+    assert np.abs(got[..., :3] - ref[..., :3]).max() < 1e-5
+    # quaternion sign is not unique near the branch boundaries: compare up to sign
+    dq = np.minimum(np.abs(got[..., 3:] - ref[..., 3:]).max(-1), np.abs(got[..., 3:] + ref[..., 3:]).max(-1))
+    assert dq.max() < 1e-5
+
+
+def test_self_collision_parity(panda_world):
+    from oracle import oracle as O
+
+    q = random_q(20000, 1)
+    c = panda_world._sync()
+    desc = c["dev"].desc
+    v, ph, st = c["dev"].collide(q, want_pairs=True, stats=True)
+    qd = q.astype(np.float32).astype(np.float64)
+    ov, oph = O.collide_batch(desc, qd)
+    n_mis, n_band = _check_pairs(desc, qd, ph, oph)
+    print(f"mismatches={n_mis} (all in band), collision rate={ov.mean():.3f}, stats={st}")
+    assert n_mis <= 20
+    assert st["narrow_capped"] == 0
+    # verdict bit == OR over pair bits
+    assert np.array_equal(v, ph.any(axis=1))
+
+
+def test_example_poses(panda_world):
+    """examples/detect_collision.py:22-34"""
+    w = panda_world
+    w.set_qpos_all([0, 0.19, 0.0, -2.61, 0.0, 2.94, 0.78])
+    assert w.self_collide() == [] and not w.collide()
+    w.set_qpos_all([0, 1.36, 0, -3, -3, 3, -1])
+    r = w.self_collide()
+    assert len(r) > 0 and all(x.collision_type == "self" for x in r)
+    assert w.collide()
+
+
+def test_ragged_and_empty(panda_world):
+    dev = panda_world._sync()["dev"]
+    v, ph = dev.collide(np.zeros((0, 7)))
+    assert v.shape == (0,)
+    for n in (1, 31, 33, 1000):
+        q = random_q(n, 5)
+        v, ph = dev.collide(q)
+        v2, ph2 = dev.collide(q[::-1].copy())
+        assert np.array_equal(v, v2[::-1]) and np.array_equal(ph, ph2[::-1])
