@@ -16,7 +16,7 @@
 #define MPB_MAX_DYN 40      // objects that move with a joint
 #define MPB_ITEM_WORDS 14   // 12 floats relative transform + cfg + pair
 
-struct DevJoint {
+struct alignas(16) DevJoint {
   float P[12];   // placement in the parent joint frame
   float ax[3];
   int type;      // MPB_JOINT_*
@@ -26,7 +26,7 @@ struct DevJoint {
   int pad;
 };
 
-struct DevObject {
+struct alignas(16) DevObject {
   float L[12];      // pose in the owner joint frame (joint == 0: world pose)
   int joint;        // model joint index, 0 = world-fixed
   int type;         // MPB_GEOM_*
@@ -40,8 +40,9 @@ struct DevObject {
   float oR[9];      // OBB axes as columns of a rotation (object frame)
   float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
   int voff, vcnt;   // hull vertices in the pool
-  int pad;
+  int pad[4];       // sizeof == 192: float4 loads of L stay aligned
 };
+static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
 
 struct DevPair {
   int a, b, bin, pad;
