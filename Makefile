@@ -13,7 +13,7 @@ $(LIB): $(SRC) $(HDR)
 oracle: oracle/_build/liboracle.so
 oracle/_build/liboracle.so: oracle/oracle.c include/mpb.h
 	mkdir -p oracle/_build
-	gcc -O3 -fPIC -shared -Wall -Wextra -o $@ oracle/oracle.c -lm
+	gcc -O3 -fopenmp -fPIC -shared -Wall -Wextra -o $@ oracle/oracle.c -lm
 
 clean:
 	rm -f $(LIB) oracle/_build/liboracle.so

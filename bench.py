@@ -1,0 +1,276 @@
+#!/usr/bin/env python
+"""bench.py -- Panda collision checks/sec (FK + self [+ env]) on B200, one process per GPU.
+
+A *step* is one pass of the hot path (batched FK + broadphase + narrowphase + verdict pack) over one
+batch of synthetic configurations; `value` = checks/s with q resident in HBM, `e2e` = the same through
+the C-ABI with pinned HOST buffers (H2D of q and D2H of verdict/pair bits inside the timed region).
+`--impl reference` times the CPU restatement of the reference path (oracle/, all host threads) on a
+bounded sample of the same workload.  See DESIGN.md "Measurement".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "panda_collision_checks_per_sec"
+UNIT = "checks/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3"])
+    ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args):
+    from tests import workloads as WL
+
+    return WL.get(args.workload, args.batch)
+
+
+class ClockSampler:
+    """nvidia-smi sampling during the timed region (B200_PROFILING.md 'clocks' line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_leg(desc, q, threads, budget_s, chunk):
+    """Time the oracle on successive chunks of q until ~budget_s of wall time is spent."""
+    from oracle import oracle as O
+
+    O.collide_batch(desc, q[:1000], threads=threads)  # warm-up (page-in, OpenMP pool)
+    done, t0 = 0, time.perf_counter()
+    while done < q.shape[0] and time.perf_counter() - t0 < budget_s:
+        m = min(chunk, q.shape[0] - done)
+        O.collide_batch(desc, q[done:done + m], threads=threads)
+        done += m
+    dt = time.perf_counter() - t0
+    return done / dt, done, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = workload_config(args)
+    desc = wl["desc"]
+    threads = os.cpu_count() or 1
+    q = wl["make_q"](0, min(wl["batch"], 1 << 18)).astype(np.float64)
+    per_step = []
+    for s in range(args.warmup + args.steps):
+        v, n, dt = cpu_leg(desc, q, threads, budget_s=3.0, chunk=q.shape[0])
+        if s >= args.warmup:
+            per_step.append((n, dt))
+    n_tot = sum(n for n, _ in per_step)
+    t_tot = sum(dt for _, dt in per_step)
+    val = n_tot / t_tot
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / max(len(per_step), 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl["config"],
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{per_step[0][0] if per_step else 0} states/step of the same seeded workload, OpenMP x{threads}"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+
+    from mplib_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if _lib.load().mpb_device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    wl = workload_config(args)
+    desc, N, D = wl["desc"], wl["batch"], wl["desc"].state_dim
+    dev = _lib.DeviceScene(desc, local)
+    W = dev.pair_words
+    stream = torch.cuda.current_stream()
+    # rotating pool of input batches larger than L2 (126 MB) so no step re-reads cached q
+    n_pool = max(2, int(np.ceil(160e6 / (N * D * 4))))
+    n_pool = min(n_pool, 16)
+    pool_h = [torch.from_numpy(wl["make_q"](rank * 1000 + k, N).astype(np.float32)).pin_memory() for k in range(n_pool)]
+    pool_d = [t.cuda(non_blocking=True) for t in pool_h]
+    vwords = (N + 31) // 32
+    verdict_d = torch.zeros(vwords, dtype=torch.int32, device="cuda")
+    pairs_d = torch.zeros((N, max(W, 1)), dtype=torch.int32, device="cuda")
+    gathered = torch.zeros((world, vwords), dtype=torch.int32, device="cuda") if world > 1 else None
+    verdict_h = torch.zeros(vwords, dtype=torch.int32).pin_memory()
+    pairs_h = torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()
+    torch.cuda.synchronize()
+
+    def step_device(k):
+        st = dev.collide_raw(pool_d[k % n_pool], N, verdict_d, pairs_d, _lib.MPB_DEVICE, stream.cuda_stream)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, verdict_d)  # the only inter-GPU traffic: verdict words
+        return st
+
+    def step_host(k):
+        return dev.collide_raw(pool_h[k % n_pool], N, verdict_h, pairs_h, _lib.MPB_HOST, stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        step_device(k)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "pairs_after_cull": 0, "narrow_iterations": 0, "narrow_capped": 0,
+           "kernel_launches": 0}
+    e0.record(stream)
+    for k in range(args.steps):
+        st = step_device(args.warmup + k)
+        for key in agg:
+            agg[key] += st[key]
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+
+    # end-to-end through the C-ABI with pinned host buffers
+    for k in range(min(args.warmup, 3)):
+        step_host(k)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step_host(args.warmup + k)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+
+    if rank == 0:
+        K = args.steps
+        total_checks = float(N) * world * K
+        value = total_checks / (ms * 1e-3)
+        # algorithmic flop model of SURVEY 8(d)
+        f = wl["flop_model"]
+        iters_per_step = agg["narrow_iterations"] / K
+        F_step = N * (f["F_fk"] + 12.0 * desc.n_pairs) + iters_per_step * (2.0 * (5.0 * f["V_mean"] + 33.0) + 150.0)
+        kernels_ms = (agg["gpu_ms_cull"] + agg["gpu_ms_narrow"]) / K
+        peak_probe = _lib.fp32_peak_tflops(local)
+        props = torch.cuda.get_device_properties(local)
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        peak_formula = props.multi_processor_count * 128 * 2 * sm_mhz * 1e6 / 1e12
+        achieved = F_step / (kernels_ms * 1e-3) / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        B_alg = 4.0 * D + 4.0
+        hbm_achieved = N * B_alg / (kernels_ms * 1e-3) / 1e9
+        dominant = "fk_cull_kernel" if agg["gpu_ms_cull"] >= agg["gpu_ms_narrow"] else "narrow_kernel"
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": wl["config"],
+            "e2e": {"value": total_checks / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(N * D * 4),
+                    "d2h_bytes_per_step": int(vwords * 4 + N * max(W, 1) * 4)},
+            "gpu_launches": int(agg["kernel_launches"]),
+            "clocks": clocks,
+            "roofline": {
+                "bound": "fp32", "scope": "all kernels of one step (FK+cull x2 passes, scan, narrowphase)",
+                "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
+                "peak_source": "in-run FFMA probe (mpb_fp32_peak); formula SMs*128*2*f_sampled = %.1f" % peak_formula,
+                "flop_per_check": F_step / N, "traffic": None, "dominant_kernel": dominant,
+                "kernel_ms_per_step": {"fk_cull_x2+scan": agg["gpu_ms_cull"] / K, "narrow": agg["gpu_ms_narrow"] / K},
+                "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
+                        "bytes_per_check": B_alg, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+            },
+            "stats_per_step": {"pairs_after_cull": agg["pairs_after_cull"] / K, "support_evals": iters_per_step,
+                               "capped": agg["narrow_capped"] / K},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            qs = wl["make_q"](0, min(N, 1 << 20)).astype(np.float64)
+            v, n, dt = cpu_leg(desc, qs, 1, budget_s=12.0, chunk=50000)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                                    "sample": f"first {n} states of the seeded workload, oracle.c single thread, {dt:.1f}s"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

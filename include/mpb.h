@@ -156,6 +156,10 @@ int mpb_collide_batch(mpb_scene *scene, const float *q, int64_t n, uint32_t *ver
 int mpb_scene_info(const mpb_scene *scene, int32_t *n_pairs, int32_t *state_dim, int32_t *n_links,
                    int32_t *n_objects, int32_t *device);
 
+/* FP32 FMA micro-benchmark on `device`: achieved TFLOP/s of a register-resident FFMA chain on every SM
+ * (the in-run confirmation of SMs x 128 x 2 x f that BASELINE.md 2 asks for; no reference counterpart). */
+int mpb_fp32_peak(int device, float *tflops);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libmpb.so")
 # every symbol include/mpb.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "mpb_last_error", "mpb_device_count", "mpb_scene_create", "mpb_scene_destroy", "mpb_scene_set_q_base",
-    "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info",
+    "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
 ]
 
 _lib = None
@@ -46,6 +46,7 @@ def load():
     lib.mpb_collide_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.POINTER(MpbStats), C.c_int, C.c_void_p]
     lib.mpb_scene_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int32)] * 5
+    lib.mpb_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_float)]
     _lib = lib
     return lib
 
@@ -138,3 +139,9 @@ class DeviceScene:
 
     def fk_raw(self, q_ptr, n, poses_ptr, space=MPB_HOST, stream=None):
         _check(load().mpb_fk_batch(self._h, _ptr(q_ptr), int(n), _ptr(poses_ptr), space, _ptr(stream)))
+
+
+def fp32_peak_tflops(device=0):
+    v = C.c_float(0)
+    _check(load().mpb_fp32_peak(device, C.byref(v)))
+    return float(v.value)

@@ -597,3 +597,52 @@ extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *pose
   if (space == MPB_HOST) CU(cudaStreamSynchronize(st));
   return MPB_OK;
 }
+
+// ------------------------------------------------------------------------------------------ FP32 peak probe
+__global__ void __launch_bounds__(256) fma_probe_kernel(float *out, int iters) {
+  float a[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) a[k] = 1.0f + 1e-3f * (threadIdx.x + k);
+  const float m = 1.000001f, c = 1e-7f;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+      for (int k = 0; k < 8; k++) a[k] = fmaf(a[k], m, c);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; k++) s += a[k];
+  if (s == 12345.678f) out[0] = s;  // keep the chain alive
+}
+
+extern "C" int mpb_fp32_peak(int device, float *tflops) {
+  if (!tflops) return fail(MPB_ERR_INVALID, "null argument");
+  int ndev = mpb_device_count();
+  if (device < 0 || device >= ndev) return fail(MPB_ERR_CUDA, "no such CUDA device");
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  float *d_out = nullptr;
+  CU(cudaMalloc(&d_out, 16));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+  float best = 0.f;
+  for (int rep = 0; rep < 4; rep++) {
+    CU(cudaEventRecord(e0));
+    fma_probe_kernel<<<blocks, 256>>>(d_out, iters);
+    CU(cudaEventRecord(e1));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    const double flop = (double)blocks * 256.0 * iters * 64.0 * 2.0;
+    if (rep > 0) best = std::max(best, (float)(flop / (ms * 1e-3) / 1e12));
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d_out);
+  *tflops = best;
+  return MPB_OK;
+}

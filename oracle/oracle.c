@@ -742,12 +742,12 @@ int orc_object_poses(const mpb_scene_desc *d, const double *states, int64_t n, d
 /* ValidityCheckerTpl::isValid for a batch (src/ompl_planner.h:59-62): per state, every admitted pair
  * is tested (no early exit, src/planning_world.h:248-250).  pair_hit: [n][n_pairs] bytes (nullable),
  * verdict: [n] bytes (nullable).  Returns total support evaluations through *iters (nullable). */
-int orc_collide_batch(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters) {
+static int64_t collide_range(const mpb_scene_desc *d, const double *states, int64_t i0, int64_t i1, uint8_t *pair_hit, uint8_t *verdict) {
   xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
   xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
   double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
   g_cnt.iters = 0;
-  for (int64_t i = 0; i < n; i++) {
+  for (int64_t i = i0; i < i1; i++) {
     scatter_state(d, states + i * d->state_dim, qf);
     fk_joints(d, qf, oMi);
     object_transforms(d, oMi, objT, NULL);
@@ -760,8 +760,25 @@ int orc_collide_batch(const mpb_scene_desc *d, const double *states, int64_t n, 
     }
     if (verdict) verdict[i] = (uint8_t)any;
   }
-  if (iters) *iters = g_cnt.iters;
   free(oMi); free(objT); free(qf);
+  return g_cnt.iters;
+}
+int orc_collide_batch(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters) {
+  int64_t it = collide_range(d, states, 0, n, pair_hit, verdict);
+  if (iters) *iters = it;
+  return 0;
+}
+/* All-host-core variant: the stateful reference can only use more than one core as independent world
+ * clones, one per thread; each thread owns its scratch and a contiguous slice. */
+int orc_collide_batch_mt(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters, int nthreads) {
+  int64_t total = 0;
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel for num_threads(nthreads) schedule(static) reduction(+ : total)
+  for (int t = 0; t < nthreads; t++) {
+    int64_t i0 = n * t / nthreads, i1 = n * (t + 1) / nthreads;
+    total += collide_range(d, states, i0, i1, pair_hit, verdict);
+  }
+  if (iters) *iters = total;
   return 0;
 }
 

@@ -18,7 +18,7 @@ def build(force=False):
     src = os.path.join(_HERE, "oracle.c")
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
         os.makedirs(os.path.dirname(_SO), exist_ok=True)
-        subprocess.check_call(["gcc", "-O3", "-fPIC", "-shared", "-o", _SO, src, "-lm"])
+        subprocess.check_call(["gcc", "-O3", "-fopenmp", "-fPIC", "-shared", "-o", _SO, src, "-lm"])
     return _SO
 
 
@@ -53,14 +53,14 @@ def object_poses(desc, states):
     return out.reshape(s.shape[0], desc.n_objects, 3, 4)
 
 
-def collide_batch(desc, states, return_iters=False):
+def collide_batch(desc, states, return_iters=False, threads=1):
     s = _states(desc, states)
     n = s.shape[0]
     ph = np.zeros((n, max(desc.n_pairs, 1)), dtype=np.uint8)
     vd = np.zeros(n, dtype=np.uint8)
     it = C.c_int64(0)
-    lib().orc_collide_batch(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(ph.ctypes.data),
-                            C.c_void_p(vd.ctypes.data), C.byref(it))
+    lib().orc_collide_batch_mt(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(ph.ctypes.data),
+                               C.c_void_p(vd.ctypes.data), C.byref(it), C.c_int(int(threads)))
     ph = ph[:, : desc.n_pairs].astype(bool)
     if return_iters:
         return vd.astype(bool), ph, it.value
