@@ -42,7 +42,11 @@ struct mpb_scene {
   float4 *d_verts = nullptr;
   float *d_linkL = nullptr;
   int *d_linkJoint = nullptr;
+  int *d_dynlist = nullptr;
   SceneImg img{};
+  int cull_block = 128;
+  size_t cull_smem = 0;
+  int cull_blocks_per_sm = 1;
   size_t pairs_cap = 0;
   // work buffers
   long long chunk = 0;
@@ -193,7 +197,9 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
     auto key = std::make_pair(s->obj_key[a], s->obj_key[b]);
     auto it = bins.find(key);
     int bin = it == bins.end() ? (bins[key] = (int)bins.size()) : it->second;
-    s->h_pairs[p] = DevPair{a, b, bin, 0};
+    if (bin > 0xffff) return fail(MPB_ERR_CAPACITY, "too many geometry-class bins");
+    const int da = s->h_objs[a].dyn + 1, db = s->h_objs[b].dyn + 1;
+    s->h_pairs[p] = DevPair{a, b, bin | (da << 16) | (db << 24), s->h_objs[a].br + s->h_objs[b].br + 1e-5f};
   }
   s->img.n_pairs = n_pairs;
   s->img.n_bins = (int)bins.size();
@@ -251,7 +257,24 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     if (qi < 0 || qi >= d->nq_full) { delete s; return fail(MPB_ERR_INVALID, "joint_qidx out of range"); }
     J.slot = slot_of_q[qi];
     J.qconst = (float)d->q_base[qi];
+    J.save_slot = -1;
+    J.pslot = -1;
+    J.dyn_first = 0;
+    J.dyn_count = 0;
     J.pad = 0;
+  }
+  {  // a joint whose child is not the next joint in the table must park its transform
+    int n_saved = 0;
+    for (int j = 0; j < d->n_joints; j++) {
+      const int par = s->h_joints[j].parent;  // model index; the previous joint has model index j
+      if (par == 0 || par == j) continue;
+      DevJoint &P = s->h_joints[par - 1];
+      if (P.save_slot < 0) {
+        if (n_saved >= MPB_MAX_SAVED) { delete s; return fail(MPB_ERR_CAPACITY, "kinematic tree has too many branch points (MPB_MAX_SAVED)"); }
+        P.save_slot = n_saved++;
+      }
+      s->h_joints[j].pslot = P.save_slot;
+    }
   }
   // objects
   s->h_objs.resize(d->n_objects);
@@ -326,6 +349,19 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     s->obj_key[o] = geom_key(O.type, O.geom);
   }
   if (ndyn > MPB_MAX_DYN) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (MPB_MAX_DYN)"); }
+  std::vector<int> dynlist;
+  for (int j = 0; j < d->n_joints; j++) {
+    s->h_joints[j].dyn_first = (int)dynlist.size();
+    for (int o = 0; o < d->n_objects; o++)
+      if (s->h_objs[o].joint == j + 1) dynlist.push_back(o);
+    s->h_joints[j].dyn_count = (int)dynlist.size() - s->h_joints[j].dyn_first;
+  }
+  for (int o = 0; o < d->n_objects; o++) {
+    DevObject &O = s->h_objs[o];
+    for (int r = 0; r < 3; r++)
+      O.bcw[r] = O.L[4 * r] * O.bc[0] + O.L[4 * r + 1] * O.bc[1] + O.L[4 * r + 2] * O.bc[2] + O.L[4 * r + 3];
+  }
+  s->img.n_dyn = ndyn;
 
   s->img.n_joints = d->n_joints;
   s->img.n_objects = d->n_objects;
@@ -349,6 +385,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   for (size_t k = 0; k < linkL.size(); k++) linkL[k] = (float)d->link_placement[k];
   CU(up((void **)&s->d_linkL, linkL.data(), linkL.size() * sizeof(float)));
   CU(up((void **)&s->d_linkJoint, d->link_joint, (size_t)d->n_links * sizeof(int)));
+  CU(up((void **)&s->d_dynlist, dynlist.data(), dynlist.size() * sizeof(int)));
+  s->img.dynlist = s->d_dynlist;
   s->img.joints = s->d_joints;
   s->img.objs = s->d_objs;
   s->img.verts = s->d_verts;
@@ -368,6 +406,12 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<false>, 256, 0));
   }
   s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
+  // FK + cull launch shape: moving-object poses in shared memory, [object][15 words][thread]
+  s->cull_block = 64;
+  s->cull_smem = std::max<size_t>((size_t)ndyn * 15 * s->cull_block * sizeof(float), 16);
+  CU(cudaFuncSetAttribute(fk_cull_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->cull_blocks_per_sm, fk_cull_kernel<64>, s->cull_block, s->cull_smem));
+  s->cull_blocks_per_sm = std::max(s->cull_blocks_per_sm, 1);
   *out = s;
   return MPB_OK;
 }
@@ -377,7 +421,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q, s->d_verdict,
-                  s->d_pairbits, s->d_poses, s->wq.itf, s->wq.icfg, s->wq.ipair, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_pairbits, s->d_poses, s->d_dynlist, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto e : s->events) cudaEventDestroy(e);
@@ -434,12 +478,17 @@ static const size_t kMaxItems = (size_t)48 << 20;   // work-queue capacity bound
 static int prepare_work(mpb_scene *s, long long chunk) {
   if (s->chunk == chunk && s->wq.itf) return MPB_OK;
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
-  size_t cap = std::min((size_t)chunk * P, kMaxItems);
-  cap = std::max<size_t>(cap, 1024);
-  if (s->wq.itf) { cudaFree(s->wq.itf); cudaFree(s->wq.icfg); cudaFree(s->wq.ipair); s->wq.itf = nullptr; }
-  CU(cudaMalloc((void **)&s->wq.itf, cap * 12 * sizeof(float)));
-  CU(cudaMalloc((void **)&s->wq.icfg, cap * sizeof(int)));
-  CU(cudaMalloc((void **)&s->wq.ipair, cap * sizeof(int)));
+  // staging may hold up to one unused half-chunk per reservation: worst case 2 x items + one chunk per warp
+  size_t cap = std::min((size_t)chunk * P * 2 + (size_t)(chunk / 32 + 1) * 64, kMaxItems);
+  cap = std::max<size_t>(cap, 4096);
+  if (s->wq.stf) { cudaFree(s->wq.stf); s->wq.stf = nullptr; s->wq.itf = nullptr; }
+  // one slab: staging [12 f + cfg + pair][cap], then binned [12 f + cfg + pair][cap]
+  CU(cudaMalloc((void **)&s->wq.stf, cap * 28 * sizeof(float)));
+  s->wq.scfg = reinterpret_cast<int *>(s->wq.stf + cap * 12);
+  s->wq.spair = s->wq.scfg + cap;
+  s->wq.itf = reinterpret_cast<float *>(s->wq.spair + cap);
+  s->wq.icfg = reinterpret_cast<int *>(s->wq.itf + cap * 12);
+  s->wq.ipair = s->wq.icfg + cap;
   s->wq.cap = (unsigned)cap;
   const size_t nb = (size_t)std::max(s->img.n_bins, 1);
   if (nb > s->bins_cap || !s->wq.bin_count) {
@@ -496,13 +545,14 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
     CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
     if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
     CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
+    CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
     if (s->img.n_pairs > 0) {
-      const int blocks = (int)std::min<long long>((m + 127) / 128, (long long)s->num_sms * 16);
+      const int cblocks = (int)std::min<long long>((m + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
       cudaEvent_t e0 = get_event(s, ev++), e1 = get_event(s, ev++), e2 = get_event(s, ev++);
       CU(cudaEventRecord(e0, st));
-      fk_cull_kernel<0><<<blocks, 128, 0, st>>>(s->img, dq, m, s->wq);
+      fk_cull_kernel<64><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, s->wq);
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins);
-      fk_cull_kernel<1><<<blocks, 128, 0, st>>>(s->img, dq, m, s->wq);
+      scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq);
       CU(cudaEventRecord(e1, st));
       if (s->smem_verts)
         narrow_kernel<true><<<s->narrow_blocks, 256, (size_t)s->img.n_verts * sizeof(float4), st>>>(s->img, s->wq, dv, dp);

@@ -23,8 +23,13 @@ struct alignas(16) DevJoint {
   int parent;    // model index (0 = universe)
   int slot;      // index into the batch state, or -1
   float qconst;  // value when slot < 0 (q_base)
+  int save_slot; // >= 0: this joint's transform is kept for a later, non-adjacent child
+  int pslot;     // >= 0: parent transform comes from that saved slot; -1: previous joint (or universe)
+  int dyn_first; // first entry of SceneImg::dynlist owned by this joint
+  int dyn_count; // number of moving collision objects on this joint
   int pad;
 };
+static_assert(sizeof(DevJoint) % 16 == 0, "DevJoint must keep 16-byte alignment");
 
 struct alignas(16) DevObject {
   float L[12];      // pose in the owner joint frame (joint == 0: world pose)
@@ -40,13 +45,17 @@ struct alignas(16) DevObject {
   float oR[9];      // OBB axes as columns of a rotation (object frame)
   float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
   int voff, vcnt;   // hull vertices in the pool
-  int pad[4];       // sizeof == 192: float4 loads of L stay aligned
+  float bcw[3];     // world-fixed objects: bounding-sphere centre in the world frame
+  int pad;          // sizeof == 192: float4 loads of L stay aligned
 };
 static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
 
 struct DevPair {
-  int a, b, bin, pad;
+  int a, b;
+  int bin_dyn;  // bin | (dynA + 1) << 16 | (dynB + 1) << 24   (0 in a dyn field = world-fixed)
+  float rr;     // sum of the two bounding-sphere radii (+ margin)
 };
+#define MPB_MAX_SAVED 8   // kinematic branch points kept per thread
 
 struct Xf {  // rigid transform, row-major rotation
   float r[9];

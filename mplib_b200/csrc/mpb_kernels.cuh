@@ -1,22 +1,26 @@
 // mpb_kernels.cuh -- sm_100a kernels of the batched state-validity path.
 //
-//   fk_cull_kernel<PASS>  thread per configuration: FK over the kinematic forest (replaces
-//                         PinocchioModelTpl::computeForwardKinematics + getLinkPose +
-//                         FCLModelTpl::updateCollisionObjects + AttachedBodyTpl::updatePose,
-//                         src/pinocchio_model.cpp:271-312, src/fcl_model.cpp:138-148,
-//                         src/attached_body.h:48-54), then for every admitted pair a bounding-sphere
-//                         and an OBB-OBB SAT reject; survivors are ballot-compacted into per-bin work
-//                         queues.  PASS 0 counts, PASS 1 fills (exact allocation, no overflow).
-//   scan_bins_kernel      prefix sums of the bin counts -> queue offsets and 32-item work units.
-//   narrow_kernel         lane per work item, warp per 32 items of ONE bin, so every lane walks the
-//                         same hull: the vertex loop is a broadcast LDS.128 + 3 FFMA per vertex for 32
-//                         items at once.  Hull pool staged in shared memory by one TMA bulk copy
-//                         (cp.async.bulk + mbarrier).  MPR (replaces ::fcl::collide -> ccdMPRIntersect on
-//                         the pairs of FCLModelTpl::collideFull / PlanningWorldTpl::selfCollide /
-//                         collideWithOthers, src/fcl_model.cpp:181-193, src/planning_world.cpp:276-481)
-//                         is written as a state machine with a single support call site so divergent
-//                         lanes re-converge at the vertex loop.
-//   fk_pose_kernel        FK-only API: link poses as [x,y,z,qw,qx,qy,qz].
+//   fk_cull_kernel     thread per configuration.  FK streams down the kinematic forest with the running
+//                      joint transform in registers (branch points parked in a small per-thread table);
+//                      the world poses of the moving collision objects live in SHARED memory, transposed
+//                      [object][word][thread] so every access is conflict-free -- poses never leave the SM.
+//                      (Replaces PinocchioModelTpl::computeForwardKinematics + getLinkPose +
+//                      FCLModelTpl::updateCollisionObjects + AttachedBodyTpl::updatePose,
+//                      src/pinocchio_model.cpp:271-312, src/fcl_model.cpp:138-148, src/attached_body.h:48-54.)
+//                      Admitted pairs are walked 32 at a time: a uniform bounding-sphere test builds a
+//                      per-lane bitmask, then the lanes pop their own survivors for a 15-axis OBB SAT;
+//                      what is left is ballot-compacted into a staging queue (one atomic per warp).
+//   scan_bins_kernel   prefix sums of the per-bin counts -> binned queue offsets.
+//   scatter_kernel     staging queue -> binned queue (bin = (geometry A, geometry B) class).
+//   narrow_kernel      lane per work item with PERSISTENT lanes: a warp owns a slice of ONE bin, so all
+//                      lanes walk the same hulls and the vertex loop is a broadcast LDS.128 + 3 FFMA per
+//                      vertex for 32 items at once; a lane that finishes its item pulls the next one of the
+//                      slice, so short and long MPR runs do not wait for each other.  Hull pool staged in
+//                      shared memory by TMA bulk copies (cp.async.bulk + mbarrier).  MPR (replaces
+//                      ::fcl::collide -> ccdMPRIntersect on the pairs of FCLModelTpl::collideFull /
+//                      PlanningWorldTpl::selfCollide / collideWithOthers, src/fcl_model.cpp:181-193,
+//                      src/planning_world.cpp:276-481) is a state machine with a single support call site.
+//   fk_pose_kernel     FK-only API: link poses as [x,y,z,qw,qx,qy,qz].
 #pragma once
 #include <float.h>
 
@@ -28,20 +32,22 @@ struct SceneImg {
   const DevObject *objs;
   const DevPair *pairs;
   const float4 *verts;
+  const int *dynlist;   // moving objects grouped by owner joint
   const float *linkL;   // [n_links][12] link placement in its joint frame
   const int *linkJoint; // [n_links]
-  int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words;
+  int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn;
 };
 
 struct WorkQ {
-  float *itf;            // [12][cap] relative transform B in A (SoA)
-  int *icfg;             // [cap]
-  int *ipair;            // [cap]
+  float *stf;            // staging: [12][cap] relative transform B in A (SoA)
+  int *scfg, *spair;     // staging: [cap]
+  float *itf;            // binned:  [12][cap]
+  int *icfg, *ipair;     // binned:  [cap]
   unsigned int *bin_count;   // [n_bins]
   unsigned int *bin_cursor;  // [n_bins]
   unsigned int *bin_start;   // [n_bins+1]
-  unsigned int *unit_start;  // [n_bins+1]
-  unsigned int *totals;      // [0]=items [1]=units [2]=overflow flag
+  unsigned int *unit_start;  // [n_bins+1]   units of MPB_UNIT_ITEMS items
+  unsigned int *totals;      // [0]=staged items [1]=units [2]=overflow flag [3]=unit ticket
   unsigned long long *counters;  // [0]=items after cull [1]=support evaluations [2]=capped items
   unsigned int cap;
 };
@@ -49,12 +55,20 @@ struct WorkQ {
 #define MPB_EPS FLT_EPSILON
 #define MPB_MPR_TOL 1e-6f
 #define MPB_MPR_MAX_ITERS 96
+#define MPB_UNIT_ITEMS 128   // items a warp owns at a time in the narrowphase
+#define MPB_STAGE_CHUNK 64   // staging slots a warp reserves per atomic (>= 32)
 
 // ---------------------------------------------------------------------------------------------- FK
+__device__ __forceinline__ Xf xf_identity() {
+  Xf m;
+  m.r[0] = 1.f; m.r[1] = 0.f; m.r[2] = 0.f; m.r[3] = 0.f; m.r[4] = 1.f; m.r[5] = 0.f; m.r[6] = 0.f; m.r[7] = 0.f; m.r[8] = 1.f;
+  m.p[0] = m.p[1] = m.p[2] = 0.f;
+  return m;
+}
 __device__ __forceinline__ Xf joint_motion(const DevJoint &J, float q) {
   Xf m;
   if (J.type == MPB_JOINT_PRISMATIC) {
-    m.r[0] = 1.f; m.r[1] = 0.f; m.r[2] = 0.f; m.r[3] = 0.f; m.r[4] = 1.f; m.r[5] = 0.f; m.r[6] = 0.f; m.r[7] = 0.f; m.r[8] = 1.f;
+    m = xf_identity();
     m.p[0] = J.ax[0] * q; m.p[1] = J.ax[1] * q; m.p[2] = J.ax[2] * q;
     return m;
   }
@@ -78,10 +92,9 @@ __device__ __forceinline__ Xf load_xf12(const float *p) {
   return o;
 }
 
-// oMi for all joints of one configuration; T[0] = identity (universe).
+// oMi for all joints of one configuration into a per-thread table; T[0] = identity (FK-only API).
 __device__ __forceinline__ void fk_joints(const SceneImg &img, const float *qrow, Xf *T) {
-  T[0].r[0] = 1.f; T[0].r[1] = 0.f; T[0].r[2] = 0.f; T[0].r[3] = 0.f; T[0].r[4] = 1.f; T[0].r[5] = 0.f;
-  T[0].r[6] = 0.f; T[0].r[7] = 0.f; T[0].r[8] = 1.f; T[0].p[0] = T[0].p[1] = T[0].p[2] = 0.f;
+  T[0] = xf_identity();
   for (int j = 0; j < img.n_joints; j++) {
     const DevJoint &J = img.joints[j];
     float q = J.slot >= 0 ? qrow[J.slot] : J.qconst;
@@ -120,37 +133,85 @@ __device__ __forceinline__ bool obb_disjoint(const float *R, const float *t, con
   return false;
 }
 
-template <int PASS>
-__global__ void __launch_bounds__(128) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, WorkQ wq) {
+// shared-memory pose table: word k (0..11 pose, 12..14 bounding-sphere centre) of moving object d
+#define SMW(d, k) sW[((d) * 15 + (k)) * BLOCK + tid]
+
+template <int BLOCK>
+__device__ __forceinline__ Xf smem_pose(const float *sW, int d, int tid) {
+  Xf w;
+#pragma unroll
+  for (int k = 0; k < 9; k++) w.r[k] = SMW(d, k);
+#pragma unroll
+  for (int k = 0; k < 3; k++) w.p[k] = SMW(d, 9 + k);
+  return w;
+}
+
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, WorkQ wq) {
+  extern __shared__ __align__(16) float sW[];
+  const int tid = threadIdx.x;
   const unsigned lane = threadIdx.x & 31;
-  const long long stride = (long long)gridDim.x * blockDim.x;
+  const unsigned FULL = 0xffffffffu;
+  const long long stride = (long long)gridDim.x * BLOCK;
   const long long n_round = (n + 31) / 32 * 32;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+  unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
+  for (long long i = (long long)blockIdx.x * BLOCK + tid; i < n_round; i += stride) {
     const bool valid = i < n;
-    Xf T[MPB_MAX_JOINTS + 1];
-    Xf W[MPB_MAX_DYN];
+    // ---- FK, running transform in registers
     if (valid) {
-      fk_joints(img, q + i * img.state_dim, T);
-      for (int o = 0; o < img.n_objects; o++) {
-        const DevObject &O = img.objs[o];
-        if (O.dyn >= 0) W[O.dyn] = xf_mul(T[O.joint], load_xf12(O.L));
+      Xf cur = xf_identity();
+      Xf saved[MPB_MAX_SAVED];
+      const float *qrow = q + i * img.state_dim;
+      for (int j = 0; j < img.n_joints; j++) {
+        const DevJoint &J = img.joints[j];
+        const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
+        const Xf li = xf_mul(load_xf12(J.P), joint_motion(J, qj));
+        if (J.parent == 0) cur = li;
+        else if (J.pslot >= 0) cur = xf_mul(saved[J.pslot], li);
+        else cur = xf_mul(cur, li);
+        if (J.save_slot >= 0) saved[J.save_slot] = cur;
+        for (int e = 0; e < J.dyn_count; e++) {
+          const DevObject &O = img.objs[img.dynlist[J.dyn_first + e]];
+          const Xf w = xf_mul(cur, load_xf12(O.L));
+          float c[3];
+          xf_point(w, O.bc, c);
+#pragma unroll
+          for (int k = 0; k < 9; k++) SMW(O.dyn, k) = w.r[k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) { SMW(O.dyn, 9 + k) = w.p[k]; SMW(O.dyn, 12 + k) = c[k]; }
+        }
       }
     }
-    for (int p = 0; p < img.n_pairs; p++) {
-      const DevPair pr = img.pairs[p];
-      bool keep = false;
-      Xf rel;
+    // ---- pairs, 32 at a time: uniform sphere test -> per-lane survivor mask -> per-lane OBB SAT
+    for (int base = 0; base < img.n_pairs; base += 32) {
+      unsigned mask = 0;
+      const int cnt = min(32, img.n_pairs - base);
       if (valid) {
-        const DevObject &A = img.objs[pr.a];
-        const DevObject &B = img.objs[pr.b];
-        Xf Wa = A.dyn >= 0 ? W[A.dyn] : load_xf12(A.L);
-        Xf Wb = B.dyn >= 0 ? W[B.dyn] : load_xf12(B.L);
-        float ca[3], cb[3];
-        xf_point(Wa, A.bc, ca);
-        xf_point(Wb, B.bc, cb);
-        float dx = ca[0] - cb[0], dy = ca[1] - cb[1], dz = ca[2] - cb[2];
-        float rr = A.br + B.br + 1e-5f;
-        if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= rr * rr) {
+        for (int k = 0; k < cnt; k++) {
+          const DevPair pr = img.pairs[base + k];
+          const int da = ((pr.bin_dyn >> 16) & 0xff) - 1, db = ((pr.bin_dyn >> 24) & 0xff) - 1;
+          float ax, ay, az, bx, by, bz;
+          if (da >= 0) { ax = SMW(da, 12); ay = SMW(da, 13); az = SMW(da, 14); }
+          else { const float *c = img.objs[pr.a].bcw; ax = c[0]; ay = c[1]; az = c[2]; }
+          if (db >= 0) { bx = SMW(db, 12); by = SMW(db, 13); bz = SMW(db, 14); }
+          else { const float *c = img.objs[pr.b].bcw; bx = c[0]; by = c[1]; bz = c[2]; }
+          const float dx = ax - bx, dy = ay - by, dz = az - bz;
+          if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rr * pr.rr) mask |= 1u << k;
+        }
+      }
+      while (__any_sync(FULL, mask != 0)) {
+        bool keep = false;
+        Xf rel;
+        int p = 0;
+        if (mask) {
+          const int k = __ffs(mask) - 1;
+          mask &= mask - 1;
+          p = base + k;
+          const DevPair pr = img.pairs[p];
+          const DevObject &A = img.objs[pr.a];
+          const DevObject &B = img.objs[pr.b];
+          const Xf Wa = A.dyn >= 0 ? smem_pose<BLOCK>(sW, A.dyn, tid) : load_xf12(A.L);
+          const Xf Wb = B.dyn >= 0 ? smem_pose<BLOCK>(sW, B.dyn, tid) : load_xf12(B.L);
           rel = xf_inv_mul(Wa, Wb);
           // box B in box A's frame:  Ra^T (rel.R Rb),  Ra^T (rel*ocB - ocA)
           float M[9], R[9], cbA[3], t[3];
@@ -165,33 +226,47 @@ __global__ void __launch_bounds__(128) fk_cull_kernel(SceneImg img, const float 
             for (int c = 0; c < 3; c++)
               R[3 * r + c] = fmaf(A.oR[r], M[c], fmaf(A.oR[3 + r], M[3 + c], A.oR[6 + r] * M[6 + c]));
           xf_point(rel, B.oc, cbA);
-          float d0 = cbA[0] - A.oc[0], d1 = cbA[1] - A.oc[1], d2 = cbA[2] - A.oc[2];
+          const float d0 = cbA[0] - A.oc[0], d1 = cbA[1] - A.oc[1], d2 = cbA[2] - A.oc[2];
 #pragma unroll
           for (int r = 0; r < 3; r++) t[r] = fmaf(A.oR[r], d0, fmaf(A.oR[3 + r], d1, A.oR[6 + r] * d2));
           keep = !obb_disjoint(R, t, A.oh, B.oh);
         }
-      }
-      const unsigned m = __ballot_sync(0xffffffffu, keep);
-      if (m == 0) continue;
-      if (PASS == 0) {
-        if (lane == 0) atomicAdd(&wq.bin_count[pr.bin], (unsigned)__popc(m));
-      } else {
-        unsigned base = 0;
-        if (lane == 0) base = atomicAdd(&wq.bin_cursor[pr.bin], (unsigned)__popc(m));
-        base = __shfl_sync(0xffffffffu, base, 0);
+        const unsigned km = __ballot_sync(FULL, keep);
+        if (km == 0) continue;
+        // warp-private chunk of staging slots: one same-address atomic per MPB_STAGE_CHUNK items
+        const unsigned cntk = (unsigned)__popc(km);
+        if (wused + cntk > MPB_STAGE_CHUNK) {
+          if (wbase != 0xffffffffu && wused + lane < MPB_STAGE_CHUNK && wbase + wused + lane < wq.cap)
+            wq.scfg[wbase + wused + lane] = -1;  // unused tail of the old chunk
+          if (wbase != 0xffffffffu && wused + 32 + lane < MPB_STAGE_CHUNK && wbase + wused + 32 + lane < wq.cap)
+            wq.scfg[wbase + wused + 32 + lane] = -1;
+          unsigned nb = 0;
+          if (lane == 0) nb = atomicAdd(&wq.totals[0], (unsigned)MPB_STAGE_CHUNK);
+          wbase = __shfl_sync(FULL, nb, 0);
+          wused = 0;
+        }
         if (keep) {
-          const unsigned slot = wq.bin_start[pr.bin] + base + __popc(m & ((1u << lane) - 1u));
+          const unsigned slot = wbase + wused + __popc(km & ((1u << lane) - 1u));
+          const int bin = img.pairs[p].bin_dyn & 0xffff;
           if (slot < wq.cap) {
 #pragma unroll
-            for (int k = 0; k < 9; k++) wq.itf[(size_t)k * wq.cap + slot] = rel.r[k];
+            for (int k = 0; k < 9; k++) wq.stf[(size_t)k * wq.cap + slot] = rel.r[k];
 #pragma unroll
-            for (int k = 0; k < 3; k++) wq.itf[(size_t)(9 + k) * wq.cap + slot] = rel.p[k];
-            wq.icfg[slot] = (int)i;
-            wq.ipair[slot] = p;
+            for (int k = 0; k < 3; k++) wq.stf[(size_t)(9 + k) * wq.cap + slot] = rel.p[k];
+            wq.scfg[slot] = (int)i;
+            wq.spair[slot] = p;
           }
+          const unsigned grp = __match_any_sync(km, slot < wq.cap ? bin : -1);
+          if (slot < wq.cap && lane == (unsigned)(__ffs(grp) - 1)) atomicAdd(&wq.bin_count[bin], (unsigned)__popc(grp));
         }
+        wused += cntk;
       }
     }
+  }
+  // invalidate the unused tail of the last chunk
+  if (wbase != 0xffffffffu) {
+    for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
+      if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;
   }
 }
 
@@ -203,15 +278,38 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins) {
       wq.unit_start[b] = units;
       const unsigned c = wq.bin_count[b];
       items += c;
-      units += (c + 31u) >> 5;
+      units += (c + MPB_UNIT_ITEMS - 1u) / MPB_UNIT_ITEMS;
       wq.bin_cursor[b] = 0;
     }
     wq.bin_start[n_bins] = items;
     wq.unit_start[n_bins] = units;
-    wq.totals[0] = items;
     wq.totals[1] = units;
-    if (items > wq.cap) wq.totals[2] = 1u;
+    wq.totals[3] = 0;
+    if (wq.totals[0] > wq.cap) wq.totals[2] = 1u;  // staging overflow: the host redoes the pass in smaller chunks
     atomicAdd(wq.counters, (unsigned long long)items);
+  }
+}
+
+__global__ void __launch_bounds__(256) scatter_kernel(SceneImg img, WorkQ wq) {
+  const unsigned n = min(wq.totals[0], wq.cap);
+  const unsigned n_round = (n + 31u) & ~31u;
+  const unsigned lane = threadIdx.x & 31;
+  for (unsigned s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
+    const bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
+    const int p = valid ? wq.spair[s] : 0;
+    const int bin = valid ? (img.pairs[p].bin_dyn & 0xffff) : (-1 - (int)lane);
+    const unsigned grp = __match_any_sync(0xffffffffu, bin);
+    const int leader = __ffs(grp) - 1;
+    unsigned base = 0;
+    if (valid && (int)lane == leader) base = atomicAdd(&wq.bin_cursor[bin], (unsigned)__popc(grp));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (valid) {
+      const unsigned dst = wq.bin_start[bin] + base + __popc(grp & ((1u << lane) - 1u));
+#pragma unroll
+      for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = wq.stf[(size_t)k * wq.cap + s];
+      wq.icfg[dst] = wq.scfg[s];
+      wq.ipair[dst] = p;
+    }
   }
 }
 
@@ -276,80 +374,6 @@ __device__ __forceinline__ V3 rot_t(const float *R, V3 v) {
 }
 __device__ __forceinline__ bool is_zero(float v) { return fabsf(v) < MPB_EPS; }
 
-// ---------------------------------------------------------------------------------------------- MPR
-// ccdMPRIntersect [upstream libccd v2.1 mpr.c] in the frame of shape A; B sits at (R, t).
-// Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
-template <bool SMEM>
-__device__ __forceinline__ bool mpr_intersect(const DevShape &A, V3 cA, const DevShape &B, V3 cB, const float *R, V3 t,
-                                              const float4 *__restrict__ verts, bool active, int &iters, bool &capped) {
-  V3 v0 = cA - (rot(R, cB) + t);
-  if (is_zero(v0.x) && is_zero(v0.y) && is_zero(v0.z)) v0.x += 10.f * MPB_EPS;
-  V3 v1 = v0, v2 = v0, v3p = v0;
-  V3 dir = normalized(v0 * -1.f);
-  int phase = 1;
-  bool done = !active, hit = false;
-  iters = 0;
-  capped = false;
-  for (int it = 0; it < MPB_MPR_MAX_ITERS; it++) {
-    if (__all_sync(0xffffffffu, done)) break;
-    // Minkowski support: sA(dir) - (R sB(R^T(-dir)) + t)
-    V3 sa = support_local<SMEM>(A, dir, verts);
-    V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts);
-    V3 v = sa - (rot(R, sb) + t);
-    if (done) continue;
-    iters++;
-    const float dv = dot(v, dir);
-    if (phase == 1) {
-      v1 = v;
-      if (is_zero(dv) || dv < 0.f) { done = true; continue; }
-      dir = cross(v0, v1);
-      if (is_zero(dot(dir, dir))) { done = true; hit = true; continue; }  // origin on v1 / on the v0-v1 segment
-      dir = normalized(dir);
-      phase = 2;
-    } else if (phase == 2) {
-      v2 = v;
-      if (is_zero(dv) || dv < 0.f) { done = true; continue; }
-      dir = normalized(cross(v1 - v0, v2 - v0));
-      if (dot(dir, v0) > 0.f) { V3 tmp = v1; v1 = v2; v2 = tmp; dir = dir * -1.f; }
-      phase = 3;
-    } else if (phase == 3) {
-      v3p = v;
-      if (is_zero(dv) || dv < 0.f) { done = true; continue; }
-      bool cont = false;
-      float d1 = dot(cross(v1, v3p), v0);
-      if (d1 < 0.f && !is_zero(d1)) { v2 = v3p; cont = true; }
-      if (!cont) {
-        float d2 = dot(cross(v3p, v2), v0);
-        if (d2 < 0.f && !is_zero(d2)) { v1 = v3p; cont = true; }
-      }
-      if (cont) {
-        dir = normalized(cross(v1 - v0, v2 - v0));
-      } else {
-        phase = 4;
-        dir = normalized(cross(v2 - v1, v3p - v1));
-        float de = dot(dir, v1);
-        if (is_zero(de) || de > 0.f) { done = true; hit = true; }
-      }
-    } else {
-      // refinePortal: can v4 expand the portal past the origin, and is there still progress?
-      if (!(is_zero(dv) || dv > 0.f)) { done = true; continue; }
-      float m = fminf(dv - dot(v1, dir), fminf(dv - dot(v2, dir), dv - dot(v3p, dir)));
-      if (m <= MPB_MPR_TOL) { done = true; continue; }
-      V3 v4v0 = cross(v, v0);
-      if (dot(v1, v4v0) > 0.f) {
-        if (dot(v2, v4v0) > 0.f) v1 = v; else v3p = v;
-      } else {
-        if (dot(v3p, v4v0) > 0.f) v2 = v; else v1 = v;
-      }
-      dir = normalized(cross(v2 - v1, v3p - v1));
-      float de = dot(dir, v1);
-      if (is_zero(de) || de > 0.f) { done = true; hit = true; }
-    }
-  }
-  if (!done) capped = true;
-  return hit;
-}
-
 // ---------------------------------------------------------------------------------------------- TMA staging
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
@@ -379,6 +403,8 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 }
 
 // ---------------------------------------------------------------------------------------------- narrowphase
+// ccdMPRIntersect [upstream libccd v2.1 mpr.c] in the frame of shape A; B sits at (R, t).
+// Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
 template <bool SMEM>
 __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
                                                      unsigned int *__restrict__ pair_bits) {
@@ -386,7 +412,6 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
   if (SMEM) {
-    float4 *sv = reinterpret_cast<float4 *>(smem_raw);
     const unsigned total = (unsigned)img.n_verts * 16u;
     if (threadIdx.x == 0) {
       mbar_init(&bar, 1);
@@ -401,52 +426,146 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
       }
     }
     if (total > 0) mbar_wait(&bar, 0);
-    verts = sv;
+    verts = reinterpret_cast<const float4 *>(smem_raw);
   }
+  const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
-  const unsigned warps_total = (gridDim.x * blockDim.x) >> 5;
-  const unsigned warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const unsigned n_units = wq.totals[1];
   unsigned long long it_sum = 0, cap_sum = 0;
-  for (unsigned u = warp_id; u < n_units; u += warps_total) {
-    // bin of this unit: largest b with unit_start[b] <= u
-    int lo = 0, hi = img.n_bins;
+  for (;;) {
+    // dynamic unit ticket (one atomic per warp per MPB_UNIT_ITEMS items)
+    unsigned u = 0;
+    if (lane == 0) u = atomicAdd(&wq.totals[3], 1u);
+    u = __shfl_sync(FULL, u, 0);
+    if (u >= n_units) break;
+    int lo = 0, hi = img.n_bins;  // bin of this unit: largest b with unit_start[b] <= u
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
       if (wq.unit_start[mid] <= u) lo = mid; else hi = mid;
     }
-    const unsigned first = wq.bin_start[lo] + ((u - wq.unit_start[lo]) << 5);
-    const unsigned end = wq.bin_start[lo + 1];
-    const unsigned idx = first + lane;
-    const bool active = idx < end && idx < wq.cap;
-    const unsigned ld = active ? idx : first;  // inactive lanes mirror the first item (same hulls)
+    unsigned next = wq.bin_start[lo] + (u - wq.unit_start[lo]) * MPB_UNIT_ITEMS;
+    const unsigned end = min(min(wq.bin_start[lo + 1], next + MPB_UNIT_ITEMS), wq.cap);
+    const unsigned first = next;
+
+    // per-lane item state
+    bool busy = false;
     float R[9];
+    V3 t = v3(0.f, 0.f, 0.f), v0 = t, v1 = t, v2 = t, v3p = t, dir = v3(1.f, 0.f, 0.f), cA = t, cBl = t;
+    DevShape A, B;
+    int cfg = 0, p = 0, phase = 1, iters = 0;
+    {
+      // shapes are uniform over the bin: read them once from the first item of the slice
+      const DevPair pr0 = img.pairs[wq.ipair[first]];
+      const DevObject &OA = img.objs[pr0.a];
+      const DevObject &OB = img.objs[pr0.b];
+      A = shape_of(OA); B = shape_of(OB);
 #pragma unroll
-    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + ld];
-    V3 t = v3(wq.itf[(size_t)9 * wq.cap + ld], wq.itf[(size_t)10 * wq.cap + ld], wq.itf[(size_t)11 * wq.cap + ld]);
-    const int cfg = wq.icfg[ld];
-    const int p = wq.ipair[ld];
-    const DevPair pr = img.pairs[p];
-    const DevObject &OA = img.objs[pr.a];
-    const DevObject &OB = img.objs[pr.b];
-    const DevShape A = shape_of(OA), B = shape_of(OB);
-    int iters;
-    bool capped;
-    const bool hit = mpr_intersect<SMEM>(A, v3(OA.ctr[0], OA.ctr[1], OA.ctr[2]), B, v3(OB.ctr[0], OB.ctr[1], OB.ctr[2]), R, t,
-                                         verts, active, iters, capped);
-    if (active) {
-      it_sum += (unsigned)iters;
-      cap_sum += capped ? 1u : 0u;
-      if (hit) {
-        atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
-        if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
+      for (int k = 0; k < 9; k++) R[k] = (k % 4 == 0) ? 1.f : 0.f;
+    }
+    for (;;) {
+      // ---- refill idle lanes from the slice
+      const unsigned need = __ballot_sync(FULL, !busy);
+      if (need) {
+        const unsigned my = next + __popc(need & ((1u << lane) - 1u));
+        if (!busy && my < end) {
+#pragma unroll
+          for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + my];
+          t = v3(wq.itf[(size_t)9 * wq.cap + my], wq.itf[(size_t)10 * wq.cap + my], wq.itf[(size_t)11 * wq.cap + my]);
+          cfg = wq.icfg[my];
+          p = wq.ipair[my];
+          const DevPair pr = img.pairs[p];
+          const DevObject &OA = img.objs[pr.a];
+          const DevObject &OB = img.objs[pr.b];
+          A.p0 = OA.prm[0]; A.p1 = OA.prm[1]; A.p2 = OA.prm[2];  // primitive parameters differ per item
+          B.p0 = OB.prm[0]; B.p1 = OB.prm[1]; B.p2 = OB.prm[2];
+          cA = v3(OA.ctr[0], OA.ctr[1], OA.ctr[2]);
+          cBl = v3(OB.ctr[0], OB.ctr[1], OB.ctr[2]);
+          v0 = cA - (rot(R, cBl) + t);
+          if (is_zero(v0.x) && is_zero(v0.y) && is_zero(v0.z)) v0.x += 10.f * MPB_EPS;
+          dir = normalized(v0 * -1.f);
+          phase = 1;
+          iters = 0;
+          busy = true;
+        }
+        next += __popc(need);
+        if (__ballot_sync(FULL, busy) == 0) break;  // slice exhausted and every lane finished
+      }
+      // ---- one Minkowski support for every lane: sA(dir) - (R sB(R^T(-dir)) + t)
+      const V3 sa = support_local<SMEM>(A, dir, verts);
+      const V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts);
+      const V3 v = sa - (rot(R, sb) + t);
+      if (!busy) continue;
+      iters++;
+      bool done = false, hit = false;
+      const float dv = dot(v, dir);
+      if (phase == 1) {
+        v1 = v;
+        if (is_zero(dv) || dv < 0.f) done = true;
+        else {
+          dir = cross(v0, v1);
+          if (is_zero(dot(dir, dir))) { done = true; hit = true; }  // origin on v1 / on the v0-v1 segment
+          else { dir = normalized(dir); phase = 2; }
+        }
+      } else if (phase == 2) {
+        v2 = v;
+        if (is_zero(dv) || dv < 0.f) done = true;
+        else {
+          dir = normalized(cross(v1 - v0, v2 - v0));
+          if (dot(dir, v0) > 0.f) { V3 tmp = v1; v1 = v2; v2 = tmp; dir = dir * -1.f; }
+          phase = 3;
+        }
+      } else if (phase == 3) {
+        v3p = v;
+        if (is_zero(dv) || dv < 0.f) done = true;
+        else {
+          bool cont = false;
+          const float d1 = dot(cross(v1, v3p), v0);
+          if (d1 < 0.f && !is_zero(d1)) { v2 = v3p; cont = true; }
+          if (!cont) {
+            const float d2 = dot(cross(v3p, v2), v0);
+            if (d2 < 0.f && !is_zero(d2)) { v1 = v3p; cont = true; }
+          }
+          if (cont) dir = normalized(cross(v1 - v0, v2 - v0));
+          else {
+            phase = 4;
+            dir = normalized(cross(v2 - v1, v3p - v1));
+            const float de = dot(dir, v1);
+            if (is_zero(de) || de > 0.f) { done = true; hit = true; }
+          }
+        }
+      } else {
+        // refinePortal: can v4 expand the portal past the origin, and is there still progress?
+        if (!(is_zero(dv) || dv > 0.f)) done = true;
+        else {
+          const float m = fminf(dv - dot(v1, dir), fminf(dv - dot(v2, dir), dv - dot(v3p, dir)));
+          if (m <= MPB_MPR_TOL) done = true;
+          else {
+            const V3 v4v0 = cross(v, v0);
+            if (dot(v1, v4v0) > 0.f) {
+              if (dot(v2, v4v0) > 0.f) v1 = v; else v3p = v;
+            } else {
+              if (dot(v3p, v4v0) > 0.f) v2 = v; else v1 = v;
+            }
+            dir = normalized(cross(v2 - v1, v3p - v1));
+            const float de = dot(dir, v1);
+            if (is_zero(de) || de > 0.f) { done = true; hit = true; }
+          }
+        }
+      }
+      if (!done && iters >= MPB_MPR_MAX_ITERS) { done = true; cap_sum++; }
+      if (done) {
+        busy = false;
+        it_sum += (unsigned)iters;
+        if (hit) {
+          atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
+          if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
+        }
       }
     }
   }
-  // per-warp reduction of the counters
   for (int o = 16; o > 0; o >>= 1) {
-    it_sum += __shfl_xor_sync(0xffffffffu, it_sum, o);
-    cap_sum += __shfl_xor_sync(0xffffffffu, cap_sum, o);
+    it_sum += __shfl_xor_sync(FULL, it_sum, o);
+    cap_sum += __shfl_xor_sync(FULL, cap_sum, o);
   }
   if (lane == 0 && it_sum) atomicAdd(&wq.counters[1], it_sum);
   if (lane == 0 && cap_sum) atomicAdd(&wq.counters[2], cap_sum);

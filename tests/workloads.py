@@ -32,5 +32,111 @@ def c2(batch=0):
     }
 
 
+
+
+def _rand_rot(rng):
+    """Uniform rotation (unit quaternion w,x,y,z) from 3 uniforms (Shoemake)."""
+    u1, u2, u3 = rng.random(3)
+    return np.array([np.sqrt(u1) * np.cos(2 * np.pi * u3), np.sqrt(1 - u1) * np.sin(2 * np.pi * u2),
+                     np.sqrt(1 - u1) * np.cos(2 * np.pi * u2), np.sqrt(u1) * np.sin(2 * np.pi * u3)])
+
+
+def _shell_point(rng):
+    while True:
+        p = rng.uniform(-1.0, 1.0, 3)
+        r = np.linalg.norm(p)
+        if 0.30 <= r <= 1.0 and p[2] >= 0:
+            return p
+
+
+def box_surface_points(rng, n, size, center):
+    """Area-weighted uniform samples on the surface of an axis-aligned box (trimesh.sample stand-in,
+    examples/detect_collision.py:36-46)."""
+    sx, sy, sz = size
+    areas = np.array([sy * sz, sy * sz, sx * sz, sx * sz, sx * sy, sx * sy])
+    face = rng.choice(6, size=n, p=areas / areas.sum())
+    uv = rng.random((n, 2)) - 0.5
+    pts = np.zeros((n, 3))
+    for f in range(6):
+        m = face == f
+        ax = f // 2
+        sign = 1.0 if f % 2 == 0 else -1.0
+        o = [a for a in range(3) if a != ax]
+        pts[m, ax] = sign * 0.5 * size[ax]
+        pts[m, o[0]] = uv[m, 0] * size[o[0]]
+        pts[m, o[1]] = uv[m, 1] * size[o[1]]
+    return pts + np.asarray(center)[None, :]
+
+
+def add_c3_primitives(world, n_each=32, seed=3):
+    """n_each spheres, boxes, capsules, cylinders in the half-shell 0.3<=|p|<=1, z>=0."""
+    from mplib_b200.pymp import fcl
+
+    rng = np.random.Generator(np.random.PCG64(seed))
+    k = 0
+    for kind in ("sphere", "box", "capsule", "cylinder"):
+        for _ in range(n_each):
+            if kind == "sphere":
+                g = fcl.Sphere(rng.uniform(0.02, 0.10))
+            elif kind == "box":
+                g = fcl.Box(rng.uniform(0.04, 0.20, 3))
+            elif kind == "capsule":
+                g = fcl.Capsule(rng.uniform(0.02, 0.05), rng.uniform(0.05, 0.30))
+            else:
+                g = fcl.Cylinder(rng.uniform(0.02, 0.05), rng.uniform(0.05, 0.30))
+            world.add_normal_object(f"{kind}_{k}", fcl.CollisionObject(g, _shell_point(rng), _rand_rot(rng)))
+            k += 1
+
+
+def attach_c3_box(world):
+    """Grasped box on panda_hand (examples/collision_avoidance.py:88-90); touch links = hand + fingers."""
+    from mplib_b200.pymp import fcl
+
+    art = world.get_articulation("robot")
+    link_id = art.get_user_link_names().index("panda_hand")
+    world.attach_object("grasped", fcl.Box([0.04, 0.04, 0.12]), "robot", link_id, [0, 0, 0.14, 1, 0, 0, 0],
+                        ["panda_hand", "panda_leftfinger", "panda_rightfinger"])
+
+
+def c3_world(n_each=32, mesh=True, cloud_points=100000, primitives=True, attach=True):
+    import os
+
+    from mplib_b200.pymp import fcl
+    from tests.common import ROOT
+
+    w = make_panda_world(convex=True)
+    if primitives:
+        add_c3_primitives(w, n_each)
+    if attach:
+        attach_c3_box(w)
+    if mesh:
+        m = fcl.load_mesh_as_BVH(os.path.join(ROOT, "data/panda/franka_description/meshes/collision/link0.stl"))
+        w.add_normal_object("mesh_obstacle", fcl.CollisionObject(m, [0.6, 0.3, 0.2], [1, 0, 0, 0]))
+    if cloud_points:
+        rng = np.random.Generator(np.random.PCG64(4))
+        n1 = cloud_points // 2
+        pts = np.concatenate([box_surface_points(rng, n1, (0.8, 0.8, 0.05), (0.56, 0, -0.025)),
+                              box_surface_points(rng, cloud_points - n1, (0.05, 1.0, 0.8), (0.9, 0, 0.4))])
+        w.add_point_cloud("cloud", pts, 0.01)
+    return w
+
+
+def c3(batch=0, **kw):
+    """configs[2]: Panda + grasped box vs 128 primitives + 1 mesh + 100k-point octree, ACM-masked."""
+    n = batch or (1 << 22)
+    w = c3_world(**kw)
+    desc = compile_desc(w)
+    return {
+        "world": w, "desc": desc, "batch": n,
+        "make_q": lambda k, m: random_q(m, 2 + 7919 * k).astype(np.float32),
+        "config": {"workload": "configs[2]: Panda + grasped box (AttachedBody) vs 128 primitives + 1 mesh + 100k-point "
+                               f"octree, ACM-masked, {n} random configurations per GPU per step (seed 2)",
+                   "states_per_gpu": n, "state_dim": desc.state_dim, "pairs": desc.n_pairs,
+                   "outputs": "verdict bit + pair mask per configuration",
+                   "l2_policy": "rotating pool of input batches > 126 MB"},
+        "flop_model": _flop_model(desc),
+    }
+
+
 def get(name, batch=0):
-    return {"c2": c2}[name](batch)
+    return {"c2": c2, "c3": c3}[name](batch)
