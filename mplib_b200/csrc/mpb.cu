@@ -3,6 +3,7 @@
 // There is no CPU compute path here: every batch entry point launches the sm_100a kernels of
 // mpb_kernels.cuh or fails with MPB_ERR_CUDA.
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -43,6 +44,11 @@ struct mpb_scene {
   float *d_linkL = nullptr;
   int *d_linkJoint = nullptr;
   int *d_dynlist = nullptr;
+  DevBvhNode *d_nodes = nullptr;
+  float4 *d_prims = nullptr;
+  int *d_pair_bin2 = nullptr;
+  size_t pair_bin2_cap = 0;
+  std::vector<int> h_pair_bin2;
   SceneImg img{};
   int cull_block = 128;
   size_t cull_smem = 0;
@@ -182,27 +188,123 @@ static void bound_box(double hx, double hy, double hz, DevObject &O) {
   O.br = (float)(sqrt(hx * hx + hy * hy + hz * hz) + pad);
 }
 
+// ------------------------------------------------------------------------------------------ BVH over leaf primitives
+struct HostPrim {
+  float4 a, b, c;      // TRI: vertices; VBOX: centre, half extents, unused
+  double lo[3], hi[3];
+};
+
+static int build_bvh(std::vector<HostPrim> &prims, int first, int count, std::vector<DevBvhNode> &nodes) {
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  double clo[3] = {1e300, 1e300, 1e300}, chi[3] = {-1e300, -1e300, -1e300};
+  for (int i = first; i < first + count; i++)
+    for (int a = 0; a < 3; a++) {
+      lo[a] = std::min(lo[a], prims[i].lo[a]);
+      hi[a] = std::max(hi[a], prims[i].hi[a]);
+      const double cc = 0.5 * (prims[i].lo[a] + prims[i].hi[a]);
+      clo[a] = std::min(clo[a], cc);
+      chi[a] = std::max(chi[a], cc);
+    }
+  const int me = (int)nodes.size();
+  nodes.push_back(DevBvhNode{});
+  for (int a = 0; a < 3; a++) {
+    nodes[me].c[a] = (float)(0.5 * (lo[a] + hi[a]));
+    nodes[me].h[a] = (float)(0.5 * (hi[a] - lo[a]) + 1e-6);
+  }
+  if (count <= 2) {
+    nodes[me].left = ~first;
+    nodes[me].right = count;
+    return me;
+  }
+  int ax = 0;
+  if (chi[1] - clo[1] > chi[ax] - clo[ax]) ax = 1;
+  if (chi[2] - clo[2] > chi[ax] - clo[ax]) ax = 2;
+  const int mid = first + count / 2;
+  std::nth_element(prims.begin() + first, prims.begin() + mid, prims.begin() + first + count,
+                   [ax](const HostPrim &x, const HostPrim &y) { return x.lo[ax] + x.hi[ax] < y.lo[ax] + y.hi[ax]; });
+  const int l = build_bvh(prims, first, mid - first, nodes);
+  const int r = build_bvh(prims, mid, first + count - mid, nodes);
+  nodes[me].left = l;
+  nodes[me].right = r;
+  return me;
+}
+
+// Occupied cells -> exact cover by axis-aligned boxes: runs along x, equal runs merged along y, then z.
+// The union of the boxes equals the union of the cells (what octomap's pruning also preserves).
+struct CellBox { int lo[3], hi[3]; };  // inclusive cell ranges
+static std::vector<CellBox> merge_cells(const int32_t *cells, int n) {
+  std::vector<std::array<int, 3>> c(n);
+  for (int i = 0; i < n; i++) c[i] = {cells[3 * i + 2], cells[3 * i + 1], cells[3 * i]};  // sort key (z, y, x)
+  std::sort(c.begin(), c.end());
+  c.erase(std::unique(c.begin(), c.end()), c.end());
+  std::vector<CellBox> runs;
+  for (size_t i = 0; i < c.size();) {
+    size_t j = i + 1;
+    while (j < c.size() && c[j][0] == c[i][0] && c[j][1] == c[i][1] && c[j][2] == c[j - 1][2] + 1) j++;
+    runs.push_back(CellBox{{c[i][2], c[i][1], c[i][0]}, {c[j - 1][2], c[i][1], c[i][0]}});
+    i = j;
+  }
+  for (int axis = 1; axis <= 2; axis++) {  // merge boxes identical in the other two axes and adjacent along `axis`
+    const int o1 = axis == 1 ? 0 : 0, o2 = axis == 1 ? 2 : 1;
+    std::sort(runs.begin(), runs.end(), [&](const CellBox &x, const CellBox &y) {
+      if (x.lo[o1] != y.lo[o1]) return x.lo[o1] < y.lo[o1];
+      if (x.hi[o1] != y.hi[o1]) return x.hi[o1] < y.hi[o1];
+      if (x.lo[o2] != y.lo[o2]) return x.lo[o2] < y.lo[o2];
+      if (x.hi[o2] != y.hi[o2]) return x.hi[o2] < y.hi[o2];
+      return x.lo[axis] < y.lo[axis];
+    });
+    std::vector<CellBox> out;
+    for (const CellBox &b : runs) {
+      if (!out.empty()) {
+        CellBox &l = out.back();
+        if (l.lo[o1] == b.lo[o1] && l.hi[o1] == b.hi[o1] && l.lo[o2] == b.lo[o2] && l.hi[o2] == b.hi[o2] &&
+            l.hi[axis] + 1 == b.lo[axis]) {
+          l.hi[axis] = b.hi[axis];
+          continue;
+        }
+      }
+      out.push_back(b);
+    }
+    runs.swap(out);
+  }
+  return runs;
+}
+
 static int geom_key(int type, int geom) { return type == MPB_GEOM_CONVEX ? 16 + geom : type; }
 
 static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32_t *pb) {
   const int no = (int)s->h_objs.size();
-  std::map<std::pair<int, int>, int> bins;
+  std::map<std::pair<int, int>, int> bins, bins2;
   s->h_pairs.resize(n_pairs);
+  s->h_pair_bin2.assign(n_pairs, -1);
+  int expand_bin = -1;
   for (int p = 0; p < n_pairs; p++) {
     int a = pa[p], b = pb[p];
     if (a < 0 || a >= no || b < 0 || b >= no) return fail(MPB_ERR_INVALID, "pair index out of range");
-    int ta = s->h_objs[a].type, tb = s->h_objs[b].type;
-    if (ta >= MPB_GEOM_MESH || tb >= MPB_GEOM_MESH)
-      return fail(MPB_ERR_UNSUPPORTED, "mesh / octree pairs are not supported by this build yet");
-    auto key = std::make_pair(s->obj_key[a], s->obj_key[b]);
-    auto it = bins.find(key);
-    int bin = it == bins.end() ? (bins[key] = (int)bins.size()) : it->second;
+    const bool bvh_a = s->h_objs[a].type >= MPB_GEOM_MESH, bvh_b = s->h_objs[b].type >= MPB_GEOM_MESH;
+    if (bvh_a && bvh_b)
+      return fail(MPB_ERR_UNSUPPORTED, "mesh x mesh / mesh x octree pairs are not supported by this build yet");
+    int bin;
+    if (bvh_a || bvh_b) {
+      if (bvh_a) std::swap(a, b);  // device convention: A = shape, B = BVH object (pair index unchanged)
+      if (expand_bin < 0) { expand_bin = (int)bins.size(); bins[std::make_pair(-1, -1)] = expand_bin; }
+      bin = expand_bin;
+      auto key2 = std::make_pair(s->obj_key[a], (int)s->h_objs[b].vcnt);  // (shape class, leaf type)
+      auto it2 = bins2.find(key2);
+      s->h_pair_bin2[p] = it2 == bins2.end() ? (bins2[key2] = (int)bins2.size()) : it2->second;
+    } else {
+      auto key = std::make_pair(s->obj_key[a], s->obj_key[b]);
+      auto it = bins.find(key);
+      bin = it == bins.end() ? (bins[key] = (int)bins.size()) : it->second;
+    }
     if (bin > 0xffff) return fail(MPB_ERR_CAPACITY, "too many geometry-class bins");
     const int da = s->h_objs[a].dyn + 1, db = s->h_objs[b].dyn + 1;
     s->h_pairs[p] = DevPair{a, b, bin | (da << 16) | (db << 24), s->h_objs[a].br + s->h_objs[b].br + 1e-5f};
   }
   s->img.n_pairs = n_pairs;
   s->img.n_bins = (int)bins.size();
+  s->img.n_bins2 = (int)bins2.size();
+  s->img.expand_bin = expand_bin;
   s->img.pair_words = (n_pairs + 31) / 32;
   return MPB_OK;
 }
@@ -216,6 +318,13 @@ static int upload_pairs(mpb_scene *s) {
   }
   if (n) CU(cudaMemcpy(s->d_pairs, s->h_pairs.data(), n * sizeof(DevPair), cudaMemcpyHostToDevice));
   s->img.pairs = s->d_pairs;
+  if (n > s->pair_bin2_cap) {
+    if (s->d_pair_bin2) cudaFree(s->d_pair_bin2);
+    s->pair_bin2_cap = std::max<size_t>(n, 64);
+    CU(cudaMalloc(&s->d_pair_bin2, s->pair_bin2_cap * sizeof(int)));
+  }
+  if (n) CU(cudaMemcpy(s->d_pair_bin2, s->h_pair_bin2.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+  s->img.pair_bin2 = s->d_pair_bin2;
   s->chunk = 0;  // queue sizing depends on the pair count
   return MPB_OK;
 }
@@ -288,6 +397,66 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
       verts.push_back(make_float4((float)d->hull_verts[3 * i], (float)d->hull_verts[3 * i + 1], (float)d->hull_verts[3 * i + 2], 0.f));
   }
   hull_off[d->n_hulls] = (int)verts.size();
+  // BVH objects: one tree per mesh / octree in the pools
+  std::vector<DevBvhNode> nodes;
+  std::vector<float4> prims;
+  std::vector<int> mesh_root(std::max(d->n_meshes, 0), -1), oct_root(std::max(d->n_octrees, 0), -1);
+  auto finish_tree = [&](std::vector<HostPrim> &hp) -> int {
+    if (hp.empty()) return -1;
+    std::vector<DevBvhNode> local;
+    build_bvh(hp, 0, (int)hp.size(), local);
+    const int node0 = (int)nodes.size(), prim0 = (int)(prims.size() / 3);
+    for (DevBvhNode nd : local) {
+      if (nd.left >= 0) { nd.left += node0; nd.right += node0; }
+      else nd.left = ~(~nd.left + prim0);
+      nodes.push_back(nd);
+    }
+    for (const HostPrim &h : hp) { prims.push_back(h.a); prims.push_back(h.b); prims.push_back(h.c); }
+    return node0;
+  };
+  for (int m = 0; m < d->n_meshes; m++) {
+    std::vector<HostPrim> hp;
+    const double *V = d->mesh_verts + 3 * (size_t)d->mesh_vert_off[m];
+    for (int t = d->mesh_tri_off[m]; t < d->mesh_tri_off[m + 1]; t++) {
+      HostPrim h;
+      const double *P[3] = {V + 3 * d->mesh_tris[3 * t], V + 3 * d->mesh_tris[3 * t + 1], V + 3 * d->mesh_tris[3 * t + 2]};
+      h.a = make_float4((float)P[0][0], (float)P[0][1], (float)P[0][2], 0.f);
+      h.b = make_float4((float)P[1][0], (float)P[1][1], (float)P[1][2], 0.f);
+      h.c = make_float4((float)P[2][0], (float)P[2][1], (float)P[2][2], 0.f);
+      for (int a = 0; a < 3; a++) {
+        h.lo[a] = std::min(P[0][a], std::min(P[1][a], P[2][a]));
+        h.hi[a] = std::max(P[0][a], std::max(P[1][a], P[2][a]));
+      }
+      hp.push_back(h);
+    }
+    mesh_root[m] = finish_tree(hp);
+  }
+  std::vector<std::array<double, 6>> oct_bounds(std::max(d->n_octrees, 0));
+  for (int t = 0; t < d->n_octrees; t++) {
+    const int c0 = d->oct_cell_off[t], nc = d->oct_cell_off[t + 1] - c0;
+    const double res = d->oct_res[t];
+    std::vector<CellBox> boxes = merge_cells(d->oct_cells + 3 * (size_t)c0, nc);
+    std::vector<HostPrim> hp;
+    std::array<double, 6> bb = {1e300, 1e300, 1e300, -1e300, -1e300, -1e300};
+    for (const CellBox &b : boxes) {
+      HostPrim h;
+      double c[3], hh[3];
+      for (int a = 0; a < 3; a++) {
+        h.lo[a] = b.lo[a] * res;
+        h.hi[a] = (b.hi[a] + 1) * res;
+        c[a] = 0.5 * (h.lo[a] + h.hi[a]);
+        hh[a] = 0.5 * (h.hi[a] - h.lo[a]);
+        bb[a] = std::min(bb[a], h.lo[a]);
+        bb[3 + a] = std::max(bb[3 + a], h.hi[a]);
+      }
+      h.a = make_float4((float)c[0], (float)c[1], (float)c[2], 0.f);
+      h.b = make_float4((float)hh[0], (float)hh[1], (float)hh[2], 0.f);
+      h.c = make_float4(0.f, 0.f, 0.f, 0.f);
+      hp.push_back(h);
+    }
+    oct_bounds[t] = bb;
+    oct_root[t] = finish_tree(hp);
+  }
   for (int o = 0; o < d->n_objects; o++) {
     DevObject &O = s->h_objs[o];
     memset(&O, 0, sizeof(O));
@@ -338,13 +507,54 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
           for (int a = 0; a < 3; a++) c[a] += d->hull_verts[3 * (v0 + i) + a];
         for (int a = 0; a < 3; a++) O.ctr[a] = (float)(c[a] / nv);
       } break;
-      case MPB_GEOM_MESH:
-      case MPB_GEOM_OCTREE:
-        bound_box(1e3, 1e3, 1e3, O);
-        break;
+      case MPB_GEOM_MESH: {
+        const int m = O.geom;
+        if (m < 0 || m >= d->n_meshes || mesh_root[m] < 0) { delete s; return fail(MPB_ERR_INVALID, "obj_geom (mesh) out of range or empty mesh"); }
+        bound_points(d->mesh_verts + 3 * (size_t)d->mesh_vert_off[m], d->mesh_vert_off[m + 1] - d->mesh_vert_off[m], O);
+        O.voff = mesh_root[m];
+        O.vcnt = MPB_GEOM_TRI;
+      } break;
+      case MPB_GEOM_OCTREE: {
+        const int t = O.geom;
+        if (t < 0 || t >= d->n_octrees) { delete s; return fail(MPB_ERR_INVALID, "obj_geom (octree) out of range"); }
+        if (oct_root[t] < 0) {  // empty tree: a far-away zero box that never survives the cull
+          bound_box(0, 0, 0, O);
+          O.oc[0] = O.bc[0] = 1e6f;
+          O.voff = 0; O.vcnt = MPB_GEOM_VBOX;
+          break;
+        }
+        const auto &bb = oct_bounds[t];
+        bound_box(0.5 * (bb[3] - bb[0]), 0.5 * (bb[4] - bb[1]), 0.5 * (bb[5] - bb[2]), O);
+        for (int a = 0; a < 3; a++) O.oc[a] = O.bc[a] = (float)(0.5 * (bb[a] + bb[3 + a]));
+        O.voff = oct_root[t];
+        O.vcnt = MPB_GEOM_VBOX;
+      } break;
       default:
         delete s;
         return fail(MPB_ERR_INVALID, "unknown geometry type");
+    }
+    switch (O.type) {  // ball around ctr contained in the shape (0 disables the sufficient-hit test)
+      case MPB_GEOM_SPHERE: O.rin = O.prm[0]; break;
+      case MPB_GEOM_BOX: O.rin = std::min(O.prm[0], std::min(O.prm[1], O.prm[2])); break;
+      case MPB_GEOM_CAPSULE: O.rin = O.prm[0]; break;
+      case MPB_GEOM_CYLINDER: O.rin = std::min(O.prm[0], O.prm[1]); break;
+      case MPB_GEOM_CONVEX: {
+        const int h = O.geom;
+        const double *V = d->hull_verts + 3 * (size_t)d->hull_vert_off[h];
+        double rmin = 1e300;
+        for (int f = d->hull_face_off[h]; f < d->hull_face_off[h + 1]; f++) {
+          const double *A0 = V + 3 * d->hull_faces[3 * f], *A1 = V + 3 * d->hull_faces[3 * f + 1], *A2 = V + 3 * d->hull_faces[3 * f + 2];
+          double e1[3], e2[3], nrm[3];
+          for (int a = 0; a < 3; a++) { e1[a] = A1[a] - A0[a]; e2[a] = A2[a] - A0[a]; }
+          nrm[0] = e1[1] * e2[2] - e1[2] * e2[1]; nrm[1] = e1[2] * e2[0] - e1[0] * e2[2]; nrm[2] = e1[0] * e2[1] - e1[1] * e2[0];
+          const double l = sqrt(nrm[0] * nrm[0] + nrm[1] * nrm[1] + nrm[2] * nrm[2]);
+          if (l < 1e-14) continue;
+          const double dist = fabs(((double)O.ctr[0] - A0[0]) * nrm[0] + ((double)O.ctr[1] - A0[1]) * nrm[1] + ((double)O.ctr[2] - A0[2]) * nrm[2]) / l;
+          rmin = std::min(rmin, dist);
+        }
+        O.rin = rmin < 1e299 ? (float)(0.98 * rmin) : 0.f;  // valid for a convex hull with the centre inside
+      } break;
+      default: O.rin = 0.f; break;
     }
     s->obj_key[o] = geom_key(O.type, O.geom);
   }
@@ -387,6 +597,10 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   CU(up((void **)&s->d_linkJoint, d->link_joint, (size_t)d->n_links * sizeof(int)));
   CU(up((void **)&s->d_dynlist, dynlist.data(), dynlist.size() * sizeof(int)));
   s->img.dynlist = s->d_dynlist;
+  CU(up((void **)&s->d_nodes, nodes.data(), nodes.size() * sizeof(DevBvhNode)));
+  CU(up((void **)&s->d_prims, prims.data(), prims.size() * sizeof(float4)));
+  s->img.nodes = s->d_nodes;
+  s->img.prims = s->d_prims;
   s->img.joints = s->d_joints;
   s->img.objs = s->d_objs;
   s->img.verts = s->d_verts;
@@ -421,7 +635,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q, s->d_verdict,
-                  s->d_pairbits, s->d_poses, s->d_dynlist, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_pairbits, s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto e : s->events) cudaEventDestroy(e);
@@ -483,14 +697,16 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   cap = std::max<size_t>(cap, 4096);
   if (s->wq.stf) { cudaFree(s->wq.stf); s->wq.stf = nullptr; s->wq.itf = nullptr; }
   // one slab: staging [12 f + cfg + pair][cap], then binned [12 f + cfg + pair][cap]
-  CU(cudaMalloc((void **)&s->wq.stf, cap * 28 * sizeof(float)));
+  CU(cudaMalloc((void **)&s->wq.stf, cap * 30 * sizeof(float)));
   s->wq.scfg = reinterpret_cast<int *>(s->wq.stf + cap * 12);
   s->wq.spair = s->wq.scfg + cap;
-  s->wq.itf = reinterpret_cast<float *>(s->wq.spair + cap);
+  s->wq.saux = s->wq.spair + cap;
+  s->wq.itf = reinterpret_cast<float *>(s->wq.saux + cap);
   s->wq.icfg = reinterpret_cast<int *>(s->wq.itf + cap * 12);
   s->wq.ipair = s->wq.icfg + cap;
+  s->wq.iaux = s->wq.ipair + cap;
   s->wq.cap = (unsigned)cap;
-  const size_t nb = (size_t)std::max(s->img.n_bins, 1);
+  const size_t nb = (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
   if (nb > s->bins_cap || !s->wq.bin_count) {
     if (s->wq.bin_count) cudaFree(s->wq.bin_count);
     CU(cudaMalloc((void **)&s->wq.bin_count, (4 * nb + 8) * sizeof(unsigned)));
@@ -519,7 +735,7 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
                            cudaStream_t st, long long chunk, bool *overflow, mpb_stats *stats) {
   int rc = prepare_work(s, chunk);
   if (rc != MPB_OK) return rc;
-  const int D = s->img.state_dim, W = s->img.pair_words, nb = std::max(s->img.n_bins, 1);
+  const int D = s->img.state_dim, W = s->img.pair_words, nb = std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
   const bool host = space == MPB_HOST;
   if (host) {
     CU(ensure(&s->d_q, &s->d_q_cap, (size_t)chunk * std::max(D, 1)));
@@ -551,16 +767,25 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
       cudaEvent_t e0 = get_event(s, ev++), e1 = get_event(s, ev++), e2 = get_event(s, ev++);
       CU(cudaEventRecord(e0, st));
       fk_cull_kernel<64><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, s->wq);
-      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins);
-      scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq);
+      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin);
+      scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));
-      if (s->smem_verts)
-        narrow_kernel<true><<<s->narrow_blocks, 256, (size_t)s->img.n_verts * sizeof(float4), st>>>(s->img, s->wq, dv, dp);
-      else
-        narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp);
+      const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
+      if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
+      else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
+      launches += 4;
+      if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
+        CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
+        CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
+        expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
+        scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1);
+        scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 1);
+        if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
+        else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
+        launches += 4;
+      }
       CU(cudaEventRecord(e2, st));
       CU(cudaGetLastError());
-      launches += 4;
     }
     if (host) {
       CU(cudaMemcpyAsync(verdict + off / 32, dv, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));

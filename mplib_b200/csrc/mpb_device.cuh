@@ -46,7 +46,7 @@ struct alignas(16) DevObject {
   float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
   int voff, vcnt;   // hull vertices in the pool
   float bcw[3];     // world-fixed objects: bounding-sphere centre in the world frame
-  int pad;          // sizeof == 192: float4 loads of L stay aligned
+  float rin;        // radius of a ball around ctr that lies inside the shape (sufficient-hit test); sizeof == 192
 };
 static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
 
@@ -56,6 +56,18 @@ struct DevPair {
   float rr;     // sum of the two bounding-sphere radii (+ margin)
 };
 #define MPB_MAX_SAVED 8   // kinematic branch points kept per thread
+
+// internal leaf-primitive shape types of BVH objects (meshes, octrees)
+#define MPB_GEOM_TRI 7    // triangle: prims[3*aux + 0..2] = vertices (object frame)
+#define MPB_GEOM_VBOX 8   // box cell: prims[3*aux] = centre, prims[3*aux+1] = half extents (object frame)
+
+// AABB tree over the leaf primitives of one mesh / octree, in the object's frame.
+struct alignas(16) DevBvhNode {
+  float c[3];
+  int left;    // inner: index of the left child;   leaf: ~first_prim (negative)
+  float h[3];
+  int right;   // inner: index of the right child;  leaf: primitive count
+};
 
 struct Xf {  // rigid transform, row-major rotation
   float r[9];

@@ -33,6 +33,11 @@ struct SceneImg {
   const DevPair *pairs;
   const float4 *verts;
   const int *dynlist;   // moving objects grouped by owner joint
+  const DevBvhNode *nodes;  // BVH node pool (meshes, octrees); DevObject::voff = root, ::vcnt = leaf type
+  const float4 *prims;      // leaf primitives, 3 float4 each
+  const int *pair_bin2;     // [n_pairs] bin of the leaf-level items a BVH pair expands into (-1: not a BVH pair)
+  int expand_bin;           // first-round bin that collects the BVH pairs (-1: none)
+  int n_bins2;
   const float *linkL;   // [n_links][12] link placement in its joint frame
   const int *linkJoint; // [n_links]
   int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn;
@@ -40,9 +45,9 @@ struct SceneImg {
 
 struct WorkQ {
   float *stf;            // staging: [12][cap] relative transform B in A (SoA)
-  int *scfg, *spair;     // staging: [cap]
+  int *scfg, *spair, *saux;     // staging: [cap]
   float *itf;            // binned:  [12][cap]
-  int *icfg, *ipair;     // binned:  [cap]
+  int *icfg, *ipair, *iaux;     // binned:  [cap]   aux = leaf primitive index (second round), else 0
   unsigned int *bin_count;   // [n_bins]
   unsigned int *bin_cursor;  // [n_bins]
   unsigned int *bin_start;   // [n_bins+1]
@@ -255,6 +260,7 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
             for (int k = 0; k < 3; k++) wq.stf[(size_t)(9 + k) * wq.cap + slot] = rel.p[k];
             wq.scfg[slot] = (int)i;
             wq.spair[slot] = p;
+            wq.saux[slot] = 0;
           }
           const unsigned grp = __match_any_sync(km, slot < wq.cap ? bin : -1);
           if (slot < wq.cap && lane == (unsigned)(__ffs(grp) - 1)) atomicAdd(&wq.bin_count[bin], (unsigned)__popc(grp));
@@ -270,7 +276,7 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
   }
 }
 
-__global__ void scan_bins_kernel(WorkQ wq, int n_bins) {
+__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned items = 0, units = 0;
     for (int b = 0; b < n_bins; b++) {
@@ -278,7 +284,7 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins) {
       wq.unit_start[b] = units;
       const unsigned c = wq.bin_count[b];
       items += c;
-      units += (c + MPB_UNIT_ITEMS - 1u) / MPB_UNIT_ITEMS;
+      if (b != skip_bin) units += (c + MPB_UNIT_ITEMS - 1u) / MPB_UNIT_ITEMS;  // BVH pairs go to expand_kernel instead
       wq.bin_cursor[b] = 0;
     }
     wq.bin_start[n_bins] = items;
@@ -290,14 +296,14 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins) {
   }
 }
 
-__global__ void __launch_bounds__(256) scatter_kernel(SceneImg img, WorkQ wq) {
+__global__ void __launch_bounds__(256) scatter_kernel(SceneImg img, WorkQ wq, int round) {
   const unsigned n = min(wq.totals[0], wq.cap);
   const unsigned n_round = (n + 31u) & ~31u;
   const unsigned lane = threadIdx.x & 31;
   for (unsigned s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
     const bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
     const int p = valid ? wq.spair[s] : 0;
-    const int bin = valid ? (img.pairs[p].bin_dyn & 0xffff) : (-1 - (int)lane);
+    const int bin = valid ? (round == 0 ? (img.pairs[p].bin_dyn & 0xffff) : img.pair_bin2[p]) : (-1 - (int)lane);
     const unsigned grp = __match_any_sync(0xffffffffu, bin);
     const int leader = __ffs(grp) - 1;
     unsigned base = 0;
@@ -309,6 +315,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(SceneImg img, WorkQ wq) {
       for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = wq.stf[(size_t)k * wq.cap + s];
       wq.icfg[dst] = wq.scfg[s];
       wq.ipair[dst] = p;
+      wq.iaux[dst] = wq.saux[s];
     }
   }
 }
@@ -327,7 +334,8 @@ __device__ __forceinline__ float sgn_eps(float v) { return fabsf(v) < MPB_EPS ? 
 
 // extreme point of the shape along `d` in the shape's own frame ([upstream FCL support* functions])
 template <bool SMEM>
-__device__ __forceinline__ V3 support_local(const DevShape &s, V3 d, const float4 *__restrict__ verts) {
+__device__ __forceinline__ V3 support_local(const DevShape &s, V3 d, const float4 *__restrict__ verts,
+                                         const float4 *__restrict__ prims) {
   if (s.type == MPB_GEOM_CONVEX) {
     const float4 *v = verts + s.voff;
     float best = -FLT_MAX;
@@ -358,6 +366,20 @@ __device__ __forceinline__ V3 support_local(const DevShape &s, V3 d, const float
       if (fabsf(zd) < MPB_EPS) return v3(0.f, 0.f, sgn_eps(d.z) * s.p1);
       float rad = s.p0 / zd;
       return v3(rad * d.x, rad * d.y, sgn_eps(d.z) * s.p1);
+    }
+    case MPB_GEOM_TRI: {  // [upstream] supportTriangle: the vertex with the largest projection
+      const float4 a = __ldg(prims + 3 * s.voff), b = __ldg(prims + 3 * s.voff + 1), c = __ldg(prims + 3 * s.voff + 2);
+      const float da = fmaf(a.x, d.x, fmaf(a.y, d.y, a.z * d.z)), db = fmaf(b.x, d.x, fmaf(b.y, d.y, b.z * d.z)),
+                  dc = fmaf(c.x, d.x, fmaf(c.y, d.y, c.z * d.z));
+      float4 m = a;
+      float dm = da;
+      if (db > dm) { m = b; dm = db; }
+      if (dc > dm) m = c;
+      return v3(m.x, m.y, m.z);
+    }
+    case MPB_GEOM_VBOX: {  // voxel box: supportBox shifted to the cell centre
+      const float4 c = __ldg(prims + 3 * s.voff), h = __ldg(prims + 3 * s.voff + 1);
+      return v3(fmaf(sgn_eps(d.x), h.x, c.x), fmaf(sgn_eps(d.y), h.y, c.y), fmaf(sgn_eps(d.z), h.z, c.z));
     }
     default:
       return v3(0.f, 0.f, 0.f);
@@ -407,7 +429,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 // Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
 template <bool SMEM>
 __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
-                                                     unsigned int *__restrict__ pair_bits) {
+                                                     unsigned int *__restrict__ pair_bits, int n_bins, int round) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
@@ -438,7 +460,7 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
     if (lane == 0) u = atomicAdd(&wq.totals[3], 1u);
     u = __shfl_sync(FULL, u, 0);
     if (u >= n_units) break;
-    int lo = 0, hi = img.n_bins;  // bin of this unit: largest b with unit_start[b] <= u
+    int lo = 0, hi = n_bins;  // bin of this unit: largest b with unit_start[b] <= u
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
       if (wq.unit_start[mid] <= u) lo = mid; else hi = mid;
@@ -459,6 +481,7 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
       const DevObject &OA = img.objs[pr0.a];
       const DevObject &OB = img.objs[pr0.b];
       A = shape_of(OA); B = shape_of(OB);
+      if (round == 1) B.type = OB.vcnt;  // leaf primitives of a BVH object: MPB_GEOM_TRI / MPB_GEOM_VBOX
 #pragma unroll
       for (int k = 0; k < 9; k++) R[k] = (k % 4 == 0) ? 1.f : 0.f;
     }
@@ -468,6 +491,7 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
       if (need) {
         const unsigned my = next + __popc(need & ((1u << lane) - 1u));
         if (!busy && my < end) {
+          bool busy_ok = true;
 #pragma unroll
           for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + my];
           t = v3(wq.itf[(size_t)9 * wq.cap + my], wq.itf[(size_t)10 * wq.cap + my], wq.itf[(size_t)11 * wq.cap + my]);
@@ -480,19 +504,31 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
           B.p0 = OB.prm[0]; B.p1 = OB.prm[1]; B.p2 = OB.prm[2];
           cA = v3(OA.ctr[0], OA.ctr[1], OA.ctr[2]);
           cBl = v3(OB.ctr[0], OB.ctr[1], OB.ctr[2]);
+          if (round == 1) {  // [upstream] centerTriangle = centroid; voxel Box centre = its pose
+            B.voff = wq.iaux[my];
+            const float4 a = __ldg(img.prims + 3 * B.voff);
+            if (B.type == MPB_GEOM_TRI) {
+              const float4 b = __ldg(img.prims + 3 * B.voff + 1), c = __ldg(img.prims + 3 * B.voff + 2);
+              cBl = v3((a.x + b.x + c.x) * (1.f / 3.f), (a.y + b.y + c.y) * (1.f / 3.f), (a.z + b.z + c.z) * (1.f / 3.f));
+            } else cBl = v3(a.x, a.y, a.z);
+            // early exit: this (configuration, pair) is already known to collide
+            const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
+                                         : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
+            busy_ok = !known;
+          }
           v0 = cA - (rot(R, cBl) + t);
           if (is_zero(v0.x) && is_zero(v0.y) && is_zero(v0.z)) v0.x += 10.f * MPB_EPS;
           dir = normalized(v0 * -1.f);
           phase = 1;
           iters = 0;
-          busy = true;
+          busy = !(round == 1 && !busy_ok);
         }
         next += __popc(need);
         if (__ballot_sync(FULL, busy) == 0) break;  // slice exhausted and every lane finished
       }
       // ---- one Minkowski support for every lane: sA(dir) - (R sB(R^T(-dir)) + t)
-      const V3 sa = support_local<SMEM>(A, dir, verts);
-      const V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts);
+      const V3 sa = support_local<SMEM>(A, dir, verts, img.prims);
+      const V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts, img.prims);
       const V3 v = sa - (rot(R, sb) + t);
       if (!busy) continue;
       iters++;
@@ -503,7 +539,9 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
         if (is_zero(dv) || dv < 0.f) done = true;
         else {
           dir = cross(v0, v1);
-          if (is_zero(dot(dir, dir))) { done = true; hit = true; }  // origin on v1 / on the v0-v1 segment
+          // libccd tests |v0 x v1|^2 against DBL_EPSILON (effectively exact zero); in fp32 the test must be
+          // relative to the operand lengths or centimetre-sized shapes alias to "origin on the segment"
+          if (dot(dir, dir) <= 1e-12f * dot(v0, v0) * dot(v1, v1)) { done = true; hit = true; }
           else { dir = normalized(dir); phase = 2; }
         }
       } else if (phase == 2) {
@@ -520,10 +558,10 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
         else {
           bool cont = false;
           const float d1 = dot(cross(v1, v3p), v0);
-          if (d1 < 0.f && !is_zero(d1)) { v2 = v3p; cont = true; }
+          if (d1 < 0.f) { v2 = v3p; cont = true; }  // triple products: exact sign (DBL_EPSILON-scale zero band upstream)
           if (!cont) {
             const float d2 = dot(cross(v3p, v2), v0);
-            if (d2 < 0.f && !is_zero(d2)) { v1 = v3p; cont = true; }
+            if (d2 < 0.f) { v1 = v3p; cont = true; }
           }
           if (cont) dir = normalized(cross(v1 - v0, v2 - v0));
           else {
@@ -604,6 +642,129 @@ __global__ void __launch_bounds__(128) fk_pose_kernel(SceneImg img, const float 
       float qt[4];
       mat_to_quat(w.r, qt);
       o[0] = w.p[0]; o[1] = w.p[1]; o[2] = w.p[2]; o[3] = qt[0]; o[4] = qt[1]; o[5] = qt[2]; o[6] = qt[3];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- BVH expansion
+// Thread per (configuration, shape x BVH-object) item of the first round.  Walks the object's AABB tree
+// (mesh triangles, or octree cells merged into boxes) against the shape's OBB, both in the object's frame
+// (replaces the OBBRSS descent of MeshShapeCollisionTraversalNodeOBBRSS and OcTreeSolver::
+// OcTreeShapeIntersectRecurse that ::fcl::collide runs for src/planning_world.cpp:419-434, 464-478), and
+// emits one leaf-level item per surviving primitive for the second narrowphase round.  A leaf whose closest
+// point lies inside the shape's inscribed ball is an immediate hit (no item needed).
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+
+__global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
+                                                     unsigned int *__restrict__ pair_bits) {
+  const int eb = img.expand_bin;
+  if (eb < 0) return;
+  const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
+  for (unsigned it = first + blockIdx.x * blockDim.x + threadIdx.x; it < end; it += gridDim.x * blockDim.x) {
+    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
+                                 : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
+    if (known) continue;
+    const DevPair pr = img.pairs[p];
+    const DevObject &A = img.objs[pr.a];  // the shape
+    const DevObject &B = img.objs[pr.b];  // the BVH object
+    float R[9], t[3];
+#pragma unroll
+    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
+#pragma unroll
+    for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + it];
+    // shape OBB expressed in the object frame B:  x_B = R^T (x_A - t)
+    float Ra[9], ca[3];  // OBB axes (columns) and centre in B
+    {
+      const float d0 = A.oc[0] - t[0], d1 = A.oc[1] - t[1], d2 = A.oc[2] - t[2];
+#pragma unroll
+      for (int r = 0; r < 3; r++) {
+        ca[r] = fmaf(R[r], d0, fmaf(R[3 + r], d1, R[6 + r] * d2));
+#pragma unroll
+        for (int c = 0; c < 3; c++) Ra[3 * r + c] = fmaf(R[r], A.oR[c], fmaf(R[3 + r], A.oR[3 + c], R[6 + r] * A.oR[6 + c]));
+      }
+    }
+    // inscribed-ball centre of the shape in B
+    float cin[3];
+    {
+      const float d0 = A.ctr[0] - t[0], d1 = A.ctr[1] - t[1], d2 = A.ctr[2] - t[2];
+#pragma unroll
+      for (int r = 0; r < 3; r++) cin[r] = fmaf(R[r], d0, fmaf(R[3 + r], d1, R[6 + r] * d2));
+    }
+    const float rin2 = A.rin * A.rin;
+    const int leaf_type = B.vcnt;
+    int stack[48];
+    int sp = 0;
+    stack[sp++] = B.voff;
+    bool hit = false;
+    while (sp > 0 && !hit) {
+      const DevBvhNode nd = img.nodes[stack[--sp]];
+      // node AABB (axes = identity) in the OBB's frame: Rrel = Ra^T, trel = Ra^T (c_node - ca)
+      float Rrel[9], trel[3];
+      const float e0 = nd.c[0] - ca[0], e1 = nd.c[1] - ca[1], e2 = nd.c[2] - ca[2];
+#pragma unroll
+      for (int r = 0; r < 3; r++) {
+        trel[r] = fmaf(Ra[r], e0, fmaf(Ra[3 + r], e1, Ra[6 + r] * e2));
+#pragma unroll
+        for (int c = 0; c < 3; c++) Rrel[3 * r + c] = Ra[3 * c + r];
+      }
+      if (obb_disjoint(Rrel, trel, A.oh, nd.h)) continue;
+      if (nd.left >= 0) {
+        if (sp + 2 <= 48) { stack[sp++] = nd.left; stack[sp++] = nd.right; }
+        continue;
+      }
+      const int pfirst = ~nd.left;
+      for (int k = 0; k < nd.right && !hit; k++) {
+        const int prim = pfirst + k;
+        const float4 a = __ldg(img.prims + 3 * prim), b = __ldg(img.prims + 3 * prim + 1);
+        float pc[3], ph[3];
+        if (leaf_type == MPB_GEOM_VBOX) {
+          pc[0] = a.x; pc[1] = a.y; pc[2] = a.z; ph[0] = b.x; ph[1] = b.y; ph[2] = b.z;
+        } else {
+          const float4 c = __ldg(img.prims + 3 * prim + 2);
+          const float lo0 = fminf(a.x, fminf(b.x, c.x)), hi0 = fmaxf(a.x, fmaxf(b.x, c.x));
+          const float lo1 = fminf(a.y, fminf(b.y, c.y)), hi1 = fmaxf(a.y, fmaxf(b.y, c.y));
+          const float lo2 = fminf(a.z, fminf(b.z, c.z)), hi2 = fmaxf(a.z, fmaxf(b.z, c.z));
+          pc[0] = 0.5f * (lo0 + hi0); pc[1] = 0.5f * (lo1 + hi1); pc[2] = 0.5f * (lo2 + hi2);
+          ph[0] = 0.5f * (hi0 - lo0) + 1e-6f; ph[1] = 0.5f * (hi1 - lo1) + 1e-6f; ph[2] = 0.5f * (hi2 - lo2) + 1e-6f;
+        }
+        if (nd.right > 1 || leaf_type == MPB_GEOM_TRI) {  // primitive-level reject
+          const float g0 = pc[0] - ca[0], g1 = pc[1] - ca[1], g2 = pc[2] - ca[2];
+          float tr[3];
+#pragma unroll
+          for (int r = 0; r < 3; r++) tr[r] = fmaf(Ra[r], g0, fmaf(Ra[3 + r], g1, Ra[6 + r] * g2));
+          if (obb_disjoint(Rrel, tr, A.oh, ph)) continue;
+        }
+        if (leaf_type == MPB_GEOM_VBOX && rin2 > 0.f) {  // sufficient test: cell touches the inscribed ball
+          const float q0 = clampf(cin[0], pc[0] - ph[0], pc[0] + ph[0]) - cin[0];
+          const float q1 = clampf(cin[1], pc[1] - ph[1], pc[1] + ph[1]) - cin[1];
+          const float q2 = clampf(cin[2], pc[2] - ph[2], pc[2] + ph[2]) - cin[2];
+          if (fmaf(q0, q0, fmaf(q1, q1, q2 * q2)) < rin2) { hit = true; break; }
+        }
+        // emit a leaf-level item (warp-aggregated slot allocation)
+        cg::coalesced_group g = cg::coalesced_threads();
+        unsigned base = 0;
+        if (g.thread_rank() == 0) base = atomicAdd(&wq.totals[0], (unsigned)g.size());
+        base = g.shfl(base, 0);
+        const unsigned slot = base + g.thread_rank();
+        if (slot < wq.cap) {
+#pragma unroll
+          for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = R[k2];
+#pragma unroll
+          for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = t[k2];
+          wq.scfg[slot] = cfg;
+          wq.spair[slot] = p;
+          wq.saux[slot] = prim;
+          atomicAdd(&wq.bin_count[img.pair_bin2[p]], 1u);
+        }
+      }
+    }
+    if (hit) {
+      atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
+      if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
     }
   }
 }

@@ -785,6 +785,44 @@ int orc_collide_batch_mt(const mpb_scene_desc *d, const double *states, int64_t 
 /* Band classifier for one (state, pair): signed distance estimate.  > 0: GJK separation distance;
  * < 0: -(MPR penetration depth) (an upper bound of the true depth => |value| >= true depth);
  * mesh/octree pairs return NaN (callers treat those with the exhaustive-leaf margin test). */
+static double leafset_signed_distance(const mpb_scene_desc *d, int ob, const xf_t *Tb, int os, const xf_t *Ts) {
+  /* ob = mesh or octree object, os = shape.  Separated: min leaf distance; intersecting: -(max leaf MPR depth). */
+  shape_t S; shape_from_object(d, os, Ts, &S);
+  double cl[3]; double rad = shape_bound_radius(d, os, cl);
+  double mind = DBL_MAX, maxdepth = -1.0;
+  if (d->obj_type[ob] == MPB_GEOM_OCTREE) {
+    int t = d->obj_geom[ob]; double res = d->oct_res[t];
+    const int32_t *C = d->oct_cells + 3 * d->oct_cell_off[t];
+    int nc = d->oct_cell_off[t + 1] - d->oct_cell_off[t];
+    double cs[3]; xf_apply_inv(cs, Tb, Ts->p);
+    double reach = rad + 0.5 * res * sqrt(3.0) + 0.01;
+    shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+    for (int i = 0; i < nc; i++) {
+      double c[3] = {(C[3 * i] + 0.5) * res, (C[3 * i + 1] + 0.5) * res, (C[3 * i + 2] + 0.5) * res};
+      double dd[3]; sub3(dd, c, cs);
+      if (len2_3(dd) > reach * reach) continue;
+      bx.T = *Tb; xf_apply(bx.T.p, Tb, c);
+      double g = gjk_distance(&bx, &S);
+      if (g > 0) { if (g < mind) mind = g; }
+      else { double pd = mpr_penetration_depth(&bx, &S); if (pd < 0) pd = 0; if (pd > maxdepth) maxdepth = pd; }
+    }
+  } else {
+    int m = d->obj_geom[ob];
+    const double *V = d->mesh_verts + 3 * d->mesh_vert_off[m];
+    const int32_t *Tr = d->mesh_tris + 3 * d->mesh_tri_off[m];
+    int nt = d->mesh_tri_off[m + 1] - d->mesh_tri_off[m];
+    for (int t = 0; t < nt; t++) {
+      shape_t tri; memset(&tri, 0, sizeof(tri)); tri.type = ORC_TRI; tri.T = *Tb;
+      copy3(tri.tri, V + 3 * Tr[3 * t]); copy3(tri.tri + 3, V + 3 * Tr[3 * t + 1]); copy3(tri.tri + 6, V + 3 * Tr[3 * t + 2]);
+      double g = gjk_distance(&S, &tri);
+      if (g > 0) { if (g < mind) mind = g; }
+      else { double pd = mpr_penetration_depth(&S, &tri); if (pd < 0) pd = 0; if (pd > maxdepth) maxdepth = pd; }
+    }
+  }
+  if (maxdepth >= 0) return -maxdepth;
+  return mind;
+}
+
 int orc_pair_signed_distance(const mpb_scene_desc *d, const double *state, int pair, double *out) {
   xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
   xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
@@ -792,7 +830,9 @@ int orc_pair_signed_distance(const mpb_scene_desc *d, const double *state, int p
   scatter_state(d, state, qf); fk_joints(d, qf, oMi); object_transforms(d, oMi, objT, NULL);
   int a = d->pair_a[pair], b = d->pair_b[pair];
   int ta = d->obj_type[a], tb = d->obj_type[b];
-  if (ta >= MPB_GEOM_MESH || tb >= MPB_GEOM_MESH) { *out = NAN; }
+  if (ta >= MPB_GEOM_MESH && tb >= MPB_GEOM_MESH) { *out = NAN; }
+  else if (ta >= MPB_GEOM_MESH) *out = leafset_signed_distance(d, a, &objT[a], b, &objT[b]);
+  else if (tb >= MPB_GEOM_MESH) *out = leafset_signed_distance(d, b, &objT[b], a, &objT[a]);
   else {
     shape_t A, B; shape_from_object(d, a, &objT[a], &A); shape_from_object(d, b, &objT[b], &B);
     double g = gjk_distance(&A, &B);

@@ -73,3 +73,54 @@ def test_ragged_and_empty(panda_world):
         v, ph = dev.collide(q)
         v2, ph2 = dev.collide(q[::-1].copy())
         assert np.array_equal(v, v2[::-1]) and np.array_equal(ph, ph2[::-1])
+
+
+def _env_parity(world, n, seed, max_mismatch):
+    from oracle import oracle as O
+
+    q = random_q(n, seed)
+    c = world._sync()
+    desc = c["dev"].desc
+    v, ph, st = c["dev"].collide(q, want_pairs=True, stats=True)
+    qd = q.astype(np.float32).astype(np.float64)
+    ov, oph = O.collide_batch(desc, qd, threads=8)
+    mism = np.argwhere(ph != oph)
+    bad = []
+    for i, p in mism:
+        sd = O.pair_signed_distance(desc, qd[i], int(p))
+        if not (abs(sd) < BAND):
+            bad.append((int(i), int(p), desc.pair_kinds[p], desc.object_names[desc.pair_a[p]], desc.object_names[desc.pair_b[p]],
+                        bool(ph[i, p]), bool(oph[i, p]), sd))
+    print(f"pairs={desc.n_pairs} mismatches={len(mism)} out-of-band={len(bad)} collide-rate={ov.mean():.3f} stats={st}")
+    assert not bad, bad[:10]
+    assert len(mism) <= max_mismatch
+    assert np.array_equal(v, ph.any(axis=1))
+    assert st["narrow_capped"] <= max(2, n // 1000)
+    # verdict-only mode (early exits enabled) must give the same verdicts
+    v2, _ = c["dev"].collide(q, want_pairs=False)
+    assert np.array_equal(v2, v)
+
+
+def test_env_primitives_attached():
+    """C3 minus mesh and cloud: 128 primitives + grasped box (AttachedBody), ACM touch links."""
+    from tests.workloads import c3_world
+
+    _env_parity(c3_world(mesh=False, cloud_points=0), 3000, 21, 30)
+
+
+def test_env_octree():
+    from tests.workloads import c3_world
+
+    _env_parity(c3_world(primitives=False, mesh=False, cloud_points=20000, attach=True), 3000, 22, 30)
+
+
+def test_env_mesh():
+    from tests.workloads import c3_world
+
+    _env_parity(c3_world(primitives=False, mesh=True, cloud_points=0, attach=True), 3000, 23, 30)
+
+
+def test_env_full_c3():
+    from tests.workloads import c3_world
+
+    _env_parity(c3_world(), 1500, 24, 30)
