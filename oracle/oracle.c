@@ -934,3 +934,19 @@ double orc_object_distance(const mpb_scene_desc *d, int a, const double *Ta12, i
   shape_t A, B; shape_from_object(d, a, &Ta, &A); shape_from_object(d, b, &Tb, &B);
   return gjk_distance(&A, &B);
 }
+
+/* Batched orc_sat_pair over (state index, pair) items on `nthreads` OpenMP threads (tests). */
+int orc_sat_batch_mt(const mpb_scene_desc *d, const double *states, int64_t n_items, const int64_t *item_state,
+                     const int32_t *item_pair, double *gap_out, int nthreads) {
+  int rc = 0;
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 8)
+  for (int64_t k = 0; k < n_items; k++) {
+    int r = orc_sat_pair(d, states + item_state[k] * d->state_dim, item_pair[k], gap_out + k);
+    if (r != 0) {
+#pragma omp atomic write
+      rc = r;
+    }
+  }
+  return rc;
+}

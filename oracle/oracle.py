@@ -83,6 +83,19 @@ def sat_pair(desc, state, pair):
     return out.value
 
 
+def sat_batch(desc, states, item_state, item_pair, threads=8):
+    s = _states(desc, states)
+    ist = np.ascontiguousarray(np.asarray(item_state, dtype=np.int64))
+    ip = np.ascontiguousarray(np.asarray(item_pair, dtype=np.int32))
+    out = np.zeros(ist.shape[0], dtype=np.float64)
+    rc = lib().orc_sat_batch_mt(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(ist.shape[0]),
+                                C.c_void_p(ist.ctypes.data), C.c_void_p(ip.ctypes.data), C.c_void_p(out.ctypes.data),
+                                C.c_int(int(threads)))
+    if rc != 0:
+        raise ValueError("orc_sat_batch_mt: a pair is not convex/convex")
+    return out
+
+
 def distance_batch(desc, states):
     s = _states(desc, states)
     n = s.shape[0]
