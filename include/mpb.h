@@ -119,6 +119,8 @@ typedef struct mpb_stats {
   float gpu_ms;              /* device time of the call's kernels (CUDA events)      */
   float gpu_ms_cull;         /* FK + broadphase kernels                              */
   float gpu_ms_narrow;       /* narrowphase kernel(s)                                */
+  float host_ms_enqueue;     /* host time spent issuing the call's copies and launches */
+  float host_ms_total;       /* host wall time of the call, including the final synchronisation */
 } mpb_stats;
 
 /* Thread-local message of the last failing call on this thread. */

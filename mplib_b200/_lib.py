@@ -86,8 +86,8 @@ class DeviceScene:
         self.n_links = desc.n_links
 
     def close(self):
-        if getattr(self, "_h", None):
-            load().mpb_scene_destroy(self._h)
+        if getattr(self, "_h", None) and _lib is not None:  # _lib is None during interpreter shutdown
+            _lib.mpb_scene_destroy(self._h)
             self._h = None
 
     __del__ = close

@@ -4,8 +4,10 @@
 // mpb_kernels.cuh or fails with MPB_ERR_CUDA.
 #include <algorithm>
 #include <array>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -57,11 +59,15 @@ struct mpb_scene {
   // work buffers
   long long chunk = 0;
   WorkQ wq{};
-  float *d_q = nullptr;
-  unsigned int *d_verdict = nullptr;
-  unsigned int *d_pairbits = nullptr;
+  // host-buffer calls: double-buffered device copies so H2D / kernels / D2H of consecutive chunks overlap
+  float *d_q[2] = {nullptr, nullptr};
+  unsigned int *d_verdict[2] = {nullptr, nullptr};
+  unsigned int *d_pairbits[2] = {nullptr, nullptr};
   float *d_poses = nullptr;
-  size_t d_q_cap = 0, d_verdict_cap = 0, d_pairbits_cap = 0, d_poses_cap = 0, bins_cap = 0;
+  size_t d_q_cap[2] = {0, 0}, d_verdict_cap[2] = {0, 0}, d_pairbits_cap[2] = {0, 0}, d_poses_cap = 0, bins_cap = 0;
+  cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
+  std::vector<cudaEvent_t> sync_events;
+  long long host_chunk = 0;
   bool smem_verts = true;
   int narrow_blocks = 0;
   std::vector<cudaEvent_t> events;
@@ -366,24 +372,19 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     if (qi < 0 || qi >= d->nq_full) { delete s; return fail(MPB_ERR_INVALID, "joint_qidx out of range"); }
     J.slot = slot_of_q[qi];
     J.qconst = (float)d->q_base[qi];
-    J.save_slot = -1;
-    J.pslot = -1;
+    J.jslot = -1;
+    J.pjslot = -1;
     J.dyn_first = 0;
     J.dyn_count = 0;
-    J.pad = 0;
-  }
-  {  // a joint whose child is not the next joint in the table must park its transform
-    int n_saved = 0;
-    for (int j = 0; j < d->n_joints; j++) {
-      const int par = s->h_joints[j].parent;  // model index; the previous joint has model index j
-      if (par == 0 || par == j) continue;
-      DevJoint &P = s->h_joints[par - 1];
-      if (P.save_slot < 0) {
-        if (n_saved >= MPB_MAX_SAVED) { delete s; return fail(MPB_ERR_CAPACITY, "kinematic tree has too many branch points (MPB_MAX_SAVED)"); }
-        P.save_slot = n_saved++;
-      }
-      s->h_joints[j].pslot = P.save_slot;
-    }
+    J.kind = MPB_JK_GENERIC;
+    if (J.type == MPB_JOINT_PRISMATIC) J.kind = MPB_JK_PRISMATIC;
+    else
+      for (int a = 0; a < 3; a++)
+        if (fabs(fabs(d->joint_axis[3 * j + a]) - 1.0) < 1e-12 && fabs(d->joint_axis[3 * j + (a + 1) % 3]) < 1e-12 &&
+            fabs(d->joint_axis[3 * j + (a + 2) % 3]) < 1e-12) {
+          J.kind = MPB_JK_RX + a;
+          J.ax[a] = d->joint_axis[3 * j + a] > 0 ? 1.f : -1.f;
+        }
   }
   // objects
   s->h_objs.resize(d->n_objects);
@@ -558,7 +559,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     }
     s->obj_key[o] = geom_key(O.type, O.geom);
   }
-  if (ndyn > MPB_MAX_DYN) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (MPB_MAX_DYN)"); }
+  if (ndyn > 254) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (254)"); }
   std::vector<int> dynlist;
   for (int j = 0; j < d->n_joints; j++) {
     s->h_joints[j].dyn_first = (int)dynlist.size();
@@ -566,12 +567,25 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
       if (s->h_objs[o].joint == j + 1) dynlist.push_back(o);
     s->h_joints[j].dyn_count = (int)dynlist.size() - s->h_joints[j].dyn_first;
   }
+  // joint-table slots: joints that own moving objects, and parents of non-adjacent children (branch points)
+  int n_jslots = 0;
+  for (int j = 0; j < d->n_joints; j++)
+    if (s->h_joints[j].dyn_count > 0) s->h_joints[j].jslot = n_jslots++;
+  for (int j = 0; j < d->n_joints; j++) {
+    const int par = s->h_joints[j].parent;  // model index; the previous joint has model index j
+    if (par == 0 || par == j) continue;
+    DevJoint &P = s->h_joints[par - 1];
+    if (P.jslot < 0) P.jslot = n_jslots++;
+    s->h_joints[j].pjslot = P.jslot;
+  }
   for (int o = 0; o < d->n_objects; o++) {
     DevObject &O = s->h_objs[o];
     for (int r = 0; r < 3; r++)
-      O.bcw[r] = O.L[4 * r] * O.bc[0] + O.L[4 * r + 1] * O.bc[1] + O.L[4 * r + 2] * O.bc[2] + O.L[4 * r + 3];
+      O.bcw[r] = O.bcj[r] = O.L[4 * r] * O.bc[0] + O.L[4 * r + 1] * O.bc[1] + O.L[4 * r + 2] * O.bc[2] + O.L[4 * r + 3];
+    O.jslot = O.joint > 0 ? s->h_joints[O.joint - 1].jslot : -1;
   }
   s->img.n_dyn = ndyn;
+  s->img.n_jslots = n_jslots;
 
   s->img.n_joints = d->n_joints;
   s->img.n_objects = d->n_objects;
@@ -622,7 +636,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
   // FK + cull launch shape: moving-object poses in shared memory, [object][15 words][thread]
   s->cull_block = 64;
-  s->cull_smem = std::max<size_t>((size_t)ndyn * 15 * s->cull_block * sizeof(float), 16);
+  s->cull_smem = ((size_t)n_jslots * 12 + (size_t)ndyn * 3) * s->cull_block * sizeof(float) + (size_t)s->cull_block * 32 * sizeof(unsigned short) + 16;
+  if (s->cull_smem > 227 * 1024) { mpb_scene_destroy(s); return fail(MPB_ERR_CAPACITY, "too many moving joints / objects for the shared-memory pose table"); }
   CU(cudaFuncSetAttribute(fk_cull_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->cull_blocks_per_sm, fk_cull_kernel<64>, s->cull_block, s->cull_smem));
   s->cull_blocks_per_sm = std::max(s->cull_blocks_per_sm, 1);
@@ -634,11 +649,14 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   if (!s) return;
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
-  void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q, s->d_verdict,
-                  s->d_pairbits, s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+  void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto e : s->events) cudaEventDestroy(e);
+  for (auto e : s->sync_events) cudaEventDestroy(e);
+  if (s->stream_h2d) cudaStreamDestroy(s->stream_h2d);
+  if (s->stream_d2h) cudaStreamDestroy(s->stream_d2h);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
 }
@@ -715,7 +733,7 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   s->wq.bin_cursor = s->wq.bin_count + nb;
   s->wq.bin_start = s->wq.bin_cursor + nb;
   s->wq.unit_start = s->wq.bin_start + nb + 1;
-  if (!s->wq.totals) CU(cudaMalloc((void **)&s->wq.totals, 4 * sizeof(unsigned)));
+  if (!s->wq.totals) CU(cudaMalloc((void **)&s->wq.totals, 8 * sizeof(unsigned)));
   if (!s->wq.counters) CU(cudaMalloc((void **)&s->wq.counters, 4 * sizeof(unsigned long long)));
   s->chunk = chunk;
   return MPB_OK;
@@ -730,74 +748,131 @@ static cudaEvent_t get_event(mpb_scene *s, size_t i) {
   return s->events[i];
 }
 
+static cudaEvent_t get_sync_event(mpb_scene *s, size_t i) {
+  while (s->sync_events.size() <= i) {
+    cudaEvent_t e;
+    cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+    s->sync_events.push_back(e);
+  }
+  return s->sync_events[i];
+}
+
+// Kernels of one pass over m configurations.  hq == nullptr: q already sits at dq.  Otherwise the pass's q is
+// copied from the host pointer hq in sub-ranges on stream_h2d and FK + cull runs per sub-range as it lands, all
+// appending to the same staging queue; binning and narrowphase then run once over the whole pass.
+static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, uint32_t *dv, uint32_t *dp, cudaStream_t st,
+                       size_t *ev, long long *launches, const float *hq, size_t *sync_ev) {
+  const int D = s->img.state_dim, W = s->img.pair_words, nb = std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
+  const size_t vwords = (size_t)(m + 31) / 32;
+  CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
+  if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
+  CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
+  CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
+  cudaEvent_t e0 = get_event(s, (*ev)++), e1 = get_event(s, (*ev)++), e2 = get_event(s, (*ev)++);
+  CU(cudaEventRecord(e0, st));
+  const long long sub = hq ? std::max<long long>(s->host_chunk, 64) : m;
+  for (long long off = 0; off < m; off += sub) {
+    const long long mm = std::min(sub, m - off);
+    if (hq) {
+      if (D > 0) CU(cudaMemcpyAsync(dq_w + off * D, hq + off * D, (size_t)mm * D * sizeof(float), cudaMemcpyHostToDevice, s->stream_h2d));
+      cudaEvent_t landed = get_sync_event(s, (*sync_ev)++);
+      CU(cudaEventRecord(landed, s->stream_h2d));
+      CU(cudaStreamWaitEvent(st, landed, 0));
+    }
+    if (s->img.n_pairs > 0) {
+      const int cblocks = (int)std::min<long long>((mm + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
+      fk_cull_kernel<64><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq + off * D, mm, off, s->wq);
+      *launches += 1;
+    }
+  }
+  if (s->img.n_pairs == 0) return MPB_OK;
+  static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
+  const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
+  scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, n_warps);
+  scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
+  CU(cudaEventRecord(e1, st));
+  const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
+  if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
+  else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
+  *launches += 3;
+  if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
+    CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
+    CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
+    expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
+    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, n_warps);
+    scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 1);
+    if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
+    else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
+    *launches += 4;
+  }
+  CU(cudaEventRecord(e2, st));
+  CU(cudaGetLastError());
+  return MPB_OK;
+}
+
 // One attempt over the whole batch with a given chunk size.  Returns MPB_OK and sets *overflow.
+// Host buffers: chunk c uses device buffer set c & 1; its H2D runs on stream_h2d, its kernels on `st`, its D2H on
+// stream_d2h, so the copies of neighbouring chunks overlap the kernels (PCIe is full duplex).
 static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *verdict, uint32_t *pair_bits, int space,
                            cudaStream_t st, long long chunk, bool *overflow, mpb_stats *stats) {
+  const auto t_begin = std::chrono::steady_clock::now();
   int rc = prepare_work(s, chunk);
   if (rc != MPB_OK) return rc;
-  const int D = s->img.state_dim, W = s->img.pair_words, nb = std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
+  const int D = s->img.state_dim, W = s->img.pair_words;
   const bool host = space == MPB_HOST;
   if (host) {
-    CU(ensure(&s->d_q, &s->d_q_cap, (size_t)chunk * std::max(D, 1)));
-    CU(ensure(&s->d_verdict, &s->d_verdict_cap, (size_t)(chunk + 31) / 32));
-    if (pair_bits) CU(ensure(&s->d_pairbits, &s->d_pairbits_cap, (size_t)chunk * std::max(W, 1)));
+    for (int b = 0; b < 2; b++) {
+      CU(ensure(&s->d_q[b], &s->d_q_cap[b], (size_t)chunk * std::max(D, 1)));
+      CU(ensure(&s->d_verdict[b], &s->d_verdict_cap[b], (size_t)(chunk + 31) / 32));
+      if (pair_bits) CU(ensure(&s->d_pairbits[b], &s->d_pairbits_cap[b], (size_t)chunk * std::max(W, 1)));
+    }
+    if (!s->stream_h2d) CU(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
+    if (!s->stream_d2h) CU(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
   }
-  CU(cudaMemsetAsync(s->wq.totals, 0, 4 * sizeof(unsigned), st));
+  CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
   CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
-  size_t ev = 0;
-  long long launches = 0;
-  for (long long off = 0; off < n; off += chunk) {
+  size_t ev = 0, sync_ev = 0;
+  long long launches = 0, c = 0;
+  if (host) {  // the copy stream starts after whatever the caller already queued on `st`
+    cudaEvent_t start = get_sync_event(s, sync_ev++);
+    CU(cudaEventRecord(start, st));
+    CU(cudaStreamWaitEvent(s->stream_h2d, start, 0));
+  }
+  std::vector<cudaEvent_t> ev_k, ev_out;  // per pass: kernels done, results copied out
+  for (long long off = 0; off < n; off += chunk, c++) {
     const long long m = std::min(chunk, n - off);
     const size_t vwords = (size_t)(m + 31) / 32;
-    const float *dq = q + off * D;
-    uint32_t *dv = verdict + off / 32;
-    uint32_t *dp = pair_bits ? pair_bits + (size_t)off * W : nullptr;
-    if (host) {
-      if (D > 0) CU(cudaMemcpyAsync(s->d_q, q + off * D, (size_t)m * D * sizeof(float), cudaMemcpyHostToDevice, st));
-      dq = s->d_q;
-      dv = s->d_verdict;
-      dp = pair_bits ? s->d_pairbits : nullptr;
+    if (!host) {
+      rc = launch_pass(s, nullptr, q + off * D, m, verdict + off / 32, pair_bits ? pair_bits + (size_t)off * W : nullptr, st, &ev,
+                       &launches, nullptr, &sync_ev);
+      if (rc != MPB_OK) return rc;
+      continue;
     }
-    CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
-    if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
-    CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
-    CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
-    if (s->img.n_pairs > 0) {
-      const int cblocks = (int)std::min<long long>((m + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
-      cudaEvent_t e0 = get_event(s, ev++), e1 = get_event(s, ev++), e2 = get_event(s, ev++);
-      CU(cudaEventRecord(e0, st));
-      fk_cull_kernel<64><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, s->wq);
-      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin);
-      scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
-      CU(cudaEventRecord(e1, st));
-      const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
-      if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
-      else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
-      launches += 4;
-      if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
-        CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
-        CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
-        expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
-        scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1);
-        scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 1);
-        if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
-        else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
-        launches += 4;
-      }
-      CU(cudaEventRecord(e2, st));
-      CU(cudaGetLastError());
+    const int b = (int)(c & 1);
+    if (c >= 2) {
+      CU(cudaStreamWaitEvent(s->stream_h2d, ev_k[c - 2], 0));  // kernels of pass c-2 read d_q[b]
+      CU(cudaStreamWaitEvent(st, ev_out[c - 2], 0));           // D2H of pass c-2 read the result buffers
     }
-    if (host) {
-      CU(cudaMemcpyAsync(verdict + off / 32, dv, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-      if (pair_bits)
-        CU(cudaMemcpyAsync(pair_bits + (size_t)off * W, dp, (size_t)m * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    }
+    uint32_t *dv = s->d_verdict[b], *dp = pair_bits ? s->d_pairbits[b] : nullptr;
+    rc = launch_pass(s, s->d_q[b], s->d_q[b], m, dv, dp, st, &ev, &launches, q + off * D, &sync_ev);
+    if (rc != MPB_OK) return rc;
+    ev_k.push_back(get_sync_event(s, sync_ev++));
+    ev_out.push_back(get_sync_event(s, sync_ev++));
+    CU(cudaEventRecord(ev_k[c], st));
+    CU(cudaStreamWaitEvent(s->stream_d2h, ev_k[c], 0));
+    CU(cudaMemcpyAsync(verdict + off / 32, dv, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
+    if (pair_bits)
+      CU(cudaMemcpyAsync(pair_bits + (size_t)off * W, dp, (size_t)m * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
+    CU(cudaEventRecord(ev_out[c], s->stream_d2h));
   }
-  unsigned totals[4] = {0, 0, 0, 0};
+  const auto t_enq = std::chrono::steady_clock::now();
+  unsigned totals[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   unsigned long long counters[4] = {0, 0, 0, 0};
   CU(cudaMemcpyAsync(totals, s->wq.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(counters, s->wq.counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  if (host) CU(cudaStreamSynchronize(s->stream_d2h));
+  const auto t_end = std::chrono::steady_clock::now();
   *overflow = totals[2] != 0;
   if (stats) {
     stats->n_states = n;
@@ -817,6 +892,8 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
     stats->gpu_ms_cull = cull;
     stats->gpu_ms_narrow = narrow;
     stats->gpu_ms = cull + narrow;
+    stats->host_ms_enqueue = std::chrono::duration<float, std::milli>(t_enq - t_begin).count();
+    stats->host_ms_total = std::chrono::duration<float, std::milli>(t_end - t_begin).count();
   }
   return MPB_OK;
 }
@@ -831,6 +908,10 @@ extern "C" int mpb_collide_batch(mpb_scene *s, const float *q, int64_t n, uint32
   CU(cudaSetDevice(s->device));
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   long long chunk = std::min<long long>(kMaxChunk, (n + 31) / 32 * 32);
+  if (s->host_chunk == 0) {  // host buffers: H2D sub-range size (FK + cull of one sub-range overlaps the next copy)
+    const char *e = getenv("MPB_HOST_CHUNK");
+    s->host_chunk = e ? std::max<long long>(64, atoll(e) / 64 * 64) : (1ll << 17);
+  }
   for (int attempt = 0; attempt < 12; attempt++) {
     bool overflow = false;
     int rc = collide_attempt(s, q, n, verdict_bits, pair_bits, space, st, chunk, &overflow, stats);
@@ -851,7 +932,7 @@ extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *pose
   const int D = s->img.state_dim, L = s->img.n_links;
   const long long chunk = std::min<long long>(kMaxChunk, n);
   if (space == MPB_HOST) {
-    CU(ensure(&s->d_q, &s->d_q_cap, (size_t)chunk * std::max(D, 1)));
+    CU(ensure(&s->d_q[0], &s->d_q_cap[0], (size_t)chunk * std::max(D, 1)));
     CU(ensure(&s->d_poses, &s->d_poses_cap, (size_t)chunk * L * 7));
   }
   for (long long off = 0; off < n; off += chunk) {
@@ -859,8 +940,8 @@ extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *pose
     const float *dq = q + off * D;
     float *dp = poses + (size_t)off * L * 7;
     if (space == MPB_HOST) {
-      if (D > 0) CU(cudaMemcpyAsync(s->d_q, dq, (size_t)m * D * sizeof(float), cudaMemcpyHostToDevice, st));
-      dq = s->d_q;
+      if (D > 0) CU(cudaMemcpyAsync(s->d_q[0], dq, (size_t)m * D * sizeof(float), cudaMemcpyHostToDevice, st));
+      dq = s->d_q[0];
       dp = s->d_poses;
     }
     const int blocks = (int)std::min<long long>((m + 127) / 128, (long long)s->num_sms * 16);

@@ -23,11 +23,12 @@ struct alignas(16) DevJoint {
   int parent;    // model index (0 = universe)
   int slot;      // index into the batch state, or -1
   float qconst;  // value when slot < 0 (q_base)
-  int save_slot; // >= 0: this joint's transform is kept for a later, non-adjacent child
-  int pslot;     // >= 0: parent transform comes from that saved slot; -1: previous joint (or universe)
+  int jslot;     // >= 0: this joint's world transform is kept in the shared-memory joint table (it owns moving
+                 //       collision objects, or a later non-adjacent child needs it)
+  int pjslot;    // >= 0: parent transform comes from that joint-table slot; -1: previous joint (or universe)
   int dyn_first; // first entry of SceneImg::dynlist owned by this joint
   int dyn_count; // number of moving collision objects on this joint
-  int pad;
+  int kind;      // MPB_JK_*: axis-aligned revolute joints skip the general Rodrigues product
 };
 static_assert(sizeof(DevJoint) % 16 == 0, "DevJoint must keep 16-byte alignment");
 
@@ -46,7 +47,9 @@ struct alignas(16) DevObject {
   float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
   int voff, vcnt;   // hull vertices in the pool
   float bcw[3];     // world-fixed objects: bounding-sphere centre in the world frame
-  float rin;        // radius of a ball around ctr that lies inside the shape (sufficient-hit test); sizeof == 192
+  float rin;        // radius of a ball around ctr that lies inside the shape (sufficient-hit test)
+  int jslot;        // joint-table slot of the owner joint, -1 if world-fixed
+  float bcj[3];     // bounding-sphere centre in the owner joint frame (L * bc); sizeof == 208
 };
 static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
 
@@ -55,7 +58,11 @@ struct DevPair {
   int bin_dyn;  // bin | (dynA + 1) << 16 | (dynB + 1) << 24   (0 in a dyn field = world-fixed)
   float rr;     // sum of the two bounding-sphere radii (+ margin)
 };
-#define MPB_MAX_SAVED 8   // kinematic branch points kept per thread
+#define MPB_JK_GENERIC 0  // revolute / continuous about an arbitrary unit axis
+#define MPB_JK_RX 1       // revolute about +-x (sign in ax[0])
+#define MPB_JK_RY 2
+#define MPB_JK_RZ 3
+#define MPB_JK_PRISMATIC 4
 
 // internal leaf-primitive shape types of BVH objects (meshes, octrees)
 #define MPB_GEOM_TRI 7    // triangle: prims[3*aux + 0..2] = vertices (object frame)

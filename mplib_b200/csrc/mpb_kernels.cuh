@@ -40,7 +40,7 @@ struct SceneImg {
   int n_bins2;
   const float *linkL;   // [n_links][12] link placement in its joint frame
   const int *linkJoint; // [n_links]
-  int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn;
+  int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn, n_jslots;
 };
 
 struct WorkQ {
@@ -52,7 +52,7 @@ struct WorkQ {
   unsigned int *bin_cursor;  // [n_bins]
   unsigned int *bin_start;   // [n_bins+1]
   unsigned int *unit_start;  // [n_bins+1]   units of MPB_UNIT_ITEMS items
-  unsigned int *totals;      // [0]=staged items [1]=units [2]=overflow flag [3]=unit ticket
+  unsigned int *totals;      // [0]=staged items [1]=units [2]=overflow flag [3]=unit ticket [4]=items per unit
   unsigned long long *counters;  // [0]=items after cull [1]=support evaluations [2]=capped items
   unsigned int cap;
 };
@@ -60,7 +60,8 @@ struct WorkQ {
 #define MPB_EPS FLT_EPSILON
 #define MPB_MPR_TOL 1e-6f
 #define MPB_MPR_MAX_ITERS 96
-#define MPB_UNIT_ITEMS 128   // items a warp owns at a time in the narrowphase
+#define MPB_UNIT_ITEMS 128   // most items a warp owns at a time in the narrowphase (scan_bins_kernel picks 32..128)
+#define MPB_COOP_MAX 10      // busy lanes at or below which a warp evaluates hull supports cooperatively
 #define MPB_STAGE_CHUNK 64   // staging slots a warp reserves per atomic (>= 32)
 
 // ---------------------------------------------------------------------------------------------- FK
@@ -138,57 +139,110 @@ __device__ __forceinline__ bool obb_disjoint(const float *R, const float *t, con
   return false;
 }
 
-// shared-memory pose table: word k (0..11 pose, 12..14 bounding-sphere centre) of moving object d
-#define SMW(d, k) sW[((d) * 15 + (k)) * BLOCK + tid]
+// world transform of joint J given its parent's: cur = parent * P * motion(q).  Axis-aligned revolute joints
+// (Pinocchio JointModelRX/RY/RZ) only mix two columns of parent * P.
+__device__ __forceinline__ Xf joint_step(const DevJoint &J, const Xf *parent, float q) {
+  Xf a = load_xf12(J.P);
+  if (parent) a = xf_mul(*parent, a);
+  if (J.kind == MPB_JK_PRISMATIC) {
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+      a.p[r] = fmaf(a.r[3 * r], J.ax[0] * q, fmaf(a.r[3 * r + 1], J.ax[1] * q, fmaf(a.r[3 * r + 2], J.ax[2] * q, a.p[r])));
+    return a;
+  }
+  if (J.kind == MPB_JK_GENERIC) {
+    const Xf m = joint_motion(J, q);
+    Xf o;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+#pragma unroll
+      for (int j = 0; j < 3; j++)
+        o.r[3 * i + j] = fmaf(a.r[3 * i], m.r[j], fmaf(a.r[3 * i + 1], m.r[3 + j], a.r[3 * i + 2] * m.r[6 + j]));
+      o.p[i] = a.p[i];
+    }
+    return o;
+  }
+  float s, c;
+  sincosf(q, &s, &c);
+  // rotation about +-axis k mixes the two other columns (u, v) of parent * P; -axis: opposite angle
+#define MPB_MIX(u, v)                                    \
+  _Pragma("unroll") for (int r = 0; r < 3; r++) {        \
+    const float cu = a.r[3 * r + u], cv = a.r[3 * r + v]; \
+    a.r[3 * r + u] = fmaf(c, cu, s * cv);                \
+    a.r[3 * r + v] = fmaf(c, cv, -s * cu);               \
+  }
+  if (J.kind == MPB_JK_RX) { s *= J.ax[0]; MPB_MIX(1, 2) }
+  else if (J.kind == MPB_JK_RY) { s *= J.ax[1]; MPB_MIX(2, 0) }
+  else { s *= J.ax[2]; MPB_MIX(0, 1) }
+#undef MPB_MIX
+  return a;
+}
+
+// shared-memory tables, transposed [slot][word][thread] so that every access of the FK / sphere phases is
+// conflict-free: sJ = world transforms of the kept joints (12 words), sC = bounding-sphere centres (3 words)
+#define SMJ(js, k, t) sJ[((js) * 12 + (k)) * BLOCK + (t)]
+#define SMC(d, k, t) sC[((d) * 3 + (k)) * BLOCK + (t)]
 
 template <int BLOCK>
-__device__ __forceinline__ Xf smem_pose(const float *sW, int d, int tid) {
+__device__ __forceinline__ Xf smem_joint(const float *sJ, int js, int t) {
   Xf w;
 #pragma unroll
-  for (int k = 0; k < 9; k++) w.r[k] = SMW(d, k);
+  for (int k = 0; k < 9; k++) w.r[k] = SMJ(js, k, t);
 #pragma unroll
-  for (int k = 0; k < 3; k++) w.p[k] = SMW(d, 9 + k);
+  for (int k = 0; k < 3; k++) w.p[k] = SMJ(js, 9 + k, t);
   return w;
 }
 
+// Phases per tile of BLOCK configurations:
+//   1. FK, thread per configuration: joint transforms -> sJ, bounding-sphere centres of the moving objects -> sC
+//   2. per 32 admitted pairs: bounding-sphere test, thread per configuration -> survivors pushed to a block queue
+//   3. dense: thread per queued (configuration, pair): 15-axis OBB SAT with the owner's joint transforms read
+//      from sJ; what is left is ballot-compacted into the global staging queue (one atomic per warp chunk)
 template <int BLOCK>
-__global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, WorkQ wq) {
-  extern __shared__ __align__(16) float sW[];
+__global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, long long cfg_base, WorkQ wq) {
+  extern __shared__ __align__(16) float smem_f[];
+  float *sJ = smem_f;
+  float *sC = sJ + (size_t)img.n_jslots * 12 * BLOCK;
+  unsigned short *sQ = reinterpret_cast<unsigned short *>(sC + (size_t)img.n_dyn * 3 * BLOCK);  // [BLOCK * 32]
+  __shared__ unsigned sCount[2];  // queue length, double-buffered by round parity
   const int tid = threadIdx.x;
-  const unsigned lane = threadIdx.x & 31;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
-  const long long stride = (long long)gridDim.x * BLOCK;
-  const long long n_round = (n + 31) / 32 * 32;
   unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
-  for (long long i = (long long)blockIdx.x * BLOCK + tid; i < n_round; i += stride) {
+  const long long n_tiles = (n + BLOCK - 1) / BLOCK;
+  unsigned rnd = 0;
+  if (tid < 2) sCount[tid] = 0;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long i = tile * BLOCK + tid;
     const bool valid = i < n;
-    // ---- FK, running transform in registers
+    // ---- 1. FK, running transform in registers
     if (valid) {
       Xf cur = xf_identity();
-      Xf saved[MPB_MAX_SAVED];
       const float *qrow = q + i * img.state_dim;
       for (int j = 0; j < img.n_joints; j++) {
         const DevJoint &J = img.joints[j];
         const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
-        const Xf li = xf_mul(load_xf12(J.P), joint_motion(J, qj));
-        if (J.parent == 0) cur = li;
-        else if (J.pslot >= 0) cur = xf_mul(saved[J.pslot], li);
-        else cur = xf_mul(cur, li);
-        if (J.save_slot >= 0) saved[J.save_slot] = cur;
+        if (J.parent == 0) cur = joint_step(J, nullptr, qj);
+        else if (J.pjslot >= 0) { const Xf par = smem_joint<BLOCK>(sJ, J.pjslot, tid); cur = joint_step(J, &par, qj); }
+        else cur = joint_step(J, &cur, qj);
+        if (J.jslot >= 0) {
+#pragma unroll
+          for (int k = 0; k < 9; k++) SMJ(J.jslot, k, tid) = cur.r[k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) SMJ(J.jslot, 9 + k, tid) = cur.p[k];
+        }
         for (int e = 0; e < J.dyn_count; e++) {
           const DevObject &O = img.objs[img.dynlist[J.dyn_first + e]];
-          const Xf w = xf_mul(cur, load_xf12(O.L));
           float c[3];
-          xf_point(w, O.bc, c);
+          xf_point(cur, O.bcj, c);  // bounding-sphere centre in the joint frame -> world
 #pragma unroll
-          for (int k = 0; k < 9; k++) SMW(O.dyn, k) = w.r[k];
-#pragma unroll
-          for (int k = 0; k < 3; k++) { SMW(O.dyn, 9 + k) = w.p[k]; SMW(O.dyn, 12 + k) = c[k]; }
+          for (int k = 0; k < 3; k++) SMC(O.dyn, k, tid) = c[k];
         }
       }
     }
-    // ---- pairs, 32 at a time: uniform sphere test -> per-lane survivor mask -> per-lane OBB SAT
     for (int base = 0; base < img.n_pairs; base += 32) {
+      __syncthreads();  // FK tables complete (first round); previous dense phase done with sQ
+      // ---- 2. bounding spheres
       unsigned mask = 0;
       const int cnt = min(32, img.n_pairs - base);
       if (valid) {
@@ -196,27 +250,52 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
           const DevPair pr = img.pairs[base + k];
           const int da = ((pr.bin_dyn >> 16) & 0xff) - 1, db = ((pr.bin_dyn >> 24) & 0xff) - 1;
           float ax, ay, az, bx, by, bz;
-          if (da >= 0) { ax = SMW(da, 12); ay = SMW(da, 13); az = SMW(da, 14); }
+          if (da >= 0) { ax = SMC(da, 0, tid); ay = SMC(da, 1, tid); az = SMC(da, 2, tid); }
           else { const float *c = img.objs[pr.a].bcw; ax = c[0]; ay = c[1]; az = c[2]; }
-          if (db >= 0) { bx = SMW(db, 12); by = SMW(db, 13); bz = SMW(db, 14); }
+          if (db >= 0) { bx = SMC(db, 0, tid); by = SMC(db, 1, tid); bz = SMC(db, 2, tid); }
           else { const float *c = img.objs[pr.b].bcw; bx = c[0]; by = c[1]; bz = c[2]; }
           const float dx = ax - bx, dy = ay - by, dz = az - bz;
           if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rr * pr.rr) mask |= 1u << k;
         }
       }
-      while (__any_sync(FULL, mask != 0)) {
-        bool keep = false;
-        Xf rel;
-        int p = 0;
-        if (mask) {
+      {  // push (thread, pair-in-tile) survivors: warp prefix sum + one shared atomic per warp
+        const unsigned c = __popc(mask);
+        unsigned incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const unsigned t = __shfl_up_sync(FULL, incl, o);
+          if ((int)lane >= o) incl += t;
+        }
+        const unsigned wtot = __shfl_sync(FULL, incl, 31);
+        unsigned wb = 0;
+        if (lane == 31 && wtot) wb = atomicAdd(&sCount[rnd & 1], wtot);
+        wb = __shfl_sync(FULL, wb, 31);
+        unsigned pos = wb + incl - c;
+        while (mask) {
           const int k = __ffs(mask) - 1;
           mask &= mask - 1;
-          p = base + k;
+          sQ[pos++] = (unsigned short)(tid | (k << 8));
+        }
+      }
+      __syncthreads();
+      // ---- 3. dense OBB SAT over the queue
+      const unsigned total = sCount[rnd & 1];
+      if (tid == 0) sCount[(rnd + 1) & 1] = 0;  // nobody reads the other counter between the two barriers
+      rnd++;
+      for (unsigned e0 = warp * 32; e0 < total; e0 += BLOCK) {
+        const unsigned e = e0 + lane;
+        bool keep = false;
+        Xf rel;
+        int p = 0, owner = 0;
+        if (e < total) {
+          const unsigned ent = sQ[e];
+          owner = ent & 0xff;
+          p = base + (ent >> 8);
           const DevPair pr = img.pairs[p];
           const DevObject &A = img.objs[pr.a];
           const DevObject &B = img.objs[pr.b];
-          const Xf Wa = A.dyn >= 0 ? smem_pose<BLOCK>(sW, A.dyn, tid) : load_xf12(A.L);
-          const Xf Wb = B.dyn >= 0 ? smem_pose<BLOCK>(sW, B.dyn, tid) : load_xf12(B.L);
+          const Xf Wa = A.jslot >= 0 ? xf_mul(smem_joint<BLOCK>(sJ, A.jslot, owner), load_xf12(A.L)) : load_xf12(A.L);
+          const Xf Wb = B.jslot >= 0 ? xf_mul(smem_joint<BLOCK>(sJ, B.jslot, owner), load_xf12(B.L)) : load_xf12(B.L);
           rel = xf_inv_mul(Wa, Wb);
           // box B in box A's frame:  Ra^T (rel.R Rb),  Ra^T (rel*ocB - ocA)
           float M[9], R[9], cbA[3], t[3];
@@ -258,7 +337,7 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
             for (int k = 0; k < 9; k++) wq.stf[(size_t)k * wq.cap + slot] = rel.r[k];
 #pragma unroll
             for (int k = 0; k < 3; k++) wq.stf[(size_t)(9 + k) * wq.cap + slot] = rel.p[k];
-            wq.scfg[slot] = (int)i;
+            wq.scfg[slot] = (int)(cfg_base + tile * BLOCK + owner);
             wq.spair[slot] = p;
             wq.saux[slot] = 0;
           }
@@ -268,6 +347,7 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
         wused += cntk;
       }
     }
+    __syncthreads();  // the next tile's FK overwrites sJ / sC
   }
   // invalidate the unused tail of the last chunk
   if (wbase != 0xffffffffu) {
@@ -276,15 +356,23 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
   }
 }
 
-__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin) {
+__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_warps) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned items = 0, units = 0;
+    // unit = slice of one bin a warp owns: as large as possible (persistent lanes keep all 32 lanes busy across the
+    // spread of MPR run lengths; the tail of a slice runs in the cooperative mode) while still feeding n_warps
+    unsigned all = 0;
+    for (int b = 0; b < n_bins; b++)
+      if (b != skip_bin) all += wq.bin_count[b];
+    unsigned unit = MPB_UNIT_ITEMS;
+    while (unit > 32u && all / unit < n_warps) unit >>= 1;
+    wq.totals[4] = unit;
     for (int b = 0; b < n_bins; b++) {
       wq.bin_start[b] = items;
       wq.unit_start[b] = units;
       const unsigned c = wq.bin_count[b];
       items += c;
-      if (b != skip_bin) units += (c + MPB_UNIT_ITEMS - 1u) / MPB_UNIT_ITEMS;  // BVH pairs go to expand_kernel instead
+      if (b != skip_bin) units += (c + unit - 1u) / unit;  // BVH pairs go to expand_kernel instead
       wq.bin_cursor[b] = 0;
     }
     wq.bin_start[n_bins] = items;
@@ -396,6 +484,27 @@ __device__ __forceinline__ V3 rot_t(const float *R, V3 v) {
 }
 __device__ __forceinline__ bool is_zero(float v) { return fabsf(v) < MPB_EPS; }
 
+// Hull support evaluated by the whole warp for ONE query direction (same on every lane): lane-strided scan and a
+// shuffle arg-max.  Ties resolve to the lowest vertex index, exactly like the serial scan of support_local.
+template <bool SMEM>
+__device__ __forceinline__ V3 support_hull_coop(const float4 *__restrict__ v, int vcnt, V3 d, unsigned lane) {
+  float best = -FLT_MAX;
+  int bi = 0x7fffffff;
+  for (int i = (int)lane; i < vcnt; i += 32) {
+    const float4 p = SMEM ? v[i] : __ldg(v + i);
+    const float t = fmaf(p.x, d.x, fmaf(p.y, d.y, p.z * d.z));
+    if (t > best) { best = t; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  const float4 p = SMEM ? v[bi] : __ldg(v + bi);
+  return v3(p.x, p.y, p.z);
+}
+
 // ---------------------------------------------------------------------------------------------- TMA staging
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
@@ -452,7 +561,7 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
   }
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
-  const unsigned n_units = wq.totals[1];
+  const unsigned n_units = wq.totals[1], unit_items = wq.totals[4];
   unsigned long long it_sum = 0, cap_sum = 0;
   for (;;) {
     // dynamic unit ticket (one atomic per warp per MPB_UNIT_ITEMS items)
@@ -465,8 +574,8 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
       const int mid = (lo + hi) >> 1;
       if (wq.unit_start[mid] <= u) lo = mid; else hi = mid;
     }
-    unsigned next = wq.bin_start[lo] + (u - wq.unit_start[lo]) * MPB_UNIT_ITEMS;
-    const unsigned end = min(min(wq.bin_start[lo + 1], next + MPB_UNIT_ITEMS), wq.cap);
+    unsigned next = wq.bin_start[lo] + (u - wq.unit_start[lo]) * unit_items;
+    const unsigned end = min(min(wq.bin_start[lo + 1], next + unit_items), wq.cap);
     const unsigned first = next;
 
     // per-lane item state
@@ -527,8 +636,32 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
         if (__ballot_sync(FULL, busy) == 0) break;  // slice exhausted and every lane finished
       }
       // ---- one Minkowski support for every lane: sA(dir) - (R sB(R^T(-dir)) + t)
-      const V3 sa = support_local<SMEM>(A, dir, verts, img.prims);
-      const V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts, img.prims);
+      const unsigned bm = __ballot_sync(FULL, busy);
+      const V3 dB = rot_t(R, dir * -1.f);
+      V3 sa, sb;
+      if (__popc(bm) <= MPB_COOP_MAX) {
+        // few lanes left (the tail of a slice): the whole warp scans the hulls for one busy lane at a time
+        // (lane-strided vertices + shuffle arg-max) instead of every lane scanning every vertex for itself
+        const bool ca = A.type == MPB_GEOM_CONVEX, cb = B.type == MPB_GEOM_CONVEX;  // warp-uniform (bin-uniform shapes)
+        if (!ca) sa = support_local<SMEM>(A, dir, verts, img.prims);
+        if (!cb) sb = support_local<SMEM>(B, dB, verts, img.prims);
+        for (unsigned m = bm; m; m &= m - 1) {
+          const int src = __ffs(m) - 1;
+          if (ca) {
+            const V3 d = v3(__shfl_sync(FULL, dir.x, src), __shfl_sync(FULL, dir.y, src), __shfl_sync(FULL, dir.z, src));
+            const V3 r = support_hull_coop<SMEM>(verts + A.voff, A.vcnt, d, lane);
+            if ((int)lane == src) sa = r;
+          }
+          if (cb) {
+            const V3 d = v3(__shfl_sync(FULL, dB.x, src), __shfl_sync(FULL, dB.y, src), __shfl_sync(FULL, dB.z, src));
+            const V3 r = support_hull_coop<SMEM>(verts + B.voff, B.vcnt, d, lane);
+            if ((int)lane == src) sb = r;
+          }
+        }
+      } else {
+        sa = support_local<SMEM>(A, dir, verts, img.prims);
+        sb = support_local<SMEM>(B, dB, verts, img.prims);
+      }
       const V3 v = sa - (rot(R, sb) + t);
       if (!busy) continue;
       iters++;

@@ -69,6 +69,8 @@ class MpbStats(C.Structure):
         ("gpu_ms", C.c_float),
         ("gpu_ms_cull", C.c_float),
         ("gpu_ms_narrow", C.c_float),
+        ("host_ms_enqueue", C.c_float),
+        ("host_ms_total", C.c_float),
     ]
 
     def as_dict(self):
