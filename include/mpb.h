@@ -154,6 +154,67 @@ int mpb_fk_batch(mpb_scene *scene, const float *q, int64_t n, float *poses, int 
 int mpb_collide_batch(mpb_scene *scene, const float *q, int64_t n, uint32_t *verdict_bits,
                       uint32_t *pair_bits, mpb_stats *stats, int space, void *stream);
 
+/*
+ * Planning state space as OMPLPlannerTpl::build_state_space builds it (src/ompl_planner.cpp:245-296): one 1-D
+ * RealVector subspace per bounded joint, one SO(2) subspace per continuous joint, all with weight 1, so the
+ * space distance is the sum of the per-dimension distances.  `seg[j]` is the longest valid segment of subspace j:
+ * 0.01 * (hi[j] - lo[j]) for RealVector, 0.01 * pi for SO(2) (OMPL's default 1 % validity resolution, which
+ * the reference never changes).
+ */
+typedef struct mpb_space_desc {
+  int32_t dim;           /* == state_dim of the scene */
+  const float *lo;       /* [dim] lower_joint_limits_ (-pi for SO(2))  */
+  const float *hi;       /* [dim] upper_joint_limits_ (+pi for SO(2))  */
+  const float *seg;      /* [dim] longest valid segment per subspace   */
+  const uint8_t *so2;    /* [dim] 1 = SO(2) subspace; nullable = none  */
+} mpb_space_desc;
+
+/* Batched ompl::base::DiscreteMotionValidator::checkMotion(a, b) with ValidityCheckerTpl::isValid as the state
+ * test (the validator OMPL installs for the reference's SpaceInformation, src/ompl_planner.cpp:62-70):
+ * valid iff b and every interior sample a + (j/nd)(b-a), j = 1..nd-1, is collision-free, where
+ * nd = max_j ceil(|b_j - a_j| / seg[j]).  `a` is assumed valid, as in OMPL.
+ *   a, b        [n_edges][dim] float32
+ *   valid_bits  [ceil(n_edges/32)] uint32, bit e set iff motion e is valid
+ * stats->n_states reports the number of sampled states. */
+int mpb_check_motion_batch(mpb_scene *scene, const mpb_space_desc *space, const float *a, const float *b, int64_t n_edges,
+                           uint32_t *valid_bits, mpb_stats *stats, int space_flag, void *stream);
+
+#define MPB_RRT_ACTIVE 0         /* not finished within max_rounds / time_limit ("Timeout" in OMPL terms) */
+#define MPB_RRT_SOLVED 1         /* "Exact solution" */
+#define MPB_RRT_CAPACITY 2       /* a tree reached tree_capacity nodes */
+#define MPB_RRT_INVALID_GOAL 3   /* no goal state given ("Invalid goal") */
+#define MPB_RRT_PATH_TOO_LONG 4  /* solved, but the path has more than max_path waypoints */
+
+typedef struct mpb_rrt_params {
+  float range;            /* RRTConnect::setRange; <= 0: OMPL's default 0.2 * maximum extent of the space */
+  int32_t max_rounds;     /* growTree calls per query at most (one per lock-step round)               */
+  float time_limit_s;     /* wall-clock budget of the call (OMPL's `time`), <= 0: none                */
+  int32_t tree_capacity;  /* nodes per tree per query                                                 */
+  int32_t max_path;       /* waypoints per returned path at most                                      */
+  uint64_t seed;
+  int32_t check_every;    /* rounds between host checks of the active-query counter (<= 0: 16)        */
+} mpb_rrt_params;
+
+typedef struct mpb_rrt_stats {
+  int64_t rounds;          /* lock-step rounds executed                       */
+  int64_t grow_calls;      /* growTree calls summed over queries              */
+  int64_t states_checked;  /* states sent through the validity kernels        */
+  int64_t n_solved;
+  int64_t kernel_launches;
+  float gpu_ms;            /* device time of the whole call (CUDA events)     */
+  float host_ms_total;
+} mpb_rrt_stats;
+
+/* RRTConnect branch of OMPLPlannerTpl::plan (src/ompl_planner.cpp:97-243) for n_queries independent queries in
+ * lock-step on the device; start and goal states must already be valid (the host layer runs the start fix-up and
+ * the goal-image enumeration of src/ompl_planner.cpp:110-158 first).  Host pointers only.
+ *   starts   [n_queries][dim]             goals  [n_queries][max_goals][dim]     n_goals [n_queries]
+ *   status   [n_queries] MPB_RRT_*        path_len [n_queries]
+ *   paths    [n_queries][max_path][dim]   start ... goal waypoints of solved queries */
+int mpb_rrtconnect_batch(mpb_scene *scene, const mpb_space_desc *space, const float *starts, const float *goals,
+                         const int32_t *n_goals, int32_t max_goals, int64_t n_queries, const mpb_rrt_params *params,
+                         int32_t *status, int32_t *path_len, float *paths, mpb_rrt_stats *stats);
+
 /* Query geometry constants of the compiled scene (for tests / host layer). */
 int mpb_scene_info(const mpb_scene *scene, int32_t *n_pairs, int32_t *state_dim, int32_t *n_links,
                    int32_t *n_objects, int32_t *device);

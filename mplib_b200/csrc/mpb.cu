@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "mpb_kernels.cuh"
+#include "mpb_plan.cuh"
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) {
@@ -768,8 +769,9 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
   CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
   CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
-  cudaEvent_t e0 = get_event(s, (*ev)++), e1 = get_event(s, (*ev)++), e2 = get_event(s, (*ev)++);
-  CU(cudaEventRecord(e0, st));
+  cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;  // ev == nullptr: no timing events (graph capture)
+  if (ev) { e0 = get_event(s, (*ev)++); e1 = get_event(s, (*ev)++); e2 = get_event(s, (*ev)++); }
+  if (ev) CU(cudaEventRecord(e0, st));
   const long long sub = hq ? std::max<long long>(s->host_chunk, 64) : m;
   for (long long off = 0; off < m; off += sub) {
     const long long mm = std::min(sub, m - off);
@@ -790,7 +792,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
   scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, n_warps);
   scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
-  CU(cudaEventRecord(e1, st));
+  if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
   if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
   else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
@@ -805,7 +807,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
     *launches += 4;
   }
-  CU(cudaEventRecord(e2, st));
+  if (ev) CU(cudaEventRecord(e2, st));
   CU(cudaGetLastError());
   return MPB_OK;
 }
@@ -1000,5 +1002,263 @@ extern "C" int mpb_fp32_peak(int device, float *tflops) {
   cudaEventDestroy(e1);
   cudaFree(d_out);
   *tflops = best;
+  return MPB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ planning layer
+struct DevSpace {
+  SpaceDesc sp{};
+  float *buf = nullptr;  // lo | hi | seg | so2 bytes
+};
+
+static int upload_space(const mpb_scene *s, const mpb_space_desc *space, DevSpace *out) {
+  if (!space || !space->lo || !space->hi || !space->seg) return fail(MPB_ERR_INVALID, "null state-space description");
+  const int D = space->dim;
+  if (D != s->img.state_dim) return fail(MPB_ERR_INVALID, "state-space dimension does not match the scene's state_dim");
+  if (D <= 0) return fail(MPB_ERR_INVALID, "empty state space");
+  for (int j = 0; j < D; j++)
+    if (!(space->seg[j] > 0.f) || !(space->hi[j] >= space->lo[j])) return fail(MPB_ERR_INVALID, "state-space bounds / segment lengths must be positive");
+  std::vector<float> h((size_t)4 * D, 0.f);
+  memcpy(h.data(), space->lo, D * sizeof(float));
+  memcpy(h.data() + D, space->hi, D * sizeof(float));
+  memcpy(h.data() + 2 * D, space->seg, D * sizeof(float));
+  unsigned char *so2 = reinterpret_cast<unsigned char *>(h.data() + 3 * D);
+  for (int j = 0; j < D; j++) so2[j] = space->so2 ? space->so2[j] : 0;
+  CU(cudaMalloc((void **)&out->buf, h.size() * sizeof(float)));
+  CU(cudaMemcpy(out->buf, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  out->sp.dim = D;
+  out->sp.lo = out->buf;
+  out->sp.hi = out->buf + D;
+  out->sp.seg = out->buf + 2 * D;
+  out->sp.so2 = reinterpret_cast<const unsigned char *>(out->buf + 3 * D);
+  return MPB_OK;
+}
+
+struct DevBufs {  // frees everything on scope exit
+  std::vector<void *> ptrs;
+  template <typename T>
+  cudaError_t alloc(T **p, size_t n) {
+    cudaError_t e = cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T));
+    if (e == cudaSuccess) ptrs.push_back(*p);
+    return e;
+  }
+  ~DevBufs() {
+    for (void *p : ptrs) cudaFree(p);
+  }
+};
+
+extern "C" int mpb_check_motion_batch(mpb_scene *s, const mpb_space_desc *space, const float *a, const float *b, int64_t n_edges,
+                                      uint32_t *valid_bits, mpb_stats *stats, int space_flag, void *stream) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n_edges < 0 || (n_edges > 0 && (!a || !b || !valid_bits))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (space_flag != MPB_HOST && space_flag != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
+  if (stats) memset(stats, 0, sizeof(*stats));
+  if (n_edges == 0) return MPB_OK;
+  if (n_edges > (1ll << 30)) return fail(MPB_ERR_CAPACITY, "too many edges in one call");
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  DevBufs bufs;
+  DevSpace dsp;
+  int rc = upload_space(s, space, &dsp);
+  if (dsp.buf) bufs.ptrs.push_back(dsp.buf);
+  if (rc != MPB_OK) return rc;
+  const int D = s->img.state_dim;
+  const bool host = space_flag == MPB_HOST;
+  const float *da = a, *db = b;
+  uint32_t *dvalid = valid_bits;
+  const size_t vwords = (size_t)(n_edges + 31) / 32;
+  if (host) {
+    float *ta = nullptr, *tb = nullptr;
+    CU(bufs.alloc(&ta, (size_t)n_edges * D));
+    CU(bufs.alloc(&tb, (size_t)n_edges * D));
+    CU(bufs.alloc(&dvalid, vwords));
+    CU(cudaMemcpyAsync(ta, a, (size_t)n_edges * D * sizeof(float), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(tb, b, (size_t)n_edges * D * sizeof(float), cudaMemcpyHostToDevice, st));
+    da = ta;
+    db = tb;
+  }
+  int *d_nd = nullptr;
+  unsigned *d_first = nullptr, *d_total = nullptr;
+  CU(bufs.alloc(&d_nd, (size_t)n_edges));
+  CU(bufs.alloc(&d_first, (size_t)n_edges));
+  CU(bufs.alloc(&d_total, 2));
+  CU(cudaMemsetAsync(d_total, 0, 2 * sizeof(unsigned), st));
+  const int eblocks = (int)((n_edges + 255) / 256);
+  motion_count_kernel<<<eblocks, 256, 0, st>>>(dsp.sp, da, db, n_edges, d_nd, d_first, d_total);
+  unsigned total = 0;
+  CU(cudaMemcpyAsync(&total, d_total, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (total == 0 || total > (1u << 30)) return fail(MPB_ERR_CAPACITY, "motion batch expands to too many states");
+  float *d_states = nullptr;
+  int *d_owner = nullptr;
+  uint32_t *d_verdict = nullptr;
+  CU(bufs.alloc(&d_states, (size_t)total * D));
+  CU(bufs.alloc(&d_owner, (size_t)total));
+  CU(bufs.alloc(&d_verdict, (size_t)(total + 31) / 32));
+  motion_expand_kernel<<<eblocks, 256, 0, st>>>(dsp.sp, da, db, n_edges, d_nd, d_first, 0, d_states, d_owner);
+  fill_valid_bits_kernel<<<(int)((vwords + 255) / 256), 256, 0, st>>>(dvalid, n_edges);
+  CU(cudaGetLastError());
+  mpb_stats inner;
+  rc = mpb_collide_batch(s, d_states, (int64_t)total, d_verdict, nullptr, &inner, MPB_DEVICE, (void *)st);
+  if (rc != MPB_OK) return rc;
+  motion_reduce_kernel<<<(int)((total + 255u) / 256u), 256, 0, st>>>(d_verdict, d_owner, total, dvalid);
+  CU(cudaGetLastError());
+  if (host) CU(cudaMemcpyAsync(valid_bits, dvalid, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));  // the scratch buffers are freed on return
+  if (stats) {
+    *stats = inner;
+    stats->kernel_launches += 4;
+  }
+  return MPB_OK;
+}
+
+extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, const float *starts, const float *goals,
+                                    const int32_t *n_goals, int32_t max_goals, int64_t n_queries, const mpb_rrt_params *params,
+                                    int32_t *status, int32_t *path_len, float *paths, mpb_rrt_stats *stats) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (!params) return fail(MPB_ERR_INVALID, "null parameters");
+  if (n_queries < 0 || max_goals < 1) return fail(MPB_ERR_INVALID, "bad query count / max_goals");
+  if (n_queries > 0 && (!starts || !goals || !n_goals || !status || !path_len || !paths)) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (stats) memset(stats, 0, sizeof(*stats));
+  if (n_queries == 0) return MPB_OK;
+  if (n_queries > (1 << 20)) return fail(MPB_ERR_CAPACITY, "too many queries in one call");
+  const auto t_begin = std::chrono::steady_clock::now();
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  DevBufs bufs;
+  DevSpace dsp;
+  int rc = upload_space(s, space, &dsp);
+  if (dsp.buf) bufs.ptrs.push_back(dsp.buf);
+  if (rc != MPB_OK) return rc;
+  const int D = s->img.state_dim, Q = (int)n_queries;
+  const int cap = std::max(params->tree_capacity, 2), max_path = std::max(params->max_path, 2);
+  const int max_rounds = std::max(params->max_rounds, 1), check_every = params->check_every > 0 ? params->check_every : 16;
+  float range = params->range;
+  if (!(range > 1e-6f)) {  // OMPL selfConfig: 20 % of the maximum extent (sum over the weighted subspaces)
+    double ext = 0;
+    for (int j = 0; j < D; j++) ext += (space->so2 && space->so2[j]) ? 3.14159265358979323846 : (double)space->hi[j] - space->lo[j];
+    range = (float)(0.2 * ext);
+  }
+  int smax = 1;
+  for (int j = 0; j < D; j++) smax = std::max(smax, (int)std::ceil((double)range / space->seg[j]) + 1);
+  if (smax > 4096) return fail(MPB_ERR_CAPACITY, "range / validity resolution gives too many samples per edge");
+  const long long n_states = (long long)Q * smax;
+  rc = prepare_work(s, (n_states + 31) / 32 * 32);
+  if (rc != MPB_OK) return rc;
+
+  RrtState r{};
+  r.n_queries = Q; r.cap = cap; r.dim = D; r.smax = smax; r.max_goals = max_goals; r.max_path = max_path;
+  r.seed = params->seed;
+  float *d_start = nullptr, *d_goals = nullptr, *d_states = nullptr, *d_paths = nullptr;
+  int *d_ngoals = nullptr, *d_ints = nullptr, *d_pathlen = nullptr;
+  uint32_t *d_verdict = nullptr;
+  CU(bufs.alloc(&r.nodes, (size_t)Q * 2 * cap * D));
+  CU(bufs.alloc(&r.parent, (size_t)Q * 2 * cap));
+  CU(bufs.alloc(&d_start, (size_t)Q * D));
+  CU(bufs.alloc(&d_goals, (size_t)Q * max_goals * D));
+  CU(bufs.alloc(&d_ngoals, (size_t)Q));
+  CU(bufs.alloc(&d_ints, (size_t)Q * 13 + 4));  // size[2] goals_used status phase flag tsel nearest reach added sol[2] iters
+  CU(bufs.alloc(&r.target, (size_t)Q * D));
+  CU(bufs.alloc(&r.edge_a, (size_t)Q * D));
+  CU(bufs.alloc(&r.edge_b, (size_t)Q * D));
+  CU(bufs.alloc(&d_states, (size_t)n_states * D));
+  CU(bufs.alloc(&d_verdict, (size_t)(n_states + 31) / 32 + 1));
+  CU(bufs.alloc(&d_paths, (size_t)Q * max_path * D));
+  CU(bufs.alloc(&d_pathlen, (size_t)Q));
+  r.size = d_ints;
+  r.goals_used = d_ints + 2 * Q; r.status = d_ints + 3 * Q; r.phase = d_ints + 4 * Q; r.flag_start = d_ints + 5 * Q;
+  r.tsel = d_ints + 6 * Q; r.nearest = d_ints + 7 * Q; r.reach = d_ints + 8 * Q; r.added = d_ints + 9 * Q;
+  r.sol = d_ints + 10 * Q; r.iters = d_ints + 12 * Q;
+  r.n_active = reinterpret_cast<unsigned *>(d_ints + 13 * Q);
+  r.start = d_start; r.goals = d_goals; r.n_goals = d_ngoals;
+  {
+    std::vector<int> h((size_t)Q * 13 + 4, 0);
+    for (int q = 0; q < Q; q++) {
+      h[2 * q] = 1;          // tStart_ holds the start state
+      h[5 * (size_t)Q + q] = 1;  // startTree_ = true
+    }
+    h[13 * (size_t)Q] = Q;
+    CU(cudaMemcpyAsync(d_ints, h.data(), h.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(r.parent, 0xff, (size_t)Q * 2 * cap * sizeof(int), st));
+    CU(cudaMemcpyAsync(d_start, starts, (size_t)Q * D * sizeof(float), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_goals, goals, (size_t)Q * max_goals * D * sizeof(float), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_ngoals, n_goals, (size_t)Q * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpy2DAsync(r.nodes, (size_t)2 * cap * D * sizeof(float), d_start, (size_t)D * sizeof(float), (size_t)D * sizeof(float), Q,
+                         cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemsetAsync(d_verdict, 0, ((size_t)(n_states + 31) / 32 + 1) * sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(r.edge_a, 0, (size_t)Q * D * sizeof(float), st));
+    CU(cudaMemsetAsync(r.edge_b, 0, (size_t)Q * D * sizeof(float), st));
+    CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
+    CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
+    CU(cudaStreamSynchronize(st));  // h goes out of scope
+  }
+  long long launches_per_round = 0;
+  auto enqueue_round = [&](long long *launches) -> int {
+    size_t sync_ev = 0;
+    rrt_advance_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
+    motion_expand_kernel<<<(Q + 255) / 256, 256, 0, st>>>(dsp.sp, r.edge_a, r.edge_b, Q, nullptr, nullptr, smax, d_states, nullptr);
+    *launches += 2;
+    return launch_pass(s, nullptr, d_states, n_states, d_verdict, nullptr, st, nullptr, launches, nullptr, &sync_ev);
+  };
+  // the round has fixed launch shapes: capture it once, replay it
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  const bool use_graph = getenv("MPB_NO_GRAPH") == nullptr;
+  if (use_graph) {
+    CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue_round(&launches_per_round);
+    cudaError_t ce = cudaStreamEndCapture(st, &graph);
+    if (rc != MPB_OK || ce != cudaSuccess) {
+      if (graph) cudaGraphDestroy(graph);
+      return rc != MPB_OK ? rc : fail(MPB_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(ce));
+    }
+    CU(cudaGraphInstantiate(&exec, graph, 0));
+  }
+  cudaEvent_t e0 = get_event(s, 0), e1 = get_event(s, 1);
+  CU(cudaEventRecord(e0, st));
+  long long rounds = 0, launches = 0;
+  unsigned n_active = (unsigned)Q;
+  unsigned totals[8] = {0};
+  while (rounds < max_rounds && n_active > 0) {
+    const int k = (int)std::min<long long>(check_every, max_rounds - rounds);
+    for (int i = 0; i < k; i++) {
+      if (use_graph) { CU(cudaGraphLaunch(exec, st)); launches += launches_per_round; }
+      else { rc = enqueue_round(&launches); if (rc != MPB_OK) return rc; }
+    }
+    rounds += k;
+    CU(cudaMemcpyAsync(&n_active, r.n_active, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(totals, s->wq.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (totals[2]) { rc = fail(MPB_ERR_CAPACITY, "work queue overflow inside the planning round"); break; }
+    if (params->time_limit_s > 0.f &&
+        std::chrono::duration<float>(std::chrono::steady_clock::now() - t_begin).count() > params->time_limit_s) break;
+  }
+  if (exec) cudaGraphExecDestroy(exec);
+  if (graph) cudaGraphDestroy(graph);
+  if (rc != MPB_OK) return rc;
+  // one more advance so that the verdict of the last round is consumed (it may complete a query)
+  rrt_advance_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
+  r.max_path = max_path;
+  rrt_extract_kernel<<<(Q + 127) / 128, 128, 0, st>>>(r, d_paths, d_pathlen);
+  launches += 2;
+  CU(cudaEventRecord(e1, st));
+  CU(cudaGetLastError());
+  std::vector<int> h_iters(Q);
+  CU(cudaMemcpyAsync(status, r.status, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(path_len, d_pathlen, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(paths, d_paths, (size_t)Q * max_path * D * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(h_iters.data(), r.iters, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (stats) {
+    stats->rounds = rounds;
+    stats->states_checked = rounds * n_states;
+    stats->kernel_launches = launches;
+    for (int q = 0; q < Q; q++) {
+      stats->grow_calls += h_iters[q];
+      stats->n_solved += status[q] == MPB_RRT_SOLVED;
+    }
+    cudaEventElapsedTime(&stats->gpu_ms, e0, e1);
+    stats->host_ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+  }
   return MPB_OK;
 }

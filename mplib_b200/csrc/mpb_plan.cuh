@@ -1,0 +1,280 @@
+// mpb_plan.cuh -- kernels of the planning layer on top of the batched validity check.
+//
+//   motion_count_kernel / motion_expand_kernel / motion_reduce_kernel
+//       Batched ompl::base::DiscreteMotionValidator::checkMotion [upstream OMPL 1.6.0] as the reference sets it up
+//       (src/ompl_planner.cpp:62-70, validity resolution 1 %): an edge (a, b) is valid iff b and the interior samples
+//       a + (j/nd)(b - a), j = 1..nd-1, are valid, with nd = max over the 1-D subspaces of
+//       ceil(|b_j - a_j| / (0.01 * extent_j))  (CompoundStateSpace::validSegmentCount).  All samples of all edges
+//       become ONE batch for the validity kernels; a per-edge AND folds the verdicts.
+//   rrt_advance_kernel / rrt_extract_kernel
+//       RRTConnect [upstream OMPL 1.6.0 geometric/planners/rrt/src/RRTConnect.cpp] for Q independent queries in
+//       lock-step (replaces the RRTConnect branch of OMPLPlannerTpl::plan, src/ompl_planner.cpp:97-243).  One
+//       warp per query; one growTree() call per query per round.  A round is: advance (consume the previous
+//       edge verdict, update the trees, emit the next edge) -> expand the edges into samples -> validity kernels.
+//       The per-round kernel sequence has fixed shapes, so the host captures it once in a CUDA graph.
+#pragma once
+#include "mpb_kernels.cuh"
+
+// distance / interpolation of the compound space: 1-D RealVector subspaces (L1 sum) and SO(2) subspaces
+__device__ __forceinline__ float ss_delta(float a, float b, bool so2) {
+  float d = b - a;
+  if (so2) {
+    const float PI_F = 3.14159265358979323846f;
+    if (d > PI_F) d -= 2.f * PI_F;
+    else if (d < -PI_F) d += 2.f * PI_F;
+  }
+  return d;
+}
+__device__ __forceinline__ float ss_interp(float a, float b, float t, bool so2) {
+  float v = fmaf(ss_delta(a, b, so2), t, a);
+  if (so2) {
+    const float PI_F = 3.14159265358979323846f;
+    if (v > PI_F) v -= 2.f * PI_F;
+    else if (v < -PI_F) v += 2.f * PI_F;
+  }
+  return v;
+}
+
+struct SpaceDesc {
+  int dim;
+  const float *lo, *hi;      // [dim] sampling bounds
+  const float *seg;          // [dim] longest valid segment per subspace (0.01 * extent)
+  const unsigned char *so2;  // [dim] 1 = SO(2) subspace (continuous joint)
+};
+
+__device__ __forceinline__ int ss_segment_count(const SpaceDesc &sp, const float *a, const float *b) {
+  int nd = 0;
+  for (int j = 0; j < sp.dim; j++) {
+    const float d = fabsf(ss_delta(a[j], b[j], sp.so2[j] != 0));
+    nd = max(nd, (int)ceilf(d / sp.seg[j]));
+  }
+  return nd;
+}
+
+// ---------------------------------------------------------------------------------------------- motion validation
+// pass 1: samples per edge (max(nd, 1): b itself plus nd-1 interior points) and unordered slot allocation
+__global__ void __launch_bounds__(256) motion_count_kernel(SpaceDesc sp, const float *__restrict__ a, const float *__restrict__ b,
+                                                           long long n_edges, int *__restrict__ nd_out,
+                                                           unsigned *__restrict__ first_out, unsigned *__restrict__ total) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int nd = 0;
+  if (e < n_edges) nd = ss_segment_count(sp, a + e * sp.dim, b + e * sp.dim);
+  const unsigned cnt = e < n_edges ? (unsigned)max(nd, 1) : 0u;
+  // warp-aggregated allocation
+  unsigned incl = cnt;
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  const unsigned wtot = __shfl_sync(0xffffffffu, incl, 31);
+  unsigned base = 0;
+  if (lane == 31 && wtot) base = atomicAdd(total, wtot);
+  base = __shfl_sync(0xffffffffu, base, 31);
+  if (e < n_edges) {
+    nd_out[e] = nd;
+    first_out[e] = base + incl - cnt;
+  }
+}
+
+// pass 2: write the samples.  Fixed-stride mode (first == nullptr): edge e owns slots [e*stride, (e+1)*stride) and
+// unused slots repeat b, so the per-edge OR over all its slots is unchanged.
+__global__ void __launch_bounds__(256) motion_expand_kernel(SpaceDesc sp, const float *__restrict__ a, const float *__restrict__ b,
+                                                            long long n_edges, const int *__restrict__ nd_in,
+                                                            const unsigned *__restrict__ first, int stride,
+                                                            float *__restrict__ states, int *__restrict__ owner) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_edges) return;
+  const float *pa = a + e * sp.dim, *pb = b + e * sp.dim;
+  const int nd = nd_in ? nd_in[e] : ss_segment_count(sp, pa, pb);
+  const int cnt = first ? max(nd, 1) : stride;
+  const size_t s0 = first ? (size_t)first[e] : (size_t)e * stride;
+  for (int k = 0; k < cnt; k++) {
+    const int j = k + 1;  // sample j/nd; j >= nd is b itself
+    float *o = states + (s0 + k) * sp.dim;
+    if (j >= nd) {
+      for (int c = 0; c < sp.dim; c++) o[c] = pb[c];
+    } else {
+      const float t = (float)j / (float)nd;
+      for (int c = 0; c < sp.dim; c++) o[c] = ss_interp(pa[c], pb[c], t, sp.so2[c] != 0);
+    }
+    if (owner) owner[s0 + k] = (int)e;
+  }
+}
+
+// pass 3: valid_bits starts all-ones; a colliding sample clears the bit of its edge
+__global__ void __launch_bounds__(256) motion_reduce_kernel(const unsigned *__restrict__ verdict_bits, const int *__restrict__ owner,
+                                                            unsigned n_states, unsigned *__restrict__ valid_bits) {
+  const unsigned s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_states) return;
+  if ((verdict_bits[s >> 5] >> (s & 31)) & 1u) {
+    const int e = owner[s];
+    atomicAnd(&valid_bits[e >> 5], ~(1u << (e & 31)));
+  }
+}
+
+__global__ void fill_valid_bits_kernel(unsigned *__restrict__ valid_bits, long long n_edges) {
+  const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long words = (n_edges + 31) / 32;
+  if (w >= words) return;
+  const long long rem = n_edges - w * 32;
+  valid_bits[w] = rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+}
+
+// ---------------------------------------------------------------------------------------------- RRTConnect, lock-step
+struct RrtState {
+  int n_queries, cap, dim, smax, max_goals, max_path;
+  float *nodes;        // [Q][2][cap][dim]   tree 0 = tStart_, tree 1 = tGoal_
+  int *parent;         // [Q][2][cap]        -1 = root
+  int *size;           // [Q][2]
+  const float *start;  // [Q][dim]
+  const float *goals;  // [Q][max_goals][dim]
+  const int *n_goals;  // [Q]
+  int *goals_used;     // [Q]  pis_.getSampledGoalsCount()
+  int *status;         // [Q]  MPB_RRT_*
+  int *phase;          // [Q]  0 = nothing pending, 1 = first growTree of an iteration pending, 2 = connect step pending
+  int *flag_start;     // [Q]  startTree_
+  int *tsel;           // [Q]  tree the pending edge grows
+  int *nearest;        // [Q]  nmotion of the pending edge
+  int *reach;          // [Q]
+  int *added;          // [Q]  addedMotion (index in tree 1 - tsel while connecting)
+  float *target;       // [Q][dim]  rstate
+  float *edge_a;       // [Q][dim]  nmotion->state
+  float *edge_b;       // [Q][dim]  dstate
+  int *sol;            // [Q][2]   solution motions in tree 0 / tree 1
+  int *iters;          // [Q]      growTree calls issued
+  unsigned *n_active;  // [1]
+  unsigned long long seed;
+};
+
+__device__ __forceinline__ float rrt_uniform(unsigned long long seed, unsigned q, unsigned counter, unsigned j) {
+  unsigned long long z = seed + 0x9E3779B97F4A7C15ull * ((((unsigned long long)q << 32) | counter) * 64ull + j + 1ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;  // splitmix64 finaliser
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+// One warp per query, one RRTConnect::growTree call per round.
+__global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc sp, float range, const unsigned *__restrict__ verdict_bits) {
+  const unsigned FULL = 0xffffffffu;
+  const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (q >= r.n_queries) return;
+  if (r.status[q] != MPB_RRT_ACTIVE) return;
+  const int D = r.dim;
+  float *ea = r.edge_a + (size_t)q * D, *eb = r.edge_b + (size_t)q * D, *tg = r.target + (size_t)q * D;
+  int phase = r.phase[q];
+  int T = r.tsel[q];
+  bool new_iter = phase == 0;
+  if (phase != 0) {
+    // ---- verdict of the pending edge: invalid if any of its samples collides
+    bool coll = false;
+    for (int k = lane; k < r.smax; k += 32) {
+      const unsigned s = (unsigned)q * r.smax + k;
+      coll |= ((verdict_bits[s >> 5] >> (s & 31)) & 1u) != 0;
+    }
+    coll = __any_sync(FULL, coll);
+    if (coll) new_iter = true;  // TRAPPED
+    else {
+      const int n = r.size[q * 2 + T];
+      if (n >= r.cap) {
+        if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
+        return;
+      }
+      float *node = r.nodes + (((size_t)q * 2 + T) * r.cap + n) * D;
+      for (int j = lane; j < D; j += 32) node[j] = eb[j];
+      if (lane == 0) { r.parent[((size_t)q * 2 + T) * r.cap + n] = r.nearest[q]; r.size[q * 2 + T] = n + 1; }
+      if (phase == 1) {  // first tree advanced: now connect the other tree to the new state
+        for (int j = lane; j < D; j += 32) tg[j] = eb[j];
+        if (lane == 0) { r.added[q] = n; r.tsel[q] = 1 - T; r.phase[q] = 2; }
+        T = 1 - T;
+        phase = 2;
+      } else if (r.reach[q]) {  // REACHED: the trees meet
+        if (lane == 0) {
+          const int m_first = r.added[q], m_other = n;  // first tree = 1 - T
+          int is = T == 0 ? m_other : m_first, ig = T == 0 ? m_first : m_other;
+          const int ps = r.parent[((size_t)q * 2 + 0) * r.cap + is];
+          if (ps >= 0) is = ps;  // one step back so the shared state is not duplicated on the path
+          else ig = r.parent[((size_t)q * 2 + 1) * r.cap + ig];
+          r.sol[q * 2] = is;
+          r.sol[q * 2 + 1] = ig;
+          r.status[q] = MPB_RRT_SOLVED;
+          atomicSub(r.n_active, 1u);
+        }
+        return;
+      }
+      __syncwarp();
+    }
+  }
+  if (new_iter) {
+    // ---- head of the solve loop: pick the tree, maybe admit another goal, sample
+    const int fs = r.flag_start[q];
+    T = fs ? 0 : 1;
+    const int gsz = r.size[q * 2 + 1], used = r.goals_used[q];
+    if ((gsz == 0 || used < gsz / 2) && used < r.n_goals[q]) {
+      if (gsz >= r.cap) {
+        if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
+        return;
+      }
+      float *node = r.nodes + (((size_t)q * 2 + 1) * r.cap + gsz) * D;
+      const float *g = r.goals + ((size_t)q * r.max_goals + used) * D;
+      for (int j = lane; j < D; j += 32) node[j] = g[j];
+      if (lane == 0) { r.parent[((size_t)q * 2 + 1) * r.cap + gsz] = -1; r.size[q * 2 + 1] = gsz + 1; r.goals_used[q] = used + 1; }
+    } else if (gsz == 0) {
+      if (lane == 0) { r.status[q] = MPB_RRT_INVALID_GOAL; atomicSub(r.n_active, 1u); }
+      return;
+    }
+    const unsigned ctr = (unsigned)r.iters[q];
+    for (int j = lane; j < D; j += 32) tg[j] = fmaf(sp.hi[j] - sp.lo[j], rrt_uniform(r.seed, (unsigned)q, ctr, (unsigned)j), sp.lo[j]);
+    if (lane == 0) { r.flag_start[q] = !fs; r.tsel[q] = T; r.phase[q] = 1; }
+    __syncwarp();
+  }
+  // ---- growTree, first half: nearest neighbour in tree T and the state to add
+  const int n = r.size[q * 2 + T];
+  const float *base = r.nodes + ((size_t)q * 2 + T) * r.cap * D;
+  float best = FLT_MAX;
+  int bi = 0x7fffffff;
+  for (int i = lane; i < n; i += 32) {
+    float d = 0.f;
+    for (int j = 0; j < D; j++) d += fabsf(ss_delta(base[(size_t)i * D + j], tg[j], sp.so2[j] != 0));
+    if (d < best) { best = d; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(FULL, best, o);
+    const int oi = __shfl_xor_sync(FULL, bi, o);
+    if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  const bool reach = !(best > range);
+  for (int j = lane; j < D; j += 32) {
+    const float a = base[(size_t)bi * D + j];
+    ea[j] = a;
+    eb[j] = reach ? tg[j] : ss_interp(a, tg[j], range / best, sp.so2[j] != 0);
+  }
+  if (lane == 0) { r.nearest[q] = bi; r.reach[q] = reach ? 1 : 0; r.iters[q] += 1; }
+}
+
+// Solution path of every solved query: start chain (root first) then goal chain (towards its root).
+__global__ void rrt_extract_kernel(RrtState r, float *__restrict__ paths, int *__restrict__ path_len) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= r.n_queries) return;
+  path_len[q] = 0;
+  if (r.status[q] != MPB_RRT_SOLVED) return;
+  const int D = r.dim;
+  const int *p0 = r.parent + ((size_t)q * 2 + 0) * r.cap, *p1 = r.parent + ((size_t)q * 2 + 1) * r.cap;
+  int ls = 0, lg = 0;
+  for (int i = r.sol[q * 2]; i >= 0; i = p0[i]) ls++;
+  for (int i = r.sol[q * 2 + 1]; i >= 0; i = p1[i]) lg++;
+  if (ls + lg > r.max_path) { r.status[q] = MPB_RRT_PATH_TOO_LONG; return; }
+  float *out = paths + (size_t)q * r.max_path * D;
+  const float *n0 = r.nodes + ((size_t)q * 2 + 0) * r.cap * D, *n1 = r.nodes + ((size_t)q * 2 + 1) * r.cap * D;
+  int k = ls - 1;
+  for (int i = r.sol[q * 2]; i >= 0; i = p0[i], k--)
+    for (int j = 0; j < D; j++) out[(size_t)k * D + j] = n0[(size_t)i * D + j];
+  k = ls;
+  for (int i = r.sol[q * 2 + 1]; i >= 0; i = p1[i], k++)
+    for (int j = 0; j < D; j++) out[(size_t)k * D + j] = n1[(size_t)i * D + j];
+  path_len[q] = ls + lg;
+}

@@ -950,3 +950,198 @@ int orc_sat_batch_mt(const mpb_scene_desc *d, const double *states, int64_t n_it
   }
   return rc;
 }
+
+/* ------------------------------------------------------------------ planning layer (CPU restatement)
+ * State space of OMPLPlannerTpl::build_state_space (src/ompl_planner.cpp:245-296): 1-D RealVector subspaces
+ * (and SO(2) for continuous joints), weight 1 each => distance = sum_j |delta_j|  [upstream OMPL 1.6.0
+ * CompoundStateSpace::distance / interpolate / validSegmentCount].  seg[j] = 0.01 * extent_j. */
+#include <time.h>
+#define ORC_PI 3.14159265358979323846
+static double ss_delta(double a, double b, int so2) {
+  double d = b - a;
+  if (so2) { if (d > ORC_PI) d -= 2 * ORC_PI; else if (d < -ORC_PI) d += 2 * ORC_PI; }
+  return d;
+}
+static double ss_interp1(double a, double b, double t, int so2) {
+  double v = a + ss_delta(a, b, so2) * t;
+  if (so2) { if (v > ORC_PI) v -= 2 * ORC_PI; else if (v < -ORC_PI) v += 2 * ORC_PI; }
+  return v;
+}
+static double ss_distance(int D, const uint8_t *so2, const double *a, const double *b) {
+  double d = 0; for (int j = 0; j < D; j++) d += fabs(ss_delta(a[j], b[j], so2 ? so2[j] : 0)); return d;
+}
+static int ss_segment_count(int D, const double *seg, const uint8_t *so2, const double *a, const double *b) {
+  int nd = 0;
+  for (int j = 0; j < D; j++) { int c = (int)ceil(fabs(ss_delta(a[j], b[j], so2 ? so2[j] : 0)) / seg[j]); if (c > nd) nd = c; }
+  return nd;
+}
+
+typedef struct { const mpb_scene_desc *d; xf_t *oMi; xf_t *objT; double *qf; int64_t checks; } orc_checker;
+static void checker_init(orc_checker *c, const mpb_scene_desc *d) {
+  c->d = d; c->checks = 0;
+  c->oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  c->objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
+  c->qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+}
+static void checker_free(orc_checker *c) { free(c->oMi); free(c->objT); free(c->qf); }
+/* ValidityCheckerTpl::isValid (src/ompl_planner.h:59-62): setQposAll + !collide(); collide() has no early exit
+ * (src/planning_world.h:248-250), so every admitted pair is tested. */
+static int checker_is_valid(orc_checker *c, const double *state) {
+  const mpb_scene_desc *d = c->d;
+  scatter_state(d, state, c->qf); fk_joints(d, c->qf, c->oMi); object_transforms(d, c->oMi, c->objT, NULL);
+  int any = 0;
+  for (int p = 0; p < d->n_pairs; p++) { int a = d->pair_a[p], b = d->pair_b[p]; any |= object_collide(d, a, &c->objT[a], b, &c->objT[b]); }
+  c->checks++;
+  return !any;
+}
+/* [upstream OMPL 1.6.0] DiscreteMotionValidator::checkMotion(s1, s2): s2 first, then the interior points in
+ * bisection order with early exit. */
+static int checker_motion(orc_checker *c, int D, const double *seg, const uint8_t *so2, const double *s1, const double *s2) {
+  if (!checker_is_valid(c, s2)) return 0;
+  int nd = ss_segment_count(D, seg, so2, s1, s2);
+  int result = 1;
+  if (nd >= 2) {
+    int *queue = (int *)malloc(sizeof(int) * 2 * (size_t)(nd + 2));
+    double *test = (double *)malloc(sizeof(double) * (size_t)D);
+    int head = 0, tail = 0;
+    queue[2 * tail] = 1; queue[2 * tail + 1] = nd - 1; tail++;
+    while (head < tail) {
+      int lo = queue[2 * head], hi = queue[2 * head + 1];
+      int mid = (lo + hi) / 2;
+      for (int j = 0; j < D; j++) test[j] = ss_interp1(s1[j], s2[j], (double)mid / (double)nd, so2 ? so2[j] : 0);
+      if (!checker_is_valid(c, test)) { result = 0; break; }
+      head++;
+      if (lo < mid) { queue[2 * tail] = lo; queue[2 * tail + 1] = mid - 1; tail++; }
+      if (hi > mid) { queue[2 * tail] = mid + 1; queue[2 * tail + 1] = hi; tail++; }
+    }
+    free(queue); free(test);
+  }
+  return result;
+}
+
+int orc_check_motion_batch(const mpb_scene_desc *d, int D, const double *seg, const uint8_t *so2, const double *a, const double *b,
+                           int64_t n_edges, uint8_t *valid, int64_t *n_states, int nthreads) {
+  if (D != d->state_dim) return MPB_ERR_INVALID;
+  int64_t total = 0;
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel for num_threads(nthreads) schedule(static) reduction(+ : total)
+  for (int t = 0; t < nthreads; t++) {
+    orc_checker c; checker_init(&c, d);
+    for (int64_t e = n_edges * t / nthreads; e < n_edges * (t + 1) / nthreads; e++)
+      valid[e] = (uint8_t)checker_motion(&c, D, seg, so2, a + e * D, b + e * D);
+    total += c.checks;
+    checker_free(&c);
+  }
+  if (n_states) *n_states = total;
+  return 0;
+}
+
+/* ---- RRTConnect [upstream OMPL 1.6.0 geometric/planners/rrt/src/RRTConnect.cpp], as OMPLPlannerTpl::plan runs it
+ * (src/ompl_planner.cpp:160-165, 217-221): no path simplification, GoalStates goal, brute-force nearest. */
+typedef struct { double *st; int *parent; int n, cap; } orc_tree;
+static int tree_add(orc_tree *t, int D, const double *s, int parent) {
+  if (t->n == t->cap) { t->cap = t->cap ? 2 * t->cap : 256; t->st = (double *)realloc(t->st, sizeof(double) * (size_t)t->cap * D); t->parent = (int *)realloc(t->parent, sizeof(int) * (size_t)t->cap); }
+  memcpy(t->st + (size_t)t->n * D, s, sizeof(double) * (size_t)D); t->parent[t->n] = parent; return t->n++;
+}
+static uint64_t orc_rng_next(uint64_t *s) { uint64_t z = (*s += 0x9E3779B97F4A7C15ull); z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; return z ^ (z >> 31); }
+static double orc_rng_uniform(uint64_t *s) { return (double)(orc_rng_next(s) >> 11) * (1.0 / 9007199254740992.0); }
+
+typedef struct { int D; const double *lo, *hi, *seg; const uint8_t *so2; double range; orc_checker *chk; double *xstate; int xmotion; } orc_rrt_ctx;
+enum { ORC_TRAPPED = 0, ORC_ADVANCED = 1, ORC_REACHED = 2 };
+static int grow_tree(orc_rrt_ctx *c, orc_tree *tree, int is_start, const double *rstate) {
+  int D = c->D, nm = 0; double best = DBL_MAX;
+  for (int i = 0; i < tree->n; i++) { double dd = ss_distance(D, c->so2, tree->st + (size_t)i * D, rstate); if (dd < best) { best = dd; nm = i; } }
+  const double *ns = tree->st + (size_t)nm * D;
+  const double *dstate = rstate; int reach = 1;
+  if (best > c->range) {
+    for (int j = 0; j < D; j++) c->xstate[j] = ss_interp1(ns[j], rstate[j], c->range / best, c->so2 ? c->so2[j] : 0);
+    int same = 1; for (int j = 0; j < D; j++) if (c->xstate[j] != ns[j]) same = 0;
+    if (same) return ORC_TRAPPED;
+    dstate = c->xstate; reach = 0;
+  }
+  int valid = is_start ? checker_motion(c->chk, D, c->seg, c->so2, ns, dstate)
+                       : (checker_is_valid(c->chk, dstate) && checker_motion(c->chk, D, c->seg, c->so2, dstate, ns));
+  if (!valid) return ORC_TRAPPED;
+  double *tmp = (double *)malloc(sizeof(double) * (size_t)D); memcpy(tmp, dstate, sizeof(double) * (size_t)D);
+  c->xmotion = tree_add(tree, D, tmp, nm); free(tmp);
+  return reach ? ORC_REACHED : ORC_ADVANCED;
+}
+
+/* Returns 1 = "Exact solution", 0 = timeout / iteration budget exhausted, 3 = no valid goal.
+ * path_out: [max_path][D]; *path_len = 0 unless solved and it fits. */
+int orc_rrtconnect(const mpb_scene_desc *d, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
+                   const double *start, const double *goals, int n_goals, double range, int64_t max_grow_calls, double time_limit_s,
+                   uint64_t seed, double *path_out, int max_path, int *path_len, int64_t *grow_calls, int64_t *state_checks) {
+  if (D != d->state_dim) return MPB_ERR_INVALID;
+  orc_checker chk; checker_init(&chk, d);
+  orc_rrt_ctx c; c.D = D; c.lo = lo; c.hi = hi; c.seg = seg; c.so2 = so2; c.range = range; c.chk = &chk;
+  c.xstate = (double *)malloc(sizeof(double) * (size_t)D); c.xmotion = -1;
+  if (!(range > 1e-6)) { double ext = 0; for (int j = 0; j < D; j++) ext += (so2 && so2[j]) ? ORC_PI : hi[j] - lo[j]; c.range = 0.2 * ext; }
+  orc_tree T[2]; memset(T, 0, sizeof(T));
+  tree_add(&T[0], D, start, -1);
+  double *rstate = (double *)malloc(sizeof(double) * (size_t)D);
+  int goals_used = 0, start_tree = 1, solved = 0; int64_t calls = 0;
+  struct timespec t0; clock_gettime(CLOCK_MONOTONIC, &t0);
+  *path_len = 0;
+  int status = 0;
+  while (calls < max_grow_calls) {
+    if (time_limit_s > 0) { struct timespec t1; clock_gettime(CLOCK_MONOTONIC, &t1); if ((t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec) > time_limit_s) break; }
+    orc_tree *tree = start_tree ? &T[0] : &T[1]; int tgi_start = start_tree; start_tree = !start_tree;
+    orc_tree *other = start_tree ? &T[0] : &T[1];
+    if (T[1].n == 0 || goals_used < T[1].n / 2) {
+      while (goals_used < n_goals) { /* pis_.nextGoal(): invalid goal states are skipped */
+        const double *g = goals + (size_t)goals_used * D; goals_used++;
+        if (checker_is_valid(&chk, g)) { tree_add(&T[1], D, g, -1); break; }
+      }
+      if (T[1].n == 0) { status = 3; break; }
+    }
+    for (int j = 0; j < D; j++) rstate[j] = lo[j] + (hi[j] - lo[j]) * orc_rng_uniform(&seed);
+    int gs = grow_tree(&c, tree, tgi_start, rstate); calls++;
+    if (gs != ORC_TRAPPED) {
+      int added = c.xmotion;
+      if (gs != ORC_REACHED) memcpy(rstate, tree->st + (size_t)added * D, sizeof(double) * (size_t)D);
+      int other_is_start = start_tree;
+      int gsc = ORC_ADVANCED;
+      while (gsc == ORC_ADVANCED && calls < max_grow_calls) { gsc = grow_tree(&c, other, other_is_start, rstate); calls++; }
+      if (gsc == ORC_REACHED) {
+        int is = other_is_start ? c.xmotion : added, ig = other_is_start ? added : c.xmotion;
+        if (T[0].parent[is] >= 0) is = T[0].parent[is]; else ig = T[1].parent[ig];
+        int ls = 0, lg = 0;
+        for (int i = is; i >= 0; i = T[0].parent[i]) ls++;
+        for (int i = ig; i >= 0; i = T[1].parent[i]) lg++;
+        if (ls + lg <= max_path) {
+          int k = ls - 1;
+          for (int i = is; i >= 0; i = T[0].parent[i], k--) memcpy(path_out + (size_t)k * D, T[0].st + (size_t)i * D, sizeof(double) * (size_t)D);
+          k = ls;
+          for (int i = ig; i >= 0; i = T[1].parent[i], k++) memcpy(path_out + (size_t)k * D, T[1].st + (size_t)i * D, sizeof(double) * (size_t)D);
+          *path_len = ls + lg;
+        }
+        solved = 1; status = 1; break;
+      }
+    }
+  }
+  (void)solved;
+  if (grow_calls) *grow_calls = calls;
+  if (state_checks) *state_checks = chk.checks;
+  free(T[0].st); free(T[0].parent); free(T[1].st); free(T[1].parent); free(rstate); free(c.xstate); checker_free(&chk);
+  return status;
+}
+
+/* Q independent queries, one per OpenMP thread at a time (the all-host-core CPU baseline of BASELINE.md 3). */
+int orc_rrtconnect_batch(const mpb_scene_desc *d, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
+                         const double *starts, const double *goals, const int32_t *n_goals, int max_goals, int64_t n_queries, double range,
+                         int64_t max_grow_calls, double time_limit_s, uint64_t seed, int32_t *status, int32_t *path_len, double *paths,
+                         int max_path, int64_t *grow_calls, int64_t *state_checks, int nthreads) {
+  int64_t gc = 0, sc = 0;
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 1) reduction(+ : gc, sc)
+  for (int64_t q = 0; q < n_queries; q++) {
+    int pl = 0; int64_t g1 = 0, s1 = 0;
+    status[q] = orc_rrtconnect(d, D, lo, hi, seg, so2, starts + q * D, goals + (size_t)q * max_goals * D, n_goals[q], range, max_grow_calls,
+                               time_limit_s, seed + 7919ull * (uint64_t)q, paths + (size_t)q * max_path * D, max_path, &pl, &g1, &s1);
+    path_len[q] = pl; gc += g1; sc += s1;
+  }
+  if (grow_calls) *grow_calls = gc;
+  if (state_checks) *state_checks = sc;
+  return 0;
+}
