@@ -8,6 +8,45 @@ import numpy as np
 
 from .scene import MpbSceneDesc, MpbStats, SceneDesc
 
+
+class MpbSpaceDesc(C.Structure):
+    """``mpb_space_desc``: the compound planning space of ``OMPLPlannerTpl::build_state_space``."""
+
+    _fields_ = [("dim", C.c_int32), ("lo", C.POINTER(C.c_float)), ("hi", C.POINTER(C.c_float)),
+                ("seg", C.POINTER(C.c_float)), ("so2", C.POINTER(C.c_uint8))]
+
+
+class MpbRrtParams(C.Structure):
+    _fields_ = [("range", C.c_float), ("max_rounds", C.c_int32), ("time_limit_s", C.c_float), ("tree_capacity", C.c_int32),
+                ("max_path", C.c_int32), ("seed", C.c_uint64), ("check_every", C.c_int32)]
+
+
+class MpbRrtStats(C.Structure):
+    _fields_ = [("rounds", C.c_int64), ("grow_calls", C.c_int64), ("states_checked", C.c_int64), ("n_solved", C.c_int64),
+                ("kernel_launches", C.c_int64), ("gpu_ms", C.c_float), ("host_ms_total", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+RRT_ACTIVE, RRT_SOLVED, RRT_CAPACITY, RRT_INVALID_GOAL, RRT_PATH_TOO_LONG = range(5)
+
+
+class Space:
+    """Host arrays of a planning space + the ctypes struct pointing into them."""
+
+    def __init__(self, lo, hi, so2=None, resolution=0.01):
+        self.lo = np.ascontiguousarray(np.asarray(lo, dtype=np.float32))
+        self.hi = np.ascontiguousarray(np.asarray(hi, dtype=np.float32))
+        self.dim = int(self.lo.shape[0])
+        self.so2 = np.ascontiguousarray(np.zeros(self.dim, np.uint8) if so2 is None else np.asarray(so2, dtype=np.uint8))
+        # longest valid segment per subspace: resolution * maximum extent (pi for SO(2))  [upstream OMPL]
+        ext = np.where(self.so2 != 0, np.pi, self.hi.astype(np.float64) - self.lo.astype(np.float64))
+        self.seg64 = resolution * ext
+        self.seg = np.ascontiguousarray(self.seg64.astype(np.float32))
+        self.struct = MpbSpaceDesc(self.dim, self.lo.ctypes.data_as(C.POINTER(C.c_float)), self.hi.ctypes.data_as(C.POINTER(C.c_float)),
+                                   self.seg.ctypes.data_as(C.POINTER(C.c_float)), self.so2.ctypes.data_as(C.POINTER(C.c_uint8)))
+
 MPB_HOST, MPB_DEVICE = 0, 1
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmpb.so")
@@ -16,6 +55,7 @@ LIB_PATH = os.path.join(_HERE, "libmpb.so")
 SYMBOLS = [
     "mpb_last_error", "mpb_device_count", "mpb_scene_create", "mpb_scene_destroy", "mpb_scene_set_q_base",
     "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
+    "mpb_check_motion_batch", "mpb_rrtconnect_batch",
 ]
 
 _lib = None
@@ -47,6 +87,11 @@ def load():
                                       C.POINTER(MpbStats), C.c_int, C.c_void_p]
     lib.mpb_scene_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int32)] * 5
     lib.mpb_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_float)]
+    lib.mpb_check_motion_batch.argtypes = [C.c_void_p, C.POINTER(MpbSpaceDesc), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                           C.POINTER(MpbStats), C.c_int, C.c_void_p]
+    lib.mpb_rrtconnect_batch.argtypes = [C.c_void_p, C.POINTER(MpbSpaceDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                         C.c_int64, C.POINTER(MpbRrtParams), C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.POINTER(MpbRrtStats)]
     _lib = lib
     return lib
 
@@ -136,6 +181,43 @@ class DeviceScene:
         out = np.zeros((q.shape[0], self.n_links, 7), dtype=np.float32)
         _check(load().mpb_fk_batch(self._h, _ptr(q), q.shape[0], _ptr(out), MPB_HOST, None))
         return out
+
+    def check_motion(self, space: Space, a, b, stats=False):
+        """Batched DiscreteMotionValidator::checkMotion: a, b [E, D] -> valid bool[E]."""
+        a = np.ascontiguousarray(np.asarray(a, dtype=np.float32))
+        b = np.ascontiguousarray(np.asarray(b, dtype=np.float32))
+        if a.ndim != 2 or a.shape != b.shape or a.shape[1] != self.state_dim:
+            raise RuntimeError(f"State dimension is not correct: expected two [E,{self.state_dim}] arrays")
+        E = a.shape[0]
+        vb = np.zeros((E + 31) // 32, dtype=np.uint32)
+        st = MpbStats()
+        _check(load().mpb_check_motion_batch(self._h, C.byref(space.struct), _ptr(a), _ptr(b), E, _ptr(vb), C.byref(st), MPB_HOST, None))
+        valid = np.unpackbits(vb.view(np.uint8), bitorder="little")[:E].astype(bool)
+        return (valid, st.as_dict()) if stats else valid
+
+    def rrtconnect(self, space: Space, starts, goals, n_goals=None, range_=0.1, max_rounds=4096, time_limit=0.0,
+                   tree_capacity=2048, max_path=1024, seed=0, check_every=16):
+        """Lock-step RRTConnect for Q queries.  starts [Q, D]; goals [Q, G, D] (or [Q, D]); n_goals [Q].
+        -> (status int32[Q], list of float64 paths ([n_i, D], empty if unsolved), stats dict)"""
+        starts = np.ascontiguousarray(np.asarray(starts, dtype=np.float32))
+        goals = np.asarray(goals, dtype=np.float32)
+        if goals.ndim == 2:
+            goals = goals[:, None, :]
+        goals = np.ascontiguousarray(goals)
+        Q, D = starts.shape
+        if D != self.state_dim or goals.shape[0] != Q or goals.shape[2] != D:
+            raise RuntimeError("Length of start state and goal state should be equal")
+        G = goals.shape[1]
+        ng = np.ascontiguousarray(np.full(Q, G, np.int32) if n_goals is None else np.asarray(n_goals, dtype=np.int32))
+        prm = MpbRrtParams(float(range_), int(max_rounds), float(time_limit), int(tree_capacity), int(max_path), int(seed), int(check_every))
+        status = np.zeros(Q, dtype=np.int32)
+        plen = np.zeros(Q, dtype=np.int32)
+        paths = np.zeros((Q, max_path, D), dtype=np.float32)
+        st = MpbRrtStats()
+        _check(load().mpb_rrtconnect_batch(self._h, C.byref(space.struct), _ptr(starts), _ptr(goals), _ptr(ng), G, Q, C.byref(prm),
+                                           _ptr(status), _ptr(plen), _ptr(paths), C.byref(st)))
+        out = [paths[i, : plen[i]].astype(np.float64) for i in range(Q)]
+        return status, out, st.as_dict()
 
     def fk_raw(self, q_ptr, n, poses_ptr, space=MPB_HOST, stream=None):
         _check(load().mpb_fk_batch(self._h, _ptr(q_ptr), int(n), _ptr(poses_ptr), space, _ptr(stream)))

@@ -120,3 +120,51 @@ def object_distance(desc, a, Ta, b, Tb):
     ta, tb = _T12(Ta), _T12(Tb)
     return float(lib().orc_object_distance(C.byref(desc.as_struct()), C.c_int(a), C.c_void_p(ta.ctypes.data), C.c_int(b),
                                            C.c_void_p(tb.ctypes.data)))
+
+
+def _space_args(lo, hi, so2, resolution=0.01):
+    lo = np.ascontiguousarray(np.asarray(lo, dtype=np.float64))
+    hi = np.ascontiguousarray(np.asarray(hi, dtype=np.float64))
+    so2 = np.ascontiguousarray(np.zeros(lo.shape[0], np.uint8) if so2 is None else np.asarray(so2, dtype=np.uint8))
+    seg = np.ascontiguousarray(resolution * np.where(so2 != 0, np.pi, hi - lo))
+    return lo, hi, seg, so2
+
+
+def check_motion_batch(desc, lo, hi, a, b, so2=None, threads=8):
+    """DiscreteMotionValidator::checkMotion per edge -> (valid bool[E], states checked)."""
+    lo, hi, seg, so2 = _space_args(lo, hi, so2)
+    a, b = _states(desc, a), _states(desc, b)
+    E = a.shape[0]
+    valid = np.zeros(E, dtype=np.uint8)
+    ns = C.c_int64(0)
+    rc = lib().orc_check_motion_batch(C.byref(desc.as_struct()), C.c_int(desc.state_dim), C.c_void_p(seg.ctypes.data),
+                                      C.c_void_p(so2.ctypes.data), C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_int64(E),
+                                      C.c_void_p(valid.ctypes.data), C.byref(ns), C.c_int(int(threads)))
+    assert rc == 0
+    return valid.astype(bool), ns.value
+
+
+def rrtconnect_batch(desc, lo, hi, starts, goals, n_goals=None, so2=None, range_=0.1, max_grow_calls=1 << 20, time_limit=1.0, seed=0,
+                     max_path=4096, threads=1):
+    """CPU RRTConnect restatement for Q queries (one per thread at a time).
+    -> (status int32[Q], list of paths, grow calls, state checks)"""
+    lo, hi, seg, so2 = _space_args(lo, hi, so2)
+    starts = _states(desc, starts)
+    goals = np.asarray(goals, dtype=np.float64)
+    if goals.ndim == 2:
+        goals = goals[:, None, :]
+    goals = np.ascontiguousarray(goals)
+    Q, D = starts.shape
+    G = goals.shape[1]
+    ng = np.ascontiguousarray(np.full(Q, G, np.int32) if n_goals is None else np.asarray(n_goals, dtype=np.int32))
+    status = np.zeros(Q, dtype=np.int32)
+    plen = np.zeros(Q, dtype=np.int32)
+    paths = np.zeros((Q, max_path, D), dtype=np.float64)
+    gc, sc = C.c_int64(0), C.c_int64(0)
+    lib().orc_rrtconnect_batch(C.byref(desc.as_struct()), C.c_int(D), C.c_void_p(lo.ctypes.data), C.c_void_p(hi.ctypes.data),
+                               C.c_void_p(seg.ctypes.data), C.c_void_p(so2.ctypes.data), C.c_void_p(starts.ctypes.data),
+                               C.c_void_p(goals.ctypes.data), C.c_void_p(ng.ctypes.data), C.c_int(G), C.c_int64(Q), C.c_double(range_),
+                               C.c_int64(int(max_grow_calls)), C.c_double(time_limit), C.c_uint64(int(seed)), C.c_void_p(status.ctypes.data),
+                               C.c_void_p(plen.ctypes.data), C.c_void_p(paths.ctypes.data), C.c_int(max_path), C.byref(gc), C.byref(sc),
+                               C.c_int(int(threads)))
+    return status, [paths[i, : plen[i]].copy() for i in range(Q)], gc.value, sc.value

@@ -68,7 +68,7 @@ def box_surface_points(rng, n, size, center):
     return pts + np.asarray(center)[None, :]
 
 
-def add_c3_primitives(world, n_each=32, seed=3):
+def add_c3_primitives(world, n_each=32, seed=3, keep=None):
     """n_each spheres, boxes, capsules, cylinders in the half-shell 0.3<=|p|<=1, z>=0."""
     from mplib_b200.pymp import fcl
 
@@ -84,7 +84,9 @@ def add_c3_primitives(world, n_each=32, seed=3):
                 g = fcl.Capsule(rng.uniform(0.02, 0.05), rng.uniform(0.05, 0.30))
             else:
                 g = fcl.Cylinder(rng.uniform(0.02, 0.05), rng.uniform(0.05, 0.30))
-            world.add_normal_object(f"{kind}_{k}", fcl.CollisionObject(g, _shell_point(rng), _rand_rot(rng)))
+            pos, rot = _shell_point(rng), _rand_rot(rng)
+            if keep is None or keep(kind, k, pos):
+                world.add_normal_object(f"{kind}_{k}", fcl.CollisionObject(g, pos, rot))
             k += 1
 
 
@@ -136,6 +138,41 @@ def c3(batch=0, **kw):
                    "l2_policy": "rotating pool of input batches > 126 MB"},
         "flop_model": _flop_model(desc),
     }
+
+
+def c4_world(cloud_points=50000):
+    """SURVEY 8(d) C4 scene: the C3 scene restricted to its first 16 boxes + the table cloud (grasped box kept)."""
+    w = make_panda_world(convex=True)
+    # SURVEY's half-shell (0.3 <= |p| <= 1) reaches the robot's own base column: a box there intersects link1/link2 in
+    # every configuration and no collision-free start/goal exists.  Planning scenes therefore skip boxes whose centre
+    # lies within 0.30 m of the base axis segment x = y = 0, 0 <= z <= 0.65, and take the first 16 that remain.
+    taken = []
+
+    def keep(kind, k, pos):
+        if kind != "box" or len(taken) >= 16:
+            return False
+        d = np.linalg.norm(pos - np.array([0.0, 0.0, np.clip(pos[2], 0.0, 0.65)]))
+        if d < 0.30:
+            return False
+        taken.append(k)
+        return True
+
+    add_c3_primitives(w, 32, keep=keep)
+    attach_c3_box(w)
+    if cloud_points:
+        rng = np.random.Generator(np.random.PCG64(4))
+        w.add_point_cloud("cloud", box_surface_points(rng, cloud_points, (0.8, 0.8, 0.05), (0.56, 0, -0.025)), 0.01)
+    return w
+
+
+def free_states(world, n, seed, checker):
+    """Rejection-sample n collision-free states; ``checker(states) -> colliding bool[n]``."""
+    out, k = [], 0
+    while sum(len(x) for x in out) < n:
+        q = random_q(4 * n, seed + 7919 * k)
+        out.append(q[~checker(q)])
+        k += 1
+    return np.concatenate(out)[:n]
 
 
 def get(name, batch=0):
