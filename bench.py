@@ -30,7 +30,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"])
     ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()

@@ -76,9 +76,13 @@ def test_ragged_and_empty(panda_world):
 
 
 def _env_parity(world, n, seed, max_mismatch):
+    _env_parity_q(world, random_q(n, seed), max_mismatch)
+
+
+def _env_parity_q(world, q, max_mismatch):
     from oracle import oracle as O
 
-    q = random_q(n, seed)
+    n = q.shape[0]
     c = world._sync()
     desc = c["dev"].desc
     v, ph, st = c["dev"].collide(q, want_pairs=True, stats=True)
@@ -124,3 +128,24 @@ def test_env_full_c3():
     from tests.workloads import c3_world
 
     _env_parity(c3_world(), 1500, 24, 30)
+
+
+def test_two_panda_c5():
+    """configs[4]: two planned articulations, name-ordered 14-dof state, cross-robot pairs with ACM entries."""
+    from oracle import oracle as O
+    from tests.workloads import c5
+
+    wl = c5(4096)
+    w, q = wl["world"], wl["make_q"](0, 4096)
+    _env_parity_q(w, q, 30)
+    # FK of both robots (26 link frames) against the oracle
+    dev = w._sync()["dev"]
+    got = dev.fk(q[:512])
+    ref = O.fk_batch(dev.desc, q[:512].astype(np.float64))
+    assert np.abs(got[..., :3] - ref[..., :3]).max() < 1e-5
+    # an ACM edit re-uses the compiled scene with a new pair list
+    n0 = dev.n_pairs
+    w.get_allowed_collision_matrix().set_entry("a_panda_hand", "b_panda_hand", True)
+    dev2 = w._sync()["dev"]
+    assert dev2 is dev and dev2.n_pairs == n0 - 1
+    _env_parity_q(w, q[:1024], 30)

@@ -175,5 +175,80 @@ def free_states(world, n, seed, checker):
     return np.concatenate(out)[:n]
 
 
+def prefixed_panda_files(prefix, xyz, yaw):
+    """URDF/SRDF of a Panda whose link and joint names carry ``prefix`` and whose base sits at ``xyz`` with ``yaw``:
+    the reference has no base-pose API and the ACM is keyed by link name only, so the two robots of
+    configs[4] are separate URDFs with an extra fixed root joint.  Files are generated next to panda.urdf so that the
+    relative mesh paths keep resolving."""
+    import os
+    import re
+
+    from tests.common import SRDF, URDF
+
+    d = os.path.dirname(URDF)
+    urdf_out = os.path.join(d, f"_gen_{prefix}panda.urdf")
+    srdf_out = os.path.join(d, f"_gen_{prefix}panda.srdf")
+    u = open(URDF).read()
+    u = re.sub(r'(<(?:link|joint)\s+name=")', r"\g<1>" + prefix, u)
+    u = re.sub(r'(<(?:parent|child)\s+link=")', r"\g<1>" + prefix, u)
+    u = re.sub(r'(<mimic\s+joint=")', r"\g<1>" + prefix, u)
+    root = (f'  <link name="{prefix}base"/>\n  <joint name="{prefix}base_joint" type="fixed">\n'
+            f'    <origin rpy="0 0 {yaw!r}" xyz="{xyz[0]!r} {xyz[1]!r} {xyz[2]!r}"/>\n'
+            f'    <parent link="{prefix}base"/>\n    <child link="{prefix}panda_link0"/>\n  </joint>\n')
+    u = u.replace("</robot>", root + "</robot>")
+    sr = open(SRDF).read()
+    sr = re.sub(r'((?:link1|link2|link|parent_link|child_link|joint)\s*=\s*")', r"\g<1>" + prefix, sr)
+    for path, txt in ((urdf_out, u), (srdf_out, sr)):
+        if not os.path.exists(path) or open(path).read() != txt:
+            with open(path, "w") as f:
+                f.write(txt)
+    return urdf_out, srdf_out
+
+
+def c5_world():
+    """configs[4]: two Pandas (a_ at y=-0.35 yaw 0, b_ at y=+0.35 yaw pi), both planned, cross-robot ACM entries."""
+    from mplib_b200.pymp import ArticulatedModel, PlanningWorld
+    from tests.common import PANDA_JOINTS, PANDA_LINKS
+
+    arts = []
+    for prefix, xyz, yaw in (("a_", (0.0, -0.35, 0.0), 0.0), ("b_", (0.0, 0.35, 0.0), float(np.pi))):
+        urdf, srdf = prefixed_panda_files(prefix, xyz, yaw)
+        art = ArticulatedModel(urdf, srdf, (0, 0, -9.81), [prefix + j for j in PANDA_JOINTS], [prefix + l for l in PANDA_LINKS],
+                               verbose=False, convex=True)
+        art.set_move_group(prefix + "panda_hand")
+        arts.append(art)
+    w = PlanningWorld(arts, ["robot_a", "robot_b"])
+    acm = w.get_allowed_collision_matrix()
+    acm.set_entry("a_panda_link0", "b_panda_link0", True)
+    rng = np.random.Generator(np.random.PCG64(7))
+    coll = [l for l in PANDA_LINKS if l != "panda_link8"]
+    done = {("panda_link0", "panda_link0")}
+    while len(done) < 9:  # 8 further random cross entries
+        x, y = coll[rng.integers(len(coll))], coll[rng.integers(len(coll))]
+        if (x, y) in done:
+            continue
+        done.add((x, y))
+        acm.set_entry("a_" + x, "b_" + y, True)
+    return w
+
+
+def c5(batch=0):
+    """configs[4]: Two-Panda PlanningWorld with cross-robot ACM, 14-dof states."""
+    n = batch or (1 << 22)
+    w = c5_world()
+    desc = compile_desc(w)
+    lo, hi = np.concatenate([PANDA_LO, PANDA_LO]), np.concatenate([PANDA_HI, PANDA_HI])
+    return {
+        "world": w, "desc": desc, "batch": n,
+        "make_q": lambda k, m: random_q(m, 6 + 7919 * k, lo, hi).astype(np.float32),
+        "config": {"workload": "configs[4]: two Pandas (bases at y=-0.35/+0.35, yaw 0/pi), 2x19 self + 11x11 cross pairs minus 9 "
+                               f"cross-robot ACM entries, {n} random 14-dof configurations per GPU per step (seed 6)",
+                   "states_per_gpu": n, "state_dim": desc.state_dim, "pairs": desc.n_pairs,
+                   "outputs": "verdict bit + pair mask per configuration",
+                   "l2_policy": "rotating pool of input batches > 126 MB"},
+        "flop_model": _flop_model(desc),
+    }
+
+
 def get(name, batch=0):
-    return {"c2": c2, "c3": c3}[name](batch)
+    return {"c2": c2, "c3": c3, "c5": c5}[name](batch)
