@@ -3,7 +3,7 @@ NVCC ?= nvcc
 NVCCFLAGS = -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC,-Wall -shared
 LIB = mplib_b200/libmpb.so
 SRC = mplib_b200/csrc/mpb.cu
-HDR = mplib_b200/csrc/mpb_device.cuh mplib_b200/csrc/mpb_kernels.cuh include/mpb.h
+HDR = $(wildcard mplib_b200/csrc/*.cuh) include/mpb.h
 
 all: $(LIB) oracle
 

@@ -154,6 +154,15 @@ int mpb_fk_batch(mpb_scene *scene, const float *q, int64_t n, float *poses, int 
 int mpb_collide_batch(mpb_scene *scene, const float *q, int64_t n, uint32_t *verdict_bits,
                       uint32_t *pair_bits, mpb_stats *stats, int space, void *stream);
 
+/* Batched ValidityCheckerTpl::clearance = setQposAll + distanceFull (src/ompl_planner.h:69-72,
+ * src/planning_world.cpp:492-720) with the default DistanceRequest (python/pybind_fcl.hpp:311-315):
+ *   min_dist [n] float32   minimum over the ACM-admitted pairs of ::fcl::distance: the separation distance, or -1 when
+ *                          some admitted pair touches / intersects; FLT_MAX when no pair is admitted
+ *   argmin   [n] int32     nullable; index of the pair attaining it (first such pair in list order), -1 if none
+ * Pairs involving a mesh or an octree return MPB_ERR_UNSUPPORTED in this build. */
+int mpb_distance_batch(mpb_scene *scene, const float *q, int64_t n, float *min_dist, int32_t *argmin, mpb_stats *stats,
+                       int space, void *stream);
+
 /*
  * Planning state space as OMPLPlannerTpl::build_state_space builds it (src/ompl_planner.cpp:245-296): one 1-D
  * RealVector subspace per bounded joint, one SO(2) subspace per continuous joint, all with weight 1, so the

@@ -49,13 +49,13 @@ class Space:
 
 MPB_HOST, MPB_DEVICE = 0, 1
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmpb.so")
+LIB_PATH = os.environ.get("MPB_LIB_PATH") or os.path.join(_HERE, "libmpb.so")  # override: debugging builds only
 
 # every symbol include/mpb.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "mpb_last_error", "mpb_device_count", "mpb_scene_create", "mpb_scene_destroy", "mpb_scene_set_q_base",
     "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
-    "mpb_check_motion_batch", "mpb_rrtconnect_batch",
+    "mpb_check_motion_batch", "mpb_rrtconnect_batch", "mpb_distance_batch",
 ]
 
 _lib = None
@@ -87,6 +87,8 @@ def load():
                                       C.POINTER(MpbStats), C.c_int, C.c_void_p]
     lib.mpb_scene_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int32)] * 5
     lib.mpb_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_float)]
+    lib.mpb_distance_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(MpbStats), C.c_int,
+                                       C.c_void_p]
     lib.mpb_check_motion_batch.argtypes = [C.c_void_p, C.POINTER(MpbSpaceDesc), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                            C.POINTER(MpbStats), C.c_int, C.c_void_p]
     lib.mpb_rrtconnect_batch.argtypes = [C.c_void_p, C.POINTER(MpbSpaceDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
@@ -181,6 +183,21 @@ class DeviceScene:
         out = np.zeros((q.shape[0], self.n_links, 7), dtype=np.float32)
         _check(load().mpb_fk_batch(self._h, _ptr(q), q.shape[0], _ptr(out), MPB_HOST, None))
         return out
+
+    def distance(self, q, stats=False):
+        """q [n, D] -> (min_distance float64[n] (-1 where an admitted pair collides, float64 max if no pair),
+        argmin pair int32[n])"""
+        q = np.ascontiguousarray(np.asarray(q, dtype=np.float32))
+        if q.ndim != 2 or q.shape[1] != self.state_dim:
+            raise RuntimeError(f"State dimension is not correct: expected [n,{self.state_dim}], got {q.shape}")
+        n = q.shape[0]
+        md = np.zeros(n, dtype=np.float32)
+        am = np.zeros(n, dtype=np.int32)
+        st = MpbStats()
+        _check(load().mpb_distance_batch(self._h, _ptr(q), n, _ptr(md), _ptr(am), C.byref(st), MPB_HOST, None))
+        out = md.astype(np.float64)
+        out[am < 0] = np.finfo(np.float64).max  # WorldDistanceResult::min_distance starts at max (src/planning_world.h:30-41)
+        return (out, am, st.as_dict()) if stats else (out, am)
 
     def check_motion(self, space: Space, a, b, stats=False):
         """Batched DiscreteMotionValidator::checkMotion: a, b [E, D] -> valid bool[E]."""

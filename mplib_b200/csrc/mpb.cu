@@ -639,8 +639,9 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   s->cull_block = 64;
   s->cull_smem = ((size_t)n_jslots * 12 + (size_t)ndyn * 3) * s->cull_block * sizeof(float) + (size_t)s->cull_block * 32 * sizeof(unsigned short) + 16;
   if (s->cull_smem > 227 * 1024) { mpb_scene_destroy(s); return fail(MPB_ERR_CAPACITY, "too many moving joints / objects for the shared-memory pose table"); }
-  CU(cudaFuncSetAttribute(fk_cull_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->cull_blocks_per_sm, fk_cull_kernel<64>, s->cull_block, s->cull_smem));
+  CU(cudaFuncSetAttribute(fk_cull_kernel<64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
+  CU(cudaFuncSetAttribute(fk_cull_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->cull_blocks_per_sm, fk_cull_kernel<64, 0>, s->cull_block, s->cull_smem));
   s->cull_blocks_per_sm = std::max(s->cull_blocks_per_sm, 1);
   *out = s;
   return MPB_OK;
@@ -783,7 +784,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)std::min<long long>((mm + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
-      fk_cull_kernel<64><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq + off * D, mm, off, s->wq);
+      fk_cull_kernel<64, 0><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq + off * D, mm, off, s->wq);
       *launches += 1;
     }
   }
@@ -1258,6 +1259,119 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
       stats->n_solved += status[q] == MPB_RRT_SOLVED;
     }
     cudaEventElapsedTime(&stats->gpu_ms, e0, e1);
+    stats->host_ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+  }
+  return MPB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ distance
+#include "mpb_distance.cuh"
+
+extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float *min_dist, int32_t *argmin, mpb_stats *stats,
+                                  int space, void *stream) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!min_dist || (!q && s->img.state_dim > 0)))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (space != MPB_HOST && space != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
+  if (stats) memset(stats, 0, sizeof(*stats));
+  if (n == 0) return MPB_OK;
+  if (s->img.expand_bin >= 0) return fail(MPB_ERR_UNSUPPORTED, "distance to mesh / octree objects is not supported by this build yet");
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  const auto t_begin = std::chrono::steady_clock::now();
+  const int D = s->img.state_dim;
+  const bool host = space == MPB_HOST;
+  static bool attr_set = false;
+  const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
+  if (!attr_set && s->smem_verts) {
+    CU(cudaFuncSetAttribute(distance_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vsm, 16)));
+    attr_set = true;
+  }
+  if (s->smem_verts) CU(cudaFuncSetAttribute(distance_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vsm, 16)));
+  int per_sm = 0;
+  if (s->smem_verts) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, distance_kernel<true>, 256, vsm));
+  else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, distance_kernel<false>, 256, 0));
+  const int dblocks = s->num_sms * std::max(per_sm, 1);
+  DevBufs bufs;
+  long long chunk = std::min<long long>(kMaxChunk, (n + 31) / 32 * 32);
+  // candidates can be a large fraction of n * n_pairs: start from a pass size the queue certainly holds
+  while (chunk > 4096 && (size_t)chunk * std::max(s->img.n_pairs, 1) > kMaxItems / 2) chunk = (chunk / 2 + 31) / 32 * 32;
+  float *dq_buf = nullptr, *dmin = nullptr;
+  int *darg = nullptr;
+  unsigned long long *dbest = nullptr;
+  CU(bufs.alloc(&dbest, (size_t)chunk));
+  if (host) {
+    CU(bufs.alloc(&dq_buf, (size_t)chunk * std::max(D, 1)));
+    CU(bufs.alloc(&dmin, (size_t)chunk));
+    CU(bufs.alloc(&darg, (size_t)chunk));
+  }
+  long long launches = 0;
+  unsigned long long counters_total[4] = {0, 0, 0, 0};
+  float ms_cull = 0.f, ms_narrow = 0.f;
+  for (long long off = 0; off < n;) {
+    const long long m = std::min(chunk, n - off);
+    int rc = prepare_work(s, chunk);
+    if (rc != MPB_OK) return rc;
+    const int nb = std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
+    const float *dq = q + off * D;
+    if (host) {
+      if (D > 0) CU(cudaMemcpyAsync(dq_buf, q + off * D, (size_t)m * D * sizeof(float), cudaMemcpyHostToDevice, st));
+      dq = dq_buf;
+    }
+    float *omin = host ? dmin : min_dist + off;
+    int *oarg = host ? darg : (argmin ? argmin + off : nullptr);
+    CU(cudaMemsetAsync(dbest, 0xff, (size_t)m * sizeof(unsigned long long), st));
+    CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
+    CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
+    CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
+    cudaEvent_t e0 = get_event(s, 0), e1 = get_event(s, 1), e2 = get_event(s, 2);
+    CU(cudaEventRecord(e0, st));
+    if (s->img.n_pairs > 0) {
+      const int cblocks = (int)std::min<long long>((m + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
+      fk_cull_kernel<64, 1><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, 0, s->wq);
+      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, (unsigned)dblocks * 8u);
+      scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
+      CU(cudaEventRecord(e1, st));
+      if (s->smem_verts) distance_kernel<true><<<dblocks, 256, vsm, st>>>(s->img, s->wq, dbest, s->img.n_bins);
+      else distance_kernel<false><<<dblocks, 256, 0, st>>>(s->img, s->wq, dbest, s->img.n_bins);
+      launches += 4;
+    } else CU(cudaEventRecord(e1, st));
+    distance_unpack_kernel<<<(int)((m + 255) / 256), 256, 0, st>>>(dbest, m, omin, oarg);
+    launches += 1;
+    CU(cudaEventRecord(e2, st));
+    CU(cudaGetLastError());
+    unsigned totals[8] = {0};
+    unsigned long long counters[4] = {0, 0, 0, 0};
+    CU(cudaMemcpyAsync(totals, s->wq.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(counters, s->wq.counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (totals[2]) {  // candidate queue overflow: redo this pass with a smaller chunk (exact redo)
+      if (chunk <= 32) return fail(MPB_ERR_CAPACITY, "work queue overflow persists at the minimum chunk size");
+      chunk = std::max<long long>(32, (chunk / 4 + 31) / 32 * 32);
+      continue;
+    }
+    if (host) {
+      CU(cudaMemcpyAsync(min_dist + off, dmin, (size_t)m * sizeof(float), cudaMemcpyDeviceToHost, st));
+      if (argmin) CU(cudaMemcpyAsync(argmin + off, darg, (size_t)m * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+    }
+    float a = 0.f, b = 0.f;
+    cudaEventElapsedTime(&a, e0, e1);
+    cudaEventElapsedTime(&b, e1, e2);
+    ms_cull += a;
+    ms_narrow += b;
+    for (int k = 0; k < 4; k++) counters_total[k] += counters[k];
+    off += m;
+  }
+  if (stats) {
+    stats->n_states = n;
+    stats->pairs_admitted = n * (long long)s->img.n_pairs;
+    stats->pairs_after_cull = (long long)counters_total[0];
+    stats->narrow_iterations = (long long)counters_total[1];
+    stats->narrow_capped = (long long)counters_total[2];
+    stats->kernel_launches = launches;
+    stats->gpu_ms_cull = ms_cull;
+    stats->gpu_ms_narrow = ms_narrow;
+    stats->gpu_ms = ms_cull + ms_narrow;
     stats->host_ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
   }
   return MPB_OK;

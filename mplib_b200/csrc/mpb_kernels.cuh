@@ -198,7 +198,10 @@ __device__ __forceinline__ Xf smem_joint(const float *sJ, int js, int t) {
 //   2. per 32 admitted pairs: bounding-sphere test, thread per configuration -> survivors pushed to a block queue
 //   3. dense: thread per queued (configuration, pair): 15-axis OBB SAT with the owner's joint transforms read
 //      from sJ; what is left is ballot-compacted into the global staging queue (one atomic per warp chunk)
-template <int BLOCK>
+//   MODE 0 (collide): as above.  MODE 1 (distance): a pair is a candidate for the minimum iff its bounding-sphere
+//   lower bound |c| - R does not exceed the smallest upper bound |c| + R over all admitted pairs of the
+//   configuration; candidates skip the SAT (overlap is not the question) and go to the GJK distance kernel.
+template <int BLOCK, int MODE>
 __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, long long cfg_base, WorkQ wq) {
   extern __shared__ __align__(16) float smem_f[];
   float *sJ = smem_f;
@@ -240,6 +243,21 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
         }
       }
     }
+    float ub_min = FLT_MAX;
+    if (MODE == 1 && valid) {
+      for (int p = 0; p < img.n_pairs; p++) {
+        const DevPair pr = img.pairs[p];
+        const int da = ((pr.bin_dyn >> 16) & 0xff) - 1, db = ((pr.bin_dyn >> 24) & 0xff) - 1;
+        float ax, ay, az, bx, by, bz;
+        if (da >= 0) { ax = SMC(da, 0, tid); ay = SMC(da, 1, tid); az = SMC(da, 2, tid); }
+        else { const float *c = img.objs[pr.a].bcw; ax = c[0]; ay = c[1]; az = c[2]; }
+        if (db >= 0) { bx = SMC(db, 0, tid); by = SMC(db, 1, tid); bz = SMC(db, 2, tid); }
+        else { const float *c = img.objs[pr.b].bcw; bx = c[0]; by = c[1]; bz = c[2]; }
+        const float dx = ax - bx, dy = ay - by, dz = az - bz;
+        ub_min = fminf(ub_min, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + pr.rr);
+      }
+      ub_min *= 1.000001f;
+    }
     for (int base = 0; base < img.n_pairs; base += 32) {
       __syncthreads();  // FK tables complete (first round); previous dense phase done with sQ
       // ---- 2. bounding spheres
@@ -255,7 +273,8 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
           if (db >= 0) { bx = SMC(db, 0, tid); by = SMC(db, 1, tid); bz = SMC(db, 2, tid); }
           else { const float *c = img.objs[pr.b].bcw; bx = c[0]; by = c[1]; bz = c[2]; }
           const float dx = ax - bx, dy = ay - by, dz = az - bz;
-          if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= pr.rr * pr.rr) mask |= 1u << k;
+          const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+          if (MODE == 0 ? (d2c <= pr.rr * pr.rr) : (sqrtf(d2c) - pr.rr <= ub_min)) mask |= 1u << k;
         }
       }
       {  // push (thread, pair-in-tile) survivors: warp prefix sum + one shared atomic per warp
@@ -297,6 +316,8 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
           const Xf Wa = A.jslot >= 0 ? xf_mul(smem_joint<BLOCK>(sJ, A.jslot, owner), load_xf12(A.L)) : load_xf12(A.L);
           const Xf Wb = B.jslot >= 0 ? xf_mul(smem_joint<BLOCK>(sJ, B.jslot, owner), load_xf12(B.L)) : load_xf12(B.L);
           rel = xf_inv_mul(Wa, Wb);
+          keep = true;
+          if (MODE == 0) {
           // box B in box A's frame:  Ra^T (rel.R Rb),  Ra^T (rel*ocB - ocA)
           float M[9], R[9], cbA[3], t[3];
 #pragma unroll
@@ -314,6 +335,7 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
 #pragma unroll
           for (int r = 0; r < 3; r++) t[r] = fmaf(A.oR[r], d0, fmaf(A.oR[3 + r], d1, A.oR[6 + r] * d2));
           keep = !obb_disjoint(R, t, A.oh, B.oh);
+          }
         }
         const unsigned km = __ballot_sync(FULL, keep);
         if (km == 0) continue;

@@ -434,3 +434,45 @@ class PlanningWorld:
 
     def collide(self, request=None):
         return len(self.collide_full(request)) > 0
+
+    # -- distance (src/planning_world.cpp:492-720) ---------------------------------------------------------
+    def distance_batch(self, states, stats=False):
+        """Batched ``ValidityCheckerTpl::clearance``: states [n, D] -> (min_distance float64[n], argmin pair int32[n]);
+        ``get_pair_metadata()[argmin]`` names the pair.  -1 where an admitted pair touches / intersects."""
+        c = self._sync()
+        states = np.asarray(states)
+        if states.ndim != 2 or states.shape[1] != c["dev"].state_dim:
+            raise RuntimeError("State dimension is not correct")
+        return c["dev"].distance(states, stats=stats)
+
+    def _distance_query(self, section):
+        c = self._sync()
+        pairs = c["pairs"]
+        sel = [k for k, p in enumerate(pairs) if section is None or p[2] == section]
+        dev = c["dev"]
+        if len(sel) != len(pairs):  # query a sub-list of the admitted pairs, then restore the full list
+            dev.set_pairs([pairs[k][0] for k in sel], [pairs[k][1] for k in sel], [pairs[k][3] for k in sel])
+        try:
+            md, am = dev.distance(self._current_state()[None, :])
+        finally:
+            if len(sel) != len(pairs):
+                dev.set_pairs([p[0] for p in pairs], [p[1] for p in pairs], [p[3] for p in pairs])
+        r = WorldDistanceResult()
+        if am[0] >= 0:
+            p = pairs[sel[int(am[0])]]
+            r.min_distance = float(md[0])
+            r.res = fcl.DistanceResult(float(md[0]))
+            r.distance_type, r.object_name1, r.object_name2, r.link_name1, r.link_name2 = p[3], p[4], p[5], p[6], p[7]
+        return r
+
+    def self_distance(self, request=None):
+        return self._distance_query("self")
+
+    def distance_with_others(self, request=None):
+        return self._distance_query("others")
+
+    def distance_full(self, request=None):
+        return self._distance_query(None)
+
+    def distance(self, request=None):
+        return self.distance_full(request).min_distance
