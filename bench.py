@@ -30,9 +30,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
     return ap.parse_args()
 
 
@@ -103,10 +104,133 @@ def cpu_leg(desc, q, threads, budget_s, chunk):
     return done / dt, done, dt
 
 
+PLAN_METRIC = "panda_rrtconnect_plans_per_sec"
+PLAN_UNIT = "plans/s"
+
+
+def run_c4_reference(args):
+    """Reference arm of configs[3]: the oracle's RRTConnect restatement (OMPL semantics, one query per host thread,
+    `time` = 1 s per query as Planner.plan passes) on a bounded sample of the same seeded queries."""
+    from oracle import oracle as O
+    from mplib_b200.pymp import OMPLPlanner
+    from tests import workloads as WL
+
+    wl = WL.get("c4", args.batch)
+    desc, w = wl["desc"], wl["world"]
+    threads = os.cpu_count() or 1
+    pl = OMPLPlanner(w)
+    lo, hi = pl.lower_joint_limits, pl.upper_joint_limits
+    n_q = max(threads * 2, 16)
+    checker = lambda q: O.collide_batch(desc, q, threads=threads)[0]
+    per_step, solved_tot = [], 0
+    for s in range(args.warmup + args.steps):
+        starts, goals = WL.c4_queries(n_q, 5 + 104729 * s, checker)
+        t0 = time.perf_counter()
+        st, paths, gc, sc = O.rrtconnect_batch(desc, lo, hi, starts, goals, range_=0.1, time_limit=1.0, seed=s, threads=threads)
+        dt = time.perf_counter() - t0
+        if s >= args.warmup:
+            per_step.append((int((st == 1).sum()), dt, n_q))
+    n_solved = sum(a for a, _, _ in per_step)
+    t_tot = sum(b for _, b, _ in per_step)
+    val = n_solved / t_tot
+    line = {
+        "impl": "reference", "metric": PLAN_METRIC, "value": val, "unit": PLAN_UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / max(len(per_step), 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl["config"],
+        "solve_rate": n_solved / max(sum(c for _, _, c in per_step), 1),
+        "cpu_baseline": {"value": val, "unit": PLAN_UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{n_q} queries/step of the same seeded workload, one query per thread, OpenMP x{threads}, "
+                                   "time limit 1 s per query"},
+        "e2e": {"value": val, "unit": PLAN_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_c4(args):
+    """configs[3]: plans/s of lock-step RRTConnect.  `value` = solved queries / device time of mpb_rrtconnect_batch
+    (CUDA events inside the call); `e2e` = solved / wall time of OMPLPlanner.plan_batch (start/goal validity checks, goal
+    images, H2D of the queries, D2H of status + paths)."""
+    import torch
+    import torch.distributed as dist
+
+    from mplib_b200 import _lib
+    from mplib_b200.pymp import OMPLPlanner
+    from tests import workloads as WL
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if _lib.load().mpb_device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = WL.get("c4", args.batch)
+    w, desc, Q = wl["world"], wl["desc"], wl["batch"]
+    w.device = local  # the world compiles its scene image on this rank's GPU
+    pl = OMPLPlanner(w)
+    n_sets = min(args.warmup + args.steps, 4)
+    sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, w.collide_batch) for k in range(n_sets)]
+    kw = dict(range=0.1, time=60.0, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        pl.plan_batch(*sets[k % n_sets], seed=k, **kw)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    solved = gpu_ms = launches = rounds = states = 0
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        status, paths, st = pl.plan_batch(*sets[(args.warmup + k) % n_sets], seed=args.warmup + k, **kw)
+        solved += st["n_solved"]; gpu_ms += st["gpu_ms"]; launches += st["kernel_launches"]; rounds += st["rounds"]
+        states += st["states_checked"]
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([gpu_ms, wall], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gpu_ms, wall = float(t[0]), float(t[1])
+        c = torch.tensor([solved, launches, states], device="cuda", dtype=torch.float64)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        solved, launches, states = float(c[0]), float(c[1]), float(c[2])
+    if rank == 0:
+        K = args.steps
+        f = wl["flop_model"]
+        peak_probe = _lib.fp32_peak_tflops(local)
+        F_state = f["F_fk"] + 12.0 * desc.n_pairs  # FK + sphere cull per checked state (narrowphase not counted here)
+        achieved = states * F_state / (gpu_ms * 1e-3) / 1e12
+        line = {
+            "metric": PLAN_METRIC, "value": solved / (gpu_ms * 1e-3), "unit": PLAN_UNIT, "n_gpus": world, "steps": K,
+            "warmup": args.warmup, "ms_per_step": gpu_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": wl["config"],
+            "solve_rate": solved / (float(Q) * world * K),
+            "e2e": {"value": solved / wall, "unit": PLAN_UNIT, "h2d_bytes_per_step": int(Q * 2 * desc.state_dim * 4 + Q * 4),
+                    "d2h_bytes_per_step": int(Q * 8 + Q * kw["max_path"] * desc.state_dim * 4)},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "fp32", "scope": "all kernels of the planning rounds; FK + cull flops of the checked states only",
+                         "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
+                         "traffic": None, "states_checked_per_step": states / K / world, "rounds_per_step": rounds / K},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if args.workload == "c4":
+        return run_c4_reference(args)
     wl = workload_config(args)
     desc = wl["desc"]
     threads = os.cpu_count() or 1
@@ -135,6 +259,8 @@ def main():
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "c4":
+        return run_c4(args)
 
     import torch
     import torch.distributed as dist

@@ -250,5 +250,30 @@ def c5(batch=0):
     }
 
 
+def c4(batch=0):
+    """configs[3]: RRTConnect plan_qpos queries in the C4 scene.  ``batch`` = planning queries per GPU per step."""
+    n = batch or 1024
+    w = c4_world()
+    desc = compile_desc(w)
+    return {
+        "world": w, "desc": desc, "batch": n,
+        "config": {"workload": "configs[3]: RRTConnect plan_qpos, C4 scene (Panda + grasped box vs 16 boxes + 50k-point table "
+                               f"octree), {n} independent (start, goal) queries per GPU per step (seed 5), range 0.1, validity "
+                               "resolution 1 %, one goal per query, every state of every edge checked (DiscreteMotionValidator)",
+                   "queries_per_gpu": n, "state_dim": desc.state_dim, "pairs": desc.n_pairs,
+                   "outputs": "status + waypoint matrix per query",
+                   "l2_policy": "each round rewrites the tree/edge/work-queue buffers (> L2 at this batch); queries differ per step"},
+        "flop_model": _flop_model(desc),
+    }
+
+
+def c4_queries(n, seed, checker):
+    """n (start, goal) pairs, both collision-free under ``checker(states) -> colliding bool``."""
+    from tests.common import make_panda_world  # noqa: F401  (documented dependency: Panda limits)
+
+    pts = free_states(None, 2 * n, seed, checker)
+    return pts[:n], pts[n:]
+
+
 def get(name, batch=0):
-    return {"c2": c2, "c3": c3, "c5": c5}[name](batch)
+    return {"c2": c2, "c3": c3, "c4": c4, "c5": c5}[name](batch)
