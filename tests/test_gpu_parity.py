@@ -149,3 +149,47 @@ def test_two_panda_c5():
     dev2 = w._sync()["dev"]
     assert dev2 is dev and dev2.n_pairs == n0 - 1
     _env_parity_q(w, q[:1024], 30)
+
+
+def _golden_parity(world, fixture, max_mismatch):
+    """CUDA path vs the committed oracle vectors of tests/golden/ (no oracle run except the signed distance of a
+    mismatching pair, to prove it lies inside the contact band)."""
+    from oracle import oracle as O
+    from tests.test_golden_cpu import load_golden, pair_names
+
+    q, v, ph, names = load_golden(fixture)
+    c = world._sync()
+    desc = c["dev"].desc
+    assert names == pair_names(desc)
+    gv, gph = c["dev"].collide(q, want_pairs=True)
+    mism = np.argwhere(gph != ph)
+    for i, p in mism:
+        sd = O.pair_signed_distance(desc, q[i].astype(np.float64), int(p))
+        assert abs(sd) < BAND, (fixture, int(i), names[p], sd)
+    print(f"{fixture}: states={q.shape[0]} pairs={len(names)} mismatches={len(mism)} (all inside the 1e-4 m band)")
+    assert len(mism) <= max_mismatch
+    assert np.array_equal(gv, gph.any(axis=1))
+
+
+def test_golden_c1_scene_a():
+    """configs[0], scene A: examples/detect_collision.py floor point cloud (octree at 1e-3), 10k qpos."""
+    from tests.workloads import c1_world
+
+    _golden_parity(c1_world("A"), "c1_sceneA.npz", 20)
+
+
+def test_golden_c1_scene_b():
+    """configs[0], scene B: box + sphere obstacles, 10k qpos."""
+    from tests.workloads import c1_world
+
+    _golden_parity(c1_world("B"), "c1_sceneB.npz", 20)
+
+
+def test_golden_c2_self(panda_world):
+    _golden_parity(panda_world, "c2_self_20k.npz", 20)
+
+
+def test_golden_c5_two_panda():
+    from tests.workloads import c5_world
+
+    _golden_parity(c5_world(), "c5_two_panda_4k.npz", 20)

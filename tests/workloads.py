@@ -250,6 +250,27 @@ def c5(batch=0):
     }
 
 
+def c1_world(scene="B"):
+    """configs[0]: Panda self+env check of 10k random qpos.  Scene "A" is examples/detect_collision.py:36-46 (10 000 points
+    on the surface of a 2 x 2 x 0.1 m box centred (0, 0, -0.1), add_point_cloud at resolution 1e-3; trimesh's sampler is
+    restated as an area-weighted face sampler, seed 100); scene "B" is the "box/sphere" reading: Box(2, 2, 0.1) at
+    (0, 0, -0.1) + Sphere(0.1) at (0.5, 0, 0.3)."""
+    from mplib_b200.pymp import fcl
+
+    w = make_panda_world(convex=True)
+    if scene == "A":
+        rng = np.random.Generator(np.random.PCG64(100))
+        w.add_point_cloud("floor", box_surface_points(rng, 10000, (2.0, 2.0, 0.1), (0.0, 0.0, -0.1)), 1e-3)
+    else:
+        w.add_normal_object("floor_box", fcl.CollisionObject(fcl.Box([2.0, 2.0, 0.1]), [0.0, 0.0, -0.1], [1, 0, 0, 0]))
+        w.add_normal_object("ball", fcl.CollisionObject(fcl.Sphere(0.1), [0.5, 0.0, 0.3], [1, 0, 0, 0]))
+    return w
+
+
+def c1_q(n=10000):
+    return random_q(n, 0)
+
+
 def c4(batch=0):
     """configs[3]: RRTConnect plan_qpos queries in the C4 scene.  ``batch`` = planning queries per GPU per step."""
     n = batch or 1024
