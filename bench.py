@@ -34,6 +34,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
+    ap.add_argument("--plan-time", type=float, default=1.0,
+                    help="c4: OMPL `time` budget in seconds (Planner.plan passes 1.0); the batched call applies it to the whole "
+                         "lock-step batch, the reference to every single query")
     return ap.parse_args()
 
 
@@ -172,7 +175,7 @@ def run_c4(args):
     pl = OMPLPlanner(w)
     n_sets = min(args.warmup + args.steps, 4)
     sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, w.collide_batch) for k in range(n_sets)]
-    kw = dict(range=0.1, time=60.0, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048)
+    kw = dict(range=0.1, time=args.plan_time, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048)
 
     def barrier():
         if world > 1:
@@ -212,7 +215,7 @@ def run_c4(args):
             "metric": PLAN_METRIC, "value": solved / (gpu_ms * 1e-3), "unit": PLAN_UNIT, "n_gpus": world, "steps": K,
             "warmup": args.warmup, "ms_per_step": gpu_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": wl["config"],
-            "solve_rate": solved / (float(Q) * world * K),
+            "solve_rate": solved / (float(Q) * world * K), "plan_time_budget_s": args.plan_time,
             "e2e": {"value": solved / wall, "unit": PLAN_UNIT, "h2d_bytes_per_step": int(Q * 2 * desc.state_dim * 4 + Q * 4),
                     "d2h_bytes_per_step": int(Q * 8 + Q * kw["max_path"] * desc.state_dim * 4)},
             "gpu_launches": int(launches), "clocks": clocks,

@@ -196,12 +196,13 @@ int mpb_check_motion_batch(mpb_scene *scene, const mpb_space_desc *space, const 
 
 typedef struct mpb_rrt_params {
   float range;            /* RRTConnect::setRange; <= 0: OMPL's default 0.2 * maximum extent of the space */
-  int32_t max_rounds;     /* growTree calls per query at most (one per lock-step round)               */
+  int32_t max_rounds;     /* lock-step rounds at most (a round consumes 1 .. connect_steps growTree calls per query) */
   float time_limit_s;     /* wall-clock budget of the call (OMPL's `time`), <= 0: none                */
   int32_t tree_capacity;  /* nodes per tree per query                                                 */
   int32_t max_path;       /* waypoints per returned path at most                                      */
   uint64_t seed;
   int32_t check_every;    /* rounds between host checks of the active-query counter (<= 0: 16)        */
+  int32_t connect_steps;  /* steps of the connect loop validated per round (<= 0: 8, at most 32)      */
 } mpb_rrt_params;
 
 typedef struct mpb_rrt_stats {

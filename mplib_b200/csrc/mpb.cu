@@ -52,6 +52,14 @@ struct mpb_scene {
   int *d_pair_bin2 = nullptr;
   size_t pair_bin2_cap = 0;
   std::vector<int> h_pair_bin2;
+  // cull table (fk_cull_kernel phase 2): pairs re-ordered into runs that share their moving object
+  std::vector<float4> h_cullc;
+  std::vector<int2> h_cullm;
+  std::vector<int4> h_runs;
+  float4 *d_cullc = nullptr;
+  int2 *d_cullm = nullptr;
+  int4 *d_runs = nullptr;
+  size_t cull_cap = 0;
   SceneImg img{};
   int cull_block = 128;
   size_t cull_smem = 0;
@@ -72,6 +80,9 @@ struct mpb_scene {
   bool smem_verts = true;
   int narrow_blocks = 0;
   std::vector<cudaEvent_t> events;
+  // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
+  // buffers cost more than a thousand planning rounds)
+  std::vector<std::pair<void *, size_t>> pool;
 };
 
 extern "C" const char *mpb_last_error(void) { return g_err.c_str(); }
@@ -308,6 +319,45 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
     const int da = s->h_objs[a].dyn + 1, db = s->h_objs[b].dyn + 1;
     s->h_pairs[p] = DevPair{a, b, bin | (da << 16) | (db << 24), s->h_objs[a].br + s->h_objs[b].br + 1e-5f};
   }
+  // cull table: entries sorted by (moving object, partner kind, pair index); see fk_cull_kernel phase 2
+  {
+    struct Ent { int m1, kind, p, m2; float c[3]; float rr2; };
+    std::vector<Ent> ents((size_t)n_pairs);
+    for (int p = 0; p < n_pairs; p++) {
+      const DevPair &pr = s->h_pairs[p];
+      const DevObject &A = s->h_objs[pr.a], &B = s->h_objs[pr.b];
+      Ent e{};
+      e.p = p;
+      e.rr2 = pr.rr * pr.rr;
+      if (A.dyn >= 0 && B.dyn >= 0) { e.m1 = A.dyn; e.m2 = B.dyn; e.kind = 1; }
+      else if (A.dyn >= 0) { e.m1 = A.dyn; e.m2 = -1; e.kind = 0; for (int k = 0; k < 3; k++) e.c[k] = B.bcw[k]; }
+      else if (B.dyn >= 0) { e.m1 = B.dyn; e.m2 = -1; e.kind = 0; for (int k = 0; k < 3; k++) e.c[k] = A.bcw[k]; }
+      else {  // both world-fixed: the sphere verdict is a constant (the moving centre reads as the origin)
+        e.m1 = -1; e.m2 = -1; e.kind = 0;
+        const float dx = A.bcw[0] - B.bcw[0], dy = A.bcw[1] - B.bcw[1], dz = A.bcw[2] - B.bcw[2];
+        e.rr2 = (dx * dx + dy * dy + dz * dz <= pr.rr * pr.rr) ? FLT_MAX : -1.f;
+      }
+      ents[p] = e;
+    }
+    std::stable_sort(ents.begin(), ents.end(), [](const Ent &x, const Ent &y) {
+      if (x.m1 != y.m1) return x.m1 < y.m1;
+      if (x.kind != y.kind) return x.kind < y.kind;
+      return x.p < y.p;
+    });
+    s->h_cullc.resize(n_pairs);
+    s->h_cullm.resize(n_pairs);
+    s->h_runs.clear();
+    for (int k = 0; k < n_pairs; k++) {
+      const Ent &e = ents[k];
+      s->h_cullc[k] = make_float4(e.c[0], e.c[1], e.c[2], e.rr2);
+      s->h_cullm[k] = make_int2(e.p, (e.m1 + 1) | ((e.m2 + 1) << 16));
+      if (s->h_runs.empty() || s->h_runs.back().x != e.m1 || s->h_runs.back().w != e.kind)
+        s->h_runs.push_back(make_int4(e.m1, k, 1, e.kind));
+      else
+        s->h_runs.back().z++;
+    }
+    s->h_runs.push_back(make_int4(-1, n_pairs, 0, 0));  // sentinel: the run cursor may step one past the last run
+  }
   s->img.n_pairs = n_pairs;
   s->img.n_bins = (int)bins.size();
   s->img.n_bins2 = (int)bins2.size();
@@ -332,6 +382,21 @@ static int upload_pairs(mpb_scene *s) {
   }
   if (n) CU(cudaMemcpy(s->d_pair_bin2, s->h_pair_bin2.data(), n * sizeof(int), cudaMemcpyHostToDevice));
   s->img.pair_bin2 = s->d_pair_bin2;
+  if (n + 1 > s->cull_cap) {
+    if (s->d_cullc) cudaFree(s->d_cullc);
+    if (s->d_cullm) cudaFree(s->d_cullm);
+    if (s->d_runs) cudaFree(s->d_runs);
+    s->cull_cap = std::max<size_t>(n + 1, 64);
+    CU(cudaMalloc(&s->d_cullc, s->cull_cap * sizeof(float4)));
+    CU(cudaMalloc(&s->d_cullm, s->cull_cap * sizeof(int2)));
+    CU(cudaMalloc(&s->d_runs, s->cull_cap * sizeof(int4)));
+  }
+  if (n) CU(cudaMemcpy(s->d_cullc, s->h_cullc.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+  if (n) CU(cudaMemcpy(s->d_cullm, s->h_cullm.data(), n * sizeof(int2), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(s->d_runs, s->h_runs.data(), s->h_runs.size() * sizeof(int4), cudaMemcpyHostToDevice));
+  s->img.cullc = s->d_cullc;
+  s->img.cullm = s->d_cullm;
+  s->img.runs = s->d_runs;
   s->chunk = 0;  // queue sizing depends on the pair count
   return MPB_OK;
 }
@@ -637,7 +702,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
   // FK + cull launch shape: moving-object poses in shared memory, [object][15 words][thread]
   s->cull_block = 64;
-  s->cull_smem = ((size_t)n_jslots * 12 + (size_t)ndyn * 3) * s->cull_block * sizeof(float) + (size_t)s->cull_block * 32 * sizeof(unsigned short) + 16;
+  s->cull_smem = (((size_t)n_jslots * 12 + (size_t)ndyn * 3) * 32 + MPB_CULL_QCAP) * sizeof(float) * (s->cull_block / 32);
   if (s->cull_smem > 227 * 1024) { mpb_scene_destroy(s); return fail(MPB_ERR_CAPACITY, "too many moving joints / objects for the shared-memory pose table"); }
   CU(cudaFuncSetAttribute(fk_cull_kernel<64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
   CU(cudaFuncSetAttribute(fk_cull_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
@@ -652,9 +717,10 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
+  for (auto &b : s->pool) cudaFree(b.first);
   for (auto e : s->events) cudaEventDestroy(e);
   for (auto e : s->sync_events) cudaEventDestroy(e);
   if (s->stream_h2d) cudaStreamDestroy(s->stream_h2d);
@@ -1012,7 +1078,8 @@ struct DevSpace {
   float *buf = nullptr;  // lo | hi | seg | so2 bytes
 };
 
-static int upload_space(const mpb_scene *s, const mpb_space_desc *space, DevSpace *out) {
+struct DevBufs;
+static int upload_space(const mpb_scene *s, const mpb_space_desc *space, DevSpace *out, float *buf) {
   if (!space || !space->lo || !space->hi || !space->seg) return fail(MPB_ERR_INVALID, "null state-space description");
   const int D = space->dim;
   if (D != s->img.state_dim) return fail(MPB_ERR_INVALID, "state-space dimension does not match the scene's state_dim");
@@ -1025,7 +1092,7 @@ static int upload_space(const mpb_scene *s, const mpb_space_desc *space, DevSpac
   memcpy(h.data() + 2 * D, space->seg, D * sizeof(float));
   unsigned char *so2 = reinterpret_cast<unsigned char *>(h.data() + 3 * D);
   for (int j = 0; j < D; j++) so2[j] = space->so2 ? space->so2[j] : 0;
-  CU(cudaMalloc((void **)&out->buf, h.size() * sizeof(float)));
+  out->buf = buf;  // caller-owned, >= 4 * dim floats
   CU(cudaMemcpy(out->buf, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
   out->sp.dim = D;
   out->sp.lo = out->buf;
@@ -1035,16 +1102,40 @@ static int upload_space(const mpb_scene *s, const mpb_space_desc *space, DevSpac
   return MPB_OK;
 }
 
-struct DevBufs {  // frees everything on scope exit
-  std::vector<void *> ptrs;
+struct DevBufs {  // scratch blocks of one call: taken from the scene's pool, handed back on scope exit
+  mpb_scene *s;
+  std::vector<std::pair<void *, size_t>> held;
+  explicit DevBufs(mpb_scene *scene) : s(scene) {}
   template <typename T>
   cudaError_t alloc(T **p, size_t n) {
-    cudaError_t e = cudaMalloc((void **)p, std::max<size_t>(n, 1) * sizeof(T));
-    if (e == cudaSuccess) ptrs.push_back(*p);
+    const size_t bytes = (std::max<size_t>(n, 1) * sizeof(T) + 255) / 256 * 256;
+    int best = -1;  // smallest pooled block that fits without wasting more than half of itself
+    for (size_t i = 0; i < s->pool.size(); i++)
+      if (s->pool[i].second >= bytes && s->pool[i].second <= 2 * bytes + 4096 &&
+          (best < 0 || s->pool[i].second < s->pool[(size_t)best].second))
+        best = (int)i;
+    if (best >= 0) {
+      *p = (T *)s->pool[(size_t)best].first;
+      held.push_back(s->pool[(size_t)best]);
+      s->pool.erase(s->pool.begin() + best);
+      return cudaSuccess;
+    }
+    cudaError_t e = cudaMalloc((void **)p, bytes);
+    if (e != cudaSuccess) {  // pooled blocks of other shapes may be what exhausts the device: drop them and retry
+      cudaGetLastError();
+      for (auto &b : s->pool) cudaFree(b.first);
+      s->pool.clear();
+      e = cudaMalloc((void **)p, bytes);
+    }
+    if (e == cudaSuccess) held.push_back(std::make_pair((void *)*p, bytes));
     return e;
   }
-  ~DevBufs() {
-    for (void *p : ptrs) cudaFree(p);
+  ~DevBufs() {  // every entry point synchronises its stream before returning, so the blocks are idle here
+    for (auto &b : held) s->pool.push_back(b);
+    while (s->pool.size() > 48) {
+      cudaFree(s->pool.front().first);
+      s->pool.erase(s->pool.begin());
+    }
   }
 };
 
@@ -1058,10 +1149,11 @@ extern "C" int mpb_check_motion_batch(mpb_scene *s, const mpb_space_desc *space,
   if (n_edges > (1ll << 30)) return fail(MPB_ERR_CAPACITY, "too many edges in one call");
   CU(cudaSetDevice(s->device));
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  DevBufs bufs;
+  DevBufs bufs(s);
   DevSpace dsp;
-  int rc = upload_space(s, space, &dsp);
-  if (dsp.buf) bufs.ptrs.push_back(dsp.buf);
+  float *d_space = nullptr;
+  CU(bufs.alloc(&d_space, (size_t)4 * std::max(s->img.state_dim, 1)));
+  int rc = upload_space(s, space, &dsp, d_space);
   if (rc != MPB_OK) return rc;
   const int D = s->img.state_dim;
   const bool host = space_flag == MPB_HOST;
@@ -1126,10 +1218,11 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   const auto t_begin = std::chrono::steady_clock::now();
   CU(cudaSetDevice(s->device));
   cudaStream_t st = s->stream;
-  DevBufs bufs;
+  DevBufs bufs(s);
   DevSpace dsp;
-  int rc = upload_space(s, space, &dsp);
-  if (dsp.buf) bufs.ptrs.push_back(dsp.buf);
+  float *d_space = nullptr;
+  CU(bufs.alloc(&d_space, (size_t)4 * std::max(s->img.state_dim, 1)));
+  int rc = upload_space(s, space, &dsp, d_space);
   if (rc != MPB_OK) return rc;
   const int D = s->img.state_dim, Q = (int)n_queries;
   const int cap = std::max(params->tree_capacity, 2), max_path = std::max(params->max_path, 2);
@@ -1143,12 +1236,14 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   int smax = 1;
   for (int j = 0; j < D; j++) smax = std::max(smax, (int)std::ceil((double)range / space->seg[j]) + 1);
   if (smax > 4096) return fail(MPB_ERR_CAPACITY, "range / validity resolution gives too many samples per edge");
-  const long long n_states = (long long)Q * smax;
+  const int S = params->connect_steps > 0 ? std::min(params->connect_steps, 32) : 8;
+  const long long n_states = (long long)Q * S * smax;
   rc = prepare_work(s, (n_states + 31) / 32 * 32);
   if (rc != MPB_OK) return rc;
 
   RrtState r{};
   r.n_queries = Q; r.cap = cap; r.dim = D; r.smax = smax; r.max_goals = max_goals; r.max_path = max_path;
+  r.S = S;
   r.seed = params->seed;
   float *d_start = nullptr, *d_goals = nullptr, *d_states = nullptr, *d_paths = nullptr;
   int *d_ngoals = nullptr, *d_ints = nullptr, *d_pathlen = nullptr;
@@ -1158,10 +1253,10 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   CU(bufs.alloc(&d_start, (size_t)Q * D));
   CU(bufs.alloc(&d_goals, (size_t)Q * max_goals * D));
   CU(bufs.alloc(&d_ngoals, (size_t)Q));
-  CU(bufs.alloc(&d_ints, (size_t)Q * 13 + 4));  // size[2] goals_used status phase flag tsel nearest reach added sol[2] iters
+  CU(bufs.alloc(&d_ints, (size_t)Q * 14 + 4));  // size[2] goals_used status phase flag tsel nearest reach added sol[2] iters n_steps
   CU(bufs.alloc(&r.target, (size_t)Q * D));
-  CU(bufs.alloc(&r.edge_a, (size_t)Q * D));
-  CU(bufs.alloc(&r.edge_b, (size_t)Q * D));
+  CU(bufs.alloc(&r.edge_a, (size_t)Q * S * D));
+  CU(bufs.alloc(&r.edge_b, (size_t)Q * S * D));
   CU(bufs.alloc(&d_states, (size_t)n_states * D));
   CU(bufs.alloc(&d_verdict, (size_t)(n_states + 31) / 32 + 1));
   CU(bufs.alloc(&d_paths, (size_t)Q * max_path * D));
@@ -1170,15 +1265,16 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   r.goals_used = d_ints + 2 * Q; r.status = d_ints + 3 * Q; r.phase = d_ints + 4 * Q; r.flag_start = d_ints + 5 * Q;
   r.tsel = d_ints + 6 * Q; r.nearest = d_ints + 7 * Q; r.reach = d_ints + 8 * Q; r.added = d_ints + 9 * Q;
   r.sol = d_ints + 10 * Q; r.iters = d_ints + 12 * Q;
-  r.n_active = reinterpret_cast<unsigned *>(d_ints + 13 * Q);
+  r.n_steps = d_ints + 13 * Q;
+  r.n_active = reinterpret_cast<unsigned *>(d_ints + 14 * Q);
   r.start = d_start; r.goals = d_goals; r.n_goals = d_ngoals;
   {
-    std::vector<int> h((size_t)Q * 13 + 4, 0);
+    std::vector<int> h((size_t)Q * 14 + 4, 0);
     for (int q = 0; q < Q; q++) {
       h[2 * q] = 1;          // tStart_ holds the start state
       h[5 * (size_t)Q + q] = 1;  // startTree_ = true
     }
-    h[13 * (size_t)Q] = Q;
+    h[14 * (size_t)Q] = Q;
     CU(cudaMemcpyAsync(d_ints, h.data(), h.size() * sizeof(int), cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(r.parent, 0xff, (size_t)Q * 2 * cap * sizeof(int), st));
     CU(cudaMemcpyAsync(d_start, starts, (size_t)Q * D * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -1187,8 +1283,8 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
     CU(cudaMemcpy2DAsync(r.nodes, (size_t)2 * cap * D * sizeof(float), d_start, (size_t)D * sizeof(float), (size_t)D * sizeof(float), Q,
                          cudaMemcpyDeviceToDevice, st));
     CU(cudaMemsetAsync(d_verdict, 0, ((size_t)(n_states + 31) / 32 + 1) * sizeof(uint32_t), st));
-    CU(cudaMemsetAsync(r.edge_a, 0, (size_t)Q * D * sizeof(float), st));
-    CU(cudaMemsetAsync(r.edge_b, 0, (size_t)Q * D * sizeof(float), st));
+    CU(cudaMemsetAsync(r.edge_a, 0, (size_t)Q * S * D * sizeof(float), st));
+    CU(cudaMemsetAsync(r.edge_b, 0, (size_t)Q * S * D * sizeof(float), st));
     CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
     CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaStreamSynchronize(st));  // h goes out of scope
@@ -1197,7 +1293,7 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   auto enqueue_round = [&](long long *launches) -> int {
     size_t sync_ev = 0;
     rrt_advance_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
-    motion_expand_kernel<<<(Q + 255) / 256, 256, 0, st>>>(dsp.sp, r.edge_a, r.edge_b, Q, nullptr, nullptr, smax, d_states, nullptr);
+    motion_expand_kernel<<<(Q * S + 255) / 256, 256, 0, st>>>(dsp.sp, r.edge_a, r.edge_b, (long long)Q * S, nullptr, nullptr, smax, d_states, nullptr);
     *launches += 2;
     return launch_pass(s, nullptr, d_states, n_states, d_verdict, nullptr, st, nullptr, launches, nullptr, &sync_ev);
   };
@@ -1247,9 +1343,28 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   std::vector<int> h_iters(Q);
   CU(cudaMemcpyAsync(status, r.status, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(path_len, d_pathlen, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(paths, d_paths, (size_t)Q * max_path * D * sizeof(float), cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(h_iters.data(), r.iters, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  {  // waypoints: only the used rows cross PCIe (packed on the device, scattered into the caller's matrix here)
+    std::vector<int> off((size_t)Q + 1, 0);
+    for (int q = 0; q < Q; q++) off[(size_t)q + 1] = off[(size_t)q] + path_len[q];
+    const int total = off[(size_t)Q];
+    if (total > 0) {
+      int *d_off = nullptr;
+      float *d_packed = nullptr;
+      CU(bufs.alloc(&d_off, (size_t)Q + 1));
+      CU(bufs.alloc(&d_packed, (size_t)total * D));
+      CU(cudaMemcpyAsync(d_off, off.data(), ((size_t)Q + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+      pack_paths_kernel<<<Q, 128, 0, st>>>(d_paths, d_off, D, max_path, d_packed);
+      launches += 1;
+      std::vector<float> h_packed((size_t)total * D);
+      CU(cudaMemcpyAsync(h_packed.data(), d_packed, h_packed.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      for (int q = 0; q < Q; q++)
+        if (path_len[q] > 0)
+          memcpy(paths + (size_t)q * max_path * D, h_packed.data() + (size_t)off[(size_t)q] * D, (size_t)path_len[q] * D * sizeof(float));
+    }
+  }
   if (stats) {
     stats->rounds = rounds;
     stats->states_checked = rounds * n_states;
@@ -1291,7 +1406,7 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
   if (s->smem_verts) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, distance_kernel<true>, 256, vsm));
   else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, distance_kernel<false>, 256, 0));
   const int dblocks = s->num_sms * std::max(per_sm, 1);
-  DevBufs bufs;
+  DevBufs bufs(s);
   long long chunk = std::min<long long>(kMaxChunk, (n + 31) / 32 * 32);
   // candidates can be a large fraction of n * n_pairs: start from a pass size the queue certainly holds
   while (chunk > 4096 && (size_t)chunk * std::max(s->img.n_pairs, 1) > kMaxItems / 2) chunk = (chunk / 2 + 31) / 32 * 32;

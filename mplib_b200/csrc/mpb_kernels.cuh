@@ -35,6 +35,9 @@ struct SceneImg {
   const int *dynlist;   // moving objects grouped by owner joint
   const DevBvhNode *nodes;  // BVH node pool (meshes, octrees); DevObject::voff = root, ::vcnt = leaf type
   const float4 *prims;      // leaf primitives, 3 float4 each
+  const float4 *cullc;      // [n_pairs] cull table: world-fixed partner's sphere centre (xyz), (R1 + R2 + margin)^2 (w)
+  const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}
+  const int4 *runs;         // cull-table runs: {moving slot or -1, first entry, count, partner kind (0 fixed, 1 moving)}
   const int *pair_bin2;     // [n_pairs] bin of the leaf-level items a BVH pair expands into (-1: not a BVH pair)
   int expand_bin;           // first-round bin that collects the BVH pairs (-1: none)
   int n_bins2;
@@ -60,7 +63,7 @@ struct WorkQ {
 #define MPB_EPS FLT_EPSILON
 #define MPB_MPR_TOL 1e-6f
 #define MPB_MPR_MAX_ITERS 96
-#define MPB_UNIT_ITEMS 128   // most items a warp owns at a time in the narrowphase (scan_bins_kernel picks 32..128)
+#define MPB_UNIT_ITEMS 128   // most items a warp owns at a time in the narrowphase (scan_bins_kernel picks 2..128)
 #define MPB_COOP_MAX 10      // busy lanes at or below which a warp evaluates hull supports cooperatively
 #define MPB_STAGE_CHUNK 64   // staging slots a warp reserves per atomic (>= 32)
 
@@ -178,12 +181,16 @@ __device__ __forceinline__ Xf joint_step(const DevJoint &J, const Xf *parent, fl
   return a;
 }
 
-// shared-memory tables, transposed [slot][word][thread] so that every access of the FK / sphere phases is
-// conflict-free: sJ = world transforms of the kept joints (12 words), sC = bounding-sphere centres (3 words)
-#define SMJ(js, k, t) sJ[((js) * 12 + (k)) * BLOCK + (t)]
-#define SMC(d, k, t) sC[((d) * 3 + (k)) * BLOCK + (t)]
+// Per-WARP shared-memory tables, transposed [slot][word][lane] so that every access of the FK / sphere phases is
+// conflict-free: sJ = world transforms of the kept joints (12 words), sC = bounding-sphere centres (3 words), sQ =
+// the warp's private survivor queue.  A warp owns a tile of 32 configurations from FK to the staging queue; nothing
+// in this kernel needs a block-level barrier.
+#define MPB_CULL_GROUP 16   // cull-table entries tested between two queue pushes
+#define MPB_CULL_DRAIN 64   // queue length at which the warp runs the dense OBB phase
+#define MPB_CULL_QCAP (MPB_CULL_GROUP * 32 + MPB_CULL_DRAIN)
+#define SMJ(js, k, t) sJ[((js) * 12 + (k)) * 32 + (t)]
+#define SMC(d, k, t) sC[((d) * 3 + (k)) * 32 + (t)]
 
-template <int BLOCK>
 __device__ __forceinline__ Xf smem_joint(const float *sJ, int js, int t) {
   Xf w;
 #pragma unroll
@@ -193,30 +200,31 @@ __device__ __forceinline__ Xf smem_joint(const float *sJ, int js, int t) {
   return w;
 }
 
-// Phases per tile of BLOCK configurations:
-//   1. FK, thread per configuration: joint transforms -> sJ, bounding-sphere centres of the moving objects -> sC
-//   2. per 32 admitted pairs: bounding-sphere test, thread per configuration -> survivors pushed to a block queue
-//   3. dense: thread per queued (configuration, pair): 15-axis OBB SAT with the owner's joint transforms read
-//      from sJ; what is left is ballot-compacted into the global staging queue (one atomic per warp chunk)
+// Phases per tile of 32 configurations (one warp):
+//   1. FK, lane per configuration: joint transforms -> sJ, bounding-sphere centres of the moving objects -> sC
+//   2. bounding spheres, lane per configuration, over the CULL TABLE: the admitted pairs re-ordered into runs that
+//      share their moving object (its centre stays in registers) and whose partner is either world-fixed (centre and
+//      squared radius sum in one float4, a uniform 16-byte load) or another moving object (centre from sC);
+//      survivors of MPB_CULL_GROUP entries are pushed to the warp queue
+//   3. dense, lane per queued (configuration, pair): 15-axis OBB SAT with the owner's joint transforms read from sJ;
+//      what is left is ballot-compacted into the global staging queue (one atomic per warp chunk)
 //   MODE 0 (collide): as above.  MODE 1 (distance): a pair is a candidate for the minimum iff its bounding-sphere
 //   lower bound |c| - R does not exceed the smallest upper bound |c| + R over all admitted pairs of the
 //   configuration; candidates skip the SAT (overlap is not the question) and go to the GJK distance kernel.
 template <int BLOCK, int MODE>
 __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, long long cfg_base, WorkQ wq) {
   extern __shared__ __align__(16) float smem_f[];
-  float *sJ = smem_f;
-  float *sC = sJ + (size_t)img.n_jslots * 12 * BLOCK;
-  unsigned short *sQ = reinterpret_cast<unsigned short *>(sC + (size_t)img.n_dyn * 3 * BLOCK);  // [BLOCK * 32]
-  __shared__ unsigned sCount[2];  // queue length, double-buffered by round parity
-  const int tid = threadIdx.x;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
+  const size_t warp_words = ((size_t)img.n_jslots * 12 + (size_t)img.n_dyn * 3) * 32 + MPB_CULL_QCAP;
+  float *sJ = smem_f + warp * warp_words;
+  float *sC = sJ + (size_t)img.n_jslots * 12 * 32;
+  unsigned *sQ = reinterpret_cast<unsigned *>(sC + (size_t)img.n_dyn * 3 * 32);
   unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
-  const long long n_tiles = (n + BLOCK - 1) / BLOCK;
-  unsigned rnd = 0;
-  if (tid < 2) sCount[tid] = 0;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long i = tile * BLOCK + tid;
+  const long long n_tiles = (n + 31) / 32;
+  const long long warp_stride = (long long)gridDim.x * (BLOCK / 32);
+  for (long long tile = (long long)blockIdx.x * (BLOCK / 32) + warp; tile < n_tiles; tile += warp_stride) {
+    const long long i = tile * 32 + lane;
     const bool valid = i < n;
     // ---- 1. FK, running transform in registers
     if (valid) {
@@ -226,58 +234,74 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
         const DevJoint &J = img.joints[j];
         const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
         if (J.parent == 0) cur = joint_step(J, nullptr, qj);
-        else if (J.pjslot >= 0) { const Xf par = smem_joint<BLOCK>(sJ, J.pjslot, tid); cur = joint_step(J, &par, qj); }
+        else if (J.pjslot >= 0) { const Xf par = smem_joint(sJ, J.pjslot, lane); cur = joint_step(J, &par, qj); }
         else cur = joint_step(J, &cur, qj);
         if (J.jslot >= 0) {
 #pragma unroll
-          for (int k = 0; k < 9; k++) SMJ(J.jslot, k, tid) = cur.r[k];
+          for (int k = 0; k < 9; k++) SMJ(J.jslot, k, lane) = cur.r[k];
 #pragma unroll
-          for (int k = 0; k < 3; k++) SMJ(J.jslot, 9 + k, tid) = cur.p[k];
+          for (int k = 0; k < 3; k++) SMJ(J.jslot, 9 + k, lane) = cur.p[k];
         }
         for (int e = 0; e < J.dyn_count; e++) {
           const DevObject &O = img.objs[img.dynlist[J.dyn_first + e]];
           float c[3];
           xf_point(cur, O.bcj, c);  // bounding-sphere centre in the joint frame -> world
 #pragma unroll
-          for (int k = 0; k < 3; k++) SMC(O.dyn, k, tid) = c[k];
+          for (int k = 0; k < 3; k++) SMC(O.dyn, k, lane) = c[k];
         }
       }
     }
+    __syncwarp();
     float ub_min = FLT_MAX;
     if (MODE == 1 && valid) {
-      for (int p = 0; p < img.n_pairs; p++) {
-        const DevPair pr = img.pairs[p];
-        const int da = ((pr.bin_dyn >> 16) & 0xff) - 1, db = ((pr.bin_dyn >> 24) & 0xff) - 1;
-        float ax, ay, az, bx, by, bz;
-        if (da >= 0) { ax = SMC(da, 0, tid); ay = SMC(da, 1, tid); az = SMC(da, 2, tid); }
-        else { const float *c = img.objs[pr.a].bcw; ax = c[0]; ay = c[1]; az = c[2]; }
-        if (db >= 0) { bx = SMC(db, 0, tid); by = SMC(db, 1, tid); bz = SMC(db, 2, tid); }
-        else { const float *c = img.objs[pr.b].bcw; bx = c[0]; by = c[1]; bz = c[2]; }
+      for (int k = 0; k < img.n_pairs; k++) {
+        const float4 c = __ldg(img.cullc + k);
+        const int2 m = __ldg(img.cullm + k);
+        const int m1 = m.y & 0xffff, m2 = m.y >> 16;  // biased by one; 0 = none
+        float ax = 0.f, ay = 0.f, az = 0.f, bx = c.x, by = c.y, bz = c.z;
+        if (m1) { ax = SMC(m1 - 1, 0, lane); ay = SMC(m1 - 1, 1, lane); az = SMC(m1 - 1, 2, lane); }
+        if (m2) { bx = SMC(m2 - 1, 0, lane); by = SMC(m2 - 1, 1, lane); bz = SMC(m2 - 1, 2, lane); }
         const float dx = ax - bx, dy = ay - by, dz = az - bz;
-        ub_min = fminf(ub_min, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + pr.rr);
+        ub_min = fminf(ub_min, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + sqrtf(c.w));
       }
       ub_min *= 1.000001f;
     }
-    for (int base = 0; base < img.n_pairs; base += 32) {
-      __syncthreads();  // FK tables complete (first round); previous dense phase done with sQ
-      // ---- 2. bounding spheres
+    unsigned qn = 0;  // warp-uniform queue length
+    int r = 0;        // run cursor
+    for (int gbase = 0; gbase < img.n_pairs; gbase += MPB_CULL_GROUP) {
+      const int gend = min(gbase + MPB_CULL_GROUP, img.n_pairs);
+      // ---- 2. bounding spheres over the cull table
       unsigned mask = 0;
-      const int cnt = min(32, img.n_pairs - base);
-      if (valid) {
-        for (int k = 0; k < cnt; k++) {
-          const DevPair pr = img.pairs[base + k];
-          const int da = ((pr.bin_dyn >> 16) & 0xff) - 1, db = ((pr.bin_dyn >> 24) & 0xff) - 1;
-          float ax, ay, az, bx, by, bz;
-          if (da >= 0) { ax = SMC(da, 0, tid); ay = SMC(da, 1, tid); az = SMC(da, 2, tid); }
-          else { const float *c = img.objs[pr.a].bcw; ax = c[0]; ay = c[1]; az = c[2]; }
-          if (db >= 0) { bx = SMC(db, 0, tid); by = SMC(db, 1, tid); bz = SMC(db, 2, tid); }
-          else { const float *c = img.objs[pr.b].bcw; bx = c[0]; by = c[1]; bz = c[2]; }
-          const float dx = ax - bx, dy = ay - by, dz = az - bz;
-          const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-          if (MODE == 0 ? (d2c <= pr.rr * pr.rr) : (sqrtf(d2c) - pr.rr <= ub_min)) mask |= 1u << k;
+      int k = gbase;
+      while (k < gend) {
+        const int4 run = __ldg(img.runs + r);  // {moving slot or -1, first, count, partner kind}
+        const int rlast = run.y + run.z;
+        const int rend = min(rlast, gend);
+        float ax = 0.f, ay = 0.f, az = 0.f;
+        if (run.x >= 0) { ax = SMC(run.x, 0, lane); ay = SMC(run.x, 1, lane); az = SMC(run.x, 2, lane); }
+        if (run.w == 0) {  // world-fixed partners: centre + (R1 + R2)^2 in one uniform 16-byte load
+#pragma unroll 4
+          for (; k < rend; k++) {
+            const float4 c = __ldg(img.cullc + k);
+            const float dx = ax - c.x, dy = ay - c.y, dz = az - c.z;
+            const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+            const bool s = MODE == 0 ? (d2c <= c.w) : (sqrtf(d2c) - sqrtf(c.w) <= ub_min);
+            mask |= (unsigned)s << (k - gbase);
+          }
+        } else {  // moving partners
+          for (; k < rend; k++) {
+            const float rr2 = __ldg(&img.cullc[k].w);
+            const int m2 = (__ldg(&img.cullm[k].y) >> 16) - 1;
+            const float dx = ax - SMC(m2, 0, lane), dy = ay - SMC(m2, 1, lane), dz = az - SMC(m2, 2, lane);
+            const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+            const bool s = MODE == 0 ? (d2c <= rr2) : (sqrtf(d2c) - sqrtf(rr2) <= ub_min);
+            mask |= (unsigned)s << (k - gbase);
+          }
         }
+        if (rend == rlast) r++;
       }
-      {  // push (thread, pair-in-tile) survivors: warp prefix sum + one shared atomic per warp
+      if (!valid) mask = 0;
+      if (__any_sync(FULL, mask != 0)) {  // push (lane, entry) survivors: warp prefix sum, no atomics
         const unsigned c = __popc(mask);
         unsigned incl = c;
 #pragma unroll
@@ -285,56 +309,53 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
           const unsigned t = __shfl_up_sync(FULL, incl, o);
           if ((int)lane >= o) incl += t;
         }
-        const unsigned wtot = __shfl_sync(FULL, incl, 31);
-        unsigned wb = 0;
-        if (lane == 31 && wtot) wb = atomicAdd(&sCount[rnd & 1], wtot);
-        wb = __shfl_sync(FULL, wb, 31);
-        unsigned pos = wb + incl - c;
+        unsigned pos = qn + incl - c;
         while (mask) {
-          const int k = __ffs(mask) - 1;
+          const int kk = __ffs(mask) - 1;
           mask &= mask - 1;
-          sQ[pos++] = (unsigned short)(tid | (k << 8));
+          sQ[pos++] = lane | ((unsigned)(gbase + kk) << 5);
         }
+        qn += __shfl_sync(FULL, incl, 31);
+        __syncwarp();
       }
-      __syncthreads();
-      // ---- 3. dense OBB SAT over the queue
-      const unsigned total = sCount[rnd & 1];
-      if (tid == 0) sCount[(rnd + 1) & 1] = 0;  // nobody reads the other counter between the two barriers
-      rnd++;
-      for (unsigned e0 = warp * 32; e0 < total; e0 += BLOCK) {
+      const bool last = gend == img.n_pairs;
+      if (qn < MPB_CULL_DRAIN && !(last && qn > 0)) continue;
+      // ---- 3. dense OBB SAT over the queue (full warps; a remainder < 32 waits for the next drain)
+      const unsigned qfull = last ? qn : (qn & ~31u);
+      for (unsigned e0 = 0; e0 < qfull; e0 += 32) {
         const unsigned e = e0 + lane;
         bool keep = false;
         Xf rel;
         int p = 0, owner = 0;
-        if (e < total) {
+        if (e < qfull) {
           const unsigned ent = sQ[e];
-          owner = ent & 0xff;
-          p = base + (ent >> 8);
+          owner = ent & 31;
+          p = __ldg(&img.cullm[ent >> 5].x);
           const DevPair pr = img.pairs[p];
           const DevObject &A = img.objs[pr.a];
           const DevObject &B = img.objs[pr.b];
-          const Xf Wa = A.jslot >= 0 ? xf_mul(smem_joint<BLOCK>(sJ, A.jslot, owner), load_xf12(A.L)) : load_xf12(A.L);
-          const Xf Wb = B.jslot >= 0 ? xf_mul(smem_joint<BLOCK>(sJ, B.jslot, owner), load_xf12(B.L)) : load_xf12(B.L);
+          const Xf Wa = A.jslot >= 0 ? xf_mul(smem_joint(sJ, A.jslot, owner), load_xf12(A.L)) : load_xf12(A.L);
+          const Xf Wb = B.jslot >= 0 ? xf_mul(smem_joint(sJ, B.jslot, owner), load_xf12(B.L)) : load_xf12(B.L);
           rel = xf_inv_mul(Wa, Wb);
           keep = true;
           if (MODE == 0) {
-          // box B in box A's frame:  Ra^T (rel.R Rb),  Ra^T (rel*ocB - ocA)
-          float M[9], R[9], cbA[3], t[3];
+            // box B in box A's frame:  Ra^T (rel.R Rb),  Ra^T (rel*ocB - ocA)
+            float M[9], R[9], cbA[3], t[3];
 #pragma unroll
-          for (int r = 0; r < 3; r++)
+            for (int rr = 0; rr < 3; rr++)
 #pragma unroll
-            for (int c = 0; c < 3; c++)
-              M[3 * r + c] = fmaf(rel.r[3 * r], B.oR[c], fmaf(rel.r[3 * r + 1], B.oR[3 + c], rel.r[3 * r + 2] * B.oR[6 + c]));
+              for (int c = 0; c < 3; c++)
+                M[3 * rr + c] = fmaf(rel.r[3 * rr], B.oR[c], fmaf(rel.r[3 * rr + 1], B.oR[3 + c], rel.r[3 * rr + 2] * B.oR[6 + c]));
 #pragma unroll
-          for (int r = 0; r < 3; r++)
+            for (int rr = 0; rr < 3; rr++)
 #pragma unroll
-            for (int c = 0; c < 3; c++)
-              R[3 * r + c] = fmaf(A.oR[r], M[c], fmaf(A.oR[3 + r], M[3 + c], A.oR[6 + r] * M[6 + c]));
-          xf_point(rel, B.oc, cbA);
-          const float d0 = cbA[0] - A.oc[0], d1 = cbA[1] - A.oc[1], d2 = cbA[2] - A.oc[2];
+              for (int c = 0; c < 3; c++)
+                R[3 * rr + c] = fmaf(A.oR[rr], M[c], fmaf(A.oR[3 + rr], M[3 + c], A.oR[6 + rr] * M[6 + c]));
+            xf_point(rel, B.oc, cbA);
+            const float d0 = cbA[0] - A.oc[0], d1 = cbA[1] - A.oc[1], d2 = cbA[2] - A.oc[2];
 #pragma unroll
-          for (int r = 0; r < 3; r++) t[r] = fmaf(A.oR[r], d0, fmaf(A.oR[3 + r], d1, A.oR[6 + r] * d2));
-          keep = !obb_disjoint(R, t, A.oh, B.oh);
+            for (int rr = 0; rr < 3; rr++) t[rr] = fmaf(A.oR[rr], d0, fmaf(A.oR[3 + rr], d1, A.oR[6 + rr] * d2));
+            keep = !obb_disjoint(R, t, A.oh, B.oh);
           }
         }
         const unsigned km = __ballot_sync(FULL, keep);
@@ -356,10 +377,10 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
           const int bin = img.pairs[p].bin_dyn & 0xffff;
           if (slot < wq.cap) {
 #pragma unroll
-            for (int k = 0; k < 9; k++) wq.stf[(size_t)k * wq.cap + slot] = rel.r[k];
+            for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = rel.r[k2];
 #pragma unroll
-            for (int k = 0; k < 3; k++) wq.stf[(size_t)(9 + k) * wq.cap + slot] = rel.p[k];
-            wq.scfg[slot] = (int)(cfg_base + tile * BLOCK + owner);
+            for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = rel.p[k2];
+            wq.scfg[slot] = (int)(cfg_base + tile * 32 + owner);
             wq.spair[slot] = p;
             wq.saux[slot] = 0;
           }
@@ -368,8 +389,15 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
         }
         wused += cntk;
       }
+      const unsigned left = qn - qfull;  // < 32: move the remainder to the front of the queue
+      unsigned carry = 0;
+      if (lane < left) carry = sQ[qfull + lane];
+      __syncwarp();
+      if (lane < left) sQ[lane] = carry;
+      __syncwarp();
+      qn = left;
     }
-    __syncthreads();  // the next tile's FK overwrites sJ / sC
+    __syncwarp();  // the next tile's FK overwrites sJ / sC
   }
   // invalidate the unused tail of the last chunk
   if (wbase != 0xffffffffu) {
@@ -387,7 +415,7 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_
     for (int b = 0; b < n_bins; b++)
       if (b != skip_bin) all += wq.bin_count[b];
     unsigned unit = MPB_UNIT_ITEMS;
-    while (unit > 32u && all / unit < n_warps) unit >>= 1;
+    while (unit > 2u && all / unit < n_warps) unit >>= 1;  // few items (a planning round): short slices -> cooperative supports
     wq.totals[4] = unit;
     for (int b = 0; b < n_bins; b++) {
       wq.bin_start[b] = items;
@@ -401,6 +429,7 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_
     wq.unit_start[n_bins] = units;
     wq.totals[1] = units;
     wq.totals[3] = 0;
+    wq.totals[5] = 0;  // expand_kernel's item ticket
     if (wq.totals[0] > wq.cap) wq.totals[2] = 1u;  // staging overflow: the host redoes the pass in smaller chunks
     atomicAdd(wq.counters, (unsigned long long)items);
   }
@@ -802,7 +831,7 @@ __global__ void __launch_bounds__(128) fk_pose_kernel(SceneImg img, const float 
 }
 
 // ---------------------------------------------------------------------------------------------- BVH expansion
-// Thread per (configuration, shape x BVH-object) item of the first round.  Walks the object's AABB tree
+// Warp per (configuration, shape x BVH-object) item of the first round.  Walks the object's AABB tree
 // (mesh triangles, or octree cells merged into boxes) against the shape's OBB, both in the object's frame
 // (replaces the OBBRSS descent of MeshShapeCollisionTraversalNodeOBBRSS and OcTreeSolver::
 // OcTreeShapeIntersectRecurse that ::fcl::collide runs for src/planning_world.cpp:419-434, 464-478), and
@@ -813,12 +842,27 @@ namespace cg = cooperative_groups;
 
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
+#define MPB_EXP_STACK 1024  // node frontier per warp
+
+// Warp per item: the frontier of BVH nodes lives in a shared-memory stack; every trip pops up to 32 nodes (one per
+// lane), tests them against the shape's OBB, pushes the children of the surviving inner nodes (ballot compaction) and
+// lets the lanes that hold surviving leaves test / emit their primitives.  No divergence inside the 15-axis test and
+// a short critical path even for small batches (a planning round); when the stack runs nearly full the warp pops
+// one node per trip (depth-first), which bounds the growth by the tree depth.
 __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
                                                      unsigned int *__restrict__ pair_bits) {
+  __shared__ int s_stack[4][MPB_EXP_STACK];
   const int eb = img.expand_bin;
   if (eb < 0) return;
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int *stack = s_stack[warp];
   const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
-  for (unsigned it = first + blockIdx.x * blockDim.x + threadIdx.x; it < end; it += gridDim.x * blockDim.x) {
+  for (;;) {
+    unsigned it = 0;
+    if (lane == 0) it = atomicAdd(&wq.totals[5], 1u);
+    it = first + __shfl_sync(FULL, it, 0);
+    if (it >= end) break;
     const int cfg = wq.icfg[it], p = wq.ipair[it];
     const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
                                  : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
@@ -842,6 +886,12 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
         for (int c = 0; c < 3; c++) Ra[3 * r + c] = fmaf(R[r], A.oR[c], fmaf(R[3 + r], A.oR[3 + c], R[6 + r] * A.oR[6 + c]));
       }
     }
+    // node AABB (axes = identity) in the OBB's frame: Rrel = Ra^T
+    float Rrel[9];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+      for (int c = 0; c < 3; c++) Rrel[3 * r + c] = Ra[3 * c + r];
     // inscribed-ball centre of the shape in B
     float cin[3];
     {
@@ -850,76 +900,93 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
       for (int r = 0; r < 3; r++) cin[r] = fmaf(R[r], d0, fmaf(R[3 + r], d1, R[6 + r] * d2));
     }
     const float rin2 = A.rin * A.rin;
+    const float ah[3] = {A.oh[0], A.oh[1], A.oh[2]};
     const int leaf_type = B.vcnt;
-    int stack[48];
-    int sp = 0;
-    stack[sp++] = B.voff;
+    const int bin2 = img.pair_bin2[p];
+    int sp = 1;
+    if (lane == 0) stack[0] = B.voff;
+    __syncwarp();
     bool hit = false;
-    while (sp > 0 && !hit) {
-      const DevBvhNode nd = img.nodes[stack[--sp]];
-      // node AABB (axes = identity) in the OBB's frame: Rrel = Ra^T, trel = Ra^T (c_node - ca)
-      float Rrel[9], trel[3];
-      const float e0 = nd.c[0] - ca[0], e1 = nd.c[1] - ca[1], e2 = nd.c[2] - ca[2];
+    while (sp > 0) {
+      const int take = sp > MPB_EXP_STACK - 64 ? 1 : min(sp, 32);
+      int node = -1;
+      if ((int)lane < take) node = stack[sp - 1 - (int)lane];
+      sp -= take;
+      __syncwarp();
+      bool pass = false;
+      DevBvhNode nd;
+      nd.left = 0; nd.right = 0;
+      if (node >= 0) {
+        nd = img.nodes[node];
+        float trel[3];
+        const float e0 = nd.c[0] - ca[0], e1 = nd.c[1] - ca[1], e2 = nd.c[2] - ca[2];
 #pragma unroll
-      for (int r = 0; r < 3; r++) {
-        trel[r] = fmaf(Ra[r], e0, fmaf(Ra[3 + r], e1, Ra[6 + r] * e2));
-#pragma unroll
-        for (int c = 0; c < 3; c++) Rrel[3 * r + c] = Ra[3 * c + r];
+        for (int r = 0; r < 3; r++) trel[r] = fmaf(Ra[r], e0, fmaf(Ra[3 + r], e1, Ra[6 + r] * e2));
+        pass = !obb_disjoint(Rrel, trel, ah, nd.h);
       }
-      if (obb_disjoint(Rrel, trel, A.oh, nd.h)) continue;
-      if (nd.left >= 0) {
-        if (sp + 2 <= 48) { stack[sp++] = nd.left; stack[sp++] = nd.right; }
-        continue;
+      const bool inner = pass && nd.left >= 0;
+      const unsigned im = __ballot_sync(FULL, inner);
+      if (inner) {
+        const int pos = sp + 2 * __popc(im & ((1u << lane) - 1u));
+        if (pos + 1 < MPB_EXP_STACK) { stack[pos] = nd.left; stack[pos + 1] = nd.right; }
+        else atomicAdd(&wq.counters[2], 1ull);  // dropped subtree: reported as a capped item, never silent
       }
-      const int pfirst = ~nd.left;
-      for (int k = 0; k < nd.right && !hit; k++) {
-        const int prim = pfirst + k;
-        const float4 a = __ldg(img.prims + 3 * prim), b = __ldg(img.prims + 3 * prim + 1);
-        float pc[3], ph[3];
-        if (leaf_type == MPB_GEOM_VBOX) {
-          pc[0] = a.x; pc[1] = a.y; pc[2] = a.z; ph[0] = b.x; ph[1] = b.y; ph[2] = b.z;
-        } else {
-          const float4 c = __ldg(img.prims + 3 * prim + 2);
-          const float lo0 = fminf(a.x, fminf(b.x, c.x)), hi0 = fmaxf(a.x, fmaxf(b.x, c.x));
-          const float lo1 = fminf(a.y, fminf(b.y, c.y)), hi1 = fmaxf(a.y, fmaxf(b.y, c.y));
-          const float lo2 = fminf(a.z, fminf(b.z, c.z)), hi2 = fmaxf(a.z, fmaxf(b.z, c.z));
-          pc[0] = 0.5f * (lo0 + hi0); pc[1] = 0.5f * (lo1 + hi1); pc[2] = 0.5f * (lo2 + hi2);
-          ph[0] = 0.5f * (hi0 - lo0) + 1e-6f; ph[1] = 0.5f * (hi1 - lo1) + 1e-6f; ph[2] = 0.5f * (hi2 - lo2) + 1e-6f;
-        }
-        if (nd.right > 1 || leaf_type == MPB_GEOM_TRI) {  // primitive-level reject
-          const float g0 = pc[0] - ca[0], g1 = pc[1] - ca[1], g2 = pc[2] - ca[2];
-          float tr[3];
+      sp = min(sp + 2 * __popc(im), MPB_EXP_STACK);  // (a frontier beyond the stack would need a tree deeper than ~60)
+      __syncwarp();
+      bool lhit = false;
+      if (pass && nd.left < 0) {
+        const int pfirst = ~nd.left;
+        for (int k = 0; k < nd.right && !lhit; k++) {
+          const int prim = pfirst + k;
+          const float4 a = __ldg(img.prims + 3 * prim), b = __ldg(img.prims + 3 * prim + 1);
+          float pc[3], ph[3];
+          if (leaf_type == MPB_GEOM_VBOX) {
+            pc[0] = a.x; pc[1] = a.y; pc[2] = a.z; ph[0] = b.x; ph[1] = b.y; ph[2] = b.z;
+          } else {
+            const float4 c = __ldg(img.prims + 3 * prim + 2);
+            const float lo0 = fminf(a.x, fminf(b.x, c.x)), hi0 = fmaxf(a.x, fmaxf(b.x, c.x));
+            const float lo1 = fminf(a.y, fminf(b.y, c.y)), hi1 = fmaxf(a.y, fmaxf(b.y, c.y));
+            const float lo2 = fminf(a.z, fminf(b.z, c.z)), hi2 = fmaxf(a.z, fmaxf(b.z, c.z));
+            pc[0] = 0.5f * (lo0 + hi0); pc[1] = 0.5f * (lo1 + hi1); pc[2] = 0.5f * (lo2 + hi2);
+            ph[0] = 0.5f * (hi0 - lo0) + 1e-6f; ph[1] = 0.5f * (hi1 - lo1) + 1e-6f; ph[2] = 0.5f * (hi2 - lo2) + 1e-6f;
+          }
+          if (nd.right > 1 || leaf_type == MPB_GEOM_TRI) {  // primitive-level reject
+            const float g0 = pc[0] - ca[0], g1 = pc[1] - ca[1], g2 = pc[2] - ca[2];
+            float tr[3];
 #pragma unroll
-          for (int r = 0; r < 3; r++) tr[r] = fmaf(Ra[r], g0, fmaf(Ra[3 + r], g1, Ra[6 + r] * g2));
-          if (obb_disjoint(Rrel, tr, A.oh, ph)) continue;
-        }
-        if (leaf_type == MPB_GEOM_VBOX && rin2 > 0.f) {  // sufficient test: cell touches the inscribed ball
-          const float q0 = clampf(cin[0], pc[0] - ph[0], pc[0] + ph[0]) - cin[0];
-          const float q1 = clampf(cin[1], pc[1] - ph[1], pc[1] + ph[1]) - cin[1];
-          const float q2 = clampf(cin[2], pc[2] - ph[2], pc[2] + ph[2]) - cin[2];
-          if (fmaf(q0, q0, fmaf(q1, q1, q2 * q2)) < rin2) { hit = true; break; }
-        }
-        // emit a leaf-level item (warp-aggregated slot allocation)
-        cg::coalesced_group g = cg::coalesced_threads();
-        unsigned base = 0;
-        if (g.thread_rank() == 0) base = atomicAdd(&wq.totals[0], (unsigned)g.size());
-        base = g.shfl(base, 0);
-        const unsigned slot = base + g.thread_rank();
-        if (slot < wq.cap) {
+            for (int r = 0; r < 3; r++) tr[r] = fmaf(Ra[r], g0, fmaf(Ra[3 + r], g1, Ra[6 + r] * g2));
+            if (obb_disjoint(Rrel, tr, ah, ph)) continue;
+          }
+          if (leaf_type == MPB_GEOM_VBOX && rin2 > 0.f) {  // sufficient test: cell touches the inscribed ball
+            const float q0 = clampf(cin[0], pc[0] - ph[0], pc[0] + ph[0]) - cin[0];
+            const float q1 = clampf(cin[1], pc[1] - ph[1], pc[1] + ph[1]) - cin[1];
+            const float q2 = clampf(cin[2], pc[2] - ph[2], pc[2] + ph[2]) - cin[2];
+            if (fmaf(q0, q0, fmaf(q1, q1, q2 * q2)) < rin2) { lhit = true; break; }
+          }
+          // emit a leaf-level item (warp-aggregated slot allocation)
+          cg::coalesced_group g = cg::coalesced_threads();
+          unsigned base = 0;
+          if (g.thread_rank() == 0) base = atomicAdd(&wq.totals[0], (unsigned)g.size());
+          base = g.shfl(base, 0);
+          const unsigned slot = base + g.thread_rank();
+          if (slot < wq.cap) {
 #pragma unroll
-          for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = R[k2];
+            for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = R[k2];
 #pragma unroll
-          for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = t[k2];
-          wq.scfg[slot] = cfg;
-          wq.spair[slot] = p;
-          wq.saux[slot] = prim;
-          atomicAdd(&wq.bin_count[img.pair_bin2[p]], 1u);
+            for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = t[k2];
+            wq.scfg[slot] = cfg;
+            wq.spair[slot] = p;
+            wq.saux[slot] = prim;
+            atomicAdd(&wq.bin_count[bin2], 1u);
+          }
         }
       }
+      if (__any_sync(FULL, lhit)) { hit = true; break; }
     }
-    if (hit) {
+    if (hit && lane == 0) {
       atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
       if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
     }
+    __syncwarp();
   }
 }

@@ -125,6 +125,7 @@ __global__ void fill_valid_bits_kernel(unsigned *__restrict__ valid_bits, long l
 // ---------------------------------------------------------------------------------------------- RRTConnect, lock-step
 struct RrtState {
   int n_queries, cap, dim, smax, max_goals, max_path;
+  int S;               // sub-edges a query may emit per round (connect steps validated speculatively)
   float *nodes;        // [Q][2][cap][dim]   tree 0 = tStart_, tree 1 = tGoal_
   int *parent;         // [Q][2][cap]        -1 = root
   int *size;           // [Q][2]
@@ -133,17 +134,18 @@ struct RrtState {
   const int *n_goals;  // [Q]
   int *goals_used;     // [Q]  pis_.getSampledGoalsCount()
   int *status;         // [Q]  MPB_RRT_*
-  int *phase;          // [Q]  0 = nothing pending, 1 = first growTree of an iteration pending, 2 = connect step pending
+  int *phase;          // [Q]  0 = nothing pending, 1 = first growTree of an iteration pending, 2 = connect steps pending
   int *flag_start;     // [Q]  startTree_
-  int *tsel;           // [Q]  tree the pending edge grows
-  int *nearest;        // [Q]  nmotion of the pending edge
-  int *reach;          // [Q]
+  int *tsel;           // [Q]  tree the pending edges grow
+  int *nearest;        // [Q]  nmotion of the first pending edge
+  int *reach;          // [Q]  the last pending edge ends on the target
+  int *n_steps;        // [Q]  pending sub-edges (1 .. S)
   int *added;          // [Q]  addedMotion (index in tree 1 - tsel while connecting)
   float *target;       // [Q][dim]  rstate
-  float *edge_a;       // [Q][dim]  nmotion->state
-  float *edge_b;       // [Q][dim]  dstate
+  float *edge_a;       // [Q][S][dim]  sub-edge k runs from edge_a[k] to edge_b[k]; edge_a[k] = edge_b[k-1]
+  float *edge_b;       // [Q][S][dim]
   int *sol;            // [Q][2]   solution motions in tree 0 / tree 1
-  int *iters;          // [Q]      growTree calls issued
+  int *iters;          // [Q]      growTree calls consumed
   unsigned *n_active;  // [1]
   unsigned long long seed;
 };
@@ -156,44 +158,64 @@ __device__ __forceinline__ float rrt_uniform(unsigned long long seed, unsigned q
   return (float)(z >> 40) * (1.0f / 16777216.0f);
 }
 
-// One warp per query, one RRTConnect::growTree call per round.
+// A query that has finished (or a speculative slot that is not used this round) must not cost narrowphase work:
+// its edge slots are set to NaN, which every bounding-sphere comparison of fk_cull_kernel rejects.
+__device__ __forceinline__ void rrt_blank_edges(float *ea, float *eb, int n, int lane) {
+  const float nanv = __int_as_float(0x7fc00000);
+  for (int i = lane; i < n; i += 32) { ea[i] = nanv; eb[i] = nanv; }
+}
+
+// One warp per query.  A round consumes the verdicts of the query's pending sub-edges and emits the next ones.
+// The first growTree() of an iteration emits ONE sub-edge (extend towards the random state).  The connect loop
+// `while (gsc == ADVANCED) gsc = growTree(otherTree, tgi, rmotion)` walks the straight line from the nearest node
+// of the other tree towards the new state in steps of `range` -- after every ADVANCED step the node just added is
+// the nearest one (its distance to the target dropped by exactly `range`, every other node is at least as far as
+// the previous nearest) -- so up to S of those steps are emitted at once and validated speculatively; the valid
+// prefix is added node by node exactly as the sequential loop would, the first invalid step is the TRAPPED call.
 __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc sp, float range, const unsigned *__restrict__ verdict_bits) {
   const unsigned FULL = 0xffffffffu;
   const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
   if (q >= r.n_queries) return;
   if (r.status[q] != MPB_RRT_ACTIVE) return;
-  const int D = r.dim;
-  float *ea = r.edge_a + (size_t)q * D, *eb = r.edge_b + (size_t)q * D, *tg = r.target + (size_t)q * D;
+  const int D = r.dim, S = r.S;
+  float *ea = r.edge_a + (size_t)q * S * D, *eb = r.edge_b + (size_t)q * S * D, *tg = r.target + (size_t)q * D;
   int phase = r.phase[q];
   int T = r.tsel[q];
   bool new_iter = phase == 0;
   if (phase != 0) {
-    // ---- verdict of the pending edge: invalid if any of its samples collides
-    bool coll = false;
-    for (int k = lane; k < r.smax; k += 32) {
-      const unsigned s = (unsigned)q * r.smax + k;
-      coll |= ((verdict_bits[s >> 5] >> (s & 31)) & 1u) != 0;
+    // ---- verdicts of the pending sub-edges: sub-edge k is invalid if any of its samples collides
+    const int ns = r.n_steps[q];
+    unsigned bad = 0;
+    for (int k = lane; k < ns * r.smax; k += 32) {
+      const unsigned s = (unsigned)q * S * r.smax + k;
+      if ((verdict_bits[s >> 5] >> (s & 31)) & 1u) bad |= 1u << (k / r.smax);
     }
-    coll = __any_sync(FULL, coll);
-    if (coll) new_iter = true;  // TRAPPED
+    bad = __reduce_or_sync(FULL, bad);
+    const int n_add = bad ? (__ffs(bad) - 1) : ns;  // valid prefix
+    if (lane == 0) r.iters[q] += n_add + (bad ? 1 : 0);
+    __syncwarp();  // the sampling counter below reads it
+    if (n_add == 0) new_iter = true;  // TRAPPED at the first step
     else {
       const int n = r.size[q * 2 + T];
-      if (n >= r.cap) {
+      if (n + n_add > r.cap) {
         if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
+        rrt_blank_edges(ea, eb, S * D, lane);
         return;
       }
       float *node = r.nodes + (((size_t)q * 2 + T) * r.cap + n) * D;
-      for (int j = lane; j < D; j += 32) node[j] = eb[j];
-      if (lane == 0) { r.parent[((size_t)q * 2 + T) * r.cap + n] = r.nearest[q]; r.size[q * 2 + T] = n + 1; }
+      for (int j = lane; j < n_add * D; j += 32) node[j] = eb[j];
+      for (int k = lane; k < n_add; k += 32) r.parent[((size_t)q * 2 + T) * r.cap + n + k] = k == 0 ? r.nearest[q] : n + k - 1;
+      if (lane == 0) r.size[q * 2 + T] = n + n_add;
+      const int n_last = n + n_add - 1;
       if (phase == 1) {  // first tree advanced: now connect the other tree to the new state
         for (int j = lane; j < D; j += 32) tg[j] = eb[j];
-        if (lane == 0) { r.added[q] = n; r.tsel[q] = 1 - T; r.phase[q] = 2; }
+        if (lane == 0) { r.added[q] = n_last; r.tsel[q] = 1 - T; r.phase[q] = 2; }
         T = 1 - T;
         phase = 2;
-      } else if (r.reach[q]) {  // REACHED: the trees meet
+      } else if (n_add == ns && r.reach[q]) {  // REACHED: the trees meet
         if (lane == 0) {
-          const int m_first = r.added[q], m_other = n;  // first tree = 1 - T
+          const int m_first = r.added[q], m_other = n_last;  // first tree = 1 - T
           int is = T == 0 ? m_other : m_first, ig = T == 0 ? m_first : m_other;
           const int ps = r.parent[((size_t)q * 2 + 0) * r.cap + is];
           if (ps >= 0) is = ps;  // one step back so the shared state is not duplicated on the path
@@ -203,8 +225,9 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
           r.status[q] = MPB_RRT_SOLVED;
           atomicSub(r.n_active, 1u);
         }
+        rrt_blank_edges(ea, eb, S * D, lane);
         return;
-      }
+      } else if (n_add < ns) new_iter = true;  // ADVANCED n_add times, then TRAPPED
       __syncwarp();
     }
   }
@@ -216,6 +239,7 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
     if ((gsz == 0 || used < gsz / 2) && used < r.n_goals[q]) {
       if (gsz >= r.cap) {
         if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
+        rrt_blank_edges(ea, eb, S * D, lane);
         return;
       }
       float *node = r.nodes + (((size_t)q * 2 + 1) * r.cap + gsz) * D;
@@ -224,14 +248,16 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
       if (lane == 0) { r.parent[((size_t)q * 2 + 1) * r.cap + gsz] = -1; r.size[q * 2 + 1] = gsz + 1; r.goals_used[q] = used + 1; }
     } else if (gsz == 0) {
       if (lane == 0) { r.status[q] = MPB_RRT_INVALID_GOAL; atomicSub(r.n_active, 1u); }
+      rrt_blank_edges(ea, eb, S * D, lane);
       return;
     }
     const unsigned ctr = (unsigned)r.iters[q];
     for (int j = lane; j < D; j += 32) tg[j] = fmaf(sp.hi[j] - sp.lo[j], rrt_uniform(r.seed, (unsigned)q, ctr, (unsigned)j), sp.lo[j]);
     if (lane == 0) { r.flag_start[q] = !fs; r.tsel[q] = T; r.phase[q] = 1; }
+    phase = 1;
     __syncwarp();
   }
-  // ---- growTree, first half: nearest neighbour in tree T and the state to add
+  // ---- growTree, first half: nearest neighbour in tree T and the state(s) to add
   const int n = r.size[q * 2 + T];
   const float *base = r.nodes + ((size_t)q * 2 + T) * r.cap * D;
   float best = FLT_MAX;
@@ -247,13 +273,22 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
     const int oi = __shfl_xor_sync(FULL, bi, o);
     if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
   }
-  const bool reach = !(best > range);
-  for (int j = lane; j < D; j += 32) {
+  // steps of length `range` along the line nearest -> target; the last one lands on the target itself
+  const int k_total = best > range ? (int)ceilf(best / range) : 1;
+  const int ns = min(phase == 2 ? S : 1, k_total);
+  const bool reach = ns == k_total;
+  for (int idx = lane; idx < S * D; idx += 32) {
+    const int k = idx / D, j = idx - k * D;
     const float a = base[(size_t)bi * D + j];
-    ea[j] = a;
-    eb[j] = reach ? tg[j] : ss_interp(a, tg[j], range / best, sp.so2[j] != 0);
+    const bool so2 = sp.so2[j] != 0;
+    // point k of the walk (k = 0: the nearest node); slots past the pending steps are blanked (NaN)
+    const float pk = k == 0 ? a : ((k == k_total) ? tg[j] : ss_interp(a, tg[j], (float)k * range / best, so2));
+    const float pk1 = (k + 1 >= k_total) ? tg[j] : ss_interp(a, tg[j], (float)(k + 1) * range / best, so2);
+    const float nanv = __int_as_float(0x7fc00000);
+    ea[idx] = k < ns ? pk : nanv;
+    eb[idx] = k < ns ? pk1 : nanv;
   }
-  if (lane == 0) { r.nearest[q] = bi; r.reach[q] = reach ? 1 : 0; r.iters[q] += 1; }
+  if (lane == 0) { r.nearest[q] = bi; r.reach[q] = reach ? 1 : 0; r.n_steps[q] = ns; }
 }
 
 // Solution path of every solved query: start chain (root first) then goal chain (towards its root).
@@ -277,4 +312,13 @@ __global__ void rrt_extract_kernel(RrtState r, float *__restrict__ paths, int *_
   for (int i = r.sol[q * 2 + 1]; i >= 0; i = p1[i], k++)
     for (int j = 0; j < D; j++) out[(size_t)k * D + j] = n1[(size_t)i * D + j];
   path_len[q] = ls + lg;
+}
+
+// [Q][max_path][D] -> packed rows: query q owns rows off[q] .. off[q+1] of `packed`
+__global__ void pack_paths_kernel(const float *__restrict__ paths, const int *__restrict__ off, int D, int max_path,
+                                  float *__restrict__ packed) {
+  const int q = blockIdx.x;
+  const int o = off[q], n = (off[q + 1] - o) * D;
+  const float *src = paths + (size_t)q * max_path * D;
+  for (int k = threadIdx.x; k < n; k += blockDim.x) packed[(size_t)o * D + k] = src[k];
 }

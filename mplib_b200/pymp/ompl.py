@@ -117,7 +117,7 @@ class OMPLPlanner:
         return status[0], paths[0]
 
     def plan_batch(self, start_states, goal_states, planner_name="RRTConnect", time=1.0, range=0.0, verbose=False,
-                   max_rounds=8192, tree_capacity=4096, max_path=2048, seed=None, check_every=16):
+                   max_rounds=8192, tree_capacity=4096, max_path=2048, seed=None, check_every=16, connect_steps=8):
         """Q independent queries.  start_states [Q, dim]; goal_states: per query a list of goal states (or an array
         [Q, dim] for one goal each).  -> (list of status strings, list of float64 paths [n_i, dim], stats)"""
         if planner_name != "RRTConnect":
@@ -155,7 +155,8 @@ class OMPLPlanner:
         dev = self.world._sync()["dev"]
         seed = int(_global_rng.randint(0, 2 ** 31 - 1)) if seed is None else int(seed)
         st, paths, stats = dev.rrtconnect(self.space, starts, goals, ng, range_=range, max_rounds=max_rounds, time_limit=time,
-                                          tree_capacity=tree_capacity, max_path=max_path, seed=seed, check_every=check_every)
+                                          tree_capacity=tree_capacity, max_path=max_path, seed=seed, check_every=check_every,
+                                          connect_steps=connect_steps)
         status, out = [], []
         for i in builtins.range(Q):  # `range` is the reference's argument name
             s = _STATUS.get(int(st[i]), "Unknown")
