@@ -56,6 +56,7 @@ struct mpb_scene {
   std::vector<float4> h_cullc;
   std::vector<int2> h_cullm;
   std::vector<int4> h_runs;
+  float4 *d_cobb = nullptr;
   float4 *d_cullc = nullptr;
   int2 *d_cullm = nullptr;
   int4 *d_runs = nullptr;
@@ -652,6 +653,26 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   }
   s->img.n_dyn = ndyn;
   s->img.n_jslots = n_jslots;
+  // cull records: [L * (oR | oc)] rows, (oh, rin), (L * ctr, joint-table slot)
+  std::vector<float4> cobb((size_t)d->n_objects * 5);
+  for (int o = 0; o < d->n_objects; o++) {
+    const DevObject &O = s->h_objs[o];
+    double Lm[12], E[12], M[12];
+    for (int k = 0; k < 12; k++) Lm[k] = O.L[k];
+    for (int r = 0; r < 3; r++) {
+      for (int c = 0; c < 3; c++) E[4 * r + c] = O.oR[3 * r + c];
+      E[4 * r + 3] = O.oc[r];
+    }
+    mul12(Lm, E, M);
+    for (int r = 0; r < 3; r++) cobb[(size_t)5 * o + r] = make_float4((float)M[4 * r], (float)M[4 * r + 1], (float)M[4 * r + 2], (float)M[4 * r + 3]);
+    cobb[(size_t)5 * o + 3] = make_float4(O.oh[0], O.oh[1], O.oh[2], O.type >= MPB_GEOM_MESH ? 0.f : O.rin);
+    float cw[3];
+    for (int r = 0; r < 3; r++) cw[r] = (float)(Lm[4 * r] * O.ctr[0] + Lm[4 * r + 1] * O.ctr[1] + Lm[4 * r + 2] * O.ctr[2] + Lm[4 * r + 3]);
+    int js = O.jslot;
+    float jsf;
+    memcpy(&jsf, &js, sizeof(float));
+    cobb[(size_t)5 * o + 4] = make_float4(cw[0], cw[1], cw[2], jsf);
+  }
 
   s->img.n_joints = d->n_joints;
   s->img.n_objects = d->n_objects;
@@ -671,6 +692,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   CU(up((void **)&s->d_joints, s->h_joints.data(), s->h_joints.size() * sizeof(DevJoint)));
   CU(up((void **)&s->d_objs, s->h_objs.data(), s->h_objs.size() * sizeof(DevObject)));
   CU(up((void **)&s->d_verts, verts.data(), verts.size() * sizeof(float4)));
+  CU(up((void **)&s->d_cobb, cobb.data(), cobb.size() * sizeof(float4)));
+  s->img.cobb = s->d_cobb;
   std::vector<float> linkL((size_t)d->n_links * 12);
   for (size_t k = 0; k < linkL.size(); k++) linkL[k] = (float)d->link_placement[k];
   CU(up((void **)&s->d_linkL, linkL.data(), linkL.size() * sizeof(float)));
@@ -717,7 +740,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_cobb, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &b : s->pool) cudaFree(b.first);
@@ -850,7 +873,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)std::min<long long>((mm + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
-      fk_cull_kernel<64, 0><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq + off * D, mm, off, s->wq);
+      fk_cull_kernel<64, 0><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq + off * D, mm, off, s->wq, dv, dp);
       *launches += 1;
     }
   }
@@ -1442,7 +1465,7 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     CU(cudaEventRecord(e0, st));
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)std::min<long long>((m + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
-      fk_cull_kernel<64, 1><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, 0, s->wq);
+      fk_cull_kernel<64, 1><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, 0, s->wq, nullptr, nullptr);
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, (unsigned)dblocks * 8u);
       scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));

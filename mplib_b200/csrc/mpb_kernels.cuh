@@ -35,6 +35,7 @@ struct SceneImg {
   const int *dynlist;   // moving objects grouped by owner joint
   const DevBvhNode *nodes;  // BVH node pool (meshes, octrees); DevObject::voff = root, ::vcnt = leaf type
   const float4 *prims;      // leaf primitives, 3 float4 each
+  const float4 *cobb;       // [n_objects][5] cull records (see fk_cull_kernel phase 3)
   const float4 *cullc;      // [n_pairs] cull table: world-fixed partner's sphere centre (xyz), (R1 + R2 + margin)^2 (w)
   const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}
   const int4 *runs;         // cull-table runs: {moving slot or -1, first entry, count, partner kind (0 fixed, 1 moving)}
@@ -91,6 +92,13 @@ __device__ __forceinline__ Xf joint_motion(const DevJoint &J, float q) {
   return m;
 }
 
+__device__ __forceinline__ Xf xf_rows(float4 a, float4 b, float4 c) {
+  Xf o;
+  o.r[0] = a.x; o.r[1] = a.y; o.r[2] = a.z; o.p[0] = a.w;
+  o.r[3] = b.x; o.r[4] = b.y; o.r[5] = b.z; o.p[1] = b.w;
+  o.r[6] = c.x; o.r[7] = c.y; o.r[8] = c.z; o.p[2] = c.w;
+  return o;
+}
 __device__ __forceinline__ Xf load_xf12(const float *p) {
   Xf o;
   const float4 *p4 = reinterpret_cast<const float4 *>(p);
@@ -212,7 +220,8 @@ __device__ __forceinline__ Xf smem_joint(const float *sJ, int js, int t) {
 //   lower bound |c| - R does not exceed the smallest upper bound |c| + R over all admitted pairs of the
 //   configuration; candidates skip the SAT (overlap is not the question) and go to the GJK distance kernel.
 template <int BLOCK, int MODE>
-__global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, long long cfg_base, WorkQ wq) {
+__global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, long long cfg_base, WorkQ wq,
+                                                        unsigned int *__restrict__ verdict_bits, unsigned int *__restrict__ pair_bits) {
   extern __shared__ __align__(16) float smem_f[];
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned FULL = 0xffffffffu;
@@ -332,30 +341,47 @@ __global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const floa
           owner = ent & 31;
           p = __ldg(&img.cullm[ent >> 5].x);
           const DevPair pr = img.pairs[p];
-          const DevObject &A = img.objs[pr.a];
-          const DevObject &B = img.objs[pr.b];
-          const Xf Wa = A.jslot >= 0 ? xf_mul(smem_joint(sJ, A.jslot, owner), load_xf12(A.L)) : load_xf12(A.L);
-          const Xf Wb = B.jslot >= 0 ? xf_mul(smem_joint(sJ, B.jslot, owner), load_xf12(B.L)) : load_xf12(B.L);
-          rel = xf_inv_mul(Wa, Wb);
+          // cull records: OBB frame [axes | centre] (world frame if the object is fixed, owner-joint frame if it moves),
+          // half extents + inscribed radius, inscribed-ball centre + joint-table slot: five 16-byte loads per object
+          const float4 *ca = img.cobb + 5 * pr.a, *cb = img.cobb + 5 * pr.b;
+          Xf Ea = xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2)), Eb = xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
+          const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
+          const int jsa = __float_as_int(ia.w), jsb = __float_as_int(ib.w);
+          const float ia3[3] = {ia.x, ia.y, ia.z}, ib3[3] = {ib.x, ib.y, ib.z};
+          float ica[3] = {ia.x, ia.y, ia.z}, icb[3] = {ib.x, ib.y, ib.z};
+          Xf Ja, Jb;
+          if (jsa >= 0) { Ja = smem_joint(sJ, jsa, owner); Ea = xf_mul(Ja, Ea); xf_point(Ja, ia3, ica); }
+          if (jsb >= 0) { Jb = smem_joint(sJ, jsb, owner); Eb = xf_mul(Jb, Eb); xf_point(Jb, ib3, icb); }
           keep = true;
           if (MODE == 0) {
-            // box B in box A's frame:  Ra^T (rel.R Rb),  Ra^T (rel*ocB - ocA)
-            float M[9], R[9], cbA[3], t[3];
+            // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)
+            float R[9], t[3];
+            const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
 #pragma unroll
-            for (int rr = 0; rr < 3; rr++)
+            for (int rr = 0; rr < 3; rr++) {
 #pragma unroll
-              for (int c = 0; c < 3; c++)
-                M[3 * rr + c] = fmaf(rel.r[3 * rr], B.oR[c], fmaf(rel.r[3 * rr + 1], B.oR[3 + c], rel.r[3 * rr + 2] * B.oR[6 + c]));
-#pragma unroll
-            for (int rr = 0; rr < 3; rr++)
-#pragma unroll
-              for (int c = 0; c < 3; c++)
-                R[3 * rr + c] = fmaf(A.oR[rr], M[c], fmaf(A.oR[3 + rr], M[3 + c], A.oR[6 + rr] * M[6 + c]));
-            xf_point(rel, B.oc, cbA);
-            const float d0 = cbA[0] - A.oc[0], d1 = cbA[1] - A.oc[1], d2 = cbA[2] - A.oc[2];
-#pragma unroll
-            for (int rr = 0; rr < 3; rr++) t[rr] = fmaf(A.oR[rr], d0, fmaf(A.oR[3 + rr], d1, A.oR[6 + rr] * d2));
-            keep = !obb_disjoint(R, t, A.oh, B.oh);
+              for (int c = 0; c < 3; c++) R[3 * rr + c] = fmaf(Ea.r[rr], Eb.r[c], fmaf(Ea.r[3 + rr], Eb.r[3 + c], Ea.r[6 + rr] * Eb.r[6 + c]));
+              t[rr] = fmaf(Ea.r[rr], d0, fmaf(Ea.r[3 + rr], d1, Ea.r[6 + rr] * d2));
+            }
+            const float ah[3] = {ha.x, ha.y, ha.z}, bh[3] = {hb.x, hb.y, hb.z};
+            keep = !obb_disjoint(R, t, ah, bh);
+            if (keep && ha.w > 0.f && hb.w > 0.f) {
+              // sufficient test: balls inscribed in the two shapes overlap -> the pair collides, no narrowphase needed
+              const float e0 = ica[0] - icb[0], e1 = ica[1] - icb[1], e2 = ica[2] - icb[2];
+              const float rs = 0.999f * (ha.w + hb.w);
+              if (fmaf(e0, e0, fmaf(e1, e1, e2 * e2)) < rs * rs) {
+                keep = false;
+                const long long cfg = cfg_base + tile * 32 + owner;
+                atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
+                if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
+              }
+            }
+          }
+          if (keep) {  // relative pose of the two OBJECT frames for the narrowphase
+            const Xf La = load_xf12(img.objs[pr.a].L), Lb = load_xf12(img.objs[pr.b].L);
+            const Xf Wa = jsa >= 0 ? xf_mul(Ja, La) : La;
+            const Xf Wb = jsb >= 0 ? xf_mul(Jb, Lb) : Lb;
+            rel = xf_inv_mul(Wa, Wb);
           }
         }
         const unsigned km = __ballot_sync(FULL, keep);
