@@ -318,7 +318,7 @@ def main():
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "pairs_after_cull": 0, "narrow_iterations": 0, "narrow_capped": 0,
+    agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "pairs_after_cull": 0, "pairs_after_spheres": 0, "narrow_iterations": 0, "narrow_capped": 0,
            "kernel_launches": 0}
     e0.record(stream)
     for k in range(args.steps):
@@ -388,7 +388,7 @@ def main():
                 "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
                         "bytes_per_check": B_alg, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
             },
-            "stats_per_step": {"pairs_after_cull": agg["pairs_after_cull"] / K, "support_evals": iters_per_step,
+            "stats_per_step": {"pairs_after_spheres": agg["pairs_after_spheres"] / K, "pairs_after_cull": agg["pairs_after_cull"] / K, "support_evals": iters_per_step,
                                "capped": agg["narrow_capped"] / K},
         }
         if not args.no_cpu_baseline and world == 1:

@@ -113,6 +113,7 @@ typedef struct mpb_stats {
   int64_t n_states;
   int64_t pairs_admitted;    /* n_states * n_pairs                                   */
   int64_t pairs_after_cull;  /* items that reached an exact narrowphase              */
+  int64_t pairs_after_spheres; /* survivor-queue slots after the bounding-sphere phase (incl. chunk padding) */
   int64_t narrow_iterations; /* support-mapping evaluations (MPR/GJK iterations)     */
   int64_t narrow_capped;     /* items that hit the iteration cap (reported, not hidden) */
   int64_t kernel_launches;   /* kernels launched by this call                        */

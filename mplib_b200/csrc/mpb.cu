@@ -62,9 +62,10 @@ struct mpb_scene {
   int4 *d_runs = nullptr;
   size_t cull_cap = 0;
   SceneImg img{};
-  int cull_block = 128;
-  size_t cull_smem = 0;
-  int cull_blocks_per_sm = 1;
+  float *d_pose = nullptr;   // pose table [n_jslots * 12 + n_dyn * 3][pose_ld]
+  size_t pose_ld = 0;
+  uint2 *d_sq = nullptr;     // survivor queue of the sphere phase: (configuration, cull-table entry)
+  unsigned sq_cap = 0;
   size_t pairs_cap = 0;
   // work buffers
   long long chunk = 0;
@@ -636,8 +637,6 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   }
   // joint-table slots: joints that own moving objects, and parents of non-adjacent children (branch points)
   int n_jslots = 0;
-  for (int j = 0; j < d->n_joints; j++)
-    if (s->h_joints[j].dyn_count > 0) s->h_joints[j].jslot = n_jslots++;
   for (int j = 0; j < d->n_joints; j++) {
     const int par = s->h_joints[j].parent;  // model index; the previous joint has model index j
     if (par == 0 || par == j) continue;
@@ -653,25 +652,33 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   }
   s->img.n_dyn = ndyn;
   s->img.n_jslots = n_jslots;
-  // cull records: [L * (oR | oc)] rows, (oh, rin), (L * ctr, joint-table slot)
-  std::vector<float4> cobb((size_t)d->n_objects * 5);
+  s->img.w_sphere = ndyn * 12;
+  s->img.w_joint = ndyn * 15;
+  // cull records (MPB_COBB_WORDS float4 per object), see dense_kernel
+  std::vector<float4> cobb((size_t)d->n_objects * MPB_COBB_WORDS);
   for (int o = 0; o < d->n_objects; o++) {
     const DevObject &O = s->h_objs[o];
-    double Lm[12], E[12], M[12];
+    double Lm[12], E[12], Ei[12], M[12];
     for (int k = 0; k < 12; k++) Lm[k] = O.L[k];
     for (int r = 0; r < 3; r++) {
-      for (int c = 0; c < 3; c++) E[4 * r + c] = O.oR[3 * r + c];
+      for (int c = 0; c < 3; c++) { E[4 * r + c] = O.oR[3 * r + c]; Ei[4 * r + c] = O.oR[3 * c + r]; }
       E[4 * r + 3] = O.oc[r];
     }
+    for (int r = 0; r < 3; r++) Ei[4 * r + 3] = -(Ei[4 * r] * O.oc[0] + Ei[4 * r + 1] * O.oc[1] + Ei[4 * r + 2] * O.oc[2]);
     mul12(Lm, E, M);
-    for (int r = 0; r < 3; r++) cobb[(size_t)5 * o + r] = make_float4((float)M[4 * r], (float)M[4 * r + 1], (float)M[4 * r + 2], (float)M[4 * r + 3]);
-    cobb[(size_t)5 * o + 3] = make_float4(O.oh[0], O.oh[1], O.oh[2], O.type >= MPB_GEOM_MESH ? 0.f : O.rin);
-    float cw[3];
-    for (int r = 0; r < 3; r++) cw[r] = (float)(Lm[4 * r] * O.ctr[0] + Lm[4 * r + 1] * O.ctr[1] + Lm[4 * r + 2] * O.ctr[2] + Lm[4 * r + 3]);
-    int js = O.jslot;
-    float jsf;
-    memcpy(&jsf, &js, sizeof(float));
-    cobb[(size_t)5 * o + 4] = make_float4(cw[0], cw[1], cw[2], jsf);
+    float4 *rec = cobb.data() + (size_t)MPB_COBB_WORDS * o;
+    for (int r = 0; r < 3; r++) {
+      rec[r] = make_float4((float)M[4 * r], (float)M[4 * r + 1], (float)M[4 * r + 2], (float)M[4 * r + 3]);
+      rec[5 + r] = make_float4((float)E[4 * r], (float)E[4 * r + 1], (float)E[4 * r + 2], (float)E[4 * r + 3]);
+      rec[8 + r] = make_float4((float)Ei[4 * r], (float)Ei[4 * r + 1], (float)Ei[4 * r + 2], (float)Ei[4 * r + 3]);
+    }
+    rec[3] = make_float4(O.oh[0], O.oh[1], O.oh[2], O.type >= MPB_GEOM_MESH ? 0.f : O.rin);
+    float co[3];  // inscribed-ball centre in the OBB frame
+    for (int r = 0; r < 3; r++) co[r] = (float)(Ei[4 * r] * O.ctr[0] + Ei[4 * r + 1] * O.ctr[1] + Ei[4 * r + 2] * O.ctr[2] + Ei[4 * r + 3]);
+    int dyn = O.dyn;
+    float df;
+    memcpy(&df, &dyn, sizeof(float));
+    rec[4] = make_float4(co[0], co[1], co[2], df);
   }
 
   s->img.n_joints = d->n_joints;
@@ -723,14 +730,6 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<false>, 256, 0));
   }
   s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
-  // FK + cull launch shape: moving-object poses in shared memory, [object][15 words][thread]
-  s->cull_block = 64;
-  s->cull_smem = (((size_t)n_jslots * 12 + (size_t)ndyn * 3) * 32 + MPB_CULL_QCAP) * sizeof(float) * (s->cull_block / 32);
-  if (s->cull_smem > 227 * 1024) { mpb_scene_destroy(s); return fail(MPB_ERR_CAPACITY, "too many moving joints / objects for the shared-memory pose table"); }
-  CU(cudaFuncSetAttribute(fk_cull_kernel<64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
-  CU(cudaFuncSetAttribute(fk_cull_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->cull_smem));
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->cull_blocks_per_sm, fk_cull_kernel<64, 0>, s->cull_block, s->cull_smem));
-  s->cull_blocks_per_sm = std::max(s->cull_blocks_per_sm, 1);
   *out = s;
   return MPB_OK;
 }
@@ -740,7 +739,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_cobb, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &b : s->pool) cudaFree(b.first);
@@ -797,14 +796,25 @@ static cudaError_t ensure(T **p, size_t *cap, size_t need) {
 
 static const long long kMaxChunk = 1ll << 20;       // configurations per pass
 static const size_t kMaxItems = (size_t)48 << 20;   // work-queue capacity bound (x56 B = 2.6 GiB)
+static const size_t kMaxSurvivors = (size_t)192 << 20;  // survivor-queue capacity bound (x8 B = 1.5 GiB)
 
 static int prepare_work(mpb_scene *s, long long chunk) {
   if (s->chunk == chunk && s->wq.itf) return MPB_OK;
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
   // staging may hold up to one unused half-chunk per reservation: worst case 2 x items + one chunk per warp
-  size_t cap = std::min((size_t)chunk * P * 2 + (size_t)(chunk / 32 + 1) * 64, kMaxItems);
+  // plus one partly used reservation per warp of dense_kernel / expand_kernel
+  size_t cap = std::min((size_t)chunk * P * 2 + (size_t)s->num_sms * 8 * 4 * MPB_STAGE_CHUNK, kMaxItems);
   cap = std::max<size_t>(cap, 4096);
   if (s->wq.stf) { cudaFree(s->wq.stf); s->wq.stf = nullptr; s->wq.itf = nullptr; }
+  if (s->d_pose) { cudaFree(s->d_pose); s->d_pose = nullptr; }
+  if (s->d_sq) { cudaFree(s->d_sq); s->d_sq = nullptr; }
+  s->pose_ld = (size_t)(chunk + 31) / 32 * 32;
+  const size_t pose_words = (size_t)s->img.n_jslots * 12 + (size_t)s->img.n_dyn * 15;
+  CU(cudaMalloc((void **)&s->d_pose, std::max<size_t>(pose_words * s->pose_ld, 4) * sizeof(float)));
+  // survivors of the sphere phase: every admitted pair of every configuration at worst, bounded like the work queue
+  const size_t sq_cap = std::max<size_t>(std::min((size_t)chunk * P + (size_t)s->num_sms * 64 * MPB_SQ_CHUNK, kMaxSurvivors), 4096);
+  CU(cudaMalloc((void **)&s->d_sq, sq_cap * sizeof(uint2)));
+  s->sq_cap = (unsigned)sq_cap;
   // one slab: staging [12 f + cfg + pair][cap], then binned [12 f + cfg + pair][cap]
   CU(cudaMalloc((void **)&s->wq.stf, cap * 30 * sizeof(float)));
   s->wq.scfg = reinterpret_cast<int *>(s->wq.stf + cap * 12);
@@ -859,6 +869,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
   CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
   CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
+  CU(cudaMemsetAsync(s->wq.totals + 6, 0, sizeof(unsigned), st));
   cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;  // ev == nullptr: no timing events (graph capture)
   if (ev) { e0 = get_event(s, (*ev)++); e1 = get_event(s, (*ev)++); e2 = get_event(s, (*ev)++); }
   if (ev) CU(cudaEventRecord(e0, st));
@@ -872,16 +883,20 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       CU(cudaStreamWaitEvent(st, landed, 0));
     }
     if (s->img.n_pairs > 0) {
-      const int cblocks = (int)std::min<long long>((mm + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
-      fk_cull_kernel<64, 0><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq + off * D, mm, off, s->wq, dv, dp);
-      *launches += 1;
+      const int cblocks = (int)((mm + 127) / 128);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld);
+      const int sblocks = std::min(cblocks, s->num_sms * 16);  // persistent warps: survivor-queue chunks carry over between tiles
+      sphere_kernel<0><<<sblocks, 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
+      *launches += 2;
     }
   }
   if (s->img.n_pairs == 0) return MPB_OK;
+  dense_kernel<0><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
+  *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
-  scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, n_warps);
-  scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
+  scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, n_warps, s->sq_cap);
+  scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
   if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
@@ -891,8 +906,8 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
     CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
     expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
-    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, n_warps);
-    scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 1);
+    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, n_warps, s->sq_cap);
+    scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1);
     if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
     *launches += 4;
@@ -970,6 +985,7 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
     stats->n_states = n;
     stats->pairs_admitted = n * (long long)s->img.n_pairs;
     stats->pairs_after_cull = (long long)counters[0];
+    stats->pairs_after_spheres = (long long)counters[3];
     stats->narrow_iterations = (long long)counters[1];
     stats->narrow_capped = (long long)counters[2];
     stats->kernel_launches = launches;
@@ -1464,10 +1480,12 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     cudaEvent_t e0 = get_event(s, 0), e1 = get_event(s, 1), e2 = get_event(s, 2);
     CU(cudaEventRecord(e0, st));
     if (s->img.n_pairs > 0) {
-      const int cblocks = (int)std::min<long long>((m + 63) / 64, (long long)s->num_sms * s->cull_blocks_per_sm);
-      fk_cull_kernel<64, 1><<<cblocks, 64, s->cull_smem, st>>>(s->img, dq, m, 0, s->wq, nullptr, nullptr);
-      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, (unsigned)dblocks * 8u);
-      scatter_kernel<<<s->num_sms * 4, 256, 0, st>>>(s->img, s->wq, 0);
+      const int cblocks = (int)((m + 127) / 128);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq, m, s->d_pose, s->pose_ld);
+      sphere_kernel<1><<<std::min(cblocks, s->num_sms * 16), 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
+      dense_kernel<1><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
+      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, (unsigned)dblocks * 8u, s->sq_cap);
+      scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));
       if (s->smem_verts) distance_kernel<true><<<dblocks, 256, vsm, st>>>(s->img, s->wq, dbest, s->img.n_bins);
       else distance_kernel<false><<<dblocks, 256, 0, st>>>(s->img, s->wq, dbest, s->img.n_bins);

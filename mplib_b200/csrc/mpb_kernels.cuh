@@ -45,6 +45,7 @@ struct SceneImg {
   const float *linkL;   // [n_links][12] link placement in its joint frame
   const int *linkJoint; // [n_links]
   int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn, n_jslots;
+  int w_sphere, w_joint;  // pose-table word offsets: [n_dyn][12] OBB frames, then [n_dyn][3] sphere centres, then [n_jslots][12] branch joints
 };
 
 struct WorkQ {
@@ -66,7 +67,8 @@ struct WorkQ {
 #define MPB_MPR_MAX_ITERS 96
 #define MPB_UNIT_ITEMS 128   // most items a warp owns at a time in the narrowphase (scan_bins_kernel picks 2..128)
 #define MPB_COOP_MAX 10      // busy lanes at or below which a warp evaluates hull supports cooperatively
-#define MPB_STAGE_CHUNK 64   // staging slots a warp reserves per atomic (>= 32)
+#define MPB_STAGE_CHUNK 256  // staging slots a warp reserves per atomic (>= 32)
+#define MPB_SMEM_BINS 1024    // bins a block can count in shared memory (more: global atomics)
 
 // ---------------------------------------------------------------------------------------------- FK
 __device__ __forceinline__ Xf xf_identity() {
@@ -189,250 +191,278 @@ __device__ __forceinline__ Xf joint_step(const DevJoint &J, const Xf *parent, fl
   return a;
 }
 
-// Per-WARP shared-memory tables, transposed [slot][word][lane] so that every access of the FK / sphere phases is
-// conflict-free: sJ = world transforms of the kept joints (12 words), sC = bounding-sphere centres (3 words), sQ =
-// the warp's private survivor queue.  A warp owns a tile of 32 configurations from FK to the staging queue; nothing
-// in this kernel needs a block-level barrier.
-#define MPB_CULL_GROUP 16   // cull-table entries tested between two queue pushes
-#define MPB_CULL_DRAIN 64   // queue length at which the warp runs the dense OBB phase
-#define MPB_CULL_QCAP (MPB_CULL_GROUP * 32 + MPB_CULL_DRAIN)
-#define SMJ(js, k, t) sJ[((js) * 12 + (k)) * 32 + (t)]
-#define SMC(d, k, t) sC[((d) * 3 + (k)) * 32 + (t)]
+// ---------------------------------------------------------------------------------------------- FK + cull, three kernels
+// The pose table lives in HBM, word-major [word][configuration]: 12 words per moving object (world pose of its OBB
+// frame), 3 words per moving object's bounding-sphere centre, 12 words per branch-point joint (a parent that a later,
+// non-adjacent child needs).  ~700 B per Panda configuration is cheap at HBM3e rates (a million configurations per
+// 0.2 ms, read + write) and it frees the kernels from a shared-memory pose table that capped them at ten warps per
+// SM: all three kernels below are register-only and run at full occupancy.
+//   fk_table_kernel   thread per configuration: FK down the forest; OBB frames + sphere centres -> pose table
+//   sphere_kernel     thread per configuration over the CULL TABLE: the admitted pairs re-ordered into runs that share
+//                     their moving object (its centre stays in registers) and whose partner is either world-fixed
+//                     (centre and squared radius sum in one float4, a uniform 16-byte load) or another moving object;
+//                     survivors (configuration, entry) go to the survivor queue through warp-private chunks
+//   dense_kernel      thread per survivor: 15-axis OBB SAT straight from the two OBB frames (pose table for moving
+//                     objects, cull record for fixed ones), inscribed-ball sufficient test, relative pose of what is
+//                     left -> staging queue
+// MODE 0 (collide): as above.  MODE 1 (distance): a pair is a candidate for the minimum iff its bounding-sphere lower
+// bound |c| - R does not exceed the smallest upper bound |c| + R over all admitted pairs of the configuration;
+// candidates skip the SAT (overlap is not the question) and go to the GJK distance kernel.
+#define MPB_SQ_CHUNK 128  // survivor-queue slots a warp reserves per atomic
+#define POSE(w, i) pose[(size_t)(w) * ld + (i)]
 
-__device__ __forceinline__ Xf smem_joint(const float *sJ, int js, int t) {
+#define MPB_COBB_WORDS 11  // float4 per object in the cull records
+// 12 consecutive words of the pose table, starting at word w0, of configuration i
+__device__ __forceinline__ Xf pose_joint(const float *__restrict__ pose, size_t ld, int w0, long long i) {
   Xf w;
 #pragma unroll
-  for (int k = 0; k < 9; k++) w.r[k] = SMJ(js, k, t);
+  for (int k = 0; k < 9; k++) w.r[k] = POSE(w0 + k, i);
 #pragma unroll
-  for (int k = 0; k < 3; k++) w.p[k] = SMJ(js, 9 + k, t);
+  for (int k = 0; k < 3; k++) w.p[k] = POSE(w0 + 9 + k, i);
   return w;
 }
 
-// Phases per tile of 32 configurations (one warp):
-//   1. FK, lane per configuration: joint transforms -> sJ, bounding-sphere centres of the moving objects -> sC
-//   2. bounding spheres, lane per configuration, over the CULL TABLE: the admitted pairs re-ordered into runs that
-//      share their moving object (its centre stays in registers) and whose partner is either world-fixed (centre and
-//      squared radius sum in one float4, a uniform 16-byte load) or another moving object (centre from sC);
-//      survivors of MPB_CULL_GROUP entries are pushed to the warp queue
-//   3. dense, lane per queued (configuration, pair): 15-axis OBB SAT with the owner's joint transforms read from sJ;
-//      what is left is ballot-compacted into the global staging queue (one atomic per warp chunk)
-//   MODE 0 (collide): as above.  MODE 1 (distance): a pair is a candidate for the minimum iff its bounding-sphere
-//   lower bound |c| - R does not exceed the smallest upper bound |c| + R over all admitted pairs of the
-//   configuration; candidates skip the SAT (overlap is not the question) and go to the GJK distance kernel.
-template <int BLOCK, int MODE>
-__global__ void __launch_bounds__(BLOCK) fk_cull_kernel(SceneImg img, const float *__restrict__ q, long long n, long long cfg_base, WorkQ wq,
-                                                        unsigned int *__restrict__ verdict_bits, unsigned int *__restrict__ pair_bits) {
-  extern __shared__ __align__(16) float smem_f[];
-  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int cbase = img.w_sphere, jbase = img.w_joint;
+  Xf cur = xf_identity();
+  const float *qrow = q + i * img.state_dim;
+  for (int j = 0; j < img.n_joints; j++) {
+    const DevJoint &J = img.joints[j];
+    const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
+    if (J.parent == 0) cur = joint_step(J, nullptr, qj);
+    else if (J.pjslot >= 0) { const Xf par = pose_joint(pose, ld, jbase + J.pjslot * 12, i); cur = joint_step(J, &par, qj); }
+    else cur = joint_step(J, &cur, qj);
+    if (J.jslot >= 0) {
+#pragma unroll
+      for (int k = 0; k < 9; k++) POSE(jbase + J.jslot * 12 + k, i) = cur.r[k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) POSE(jbase + J.jslot * 12 + 9 + k, i) = cur.p[k];
+    }
+    for (int e = 0; e < J.dyn_count; e++) {
+      const int o = img.dynlist[J.dyn_first + e];
+      const DevObject &O = img.objs[o];
+      float c[3];
+      xf_point(cur, O.bcj, c);  // bounding-sphere centre in the joint frame -> world
+#pragma unroll
+      for (int k = 0; k < 3; k++) POSE(cbase + O.dyn * 3 + k, i) = c[k];
+      const float4 *rec = img.cobb + MPB_COBB_WORDS * o;  // OBB frame in the joint frame -> world
+      const Xf E = xf_mul(cur, xf_rows(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2)));
+#pragma unroll
+      for (int k = 0; k < 9; k++) POSE(O.dyn * 12 + k, i) = E.r[k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) POSE(O.dyn * 12 + 9 + k, i) = E.p[k];
+    }
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) sphere_kernel(SceneImg img, const float *__restrict__ pose, size_t ld, long long n, long long cfg_base,
+                                                     uint2 *__restrict__ sq, unsigned sq_cap, unsigned *__restrict__ totals) {
   const unsigned FULL = 0xffffffffu;
-  const size_t warp_words = ((size_t)img.n_jslots * 12 + (size_t)img.n_dyn * 3) * 32 + MPB_CULL_QCAP;
-  float *sJ = smem_f + warp * warp_words;
-  float *sC = sJ + (size_t)img.n_jslots * 12 * 32;
-  unsigned *sQ = reinterpret_cast<unsigned *>(sC + (size_t)img.n_dyn * 3 * 32);
-  unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
+  const unsigned lane = threadIdx.x & 31;
+  const int cbase = img.w_sphere;
+  unsigned wbase = 0, wused = 0, wcap = 0;  // warp-uniform survivor-queue chunk, kept across the warp's tiles
   const long long n_tiles = (n + 31) / 32;
-  const long long warp_stride = (long long)gridDim.x * (BLOCK / 32);
-  for (long long tile = (long long)blockIdx.x * (BLOCK / 32) + warp; tile < n_tiles; tile += warp_stride) {
-    const long long i = tile * 32 + lane;
-    const bool valid = i < n;
-    // ---- 1. FK, running transform in registers
-    if (valid) {
-      Xf cur = xf_identity();
-      const float *qrow = q + i * img.state_dim;
-      for (int j = 0; j < img.n_joints; j++) {
-        const DevJoint &J = img.joints[j];
-        const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
-        if (J.parent == 0) cur = joint_step(J, nullptr, qj);
-        else if (J.pjslot >= 0) { const Xf par = smem_joint(sJ, J.pjslot, lane); cur = joint_step(J, &par, qj); }
-        else cur = joint_step(J, &cur, qj);
-        if (J.jslot >= 0) {
-#pragma unroll
-          for (int k = 0; k < 9; k++) SMJ(J.jslot, k, lane) = cur.r[k];
-#pragma unroll
-          for (int k = 0; k < 3; k++) SMJ(J.jslot, 9 + k, lane) = cur.p[k];
+  const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long tile = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < n_tiles; tile += warp_stride) {
+  const long long i = tile * 32 + lane;  // whole warps run; lanes past n push nothing
+  const bool valid = i < n;
+  const long long ic = valid ? i : n - 1;
+  float ub_min = FLT_MAX;
+  if (MODE == 1) {
+    for (int k = 0; k < img.n_pairs; k++) {
+      const float4 c = __ldg(img.cullc + k);
+      const int mm = __ldg(&img.cullm[k].y);
+      const int m1 = mm & 0xffff, m2 = mm >> 16;  // biased by one; 0 = none
+      float ax = 0.f, ay = 0.f, az = 0.f, bx = c.x, by = c.y, bz = c.z;
+      if (m1) { ax = POSE(cbase + (m1 - 1) * 3, ic); ay = POSE(cbase + (m1 - 1) * 3 + 1, ic); az = POSE(cbase + (m1 - 1) * 3 + 2, ic); }
+      if (m2) { bx = POSE(cbase + (m2 - 1) * 3, ic); by = POSE(cbase + (m2 - 1) * 3 + 1, ic); bz = POSE(cbase + (m2 - 1) * 3 + 2, ic); }
+      const float dx = ax - bx, dy = ay - by, dz = az - bz;
+      ub_min = fminf(ub_min, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + sqrtf(c.w));
+    }
+    ub_min *= 1.000001f;
+  }
+  int r = 0;  // run cursor
+  for (int gbase = 0; gbase < img.n_pairs; gbase += 32) {
+    const int gend = min(gbase + 32, img.n_pairs);
+    unsigned mask = 0;
+    int k = gbase;
+    while (k < gend) {
+      const int4 run = __ldg(img.runs + r);  // {moving slot or -1, first, count, partner kind}
+      const int rlast = run.y + run.z;
+      const int rend = min(rlast, gend);
+      float ax = 0.f, ay = 0.f, az = 0.f;
+      if (run.x >= 0) { ax = POSE(cbase + run.x * 3, ic); ay = POSE(cbase + run.x * 3 + 1, ic); az = POSE(cbase + run.x * 3 + 2, ic); }
+      if (run.w == 0) {  // world-fixed partners: centre + (R1 + R2)^2 in one uniform 16-byte load
+#pragma unroll 8
+        for (; k < rend; k++) {
+          const float4 c = __ldg(img.cullc + k);
+          const float dx = ax - c.x, dy = ay - c.y, dz = az - c.z;
+          const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+          const bool s = MODE == 0 ? (d2c <= c.w) : (sqrtf(d2c) - sqrtf(c.w) <= ub_min);
+          mask |= (unsigned)s << (k - gbase);
         }
-        for (int e = 0; e < J.dyn_count; e++) {
-          const DevObject &O = img.objs[img.dynlist[J.dyn_first + e]];
-          float c[3];
-          xf_point(cur, O.bcj, c);  // bounding-sphere centre in the joint frame -> world
-#pragma unroll
-          for (int k = 0; k < 3; k++) SMC(O.dyn, k, lane) = c[k];
+      } else {  // moving partners
+        for (; k < rend; k++) {
+          const float rr2 = __ldg(&img.cullc[k].w);
+          const int m2 = (__ldg(&img.cullm[k].y) >> 16) - 1;
+          const float dx = ax - POSE(cbase + m2 * 3, ic), dy = ay - POSE(cbase + m2 * 3 + 1, ic), dz = az - POSE(cbase + m2 * 3 + 2, ic);
+          const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+          const bool s = MODE == 0 ? (d2c <= rr2) : (sqrtf(d2c) - sqrtf(rr2) <= ub_min);
+          mask |= (unsigned)s << (k - gbase);
         }
+      }
+      if (rend == rlast) r++;
+    }
+    if (!valid) mask = 0;
+    if (!__any_sync(FULL, mask != 0)) continue;
+    // push (configuration, entry) survivors: warp prefix sum into the warp's chunk of the survivor queue
+    const unsigned c = __popc(mask);
+    unsigned incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(FULL, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    const unsigned wtot = __shfl_sync(FULL, incl, 31);
+    if (wused + wtot > wcap) {
+      for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+        if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);  // unused tail of the old chunk
+      const unsigned want = max((unsigned)MPB_SQ_CHUNK, wtot);
+      unsigned nb = 0;
+      if (lane == 0) nb = atomicAdd(&totals[6], want);
+      wbase = __shfl_sync(FULL, nb, 0);
+      wused = 0;
+      wcap = want;
+    }
+    unsigned pos = wbase + wused + incl - c;
+    const unsigned cfg = (unsigned)(cfg_base + i);
+    while (mask) {
+      const int kk = __ffs(mask) - 1;
+      mask &= mask - 1;
+      if (pos < sq_cap) sq[pos] = make_uint2(cfg, (unsigned)(gbase + kk));
+      pos++;
+    }
+    wused += wtot;
+  }
+  }  // tiles
+  for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+    if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float *__restrict__ pose, size_t ld, const uint2 *__restrict__ sq,
+                                                    unsigned sq_cap, WorkQ wq, unsigned int *__restrict__ verdict_bits,
+                                                    unsigned int *__restrict__ pair_bits) {
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31;
+  __shared__ unsigned s_bins[MPB_SMEM_BINS];  // per-block bin counts, flushed once at the end
+  const bool smem_bins = img.n_bins <= MPB_SMEM_BINS;
+  for (int b = threadIdx.x; b < MPB_SMEM_BINS; b += blockDim.x) s_bins[b] = 0;
+  __syncthreads();
+  unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
+  const unsigned total = min(wq.totals[6], sq_cap);
+  const unsigned total_r = (total + 31u) & ~31u;
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&wq.counters[3], (unsigned long long)total);  // incl. chunk padding
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < total_r; e += gridDim.x * blockDim.x) {
+    bool keep = false;
+    Xf rel;
+    int p = 0;
+    unsigned cfg = 0;
+    uint2 ent = make_uint2(0xffffffffu, 0u);
+    if (e < total) ent = sq[e];
+    if (ent.x != 0xffffffffu) {
+      cfg = ent.x;
+      p = __ldg(&img.cullm[ent.y].x);
+      const DevPair pr = img.pairs[p];
+      // cull records (MPB_COBB_WORDS float4 per object): [0..2] OBB frame (world frame if the object is fixed,
+      // owner-joint frame if it moves), [3] half extents + inscribed radius, [4] inscribed-ball centre in the OBB frame
+      // + moving slot, [5..7] OBB frame in the object frame, [8..10] its inverse
+      const float4 *ca = img.cobb + MPB_COBB_WORDS * pr.a, *cb = img.cobb + MPB_COBB_WORDS * pr.b;
+      const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
+      const int da = __float_as_int(ia.w), db = __float_as_int(ib.w);
+      const Xf Ea = da >= 0 ? pose_joint(pose, ld, da * 12, cfg) : xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2));
+      const Xf Eb = db >= 0 ? pose_joint(pose, ld, db * 12, cfg) : xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
+      // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)  ==  (OBB frame A)^-1 (OBB frame B)
+      Xf Rt;
+      const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
+#pragma unroll
+      for (int rr = 0; rr < 3; rr++) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) Rt.r[3 * rr + c] = fmaf(Ea.r[rr], Eb.r[c], fmaf(Ea.r[3 + rr], Eb.r[3 + c], Ea.r[6 + rr] * Eb.r[6 + c]));
+        Rt.p[rr] = fmaf(Ea.r[rr], d0, fmaf(Ea.r[3 + rr], d1, Ea.r[6 + rr] * d2));
+      }
+      keep = true;
+      if (MODE == 0) {
+        const float ah[3] = {ha.x, ha.y, ha.z}, bh[3] = {hb.x, hb.y, hb.z};
+        keep = !obb_disjoint(Rt.r, Rt.p, ah, bh);
+        if (keep && ha.w > 0.f && hb.w > 0.f) {
+          // sufficient test: balls inscribed in the two shapes overlap -> the pair collides, no narrowphase needed
+          const float ib3[3] = {ib.x, ib.y, ib.z};
+          float icb[3];
+          xf_point(Rt, ib3, icb);  // B's ball centre in A's OBB frame
+          const float e0 = ia.x - icb[0], e1 = ia.y - icb[1], e2 = ia.z - icb[2];
+          const float rs = 0.999f * (ha.w + hb.w);
+          if (fmaf(e0, e0, fmaf(e1, e1, e2 * e2)) < rs * rs) {
+            keep = false;
+            atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
+            if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
+          }
+        }
+      }
+      if (keep) {  // relative pose of the two OBJECT frames for the narrowphase: Xa (A_obb^-1 B_obb) Xb^-1
+        const Xf Xa = xf_rows(__ldg(ca + 5), __ldg(ca + 6), __ldg(ca + 7));
+        const Xf Xbi = xf_rows(__ldg(cb + 8), __ldg(cb + 9), __ldg(cb + 10));
+        rel = xf_mul(xf_mul(Xa, Rt), Xbi);
       }
     }
-    __syncwarp();
-    float ub_min = FLT_MAX;
-    if (MODE == 1 && valid) {
-      for (int k = 0; k < img.n_pairs; k++) {
-        const float4 c = __ldg(img.cullc + k);
-        const int2 m = __ldg(img.cullm + k);
-        const int m1 = m.y & 0xffff, m2 = m.y >> 16;  // biased by one; 0 = none
-        float ax = 0.f, ay = 0.f, az = 0.f, bx = c.x, by = c.y, bz = c.z;
-        if (m1) { ax = SMC(m1 - 1, 0, lane); ay = SMC(m1 - 1, 1, lane); az = SMC(m1 - 1, 2, lane); }
-        if (m2) { bx = SMC(m2 - 1, 0, lane); by = SMC(m2 - 1, 1, lane); bz = SMC(m2 - 1, 2, lane); }
-        const float dx = ax - bx, dy = ay - by, dz = az - bz;
-        ub_min = fminf(ub_min, sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) + sqrtf(c.w));
-      }
-      ub_min *= 1.000001f;
+    const unsigned km = __ballot_sync(FULL, keep);
+    if (km == 0) continue;
+    // warp-private chunk of staging slots: one same-address atomic per MPB_STAGE_CHUNK items
+    const unsigned cntk = (unsigned)__popc(km);
+    if (wused + cntk > MPB_STAGE_CHUNK) {
+      if (wbase != 0xffffffffu)
+        for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
+          if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;  // unused tail of the old chunk
+      unsigned nb = 0;
+      if (lane == 0) nb = atomicAdd(&wq.totals[0], (unsigned)MPB_STAGE_CHUNK);
+      wbase = __shfl_sync(FULL, nb, 0);
+      wused = 0;
     }
-    unsigned qn = 0;  // warp-uniform queue length
-    int r = 0;        // run cursor
-    for (int gbase = 0; gbase < img.n_pairs; gbase += MPB_CULL_GROUP) {
-      const int gend = min(gbase + MPB_CULL_GROUP, img.n_pairs);
-      // ---- 2. bounding spheres over the cull table
-      unsigned mask = 0;
-      int k = gbase;
-      while (k < gend) {
-        const int4 run = __ldg(img.runs + r);  // {moving slot or -1, first, count, partner kind}
-        const int rlast = run.y + run.z;
-        const int rend = min(rlast, gend);
-        float ax = 0.f, ay = 0.f, az = 0.f;
-        if (run.x >= 0) { ax = SMC(run.x, 0, lane); ay = SMC(run.x, 1, lane); az = SMC(run.x, 2, lane); }
-        if (run.w == 0) {  // world-fixed partners: centre + (R1 + R2)^2 in one uniform 16-byte load
-#pragma unroll 4
-          for (; k < rend; k++) {
-            const float4 c = __ldg(img.cullc + k);
-            const float dx = ax - c.x, dy = ay - c.y, dz = az - c.z;
-            const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-            const bool s = MODE == 0 ? (d2c <= c.w) : (sqrtf(d2c) - sqrtf(c.w) <= ub_min);
-            mask |= (unsigned)s << (k - gbase);
-          }
-        } else {  // moving partners
-          for (; k < rend; k++) {
-            const float rr2 = __ldg(&img.cullc[k].w);
-            const int m2 = (__ldg(&img.cullm[k].y) >> 16) - 1;
-            const float dx = ax - SMC(m2, 0, lane), dy = ay - SMC(m2, 1, lane), dz = az - SMC(m2, 2, lane);
-            const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-            const bool s = MODE == 0 ? (d2c <= rr2) : (sqrtf(d2c) - sqrtf(rr2) <= ub_min);
-            mask |= (unsigned)s << (k - gbase);
-          }
-        }
-        if (rend == rlast) r++;
+    if (keep) {
+      const unsigned slot = wbase + wused + __popc(km & ((1u << lane) - 1u));
+      const int bin = img.pairs[p].bin_dyn & 0xffff;
+      if (slot < wq.cap) {
+#pragma unroll
+        for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = rel.r[k2];
+#pragma unroll
+        for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = rel.p[k2];
+        wq.scfg[slot] = (int)cfg;
+        wq.spair[slot] = p;
+        wq.saux[slot] = 0;
       }
-      if (!valid) mask = 0;
-      if (__any_sync(FULL, mask != 0)) {  // push (lane, entry) survivors: warp prefix sum, no atomics
-        const unsigned c = __popc(mask);
-        unsigned incl = c;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const unsigned t = __shfl_up_sync(FULL, incl, o);
-          if ((int)lane >= o) incl += t;
-        }
-        unsigned pos = qn + incl - c;
-        while (mask) {
-          const int kk = __ffs(mask) - 1;
-          mask &= mask - 1;
-          sQ[pos++] = lane | ((unsigned)(gbase + kk) << 5);
-        }
-        qn += __shfl_sync(FULL, incl, 31);
-        __syncwarp();
+      if (slot < wq.cap) {
+        if (smem_bins) atomicAdd(&s_bins[bin], 1u);
+        else atomicAdd(&wq.bin_count[bin], 1u);
       }
-      const bool last = gend == img.n_pairs;
-      if (qn < MPB_CULL_DRAIN && !(last && qn > 0)) continue;
-      // ---- 3. dense OBB SAT over the queue (full warps; a remainder < 32 waits for the next drain)
-      const unsigned qfull = last ? qn : (qn & ~31u);
-      for (unsigned e0 = 0; e0 < qfull; e0 += 32) {
-        const unsigned e = e0 + lane;
-        bool keep = false;
-        Xf rel;
-        int p = 0, owner = 0;
-        if (e < qfull) {
-          const unsigned ent = sQ[e];
-          owner = ent & 31;
-          p = __ldg(&img.cullm[ent >> 5].x);
-          const DevPair pr = img.pairs[p];
-          // cull records: OBB frame [axes | centre] (world frame if the object is fixed, owner-joint frame if it moves),
-          // half extents + inscribed radius, inscribed-ball centre + joint-table slot: five 16-byte loads per object
-          const float4 *ca = img.cobb + 5 * pr.a, *cb = img.cobb + 5 * pr.b;
-          Xf Ea = xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2)), Eb = xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
-          const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
-          const int jsa = __float_as_int(ia.w), jsb = __float_as_int(ib.w);
-          const float ia3[3] = {ia.x, ia.y, ia.z}, ib3[3] = {ib.x, ib.y, ib.z};
-          float ica[3] = {ia.x, ia.y, ia.z}, icb[3] = {ib.x, ib.y, ib.z};
-          Xf Ja, Jb;
-          if (jsa >= 0) { Ja = smem_joint(sJ, jsa, owner); Ea = xf_mul(Ja, Ea); xf_point(Ja, ia3, ica); }
-          if (jsb >= 0) { Jb = smem_joint(sJ, jsb, owner); Eb = xf_mul(Jb, Eb); xf_point(Jb, ib3, icb); }
-          keep = true;
-          if (MODE == 0) {
-            // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)
-            float R[9], t[3];
-            const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
-#pragma unroll
-            for (int rr = 0; rr < 3; rr++) {
-#pragma unroll
-              for (int c = 0; c < 3; c++) R[3 * rr + c] = fmaf(Ea.r[rr], Eb.r[c], fmaf(Ea.r[3 + rr], Eb.r[3 + c], Ea.r[6 + rr] * Eb.r[6 + c]));
-              t[rr] = fmaf(Ea.r[rr], d0, fmaf(Ea.r[3 + rr], d1, Ea.r[6 + rr] * d2));
-            }
-            const float ah[3] = {ha.x, ha.y, ha.z}, bh[3] = {hb.x, hb.y, hb.z};
-            keep = !obb_disjoint(R, t, ah, bh);
-            if (keep && ha.w > 0.f && hb.w > 0.f) {
-              // sufficient test: balls inscribed in the two shapes overlap -> the pair collides, no narrowphase needed
-              const float e0 = ica[0] - icb[0], e1 = ica[1] - icb[1], e2 = ica[2] - icb[2];
-              const float rs = 0.999f * (ha.w + hb.w);
-              if (fmaf(e0, e0, fmaf(e1, e1, e2 * e2)) < rs * rs) {
-                keep = false;
-                const long long cfg = cfg_base + tile * 32 + owner;
-                atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
-                if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
-              }
-            }
-          }
-          if (keep) {  // relative pose of the two OBJECT frames for the narrowphase
-            const Xf La = load_xf12(img.objs[pr.a].L), Lb = load_xf12(img.objs[pr.b].L);
-            const Xf Wa = jsa >= 0 ? xf_mul(Ja, La) : La;
-            const Xf Wb = jsb >= 0 ? xf_mul(Jb, Lb) : Lb;
-            rel = xf_inv_mul(Wa, Wb);
-          }
-        }
-        const unsigned km = __ballot_sync(FULL, keep);
-        if (km == 0) continue;
-        // warp-private chunk of staging slots: one same-address atomic per MPB_STAGE_CHUNK items
-        const unsigned cntk = (unsigned)__popc(km);
-        if (wused + cntk > MPB_STAGE_CHUNK) {
-          if (wbase != 0xffffffffu && wused + lane < MPB_STAGE_CHUNK && wbase + wused + lane < wq.cap)
-            wq.scfg[wbase + wused + lane] = -1;  // unused tail of the old chunk
-          if (wbase != 0xffffffffu && wused + 32 + lane < MPB_STAGE_CHUNK && wbase + wused + 32 + lane < wq.cap)
-            wq.scfg[wbase + wused + 32 + lane] = -1;
-          unsigned nb = 0;
-          if (lane == 0) nb = atomicAdd(&wq.totals[0], (unsigned)MPB_STAGE_CHUNK);
-          wbase = __shfl_sync(FULL, nb, 0);
-          wused = 0;
-        }
-        if (keep) {
-          const unsigned slot = wbase + wused + __popc(km & ((1u << lane) - 1u));
-          const int bin = img.pairs[p].bin_dyn & 0xffff;
-          if (slot < wq.cap) {
-#pragma unroll
-            for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = rel.r[k2];
-#pragma unroll
-            for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = rel.p[k2];
-            wq.scfg[slot] = (int)(cfg_base + tile * 32 + owner);
-            wq.spair[slot] = p;
-            wq.saux[slot] = 0;
-          }
-          const unsigned grp = __match_any_sync(km, slot < wq.cap ? bin : -1);
-          if (slot < wq.cap && lane == (unsigned)(__ffs(grp) - 1)) atomicAdd(&wq.bin_count[bin], (unsigned)__popc(grp));
-        }
-        wused += cntk;
-      }
-      const unsigned left = qn - qfull;  // < 32: move the remainder to the front of the queue
-      unsigned carry = 0;
-      if (lane < left) carry = sQ[qfull + lane];
-      __syncwarp();
-      if (lane < left) sQ[lane] = carry;
-      __syncwarp();
-      qn = left;
     }
-    __syncwarp();  // the next tile's FK overwrites sJ / sC
+    wused += cntk;
   }
   // invalidate the unused tail of the last chunk
   if (wbase != 0xffffffffu) {
     for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
       if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;
   }
+  __syncthreads();
+  if (smem_bins)
+    for (int b = threadIdx.x; b < img.n_bins; b += blockDim.x)
+      if (s_bins[b]) atomicAdd(&wq.bin_count[b], s_bins[b]);
 }
+#undef POSE
 
-__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_warps) {
+__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_warps, unsigned sq_cap) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned items = 0, units = 0;
     // unit = slice of one bin a warp owns: as large as possible (persistent lanes keep all 32 lanes busy across the
@@ -456,26 +486,46 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_
     wq.totals[1] = units;
     wq.totals[3] = 0;
     wq.totals[5] = 0;  // expand_kernel's item ticket
-    if (wq.totals[0] > wq.cap) wq.totals[2] = 1u;  // staging overflow: the host redoes the pass in smaller chunks
+    if (wq.totals[0] > wq.cap || wq.totals[6] > sq_cap) wq.totals[2] = 1u;  // queue overflow: the host redoes the pass in smaller chunks
     atomicAdd(wq.counters, (unsigned long long)items);
   }
 }
 
-__global__ void __launch_bounds__(256) scatter_kernel(SceneImg img, WorkQ wq, int round) {
+// Staging queue -> binned queue.  A block ranks its items per bin in shared memory (the shared atomic returns the
+// rank), reserves one range per bin per trip in the global cursors, then moves the items.
+__global__ void __launch_bounds__(1024) scatter_kernel(SceneImg img, WorkQ wq, int round) {
+  __shared__ unsigned s_cnt[MPB_SMEM_BINS], s_base[MPB_SMEM_BINS];
   const unsigned n = min(wq.totals[0], wq.cap);
-  const unsigned n_round = (n + 31u) & ~31u;
+  const int n_bins = round == 0 ? img.n_bins : img.n_bins2;
+  const bool smem_bins = n_bins <= MPB_SMEM_BINS;
+  const unsigned n_round = (n + blockDim.x - 1) / blockDim.x * blockDim.x;
   const unsigned lane = threadIdx.x & 31;
   for (unsigned s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
     const bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
     const int p = valid ? wq.spair[s] : 0;
-    const int bin = valid ? (round == 0 ? (img.pairs[p].bin_dyn & 0xffff) : img.pair_bin2[p]) : (-1 - (int)lane);
-    const unsigned grp = __match_any_sync(0xffffffffu, bin);
-    const int leader = __ffs(grp) - 1;
-    unsigned base = 0;
-    if (valid && (int)lane == leader) base = atomicAdd(&wq.bin_cursor[bin], (unsigned)__popc(grp));
-    base = __shfl_sync(0xffffffffu, base, leader);
+    int bin = valid ? (round == 0 ? (img.pairs[p].bin_dyn & 0xffff) : img.pair_bin2[p]) : -1;
+    unsigned dst = 0;
+    if (smem_bins) {
+      for (int b = threadIdx.x; b < n_bins; b += blockDim.x) s_cnt[b] = 0;
+      __syncthreads();
+      unsigned rank = 0;
+      if (valid) rank = atomicAdd(&s_cnt[bin], 1u);
+      __syncthreads();
+      for (int b = threadIdx.x; b < n_bins; b += blockDim.x)
+        if (s_cnt[b]) s_base[b] = atomicAdd(&wq.bin_cursor[b], s_cnt[b]);
+      __syncthreads();
+      if (valid) dst = wq.bin_start[bin] + s_base[bin] + rank;
+      __syncthreads();  // s_cnt / s_base are rewritten by the next trip
+    } else {
+      if (!valid) bin = -1 - (int)lane;
+      const unsigned grp = __match_any_sync(0xffffffffu, bin);
+      const int leader = __ffs(grp) - 1;
+      unsigned base = 0;
+      if (valid && (int)lane == leader) base = atomicAdd(&wq.bin_cursor[bin], (unsigned)__popc(grp));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (valid) dst = wq.bin_start[bin] + base + __popc(grp & ((1u << lane) - 1u));
+    }
     if (valid) {
-      const unsigned dst = wq.bin_start[bin] + base + __popc(grp & ((1u << lane) - 1u));
 #pragma unroll
       for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = wq.stf[(size_t)k * wq.cap + s];
       wq.icfg[dst] = wq.scfg[s];

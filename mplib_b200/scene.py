@@ -63,6 +63,7 @@ class MpbStats(C.Structure):
         ("n_states", C.c_int64),
         ("pairs_admitted", C.c_int64),
         ("pairs_after_cull", C.c_int64),
+        ("pairs_after_spheres", C.c_int64),
         ("narrow_iterations", C.c_int64),
         ("narrow_capped", C.c_int64),
         ("kernel_launches", C.c_int64),
