@@ -290,6 +290,51 @@ static std::vector<CellBox> merge_cells(const int32_t *cells, int n) {
   return runs;
 }
 
+// Support cell table of one hull (layout in mpb_device.cuh).  Vertex i can be extreme for a direction of cell C only
+// if, for every other vertex j, SOME direction of C prefers i: max over C of d . (v_i - v_j) >= 0.  The cell is a
+// planar quad on the cube (directions need not be unit length), so that maximum sits at one of its four corners.
+// Checking the condition against all j gives a superset of the exact set; the quad is widened by `margin` so that
+// the device's float arithmetic may place a boundary direction in either neighbouring cell.
+static void build_cell_table(const double *V, int nv, std::vector<unsigned char> &out) {
+  const int G = MPB_CELL_G;
+  const double margin = 1e-3;
+  double scale = 0;
+  for (int i = 0; i < 3 * nv; i++) scale = std::max(scale, std::fabs(V[i]));
+  const double eps = 1e-9 * std::max(scale, 1e-9);
+  std::vector<unsigned short> first(MPB_CELL_COUNT + 1, 0);
+  std::vector<unsigned char> cand;
+  for (int face = 0; face < 6; face++)
+    for (int iv = 0; iv < G; iv++)
+      for (int iu = 0; iu < G; iu++) {
+        const double u0 = -1.0 + 2.0 * iu / G - margin, u1 = -1.0 + 2.0 * (iu + 1) / G + margin;
+        const double v0 = -1.0 + 2.0 * iv / G - margin, v1 = -1.0 + 2.0 * (iv + 1) / G + margin;
+        double c[4][3];
+        const double uu[4] = {u0, u1, u0, u1}, vv[4] = {v0, v0, v1, v1};
+        for (int k = 0; k < 4; k++) {
+          const double sgn = (face & 1) ? -1.0 : 1.0;
+          if (face < 2) { c[k][0] = sgn; c[k][1] = uu[k]; c[k][2] = vv[k]; }
+          else if (face < 4) { c[k][0] = uu[k]; c[k][1] = sgn; c[k][2] = vv[k]; }
+          else { c[k][0] = uu[k]; c[k][1] = vv[k]; c[k][2] = sgn; }
+        }
+        first[(face * G + iv) * G + iu] = (unsigned short)cand.size();
+        for (int i = 0; i < nv; i++) {
+          bool ok = true;
+          for (int j = 0; j < nv && ok; j++) {
+            if (j == i) continue;
+            const double w[3] = {V[3 * i] - V[3 * j], V[3 * i + 1] - V[3 * j + 1], V[3 * i + 2] - V[3 * j + 2]};
+            double best = -1e300;
+            for (int k = 0; k < 4; k++) best = std::max(best, c[k][0] * w[0] + c[k][1] * w[1] + c[k][2] * w[2]);
+            ok = best >= -eps;
+          }
+          if (ok) cand.push_back((unsigned char)i);
+        }
+      }
+  first[MPB_CELL_COUNT] = (unsigned short)cand.size();
+  out.resize(2 * (MPB_CELL_COUNT + 1) + cand.size());
+  memcpy(out.data(), first.data(), 2 * (MPB_CELL_COUNT + 1));
+  memcpy(out.data() + 2 * (MPB_CELL_COUNT + 1), cand.data(), cand.size());
+}
+
 static int geom_key(int type, int geom) { return type == MPB_GEOM_CONVEX ? 16 + geom : type; }
 
 static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32_t *pb) {
@@ -466,6 +511,24 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
       verts.push_back(make_float4((float)d->hull_verts[3 * i], (float)d->hull_verts[3 * i + 1], (float)d->hull_verts[3 * i + 2], 0.f));
   }
   hull_off[d->n_hulls] = (int)verts.size();
+  const int n_hull_verts = (int)verts.size();
+  // support cell tables behind the vertices (same pool: one TMA stage brings both into shared memory)
+  std::vector<int> hull_cell(std::max(d->n_hulls, 0), -1);
+  {
+    std::vector<unsigned char> pool, one;
+    for (int h = 0; h < d->n_hulls; h++) {
+      const int v0 = d->hull_vert_off[h], nv = d->hull_vert_off[h + 1] - v0;
+      if (nv <= 0 || nv > 256) continue;  // byte-sized candidate indices; larger hulls keep the full scan
+      build_cell_table(d->hull_verts + 3 * (size_t)v0, nv, one);
+      if (one.size() - 2 * (MPB_CELL_COUNT + 1) > 65535) continue;
+      hull_cell[h] = (int)pool.size();
+      pool.insert(pool.end(), one.begin(), one.end());
+      pool.resize((pool.size() + 15) / 16 * 16, 0);
+    }
+    const size_t at = verts.size();
+    verts.resize(at + pool.size() / 16);
+    if (!pool.empty()) memcpy(verts.data() + at, pool.data(), pool.size());
+  }
   // BVH objects: one tree per mesh / octree in the pools
   std::vector<DevBvhNode> nodes;
   std::vector<float4> prims;
@@ -529,6 +592,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   for (int o = 0; o < d->n_objects; o++) {
     DevObject &O = s->h_objs[o];
     memset(&O, 0, sizeof(O));
+    O.cell = -1;
     O.type = d->obj_type[o];
     O.geom = d->obj_geom[o];
     double L[12];
@@ -570,6 +634,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
         if (nv <= 0) { delete s; return fail(MPB_ERR_INVALID, "empty convex hull"); }
         O.voff = hull_off[h];
         O.vcnt = nv;
+        O.cell = hull_cell[h];
         bound_points(d->hull_verts + 3 * v0, nv, O);
         double c[3] = {0, 0, 0};
         for (int i = 0; i < nv; i++)
@@ -684,7 +749,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   s->img.n_joints = d->n_joints;
   s->img.n_objects = d->n_objects;
   s->img.n_links = d->n_links;
-  s->img.n_verts = (int)verts.size();
+  s->img.n_verts = n_hull_verts;
+  s->img.pool_bytes = (int)(verts.size() * sizeof(float4));
   s->img.state_dim = d->state_dim;
   int rc = build_pairs(s, d->n_pairs, d->pair_a, d->pair_b);
   if (rc != MPB_OK) { delete s; return rc; }
@@ -898,7 +964,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, n_warps, s->sq_cap);
   scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
   if (ev) CU(cudaEventRecord(e1, st));
-  const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
+  const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
   if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
   else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
   *launches += 3;
@@ -1435,7 +1501,7 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
   const int D = s->img.state_dim;
   const bool host = space == MPB_HOST;
   static bool attr_set = false;
-  const size_t vsm = s->smem_verts ? (size_t)s->img.n_verts * sizeof(float4) : 0;
+  const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
   if (!attr_set && s->smem_verts) {
     CU(cudaFuncSetAttribute(distance_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vsm, 16)));
     attr_set = true;

@@ -49,9 +49,30 @@ struct alignas(16) DevObject {
   float bcw[3];     // world-fixed objects: bounding-sphere centre in the world frame
   float rin;        // radius of a ball around ctr that lies inside the shape (sufficient-hit test)
   int jslot;        // joint-table slot of the owner joint, -1 if world-fixed
-  float bcj[3];     // bounding-sphere centre in the owner joint frame (L * bc); sizeof == 208
+  float bcj[3];     // bounding-sphere centre in the owner joint frame (L * bc)
+  int cell;         // convex hulls: byte offset of the support cell table behind the vertex pool, -1 = none
 };
 static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
+
+// Support cell table of a convex hull: the directions of a cube map (MPB_CELL_G x MPB_CELL_G cells per face) -> the
+// vertices that can be extreme for SOME direction of the cell (a conservative superset, built on the host), so the
+// support scan visits a handful of candidates instead of every vertex and still returns the exact arg-max.
+// Layout: uint16 first[6 G G + 1], then uint8 candidate vertex indices (ascending per cell).
+#define MPB_CELL_G 8
+#define MPB_CELL_COUNT (6 * MPB_CELL_G * MPB_CELL_G)
+__host__ __device__ __forceinline__ int mpb_cube_cell(float x, float y, float z) {
+  const float ax = fabsf(x), ay = fabsf(y), az = fabsf(z);
+  int face;
+  float m, u, v;
+  if (ax >= ay && ax >= az) { face = x >= 0.f ? 0 : 1; m = ax; u = y; v = z; }
+  else if (ay >= az) { face = y >= 0.f ? 2 : 3; m = ay; u = x; v = z; }
+  else { face = z >= 0.f ? 4 : 5; m = az; u = x; v = y; }
+  const float inv = m > 0.f ? 1.0f / m : 0.f;
+  int iu = (int)((u * inv + 1.0f) * (0.5f * MPB_CELL_G)), iv = (int)((v * inv + 1.0f) * (0.5f * MPB_CELL_G));
+  iu = iu < 0 ? 0 : (iu > MPB_CELL_G - 1 ? MPB_CELL_G - 1 : iu);
+  iv = iv < 0 ? 0 : (iv > MPB_CELL_G - 1 ? MPB_CELL_G - 1 : iv);
+  return (face * MPB_CELL_G + iv) * MPB_CELL_G + iu;
+}
 
 struct DevPair {
   int a, b;

@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(256) distance_kernel(SceneImg img, WorkQ wq, u
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
   if (SMEM) {
-    const unsigned total = (unsigned)img.n_verts * 16u;
+    const unsigned total = (unsigned)img.pool_bytes;
     if (threadIdx.x == 0) {
       mbar_init(&bar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(256) distance_kernel(SceneImg img, WorkQ wq, u
     if (total > 0) mbar_wait(&bar, 0);
     verts = reinterpret_cast<const float4 *>(smem_raw);
   }
+  const unsigned char *cells = reinterpret_cast<const unsigned char *>(verts + img.n_verts);
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
   const unsigned n_units = wq.totals[1], unit_items = wq.totals[4];
@@ -159,8 +160,8 @@ __global__ void __launch_bounds__(256) distance_kernel(SceneImg img, WorkQ wq, u
       while (__any_sync(FULL, busy)) {
         // support of A - B along -v
         const V3 dir = normalized(v) * -1.f;
-        const V3 sa = support_local<SMEM>(A, dir, verts, img.prims);
-        const V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts, img.prims);
+        const V3 sa = support_local<SMEM>(A, dir, verts, img.prims, cells);
+        const V3 sb = support_local<SMEM>(B, rot_t(R, dir * -1.f), verts, img.prims, cells);
         const V3 w = sa - (rot(R, sb) + t);
         if (!busy) continue;
         iters++;

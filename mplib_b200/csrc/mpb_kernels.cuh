@@ -31,7 +31,7 @@ struct SceneImg {
   const DevJoint *joints;
   const DevObject *objs;
   const DevPair *pairs;
-  const float4 *verts;
+  const float4 *verts;      // hull vertex pool, followed by the support cell tables (pool_bytes in all)
   const int *dynlist;   // moving objects grouped by owner joint
   const DevBvhNode *nodes;  // BVH node pool (meshes, octrees); DevObject::voff = root, ::vcnt = leaf type
   const float4 *prims;      // leaf primitives, 3 float4 each
@@ -45,6 +45,7 @@ struct SceneImg {
   const float *linkL;   // [n_links][12] link placement in its joint frame
   const int *linkJoint; // [n_links]
   int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn, n_jslots;
+  int pool_bytes;         // vertex pool + cell tables, staged as one block in shared memory
   int w_sphere, w_joint;  // pose-table word offsets: [n_dyn][12] OBB frames, then [n_dyn][3] sphere centres, then [n_jslots][12] branch joints
 };
 
@@ -537,12 +538,12 @@ __global__ void __launch_bounds__(1024) scatter_kernel(SceneImg img, WorkQ wq, i
 
 // ---------------------------------------------------------------------------------------------- supports
 struct DevShape {
-  int type, voff, vcnt;
+  int type, voff, vcnt, cell;
   float p0, p1, p2;
 };
 __device__ __forceinline__ DevShape shape_of(const DevObject &O) {
   DevShape s;
-  s.type = O.type; s.voff = O.voff; s.vcnt = O.vcnt; s.p0 = O.prm[0]; s.p1 = O.prm[1]; s.p2 = O.prm[2];
+  s.type = O.type; s.voff = O.voff; s.vcnt = O.vcnt; s.cell = O.cell; s.p0 = O.prm[0]; s.p1 = O.prm[1]; s.p2 = O.prm[2];
   return s;
 }
 __device__ __forceinline__ float sgn_eps(float v) { return fabsf(v) < MPB_EPS ? 0.f : (v < 0.f ? -1.f : 1.f); }
@@ -550,11 +551,27 @@ __device__ __forceinline__ float sgn_eps(float v) { return fabsf(v) < MPB_EPS ? 
 // extreme point of the shape along `d` in the shape's own frame ([upstream FCL support* functions])
 template <bool SMEM>
 __device__ __forceinline__ V3 support_local(const DevShape &s, V3 d, const float4 *__restrict__ verts,
-                                         const float4 *__restrict__ prims) {
+                                         const float4 *__restrict__ prims, const unsigned char *__restrict__ cells) {
   if (s.type == MPB_GEOM_CONVEX) {
     const float4 *v = verts + s.voff;
     float best = -FLT_MAX;
     int bi = 0;
+    if (s.cell >= 0) {  // candidates of the direction's cube-map cell; same arg-max (and tie order) as the full scan
+      const unsigned char *tb = cells + s.cell;
+      const unsigned short *first = reinterpret_cast<const unsigned short *>(tb);
+      const unsigned char *cand = tb + 2 * (MPB_CELL_COUNT + 1);
+      const int cell = mpb_cube_cell(d.x, d.y, d.z);
+      const int c0 = first[cell], c1 = first[cell + 1];
+      bi = cand[c0];
+      for (int c = c0; c < c1; c++) {
+        const int i = cand[c];
+        const float4 p = SMEM ? v[i] : __ldg(v + i);
+        const float t = fmaf(p.x, d.x, fmaf(p.y, d.y, p.z * d.z));
+        if (t > best) { best = t; bi = i; }
+      }
+      const float4 p = SMEM ? v[bi] : __ldg(v + bi);
+      return v3(p.x, p.y, p.z);
+    }
 #pragma unroll 4
     for (int i = 0; i < s.vcnt; i++) {
       const float4 p = SMEM ? v[i] : __ldg(v + i);
@@ -670,7 +687,7 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
   if (SMEM) {
-    const unsigned total = (unsigned)img.n_verts * 16u;
+    const unsigned total = (unsigned)img.pool_bytes;
     if (threadIdx.x == 0) {
       mbar_init(&bar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -686,6 +703,7 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
     if (total > 0) mbar_wait(&bar, 0);
     verts = reinterpret_cast<const float4 *>(smem_raw);
   }
+  const unsigned char *cells = reinterpret_cast<const unsigned char *>(verts + img.n_verts);
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
   const unsigned n_units = wq.totals[1], unit_items = wq.totals[4];
@@ -769,9 +787,10 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
       if (__popc(bm) <= MPB_COOP_MAX) {
         // few lanes left (the tail of a slice): the whole warp scans the hulls for one busy lane at a time
         // (lane-strided vertices + shuffle arg-max) instead of every lane scanning every vertex for itself
-        const bool ca = A.type == MPB_GEOM_CONVEX, cb = B.type == MPB_GEOM_CONVEX;  // warp-uniform (bin-uniform shapes)
-        if (!ca) sa = support_local<SMEM>(A, dir, verts, img.prims);
-        if (!cb) sb = support_local<SMEM>(B, dB, verts, img.prims);
+        // warp-uniform (bin-uniform shapes); hulls with a support cell table scan a handful of candidates per lane anyway
+        const bool ca = A.type == MPB_GEOM_CONVEX && A.cell < 0, cb = B.type == MPB_GEOM_CONVEX && B.cell < 0;
+        if (!ca) sa = support_local<SMEM>(A, dir, verts, img.prims, cells);
+        if (!cb) sb = support_local<SMEM>(B, dB, verts, img.prims, cells);
         for (unsigned m = bm; m; m &= m - 1) {
           const int src = __ffs(m) - 1;
           if (ca) {
@@ -786,8 +805,8 @@ __global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, uns
           }
         }
       } else {
-        sa = support_local<SMEM>(A, dir, verts, img.prims);
-        sb = support_local<SMEM>(B, dB, verts, img.prims);
+        sa = support_local<SMEM>(A, dir, verts, img.prims, cells);
+        sb = support_local<SMEM>(B, dB, verts, img.prims, cells);
       }
       const V3 v = sa - (rot(R, sb) + t);
       if (!busy) continue;
