@@ -954,14 +954,23 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
   int *stack = s_stack[warp];
   const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
   for (;;) {
-    unsigned it = 0;
-    if (lane == 0) it = atomicAdd(&wq.totals[5], 1u);
-    it = first + __shfl_sync(FULL, it, 0);
-    if (it >= end) break;
-    const int cfg = wq.icfg[it], p = wq.ipair[it];
-    const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
-                                 : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
-    if (known) continue;
+    // four items per ticket; lanes 0..3 fetch their (configuration, pair, already-known) in parallel
+    unsigned it0 = 0;
+    if (lane == 0) it0 = atomicAdd(&wq.totals[5], 4u);
+    it0 = first + __shfl_sync(FULL, it0, 0);
+    if (it0 >= end) break;
+    int my_cfg = 0, my_p = 0;
+    bool my_known = true;
+    if (lane < 4 && it0 + lane < end) {
+      my_cfg = wq.icfg[it0 + lane];
+      my_p = wq.ipair[it0 + lane];
+      my_known = pair_bits ? ((pair_bits[(size_t)my_cfg * img.pair_words + (my_p >> 5)] >> (my_p & 31)) & 1u)
+                           : ((verdict_bits[my_cfg >> 5] >> (my_cfg & 31)) & 1u);
+    }
+    for (int sub = 0; sub < 4; sub++) {
+    const unsigned it = it0 + sub;
+    const int cfg = __shfl_sync(FULL, my_cfg, sub), p = __shfl_sync(FULL, my_p, sub);
+    if (__shfl_sync(FULL, (int)my_known, sub)) continue;  // also covers slots past the end of the bin
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // the shape
     const DevObject &B = img.objs[pr.b];  // the BVH object
@@ -996,6 +1005,11 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
     }
     const float rin2 = A.rin * A.rin;
     const float ah[3] = {A.oh[0], A.oh[1], A.oh[2]};
+    // axis-aligned bounds of the shape's OBB in the object frame: the cheap test of the descent (six compares per node);
+    // the exact 15-axis test runs per leaf primitive only
+    float bh[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) bh[r] = fmaf(fabsf(Ra[3 * r]), ah[0], fmaf(fabsf(Ra[3 * r + 1]), ah[1], fabsf(Ra[3 * r + 2]) * ah[2])) + 1e-5f;
     const int leaf_type = B.vcnt;
     const int bin2 = img.pair_bin2[p];
     int sp = 1;
@@ -1013,11 +1027,8 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
       nd.left = 0; nd.right = 0;
       if (node >= 0) {
         nd = img.nodes[node];
-        float trel[3];
-        const float e0 = nd.c[0] - ca[0], e1 = nd.c[1] - ca[1], e2 = nd.c[2] - ca[2];
-#pragma unroll
-        for (int r = 0; r < 3; r++) trel[r] = fmaf(Ra[r], e0, fmaf(Ra[3 + r], e1, Ra[6 + r] * e2));
-        pass = !obb_disjoint(Rrel, trel, ah, nd.h);
+        pass = fabsf(nd.c[0] - ca[0]) <= nd.h[0] + bh[0] && fabsf(nd.c[1] - ca[1]) <= nd.h[1] + bh[1] &&
+               fabsf(nd.c[2] - ca[2]) <= nd.h[2] + bh[2];
       }
       const bool inner = pass && nd.left >= 0;
       const unsigned im = __ballot_sync(FULL, inner);
@@ -1045,7 +1056,7 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
             pc[0] = 0.5f * (lo0 + hi0); pc[1] = 0.5f * (lo1 + hi1); pc[2] = 0.5f * (lo2 + hi2);
             ph[0] = 0.5f * (hi0 - lo0) + 1e-6f; ph[1] = 0.5f * (hi1 - lo1) + 1e-6f; ph[2] = 0.5f * (hi2 - lo2) + 1e-6f;
           }
-          if (nd.right > 1 || leaf_type == MPB_GEOM_TRI) {  // primitive-level reject
+          {  // primitive-level reject: the exact OBB test
             const float g0 = pc[0] - ca[0], g1 = pc[1] - ca[1], g2 = pc[2] - ca[2];
             float tr[3];
 #pragma unroll
@@ -1083,5 +1094,6 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
       if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
     }
     __syncwarp();
+    }  // sub-items of the ticket
   }
 }
