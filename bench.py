@@ -290,18 +290,35 @@ def main():
     pool_h = [torch.from_numpy(wl["make_q"](rank * 1000 + k, N).astype(np.float32)).pin_memory() for k in range(n_pool)]
     pool_d = [t.cuda(non_blocking=True) for t in pool_h]
     vwords = (N + 31) // 32
-    verdict_d = torch.zeros(vwords, dtype=torch.int32, device="cuda")
-    pairs_d = torch.zeros((N, max(W, 1)), dtype=torch.int32, device="cuda")
-    gathered = torch.zeros((world, vwords), dtype=torch.int32, device="cuda") if world > 1 else None
+    # two result sets: the verdict gather of step k (NCCL, side stream) overlaps the kernels of step k + 1
+    verdict_d = [torch.zeros(vwords, dtype=torch.int32, device="cuda") for _ in range(2)]
+    pairs_d = [torch.zeros((N, max(W, 1)), dtype=torch.int32, device="cuda") for _ in range(2)]
+    gathered = [torch.zeros((world, vwords), dtype=torch.int32, device="cuda") for _ in range(2)] if world > 1 else None
+    comm = torch.cuda.Stream() if world > 1 else None
+    ev_done = [torch.cuda.Event() for _ in range(2)]
+    ev_gathered = [torch.cuda.Event() for _ in range(2)]
     verdict_h = torch.zeros(vwords, dtype=torch.int32).pin_memory()
     pairs_h = torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()
     torch.cuda.synchronize()
+    n_steps_done = [0]
 
     def step_device(k):
-        st = dev.collide_raw(pool_d[k % n_pool], N, verdict_d, pairs_d, _lib.MPB_DEVICE, stream.cuda_stream)
+        b = n_steps_done[0] & 1
+        if world > 1 and n_steps_done[0] >= 2:
+            stream.wait_event(ev_gathered[b])  # the gather of step k - 2 has read this result set
+        st = dev.collide_raw(pool_d[k % n_pool], N, verdict_d[b], pairs_d[b], _lib.MPB_DEVICE, stream.cuda_stream)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, verdict_d)  # the only inter-GPU traffic: verdict words
+            ev_done[b].record(stream)
+            with torch.cuda.stream(comm):
+                comm.wait_event(ev_done[b])
+                dist.all_gather_into_tensor(gathered[b], verdict_d[b])  # the only inter-GPU traffic: verdict words
+                ev_gathered[b].record(comm)
+        n_steps_done[0] += 1
         return st
+
+    def drain():
+        if world > 1:
+            stream.wait_stream(comm)
 
     def step_host(k):
         return dev.collide_raw(pool_h[k % n_pool], N, verdict_h, pairs_h, _lib.MPB_HOST, stream.cuda_stream)
@@ -313,6 +330,7 @@ def main():
 
     for k in range(args.warmup):
         step_device(k)
+    drain()
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -325,6 +343,7 @@ def main():
         st = step_device(args.warmup + k)
         for key in agg:
             agg[key] += st[key]
+    drain()  # the last gathers are inside the timed region
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)

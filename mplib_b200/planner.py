@@ -1,0 +1,217 @@
+"""Host mirror of ``mplib.Planner`` (mplib/planner.py) for the calls that sit on the accelerated path: collision
+queries, SRDF auto-generation and joint-space planning.  Every numeric query goes through the C-ABI to the GPU.
+
+Out of scope here: pose-goal IK (`Planner.IK`, `plan` with a pose goal), `plan_screw`, and TOPPRA time
+parametrisation (the `time` / `velocity` / `acceleration` keys of the reference's result dict) -- `toppra` is absent
+from this image; `plan_qpos` returns the waypoint matrix under "position" exactly as the reference hands it to TOPPRA
+(mplib/planner.py:493-510)."""
+from __future__ import annotations
+
+import os
+import xml.etree.ElementTree as ET
+from xml.dom import minidom
+
+import numpy as np
+
+from .pymp import ArticulatedModel, OMPLPlanner, PlanningWorld
+
+
+class Planner:
+    def __init__(self, urdf, user_link_names, user_joint_names, move_group, joint_vel_limits=None, joint_acc_limits=None, srdf="",
+                 package_keyword_replacement="", device=0, srdf_sample_time=1 << 20):
+        """mplib/planner.py:19-97 (same argument names and order)."""
+        self.urdf = urdf
+        if srdf == "" and os.path.exists(urdf.replace(".urdf", ".srdf")):
+            srdf = urdf.replace(".urdf", ".srdf")
+            print("No SRDF file provided. Try to load %s." % srdf)
+        self.srdf = srdf
+        self.user_link_names = list(user_link_names)
+        self.user_joint_names = list(user_joint_names)
+        self.joint_name_2_idx = {j: i for i, j in enumerate(self.user_joint_names)}
+        self.link_name_2_idx = {l: i for i, l in enumerate(self.user_link_names)}
+        urdf = self.replace_package_keyword(package_keyword_replacement)
+        self.robot = ArticulatedModel(urdf, srdf, [0, 0, -9.81], self.user_joint_names, self.user_link_names, verbose=False, convex=True)
+        self.pinocchio_model = self.robot.get_pinocchio_model()
+        self.planning_world = PlanningWorld([self.robot], ["robot"], [], [], device=device)
+        self.acm = self.planning_world.get_allowed_collision_matrix()
+        if srdf == "":
+            self.generate_collision_pair(sample_time=srdf_sample_time)
+            self.robot.update_SRDF(self.srdf)
+        assert move_group in self.user_link_names
+        self.move_group = move_group
+        self.robot.set_move_group(self.move_group)
+        self.move_group_joint_indices = self.robot.get_move_group_joint_indices()
+        self.joint_types = self.pinocchio_model.get_joint_types()
+        self.joint_limits = np.concatenate(self.pinocchio_model.get_joint_limits())
+        self.planner = OMPLPlanner(world=self.planning_world)
+        self.joint_vel_limits = joint_vel_limits
+        self.joint_acc_limits = joint_acc_limits
+        self.move_group_link_id = self.link_name_2_idx[self.move_group]
+
+    def replace_package_keyword(self, package_keyword_replacement):
+        """mplib/planner.py:99-116"""
+        rtn_urdf = self.urdf
+        with open(self.urdf, "r") as in_f:
+            content = in_f.read()
+            if "package://" in content:
+                rtn_urdf = self.urdf.replace(".urdf", "_package_keyword_replaced.urdf")
+                content = content.replace("package://", package_keyword_replacement)
+                if not os.path.exists(rtn_urdf):
+                    with open(rtn_urdf, "w") as out_f:
+                        out_f.write(content)
+        return rtn_urdf
+
+    # ------------------------------------------------------------------ SRDF auto-generation
+    def always_colliding_pairs(self, sample_time=1 << 20, seed=None, batch=1 << 18):
+        """The statistic of `generate_collision_pair` (mplib/planner.py:118-163): how often every admitted link pair
+        collides over `sample_time` random configurations (uniform in the joint limits, as
+        `get_random_configuration`), as ONE batched collide_full per chunk: the pair masks come back as bit
+        columns and are summed per pair.  -> (count[n_link, n_link] int64, samples)"""
+        w = self.planning_world
+        rng = np.random.Generator(np.random.PCG64(seed)) if seed is not None else np.random.default_rng()
+        old_qpos = self.robot.get_qpos().copy()
+        old_ee = self.robot.get_move_group_end_effectors() if getattr(self.robot, "move_group_end_effectors", None) else None
+        # the reference samples ALL joints (set_qpos(qpos, full=True)): every joint becomes a batch state for the statistic
+        self.robot.set_move_group(self.pinocchio_model.get_leaf_links())
+        idx = self.robot.get_move_group_joint_indices()
+        lim = np.concatenate(self.pinocchio_model.get_joint_limits())[idx]
+        lo, hi = lim[:, 0], lim[:, 1]
+        n_link = len(self.user_link_names)
+        cnt = np.zeros((n_link, n_link), dtype=np.int64)
+        done = 0
+        while done < sample_time:
+            m = min(batch, sample_time - done)
+            cnt += self.pair_collision_counts(lo + (hi - lo) * rng.random((m, len(idx))))
+            done += m
+        if old_ee:
+            self.robot.set_move_group(old_ee)
+        self.robot.set_qpos(old_qpos, True)
+        return cnt, sample_time
+
+    def pair_collision_counts(self, states):
+        """count[u, v] = number of `states` in which link u collides with link v (one batched collide_full)."""
+        w = self.planning_world
+        n_link = len(self.user_link_names)
+        cnt = np.zeros((n_link, n_link), dtype=np.int64)
+        _, ph = w.collide_full_batch(states, want_pairs=True)
+        meta = w.get_pair_metadata()
+        for p, c in enumerate(ph.sum(axis=0)):
+            if c and meta[p][4] in self.link_name_2_idx and meta[p][5] in self.link_name_2_idx:
+                cnt[self.link_name_2_idx[meta[p][4]], self.link_name_2_idx[meta[p][5]]] += int(c)
+        return cnt
+
+    def generate_collision_pair(self, sample_time=1000000, echo_freq=100000, seed=None):
+        """mplib/planner.py:118-163: link pairs that collide in EVERY sample are written to <urdf>.srdf as
+        disable_collisions entries."""
+        print("Since no SRDF file is provided, we will first detect link pairs that will always collide.")
+        cnt, n = self.always_colliding_pairs(sample_time, seed)
+        root = ET.Element("robot")
+        root.set("name", self.urdf.split("/")[-1].split(".")[0])
+        self.srdf = self.urdf.replace(".urdf", ".srdf")
+        for i in range(cnt.shape[0]):
+            for j in range(cnt.shape[1]):
+                if cnt[i][j] == n:
+                    link1, link2 = self.user_link_names[i], self.user_link_names[j]
+                    print("Ignore collision pair: (%s, %s), reason:  always collide" % (link1, link2))
+                    c = ET.SubElement(root, "disable_collisions")
+                    c.set("link1", link1)
+                    c.set("link2", link2)
+                    c.set("reason", "Default")
+        with open(self.srdf, "w") as f:
+            f.write(minidom.parseString(ET.tostring(root)).toprettyxml(indent="    "))
+        print("Saving the SRDF file to %s" % self.srdf)
+
+    # ------------------------------------------------------------------ collision queries
+    def check_joint_limit(self, qpos):
+        """mplib/planner.py:170-192 (qpos is clipped in place for revolute joints)."""
+        for i, (q, joint_type, qlimit) in enumerate(zip(qpos, self.joint_types, self.joint_limits)):
+            if joint_type.startswith("JointModelR"):
+                if np.abs(q - qlimit[0]) < 1e-3:
+                    continue
+                q -= 2 * np.pi * np.floor((q - qlimit[0]) / (2 * np.pi))
+                qpos[i] = q
+                if q > qlimit[1] + 1e-3:
+                    return False
+            elif q < qlimit[0] - 1e-3 or q > qlimit[1] + 1e-3:
+                return False
+        return True
+
+    def check_for_collision(self, collision_function, state=None):
+        """mplib/planner.py:194-224"""
+        planned = self.planning_world.get_planned_articulations()
+        assert len(planned) == 1, "Only support 1 planned articulation now"
+        articulation = planned[0]
+        old_qpos = articulation.get_qpos()
+        if state is None:
+            state = old_qpos
+        state = np.asarray(state, dtype=np.float64)
+        if len(state) == len(self.move_group_joint_indices):
+            tmp = old_qpos.copy()
+            tmp[: len(state)] = state
+            state = tmp
+        articulation.set_qpos(state, True)
+        collisions = collision_function()
+        articulation.set_qpos(old_qpos, True)
+        return collisions
+
+    def check_for_self_collision(self, qpos=None):
+        """mplib/planner.py:226-240"""
+        return self.check_for_collision(self.planning_world.self_collide, qpos)
+
+    def check_for_env_collision(self, qpos=None):
+        """mplib/planner.py:242-256"""
+        return self.check_for_collision(self.planning_world.collide_with_others, qpos)
+
+    def check_for_collision_batch(self, states):
+        """Batched form: states [N, len(move group joints)] -> colliding bool[N] (self + environment)."""
+        return self.planning_world.collide_batch(np.asarray(states, dtype=np.float64))
+
+    # ------------------------------------------------------------------ scene updates (mplib/planner.py:358-413)
+    def update_point_cloud(self, pc, radius=1e-3):
+        self.planning_world.add_point_cloud("scene_pcd", np.asarray(pc, dtype=np.float64), radius)
+
+    def remove_point_cloud(self):
+        return self.planning_world.remove_normal_object("scene_pcd")
+
+    def update_attached_sphere(self, radius, pose, art_name="robot", link_id=-1):
+        self.planning_world.attach_sphere(radius, art_name, self.move_group_link_id if link_id == -1 else link_id, pose)
+
+    def update_attached_box(self, size, pose, art_name="robot", link_id=-1):
+        self.planning_world.attach_box(size, art_name, self.move_group_link_id if link_id == -1 else link_id, pose)
+
+    def update_attached_mesh(self, mesh_path, pose, art_name="robot", link_id=-1):
+        self.planning_world.attach_mesh(mesh_path, art_name, self.move_group_link_id if link_id == -1 else link_id, pose)
+
+    def detach_object(self, name="attached_geom", also_remove=False):
+        return self.planning_world.detach_object(name, also_remove)
+
+    # ------------------------------------------------------------------ joint-space planning
+    def plan_qpos(self, goal_qposes, current_qpos, *, planner_name="RRTConnect", rrt_range=0.1, planning_time=1.0,
+                  fix_joint_limits=True, verbose=False, **kw):
+        """RRTConnect from `current_qpos` to any of `goal_qposes` (the RRT half of `Planner.plan`,
+        mplib/planner.py:455-524, after its IK step).  -> {"status", "position"[n, ndof]}"""
+        current_qpos = np.array(current_qpos, dtype=np.float64, copy=True)
+        n = current_qpos.shape[0]
+        if fix_joint_limits:
+            for i in range(n):
+                current_qpos[i] = np.clip(current_qpos[i], self.joint_limits[i][0], self.joint_limits[i][1])
+        self.robot.set_qpos(current_qpos, True)
+        if self.planning_world.collide():
+            if verbose:
+                print("Invalid start state!")
+        idx = self.move_group_joint_indices
+        goals = [np.asarray(g, dtype=np.float64)[idx] if len(g) == n and n != len(idx) else np.asarray(g, dtype=np.float64)[: len(idx)]
+                 for g in goal_qposes]
+        status, path = self.planner.plan(current_qpos[idx], goals, planner_name=planner_name, time=planning_time, range=rrt_range,
+                                         verbose=verbose, **kw)
+        if status == "Exact solution":
+            return {"status": "Success", "position": path}
+        return {"status": "%s failed. %s" % (planner_name, status)}
+
+    def plan_qpos_batch(self, start_qposes, goal_qposes, *, rrt_range=0.1, planning_time=1.0, **kw):
+        """Q independent joint-space queries at once (see OMPLPlanner.plan_batch).  -> list of result dicts"""
+        status, paths, stats = self.planner.plan_batch(np.asarray(start_qposes, dtype=np.float64), np.asarray(goal_qposes, dtype=np.float64),
+                                                       time=planning_time, range=rrt_range, **kw)
+        out = [{"status": "Success", "position": p} if s == "Exact solution" else {"status": "RRTConnect failed. %s" % s}
+               for s, p in zip(status, paths)]
+        return out, stats

@@ -1,0 +1,86 @@
+"""GPU tests of the Planner mirror (mplib/planner.py surface on the accelerated path): collision queries, SRDF
+auto-generation statistic vs the oracle, joint-space planning."""
+import os
+
+import numpy as np
+import pytest
+
+from tests.common import PANDA_JOINTS, PANDA_LINKS, ROOT, SRDF, URDF, random_q
+
+pytestmark = pytest.mark.gpu
+
+
+def _planner(**kw):
+    from mplib_b200.planner import Planner
+
+    return Planner(URDF, PANDA_LINKS, PANDA_JOINTS, "panda_hand", np.ones(7), np.ones(7), srdf=SRDF, **kw)
+
+
+def test_check_for_collision_calls():
+    """examples/detect_collision.py:22-65 through Planner.check_for_self_collision / check_for_env_collision."""
+    from tests.workloads import box_surface_points
+
+    pl = _planner()
+    free = [0, 0.19, 0.0, -2.61, 0.0, 2.94, 0.78, 0, 0]
+    assert pl.check_for_self_collision(free) == []
+    hits = pl.check_for_self_collision([0, 1.36, 0, -3, -3, 3, -1, 0, 0])
+    assert hits and all(h.collision_type == "self" for h in hits)
+    # 7-long qpos: finger joints are taken from the current state (mplib/planner.py:212-216)
+    assert pl.check_for_self_collision(free[:7]) == []
+    rng = np.random.Generator(np.random.PCG64(100))
+    pl.update_point_cloud(box_surface_points(rng, 10000, (2.0, 2.0, 0.1), (0.0, 0.0, -0.1)), 1e-3)
+    assert pl.check_for_env_collision(free) == []
+    env = pl.check_for_env_collision([0, 1.5, 0, -1.5, 0, 0, 0, 0, 0])  # arm reaching below the floor
+    assert env and all(h.collision_type == "articulation_sceneobject" for h in env)
+    # the robot state is restored after every query
+    assert np.allclose(pl.robot.get_qpos(), 0.0)
+
+
+def test_pair_statistic_matches_oracle(tmp_path):
+    """generate_collision_pair's statistic (mplib/planner.py:118-163) as one batched collide_full: per-pair collision
+    counts over random configurations of a Panda WITHOUT an SRDF (46 pairs) equal the oracle's column sums."""
+    from mplib_b200.planner import Planner
+    from oracle import oracle as O
+
+    d = str(tmp_path)
+    os.symlink(os.path.join(ROOT, "data/panda/franka_description"), os.path.join(d, "franka_description"))
+    urdf = os.path.join(d, "panda_nosrdf.urdf")
+    with open(urdf, "w") as f:
+        f.write(open(URDF).read())
+    pl = Planner(urdf, PANDA_LINKS, PANDA_JOINTS, "panda_hand", np.ones(7), np.ones(7), srdf="", srdf_sample_time=20000)
+    assert os.path.exists(pl.srdf)
+    txt = open(pl.srdf).read()
+    # the written SRDF holds the always-colliding pairs only; adjacent links are already removed by the URDF parent rule
+    n_disabled = txt.count("<disable_collisions")
+    # fresh planner on the generated SRDF: its pair list = 46 - n_disabled
+    w = pl.planning_world
+    assert len(w.get_pair_metadata()) == 46 - n_disabled
+    # statistic vs oracle on the same states (full 9-dof states: all joints sampled)
+    pl2 = Planner(urdf, PANDA_LINKS, PANDA_JOINTS, "panda_hand", np.ones(7), np.ones(7), srdf=pl.srdf)
+    q = random_q(20000, 7)
+    cnt = pl2.pair_collision_counts(q)
+    desc = pl2.planning_world.get_scene_desc()
+    _, oph = O.collide_batch(desc, q.astype(np.float32).astype(np.float64), threads=8)
+    meta = pl2.planning_world.get_pair_metadata()
+    ocnt = np.zeros_like(cnt)
+    for p, c in enumerate(oph.sum(axis=0)):
+        ocnt[pl2.link_name_2_idx[meta[p][4]], pl2.link_name_2_idx[meta[p][5]]] += int(c)
+    assert np.abs(cnt - ocnt).sum() <= 20  # contact-band flips only
+    # hand x link7 survives the URDF parent rule (the hand's link parent is the geometry-less link8) and always collides:
+    # it is what the generated SRDF must disable (data/panda/panda.srdf lists it as "Adjacent")
+    assert 'link1="panda_link7" link2="panda_hand"' in txt.replace("\n", " ")
+
+
+def test_plan_qpos():
+    from tests.workloads import free_states
+
+    pl = _planner()
+    pts = free_states(None, 2, 61, pl.check_for_collision_batch)
+    start9 = np.concatenate([pts[0], [0, 0]])
+    res = pl.plan_qpos([pts[1]], start9, planning_time=10.0)
+    assert res["status"] == "Success"
+    path = res["position"]
+    assert path.shape[1] == 7 and np.allclose(path[0], pts[0], atol=1e-6) and np.allclose(path[-1], pts[1], atol=1e-6)
+    assert not pl.check_for_collision_batch(path).any()
+    out, stats = pl.plan_qpos_batch(pts[:1].repeat(4, 0), pts[1:2].repeat(4, 0), planning_time=10.0)
+    assert all(r["status"] == "Success" for r in out) and stats["n_solved"] == 4
