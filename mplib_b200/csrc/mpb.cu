@@ -342,15 +342,20 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
   std::map<std::pair<int, int>, int> bins, bins2;
   s->h_pairs.resize(n_pairs);
   s->h_pair_bin2.assign(n_pairs, -1);
-  int expand_bin = -1;
+  int expand_bin = -1, expand2_bin = -1;
   for (int p = 0; p < n_pairs; p++) {
     int a = pa[p], b = pb[p];
     if (a < 0 || a >= no || b < 0 || b >= no) return fail(MPB_ERR_INVALID, "pair index out of range");
     const bool bvh_a = s->h_objs[a].type >= MPB_GEOM_MESH, bvh_b = s->h_objs[b].type >= MPB_GEOM_MESH;
-    if (bvh_a && bvh_b)
-      return fail(MPB_ERR_UNSUPPORTED, "mesh x mesh / mesh x octree pairs are not supported by this build yet");
     int bin;
-    if (bvh_a || bvh_b) {
+    if (bvh_a && bvh_b) {
+      // mesh x mesh, mesh x octree: device convention A = mesh (triangle leaves), B = mesh or octree (pair index unchanged)
+      if (s->h_objs[a].vcnt != MPB_GEOM_TRI) std::swap(a, b);
+      if (s->h_objs[a].vcnt != MPB_GEOM_TRI)
+        return fail(MPB_ERR_UNSUPPORTED, "octree x octree pairs are not produced by the reference path and are not supported");
+      if (expand2_bin < 0) { expand2_bin = (int)bins.size(); bins[std::make_pair(-2, -2)] = expand2_bin; }
+      bin = expand2_bin;
+    } else if (bvh_a || bvh_b) {
       if (bvh_a) std::swap(a, b);  // device convention: A = shape, B = BVH object (pair index unchanged)
       if (expand_bin < 0) { expand_bin = (int)bins.size(); bins[std::make_pair(-1, -1)] = expand_bin; }
       bin = expand_bin;
@@ -409,6 +414,7 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
   s->img.n_bins = (int)bins.size();
   s->img.n_bins2 = (int)bins2.size();
   s->img.expand_bin = expand_bin;
+  s->img.expand2_bin = expand2_bin;
   s->img.pair_words = (n_pairs + 31) / 32;
   return MPB_OK;
 }
@@ -865,7 +871,9 @@ static const size_t kMaxItems = (size_t)48 << 20;   // work-queue capacity bound
 static const size_t kMaxSurvivors = (size_t)192 << 20;  // survivor-queue capacity bound (x8 B = 1.5 GiB)
 
 static int prepare_work(mpb_scene *s, long long chunk) {
-  if (s->chunk == chunk && s->wq.itf) return MPB_OK;
+  // grow-only: buffers sized for a larger pass serve a smaller one (collide calls of different sizes and planning
+  // rounds alternate on one scene; re-allocating GBs of queues between them would dominate small calls)
+  if (chunk <= s->chunk && s->wq.itf) return MPB_OK;
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
   // staging may hold up to one unused half-chunk per reservation: worst case 2 x items + one chunk per warp
   // plus one partly used reservation per warp of dense_kernel / expand_kernel
@@ -961,18 +969,22 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
-  scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, n_warps, s->sq_cap);
+  scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, n_warps, s->sq_cap);
   scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
   if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
   else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
   *launches += 3;
+  if (s->img.expand2_bin >= 0) {  // mesh x mesh / mesh x octree pairs: exact leaf tests inside the descent
+    expand2_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
+    *launches += 1;
+  }
   if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
     CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
     CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
     expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
-    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, n_warps, s->sq_cap);
+    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, n_warps, s->sq_cap);
     scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1);
     if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
@@ -1341,7 +1353,7 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   int smax = 1;
   for (int j = 0; j < D; j++) smax = std::max(smax, (int)std::ceil((double)range / space->seg[j]) + 1);
   if (smax > 4096) return fail(MPB_ERR_CAPACITY, "range / validity resolution gives too many samples per edge");
-  const int S = params->connect_steps > 0 ? std::min(params->connect_steps, 32) : 8;
+  const int S = params->connect_steps > 0 ? std::min(std::max(params->connect_steps, 2), 32) : 8;
   const long long n_states = (long long)Q * S * smax;
   rc = prepare_work(s, (n_states + 31) / 32 * 32);
   if (rc != MPB_OK) return rc;
@@ -1358,7 +1370,7 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   CU(bufs.alloc(&d_start, (size_t)Q * D));
   CU(bufs.alloc(&d_goals, (size_t)Q * max_goals * D));
   CU(bufs.alloc(&d_ngoals, (size_t)Q));
-  CU(bufs.alloc(&d_ints, (size_t)Q * 14 + 4));  // size[2] goals_used status phase flag tsel nearest reach added sol[2] iters n_steps
+  CU(bufs.alloc(&d_ints, (size_t)Q * 15 + 4));  // size[2] goals_used status phase flag tsel nearest reach added sol[2] iters n_steps nearest2
   CU(bufs.alloc(&r.target, (size_t)Q * D));
   CU(bufs.alloc(&r.edge_a, (size_t)Q * S * D));
   CU(bufs.alloc(&r.edge_b, (size_t)Q * S * D));
@@ -1371,15 +1383,16 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   r.tsel = d_ints + 6 * Q; r.nearest = d_ints + 7 * Q; r.reach = d_ints + 8 * Q; r.added = d_ints + 9 * Q;
   r.sol = d_ints + 10 * Q; r.iters = d_ints + 12 * Q;
   r.n_steps = d_ints + 13 * Q;
-  r.n_active = reinterpret_cast<unsigned *>(d_ints + 14 * Q);
+  r.nearest2 = d_ints + 14 * Q;
+  r.n_active = reinterpret_cast<unsigned *>(d_ints + 15 * Q);
   r.start = d_start; r.goals = d_goals; r.n_goals = d_ngoals;
   {
-    std::vector<int> h((size_t)Q * 14 + 4, 0);
+    std::vector<int> h((size_t)Q * 15 + 4, 0);
     for (int q = 0; q < Q; q++) {
       h[2 * q] = 1;          // tStart_ holds the start state
       h[5 * (size_t)Q + q] = 1;  // startTree_ = true
     }
-    h[14 * (size_t)Q] = Q;
+    h[15 * (size_t)Q] = Q;
     CU(cudaMemcpyAsync(d_ints, h.data(), h.size() * sizeof(int), cudaMemcpyHostToDevice, st));
     CU(cudaMemsetAsync(r.parent, 0xff, (size_t)Q * 2 * cap * sizeof(int), st));
     CU(cudaMemcpyAsync(d_start, starts, (size_t)Q * D * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -1494,7 +1507,8 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
   if (space != MPB_HOST && space != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
   if (stats) memset(stats, 0, sizeof(*stats));
   if (n == 0) return MPB_OK;
-  if (s->img.expand_bin >= 0) return fail(MPB_ERR_UNSUPPORTED, "distance to mesh / octree objects is not supported by this build yet");
+  if (s->img.expand_bin >= 0 || s->img.expand2_bin >= 0)
+    return fail(MPB_ERR_UNSUPPORTED, "distance to mesh / octree objects is not supported by this build yet");
   CU(cudaSetDevice(s->device));
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   const auto t_begin = std::chrono::steady_clock::now();
@@ -1550,7 +1564,7 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq, m, s->d_pose, s->pose_ld);
       sphere_kernel<1><<<std::min(cblocks, s->num_sms * 16), 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
       dense_kernel<1><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
-      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, (unsigned)dblocks * 8u, s->sq_cap);
+      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, -1, (unsigned)dblocks * 8u, s->sq_cap);
       scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));
       if (s->smem_verts) distance_kernel<true><<<dblocks, 256, vsm, st>>>(s->img, s->wq, dbest, s->img.n_bins);

@@ -40,7 +40,8 @@ struct SceneImg {
   const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}
   const int4 *runs;         // cull-table runs: {moving slot or -1, first entry, count, partner kind (0 fixed, 1 moving)}
   const int *pair_bin2;     // [n_pairs] bin of the leaf-level items a BVH pair expands into (-1: not a BVH pair)
-  int expand_bin;           // first-round bin that collects the BVH pairs (-1: none)
+  int expand_bin;           // first-round bin that collects the shape x BVH pairs (-1: none)
+  int expand2_bin;          // first-round bin that collects the BVH x BVH pairs (-1: none)
   int n_bins2;
   const float *linkL;   // [n_links][12] link placement in its joint frame
   const int *linkJoint; // [n_links]
@@ -463,14 +464,14 @@ __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float *_
 }
 #undef POSE
 
-__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_warps, unsigned sq_cap) {
+__global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bin2, unsigned n_warps, unsigned sq_cap) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned items = 0, units = 0;
     // unit = slice of one bin a warp owns: as large as possible (persistent lanes keep all 32 lanes busy across the
     // spread of MPR run lengths; the tail of a slice runs in the cooperative mode) while still feeding n_warps
     unsigned all = 0;
     for (int b = 0; b < n_bins; b++)
-      if (b != skip_bin) all += wq.bin_count[b];
+      if (b != skip_bin && b != skip_bin2) all += wq.bin_count[b];
     unsigned unit = MPB_UNIT_ITEMS;
     while (unit > 2u && all / unit < n_warps) unit >>= 1;  // few items (a planning round): short slices -> cooperative supports
     wq.totals[4] = unit;
@@ -479,7 +480,7 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_
       wq.unit_start[b] = units;
       const unsigned c = wq.bin_count[b];
       items += c;
-      if (b != skip_bin) units += (c + unit - 1u) / unit;  // BVH pairs go to expand_kernel instead
+      if (b != skip_bin && b != skip_bin2) units += (c + unit - 1u) / unit;  // BVH pairs go to expand_kernel / expand2_kernel instead
       wq.bin_cursor[b] = 0;
     }
     wq.bin_start[n_bins] = items;
@@ -487,6 +488,7 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, unsigned n_
     wq.totals[1] = units;
     wq.totals[3] = 0;
     wq.totals[5] = 0;  // expand_kernel's item ticket
+    wq.totals[7] = 0;  // expand2_kernel's item ticket
     if (wq.totals[0] > wq.cap || wq.totals[6] > sq_cap) wq.totals[2] = 1u;  // queue overflow: the host redoes the pass in smaller chunks
     atomicAdd(wq.counters, (unsigned long long)items);
   }
@@ -1095,5 +1097,154 @@ __global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, uns
     }
     __syncwarp();
     }  // sub-items of the ticket
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- BVH x BVH
+// Mesh x mesh (BVHModel links of a `convex=False` robot, mesh obstacles) and mesh x octree pairs: replaces
+// MeshCollisionTraversalNodeOBBRSS (recursive OBB-OBB descent, triangle-triangle leaves) and
+// OcTreeSolver::OcTreeMeshIntersectRecurse (box-triangle leaves) behind ::fcl::collide.  Warp per item; the
+// frontier of (node of A, node of B) pairs lives in a shared-memory stack, 32 pairs per trip.  The leaf tests are
+// exact closed forms evaluated in place (no second narrowphase round): the verdict is "some primitive pair
+// intersects", which is what FCL returns with num_max_contacts = 1.
+#define MPB_EXP2_STACK 768
+
+// segment pq pierces triangle abc (closed sets)
+__device__ __forceinline__ bool seg_tri_hit(V3 p, V3 q, V3 a, V3 b, V3 c) {
+  const V3 ab = b - a, ac = c - a, n = cross(ab, ac), pq = q - p, ap = p - a;
+  const float dn = dot(n, pq);
+  if (dn == 0.f) return false;
+  const float t = -dot(n, ap) / dn;
+  if (t < 0.f || t > 1.f) return false;
+  const V3 x = v3(fmaf(t, pq.x, p.x) - a.x, fmaf(t, pq.y, p.y) - a.y, fmaf(t, pq.z, p.z) - a.z);
+  const float d00 = dot(ab, ab), d01 = dot(ab, ac), d11 = dot(ac, ac), d20 = dot(x, ab), d21 = dot(x, ac);
+  const float den = d00 * d11 - d01 * d01;
+  if (den == 0.f) return false;
+  const float v = (d11 * d20 - d01 * d21) / den, w = (d00 * d21 - d01 * d20) / den;
+  return v >= 0.f && w >= 0.f && v + w <= 1.f;
+}
+__device__ __forceinline__ bool tri_tri_hit(const V3 *A, const V3 *B) {
+#pragma unroll
+  for (int e = 0; e < 3; e++) {
+    if (seg_tri_hit(A[e], A[(e + 1) % 3], B[0], B[1], B[2])) return true;
+    if (seg_tri_hit(B[e], B[(e + 1) % 3], A[0], A[1], A[2])) return true;
+  }
+  return false;
+}
+// axis-aligned box (centre c, half h) vs triangle, 13-axis SAT (closed sets touch = hit)
+__device__ __forceinline__ bool box_tri_hit(V3 c, V3 h, V3 p0, V3 p1, V3 p2) {
+  const V3 v0 = p0 - c, v1 = p1 - c, v2 = p2 - c;
+  const V3 e0 = v1 - v0, e1 = v2 - v1, e2 = v0 - v2;
+  if (fminf(v0.x, fminf(v1.x, v2.x)) > h.x || fmaxf(v0.x, fmaxf(v1.x, v2.x)) < -h.x) return false;
+  if (fminf(v0.y, fminf(v1.y, v2.y)) > h.y || fmaxf(v0.y, fmaxf(v1.y, v2.y)) < -h.y) return false;
+  if (fminf(v0.z, fminf(v1.z, v2.z)) > h.z || fmaxf(v0.z, fmaxf(v1.z, v2.z)) < -h.z) return false;
+  const V3 n = cross(e0, e1);
+  if (fabsf(dot(n, v0)) > h.x * fabsf(n.x) + h.y * fabsf(n.y) + h.z * fabsf(n.z)) return false;
+  const V3 es[3] = {e0, e1, e2};
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const V3 e = es[i];
+    // axes (1,0,0) x e, (0,1,0) x e, (0,0,1) x e
+    const V3 ax[3] = {v3(0.f, -e.z, e.y), v3(e.z, 0.f, -e.x), v3(-e.y, e.x, 0.f)};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const float q0 = dot(ax[k], v0), q1 = dot(ax[k], v1), q2 = dot(ax[k], v2);
+      const float r = h.x * fabsf(ax[k].x) + h.y * fabsf(ax[k].y) + h.z * fabsf(ax[k].z);
+      if (fminf(q0, fminf(q1, q2)) > r || fmaxf(q0, fmaxf(q1, q2)) < -r) return false;
+    }
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
+                                                      unsigned int *__restrict__ pair_bits) {
+  __shared__ int2 s_stack[4][MPB_EXP2_STACK];
+  const int eb = img.expand2_bin;
+  if (eb < 0) return;
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int2 *stack = s_stack[warp];
+  const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
+  for (;;) {
+    unsigned it = 0;
+    if (lane == 0) it = atomicAdd(&wq.totals[7], 1u);
+    it = first + __shfl_sync(FULL, it, 0);
+    if (it >= end) break;
+    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
+                                 : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
+    if (known) continue;
+    const DevPair pr = img.pairs[p];
+    const DevObject &A = img.objs[pr.a];  // mesh
+    const DevObject &B = img.objs[pr.b];  // mesh or octree
+    float R[9], t[3];  // B in A
+#pragma unroll
+    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
+#pragma unroll
+    for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + it];
+    const int leaf_b = B.vcnt;  // MPB_GEOM_TRI or MPB_GEOM_VBOX (A's leaves are triangles)
+    int sp = 1;
+    if (lane == 0) stack[0] = make_int2(A.voff, B.voff);
+    __syncwarp();
+    bool hit = false;
+    while (sp > 0) {
+      const int take = sp > MPB_EXP2_STACK - 64 ? 1 : min(sp, 32);
+      int2 np = make_int2(-1, -1);
+      if ((int)lane < take) np = stack[sp - 1 - (int)lane];
+      sp -= take;
+      __syncwarp();
+      bool pass = false;
+      DevBvhNode na, nb;
+      na.left = nb.left = 0; na.right = nb.right = 0;
+      if (np.x >= 0) {
+        na = img.nodes[np.x];
+        nb = img.nodes[np.y];
+        float tt[3];
+#pragma unroll
+        for (int r = 0; r < 3; r++) tt[r] = fmaf(R[3 * r], nb.c[0], fmaf(R[3 * r + 1], nb.c[1], fmaf(R[3 * r + 2], nb.c[2], t[r]))) - na.c[r];
+        pass = !obb_disjoint(R, tt, na.h, nb.h);
+      }
+      const bool both_leaf = na.left < 0 && nb.left < 0;
+      const bool inner = pass && !both_leaf;
+      const unsigned im = __ballot_sync(FULL, inner);
+      if (inner) {
+        // descend the inner node (the larger one when both are inner)
+        const float sa = na.h[0] + na.h[1] + na.h[2], sb = nb.h[0] + nb.h[1] + nb.h[2];
+        const bool split_a = nb.left < 0 || (na.left >= 0 && sa >= sb);
+        const int pos = sp + 2 * __popc(im & ((1u << lane) - 1u));
+        if (pos + 1 < MPB_EXP2_STACK) {
+          stack[pos] = split_a ? make_int2(na.left, np.y) : make_int2(np.x, nb.left);
+          stack[pos + 1] = split_a ? make_int2(na.right, np.y) : make_int2(np.x, nb.right);
+        } else atomicAdd(&wq.counters[2], 1ull);  // dropped subtree pair: reported as a capped item, never silent
+      }
+      sp = min(sp + 2 * __popc(im), MPB_EXP2_STACK);
+      __syncwarp();
+      bool lhit = false;
+      if (pass && both_leaf) {
+        const int fa = ~na.left, fb = ~nb.left;
+        for (int i = 0; i < na.right && !lhit; i++) {
+          const float4 a0 = __ldg(img.prims + 3 * (fa + i)), a1 = __ldg(img.prims + 3 * (fa + i) + 1), a2 = __ldg(img.prims + 3 * (fa + i) + 2);
+          const V3 TA[3] = {v3(a0.x, a0.y, a0.z), v3(a1.x, a1.y, a1.z), v3(a2.x, a2.y, a2.z)};
+          for (int j = 0; j < nb.right && !lhit; j++) {
+            const float4 b0 = __ldg(img.prims + 3 * (fb + j)), b1 = __ldg(img.prims + 3 * (fb + j) + 1);
+            if (leaf_b == MPB_GEOM_TRI) {
+              const float4 b2 = __ldg(img.prims + 3 * (fb + j) + 2);
+              const V3 TB[3] = {rot(R, v3(b0.x, b0.y, b0.z)) + v3(t[0], t[1], t[2]), rot(R, v3(b1.x, b1.y, b1.z)) + v3(t[0], t[1], t[2]),
+                                rot(R, v3(b2.x, b2.y, b2.z)) + v3(t[0], t[1], t[2])};
+              lhit = tri_tri_hit(TA, TB);
+            } else {  // triangle of A into B's frame, box stays axis-aligned
+              const V3 tv = v3(t[0], t[1], t[2]);
+              lhit = box_tri_hit(v3(b0.x, b0.y, b0.z), v3(b1.x, b1.y, b1.z), rot_t(R, TA[0] - tv), rot_t(R, TA[1] - tv), rot_t(R, TA[2] - tv));
+            }
+          }
+        }
+      }
+      if (__any_sync(FULL, lhit)) { hit = true; break; }
+    }
+    if (hit && lane == 0) {
+      atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
+      if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
+    }
+    __syncwarp();
   }
 }

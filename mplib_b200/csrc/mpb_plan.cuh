@@ -134,10 +134,11 @@ struct RrtState {
   const int *n_goals;  // [Q]
   int *goals_used;     // [Q]  pis_.getSampledGoalsCount()
   int *status;         // [Q]  MPB_RRT_*
-  int *phase;          // [Q]  0 = nothing pending, 1 = first growTree of an iteration pending, 2 = connect steps pending
+  int *phase;          // [Q]  0 = nothing pending, 3 = extend edge + first connect steps pending, 2 = further connect steps pending
   int *flag_start;     // [Q]  startTree_
   int *tsel;           // [Q]  tree the pending edges grow
   int *nearest;        // [Q]  nmotion of the first pending edge
+  int *nearest2;       // [Q]  phase 3: nmotion of the first connect step (other tree)
   int *reach;          // [Q]  the last pending edge ends on the target
   int *n_steps;        // [Q]  pending sub-edges (1 .. S)
   int *added;          // [Q]  addedMotion (index in tree 1 - tsel while connecting)
@@ -165,13 +166,56 @@ __device__ __forceinline__ void rrt_blank_edges(float *ea, float *eb, int n, int
   for (int i = lane; i < n; i += 32) { ea[i] = nanv; eb[i] = nanv; }
 }
 
+// nearest node of a tree to `tg` (L1 over the 1-D subspaces, SO(2) wrap); ties -> lowest index
+__device__ __forceinline__ int rrt_nearest(const float *base, int n, int D, const float *tg, const SpaceDesc &sp, int lane, float *best_out) {
+  float best = FLT_MAX;
+  int bi = 0x7fffffff;
+  for (int i = lane; i < n; i += 32) {
+    float d = 0.f;
+    for (int j = 0; j < D; j++) d += fabsf(ss_delta(base[(size_t)i * D + j], tg[j], sp.so2[j] != 0));
+    if (d < best) { best = d; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  *best_out = best;
+  return bi;
+}
+
+// Sub-edges of the walk from node `from` towards `tg` in steps of `range` (the last one lands on `tg`): at most
+// `max_steps` of them into slots slot0.. of (ea, eb); the other slots up to slot_end are blanked.  -> steps written
+__device__ __forceinline__ int rrt_emit_walk(float *ea, float *eb, int slot0, int slot_end, int max_steps, const float *from, float best,
+                                             const float *tg, float range, int D, const SpaceDesc &sp, int lane, bool *reach) {
+  const int k_total = best > range ? (int)ceilf(best / range) : 1;
+  const int ns = min(max_steps, k_total);
+  *reach = ns == k_total;
+  const float nanv = __int_as_float(0x7fc00000);
+  for (int idx = lane; idx < (slot_end - slot0) * D; idx += 32) {
+    const int k = idx / D, j = idx - k * D;
+    const float a = from[j];
+    const bool so2 = sp.so2[j] != 0;
+    // point k of the walk (k = 0: the start node)
+    const float pk = k == 0 ? a : ((k == k_total) ? tg[j] : ss_interp(a, tg[j], (float)k * range / best, so2));
+    const float pk1 = (k + 1 >= k_total) ? tg[j] : ss_interp(a, tg[j], (float)(k + 1) * range / best, so2);
+    ea[slot0 * D + idx] = k < ns ? pk : nanv;
+    eb[slot0 * D + idx] = k < ns ? pk1 : nanv;
+  }
+  return ns;
+}
+
 // One warp per query.  A round consumes the verdicts of the query's pending sub-edges and emits the next ones.
-// The first growTree() of an iteration emits ONE sub-edge (extend towards the random state).  The connect loop
-// `while (gsc == ADVANCED) gsc = growTree(otherTree, tgi, rmotion)` walks the straight line from the nearest node
-// of the other tree towards the new state in steps of `range` -- after every ADVANCED step the node just added is
-// the nearest one (its distance to the target dropped by exactly `range`, every other node is at least as far as
-// the previous nearest) -- so up to S of those steps are emitted at once and validated speculatively; the valid
-// prefix is added node by node exactly as the sequential loop would, the first invalid step is the TRAPPED call.
+// An iteration of RRTConnect::solve is  growTree(tree, rstate)  followed, unless TRAPPED, by the connect loop
+// `while (gsc == ADVANCED) gsc = growTree(otherTree, tgi, rmotion)`.  Both are emitted in ONE round (phase 3): slot 0
+// carries the extend edge; its end state q_new is known before it is validated, so slots 1.. carry the first steps
+// of the connect walk from the other tree's nearest node towards q_new.  The walk is a straight line in steps of
+// `range` -- after every ADVANCED step the node just added is the nearest one (its distance to the target dropped by
+// exactly `range`, every other node is at least as far as the previous nearest) -- so its steps can be validated
+// speculatively; the valid prefix is added node by node exactly as the sequential loop would, the first invalid step
+// is the TRAPPED call, and a TRAPPED extend discards the speculative connect results.  A walk longer than the slots
+// continues in the following rounds (phase 2) with all S slots.
 __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc sp, float range, const unsigned *__restrict__ verdict_bits) {
   const unsigned FULL = 0xffffffffu;
   const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -180,23 +224,42 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
   if (r.status[q] != MPB_RRT_ACTIVE) return;
   const int D = r.dim, S = r.S;
   float *ea = r.edge_a + (size_t)q * S * D, *eb = r.edge_b + (size_t)q * S * D, *tg = r.target + (size_t)q * D;
-  int phase = r.phase[q];
-  int T = r.tsel[q];
+  const int phase = r.phase[q];
+  int T = r.tsel[q];  // phase 3: the tree of the extend edge; phase 2: the connecting tree
   bool new_iter = phase == 0;
   if (phase != 0) {
     // ---- verdicts of the pending sub-edges: sub-edge k is invalid if any of its samples collides
-    const int ns = r.n_steps[q];
+    const int ns_all = r.n_steps[q];
     unsigned bad = 0;
-    for (int k = lane; k < ns * r.smax; k += 32) {
+    for (int k = lane; k < ns_all * r.smax; k += 32) {
       const unsigned s = (unsigned)q * S * r.smax + k;
       if ((verdict_bits[s >> 5] >> (s & 31)) & 1u) bad |= 1u << (k / r.smax);
     }
     bad = __reduce_or_sync(FULL, bad);
-    const int n_add = bad ? (__ffs(bad) - 1) : ns;  // valid prefix
-    if (lane == 0) r.iters[q] += n_add + (bad ? 1 : 0);
-    __syncwarp();  // the sampling counter below reads it
-    if (n_add == 0) new_iter = true;  // TRAPPED at the first step
-    else {
+    int first_slot = 0, calls = 0;
+    bool go = true;
+    if (phase == 3) {
+      calls = 1;
+      if (bad & 1u) { go = false; new_iter = true; }  // the extend is TRAPPED: the speculative connect steps are void
+      else {
+        const int n = r.size[q * 2 + T];
+        if (n + 1 > r.cap) {
+          if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
+          rrt_blank_edges(ea, eb, S * D, lane);
+          return;
+        }
+        float *node = r.nodes + (((size_t)q * 2 + T) * r.cap + n) * D;
+        for (int j = lane; j < D; j += 32) node[j] = eb[j];
+        if (lane == 0) { r.parent[((size_t)q * 2 + T) * r.cap + n] = r.nearest[q]; r.size[q * 2 + T] = n + 1; r.added[q] = n; }
+        T = 1 - T;  // the connect loop grows the other tree
+        first_slot = 1;
+        bad >>= 1;
+      }
+    }
+    if (go) {
+      const int ns = ns_all - first_slot;
+      const int n_add = bad ? (__ffs(bad) - 1) : ns;  // valid prefix of the connect walk
+      calls += n_add + (bad ? 1 : 0);
       const int n = r.size[q * 2 + T];
       if (n + n_add > r.cap) {
         if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
@@ -204,18 +267,14 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
         return;
       }
       float *node = r.nodes + (((size_t)q * 2 + T) * r.cap + n) * D;
-      for (int j = lane; j < n_add * D; j += 32) node[j] = eb[j];
-      for (int k = lane; k < n_add; k += 32) r.parent[((size_t)q * 2 + T) * r.cap + n + k] = k == 0 ? r.nearest[q] : n + k - 1;
-      if (lane == 0) r.size[q * 2 + T] = n + n_add;
-      const int n_last = n + n_add - 1;
-      if (phase == 1) {  // first tree advanced: now connect the other tree to the new state
-        for (int j = lane; j < D; j += 32) tg[j] = eb[j];
-        if (lane == 0) { r.added[q] = n_last; r.tsel[q] = 1 - T; r.phase[q] = 2; }
-        T = 1 - T;
-        phase = 2;
-      } else if (n_add == ns && r.reach[q]) {  // REACHED: the trees meet
+      for (int j = lane; j < n_add * D; j += 32) node[j] = eb[first_slot * D + j];
+      const int near_c = phase == 3 ? r.nearest2[q] : r.nearest[q];
+      for (int k = lane; k < n_add; k += 32) r.parent[((size_t)q * 2 + T) * r.cap + n + k] = k == 0 ? near_c : n + k - 1;
+      if (lane == 0 && n_add) r.size[q * 2 + T] = n + n_add;
+      __syncwarp();
+      if (n_add == ns && r.reach[q]) {  // REACHED: the trees meet
         if (lane == 0) {
-          const int m_first = r.added[q], m_other = n_last;  // first tree = 1 - T
+          const int m_first = r.added[q], m_other = n + n_add - 1;  // first tree = 1 - T
           int is = T == 0 ? m_other : m_first, ig = T == 0 ? m_first : m_other;
           const int ps = r.parent[((size_t)q * 2 + 0) * r.cap + is];
           if (ps >= 0) is = ps;  // one step back so the shared state is not duplicated on the path
@@ -223,13 +282,16 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
           r.sol[q * 2] = is;
           r.sol[q * 2 + 1] = ig;
           r.status[q] = MPB_RRT_SOLVED;
+          r.iters[q] += calls;
           atomicSub(r.n_active, 1u);
         }
         rrt_blank_edges(ea, eb, S * D, lane);
         return;
-      } else if (n_add < ns) new_iter = true;  // ADVANCED n_add times, then TRAPPED
-      __syncwarp();
+      }
+      if (n_add < ns) new_iter = true;  // ADVANCED n_add times, then TRAPPED
     }
+    if (lane == 0) r.iters[q] += calls;
+    __syncwarp();  // the sampling counter below reads it
   }
   if (new_iter) {
     // ---- head of the solve loop: pick the tree, maybe admit another goal, sample
@@ -253,42 +315,35 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
     }
     const unsigned ctr = (unsigned)r.iters[q];
     for (int j = lane; j < D; j += 32) tg[j] = fmaf(sp.hi[j] - sp.lo[j], rrt_uniform(r.seed, (unsigned)q, ctr, (unsigned)j), sp.lo[j]);
-    if (lane == 0) { r.flag_start[q] = !fs; r.tsel[q] = T; r.phase[q] = 1; }
-    phase = 1;
     __syncwarp();
+    // ---- growTree(tree, rstate): the extend edge into slot 0 ...
+    const float *base = r.nodes + ((size_t)q * 2 + T) * r.cap * D;
+    float best;
+    const int bi = rrt_nearest(base, r.size[q * 2 + T], D, tg, sp, lane, &best);
+    bool reach0;
+    rrt_emit_walk(ea, eb, 0, 1, 1, base + (size_t)bi * D, best, tg, range, D, sp, lane, &reach0);
+    __syncwarp();
+    for (int j = lane; j < D; j += 32) tg[j] = eb[j];  // q_new: the target of the connect loop
+    __syncwarp();
+    // ---- ... and the first steps of the connect walk of the other tree towards q_new into slots 1..
+    const float *base2 = r.nodes + ((size_t)q * 2 + (1 - T)) * r.cap * D;
+    float best2;
+    const int bi2 = rrt_nearest(base2, r.size[q * 2 + (1 - T)], D, tg, sp, lane, &best2);
+    bool reach2;
+    const int ns2 = rrt_emit_walk(ea, eb, 1, S, S - 1, base2 + (size_t)bi2 * D, best2, tg, range, D, sp, lane, &reach2);
+    if (lane == 0) {
+      r.flag_start[q] = !fs; r.tsel[q] = T; r.phase[q] = 3;
+      r.nearest[q] = bi; r.nearest2[q] = bi2; r.reach[q] = reach2 ? 1 : 0; r.n_steps[q] = 1 + ns2;
+    }
+    return;
   }
-  // ---- growTree, first half: nearest neighbour in tree T and the state(s) to add
-  const int n = r.size[q * 2 + T];
+  // ---- the connect walk continues (phase 2): nearest neighbour of the connecting tree and the next S steps
   const float *base = r.nodes + ((size_t)q * 2 + T) * r.cap * D;
-  float best = FLT_MAX;
-  int bi = 0x7fffffff;
-  for (int i = lane; i < n; i += 32) {
-    float d = 0.f;
-    for (int j = 0; j < D; j++) d += fabsf(ss_delta(base[(size_t)i * D + j], tg[j], sp.so2[j] != 0));
-    if (d < best) { best = d; bi = i; }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const float ob = __shfl_xor_sync(FULL, best, o);
-    const int oi = __shfl_xor_sync(FULL, bi, o);
-    if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-  }
-  // steps of length `range` along the line nearest -> target; the last one lands on the target itself
-  const int k_total = best > range ? (int)ceilf(best / range) : 1;
-  const int ns = min(phase == 2 ? S : 1, k_total);
-  const bool reach = ns == k_total;
-  for (int idx = lane; idx < S * D; idx += 32) {
-    const int k = idx / D, j = idx - k * D;
-    const float a = base[(size_t)bi * D + j];
-    const bool so2 = sp.so2[j] != 0;
-    // point k of the walk (k = 0: the nearest node); slots past the pending steps are blanked (NaN)
-    const float pk = k == 0 ? a : ((k == k_total) ? tg[j] : ss_interp(a, tg[j], (float)k * range / best, so2));
-    const float pk1 = (k + 1 >= k_total) ? tg[j] : ss_interp(a, tg[j], (float)(k + 1) * range / best, so2);
-    const float nanv = __int_as_float(0x7fc00000);
-    ea[idx] = k < ns ? pk : nanv;
-    eb[idx] = k < ns ? pk1 : nanv;
-  }
-  if (lane == 0) { r.nearest[q] = bi; r.reach[q] = reach ? 1 : 0; r.n_steps[q] = ns; }
+  float best;
+  const int bi = rrt_nearest(base, r.size[q * 2 + T], D, tg, sp, lane, &best);
+  bool reach;
+  const int ns = rrt_emit_walk(ea, eb, 0, S, S, base + (size_t)bi * D, best, tg, range, D, sp, lane, &reach);
+  if (lane == 0) { r.tsel[q] = T; r.phase[q] = 2; r.nearest[q] = bi; r.reach[q] = reach ? 1 : 0; r.n_steps[q] = ns; }
 }
 
 // Solution path of every solved query: start chain (root first) then goal chain (towards its root).

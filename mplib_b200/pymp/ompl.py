@@ -135,7 +135,15 @@ class OMPLPlanner:
             print("invalid start state!! (collision)")
             starts[i] = self.random_sample_nearby(starts[i])
         # goal images; invalid goal states are skipped as pis_.nextGoal() does
-        imgs = [self.goal_images(gs) for gs in goal_states]
+        # fast path: a goal none of whose revolute coordinates has a +-2*pi image inside the limits is its own only image
+        imgs = []
+        for gs in goal_states:
+            if len(gs) == 1:
+                g = np.asarray(gs[0], dtype=np.float64).reshape(-1)
+                if not (self.is_revolute & ((g - 2 * PI > self.lower_joint_limits) | (g + 2 * PI < self.upper_joint_limits))).any():
+                    imgs.append([g])
+                    continue
+            imgs.append(self.goal_images(gs))
         flat = np.asarray([g for im in imgs for g in im], dtype=np.float64).reshape(-1, self.dim)
         ok = self._is_valid(flat) if len(flat) else np.zeros(0, bool)
         k = 0

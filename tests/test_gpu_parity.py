@@ -193,3 +193,72 @@ def test_golden_c5_two_panda():
     from tests.workloads import c5_world
 
     _golden_parity(c5_world(), "c5_two_panda_4k.npz", 20)
+
+
+# ---------------------------------------------------------------------------------------------- mesh links (convex=False)
+_DIRS26 = np.array([[x, y, z] for x in (-1, 0, 1) for y in (-1, 0, 1) for z in (-1, 0, 1) if (x, y, z) != (0, 0, 0)], dtype=np.float64)
+_DIRS26 /= np.linalg.norm(_DIRS26, axis=1, keepdims=True)
+
+
+def _in_band_by_perturbation(desc, poses, a, b, step=1.13e-4):
+    """Signed distance is 1-Lipschitz in a translation of one object, so a pair whose oracle verdict flips under
+    a translation of `step` (26 directions; 1.13e-4 = 1e-4 / cos of the largest angle to the nearest direction) has
+    |signed distance| < step.  Used where the oracle has no signed-distance routine (mesh x mesh, mesh x octree)."""
+    from oracle import oracle as O
+
+    base = O.object_collide(desc, a, poses[a], b, poses[b])
+    for d in _DIRS26:
+        Tb = poses[b].copy()
+        Tb[:, 3] += step * d
+        if O.object_collide(desc, a, poses[a], b, Tb) != base:
+            return True
+    return False
+
+
+def _mesh_parity(world, q, max_mismatch):
+    from oracle import oracle as O
+
+    c = world._sync()
+    desc = c["dev"].desc
+    v, ph, st = c["dev"].collide(q, want_pairs=True, stats=True)
+    qd = q.astype(np.float32).astype(np.float64)
+    ov, oph = O.collide_batch(desc, qd, threads=8)
+    mism = np.argwhere(ph != oph)
+    bad = []
+    for i, p in mism:
+        poses = O.object_poses(desc, qd[i:i + 1])[0]
+        if not _in_band_by_perturbation(desc, poses, int(desc.pair_a[p]), int(desc.pair_b[p])):
+            bad.append((int(i), int(p), desc.object_names[desc.pair_a[p]], desc.object_names[desc.pair_b[p]], bool(ph[i, p]), bool(oph[i, p])))
+    print(f"pairs={desc.n_pairs} mismatches={len(mism)} out-of-band={len(bad)} collide-rate={ov.mean():.3f} stats={st}")
+    assert not bad, bad[:10]
+    assert len(mism) <= max_mismatch
+    assert np.array_equal(v, ph.any(axis=1))
+    assert st["narrow_capped"] == 0
+    v2, _ = c["dev"].collide(q, want_pairs=False)
+    assert np.array_equal(v2, v)
+    return ov
+
+
+def test_mesh_links_self_collision():
+    """BVHModel links (`convex=False`, tests/test_articulated_model.cpp:14-15): mesh x mesh self pairs."""
+    w = make_panda_world(convex=False)
+    ov = _mesh_parity(w, random_q(600, 31), 12)
+    assert 0.01 < ov.mean() < 0.5
+
+
+def test_mesh_links_vs_mesh_octree_and_primitives():
+    """mesh links against a mesh obstacle (mesh x mesh), a point cloud (octree x mesh) and primitives."""
+    import os
+
+    from mplib_b200.pymp import fcl
+    from tests.common import ROOT
+    from tests.workloads import add_c3_primitives, box_surface_points
+
+    w = make_panda_world(convex=False)
+    m = fcl.load_mesh_as_BVH(os.path.join(ROOT, "data/panda/franka_description/meshes/collision/link0.stl"))
+    w.add_normal_object("mesh_obstacle", fcl.CollisionObject(m, [0.45, 0.2, 0.3], [1, 0, 0, 0]))
+    rng = np.random.Generator(np.random.PCG64(4))
+    w.add_point_cloud("cloud", box_surface_points(rng, 4000, (0.8, 0.8, 0.05), (0.56, 0, -0.025)), 0.01)
+    add_c3_primitives(w, 2)
+    ov = _mesh_parity(w, random_q(300, 32), 12)
+    assert ov.mean() > 0.05
