@@ -234,6 +234,17 @@ int mpb_scene_info(const mpb_scene *scene, int32_t *n_pairs, int32_t *state_dim,
  * (the in-run confirmation of SMs x 128 x 2 x f that BASELINE.md 2 asks for; no reference counterpart). */
 int mpb_fp32_peak(int device, float *tflops);
 
+/* PinocchioModelTpl::computeIKCLIK (src/pinocchio_model.cpp:377-432) for n independent problems, double precision:
+ * damped least squares on the 6 x nv joint Jacobian of `link`'s parent joint until |log6 error| < eps or max_iter.
+ * The unknowns are the scene's batch state (state_dim joints); joints outside it keep their q_base value.
+ *   link     user link index (as mpb_fk_batch orders its output)
+ *   poses    [n][7] goal pose of the link: x y z, qw qx qy qz
+ *   q_init   [n][state_dim]        mask [state_dim] or NULL: 1 = joint frozen (its Jacobian column is zeroed)
+ *   q_out    [n][state_dim]        success [n] 0/1        err [n][6] last log6 error (linear, angular)
+ * Reference defaults: eps 1e-5, max_iter 1000, dt 0.1, damp 1e-12 (python/pybind_pinocchio.hpp:54-57).  Host pointers. */
+int mpb_ik_clik_batch(mpb_scene *scene, int32_t link, const double *poses, const double *q_init, const uint8_t *mask, int64_t n,
+                      double eps, int32_t max_iter, double dt, double damp, double *q_out, uint8_t *success, double *err);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,7 +55,7 @@ LIB_PATH = os.environ.get("MPB_LIB_PATH") or os.path.join(_HERE, "libmpb.so")  #
 SYMBOLS = [
     "mpb_last_error", "mpb_device_count", "mpb_scene_create", "mpb_scene_destroy", "mpb_scene_set_q_base",
     "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
-    "mpb_check_motion_batch", "mpb_rrtconnect_batch", "mpb_distance_batch",
+    "mpb_check_motion_batch", "mpb_rrtconnect_batch", "mpb_distance_batch", "mpb_ik_clik_batch",
 ]
 
 _lib = None
@@ -94,6 +94,8 @@ def load():
     lib.mpb_rrtconnect_batch.argtypes = [C.c_void_p, C.POINTER(MpbSpaceDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                          C.c_int64, C.POINTER(MpbRrtParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.POINTER(MpbRrtStats)]
+    lib.mpb_ik_clik_batch.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int32,
+                                      C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 
@@ -235,6 +237,25 @@ class DeviceScene:
                                            _ptr(status), _ptr(plen), _ptr(paths), C.byref(st)))
         out = [paths[i, : plen[i]].astype(np.float64) for i in range(Q)]
         return status, out, st.as_dict()
+
+    def ik_clik(self, link, poses, q_init, mask=None, eps=1e-5, max_iter=1000, dt=1e-1, damp=1e-12):
+        """Batched computeIKCLIK: poses [n, 7], q_init [n, D] -> (q [n, D] float64, success bool[n], err [n, 6])."""
+        poses = np.ascontiguousarray(np.asarray(poses, dtype=np.float64).reshape(-1, 7))
+        q0 = np.ascontiguousarray(np.asarray(q_init, dtype=np.float64))
+        if q0.ndim != 2 or q0.shape[1] != self.state_dim or q0.shape[0] != poses.shape[0]:
+            raise RuntimeError("Qpos user2pinocchio failed")
+        n = q0.shape[0]
+        m = None
+        if mask is not None and len(mask):
+            m = np.ascontiguousarray(np.asarray(mask, dtype=np.uint8))
+            if m.shape[0] != self.state_dim:
+                raise RuntimeError("mask length does not match the number of joints")
+        q = np.zeros((n, self.state_dim), dtype=np.float64)
+        ok = np.zeros(n, dtype=np.uint8)
+        err = np.zeros((n, 6), dtype=np.float64)
+        _check(load().mpb_ik_clik_batch(self._h, int(link), _ptr(poses), _ptr(q0), _ptr(m), n, float(eps), int(max_iter), float(dt),
+                                        float(damp), _ptr(q), _ptr(ok), _ptr(err)))
+        return q, ok.astype(bool), err
 
     def fk_raw(self, q_ptr, n, poses_ptr, space=MPB_HOST, stream=None):
         _check(load().mpb_fk_batch(self._h, _ptr(q_ptr), int(n), _ptr(poses_ptr), space, _ptr(stream)))

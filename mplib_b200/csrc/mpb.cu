@@ -37,6 +37,9 @@ struct mpb_scene {
   std::vector<DevObject> h_objs;
   std::vector<DevPair> h_pairs;
   std::vector<int> joint_qidx;
+  // double-precision copy of the kinematic model for the IK entry point
+  std::vector<double> h_jP64, h_jax64, h_qbase64, h_linkL64;
+  std::vector<int> h_jtype, h_jparent, h_linkJoint;
   std::vector<int> obj_key;
   int nq_full = 0;
   // device image
@@ -480,6 +483,13 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   }
   s->h_joints.resize(d->n_joints);
   s->joint_qidx.assign(d->joint_qidx, d->joint_qidx + d->n_joints);
+  s->h_jP64.assign(d->joint_placement, d->joint_placement + (size_t)12 * d->n_joints);
+  s->h_jax64.assign(d->joint_axis, d->joint_axis + (size_t)3 * d->n_joints);
+  s->h_jtype.assign(d->joint_type, d->joint_type + d->n_joints);
+  s->h_jparent.assign(d->joint_parent, d->joint_parent + d->n_joints);
+  s->h_qbase64.assign(d->q_base, d->q_base + d->nq_full);
+  s->h_linkL64.assign(d->link_placement, d->link_placement + (size_t)12 * d->n_links);
+  s->h_linkJoint.assign(d->link_joint, d->link_joint + d->n_links);
   for (int j = 0; j < d->n_joints; j++) {
     DevJoint &J = s->h_joints[j];
     for (int k = 0; k < 12; k++) J.P[k] = (float)d->joint_placement[12 * j + k];
@@ -839,6 +849,7 @@ extern "C" int mpb_scene_set_q_base(mpb_scene *s, const double *q_base, int32_t 
   if (nq_full != s->nq_full) return fail(MPB_ERR_INVALID, "q_base length does not match the scene");
   CU(cudaSetDevice(s->device));
   for (size_t j = 0; j < s->h_joints.size(); j++) s->h_joints[j].qconst = (float)q_base[s->joint_qidx[j]];
+  s->h_qbase64.assign(q_base, q_base + nq_full);
   CU(cudaStreamSynchronize(s->stream));
   if (!s->h_joints.empty())
     CU(cudaMemcpy(s->d_joints, s->h_joints.data(), s->h_joints.size() * sizeof(DevJoint), cudaMemcpyHostToDevice));
@@ -1610,5 +1621,68 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     stats->gpu_ms = ms_cull + ms_narrow;
     stats->host_ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
   }
+  return MPB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ inverse kinematics
+#include "mpb_ik.cuh"
+
+extern "C" int mpb_ik_clik_batch(mpb_scene *s, int32_t link, const double *poses, const double *q_init, const uint8_t *mask, int64_t n,
+                                 double eps, int32_t max_iter, double dt, double damp, double *q_out, uint8_t *success, double *err) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!poses || !q_init || !q_out || !success || !err))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (link < 0 || link >= (int)s->h_linkJoint.size()) return fail(MPB_ERR_INVALID, "The link index is out of bound!");
+  if (n == 0) return MPB_OK;
+  const int D = s->img.state_dim;
+  // chain of movable joints from the root to the link's parent joint (model indices, 0 = universe)
+  std::vector<int> chain;
+  for (int j = s->h_linkJoint[link]; j != 0; j = s->h_jparent[j - 1]) chain.push_back(j);
+  std::reverse(chain.begin(), chain.end());
+  if (chain.empty()) return fail(MPB_ERR_INVALID, "the link is fixed to the world: nothing to solve for");
+  if ((int)chain.size() > MPB_IK_MAX_CHAIN) return fail(MPB_ERR_CAPACITY, "kinematic chain longer than MPB_IK_MAX_CHAIN");
+  std::vector<IkJoint> hc(chain.size());
+  for (size_t c = 0; c < chain.size(); c++) {
+    const int j = chain[c] - 1;
+    IkJoint &K = hc[c];
+    memcpy(K.P, s->h_jP64.data() + 12 * (size_t)j, sizeof(K.P));
+    memcpy(K.ax, s->h_jax64.data() + 3 * (size_t)j, sizeof(K.ax));
+    K.qconst = s->h_qbase64[s->joint_qidx[j]];
+    K.type = s->h_jtype[j];
+    K.slot = s->h_joints[j].slot;
+    K.masked = (K.slot >= 0 && mask && mask[K.slot]) ? 1 : 0;
+    K.pad = 0;
+  }
+  // inverse of the link placement in its joint frame
+  double Li[12];
+  {
+    const double *L = s->h_linkL64.data() + 12 * (size_t)link;
+    for (int r = 0; r < 3; r++) {
+      for (int c = 0; c < 3; c++) Li[4 * r + c] = L[4 * c + r];
+      Li[4 * r + 3] = -(L[r] * L[3] + L[4 + r] * L[7] + L[8 + r] * L[11]);
+    }
+  }
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  DevBufs bufs(s);
+  IkJoint *d_chain = nullptr;
+  double *d_Li = nullptr, *d_pose = nullptr, *d_q0 = nullptr, *d_q = nullptr, *d_err = nullptr;
+  unsigned char *d_ok = nullptr;
+  CU(bufs.alloc(&d_chain, hc.size()));
+  CU(bufs.alloc(&d_Li, (size_t)12));
+  CU(bufs.alloc(&d_pose, (size_t)n * 7));
+  CU(bufs.alloc(&d_q0, (size_t)n * std::max(D, 1)));
+  CU(bufs.alloc(&d_q, (size_t)n * std::max(D, 1)));
+  CU(bufs.alloc(&d_err, (size_t)n * 6));
+  CU(bufs.alloc(&d_ok, (size_t)n));
+  CU(cudaMemcpyAsync(d_chain, hc.data(), hc.size() * sizeof(IkJoint), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_Li, Li, sizeof(Li), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_pose, poses, (size_t)n * 7 * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (D > 0) CU(cudaMemcpyAsync(d_q0, q_init, (size_t)n * D * sizeof(double), cudaMemcpyHostToDevice, st));
+  ik_clik_kernel<<<(int)((n + 63) / 64), 64, 0, st>>>(d_chain, (int)hc.size(), d_Li, d_pose, d_q0, D, n, eps, max_iter, dt, damp, d_q, d_ok, d_err);
+  CU(cudaGetLastError());
+  if (D > 0) CU(cudaMemcpyAsync(q_out, d_q, (size_t)n * D * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(success, d_ok, (size_t)n, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(err, d_err, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));  // hc / Li go out of scope
   return MPB_OK;
 }

@@ -1,7 +1,7 @@
 """Host mirror of ``mplib.Planner`` (mplib/planner.py) for the calls that sit on the accelerated path: collision
 queries, SRDF auto-generation and joint-space planning.  Every numeric query goes through the C-ABI to the GPU.
 
-Out of scope here: pose-goal IK (`Planner.IK`, `plan` with a pose goal), `plan_screw`, and TOPPRA time
+Out of scope here: `plan_screw` and TOPPRA time
 parametrisation (the `time` / `velocity` / `acceleration` keys of the reference's result dict) -- `toppra` is absent
 from this image; `plan_qpos` returns the waypoint matrix under "position" exactly as the reference hands it to TOPPRA
 (mplib/planner.py:493-510)."""
@@ -165,6 +165,91 @@ class Planner:
     def check_for_collision_batch(self, states):
         """Batched form: states [N, len(move group joints)] -> colliding bool[N] (self + environment)."""
         return self.planning_world.collide_batch(np.asarray(states, dtype=np.float64))
+
+    # ------------------------------------------------------------------ inverse kinematics (SURVEY 8f rank 1)
+    def distance_6D(self, p1, q1, p2, q2):
+        """mplib/planner.py:165-168"""
+        return np.linalg.norm(p1 - p2) + min(np.linalg.norm(q1 - q2), np.linalg.norm(q1 + q2))
+
+    def IK(self, goal_pose, start_qpos, mask=(), *, n_init_qpos=20, threshold=0.001, return_closest=False, verbose=False, seed=None):
+        """mplib/planner.py:256-356.  The reference runs its `n_init_qpos` CLIK restarts, the joint-limit check, the
+        collision check and the pose check one after the other; here all restarts are ONE batched CLIK call, one batched
+        collide and one batched FK, then the same acceptance logic in the same order."""
+        status, goals = self.IK_batch(np.asarray(goal_pose, dtype=np.float64)[None, :], start_qpos, mask, n_init_qpos=n_init_qpos,
+                                      threshold=threshold, return_closest=return_closest, seed=seed)
+        return status[0], goals[0]
+
+    def IK_batch(self, goal_poses, start_qpos, mask=(), *, n_init_qpos=20, threshold=0.001, return_closest=False, seed=None):
+        """`IK` for G goal poses at once ([G, 7]); one start_qpos for all.  -> (list of status, list of q_goals)"""
+        goal_poses = np.asarray(goal_poses, dtype=np.float64).reshape(-1, 7)
+        start_qpos = np.asarray(start_qpos, dtype=np.float64)
+        G, ndof = goal_poses.shape[0], start_qpos.shape[0]
+        mask = np.zeros(ndof, dtype=bool) if len(mask) == 0 else np.asarray(mask, dtype=bool)
+        move_link_idx = self.link_name_2_idx[self.move_group]
+        move_joint_idx = self.move_group_joint_indices
+        rng = np.random.Generator(np.random.PCG64(seed)) if seed is not None else np.random.default_rng()
+        lim = np.concatenate(self.pinocchio_model.get_joint_limits())
+        # restart 0 starts from start_qpos, the others from random configurations with the masked joints kept
+        q0 = lim[:, 0] + (lim[:, 1] - lim[:, 0]) * rng.random((G, n_init_qpos, ndof))
+        q0[:, 0, :] = start_qpos
+        q0[:, :, mask] = start_qpos[mask]
+        poses_rep = np.repeat(goal_poses, n_init_qpos, axis=0)
+        q, ok, _ = self.pinocchio_model.compute_IK_CLIK_batch(move_link_idx, poses_rep, q0.reshape(-1, ndof), mask)
+        for k in range(q.shape[0]):  # check_joint_limit() clips qpos towards the lower limits
+            ok[k] = ok[k] and self.check_joint_limit(q[k])
+        self.robot.set_qpos(start_qpos, True)
+        if ok.any():
+            cand = np.nonzero(ok)[0]
+            ok[cand[self.planning_world.collide_batch(q[cand][:, move_joint_idx])]] = False
+        dist = np.full(q.shape[0], np.inf)
+        if ok.any():
+            cand = np.nonzero(ok)[0]
+            new_pose = self.pinocchio_model.compute_forward_kinematics_batch(q[cand])[:, move_link_idx, :].astype(np.float64)
+            for c, npz in zip(cand, new_pose):
+                g = poses_rep[c]
+                dist[c] = self.distance_6D(g[:3], g[3:], npz[:3], npz[3:])
+        status, out = [], []
+        for gi in range(G):
+            sl = slice(gi * n_init_qpos, (gi + 1) * n_init_qpos)
+            q_goals, min_dis = [], 1e9
+            for k in np.nonzero(ok[sl])[0] + gi * n_init_qpos:
+                min_dis = min(min_dis, dist[k])
+                if dist[k] < threshold and not any(np.linalg.norm(qg[move_joint_idx] - q[k][move_joint_idx]) < 0.1 for qg in q_goals):
+                    q_goals.append(q[k].copy())
+            if q_goals:
+                if return_closest:
+                    q_goals = self._closest_goal(np.asarray(q_goals), start_qpos)
+                status.append("Success")
+                out.append(q_goals)
+            elif min_dis != 1e9:
+                status.append(f"IK Failed! Distance {min_dis} is greater than {threshold=}.")
+                out.append(None)
+            else:
+                status.append("IK Failed! Cannot find valid solution.")
+                out.append(None)
+        return status, out
+
+    def _closest_goal(self, q_goals, start_qpos):
+        """mplib/planner.py:337-355: the solution closest to start_qpos, considering +2*pi images of wide revolute joints"""
+        equiv = np.array([t.startswith("JointModelR") for t in self.joint_types]) & (self.joint_limits[:, 1] - self.joint_limits[:, 0] > 2 * np.pi)
+        start = np.asarray(start_qpos)[None]
+        q1 = q_goals[:, equiv]
+        q2 = q1 + 2 * np.pi
+        closer = (q2 < self.joint_limits[:, 1][None, equiv]) & (np.abs(q1 - start[:, equiv]) > np.abs(q2 - start[:, equiv]))
+        q_goals[:, equiv] = np.where(closer, q2, q1)
+        return q_goals[np.linalg.norm(q_goals - start, axis=1).argmin()]
+
+    def plan(self, goal_pose, current_qpos, mask=(), *, planner_name="RRTConnect", rrt_range=0.1, planning_time=1.0,
+             fix_joint_limits=True, verbose=False, **kw):
+        """mplib/planner.py:415-524 without the TOPPRA step: IK for the goal pose, then RRTConnect to the IK solutions."""
+        current_qpos = np.array(current_qpos, dtype=np.float64, copy=True)
+        if fix_joint_limits:
+            current_qpos = np.clip(current_qpos, self.joint_limits[:, 0], self.joint_limits[:, 1])
+        ik_status, goal_qpos = self.IK(goal_pose, current_qpos, mask)
+        if ik_status != "Success":
+            return {"status": ik_status}
+        return self.plan_qpos(goal_qpos, current_qpos, planner_name=planner_name, rrt_range=rrt_range, planning_time=planning_time,
+                              fix_joint_limits=False, verbose=verbose, **kw)
 
     # ------------------------------------------------------------------ scene updates (mplib/planner.py:358-413)
     def update_point_cloud(self, pc, radius=1e-3):

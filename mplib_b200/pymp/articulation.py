@@ -166,11 +166,24 @@ class PinocchioModel:
             self.compute_forward_kinematics(np.zeros(self.km.nv))
         return self._poses[index].copy()
 
+    def compute_IK_CLIK_batch(self, index, poses, q_init, mask=(), eps=1e-5, maxIter=1000, dt=1e-1, damp=1e-12):
+        """n independent ``computeIKCLIK`` problems (``src/pinocchio_model.cpp:377-432``) in one device call:
+        poses [n, 7], q_init [n, nv] (user order) -> (qpos [n, nv], success bool[n], error [n, 6])."""
+        if not (0 <= index < len(self.user_link_names)):
+            raise RuntimeError("The link index is out of bound!")
+        return self._device_scene().ik_clik(int(self.link_user2model[index]), poses, q_init, list(mask), eps, maxIter, dt, damp)
+
+    def compute_IK_CLIK(self, index, pose, q_init, mask=(), eps=1e-5, maxIter=1000, dt=1e-1, damp=1e-12):
+        """``python/pybind_pinocchio.hpp:54-57``: -> (qpos, success, error)"""
+        q, ok, err = self.compute_IK_CLIK_batch(index, np.asarray(pose, dtype=np.float64)[None, :],
+                                                np.asarray(q_init, dtype=np.float64)[None, :], mask, eps, maxIter, dt, damp)
+        return q[0], bool(ok[0]), err[0]
+
     def _not_on_path(self, *a, **k):
-        raise NotImplementedError("Jacobian / IK are outside the accelerated path (SURVEY 8f)")
+        raise NotImplementedError("Jacobian queries / joint-limited CLIK are outside the accelerated path (SURVEY 8f)")
 
     compute_full_jacobian = get_link_jacobian = compute_single_link_local_jacobian = _not_on_path
-    compute_IK_CLIK = compute_IK_CLIK_JL = _not_on_path
+    compute_IK_CLIK_JL = _not_on_path
 
 
 class FCLModel:

@@ -1145,3 +1145,109 @@ int orc_rrtconnect_batch(const mpb_scene_desc *d, int D, const double *lo, const
   if (state_checks) *state_checks = sc;
   return 0;
 }
+
+/* ------------------------------------------------------------------ inverse kinematics */
+/* [upstream Pinocchio 2.6] log6 of an SE3: motion (v, w) */
+static void log6_xf(const xf_t *M, double *o6) {
+  const double *R = M->R;
+  double tr = R[0] + R[4] + R[8];
+  double theta = tr >= 3.0 ? 0.0 : (tr <= -1.0 ? M_PI : acos((tr - 1.0) * 0.5));
+  double w[3];
+  if (theta >= M_PI - 1e-2) {
+    double cphi = -(tr - 1.0) * 0.5, beta = theta * theta / (1.0 + cphi);
+    double t0 = (R[0] + cphi) * beta, t1 = (R[4] + cphi) * beta, t2 = (R[8] + cphi) * beta;
+    w[0] = (R[7] > R[5] ? 1.0 : -1.0) * (t0 > 0 ? sqrt(t0) : 0.0);
+    w[1] = (R[2] > R[6] ? 1.0 : -1.0) * (t1 > 0 ? sqrt(t1) : 0.0);
+    w[2] = (R[3] > R[1] ? 1.0 : -1.0) * (t2 > 0 ? sqrt(t2) : 0.0);
+  } else {
+    double t = (theta > 1e-8 ? theta / sin(theta) : 1.0) * 0.5;
+    w[0] = t * (R[7] - R[5]); w[1] = t * (R[2] - R[6]); w[2] = t * (R[3] - R[1]);
+  }
+  double t2 = theta * theta, alpha, beta;
+  if (theta < 1e-4) { alpha = 1.0 - t2 / 12.0 - t2 * t2 / 720.0; beta = 1.0 / 12.0 + t2 / 720.0; }
+  else { double st = sin(theta), ct = cos(theta); alpha = theta * st / (2.0 * (1.0 - ct)); beta = 1.0 / t2 - st / (2.0 * theta * (1.0 - ct)); }
+  const double *p = M->p;
+  double wp = dot3(w, p), c[3]; cross3(c, w, p);
+  for (int k = 0; k < 3; k++) { o6[k] = alpha * p[k] - 0.5 * c[k] + beta * wp * w[k]; o6[3 + k] = w[k]; }
+}
+static void xf_inv_mul(xf_t *o, const xf_t *a, const xf_t *b) { /* a^-1 b */
+  double d[3]; sub3(d, b->p, a->p);
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < 3; j++) o->R[3 * i + j] = a->R[i] * b->R[j] + a->R[3 + i] * b->R[3 + j] + a->R[6 + i] * b->R[6 + j];
+    o->p[i] = a->R[i] * d[0] + a->R[3 + i] * d[1] + a->R[6 + i] * d[2];
+  }
+}
+static void solve6(double A[6][6], double *b) {
+  for (int c = 0; c < 6; c++) {
+    int piv = c; double best = fabs(A[c][c]);
+    for (int r = c + 1; r < 6; r++) if (fabs(A[r][c]) > best) { best = fabs(A[r][c]); piv = r; }
+    if (piv != c) { for (int k = 0; k < 6; k++) { double t = A[c][k]; A[c][k] = A[piv][k]; A[piv][k] = t; } double t = b[c]; b[c] = b[piv]; b[piv] = t; }
+    double d = A[c][c]; if (d == 0.0) continue;
+    for (int r = c + 1; r < 6; r++) { double f = A[r][c] / d; for (int k = c; k < 6; k++) A[r][k] -= f * A[c][k]; b[r] -= f * b[c]; }
+  }
+  for (int c = 5; c >= 0; c--) { double s = b[c]; for (int k = c + 1; k < 6; k++) s -= A[c][k] * b[k]; b[c] = A[c][c] != 0.0 ? s / A[c][c] : 0.0; }
+}
+/* PinocchioModelTpl::computeIKCLIK (src/pinocchio_model.cpp:377-432) over the scene's batch state */
+int orc_ik_clik_batch(const mpb_scene_desc *d, int link, const double *poses, const double *q_init, const uint8_t *mask, int64_t n,
+                      double eps, int max_iter, double dt, double damp, double *q_out, uint8_t *success, double *err_out, int nthreads) {
+  if (link < 0 || link >= d->n_links) return -1;
+  int chain[64], nc = 0;
+  for (int j = d->link_joint[link]; j != 0 && nc < 64; j = d->joint_parent[j - 1]) chain[nc++] = j;
+  if (nc == 0) return -1;
+  for (int a = 0, b = nc - 1; a < b; a++, b--) { int t = chain[a]; chain[a] = chain[b]; chain[b] = t; }
+  int *slot_of_q = (int *)malloc(sizeof(int) * (size_t)d->nq_full);
+  for (int k = 0; k < d->nq_full; k++) slot_of_q[k] = -1;
+  for (int k = 0; k < d->state_dim; k++) slot_of_q[d->state_map[k]] = k;
+  xf_t L, Li; xf_from12(&L, d->link_placement + 12 * link);
+  xf_t I; xf_identity(&I); xf_inv_mul(&Li, &L, &I);
+  const int D = d->state_dim;
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 16)
+  for (int64_t i = 0; i < n; i++) {
+    const double *ps = poses + 7 * i;
+    double quat[4] = {ps[3], ps[4], ps[5], ps[6]};
+    xf_t lp, target; quat_to_mat(quat, lp.R); copy3(lp.p, ps);
+    xf_mul(&target, &lp, &Li);
+    double q[64]; xf_t T[64];
+    for (int c = 0; c < nc; c++) { int j = chain[c] - 1, sl = slot_of_q[d->joint_qidx[j]]; q[c] = sl >= 0 ? q_init[i * D + sl] : d->q_base[d->joint_qidx[j]]; }
+    double err[6]; int ok = 0;
+    for (int it = 0;; it++) {
+      xf_t cur; xf_identity(&cur);
+      for (int c = 0; c < nc; c++) {
+        int j = chain[c] - 1; xf_t pl, jm, li, nx;
+        xf_from12(&pl, d->joint_placement + 12 * j); joint_motion(&jm, d->joint_type[j], d->joint_axis + 3 * j, q[c]);
+        xf_mul(&li, &pl, &jm);
+        if (c == 0) cur = li; else { xf_mul(&nx, &cur, &li); cur = nx; }
+        T[c] = cur;
+      }
+      xf_t dMi; xf_inv_mul(&dMi, &target, &cur); log6_xf(&dMi, err);
+      double e2 = 0; for (int k = 0; k < 6; k++) e2 += err[k] * err[k];
+      if (sqrt(e2) < eps) { ok = 1; break; }
+      if (it >= max_iter) break;
+      double J[6][64], A[6][6];
+      for (int r = 0; r < 6; r++) for (int k = 0; k < 6; k++) A[r][k] = r == k ? damp : 0.0;
+      for (int c = 0; c < nc; c++) {
+        int j = chain[c] - 1, sl = slot_of_q[d->joint_qidx[j]]; double col[6] = {0, 0, 0, 0, 0, 0};
+        if (sl >= 0 && !(mask && mask[sl])) {
+          xf_t X; xf_inv_mul(&X, &cur, &T[c]);
+          double ra[3]; xf_rot(ra, &X, d->joint_axis + 3 * j);
+          if (d->joint_type[j] == MPB_JOINT_PRISMATIC) copy3(col, ra);
+          else { cross3(col, X.p, ra); copy3(col + 3, ra); }
+          for (int r = 0; r < 6; r++) for (int k = 0; k < 6; k++) A[r][k] += col[r] * col[k];
+        }
+        for (int r = 0; r < 6; r++) J[r][c] = col[r];
+      }
+      double y[6]; memcpy(y, err, sizeof(y)); solve6(A, y);
+      for (int c = 0; c < nc; c++) { double v = 0; for (int r = 0; r < 6; r++) v += J[r][c] * y[r]; q[c] -= v * dt; }
+    }
+    for (int s = 0; s < D; s++) q_out[i * D + s] = q_init[i * D + s];
+    for (int c = 0; c < nc; c++) {
+      int j = chain[c] - 1, sl = slot_of_q[d->joint_qidx[j]];
+      if (sl >= 0) q_out[i * D + sl] = d->joint_type[j] == MPB_JOINT_CONTINUOUS ? atan2(sin(q[c]), cos(q[c])) : q[c];
+    }
+    success[i] = (uint8_t)ok;
+    memcpy(err_out + 6 * i, err, sizeof(err));
+  }
+  free(slot_of_q);
+  return 0;
+}

@@ -168,3 +168,20 @@ def rrtconnect_batch(desc, lo, hi, starts, goals, n_goals=None, so2=None, range_
                                C.c_void_p(plen.ctypes.data), C.c_void_p(paths.ctypes.data), C.c_int(max_path), C.byref(gc), C.byref(sc),
                                C.c_int(int(threads)))
     return status, [paths[i, : plen[i]].copy() for i in range(Q)], gc.value, sc.value
+
+
+def ik_clik_batch(desc, link, poses, q_init, mask=None, eps=1e-5, max_iter=1000, dt=0.1, damp=1e-12, threads=8):
+    """computeIKCLIK restatement for n problems -> (q [n, D], success bool[n], err [n, 6])"""
+    poses = np.ascontiguousarray(np.asarray(poses, dtype=np.float64).reshape(-1, 7))
+    q0 = _states(desc, q_init)
+    n, D = q0.shape
+    m = None if mask is None or len(mask) == 0 else np.ascontiguousarray(np.asarray(mask, dtype=np.uint8))
+    q = np.zeros((n, D))
+    ok = np.zeros(n, dtype=np.uint8)
+    err = np.zeros((n, 6))
+    rc = lib().orc_ik_clik_batch(C.byref(desc.as_struct()), C.c_int(int(link)), C.c_void_p(poses.ctypes.data), C.c_void_p(q0.ctypes.data),
+                                 C.c_void_p(m.ctypes.data if m is not None else None), C.c_int64(n), C.c_double(eps), C.c_int(int(max_iter)),
+                                 C.c_double(dt), C.c_double(damp), C.c_void_p(q.ctypes.data), C.c_void_p(ok.ctypes.data),
+                                 C.c_void_p(err.ctypes.data), C.c_int(int(threads)))
+    assert rc == 0
+    return q, ok.astype(bool), err

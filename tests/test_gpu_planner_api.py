@@ -84,3 +84,54 @@ def test_plan_qpos():
     assert not pl.check_for_collision_batch(path).any()
     out, stats = pl.plan_qpos_batch(pts[:1].repeat(4, 0), pts[1:2].repeat(4, 0), planning_time=10.0)
     assert all(r["status"] == "Success" for r in out) and stats["n_solved"] == 4
+
+
+def test_ik_clik_parity_and_planner_ik():
+    """batched computeIKCLIK (FP64 kernel) vs the oracle's restatement, then Planner.IK / plan."""
+    from oracle import oracle as O
+
+    pl = _planner()
+    pm = pl.pinocchio_model
+    li = pl.link_name_2_idx["panda_hand"]
+    n = 512
+    q_true = np.concatenate([random_q(n, 81), np.zeros((n, 2))], axis=1)
+    poses = pm.compute_forward_kinematics_batch(q_true)[:, li, :].astype(np.float64)
+    q0 = np.concatenate([random_q(n, 82), np.zeros((n, 2))], axis=1)
+    mask = np.array([False] * 7 + [True] * 2)
+    q, ok, err = pm.compute_IK_CLIK_batch(li, poses, q0, mask)
+    desc = pm._device_scene().desc
+    oq, ook, oerr = O.ik_clik_batch(desc, int(pm.link_user2model[li]), poses, q0, mask)
+    print(f"CLIK success gpu={ok.mean():.3f} oracle={ook.mean():.3f}")
+    # From a random start the damped iteration (damp 1e-12) passes near singular configurations and amplifies the last
+    # bits of sincos / fma contraction, so the two double-precision runs may settle on different IK branches: compare
+    # what the reference promises (success, and the pose is reached), and compare iterates where the problem is
+    # well conditioned (start near the solution).
+    assert ok.mean() > 0.9 and abs(ok.mean() - ook.mean()) < 0.02
+    qn0 = q_true + np.concatenate([np.random.default_rng(83).normal(0, 0.1, (n, 7)), np.zeros((n, 2))], axis=1)
+    qn, okn, _ = pm.compute_IK_CLIK_batch(li, poses, qn0, mask)
+    oqn, ookn, _ = O.ik_clik_batch(desc, int(pm.link_user2model[li]), poses, qn0, mask)
+    assert okn.all() and ookn.all() and np.abs(qn - oqn).max() < 1e-6
+    assert np.linalg.norm(err[ok], axis=1).max() < 1e-5 and np.allclose(q[:, 7:], 0.0)
+    reached = pm.compute_forward_kinematics_batch(q[ok])[:, li, :3]
+    assert np.abs(reached - poses[ok, :3]).max() < 5e-5
+    # single-problem reference signature
+    q1, ok1, err1 = pm.compute_IK_CLIK(li, poses[0], q0[0], list(mask))
+    assert ok1 == ok[0] and np.allclose(q1, q[0])
+    with pytest.raises(RuntimeError):
+        pm.compute_IK_CLIK(99, poses[0], q0[0])
+    # Planner.IK: collision-free, within joint limits, reaches the pose
+    start = np.array([0, 0.2, 0, -2.6, 0, 3.0, 0.8, 0, 0])
+    goal = pm.compute_forward_kinematics_batch(np.array([[0.4, 0.3, -0.2, -2.0, 0.1, 2.4, 1.0, 0, 0]]))[0, li].astype(np.float64)
+    status, q_goals = pl.IK(goal, start, mask, seed=5)
+    assert status == "Success" and len(q_goals) >= 1
+    for qg in q_goals:
+        assert not pl.check_for_collision_batch(qg[None, :7])[0]
+        got = pm.compute_forward_kinematics_batch(qg[None, :])[0, li]
+        assert pl.distance_6D(goal[:3], goal[3:], got[:3].astype(np.float64), got[3:].astype(np.float64)) < 1e-3
+    res = pl.plan(goal, start, mask, planning_time=10.0, seed=3)
+    assert res["status"] == "Success" and np.allclose(res["position"][0], start[:7], atol=1e-6)
+    # an unreachable pose fails with the reference's message
+    far = goal.copy()
+    far[:3] = [3.0, 0.0, 0.5]
+    status, q_goals = pl.IK(far, start, mask, seed=5)
+    assert status.startswith("IK Failed") and q_goals is None

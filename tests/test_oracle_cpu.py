@@ -10,7 +10,7 @@ golden vectors (parity unpinned), so the oracle is pinned by
 import numpy as np
 import pytest
 
-from tests.common import PANDA_LINKS, compile_desc, make_panda_world, random_q
+from tests.common import PANDA_HI, PANDA_LINKS, PANDA_LO, compile_desc, make_panda_world, random_q
 
 
 @pytest.fixture(scope="module")
@@ -159,3 +159,27 @@ def test_detect_collision_example_outcomes(panda_world):
     # the base does not touch the floor (the cloud was shifted down "so we do not collide with the base")
     v, ph = O.collide_batch(d2, np.array([[0, 0.19, 0.0, -2.61, 0.0, 2.94, 0.78]]))
     assert not ph[0, env_cols].any()
+
+
+def test_ik_clik_round_trip(panda_world):
+    """Oracle restatement of computeIKCLIK (src/pinocchio_model.cpp:377-432): pose -> q -> pose round trip through the
+    oracle's own FK, masked joints untouched, an out-of-reach pose reported as a failure."""
+    from oracle import oracle as O
+
+    desc = compile_desc(panda_world)
+    li = desc.link_names.index("panda_hand")
+    rng = np.random.Generator(np.random.PCG64(9))
+    q_true = PANDA_LO + (PANDA_HI - PANDA_LO) * rng.random((256, 7))
+    poses = O.fk_batch(desc, q_true)[:, li, :]
+    q0 = q_true + rng.normal(0, 0.2, q_true.shape)
+    q, ok, err = O.ik_clik_batch(desc, li, poses, q0)
+    assert ok.all() and np.linalg.norm(err, axis=1).max() < 1e-5
+    back = O.fk_batch(desc, q)[:, li, :]
+    assert np.abs(back[:, :3] - poses[:, :3]).max() < 2e-5
+    mask = np.array([1, 0, 0, 0, 0, 0, 0], dtype=np.uint8)
+    qm, okm, _ = O.ik_clik_batch(desc, li, poses[:16], q0[:16], mask, max_iter=200)
+    assert np.array_equal(qm[:, 0], q0[:16, 0])
+    far = poses[:4].copy()
+    far[:, :3] = [3.0, 0.0, 0.5]
+    _, okf, _ = O.ik_clik_batch(desc, li, far, q0[:4], max_iter=200)
+    assert not okf.any()
