@@ -33,6 +33,7 @@ def parse():
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-inflight", type=int, default=2, help="blocking C-ABI calls kept in flight by the end-to-end leg")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
     ap.add_argument("--plan-time", type=float, default=0.5,
                     help="c4: OMPL `time` budget in seconds.  The reference arm gives EVERY query 1.0 s on its own host thread "
@@ -355,13 +356,29 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
 
-    # end-to-end through the C-ABI with pinned host buffers
-    for k in range(min(args.warmup, 3)):
-        step_host(k)
+    # end-to-end through the C-ABI with pinned host buffers.  Two calls are kept in flight (two host threads, each
+    # with its own scene handle, streams and pinned result buffers), the way a caller pipelines a blocking API: the
+    # H2D copy of one call runs under the kernels of the other.  --e2e-inflight 1 gives the strictly serial figure.
+    n_fl = max(1, args.e2e_inflight)
+    devs = [dev] + [_lib.DeviceScene(desc, local) for _ in range(n_fl - 1)]
+    outs = [(verdict_h, pairs_h)] + [(torch.zeros(vwords, dtype=torch.int32).pin_memory(),
+                                      torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()) for _ in range(n_fl - 1)]
+
+    def host_worker(t, k0, k1):
+        for k in range(k0 + t, k1, n_fl):
+            devs[t].collide_raw(pool_h[k % n_pool], N, outs[t][0], outs[t][1], _lib.MPB_HOST, None)
+
+    def run_host(k0, k1):
+        th = [threading.Thread(target=host_worker, args=(t, k0, k1)) for t in range(n_fl)]
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+
+    run_host(0, max(min(args.warmup, 3), n_fl))
     barrier()
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        step_host(args.warmup + k)
+    run_host(args.warmup, args.warmup + args.steps)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     if world > 1:
@@ -397,7 +414,7 @@ def main():
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": wl["config"],
             "e2e": {"value": total_checks / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(N * D * 4),
-                    "d2h_bytes_per_step": int(vwords * 4 + N * max(W, 1) * 4)},
+                    "d2h_bytes_per_step": int(vwords * 4 + N * max(W, 1) * 4), "calls_in_flight": n_fl},
             "gpu_launches": int(agg["kernel_launches"]),
             "clocks": clocks,
             "roofline": {
