@@ -65,7 +65,8 @@ struct mpb_scene {
   int4 *d_runs = nullptr;
   size_t cull_cap = 0;
   SceneImg img{};
-  float *d_pose = nullptr;   // pose table [n_jslots * 12 + n_dyn * 3][pose_ld]
+  float *d_pose = nullptr;   // sphere table [n_dyn * 3 + n_jslots * 12][pose_ld]
+  float4 *d_obb = nullptr;   // OBB table [pose_ld][n_dyn][3]
   size_t pose_ld = 0;
   uint2 *d_sq = nullptr;     // survivor queue of the sphere phase: (configuration, cull-table entry)
   unsigned sq_cap = 0;
@@ -733,8 +734,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   }
   s->img.n_dyn = ndyn;
   s->img.n_jslots = n_jslots;
-  s->img.w_sphere = ndyn * 12;
-  s->img.w_joint = ndyn * 15;
+  s->img.w_sphere = 0;
+  s->img.w_joint = ndyn * 3;
   // cull records (MPB_COBB_WORDS float4 per object), see dense_kernel
   std::vector<float4> cobb((size_t)d->n_objects * MPB_COBB_WORDS);
   for (int o = 0; o < d->n_objects; o++) {
@@ -821,7 +822,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &b : s->pool) cudaFree(b.first);
@@ -894,8 +895,10 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   if (s->d_pose) { cudaFree(s->d_pose); s->d_pose = nullptr; }
   if (s->d_sq) { cudaFree(s->d_sq); s->d_sq = nullptr; }
   s->pose_ld = (size_t)(chunk + 31) / 32 * 32;
-  const size_t pose_words = (size_t)s->img.n_jslots * 12 + (size_t)s->img.n_dyn * 15;
+  const size_t pose_words = (size_t)s->img.n_jslots * 12 + (size_t)s->img.n_dyn * 3;
   CU(cudaMalloc((void **)&s->d_pose, std::max<size_t>(pose_words * s->pose_ld, 4) * sizeof(float)));
+  if (s->d_obb) { cudaFree(s->d_obb); s->d_obb = nullptr; }
+  CU(cudaMalloc((void **)&s->d_obb, std::max<size_t>((size_t)s->img.n_dyn * 3 * s->pose_ld, 1) * sizeof(float4)));
   // survivors of the sphere phase: every admitted pair of every configuration at worst, bounded like the work queue
   const size_t sq_cap = std::max<size_t>(std::min((size_t)chunk * P + (size_t)s->num_sms * 64 * MPB_SQ_CHUNK, kMaxSurvivors), 4096);
   CU(cudaMalloc((void **)&s->d_sq, sq_cap * sizeof(uint2)));
@@ -969,14 +972,14 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((mm + 127) / 128);
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 3);
       const int sblocks = std::min(cblocks, s->num_sms * 16);  // persistent warps: survivor-queue chunks carry over between tiles
       sphere_kernel<0><<<sblocks, 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       *launches += 2;
     }
   }
   if (s->img.n_pairs == 0) return MPB_OK;
-  dense_kernel<0><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
+  dense_kernel<0><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
   *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
@@ -1572,9 +1575,9 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     CU(cudaEventRecord(e0, st));
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((m + 127) / 128);
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq, m, s->d_pose, s->pose_ld);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq, m, s->d_pose, s->pose_ld, s->d_obb);
       sphere_kernel<1><<<std::min(cblocks, s->num_sms * 16), 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
-      dense_kernel<1><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
+      dense_kernel<1><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, -1, (unsigned)dblocks * 8u, s->sq_cap);
       scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));

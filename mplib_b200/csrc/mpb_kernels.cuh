@@ -47,7 +47,7 @@ struct SceneImg {
   const int *linkJoint; // [n_links]
   int n_joints, n_objects, n_pairs, n_links, n_verts, n_bins, state_dim, pair_words, n_dyn, n_jslots;
   int pool_bytes;         // vertex pool + cell tables, staged as one block in shared memory
-  int w_sphere, w_joint;  // pose-table word offsets: [n_dyn][12] OBB frames, then [n_dyn][3] sphere centres, then [n_jslots][12] branch joints
+  int w_sphere, w_joint;  // sphere-table word offsets: [n_dyn][3] sphere centres, then [n_jslots][12] branch joints
 };
 
 struct WorkQ {
@@ -194,9 +194,11 @@ __device__ __forceinline__ Xf joint_step(const DevJoint &J, const Xf *parent, fl
 }
 
 // ---------------------------------------------------------------------------------------------- FK + cull, three kernels
-// The pose table lives in HBM, word-major [word][configuration]: 12 words per moving object (world pose of its OBB
-// frame), 3 words per moving object's bounding-sphere centre, 12 words per branch-point joint (a parent that a later,
-// non-adjacent child needs).  ~700 B per Panda configuration is cheap at HBM3e rates (a million configurations per
+// The pose tables live in HBM.  OBB table: [moving object][configuration][3 x float4], the world pose of each moving
+// object's OBB frame (fk_table_kernel transposes a warp's 32 frames through shared memory and stores 1536 contiguous
+// bytes; dense_kernel reads three 16-byte words per object).  Sphere table, word-major [word][configuration]: 3 words per moving object's bounding-sphere
+// centre (coalesced for the thread-per-configuration sphere phase) and 12 words per branch-point joint (a parent that a
+// later, non-adjacent child needs).  ~700 B per Panda configuration is cheap at HBM3e rates (a million configurations per
 // 0.2 ms, read + write) and it frees the kernels from a shared-memory pose table that capped them at ten warps per
 // SM: all three kernels below are register-only and run at full occupancy.
 //   fk_table_kernel   thread per configuration: FK down the forest; OBB frames + sphere centres -> pose table
@@ -224,12 +226,18 @@ __device__ __forceinline__ Xf pose_joint(const float *__restrict__ pose, size_t 
   return w;
 }
 
-__global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld) {
+__global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
+                                                       float4 *__restrict__ obb) {
+  __shared__ __align__(16) float s_tr[4][32 * 12];  // per warp: one object's 32 OBB frames, transposed for full-sector stores
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  const long long tile0 = i - lane;
+  if (tile0 >= n) return;                   // whole warps stay: the tables are padded to a multiple of 32 configurations
+  const long long ic = i < n ? i : n - 1;   // lanes past the end recompute the last configuration into the padding
   const int cbase = img.w_sphere, jbase = img.w_joint;
+  float *tr = s_tr[warp];
   Xf cur = xf_identity();
-  const float *qrow = q + i * img.state_dim;
+  const float *qrow = q + ic * img.state_dim;
   for (int j = 0; j < img.n_joints; j++) {
     const DevJoint &J = img.joints[j];
     const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
@@ -251,10 +259,16 @@ __global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float
       for (int k = 0; k < 3; k++) POSE(cbase + O.dyn * 3 + k, i) = c[k];
       const float4 *rec = img.cobb + MPB_COBB_WORDS * o;  // OBB frame in the joint frame -> world
       const Xf E = xf_mul(cur, xf_rows(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2)));
+      // OBB table [object][configuration][3 x float4]: the warp's 32 frames are 1536 contiguous bytes
+      float4 *mine = reinterpret_cast<float4 *>(tr) + lane * 3;
+      mine[0] = make_float4(E.r[0], E.r[1], E.r[2], E.p[0]);
+      mine[1] = make_float4(E.r[3], E.r[4], E.r[5], E.p[1]);
+      mine[2] = make_float4(E.r[6], E.r[7], E.r[8], E.p[2]);
+      __syncwarp();
+      float4 *dst = obb + ((size_t)O.dyn * ld + tile0) * 3;
 #pragma unroll
-      for (int k = 0; k < 9; k++) POSE(O.dyn * 12 + k, i) = E.r[k];
-#pragma unroll
-      for (int k = 0; k < 3; k++) POSE(O.dyn * 12 + 9 + k, i) = E.p[k];
+      for (int r = 0; r < 3; r++) dst[lane + 32 * r] = reinterpret_cast<const float4 *>(tr)[lane + 32 * r];
+      __syncwarp();
     }
   }
 }
@@ -355,7 +369,7 @@ __global__ void __launch_bounds__(128) sphere_kernel(SceneImg img, const float *
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float *__restrict__ pose, size_t ld, const uint2 *__restrict__ sq,
+__global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
                                                     unsigned sq_cap, WorkQ wq, unsigned int *__restrict__ verdict_bits,
                                                     unsigned int *__restrict__ pair_bits) {
   const unsigned FULL = 0xffffffffu;
@@ -385,8 +399,9 @@ __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float *_
       const float4 *ca = img.cobb + MPB_COBB_WORDS * pr.a, *cb = img.cobb + MPB_COBB_WORDS * pr.b;
       const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
       const int da = __float_as_int(ia.w), db = __float_as_int(ib.w);
-      const Xf Ea = da >= 0 ? pose_joint(pose, ld, da * 12, cfg) : xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2));
-      const Xf Eb = db >= 0 ? pose_joint(pose, ld, db * 12, cfg) : xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
+      const float4 *pa = da >= 0 ? obb + ((size_t)da * ld + cfg) * 3 : ca;  // moving: this configuration's entry of the OBB table
+      const float4 *pb = db >= 0 ? obb + ((size_t)db * ld + cfg) * 3 : cb;
+      const Xf Ea = xf_rows(pa[0], pa[1], pa[2]), Eb = xf_rows(pb[0], pb[1], pb[2]);
       // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)  ==  (OBB frame A)^-1 (OBB frame B)
       Xf Rt;
       const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
