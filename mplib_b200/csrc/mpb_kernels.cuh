@@ -488,7 +488,7 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bi
     for (int b = 0; b < n_bins; b++)
       if (b != skip_bin && b != skip_bin2) all += wq.bin_count[b];
     unsigned unit = MPB_UNIT_ITEMS;
-    while (unit > 2u && all / unit < n_warps) unit >>= 1;  // few items (a planning round): short slices -> cooperative supports
+    while (unit > 2u && all / unit < n_warps - n_warps / 4) unit >>= 1;  // few items (a planning round): short slices -> cooperative supports
     wq.totals[4] = unit;
     for (int b = 0; b < n_bins; b++) {
       wq.bin_start[b] = items;
@@ -698,7 +698,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 // ccdMPRIntersect [upstream libccd v2.1 mpr.c] in the frame of shape A; B sits at (R, t).
 // Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
 template <bool SMEM>
-__global__ void __launch_bounds__(256) narrow_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
+__global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
                                                      unsigned int *__restrict__ pair_bits, int n_bins, int round) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bar;
