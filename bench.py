@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-inflight", type=int, default=2, help="blocking C-ABI calls kept in flight by the end-to-end leg")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
+    ap.add_argument("--connect-steps", type=int, default=8, help="c4: connect-walk steps validated per lock-step round")
     ap.add_argument("--plan-time", type=float, default=0.5,
                     help="c4: OMPL `time` budget in seconds.  The reference arm gives EVERY query 1.0 s on its own host thread "
                          "(Planner.plan's default); the batched call applies its budget to the whole lock-step batch.  0.5 s is "
@@ -178,7 +179,8 @@ def run_c4(args):
     pl = OMPLPlanner(w)
     n_sets = min(args.warmup + args.steps, 4)
     sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, w.collide_batch) for k in range(n_sets)]
-    kw = dict(range=0.1, time=args.plan_time, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048)
+    kw = dict(range=0.1, time=args.plan_time, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048,
+              connect_steps=args.connect_steps)
 
     def barrier():
         if world > 1:
@@ -339,13 +341,14 @@ def main():
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "pairs_after_cull": 0, "pairs_after_spheres": 0, "narrow_iterations": 0, "narrow_capped": 0,
+    agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "gpu_ms_fk": 0.0, "pairs_after_cull": 0, "pairs_after_spheres": 0, "narrow_iterations": 0, "narrow_capped": 0,
            "kernel_launches": 0}
     e0.record(stream)
     for k in range(args.steps):
         st = step_device(args.warmup + k)
         for key in agg:
             agg[key] += st[key]
+        fk_bytes = st["fk_bytes_per_state"]
     drain()  # the last gathers are inside the timed region
     e1.record(stream)
     barrier()
@@ -425,6 +428,12 @@ def main():
                 "kernel_ms_per_step": {"fk_table+sphere+dense+scan+scatter": agg["gpu_ms_cull"] / K, "narrow(+expand)": agg["gpu_ms_narrow"] / K},
                 "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
                         "bytes_per_check": B_alg, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                # the one HBM-bound kernel of the pass, timed alone with CUDA events on its own stream inside the C-ABI call
+                "fk_table_kernel": {"bound": "hbm", "achieved": N * fk_bytes / (agg["gpu_ms_fk"] / K * 1e-3) / 1e9 if agg["gpu_ms_fk"] > 0 else None,
+                                    "peak": hbm_peak, "unit": "GB/s",
+                                    "frac": N * fk_bytes / (agg["gpu_ms_fk"] / K * 1e-3) / 1e9 / hbm_peak if agg["gpu_ms_fk"] > 0 else None,
+                                    "bytes_per_state": fk_bytes, "ms_per_step": agg["gpu_ms_fk"] / K,
+                                    "share_of_step": agg["gpu_ms_fk"] / max(agg["gpu_ms_cull"] + agg["gpu_ms_narrow"], 1e-9)},
             },
             "stats_per_step": {"pairs_after_spheres": agg["pairs_after_spheres"] / K, "pairs_after_cull": agg["pairs_after_cull"] / K, "support_evals": iters_per_step,
                                "capped": agg["narrow_capped"] / K},

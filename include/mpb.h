@@ -122,6 +122,8 @@ typedef struct mpb_stats {
   float gpu_ms_narrow;       /* narrowphase kernel(s)                                */
   float host_ms_enqueue;     /* host time spent issuing the call's copies and launches */
   float host_ms_total;       /* host wall time of the call, including the final synchronisation */
+  float gpu_ms_fk;           /* fk_table_kernel alone (device-resident input; 0 when the input is streamed from the host) */
+  int32_t fk_bytes_per_state; /* algorithmic bytes fk_table_kernel moves per state: 4*state_dim read + sphere and OBB table rows written */
 } mpb_stats;
 
 /* Thread-local message of the last failing call on this thread. */

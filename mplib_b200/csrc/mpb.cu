@@ -959,8 +959,10 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
   CU(cudaMemsetAsync(s->wq.totals + 6, 0, sizeof(unsigned), st));
   cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;  // ev == nullptr: no timing events (graph capture)
-  if (ev) { e0 = get_event(s, (*ev)++); e1 = get_event(s, (*ev)++); e2 = get_event(s, (*ev)++); }
+  cudaEvent_t f0 = nullptr, f1 = nullptr;                // around fk_table_kernel (device-resident input only)
+  if (ev) { e0 = get_event(s, (*ev)++); e1 = get_event(s, (*ev)++); e2 = get_event(s, (*ev)++); f0 = get_event(s, (*ev)++); f1 = get_event(s, (*ev)++); }
   if (ev) CU(cudaEventRecord(e0, st));
+  if (ev && hq) { CU(cudaEventRecord(f0, st)); CU(cudaEventRecord(f1, st)); }
   const long long sub = hq ? std::max<long long>(s->host_chunk, 64) : m;
   for (long long off = 0; off < m; off += sub) {
     const long long mm = std::min(sub, m - off);
@@ -972,13 +974,22 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((mm + 127) / 128);
+      if (ev && !hq) CU(cudaEventRecord(f0, st));
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 3);
+      if (ev && !hq) CU(cudaEventRecord(f1, st));
       const int sblocks = std::min(cblocks, s->num_sms * 16);  // persistent warps: survivor-queue chunks carry over between tiles
       sphere_kernel<0><<<sblocks, 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       *launches += 2;
     }
   }
-  if (s->img.n_pairs == 0) return MPB_OK;
+  if (s->img.n_pairs == 0) {
+    if (ev) {
+      if (!hq) { CU(cudaEventRecord(f0, st)); CU(cudaEventRecord(f1, st)); }
+      CU(cudaEventRecord(e1, st));
+      CU(cudaEventRecord(e2, st));
+    }
+    return MPB_OK;
+  }
   dense_kernel<0><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
   *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
@@ -1081,14 +1092,18 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
     stats->narrow_iterations = (long long)counters[1];
     stats->narrow_capped = (long long)counters[2];
     stats->kernel_launches = launches;
-    float cull = 0.f, narrow = 0.f;
-    for (size_t i = 0; i + 2 < ev + 0 && i + 2 <= ev - 1; i += 3) {
-      float a = 0.f, b = 0.f;
+    float cull = 0.f, narrow = 0.f, fk = 0.f;
+    for (size_t i = 0; i + 5 <= ev; i += 5) {
+      float a = 0.f, b = 0.f, c = 0.f;
       cudaEventElapsedTime(&a, s->events[i], s->events[i + 1]);
       cudaEventElapsedTime(&b, s->events[i + 1], s->events[i + 2]);
+      cudaEventElapsedTime(&c, s->events[i + 3], s->events[i + 4]);
       cull += a;
       narrow += b;
+      fk += c;
     }
+    stats->gpu_ms_fk = fk;
+    stats->fk_bytes_per_state = (int32_t)(4 * s->img.state_dim + 4 * (s->img.n_jslots * 12 + s->img.n_dyn * 3) + 48 * s->img.n_dyn);
     stats->gpu_ms_cull = cull;
     stats->gpu_ms_narrow = narrow;
     stats->gpu_ms = cull + narrow;

@@ -72,6 +72,8 @@ class MpbStats(C.Structure):
         ("gpu_ms_narrow", C.c_float),
         ("host_ms_enqueue", C.c_float),
         ("host_ms_total", C.c_float),
+        ("gpu_ms_fk", C.c_float),
+        ("fk_bytes_per_state", C.c_int32),
     ]
 
     def as_dict(self):
