@@ -247,6 +247,14 @@ int mpb_fp32_peak(int device, float *tflops);
 int mpb_ik_clik_batch(mpb_scene *scene, int32_t link, const double *poses, const double *q_init, const uint8_t *mask, int64_t n,
                       double eps, int32_t max_iter, double dt, double damp, double *q_out, uint8_t *success, double *err);
 
+/* PinocchioModelTpl::computeFullJacobian + getLinkJacobian(index, local) (src/pinocchio_model.cpp:335-360) for n states,
+ * double precision: the 6 x state_dim Jacobian of `link`'s parent joint, rows (linear, angular), in Pinocchio's WORLD
+ * frame (local == 0) or in the link frame (local != 0; equals computeSingleLinkLocalJacobian, :362-375).  Columns follow
+ * the scene's batch state; joints off the chain give zero columns.
+ *   q [n][state_dim]   jac [n][6][state_dim]   link_pose [n][12] nullable: the link's world placement, 3x4 row-major.
+ * Host pointers. */
+int mpb_link_jacobian_batch(mpb_scene *scene, int32_t link, const double *q, int64_t n, int32_t local, double *jac, double *link_pose);
+
 #ifdef __cplusplus
 }
 #endif

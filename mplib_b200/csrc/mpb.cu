@@ -1645,20 +1645,14 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
 // ------------------------------------------------------------------------------------------ inverse kinematics
 #include "mpb_ik.cuh"
 
-extern "C" int mpb_ik_clik_batch(mpb_scene *s, int32_t link, const double *poses, const double *q_init, const uint8_t *mask, int64_t n,
-                                 double eps, int32_t max_iter, double dt, double damp, double *q_out, uint8_t *success, double *err) {
-  if (!s) return fail(MPB_ERR_INVALID, "null scene");
-  if (n < 0 || (n > 0 && (!poses || !q_init || !q_out || !success || !err))) return fail(MPB_ERR_INVALID, "null batch pointer");
+// Chain of movable joints from the root to `link`'s parent joint, and the link placement (and its inverse) in that joint's frame.
+static int build_chain(mpb_scene *s, int32_t link, const uint8_t *mask, std::vector<IkJoint> &hc, double *L12, double *Li) {
   if (link < 0 || link >= (int)s->h_linkJoint.size()) return fail(MPB_ERR_INVALID, "The link index is out of bound!");
-  if (n == 0) return MPB_OK;
-  const int D = s->img.state_dim;
-  // chain of movable joints from the root to the link's parent joint (model indices, 0 = universe)
-  std::vector<int> chain;
+  std::vector<int> chain;  // model indices, 0 = universe
   for (int j = s->h_linkJoint[link]; j != 0; j = s->h_jparent[j - 1]) chain.push_back(j);
   std::reverse(chain.begin(), chain.end());
-  if (chain.empty()) return fail(MPB_ERR_INVALID, "the link is fixed to the world: nothing to solve for");
   if ((int)chain.size() > MPB_IK_MAX_CHAIN) return fail(MPB_ERR_CAPACITY, "kinematic chain longer than MPB_IK_MAX_CHAIN");
-  std::vector<IkJoint> hc(chain.size());
+  hc.resize(chain.size());
   for (size_t c = 0; c < chain.size(); c++) {
     const int j = chain[c] - 1;
     IkJoint &K = hc[c];
@@ -1670,15 +1664,26 @@ extern "C" int mpb_ik_clik_batch(mpb_scene *s, int32_t link, const double *poses
     K.masked = (K.slot >= 0 && mask && mask[K.slot]) ? 1 : 0;
     K.pad = 0;
   }
-  // inverse of the link placement in its joint frame
-  double Li[12];
-  {
-    const double *L = s->h_linkL64.data() + 12 * (size_t)link;
-    for (int r = 0; r < 3; r++) {
-      for (int c = 0; c < 3; c++) Li[4 * r + c] = L[4 * c + r];
-      Li[4 * r + 3] = -(L[r] * L[3] + L[4 + r] * L[7] + L[8 + r] * L[11]);
-    }
+  const double *L = s->h_linkL64.data() + 12 * (size_t)link;
+  if (L12) memcpy(L12, L, 12 * sizeof(double));
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 3; c++) Li[4 * r + c] = L[4 * c + r];
+    Li[4 * r + 3] = -(L[r] * L[3] + L[4 + r] * L[7] + L[8 + r] * L[11]);
   }
+  return MPB_OK;
+}
+
+extern "C" int mpb_ik_clik_batch(mpb_scene *s, int32_t link, const double *poses, const double *q_init, const uint8_t *mask, int64_t n,
+                                 double eps, int32_t max_iter, double dt, double damp, double *q_out, uint8_t *success, double *err) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!poses || !q_init || !q_out || !success || !err))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (link < 0 || link >= (int)s->h_linkJoint.size()) return fail(MPB_ERR_INVALID, "The link index is out of bound!");
+  if (n == 0) return MPB_OK;
+  const int D = s->img.state_dim;
+  std::vector<IkJoint> hc;
+  double Li[12];
+  if (int rc = build_chain(s, link, mask, hc, nullptr, Li)) return rc;
+  if (hc.empty()) return fail(MPB_ERR_INVALID, "the link is fixed to the world: nothing to solve for");
   CU(cudaSetDevice(s->device));
   cudaStream_t st = s->stream;
   DevBufs bufs(s);
@@ -1702,5 +1707,36 @@ extern "C" int mpb_ik_clik_batch(mpb_scene *s, int32_t link, const double *poses
   CU(cudaMemcpyAsync(success, d_ok, (size_t)n, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(err, d_err, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));  // hc / Li go out of scope
+  return MPB_OK;
+}
+
+extern "C" int mpb_link_jacobian_batch(mpb_scene *s, int32_t link, const double *q, int64_t n, int32_t local, double *jac, double *link_pose) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!q || !jac))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (link < 0 || link >= (int)s->h_linkJoint.size()) return fail(MPB_ERR_INVALID, "The link index is out of bound!");
+  if (n == 0) return MPB_OK;
+  const int D = s->img.state_dim;
+  if (D <= 0) return fail(MPB_ERR_INVALID, "the scene has no batch state");
+  std::vector<IkJoint> hc;
+  double L[12], Li[12];
+  if (int rc = build_chain(s, link, nullptr, hc, L, Li)) return rc;
+  CU(cudaSetDevice(s->device));
+  cudaStream_t st = s->stream;
+  DevBufs bufs(s);
+  IkJoint *d_chain = nullptr;
+  double *d_L = nullptr, *d_q = nullptr, *d_J = nullptr, *d_T = nullptr;
+  CU(bufs.alloc(&d_chain, std::max<size_t>(hc.size(), 1)));
+  CU(bufs.alloc(&d_L, (size_t)12));
+  CU(bufs.alloc(&d_q, (size_t)n * D));
+  CU(bufs.alloc(&d_J, (size_t)n * 6 * D));
+  CU(bufs.alloc(&d_T, (size_t)n * 12));
+  if (!hc.empty()) CU(cudaMemcpyAsync(d_chain, hc.data(), hc.size() * sizeof(IkJoint), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_L, L, sizeof(L), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_q, q, (size_t)n * D * sizeof(double), cudaMemcpyHostToDevice, st));
+  link_jacobian_kernel<<<(int)((n + 63) / 64), 64, 0, st>>>(d_chain, (int)hc.size(), d_L, d_q, D, n, local, d_J, d_T);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(jac, d_J, (size_t)n * 6 * D * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (link_pose) CU(cudaMemcpyAsync(link_pose, d_T, (size_t)n * 12 * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
   return MPB_OK;
 }

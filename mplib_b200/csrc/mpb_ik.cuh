@@ -208,3 +208,45 @@ __global__ void __launch_bounds__(64) ik_clik_kernel(const IkJoint *__restrict__
   success[i] = ok ? 1 : 0;
   for (int k = 0; k < 6; k++) err_out[i * 6 + k] = err[k];
 }
+
+// PinocchioModelTpl::computeFullJacobian + getLinkJacobian (src/pinocchio_model.cpp:335-360): the 6 x state_dim Jacobian
+// of `link`'s parent joint for n states, rows (linear, angular).  local == 0: Pinocchio's WORLD frame (spatial velocity
+// at the world origin; column of a revolute joint = (p x a, a) with p the joint origin and a its axis in the world);
+// local != 0: expressed in the link frame (link2world.toActionMatrixInverse() * J).  Columns of joints off the chain
+// are zero.  Also writes the link's world placement as a 3x4 row-major matrix.
+__global__ void __launch_bounds__(64) link_jacobian_kernel(const IkJoint *__restrict__ chain, int n_chain, const double *__restrict__ link2joint,
+                                                           const double *__restrict__ q, int D, long long n, int local,
+                                                           double *__restrict__ jac, double *__restrict__ link_T) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Xd T[MPB_IK_MAX_CHAIN];
+  Xd cur;
+#pragma unroll
+  for (int k = 0; k < 9; k++) cur.r[k] = (k % 4 == 0) ? 1.0 : 0.0;
+  cur.p[0] = cur.p[1] = cur.p[2] = 0.0;
+  for (int c = 0; c < n_chain; c++) {
+    const double qc = chain[c].slot >= 0 ? q[i * D + chain[c].slot] : chain[c].qconst;
+    const Xd li = xd_mul(xd_from12(chain[c].P), xd_joint_motion(chain[c].type, chain[c].ax, qc));
+    cur = c == 0 ? li : xd_mul(cur, li);
+    T[c] = cur;
+  }
+  const Xd lw = xd_mul(cur, xd_from12(link2joint));
+  double *J = jac + i * 6 * D;
+  for (int k = 0; k < 6 * D; k++) J[k] = 0.0;
+  for (int c = 0; c < n_chain; c++) {
+    if (chain[c].slot < 0) continue;
+    const Xd X = local ? xd_inv_mul(lw, T[c]) : T[c];
+    const double *a = chain[c].ax;
+    const double ra[3] = {X.r[0] * a[0] + X.r[1] * a[1] + X.r[2] * a[2], X.r[3] * a[0] + X.r[4] * a[1] + X.r[5] * a[2],
+                          X.r[6] * a[0] + X.r[7] * a[1] + X.r[8] * a[2]};
+    double col[6] = {0, 0, 0, 0, 0, 0};
+    if (chain[c].type == MPB_JOINT_PRISMATIC) { col[0] = ra[0]; col[1] = ra[1]; col[2] = ra[2]; }
+    else {
+      col[0] = X.p[1] * ra[2] - X.p[2] * ra[1]; col[1] = X.p[2] * ra[0] - X.p[0] * ra[2]; col[2] = X.p[0] * ra[1] - X.p[1] * ra[0];
+      col[3] = ra[0]; col[4] = ra[1]; col[5] = ra[2];
+    }
+    for (int r = 0; r < 6; r++) J[r * D + chain[c].slot] = col[r];
+  }
+  double *o = link_T + i * 12;
+  for (int r = 0; r < 3; r++) { o[4 * r] = lw.r[3 * r]; o[4 * r + 1] = lw.r[3 * r + 1]; o[4 * r + 2] = lw.r[3 * r + 2]; o[4 * r + 3] = lw.p[r]; }
+}
