@@ -56,6 +56,7 @@ SYMBOLS = [
     "mpb_last_error", "mpb_device_count", "mpb_scene_create", "mpb_scene_destroy", "mpb_scene_set_q_base",
     "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
     "mpb_check_motion_batch", "mpb_rrtconnect_batch", "mpb_distance_batch", "mpb_ik_clik_batch",
+    "mpb_link_jacobian_batch",
 ]
 
 _lib = None
@@ -96,6 +97,7 @@ def load():
                                          C.POINTER(MpbRrtStats)]
     lib.mpb_ik_clik_batch.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int32,
                                       C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpb_link_jacobian_batch.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 
@@ -256,6 +258,17 @@ class DeviceScene:
         _check(load().mpb_ik_clik_batch(self._h, int(link), _ptr(poses), _ptr(q0), _ptr(m), n, float(eps), int(max_iter), float(dt),
                                         float(damp), _ptr(q), _ptr(ok), _ptr(err)))
         return q, ok.astype(bool), err
+
+    def link_jacobian(self, link, q, local=False):
+        """Batched computeFullJacobian + getLinkJacobian: q [n, D] -> (J [n, 6, D], link placement [n, 3, 4]), float64."""
+        q = np.ascontiguousarray(np.asarray(q, dtype=np.float64))
+        if q.ndim != 2 or q.shape[1] != self.state_dim:
+            raise RuntimeError("Qpos user2pinocchio failed")
+        n = q.shape[0]
+        J = np.zeros((n, 6, self.state_dim), dtype=np.float64)
+        T = np.zeros((n, 3, 4), dtype=np.float64)
+        _check(load().mpb_link_jacobian_batch(self._h, int(link), _ptr(q), n, 1 if local else 0, _ptr(J), _ptr(T)))
+        return J, T
 
     def fk_raw(self, q_ptr, n, poses_ptr, space=MPB_HOST, stream=None):
         _check(load().mpb_fk_batch(self._h, _ptr(q_ptr), int(n), _ptr(poses_ptr), space, _ptr(stream)))

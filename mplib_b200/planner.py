@@ -1,7 +1,8 @@
 """Host mirror of ``mplib.Planner`` (mplib/planner.py) for the calls that sit on the accelerated path: collision
-queries, SRDF auto-generation and joint-space planning.  Every numeric query goes through the C-ABI to the GPU.
+queries, SRDF auto-generation, IK, joint-space planning and screw motions.  Every numeric query goes through the C-ABI
+to the GPU.
 
-Out of scope here: `plan_screw` and TOPPRA time
+Out of scope here: TOPPRA time
 parametrisation (the `time` / `velocity` / `acceleration` keys of the reference's result dict) -- `toppra` is absent
 from this image; `plan_qpos` returns the waypoint matrix under "position" exactly as the reference hands it to TOPPRA
 (mplib/planner.py:493-510)."""
@@ -14,6 +15,7 @@ from xml.dom import minidom
 import numpy as np
 
 from .pymp import ArticulatedModel, OMPLPlanner, PlanningWorld
+from .urdf import quat_to_mat as _quat_to_mat
 
 
 class Planner:
@@ -292,6 +294,88 @@ class Planner:
         if status == "Exact solution":
             return {"status": "Success", "position": path}
         return {"status": "%s failed. %s" % (planner_name, status)}
+
+    # ------------------------------------------------------------------ screw motion
+    @staticmethod
+    def _pose2exp_coordinate(T):
+        """mplib/planner.py:574-604: (twist direction [v, w], angle) of a 4x4 rigid transform."""
+        R = T[:3, :3]
+        tr = R.trace()
+        if np.isclose(tr, 3):
+            omega, theta = np.zeros(3), 1
+        elif np.isclose(tr, -1):
+            return np.zeros(3), -1e6
+        else:
+            theta = np.arccos((tr - 1) / 2)
+            omega = 1 / 2 / np.sin(theta) * np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+        ss = np.array([[0, -omega[2], omega[1]], [omega[2], 0, -omega[0]], [-omega[1], omega[0], 0]])
+        inv_left_jacobian = np.eye(3) / theta - 0.5 * ss + (1.0 / theta - 0.5 / np.tan(theta / 2)) * ss @ ss
+        return np.concatenate([inv_left_jacobian @ T[:3, 3], omega]), theta
+
+    def plan_screw_batch(self, goal_poses, current_qposes, *, qpos_step=0.1, max_steps=100000):
+        """Q straight-line screw motions in lock step (mplib/planner.py:526-671 per query).  Every step evaluates the
+        WORLD Jacobian of the move-group link for all live queries in one device call (mpb_link_jacobian_batch), takes
+        the pseudo-inverse step of norm `qpos_step` on the host, and checks all new states with one mpb_collide_batch.
+        Joints outside the move group keep the articulation's current values in the collision check.
+        -> list of {"status", "position"[n, len(move group joints)]}; TOPPRA is not run (the waypoints are returned)."""
+        goal_poses = np.asarray(goal_poses, dtype=np.float64).reshape(-1, 7)
+        q = np.array(current_qposes, dtype=np.float64, copy=True)
+        Q, nv = q.shape
+        assert goal_poses.shape[0] == Q
+        idx = np.asarray(self.move_group_joint_indices)
+        pm = self.pinocchio_model
+        dev, link = pm._device_scene(), int(pm.link_user2model[self.link_name_2_idx[self.move_group]])
+        _, T0 = dev.link_jacobian(link, q)
+        omega = np.zeros((Q, 6))
+        live = np.ones(Q, dtype=bool)
+        results = [None] * Q
+        for i in range(Q):
+            cur, tgt = np.eye(4), np.eye(4)
+            cur[:3, :] = T0[i]
+            tgt[:3, 3] = goal_poses[i, :3]
+            tgt[:3, :3] = np.asarray(_quat_to_mat(*goal_poses[i, 3:])).reshape(3, 3)
+            w, theta = self._pose2exp_coordinate(tgt @ np.linalg.inv(cur))
+            if theta < -1e4:
+                results[i], live[i] = {"status": "screw plan failed."}, False
+            omega[i] = w * theta
+        paths = [[q[i, idx].copy()] for i in range(Q)]
+        lo, hi = self.joint_limits[:, 0] - 1e-3, self.joint_limits[:, 1] + 1e-3
+        for _ in range(max_steps):
+            a = np.nonzero(live)[0]
+            if a.size == 0:
+                break
+            J, _ = dev.link_jacobian(link, q[a])
+            dq = np.einsum("nij,nj->ni", np.linalg.pinv(J), omega[a])
+            with np.errstate(divide="ignore", invalid="ignore"):
+                dq *= (qpos_step / np.linalg.norm(dq, axis=1))[:, None]
+            dtw = np.einsum("nij,nj->ni", J, dq)
+            n_tw, n_om = np.linalg.norm(dtw, axis=1), np.linalg.norm(omega[a], axis=1)
+            flag = n_tw > n_om
+            with np.errstate(divide="ignore", invalid="ignore"):
+                ratio = np.where(flag, n_om / n_tw, 1.0)
+            dq, dtw = dq * ratio[:, None], dtw * ratio[:, None]
+            q[a] += dq
+            omega[a] -= dtw
+            within = np.all((q[a] >= lo) & (q[a] <= hi), axis=1)
+            collide = self.planning_world.collide_batch(q[a][:, idx])
+            bad = ~(np.linalg.norm(dtw, axis=1) >= 1e-4) | collide | ~within
+            for k, i in enumerate(a):
+                if bad[k]:
+                    results[i], live[i] = {"status": "screw plan failed"}, False
+                    continue
+                paths[i].append(q[i, idx].copy())
+                if flag[k]:
+                    results[i], live[i] = {"status": "Success", "position": np.vstack(paths[i])}, False
+        for i in np.nonzero(live)[0]:
+            results[i] = {"status": "screw plan failed"}
+        return results
+
+    def plan_screw(self, goal_pose, current_qpos, *, time_step=0.1, qpos_step=0.1, verbose=False):
+        """mplib/planner.py:526-671 without the TOPPRA step (toppra is not in this image: the waypoints are returned
+        as "position", the hand-off format of mplib/planner.py:358-375)."""
+        current_qpos = np.array(current_qpos, dtype=np.float64, copy=True)
+        self.robot.set_qpos(current_qpos, True)
+        return self.plan_screw_batch(np.asarray(goal_pose, dtype=np.float64)[None, :], current_qpos[None, :], qpos_step=qpos_step)[0]
 
     def plan_qpos_batch(self, start_qposes, goal_qposes, *, rrt_range=0.1, planning_time=1.0, **kw):
         """Q independent joint-space queries at once (see OMPLPlanner.plan_batch).  -> list of result dicts"""

@@ -179,10 +179,36 @@ class PinocchioModel:
                                                 np.asarray(q_init, dtype=np.float64)[None, :], mask, eps, maxIter, dt, damp)
         return q[0], bool(ok[0]), err[0]
 
-    def _not_on_path(self, *a, **k):
-        raise NotImplementedError("Jacobian queries / joint-limited CLIK are outside the accelerated path (SURVEY 8f)")
+    def get_link_jacobian_batch(self, index, qpos, local=False):
+        """n states at once: qpos [n, nv] (user order) -> J [n, 6, nv], rows (linear, angular), columns in user joint
+        order (``getLinkJacobian`` after ``computeFullJacobian``, ``src/pinocchio_model.cpp:335-360``)."""
+        if not (0 <= index < len(self.user_link_names)):
+            raise RuntimeError("The link index is out of bound!")
+        return self._device_scene().link_jacobian(int(self.link_user2model[index]), qpos, local)[0]
 
-    compute_full_jacobian = get_link_jacobian = compute_single_link_local_jacobian = _not_on_path
+    def compute_full_jacobian(self, qpos):
+        """``computeFullJacobian``: remembers the state; ``get_link_jacobian`` evaluates the requested link's rows."""
+        q = np.asarray(qpos, dtype=np.float64).reshape(-1)
+        if q.shape[0] != self.km.nv:
+            raise RuntimeError("Qpos user2pinocchio failed")
+        self._jac_q = q.copy()
+
+    def get_link_jacobian(self, index, local=False):
+        q = getattr(self, "_jac_q", None)
+        if q is None:
+            raise RuntimeError("compute_full_jacobian has not been called")
+        return self.get_link_jacobian_batch(index, q[None, :], local)[0]
+
+    def compute_single_link_local_jacobian(self, qpos, index):
+        """``computeSingleLinkLocalJacobian`` (``src/pinocchio_model.cpp:362-375``): the Jacobian in the link's own frame."""
+        q = np.asarray(qpos, dtype=np.float64).reshape(-1)
+        if q.shape[0] != self.km.nv:
+            raise RuntimeError("Qpos user2pinocchio failed")
+        return self.get_link_jacobian_batch(index, q[None, :], True)[0]
+
+    def _not_on_path(self, *a, **k):
+        raise NotImplementedError("joint-limited CLIK is outside the accelerated path (SURVEY 8f)")
+
     compute_IK_CLIK_JL = _not_on_path
 
 

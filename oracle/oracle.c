@@ -1251,3 +1251,42 @@ int orc_ik_clik_batch(const mpb_scene_desc *d, int link, const double *poses, co
   free(slot_of_q);
   return 0;
 }
+
+/* PinocchioModelTpl::computeFullJacobian + getLinkJacobian (src/pinocchio_model.cpp:335-360): Pinocchio's
+ * computeJointJacobians fills data.J with column j = oMi[j].act(S_j) (the joint's motion subspace seen from the world
+ * origin: (p x a, a) for a revolute joint with origin p and world axis a, (a, 0) for a prismatic one); getJointJacobian
+ * (WORLD) keeps the columns of the joints supporting `link`'s parent joint; local: link2world.toActionMatrixInverse() * J.
+ * jac [n][6][state_dim], link_T [n][12] (3x4 row-major world placement of the link). */
+int orc_link_jacobian_batch(const mpb_scene_desc *d, int link, const double *q, int64_t n, int local, double *jac, double *link_T) {
+  if (link < 0 || link >= d->n_links) return -1;
+  const int D = d->state_dim;
+  double *qfull = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+  int *slot_of_q = (int *)malloc(sizeof(int) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+  for (int k = 0; k < d->nq_full; k++) slot_of_q[k] = -1;
+  for (int k = 0; k < D; k++) slot_of_q[d->state_map[k]] = k;
+  for (int64_t i = 0; i < n; i++) {
+    memcpy(qfull, d->q_base, sizeof(double) * (size_t)d->nq_full);
+    for (int k = 0; k < D; k++) qfull[d->state_map[k]] = q[i * D + k];
+    fk_joints(d, qfull, oMi);
+    xf_t L, lw; xf_from12(&L, d->link_placement + 12 * link);
+    const int pj = d->link_joint[link];
+    if (pj == 0) lw = L; else xf_mul(&lw, &oMi[pj], &L);
+    double *J = jac + i * 6 * D;
+    for (int k = 0; k < 6 * D; k++) J[k] = 0.0;
+    for (int j = pj; j != 0; j = d->joint_parent[j - 1]) {
+      const int sl = slot_of_q[d->joint_qidx[j - 1]];
+      if (sl < 0) continue;
+      xf_t X;
+      if (local) xf_inv_mul(&X, &lw, &oMi[j]); else X = oMi[j];
+      double a[3], col[6] = {0, 0, 0, 0, 0, 0};
+      xf_rot(a, &X, d->joint_axis + 3 * (j - 1));
+      if (d->joint_type[j - 1] == MPB_JOINT_PRISMATIC) copy3(col, a);
+      else { cross3(col, X.p, a); copy3(col + 3, a); }
+      for (int r = 0; r < 6; r++) J[r * D + sl] = col[r];
+    }
+    if (link_T) for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) link_T[12 * i + 4 * r + c] = lw.R[3 * r + c]; link_T[12 * i + 4 * r + 3] = lw.p[r]; }
+  }
+  free(qfull); free(oMi); free(slot_of_q);
+  return 0;
+}

@@ -185,3 +185,15 @@ def ik_clik_batch(desc, link, poses, q_init, mask=None, eps=1e-5, max_iter=1000,
                                  C.c_void_p(err.ctypes.data), C.c_int(int(threads)))
     assert rc == 0
     return q, ok.astype(bool), err
+
+
+def link_jacobian_batch(desc, link, q, local=False):
+    """computeFullJacobian + getLinkJacobian restatement: q [n, D] -> (J [n, 6, D], link placement [n, 3, 4])"""
+    q = _states(desc, q)
+    n, D = q.shape
+    J = np.zeros((n, 6, D))
+    T = np.zeros((n, 3, 4))
+    rc = lib().orc_link_jacobian_batch(C.byref(desc.as_struct()), C.c_int(int(link)), C.c_void_p(q.ctypes.data), C.c_int64(n),
+                                       C.c_int(1 if local else 0), C.c_void_p(J.ctypes.data), C.c_void_p(T.ctypes.data))
+    assert rc == 0
+    return J, T

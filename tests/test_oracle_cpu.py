@@ -183,3 +183,37 @@ def test_ik_clik_round_trip(panda_world):
     far[:, :3] = [3.0, 0.0, 0.5]
     _, okf, _ = O.ik_clik_batch(desc, li, far, q0[:4], max_iter=200)
     assert not okf.any()
+
+
+def test_link_jacobian_matches_finite_differences(panda_world):
+    """Oracle restatement of computeFullJacobian + getLinkJacobian (src/pinocchio_model.cpp:335-360) pinned by central
+    differences of the oracle's own FK: column j of the WORLD Jacobian is the spatial twist (v at the world origin, w)
+    of d/dq_j, i.e. dT/dq_j T^-1 = [[w]x, v]; the LOCAL form is the body twist T^-1 dT/dq_j."""
+    from oracle import oracle as O
+
+    desc = compile_desc(panda_world)
+    li = desc.link_names.index("panda_hand")
+    rng = np.random.Generator(np.random.PCG64(17))
+    q = PANDA_LO + (PANDA_HI - PANDA_LO) * rng.random((32, 7))
+    Jw, T = O.link_jacobian_batch(desc, li, q, local=False)
+    Jl, _ = O.link_jacobian_batch(desc, li, q, local=True)
+    assert np.abs(T[:, :, 3] - O.fk_batch(desc, q)[:, li, :3]).max() < 1e-12
+    h = 1e-6
+
+    def hom(q_):
+        _, T_ = O.link_jacobian_batch(desc, li, q_)
+        M = np.tile(np.eye(4), (T_.shape[0], 1, 1))
+        M[:, :3, :] = T_
+        return M
+
+    T0 = hom(q)
+    for j in range(7):
+        e = np.zeros(7)
+        e[j] = h
+        dT = (hom(q + e) - hom(q - e)) / (2 * h)
+        S = dT @ np.linalg.inv(T0)   # spatial twist matrix
+        B = np.linalg.inv(T0) @ dT   # body twist matrix
+        for M, J in ((S, Jw), (B, Jl)):
+            w = np.stack([M[:, 2, 1], M[:, 0, 2], M[:, 1, 0]], axis=1)
+            v = M[:, :3, 3]
+            assert np.abs(J[:, :3, j] - v).max() < 1e-7 and np.abs(J[:, 3:, j] - w).max() < 1e-7
