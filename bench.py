@@ -33,6 +33,7 @@ def parse():
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--inflight", type=int, default=2, help="blocking C-ABI calls kept in flight by the device-resident leg (value)")
     ap.add_argument("--e2e-inflight", type=int, default=2, help="blocking C-ABI calls kept in flight by the end-to-end leg")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
     ap.add_argument("--connect-steps", type=int, default=8, help="c4: connect-walk steps validated per lock-step round")
@@ -173,12 +174,18 @@ def run_c4(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    wl = WL.get("c4", args.batch)
-    w, desc, Q = wl["world"], wl["desc"], wl["batch"]
-    w.device = local  # the world compiles its scene image on this rank's GPU
-    pl = OMPLPlanner(w)
+    # F plan_batch calls in flight (F host threads, each with its own world / scene handle): a lock-step round is a
+    # chain of small kernels, so the rounds of independent query batches interleave on the GPU.
+    F = max(1, args.inflight)
+    wls = [WL.get("c4", args.batch) for _ in range(F)]
+    wl = wls[0]
+    desc, Q = wl["desc"], wl["batch"]
+    pls = []
+    for x in wls:
+        x["world"].device = local  # the world compiles its scene image on this rank's GPU
+        pls.append(OMPLPlanner(x["world"]))
     n_sets = min(args.warmup + args.steps, 4)
-    sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, w.collide_batch) for k in range(n_sets)]
+    sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, wl["world"].collide_batch) for k in range(n_sets)]
     kw = dict(range=0.1, time=args.plan_time, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048,
               connect_steps=args.connect_steps)
 
@@ -187,20 +194,40 @@ def run_c4(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for k in range(args.warmup):
-        pl.plan_batch(*sets[k % n_sets], seed=k, **kw)
+    def run(k0, k1):
+        out, errors = {}, []
+
+        def worker(t):
+            try:
+                torch.cuda.set_device(local)
+                for k in range(k0 + t, k1, F):
+                    out[k] = pls[t].plan_batch(*sets[k % n_sets], seed=k, **kw)[2]
+            except BaseException as e:
+                errors.append(e)
+
+        th = [threading.Thread(target=worker, args=(t,)) for t in range(F)]
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        if errors:
+            raise errors[0]
+        return out
+
+    run(0, max(args.warmup, F))
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    solved = gpu_ms = launches = rounds = states = 0
+    solved = launches = rounds = states = 0
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        status, paths, st = pl.plan_batch(*sets[(args.warmup + k) % n_sets], seed=args.warmup + k, **kw)
-        solved += st["n_solved"]; gpu_ms += st["gpu_ms"]; launches += st["kernel_launches"]; rounds += st["rounds"]
-        states += st["states_checked"]
+    res = run(args.warmup, args.warmup + args.steps)
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
+    # device time of the region: the calls of one host thread run back to back, the threads run concurrently
+    gpu_ms = max(sum(st["gpu_ms"] for k, st in res.items() if (k - args.warmup) % F == t) for t in range(F))
+    for st in res.values():
+        solved += st["n_solved"]; launches += st["kernel_launches"]; rounds += st["rounds"]; states += st["states_checked"]
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
@@ -220,7 +247,7 @@ def run_c4(args):
             "metric": PLAN_METRIC, "value": solved / (gpu_ms * 1e-3), "unit": PLAN_UNIT, "n_gpus": world, "steps": K,
             "warmup": args.warmup, "ms_per_step": gpu_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": wl["config"],
-            "solve_rate": solved / (float(Q) * world * K), "plan_time_budget_s": args.plan_time,
+            "solve_rate": solved / (float(Q) * world * K), "plan_time_budget_s": args.plan_time, "calls_in_flight": F,
             "e2e": {"value": solved / wall, "unit": PLAN_UNIT, "h2d_bytes_per_step": int(Q * 2 * desc.state_dim * 4 + Q * 4),
                     "d2h_bytes_per_step": int(Q * 8 + Q * kw["max_path"] * desc.state_dim * 4)},
             "gpu_launches": int(launches), "clocks": clocks,
@@ -295,35 +322,82 @@ def main():
     pool_h = [torch.from_numpy(wl["make_q"](rank * 1000 + k, N).astype(np.float32)).pin_memory() for k in range(n_pool)]
     pool_d = [t.cuda(non_blocking=True) for t in pool_h]
     vwords = (N + 31) // 32
-    # two result sets: the verdict gather of step k (NCCL, side stream) overlaps the kernels of step k + 1
-    verdict_d = [torch.zeros(vwords, dtype=torch.int32, device="cuda") for _ in range(2)]
-    pairs_d = [torch.zeros((N, max(W, 1)), dtype=torch.int32, device="cuda") for _ in range(2)]
-    gathered = [torch.zeros((world, vwords), dtype=torch.int32, device="cuda") for _ in range(2)] if world > 1 else None
+    # F calls in flight (F host threads, each with its own scene handle, stream and result set), the way a caller
+    # pipelines a blocking API: while one call synchronises to read its counters and the host enqueues its next pass,
+    # the other call's kernels keep the GPU busy.  The verdict gather of step k (NCCL, side stream, issued in step
+    # order by the main thread) overlaps the kernels of the following steps.  --inflight 1 is the strictly serial figure.
+    F = max(1, args.inflight)
+    devs_d = [dev] + [_lib.DeviceScene(desc, local) for _ in range(F - 1)]
+    streams = [torch.cuda.Stream() for _ in range(F)]
+    # verdict gather (NCCL): one all_gather per G steps of a call slot (G x 131 KB for C2), two buffers per slot, so a
+    # worker only waits for the gather issued two of its groups ago
+    G = 4 if world > 1 else 1
+    verdict_d = [[torch.zeros((G, vwords), dtype=torch.int32, device="cuda") for _ in range(2)] for _ in range(F)]
+    pairs_d = [[torch.zeros((N, max(W, 1)), dtype=torch.int32, device="cuda") for _ in range(2)] for _ in range(F)]
+    gathered = [[torch.zeros((world, G, vwords), dtype=torch.int32, device="cuda") for _ in range(2)] for _ in range(F)] if world > 1 else None
     comm = torch.cuda.Stream() if world > 1 else None
-    ev_done = [torch.cuda.Event() for _ in range(2)]
-    ev_gathered = [torch.cuda.Event() for _ in range(2)]
+    ev_done = [[torch.cuda.Event() for _ in range(2)] for _ in range(F)]
+    ev_gathered = [[torch.cuda.Event() for _ in range(2)] for _ in range(F)]
     verdict_h = torch.zeros(vwords, dtype=torch.int32).pin_memory()
     pairs_h = torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()
     torch.cuda.synchronize()
-    n_steps_done = [0]
 
-    def step_device(k):
-        b = n_steps_done[0] & 1
-        if world > 1 and n_steps_done[0] >= 2:
-            stream.wait_event(ev_gathered[b])  # the gather of step k - 2 has read this result set
-        st = dev.collide_raw(pool_d[k % n_pool], N, verdict_d[b], pairs_d[b], _lib.MPB_DEVICE, stream.cuda_stream)
-        if world > 1:
-            ev_done[b].record(stream)
-            with torch.cuda.stream(comm):
-                comm.wait_event(ev_done[b])
-                dist.all_gather_into_tensor(gathered[b], verdict_d[b])  # the only inter-GPU traffic: verdict words
-                ev_gathered[b].record(comm)
-        n_steps_done[0] += 1
-        return st
+    def run_device(k0, k1, start_event=None, F=F):
+        """Steps k0..k1-1 with F calls in flight; returns the per-step stats in step order."""
+        n_of = [len(range(k0 + t, k1, F)) for t in range(F)]      # steps of worker t
+        groups = [(n_of[t] + G - 1) // G for t in range(F)]         # gather groups of worker t
+        done = {(t, g): threading.Event() for t in range(F) for g in range(groups[t])}
+        issued = {(t, g): threading.Event() for t in range(F) for g in range(groups[t])}
+        stats = {}
+        errors = []
 
-    def drain():
+        def worker(t):
+            try:
+                torch.cuda.set_device(local)
+                if start_event is not None:
+                    streams[t].wait_event(start_event)
+                for j, k in enumerate(range(k0 + t, k1, F)):
+                    g, r = j // G, j % G
+                    b = g & 1
+                    if world > 1 and r == 0 and g >= 2:
+                        issued[(t, g - 2)].wait()
+                        streams[t].wait_event(ev_gathered[t][b])  # the gather that read this buffer two groups ago
+                    stats[k] = devs_d[t].collide_raw(pool_d[k % n_pool], N, verdict_d[t][b][r], pairs_d[t][b], _lib.MPB_DEVICE,
+                                                     streams[t].cuda_stream)
+                    if r == G - 1 or j == n_of[t] - 1:
+                        ev_done[t][b].record(streams[t])
+                        done[(t, g)].set()
+            except BaseException as e:  # surface worker failures instead of hanging the main thread
+                errors.append(e)
+                for ev in list(done.values()) + list(issued.values()):
+                    ev.set()
+
+        th = [threading.Thread(target=worker, args=(t,)) for t in range(F)]
+        for x in th:
+            x.start()
         if world > 1:
-            stream.wait_stream(comm)
+            for g in range(max(groups)):
+                for t in range(F):
+                    if g >= groups[t] or errors:
+                        continue
+                    done[(t, g)].wait()
+                    if errors:
+                        break
+                    b = g & 1
+                    with torch.cuda.stream(comm):
+                        comm.wait_event(ev_done[t][b])
+                        dist.all_gather_into_tensor(gathered[t][b], verdict_d[t][b])  # the only inter-GPU traffic: verdict words
+                        ev_gathered[t][b].record(comm)
+                    issued[(t, g)].set()
+        for x in th:
+            x.join()
+        if errors:
+            raise errors[0]
+        for t in range(F):
+            stream.wait_stream(streams[t])
+        if world > 1:
+            stream.wait_stream(comm)  # the last gathers are inside the timed region
+        return [stats[k] for k in range(k0, k1)]
 
     def step_host(k):
         return dev.collide_raw(pool_h[k % n_pool], N, verdict_h, pairs_h, _lib.MPB_HOST, stream.cuda_stream)
@@ -333,9 +407,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for k in range(args.warmup):
-        step_device(k)
-    drain()
+    run_device(0, args.warmup)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -344,16 +416,26 @@ def main():
     agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "gpu_ms_fk": 0.0, "pairs_after_cull": 0, "pairs_after_spheres": 0, "narrow_iterations": 0, "narrow_capped": 0,
            "kernel_launches": 0}
     e0.record(stream)
-    for k in range(args.steps):
-        st = step_device(args.warmup + k)
-        for key in agg:
-            agg[key] += st[key]
-        fk_bytes = st["fk_bytes_per_state"]
-    drain()  # the last gathers are inside the timed region
-    e1.record(stream)
+    per_step = run_device(args.warmup, args.warmup + args.steps, start_event=e0)
+    e1.record(stream)  # the worker streams and the gather stream have been joined into this one
     barrier()
     ms = e0.elapsed_time(e1)
+    # per-kernel durations: with several calls in flight the kernels of different calls share the SMs and each call's
+    # event intervals stretch, so the kernel split (and the fk_table_kernel roofline) comes from a short serial leg
+    # of the same steps, one call in flight, still inside the clock-sampled region
+    if F > 1:
+        per_step_serial = run_device(args.warmup + args.steps, args.warmup + args.steps + min(args.steps, 5), F=1)
+    else:
+        per_step_serial = per_step
     clocks = sampler.stop() if rank == 0 else None
+    Ks = len(per_step_serial)
+    for st in per_step_serial:
+        for key in ("gpu_ms_cull", "gpu_ms_narrow", "gpu_ms_fk"):
+            agg[key] += st[key] * args.steps / Ks  # scaled to K steps so the per-step divisions below stay uniform
+    for st in per_step:
+        for key in ("pairs_after_cull", "pairs_after_spheres", "narrow_iterations", "narrow_capped", "kernel_launches"):
+            agg[key] += st[key]
+        fk_bytes = st["fk_bytes_per_state"]
     if world > 1:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -363,7 +445,7 @@ def main():
     # with its own scene handle, streams and pinned result buffers), the way a caller pipelines a blocking API: the
     # H2D copy of one call runs under the kernels of the other.  --e2e-inflight 1 gives the strictly serial figure.
     n_fl = max(1, args.e2e_inflight)
-    devs = [dev] + [_lib.DeviceScene(desc, local) for _ in range(n_fl - 1)]
+    devs = (devs_d + [_lib.DeviceScene(desc, local) for _ in range(max(0, n_fl - len(devs_d)))])[:n_fl]
     outs = [(verdict_h, pairs_h)] + [(torch.zeros(vwords, dtype=torch.int32).pin_memory(),
                                       torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()) for _ in range(n_fl - 1)]
 
@@ -397,7 +479,7 @@ def main():
         f = wl["flop_model"]
         iters_per_step = agg["narrow_iterations"] / K
         F_step = N * (f["F_fk"] + 12.0 * desc.n_pairs) + iters_per_step * (2.0 * (5.0 * f["V_mean"] + 33.0) + 150.0)
-        kernels_ms = (agg["gpu_ms_cull"] + agg["gpu_ms_narrow"]) / K
+        kernels_ms = ms / K  # the whole device-timed step (with calls in flight the per-call kernel intervals overlap)
         peak_probe = _lib.fp32_peak_tflops(local)
         props = torch.cuda.get_device_properties(local)
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
@@ -418,6 +500,7 @@ def main():
             "data": "synthetic", "config": wl["config"],
             "e2e": {"value": total_checks / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(N * D * 4),
                     "d2h_bytes_per_step": int(vwords * 4 + N * max(W, 1) * 4), "calls_in_flight": n_fl},
+            "calls_in_flight": F,
             "gpu_launches": int(agg["kernel_launches"]),
             "clocks": clocks,
             "roofline": {
@@ -425,7 +508,8 @@ def main():
                 "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
                 "peak_source": "in-run FFMA probe (mpb_fp32_peak); formula SMs*128*2*f_sampled = %.1f" % peak_formula,
                 "flop_per_check": F_step / N, "traffic": None, "dominant_kernel": dominant,
-                "kernel_ms_per_step": {"fk_table+sphere+dense+scan+scatter": agg["gpu_ms_cull"] / K, "narrow(+expand)": agg["gpu_ms_narrow"] / K},
+                "kernel_ms_per_step": {"fk_table+sphere+dense+scan+scatter": agg["gpu_ms_cull"] / K, "narrow(+expand)": agg["gpu_ms_narrow"] / K,
+                                       "measured": "serial leg of %d steps, one call in flight" % Ks},
                 "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
                         "bytes_per_check": B_alg, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
                 # the one HBM-bound kernel of the pass, timed alone with CUDA events on its own stream inside the C-ABI call

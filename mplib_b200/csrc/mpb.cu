@@ -66,7 +66,7 @@ struct mpb_scene {
   size_t cull_cap = 0;
   SceneImg img{};
   float *d_pose = nullptr;   // sphere table [n_dyn * 3 + n_jslots * 12][pose_ld]
-  float4 *d_obb = nullptr;   // OBB table [pose_ld][n_dyn][3]
+  float4 *d_obb = nullptr;   // OBB table [n_dyn][pose_ld][2]: unit quaternion xyzw, translation
   size_t pose_ld = 0;
   uint2 *d_sq = nullptr;     // survivor queue of the sphere phase: (configuration, cull-table entry)
   unsigned sq_cap = 0;
@@ -898,7 +898,7 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   const size_t pose_words = (size_t)s->img.n_jslots * 12 + (size_t)s->img.n_dyn * 3;
   CU(cudaMalloc((void **)&s->d_pose, std::max<size_t>(pose_words * s->pose_ld, 4) * sizeof(float)));
   if (s->d_obb) { cudaFree(s->d_obb); s->d_obb = nullptr; }
-  CU(cudaMalloc((void **)&s->d_obb, std::max<size_t>((size_t)s->img.n_dyn * 3 * s->pose_ld, 1) * sizeof(float4)));
+  CU(cudaMalloc((void **)&s->d_obb, std::max<size_t>((size_t)s->img.n_dyn * 2 * s->pose_ld, 1) * sizeof(float4)));
   // survivors of the sphere phase: every admitted pair of every configuration at worst, bounded like the work queue
   const size_t sq_cap = std::max<size_t>(std::min((size_t)chunk * P + (size_t)s->num_sms * 64 * MPB_SQ_CHUNK, kMaxSurvivors), 4096);
   CU(cudaMalloc((void **)&s->d_sq, sq_cap * sizeof(uint2)));
@@ -975,7 +975,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((mm + 127) / 128);
       if (ev && !hq) CU(cudaEventRecord(f0, st));
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 3);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
       if (ev && !hq) CU(cudaEventRecord(f1, st));
       const int sblocks = std::min(cblocks, s->num_sms * 16);  // persistent warps: survivor-queue chunks carry over between tiles
       sphere_kernel<0><<<sblocks, 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
@@ -1103,7 +1103,7 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
       fk += c;
     }
     stats->gpu_ms_fk = fk;
-    stats->fk_bytes_per_state = (int32_t)(4 * s->img.state_dim + 4 * (s->img.n_jslots * 12 + s->img.n_dyn * 3) + 48 * s->img.n_dyn);
+    stats->fk_bytes_per_state = (int32_t)(4 * s->img.state_dim + 4 * (s->img.n_jslots * 12 + s->img.n_dyn * 3) + 32 * s->img.n_dyn);
     stats->gpu_ms_cull = cull;
     stats->gpu_ms_narrow = narrow;
     stats->gpu_ms = cull + narrow;

@@ -226,9 +226,31 @@ __device__ __forceinline__ Xf pose_joint(const float *__restrict__ pose, size_t 
   return w;
 }
 
+// OBB table rows are (unit quaternion xyzw, translation): 32 B per object and configuration instead of a 48 B matrix.
+__device__ __forceinline__ float4 rot_to_quat(const float *R) {  // Shepperd's branches, normalised
+  float x, y, z, w;
+  const float tr = R[0] + R[4] + R[8];
+  if (tr > 0.f) { w = tr + 1.f; x = R[7] - R[5]; y = R[2] - R[6]; z = R[3] - R[1]; }
+  else if (R[0] >= R[4] && R[0] >= R[8]) { x = 1.f + R[0] - R[4] - R[8]; y = R[1] + R[3]; z = R[2] + R[6]; w = R[7] - R[5]; }
+  else if (R[4] >= R[8]) { y = 1.f + R[4] - R[0] - R[8]; x = R[1] + R[3]; z = R[5] + R[7]; w = R[2] - R[6]; }
+  else { z = 1.f + R[8] - R[0] - R[4]; x = R[2] + R[6]; y = R[5] + R[7]; w = R[3] - R[1]; }
+  const float s = rsqrtf(fmaf(x, x, fmaf(y, y, fmaf(z, z, w * w))));
+  return make_float4(x * s, y * s, z * s, w * s);
+}
+__device__ __forceinline__ Xf quat_rows(const float4 q, const float4 t) {
+  Xf o;
+  const float x2 = q.x + q.x, y2 = q.y + q.y, z2 = q.z + q.z;
+  const float xx = q.x * x2, yy = q.y * y2, zz = q.z * z2, xy = q.x * y2, xz = q.x * z2, yz = q.y * z2, wx = q.w * x2, wy = q.w * y2, wz = q.w * z2;
+  o.r[0] = 1.f - (yy + zz); o.r[1] = xy - wz;         o.r[2] = xz + wy;
+  o.r[3] = xy + wz;         o.r[4] = 1.f - (xx + zz); o.r[5] = yz - wx;
+  o.r[6] = xz - wy;         o.r[7] = yz + wx;         o.r[8] = 1.f - (xx + yy);
+  o.p[0] = t.x; o.p[1] = t.y; o.p[2] = t.z;
+  return o;
+}
+
 __global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
                                                        float4 *__restrict__ obb) {
-  __shared__ __align__(16) float s_tr[4][32 * 12];  // per warp: one object's 32 OBB frames, transposed for full-sector stores
+  __shared__ __align__(16) float s_tr[4][32 * 8];  // per warp: one object's 32 OBB frames, transposed for full-sector stores
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long tile0 = i - lane;
@@ -259,15 +281,14 @@ __global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float
       for (int k = 0; k < 3; k++) POSE(cbase + O.dyn * 3 + k, i) = c[k];
       const float4 *rec = img.cobb + MPB_COBB_WORDS * o;  // OBB frame in the joint frame -> world
       const Xf E = xf_mul(cur, xf_rows(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2)));
-      // OBB table [object][configuration][3 x float4]: the warp's 32 frames are 1536 contiguous bytes
-      float4 *mine = reinterpret_cast<float4 *>(tr) + lane * 3;
-      mine[0] = make_float4(E.r[0], E.r[1], E.r[2], E.p[0]);
-      mine[1] = make_float4(E.r[3], E.r[4], E.r[5], E.p[1]);
-      mine[2] = make_float4(E.r[6], E.r[7], E.r[8], E.p[2]);
+      // OBB table [object][configuration][quaternion, translation]: the warp's 32 frames are 1024 contiguous bytes
+      float4 *mine = reinterpret_cast<float4 *>(tr) + lane * 2;
+      mine[0] = rot_to_quat(E.r);
+      mine[1] = make_float4(E.p[0], E.p[1], E.p[2], 0.f);
       __syncwarp();
-      float4 *dst = obb + ((size_t)O.dyn * ld + tile0) * 3;
+      float4 *dst = obb + ((size_t)O.dyn * ld + tile0) * 2;
 #pragma unroll
-      for (int r = 0; r < 3; r++) dst[lane + 32 * r] = reinterpret_cast<const float4 *>(tr)[lane + 32 * r];
+      for (int r = 0; r < 2; r++) dst[lane + 32 * r] = reinterpret_cast<const float4 *>(tr)[lane + 32 * r];
       __syncwarp();
     }
   }
@@ -399,9 +420,12 @@ __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *
       const float4 *ca = img.cobb + MPB_COBB_WORDS * pr.a, *cb = img.cobb + MPB_COBB_WORDS * pr.b;
       const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
       const int da = __float_as_int(ia.w), db = __float_as_int(ib.w);
-      const float4 *pa = da >= 0 ? obb + ((size_t)da * ld + cfg) * 3 : ca;  // moving: this configuration's entry of the OBB table
-      const float4 *pb = db >= 0 ? obb + ((size_t)db * ld + cfg) * 3 : cb;
-      const Xf Ea = xf_rows(pa[0], pa[1], pa[2]), Eb = xf_rows(pb[0], pb[1], pb[2]);
+      // moving: this configuration's row of the OBB table (quaternion, translation); fixed: the record's world frame
+      Xf Ea, Eb;
+      if (da >= 0) { const float4 *pa = obb + ((size_t)da * ld + cfg) * 2; Ea = quat_rows(pa[0], pa[1]); }
+      else Ea = xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2));
+      if (db >= 0) { const float4 *pb = obb + ((size_t)db * ld + cfg) * 2; Eb = quat_rows(pb[0], pb[1]); }
+      else Eb = xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
       // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)  ==  (OBB frame A)^-1 (OBB frame B)
       Xf Rt;
       const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
