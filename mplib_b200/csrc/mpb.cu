@@ -56,15 +56,16 @@ struct mpb_scene {
   size_t pair_bin2_cap = 0;
   std::vector<int> h_pair_bin2;
   // cull table (fk_cull_kernel phase 2): pairs re-ordered into runs that share their moving object
-  std::vector<float4> h_cullc;
+  std::vector<float4> h_cullc, h_cullq;
   std::vector<int2> h_cullm;
   std::vector<int4> h_runs;
   float4 *d_cobb = nullptr;
-  float4 *d_cullc = nullptr;
+  float4 *d_cullc = nullptr, *d_cullq = nullptr;
   int2 *d_cullm = nullptr;
   int4 *d_runs = nullptr;
   size_t cull_cap = 0;
   SceneImg img{};
+  FkTab fk_tab{};            // joint / moving-object records of fk_table_kernel, passed by value (constant bank)
   float *d_pose = nullptr;   // sphere table [n_dyn * 3 + n_jslots * 12][pose_ld]
   float4 *d_obb = nullptr;   // OBB table [n_dyn][pose_ld][2]: unit quaternion xyzw, translation
   size_t pose_ld = 0;
@@ -85,6 +86,7 @@ struct mpb_scene {
   long long host_chunk = 0;
   bool smem_verts = true;
   int narrow_blocks = 0;
+  int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0};  // one resident wave of the static grid-stride kernels, per MODE
   std::vector<cudaEvent_t> events;
   // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
   // buffers cost more than a thousand planning rounds)
@@ -401,11 +403,22 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
       return x.p < y.p;
     });
     s->h_cullc.resize(n_pairs);
+    s->h_cullq.resize(n_pairs);
     s->h_cullm.resize(n_pairs);
     s->h_runs.clear();
     for (int k = 0; k < n_pairs; k++) {
       const Ent &e = ents[k];
       s->h_cullc[k] = make_float4(e.c[0], e.c[1], e.c[2], e.rr2);
+      {  // expanded form of the fixed-partner test (sphere_kernel): slack = a few ulp of the largest term, (|a| + |c|)^2
+        // with |a| within R1 + R2 of |c| whenever the verdict matters
+        const double c2 = (double)e.c[0] * e.c[0] + (double)e.c[1] * e.c[1] + (double)e.c[2] * e.c[2];
+        const double rr2 = e.rr2;
+        double w;
+        if (e.rr2 >= FLT_MAX) w = -FLT_MAX;
+        else if (e.rr2 < 0.f) w = c2 + 1.0;
+        else w = c2 - rr2 - 2e-6 * std::max(c2, rr2) - 1e-9;
+        s->h_cullq[k] = make_float4(-2.f * e.c[0], -2.f * e.c[1], -2.f * e.c[2], (float)w);
+      }
       s->h_cullm[k] = make_int2(e.p, (e.m1 + 1) | ((e.m2 + 1) << 16));
       if (s->h_runs.empty() || s->h_runs.back().x != e.m1 || s->h_runs.back().w != e.kind)
         s->h_runs.push_back(make_int4(e.m1, k, 1, e.kind));
@@ -441,17 +454,21 @@ static int upload_pairs(mpb_scene *s) {
   s->img.pair_bin2 = s->d_pair_bin2;
   if (n + 1 > s->cull_cap) {
     if (s->d_cullc) cudaFree(s->d_cullc);
+    if (s->d_cullq) cudaFree(s->d_cullq);
     if (s->d_cullm) cudaFree(s->d_cullm);
     if (s->d_runs) cudaFree(s->d_runs);
     s->cull_cap = std::max<size_t>(n + 1, 64);
     CU(cudaMalloc(&s->d_cullc, s->cull_cap * sizeof(float4)));
+    CU(cudaMalloc(&s->d_cullq, s->cull_cap * sizeof(float4)));
     CU(cudaMalloc(&s->d_cullm, s->cull_cap * sizeof(int2)));
     CU(cudaMalloc(&s->d_runs, s->cull_cap * sizeof(int4)));
   }
   if (n) CU(cudaMemcpy(s->d_cullc, s->h_cullc.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
+  if (n) CU(cudaMemcpy(s->d_cullq, s->h_cullq.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
   if (n) CU(cudaMemcpy(s->d_cullm, s->h_cullm.data(), n * sizeof(int2), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(s->d_runs, s->h_runs.data(), s->h_runs.size() * sizeof(int4), cudaMemcpyHostToDevice));
   s->img.cullc = s->d_cullc;
+  s->img.cullq = s->d_cullq;
   s->img.cullm = s->d_cullm;
   s->img.runs = s->d_runs;
   s->chunk = 0;  // queue sizing depends on the pair count
@@ -709,7 +726,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     }
     s->obj_key[o] = geom_key(O.type, O.geom);
   }
-  if (ndyn > 254) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (254)"); }
+  if (ndyn > MPB_MAX_DYN) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (MPB_MAX_DYN = 128)"); }
   std::vector<int> dynlist;
   for (int j = 0; j < d->n_joints; j++) {
     s->h_joints[j].dyn_first = (int)dynlist.size();
@@ -762,6 +779,14 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     memcpy(&df, &dyn, sizeof(float));
     rec[4] = make_float4(co[0], co[1], co[2], df);
   }
+  // fk_table_kernel's parameter-space tables: joints, and the moving objects grouped by owner joint
+  for (int j = 0; j < d->n_joints; j++) s->fk_tab.j[j] = s->h_joints[j];
+  for (size_t e = 0; e < dynlist.size(); e++) {
+    const int o = dynlist[e];
+    FkObjC &F = s->fk_tab.o[e];
+    for (int r = 0; r < 3; r++) { F.rec[r] = cobb[(size_t)MPB_COBB_WORDS * o + r]; F.bcj[r] = s->h_objs[o].bcj[r]; }
+    F.dyn = s->h_objs[o].dyn;
+  }
 
   s->img.n_joints = d->n_joints;
   s->img.n_objects = d->n_objects;
@@ -813,6 +838,14 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<false>, 256, 0));
   }
   s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
+  {  // sphere_kernel / dense_kernel split their range statically over the grid: exactly one resident wave, or the
+     // blocks beyond it run as a second, mostly empty wave
+    int b = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0>, 128, 0)); s->sphere_blocks[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<1>, 128, 0)); s->sphere_blocks[1] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<0>, 128, 0)); s->dense_blocks[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<1>, 128, 0)); s->dense_blocks[1] = s->num_sms * std::max(b, 1);
+  }
   *out = s;
   return MPB_OK;
 }
@@ -822,7 +855,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &b : s->pool) cudaFree(b.first);
@@ -850,6 +883,7 @@ extern "C" int mpb_scene_set_q_base(mpb_scene *s, const double *q_base, int32_t 
   if (nq_full != s->nq_full) return fail(MPB_ERR_INVALID, "q_base length does not match the scene");
   CU(cudaSetDevice(s->device));
   for (size_t j = 0; j < s->h_joints.size(); j++) s->h_joints[j].qconst = (float)q_base[s->joint_qidx[j]];
+  for (size_t j = 0; j < s->h_joints.size(); j++) s->fk_tab.j[j].qconst = s->h_joints[j].qconst;
   s->h_qbase64.assign(q_base, q_base + nq_full);
   CU(cudaStreamSynchronize(s->stream));
   if (!s->h_joints.empty())
@@ -975,9 +1009,9 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((mm + 127) / 128);
       if (ev && !hq) CU(cudaEventRecord(f0, st));
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
       if (ev && !hq) CU(cudaEventRecord(f1, st));
-      const int sblocks = std::min(cblocks, s->num_sms * 16);  // persistent warps: survivor-queue chunks carry over between tiles
+      const int sblocks = std::min(cblocks, s->sphere_blocks[0]);  // persistent warps: survivor-queue chunks carry over between tiles
       sphere_kernel<0><<<sblocks, 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       *launches += 2;
     }
@@ -990,7 +1024,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     return MPB_OK;
   }
-  dense_kernel<0><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
+  dense_kernel<0><<<s->dense_blocks[0], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
   *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
@@ -1590,9 +1624,9 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     CU(cudaEventRecord(e0, st));
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((m + 127) / 128);
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, dq, m, s->d_pose, s->pose_ld, s->d_obb);
-      sphere_kernel<1><<<std::min(cblocks, s->num_sms * 16), 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
-      dense_kernel<1><<<s->num_sms * 8, 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, dq, m, s->d_pose, s->pose_ld, s->d_obb);
+      sphere_kernel<1><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
+      dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, -1, (unsigned)dblocks * 8u, s->sq_cap);
       scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));

@@ -13,7 +13,7 @@
 #include <stdint.h>
 
 #define MPB_MAX_JOINTS 32   // movable joints in the merged forest (two Pandas = 18)
-#define MPB_MAX_DYN 40      // objects that move with a joint
+#define MPB_MAX_DYN 128     // objects that move with a joint (8-bit slot fields; fk_table_kernel's parameter table)
 #define MPB_ITEM_WORDS 14   // 12 floats relative transform + cfg + pair
 
 struct alignas(16) DevJoint {

@@ -37,6 +37,7 @@ struct SceneImg {
   const float4 *prims;      // leaf primitives, 3 float4 each
   const float4 *cobb;       // [n_objects][5] cull records (see fk_cull_kernel phase 3)
   const float4 *cullc;      // [n_pairs] cull table: world-fixed partner's sphere centre (xyz), (R1 + R2 + margin)^2 (w)
+  const float4 *cullq;      // [n_pairs] world-fixed partners in expanded form: (-2c, |c|^2 - (R1 + R2)^2 - slack), see sphere_kernel
   const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}
   const int4 *runs;         // cull-table runs: {moving slot or -1, first entry, count, partner kind (0 fixed, 1 moving)}
   const int *pair_bin2;     // [n_pairs] bin of the leaf-level items a BVH pair expands into (-1: not a BVH pair)
@@ -177,8 +178,10 @@ __device__ __forceinline__ Xf joint_step(const DevJoint &J, const Xf *parent, fl
     }
     return o;
   }
+  // MUFU sine / cosine: absolute error < 1e-6 for |q| <= 2 pi (joint limits), i.e. < 1e-6 m per joint at 1 m reach; the
+  // pose table only feeds the culls and the narrowphase (contact band 1e-4 m).  The FK API (fk_pose_kernel) keeps sincosf.
   float s, c;
-  sincosf(q, &s, &c);
+  __sincosf(q, &s, &c);
   // rotation about +-axis k mixes the two other columns (u, v) of parent * P; -axis: opposite angle
 #define MPB_MIX(u, v)                                    \
   _Pragma("unroll") for (int r = 0; r < 3; r++) {        \
@@ -248,9 +251,24 @@ __device__ __forceinline__ Xf quat_rows(const float4 q, const float4 t) {
   return o;
 }
 
-__global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
+// The joint and moving-object records of the kernel travel as a kernel parameter (constant bank, uniform loads):
+// fetched from global memory they cost ~220 per-lane LDG per warp and made the L1/LSU data path the busiest unit of
+// the kernel (75 % of peak in the full ncu capture of round 1) although every lane reads the same address.
+struct FkObjC {
+  float4 rec[3];  // OBB frame in the owner joint frame (cull record words 0..2)
+  float bcj[3];   // bounding-sphere centre in the owner joint frame
+  int dyn;        // moving-object slot
+};
+struct FkTab {
+  DevJoint j[MPB_MAX_JOINTS];  // dyn_first indexes o[] (objects grouped by owner joint)
+  FkObjC o[MPB_MAX_DYN];
+};
+__global__ void __launch_bounds__(128) fk_table_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
+                                                       const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
                                                        float4 *__restrict__ obb) {
-  __shared__ __align__(16) float s_tr[4][32 * 8];  // per warp: one object's 32 OBB frames, transposed for full-sector stores
+  // per warp: one object's 32 OBB rows, transposed for full-sector stores.  Quaternions at float4 [0, 32), translations
+  // at [36, 68): the 4-word shift puts the two halves of a quarter-warp's interleaved read on disjoint banks
+  __shared__ __align__(16) float s_tr[4][68 * 4];
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long tile0 = i - lane;
@@ -261,7 +279,7 @@ __global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float
   Xf cur = xf_identity();
   const float *qrow = q + ic * img.state_dim;
   for (int j = 0; j < img.n_joints; j++) {
-    const DevJoint &J = img.joints[j];
+    const DevJoint &J = tab.j[j];
     const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
     if (J.parent == 0) cur = joint_step(J, nullptr, qj);
     else if (J.pjslot >= 0) { const Xf par = pose_joint(pose, ld, jbase + J.pjslot * 12, i); cur = joint_step(J, &par, qj); }
@@ -273,22 +291,23 @@ __global__ void __launch_bounds__(128) fk_table_kernel(SceneImg img, const float
       for (int k = 0; k < 3; k++) POSE(jbase + J.jslot * 12 + 9 + k, i) = cur.p[k];
     }
     for (int e = 0; e < J.dyn_count; e++) {
-      const int o = img.dynlist[J.dyn_first + e];
-      const DevObject &O = img.objs[o];
+      const FkObjC &O = tab.o[J.dyn_first + e];
       float c[3];
       xf_point(cur, O.bcj, c);  // bounding-sphere centre in the joint frame -> world
 #pragma unroll
       for (int k = 0; k < 3; k++) POSE(cbase + O.dyn * 3 + k, i) = c[k];
-      const float4 *rec = img.cobb + MPB_COBB_WORDS * o;  // OBB frame in the joint frame -> world
-      const Xf E = xf_mul(cur, xf_rows(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2)));
+      const Xf E = xf_mul(cur, xf_rows(O.rec[0], O.rec[1], O.rec[2]));  // OBB frame in the joint frame -> world
       // OBB table [object][configuration][quaternion, translation]: the warp's 32 frames are 1024 contiguous bytes
-      float4 *mine = reinterpret_cast<float4 *>(tr) + lane * 2;
-      mine[0] = rot_to_quat(E.r);
-      mine[1] = make_float4(E.p[0], E.p[1], E.p[2], 0.f);
+      float4 *tr4 = reinterpret_cast<float4 *>(tr);
+      tr4[lane] = rot_to_quat(E.r);
+      tr4[36 + lane] = make_float4(E.p[0], E.p[1], E.p[2], 0.f);
       __syncwarp();
       float4 *dst = obb + ((size_t)O.dyn * ld + tile0) * 2;
 #pragma unroll
-      for (int r = 0; r < 2; r++) dst[lane + 32 * r] = reinterpret_cast<const float4 *>(tr)[lane + 32 * r];
+      for (int r = 0; r < 2; r++) {
+        const unsigned o = lane + 32 * r;  // output word: configuration o / 2, half o % 2
+        dst[o] = tr4[(o & 1u) * 36 + (o >> 1)];
+      }
       __syncwarp();
     }
   }
@@ -332,14 +351,23 @@ __global__ void __launch_bounds__(128) sphere_kernel(SceneImg img, const float *
       const int rend = min(rlast, gend);
       float ax = 0.f, ay = 0.f, az = 0.f;
       if (run.x >= 0) { ax = POSE(cbase + run.x * 3, ic); ay = POSE(cbase + run.x * 3 + 1, ic); az = POSE(cbase + run.x * 3 + 2, ic); }
-      if (run.w == 0) {  // world-fixed partners: centre + (R1 + R2)^2 in one uniform 16-byte load
+      if (run.w == 0 && MODE == 0) {
+        // world-fixed partners, one uniform 16-byte load each.  |a - c|^2 <= rr2 in expanded form,
+        // |a|^2 + (-2c).a + (|c|^2 - rr2) <= 0: three FFMA and a compare per pair; the host subtracts a slack that
+        // covers the cancellation error, so the test stays a conservative cull
+        const float na2 = -fmaf(ax, ax, fmaf(ay, ay, az * az));
+#pragma unroll 8
+        for (; k < rend; k++) {
+          const float4 c = __ldg(img.cullq + k);
+          mask |= (unsigned)(fmaf(ax, c.x, fmaf(ay, c.y, fmaf(az, c.z, c.w))) <= na2) << (k - gbase);
+        }
+      } else if (run.w == 0) {  // distance mode: centre + (R1 + R2)^2
 #pragma unroll 8
         for (; k < rend; k++) {
           const float4 c = __ldg(img.cullc + k);
           const float dx = ax - c.x, dy = ay - c.y, dz = az - c.z;
           const float d2c = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-          const bool s = MODE == 0 ? (d2c <= c.w) : (sqrtf(d2c) - sqrtf(c.w) <= ub_min);
-          mask |= (unsigned)s << (k - gbase);
+          mask |= (unsigned)(sqrtf(d2c) - sqrtf(c.w) <= ub_min) << (k - gbase);
         }
       } else {  // moving partners
         for (; k < rend; k++) {
@@ -985,7 +1013,7 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fm
 // lets the lanes that hold surviving leaves test / emit their primitives.  No divergence inside the 15-axis test and
 // a short critical path even for small batches (a planning round); when the stack runs nearly full the warp pops
 // one node per trip (depth-first), which bounds the growth by the tree depth.
-__global__ void __launch_bounds__(128) expand_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
+__global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
                                                      unsigned int *__restrict__ pair_bits) {
   __shared__ int s_stack[4][MPB_EXP_STACK];
   const int eb = img.expand_bin;
