@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -65,6 +66,11 @@ struct mpb_scene {
   int4 *d_runs = nullptr;
   size_t cull_cap = 0;
   SceneImg img{};
+  // sphere_kernel's cull table in parameter space when it has at most 256 entries (4 KB; a 28 KB table for the C3 scene
+  // thrashed the constant cache: cull leg 12.7 -> 15.5 ms); tier 0 = global tables
+  typedef CullTabC<256, 64> CullSmall;
+  CullSmall ct_small{};
+  int cull_tier = 0;
   FkTab fk_tab{};            // joint / moving-object records of fk_table_kernel, passed by value (constant bank)
   float *d_pose = nullptr;   // sphere table [n_dyn * 3 + n_jslots * 12][pose_ld]
   float4 *d_obb = nullptr;   // OBB table [n_dyn][pose_ld][2]: unit quaternion xyzw, translation
@@ -86,7 +92,7 @@ struct mpb_scene {
   long long host_chunk = 0;
   bool smem_verts = true;
   int narrow_blocks = 0;
-  int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0};  // one resident wave of the static grid-stride kernels, per MODE
+  int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0};  // one resident wave of the static grid-stride kernels, per MODE
   std::vector<cudaEvent_t> events;
   // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
   // buffers cost more than a thousand planning rounds)
@@ -341,6 +347,8 @@ static void build_cell_table(const double *V, int nv, std::vector<unsigned char>
   memcpy(out.data() + 2 * (MPB_CELL_COUNT + 1), cand.data(), cand.size());
 }
 
+static inline float __int_as_float_host(int v) { float f; memcpy(&f, &v, sizeof f); return f; }
+
 static int geom_key(int type, int geom) { return type == MPB_GEOM_CONVEX ? 16 + geom : type; }
 
 static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32_t *pb) {
@@ -426,6 +434,18 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
         s->h_runs.back().z++;
     }
     s->h_runs.push_back(make_int4(-1, n_pairs, 0, 0));  // sentinel: the run cursor may step one past the last run
+    {  // parameter-space copy for sphere_kernel<0>
+      static const bool ct_on = !(getenv("MPB_CULL_PARAM") && atoi(getenv("MPB_CULL_PARAM")) == 0);
+      auto fill = [&](float4 *q, int4 *runs) {
+        for (int k = 0; k < n_pairs; k++) {
+          const int m2 = (s->h_cullm[k].y >> 16) - 1;
+          q[k] = m2 >= 0 ? make_float4(__int_as_float_host(m2), 0.f, 0.f, s->h_cullc[k].w) : s->h_cullq[k];
+        }
+        for (size_t r = 0; r < s->h_runs.size(); r++) runs[r] = s->h_runs[r];
+      };
+      s->cull_tier = 0;
+      if (ct_on && n_pairs <= 256 && s->h_runs.size() <= 64) { fill(s->ct_small.q, s->ct_small.runs); s->cull_tier = 1; }
+    }
   }
   s->img.n_pairs = n_pairs;
   s->img.n_bins = (int)bins.size();
@@ -841,8 +861,9 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   {  // sphere_kernel / dense_kernel split their range statically over the grid: exactly one resident wave, or the
      // blocks beyond it run as a second, mostly empty wave
     int b = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0>, 128, 0)); s->sphere_blocks[0] = s->num_sms * std::max(b, 1);
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<1>, 128, 0)); s->sphere_blocks[1] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 0, 0>, 128, 0)); s->sphere_blocks[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 256, 64>, 128, 0)); s->sphere_blocks_ct[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<1, 0, 0>, 128, 0)); s->sphere_blocks[1] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<0>, 128, 0)); s->dense_blocks[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<1>, 128, 0)); s->dense_blocks[1] = s->num_sms * std::max(b, 1);
   }
@@ -1012,7 +1033,11 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
       if (ev && !hq) CU(cudaEventRecord(f1, st));
       const int sblocks = std::min(cblocks, s->sphere_blocks[0]);  // persistent warps: survivor-queue chunks carry over between tiles
-      sphere_kernel<0><<<sblocks, 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
+      if (s->cull_tier == 1)
+        sphere_kernel<0, 256, 64><<<std::min(cblocks, s->sphere_blocks_ct[0]), 128, 0, st>>>(s->img, s->ct_small, s->d_pose + off, s->pose_ld, mm, off, s->d_sq,
+                                                                                              s->sq_cap, s->wq.totals);
+      else
+        sphere_kernel<0, 0, 0><<<sblocks, 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       *launches += 2;
     }
   }
@@ -1625,7 +1650,7 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((m + 127) / 128);
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, dq, m, s->d_pose, s->pose_ld, s->d_obb);
-      sphere_kernel<1><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
+      sphere_kernel<1, 0, 0><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
       dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, -1, (unsigned)dblocks * 8u, s->sq_cap);
       scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);

@@ -313,8 +313,18 @@ __global__ void __launch_bounds__(128) fk_table_kernel(const __grid_constant__ S
   }
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(128) sphere_kernel(SceneImg img, const float *__restrict__ pose, size_t ld, long long n, long long cfg_base,
+// Cull table in parameter space (constant bank): the entries are the same for every lane, and fetched with per-lane
+// LDG.128 each one writes 512 B back through the LSU.  NQ entries / NR runs; larger scenes use the global tables.
+template <int NQ, int NR>
+struct CullTabC {
+  float4 q[NQ];   // fixed partner: (-2c, |c|^2 - rr2 - slack); moving partner: (slot as int bits, 0, 0, rr2)
+  int4 runs[NR];
+};
+template <>
+struct CullTabC<0, 0> {};
+template <int MODE, int NQ, int NR>
+__global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ CullTabC<NQ, NR> ct,
+                                                     const float *__restrict__ pose, size_t ld, long long n, long long cfg_base,
                                                      uint2 *__restrict__ sq, unsigned sq_cap, unsigned *__restrict__ totals) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
@@ -346,12 +356,30 @@ __global__ void __launch_bounds__(128) sphere_kernel(SceneImg img, const float *
     unsigned mask = 0;
     int k = gbase;
     while (k < gend) {
-      const int4 run = __ldg(img.runs + r);  // {moving slot or -1, first, count, partner kind}
+      int4 run;  // {moving slot or -1, first, count, partner kind}
+      if constexpr (NQ > 0) run = ct.runs[r];
+      else run = __ldg(img.runs + r);
       const int rlast = run.y + run.z;
       const int rend = min(rlast, gend);
       float ax = 0.f, ay = 0.f, az = 0.f;
       if (run.x >= 0) { ax = POSE(cbase + run.x * 3, ic); ay = POSE(cbase + run.x * 3 + 1, ic); az = POSE(cbase + run.x * 3 + 2, ic); }
-      if (run.w == 0 && MODE == 0) {
+      if constexpr (NQ > 0) {  // MODE 0 only
+        const float na2 = -fmaf(ax, ax, fmaf(ay, ay, az * az));
+        if (run.w == 0) {
+#pragma unroll 8
+          for (; k < rend; k++) {
+            const float4 c = ct.q[k];
+            mask |= (unsigned)(fmaf(ax, c.x, fmaf(ay, c.y, fmaf(az, c.z, c.w))) <= na2) << (k - gbase);
+          }
+        } else {
+          for (; k < rend; k++) {
+            const float4 c = ct.q[k];
+            const int m2 = __float_as_int(c.x);
+            const float dx = ax - POSE(cbase + m2 * 3, ic), dy = ay - POSE(cbase + m2 * 3 + 1, ic), dz = az - POSE(cbase + m2 * 3 + 2, ic);
+            mask |= (unsigned)(fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= c.w) << (k - gbase);
+          }
+        }
+      } else if (run.w == 0 && MODE == 0) {
         // world-fixed partners, one uniform 16-byte load each.  |a - c|^2 <= rr2 in expanded form,
         // |a|^2 + (-2c).a + (|c|^2 - rr2) <= 0: three FFMA and a compare per pair; the host subtracts a slack that
         // covers the cancellation error, so the test stays a conservative cull
