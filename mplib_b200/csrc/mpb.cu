@@ -92,7 +92,8 @@ struct mpb_scene {
   long long host_chunk = 0;
   bool smem_verts = true;
   int narrow_blocks = 0;
-  int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0};  // one resident wave of the static grid-stride kernels, per MODE
+  int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0}, sphere_blocks_blk[2] = {0, 0};
+  int sphere_cb = 4;         // tiles of 32 configurations per warp of sphere_blk_kernel (large cull tables)  // one resident wave of the static grid-stride kernels, per MODE
   std::vector<cudaEvent_t> events;
   // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
   // buffers cost more than a thousand planning rounds)
@@ -863,6 +864,9 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     int b = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 0, 0>, 128, 0)); s->sphere_blocks[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 256, 64>, 128, 0)); s->sphere_blocks_ct[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_blk_kernel<2>, 128, 0)); s->sphere_blocks_blk[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_blk_kernel<4>, 128, 0)); s->sphere_blocks_blk[1] = s->num_sms * std::max(b, 1);
+    if (getenv("MPB_SPHERE_CB")) s->sphere_cb = atoi(getenv("MPB_SPHERE_CB"));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<1, 0, 0>, 128, 0)); s->sphere_blocks[1] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<0>, 128, 0)); s->dense_blocks[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<1>, 128, 0)); s->dense_blocks[1] = s->num_sms * std::max(b, 1);
@@ -1036,6 +1040,10 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       if (s->cull_tier == 1)
         sphere_kernel<0, 256, 64><<<std::min(cblocks, s->sphere_blocks_ct[0]), 128, 0, st>>>(s->img, s->ct_small, s->d_pose + off, s->pose_ld, mm, off, s->d_sq,
                                                                                               s->sq_cap, s->wq.totals);
+      else if (s->sphere_cb == 2)
+        sphere_blk_kernel<2><<<std::min((cblocks + 1) / 2, s->sphere_blocks_blk[0]), 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
+      else if (s->sphere_cb == 4)
+        sphere_blk_kernel<4><<<std::min((cblocks + 3) / 4, s->sphere_blocks_blk[1]), 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       else
         sphere_kernel<0, 0, 0><<<sblocks, 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       *launches += 2;

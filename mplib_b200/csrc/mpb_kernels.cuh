@@ -445,6 +445,108 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
     if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
 }
 
+// sphere_kernel<0> for cull tables too large for the parameter space (C3: 1587 entries), register-blocked over CB
+// tiles of 32 configurations: an entry fetched with a per-lane LDG.128 writes 512 B back through the LSU (4 cycles per
+// SM) although every lane reads the same address, which is more than the ~8 instructions of its test cost to issue;
+// applying each fetched entry to CB configurations per lane divides that cost by CB.
+__device__ __forceinline__ void push_survivors(unsigned mask, unsigned cfg, int gbase, unsigned lane, uint2 *__restrict__ sq, unsigned sq_cap,
+                                               unsigned *__restrict__ totals, unsigned &wbase, unsigned &wused, unsigned &wcap) {
+  const unsigned FULL = 0xffffffffu;
+  if (!__any_sync(FULL, mask != 0)) return;
+  const unsigned c = __popc(mask);
+  unsigned incl = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(FULL, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  const unsigned wtot = __shfl_sync(FULL, incl, 31);
+  if (wused + wtot > wcap) {
+    for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+      if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);  // unused tail of the old chunk
+    const unsigned want = max((unsigned)MPB_SQ_CHUNK, wtot);
+    unsigned nb = 0;
+    if (lane == 0) nb = atomicAdd(&totals[6], want);
+    wbase = __shfl_sync(FULL, nb, 0);
+    wused = 0;
+    wcap = want;
+  }
+  unsigned pos = wbase + wused + incl - c;
+  while (mask) {
+    const int kk = __ffs(mask) - 1;
+    mask &= mask - 1;
+    if (pos < sq_cap) sq[pos] = make_uint2(cfg, (unsigned)(gbase + kk));
+    pos++;
+  }
+  wused += wtot;
+}
+
+#define POSE(w, i) pose[(size_t)(w) * ld + (i)]
+template <int CB>
+__global__ void __launch_bounds__(128) sphere_blk_kernel(const __grid_constant__ SceneImg img, const float *__restrict__ pose, size_t ld, long long n,
+                                                         long long cfg_base, uint2 *__restrict__ sq, unsigned sq_cap, unsigned *__restrict__ totals) {
+  const unsigned lane = threadIdx.x & 31;
+  const int cbase = img.w_sphere;
+  unsigned wbase = 0, wused = 0, wcap = 0;  // warp-uniform survivor-queue chunk, kept across the warp's tiles
+  const long long n_tiles = (n + 31) / 32, n_groups = (n_tiles + CB - 1) / CB;
+  const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long grp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); grp < n_groups; grp += warp_stride) {
+    long long i[CB], ic[CB];
+    bool valid[CB];
+#pragma unroll
+    for (int c = 0; c < CB; c++) {
+      i[c] = (grp * CB + c) * 32 + lane;
+      valid[c] = i[c] < n;
+      ic[c] = valid[c] ? i[c] : n - 1;
+    }
+    int r = 0;  // run cursor
+    for (int gbase = 0; gbase < img.n_pairs; gbase += 32) {
+      const int gend = min(gbase + 32, img.n_pairs);
+      unsigned mask[CB];
+#pragma unroll
+      for (int c = 0; c < CB; c++) mask[c] = 0;
+      int k = gbase;
+      while (k < gend) {
+        const int4 run = __ldg(img.runs + r);  // {moving slot or -1, first, count, partner kind}
+        const int rlast = run.y + run.z;
+        const int rend = min(rlast, gend);
+        float ax[CB], ay[CB], az[CB], na2[CB];
+#pragma unroll
+        for (int c = 0; c < CB; c++) {
+          ax[c] = ay[c] = az[c] = 0.f;
+          if (run.x >= 0) { ax[c] = POSE(cbase + run.x * 3, ic[c]); ay[c] = POSE(cbase + run.x * 3 + 1, ic[c]); az[c] = POSE(cbase + run.x * 3 + 2, ic[c]); }
+          na2[c] = -fmaf(ax[c], ax[c], fmaf(ay[c], ay[c], az[c] * az[c]));
+        }
+        if (run.w == 0) {  // world-fixed partners, expanded form (see sphere_kernel)
+#pragma unroll 4
+          for (; k < rend; k++) {
+            const float4 q = __ldg(img.cullq + k);
+#pragma unroll
+            for (int c = 0; c < CB; c++) mask[c] |= (unsigned)(fmaf(ax[c], q.x, fmaf(ay[c], q.y, fmaf(az[c], q.z, q.w))) <= na2[c]) << (k - gbase);
+          }
+        } else {  // moving partners
+          for (; k < rend; k++) {
+            const float rr2 = __ldg(&img.cullc[k].w);
+            const int m2 = (__ldg(&img.cullm[k].y) >> 16) - 1;
+#pragma unroll
+            for (int c = 0; c < CB; c++) {
+              const float dx = ax[c] - POSE(cbase + m2 * 3, ic[c]), dy = ay[c] - POSE(cbase + m2 * 3 + 1, ic[c]), dz = az[c] - POSE(cbase + m2 * 3 + 2, ic[c]);
+              mask[c] |= (unsigned)(fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= rr2) << (k - gbase);
+            }
+          }
+        }
+        if (rend == rlast) r++;
+      }
+#pragma unroll
+      for (int c = 0; c < CB; c++)
+        push_survivors(valid[c] ? mask[c] : 0u, (unsigned)(cfg_base + i[c]), gbase, lane, sq, sq_cap, totals, wbase, wused, wcap);
+    }
+  }
+  for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+    if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
+}
+#undef POSE
+
 template <int MODE>
 __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
                                                     unsigned sq_cap, WorkQ wq, unsigned int *__restrict__ verdict_bits,
