@@ -561,13 +561,17 @@ __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *
   const unsigned total = min(wq.totals[6], sq_cap);
   const unsigned total_r = (total + 31u) & ~31u;
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&wq.counters[3], (unsigned long long)total);  // incl. chunk padding
-  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < total_r; e += gridDim.x * blockDim.x) {
+  const unsigned e_first = blockIdx.x * blockDim.x + threadIdx.x, e_stride = gridDim.x * blockDim.x;
+  uint2 ent_next = make_uint2(0xffffffffu, 0u);  // the survivor record of the next trip is fetched one trip ahead
+  if (e_first < total) ent_next = sq[e_first];
+  for (unsigned e = e_first; e < total_r; e += e_stride) {
     bool keep = false;
     Xf rel;
     int p = 0;
     unsigned cfg = 0;
-    uint2 ent = make_uint2(0xffffffffu, 0u);
-    if (e < total) ent = sq[e];
+    const uint2 ent = ent_next;
+    ent_next = make_uint2(0xffffffffu, 0u);
+    if (e + e_stride < total) ent_next = sq[e + e_stride];
     if (ent.x != 0xffffffffu) {
       cfg = ent.x;
       p = __ldg(&img.cullm[ent.y].x);
