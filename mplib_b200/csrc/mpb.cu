@@ -445,7 +445,8 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
         for (size_t r = 0; r < s->h_runs.size(); r++) runs[r] = s->h_runs[r];
       };
       s->cull_tier = 0;
-      if (ct_on && n_pairs <= 256 && s->h_runs.size() <= 64) { fill(s->ct_small.q, s->ct_small.runs); s->cull_tier = 1; }
+      // 30 moving objects: 46 KB of staged sphere centres per block
+      if (ct_on && n_pairs <= 256 && s->h_runs.size() <= 64 && s->img.n_dyn <= 30) { fill(s->ct_small.q, s->ct_small.runs); s->cull_tier = 1; }
     }
   }
   s->img.n_pairs = n_pairs;
@@ -863,7 +864,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
      // blocks beyond it run as a second, mostly empty wave
     int b = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 0, 0>, 128, 0)); s->sphere_blocks[0] = s->num_sms * std::max(b, 1);
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 256, 64>, 128, 0)); s->sphere_blocks_ct[0] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<0, 256, 64>, 128, (size_t)s->img.n_dyn * 3 * 128 * sizeof(float))); s->sphere_blocks_ct[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_blk_kernel<2>, 128, 0)); s->sphere_blocks_blk[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_blk_kernel<4>, 128, 0)); s->sphere_blocks_blk[1] = s->num_sms * std::max(b, 1);
     if (getenv("MPB_SPHERE_CB")) s->sphere_cb = atoi(getenv("MPB_SPHERE_CB"));
@@ -1038,7 +1039,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       if (ev && !hq) CU(cudaEventRecord(f1, st));
       const int sblocks = std::min(cblocks, s->sphere_blocks[0]);  // persistent warps: survivor-queue chunks carry over between tiles
       if (s->cull_tier == 1)
-        sphere_kernel<0, 256, 64><<<std::min(cblocks, s->sphere_blocks_ct[0]), 128, 0, st>>>(s->img, s->ct_small, s->d_pose + off, s->pose_ld, mm, off, s->d_sq,
+        sphere_kernel<0, 256, 64><<<std::min(cblocks, s->sphere_blocks_ct[0]), 128, (size_t)s->img.n_dyn * 3 * 128 * sizeof(float), st>>>(s->img, s->ct_small, s->d_pose + off, s->pose_ld, mm, off, s->d_sq,
                                                                                               s->sq_cap, s->wq.totals);
       else if (s->sphere_cb == 2)
         sphere_blk_kernel<2><<<std::min((cblocks + 1) / 2, s->sphere_blocks_blk[0]), 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);

@@ -329,6 +329,8 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
   const int cbase = img.w_sphere;
+  extern __shared__ float s_ctr[];  // NQ > 0: [warp][n_dyn * 3][32] sphere centres of the warp's tile
+  float *ctr = s_ctr + (size_t)(threadIdx.x >> 5) * (img.n_dyn * 3 * 32) + lane;
   unsigned wbase = 0, wused = 0, wcap = 0;  // warp-uniform survivor-queue chunk, kept across the warp's tiles
   const long long n_tiles = (n + 31) / 32;
   const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
@@ -336,6 +338,14 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
   const long long i = tile * 32 + lane;  // whole warps run; lanes past n push nothing
   const bool valid = i < n;
   const long long ic = valid ? i : n - 1;
+  if constexpr (NQ > 0) {
+    // parameter-space tier (few pairs, mostly moving x moving): the tile's sphere centres are staged once in the
+    // warp's [word][lane] block of shared memory; a partner's centre is then three LDS at a 32-bit address instead of
+    // three global loads with 64-bit index arithmetic (41 -> 16 instructions per moving x moving pair)
+    const float *pcol = pose + (size_t)cbase * ld + ic;
+#pragma unroll 4
+    for (int w = 0; w < img.n_dyn * 3; w++) ctr[w * 32] = pcol[(size_t)w * ld];
+  }
   float ub_min = FLT_MAX;
   if (MODE == 1) {
     for (int k = 0; k < img.n_pairs; k++) {
@@ -362,7 +372,11 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
       const int rlast = run.y + run.z;
       const int rend = min(rlast, gend);
       float ax = 0.f, ay = 0.f, az = 0.f;
-      if (run.x >= 0) { ax = POSE(cbase + run.x * 3, ic); ay = POSE(cbase + run.x * 3 + 1, ic); az = POSE(cbase + run.x * 3 + 2, ic); }
+      if constexpr (NQ > 0) {
+        if (run.x >= 0) { ax = ctr[run.x * 96]; ay = ctr[run.x * 96 + 32]; az = ctr[run.x * 96 + 64]; }
+      } else {
+        if (run.x >= 0) { ax = POSE(cbase + run.x * 3, ic); ay = POSE(cbase + run.x * 3 + 1, ic); az = POSE(cbase + run.x * 3 + 2, ic); }
+      }
       if constexpr (NQ > 0) {  // MODE 0 only
         const float na2 = -fmaf(ax, ax, fmaf(ay, ay, az * az));
         if (run.w == 0) {
@@ -372,10 +386,11 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
             mask |= (unsigned)(fmaf(ax, c.x, fmaf(ay, c.y, fmaf(az, c.z, c.w))) <= na2) << (k - gbase);
           }
         } else {
+#pragma unroll 4
           for (; k < rend; k++) {
             const float4 c = ct.q[k];
             const int m2 = __float_as_int(c.x);
-            const float dx = ax - POSE(cbase + m2 * 3, ic), dy = ay - POSE(cbase + m2 * 3 + 1, ic), dz = az - POSE(cbase + m2 * 3 + 2, ic);
+            const float dx = ax - ctr[m2 * 96], dy = ay - ctr[m2 * 96 + 32], dz = az - ctr[m2 * 96 + 64];
             mask |= (unsigned)(fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= c.w) << (k - gbase);
           }
         }
