@@ -290,6 +290,27 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def ncu_traffic(workload, kernel):
+    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of `kernel` from the committed
+    `ncu --set full` capture of this workload (profiles/r01_final_ncu_full_<w>_raw.csv), or None."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "r01_final_ncu_full_%s_raw.csv" % workload)
+    try:
+        rows = list(csv.reader(open(path)))
+        hdr, units = rows[0], rows[1]
+        ik, ir, iw, ig = (hdr.index(c) for c in ("Kernel Name", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__grid_size"))
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        for r in rows[2:]:
+            if kernel in r[ik]:
+                b = float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
+                states = int(float(r[ig])) * 128
+                return {"dram_bytes_per_launch": b, "states_per_launch": states, "dram_bytes_per_state": b / states,
+                        "source": os.path.relpath(path, ROOT)}
+    except Exception:
+        pass
+    return None
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -517,6 +538,7 @@ def main():
                                     "peak": hbm_peak, "unit": "GB/s",
                                     "frac": N * fk_bytes / (agg["gpu_ms_fk"] / K * 1e-3) / 1e9 / hbm_peak if agg["gpu_ms_fk"] > 0 else None,
                                     "bytes_per_state": fk_bytes, "ms_per_step": agg["gpu_ms_fk"] / K,
+                                    "traffic": ncu_traffic(args.workload, "fk_table_kernel"),
                                     "share_of_step": agg["gpu_ms_fk"] / max(agg["gpu_ms_cull"] + agg["gpu_ms_narrow"], 1e-9)},
             },
             "stats_per_step": {"pairs_after_spheres": agg["pairs_after_spheres"] / K, "pairs_after_cull": agg["pairs_after_cull"] / K, "support_evals": iters_per_step,

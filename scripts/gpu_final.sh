@@ -5,8 +5,8 @@ python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest 
 python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err
 python bench.py --workload c3 --steps 5 > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err
 python bench.py --workload c5 --steps 5 > gpurun_out/bench_c5.json 2> gpurun_out/bench_c5.err
-python bench.py --workload c4 --steps 3 --warmup 1 > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err
-python bench.py --workload c4 --steps 3 --warmup 1 --plan-time 0.25 > gpurun_out/bench_c4_t025.json 2>> gpurun_out/bench_c4.err
+python bench.py --workload c4 --steps 4 --warmup 2 > gpurun_out/bench_c4.json 2> gpurun_out/bench_c4.err
+python bench.py --workload c4 --steps 4 --warmup 2 --plan-time 0.25 > gpurun_out/bench_c4_t025.json 2>> gpurun_out/bench_c4.err
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_c2.json 2>&1
 python bench.py --impl reference --workload c4 --steps 2 --warmup 0 > gpurun_out/bench_ref_c4.json 2>&1
 python bench.py --impl reference --workload c3 --steps 2 --warmup 1 > gpurun_out/bench_ref_c3.json 2>&1
