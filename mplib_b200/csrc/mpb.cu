@@ -56,7 +56,7 @@ struct mpb_scene {
   int *d_pair_bin2 = nullptr;
   size_t pair_bin2_cap = 0;
   std::vector<int> h_pair_bin2;
-  // cull table (fk_cull_kernel phase 2): pairs re-ordered into runs that share their moving object
+  // cull table (sphere_kernel): pairs re-ordered into runs that share their moving object
   std::vector<float4> h_cullc, h_cullq;
   std::vector<int2> h_cullm;
   std::vector<int4> h_runs;
@@ -386,7 +386,7 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
     const int da = s->h_objs[a].dyn + 1, db = s->h_objs[b].dyn + 1;
     s->h_pairs[p] = DevPair{a, b, bin | (da << 16) | (db << 24), s->h_objs[a].br + s->h_objs[b].br + 1e-5f};
   }
-  // cull table: entries sorted by (moving object, partner kind, pair index); see fk_cull_kernel phase 2
+  // cull table: entries sorted by (moving object, partner kind, pair index); see sphere_kernel
   {
     struct Ent { int m1, kind, p, m2; float c[3]; float rr2; };
     std::vector<Ent> ents((size_t)n_pairs);

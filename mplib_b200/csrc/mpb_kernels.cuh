@@ -1,15 +1,17 @@
 // mpb_kernels.cuh -- sm_100a kernels of the batched state-validity path.
 //
-//   fk_cull_kernel     thread per configuration.  FK streams down the kinematic forest with the running
-//                      joint transform in registers (branch points parked in a small per-thread table);
-//                      the world poses of the moving collision objects live in SHARED memory, transposed
-//                      [object][word][thread] so every access is conflict-free -- poses never leave the SM.
-//                      (Replaces PinocchioModelTpl::computeForwardKinematics + getLinkPose +
-//                      FCLModelTpl::updateCollisionObjects + AttachedBodyTpl::updatePose,
+//   fk_table_kernel    thread per configuration.  FK streams down the kinematic forest with the running joint
+//                      transform in registers; joint / moving-object records come from the parameter space (FkTab).
+//                      Writes the pose tables in HBM: OBB rows (quaternion + translation, 32 B per moving object) and
+//                      the word-major sphere table.  (Replaces PinocchioModelTpl::computeForwardKinematics +
+//                      getLinkPose + FCLModelTpl::updateCollisionObjects + AttachedBodyTpl::updatePose,
 //                      src/pinocchio_model.cpp:271-312, src/fcl_model.cpp:138-148, src/attached_body.h:48-54.)
-//                      Admitted pairs are walked 32 at a time: a uniform bounding-sphere test builds a
-//                      per-lane bitmask, then the lanes pop their own survivors for a 15-axis OBB SAT;
-//                      what is left is ballot-compacted into a staging queue (one atomic per warp).
+//   sphere_kernel      thread per configuration over the cull table (admitted pairs in runs that share their moving
+//   sphere_blk_kernel  object): bounding-sphere test, 32 entries per mask word, survivors pushed into warp-private
+//                      chunks of the survivor queue.  Small tables ride in the parameter space with the tile's
+//                      sphere centres staged in shared memory; large ones are applied to four tiles per fetch.
+//   dense_kernel       thread per survivor: 15-axis OBB SAT from the two OBB rows, inscribed-ball sufficient test,
+//                      relative pose of what is left -> staging queue (one atomic per warp and 256 slots).
 //   scan_bins_kernel   prefix sums of the per-bin counts -> binned queue offsets.
 //   scatter_kernel     staging queue -> binned queue (bin = (geometry A, geometry B) class).
 //   narrow_kernel      lane per work item with PERSISTENT lanes: a warp owns a slice of ONE bin, so all
@@ -35,7 +37,7 @@ struct SceneImg {
   const int *dynlist;   // moving objects grouped by owner joint
   const DevBvhNode *nodes;  // BVH node pool (meshes, octrees); DevObject::voff = root, ::vcnt = leaf type
   const float4 *prims;      // leaf primitives, 3 float4 each
-  const float4 *cobb;       // [n_objects][5] cull records (see fk_cull_kernel phase 3)
+  const float4 *cobb;       // [n_objects][MPB_COBB_WORDS] cull records (see dense_kernel)
   const float4 *cullc;      // [n_pairs] cull table: world-fixed partner's sphere centre (xyz), (R1 + R2 + margin)^2 (w)
   const float4 *cullq;      // [n_pairs] world-fixed partners in expanded form: (-2c, |c|^2 - (R1 + R2)^2 - slack), see sphere_kernel
   const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}

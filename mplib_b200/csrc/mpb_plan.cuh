@@ -160,7 +160,7 @@ __device__ __forceinline__ float rrt_uniform(unsigned long long seed, unsigned q
 }
 
 // A query that has finished (or a speculative slot that is not used this round) must not cost narrowphase work:
-// its edge slots are set to NaN, which every bounding-sphere comparison of fk_cull_kernel rejects.
+// its edge slots are set to NaN, which every bounding-sphere comparison of sphere_kernel rejects.
 __device__ __forceinline__ void rrt_blank_edges(float *ea, float *eb, int n, int lane) {
   const float nanv = __int_as_float(0x7fc00000);
   for (int i = lane; i < n; i += 32) { ea[i] = nanv; eb[i] = nanv; }
