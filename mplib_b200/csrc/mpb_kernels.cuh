@@ -1174,69 +1174,23 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
   int *stack = s_stack[warp];
   const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
   for (;;) {
-    // 32 items per ticket.  Phase A, lane per item (coalesced reads of the binned queue): the shape's axis-aligned
-    // bounds in the BVH object's frame against the top three levels of the tree.  Most items end here (a link that is
-    // nowhere near the table), at ~150 lane-instructions instead of a warp-wide set-up; phase B below runs the
-    // warp-cooperative descent for the items that are left.
+    // four items per ticket; lanes 0..3 fetch their (configuration, pair, already-known) in parallel
     unsigned it0 = 0;
-    if (lane == 0) it0 = atomicAdd(&wq.totals[5], 32u);
+    if (lane == 0) it0 = atomicAdd(&wq.totals[5], 4u);
     it0 = first + __shfl_sync(FULL, it0, 0);
     if (it0 >= end) break;
     int my_cfg = 0, my_p = 0;
-    bool my_alive = false;
-    if (it0 + lane < end) {
-      const unsigned itx = it0 + lane;
-      my_cfg = wq.icfg[itx];
-      my_p = wq.ipair[itx];
-      const bool known = pair_bits ? ((pair_bits[(size_t)my_cfg * img.pair_words + (my_p >> 5)] >> (my_p & 31)) & 1u)
-                                   : ((verdict_bits[my_cfg >> 5] >> (my_cfg & 31)) & 1u);
-      if (!known) {
-        const DevPair pr = img.pairs[my_p];
-        const DevObject &A = img.objs[pr.a];
-        float R[9], t[3];
-#pragma unroll
-        for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + itx];
-#pragma unroll
-        for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + itx];
-        const float d0 = A.oc[0] - t[0], d1 = A.oc[1] - t[1], d2 = A.oc[2] - t[2];
-        float ca[3], bh[3];
-#pragma unroll
-        for (int r = 0; r < 3; r++) {
-          ca[r] = fmaf(R[r], d0, fmaf(R[3 + r], d1, R[6 + r] * d2));
-          float e = 1e-5f;
-#pragma unroll
-          for (int c = 0; c < 3; c++) e = fmaf(fabsf(fmaf(R[r], A.oR[c], fmaf(R[3 + r], A.oR[3 + c], R[6 + r] * A.oR[6 + c]))), A.oh[c], e);
-          bh[r] = e;
-        }
-        auto hit = [&](int node, int &l, int &rr) {
-          const DevBvhNode nd = img.nodes[node];
-          l = nd.left; rr = nd.right;
-          return fabsf(nd.c[0] - ca[0]) <= nd.h[0] + bh[0] && fabsf(nd.c[1] - ca[1]) <= nd.h[1] + bh[1] && fabsf(nd.c[2] - ca[2]) <= nd.h[2] + bh[2];
-        };
-        int l0, r0;
-        if (hit(img.objs[pr.b].voff, l0, r0)) {
-          if (l0 < 0) my_alive = true;
-          for (int a = 0; a < 2 && !my_alive; a++) {
-            int l1, r1;
-            if (!hit(a ? r0 : l0, l1, r1)) continue;
-            if (l1 < 0) { my_alive = true; break; }
-            for (int b = 0; b < 2 && !my_alive; b++) {
-              int l2, r2;
-              if (!hit(b ? r1 : l1, l2, r2)) continue;
-              if (l2 < 0) { my_alive = true; break; }
-              int l3, r3;
-              my_alive = hit(l2, l3, r3) || hit(r2, l3, r3);
-            }
-          }
-        }
-      }
+    bool my_known = true;
+    if (lane < 4 && it0 + lane < end) {
+      my_cfg = wq.icfg[it0 + lane];
+      my_p = wq.ipair[it0 + lane];
+      my_known = pair_bits ? ((pair_bits[(size_t)my_cfg * img.pair_words + (my_p >> 5)] >> (my_p & 31)) & 1u)
+                           : ((verdict_bits[my_cfg >> 5] >> (my_cfg & 31)) & 1u);
     }
-    unsigned alive = __ballot_sync(FULL, my_alive);
-    while (alive) {
-    const int sub = __ffs(alive) - 1;
-    alive &= alive - 1;
+    for (int sub = 0; sub < 4; sub++) {
     const unsigned it = it0 + sub;
     const int cfg = __shfl_sync(FULL, my_cfg, sub), p = __shfl_sync(FULL, my_p, sub);
+    if (__shfl_sync(FULL, (int)my_known, sub)) continue;  // also covers slots past the end of the bin
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // the shape
     const DevObject &B = img.objs[pr.b];  // the BVH object
@@ -1360,7 +1314,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
       if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
     }
     __syncwarp();
-    }  // surviving items of the ticket
+    }  // sub-items of the ticket
   }
 }
 
