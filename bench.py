@@ -102,7 +102,10 @@ def cpu_leg(desc, q, threads, budget_s, chunk):
     """Time the oracle on successive chunks of q until ~budget_s of wall time is spent."""
     from oracle import oracle as O
 
-    O.collide_batch(desc, q[:1000], threads=threads)  # warm-up (page-in, OpenMP pool)
+    tw = time.perf_counter()
+    O.collide_batch(desc, q[:1000], threads=threads)  # warm-up (page-in, OpenMP pool); also sizes the chunks
+    tw = max(time.perf_counter() - tw, 1e-6)
+    chunk = int(max(1000, min(chunk, 1000 * budget_s / tw / 4)))  # at most about a quarter of the budget per chunk
     done, t0 = 0, time.perf_counter()
     while done < q.shape[0] and time.perf_counter() - t0 < budget_s:
         m = min(chunk, q.shape[0] - done)
