@@ -17,4 +17,7 @@ ncu --set full --clock-control none --import-source on -k regex:'fk_table|sphere
 C3="python bench.py --workload c3 --batch 262144 --steps 1 --warmup 1 --no-cpu-baseline"
 $C3 > gpurun_out/plain_c3.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'fk_table|sphere|dense|narrow|expand|scatter' -s 10 -c 10 -o gpurun_out/prof_c3 -f $C3 > gpurun_out/ncu_c3_full.log 2>&1
+C5="python bench.py --workload c5 --steps 1 --warmup 1 --no-cpu-baseline"
+$C5 > gpurun_out/plain_c5.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'fk_table|sphere|dense|narrow|scatter' -s 6 -c 6 -o gpurun_out/prof_c5 -f $C5 > gpurun_out/ncu_c5_full.log 2>&1
 tail -3 gpurun_out/pytest_gpu.log
