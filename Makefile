@@ -8,7 +8,8 @@ HDR = $(wildcard mplib_b200/csrc/*.cuh) include/mpb.h
 all: $(LIB) oracle
 
 $(LIB): $(SRC) $(HDR)
-	$(NVCC) $(NVCCFLAGS) -Xptxas -v -o $@ $(SRC) 2> mplib_b200/csrc/ptxas.log || (cat mplib_b200/csrc/ptxas.log; false)
+	mkdir -p build
+	$(NVCC) $(NVCCFLAGS) -Xptxas -v -o $@ $(SRC) 2> build/ptxas.log || (cat build/ptxas.log; false)
 
 oracle: oracle/_build/liboracle.so
 oracle/_build/liboracle.so: oracle/oracle.c include/mpb.h

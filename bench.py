@@ -1,11 +1,18 @@
 #!/usr/bin/env python
-"""bench.py -- Panda collision checks/sec (FK + self [+ env]) on B200, one process per GPU.
+"""bench.py -- Panda collision checks/sec (FK + self + env) and RRTConnect plans/sec on B200, one process per GPU.
 
-A *step* is one pass of the hot path (batched FK + broadphase + narrowphase + verdict pack) over one
-batch of synthetic configurations; `value` = checks/s with q resident in HBM, `e2e` = the same through
-the C-ABI with pinned HOST buffers (H2D of q and D2H of verdict/pair bits inside the timed region).
-`--impl reference` times the CPU restatement of the reference path (oracle/, all host threads) on a
-bounded sample of the same workload.  See DESIGN.md "Measurement".
+One run measures every workload BASELINE.json's metric names and prints ONE JSON line:
+
+  headline   configs[2] (C3): Panda + grasped box vs 128 primitives + mesh + 100k-point octree, 2^22 states per GPU per step
+  "also"     configs[1] (C2, FK + self-collision), configs[4] (C5, two Pandas), configs[3] (C4, RRTConnect plans/s)
+
+A *step* is one pass of the hot path (batched FK + broadphase + narrowphase + verdict / hit-list output) over one batch
+of synthetic configurations.  `value` = checks/s with q resident in HBM (device-pointer C-ABI calls enqueued back to
+back on one stream, CUDA events around the K steps); `e2e` = the same through the C-ABI with pinned HOST buffers
+(H2D of q, D2H of verdict words + sparse hit list inside the timed region).  Every record carries `roofline`,
+`cpu_baseline` (the hierarchical CPU restatement of the reference path, oracle/, timed beside it on a bounded sample)
+and `parity` (a sample of the same inputs checked against the exhaustive oracle outside the timed region).
+`--impl reference` times the CPU restatement with all host threads on the same workloads.  See DESIGN.md "Measurement".
 """
 import argparse
 import json
@@ -22,6 +29,9 @@ sys.path.insert(0, ROOT)
 
 METRIC = "panda_collision_checks_per_sec"
 UNIT = "checks/s"
+PLAN_METRIC = "panda_rrtconnect_plans_per_sec"
+PLAN_UNIT = "plans/s"
+BAND = 1e-4  # north_star: verdicts may differ only where the reference signed distance is within 1e-4 m of contact
 
 
 def parse():
@@ -30,25 +40,19 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
-    ap.add_argument("--batch", type=int, default=0, help="configurations per GPU per step (0 = workload default)")
+    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5"], help="the headline workload")
+    ap.add_argument("--also", default="c2,c5,c4", help="comma list of further workloads reported under \"also\" (\"none\" = just the headline)")
+    ap.add_argument("--batch", type=int, default=0, help="configurations (c4: queries) per GPU per step of the headline (0 = workload default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--inflight", type=int, default=2, help="blocking C-ABI calls kept in flight by the device-resident leg (value)")
-    ap.add_argument("--e2e-inflight", type=int, default=2, help="blocking C-ABI calls kept in flight by the end-to-end leg")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--plan-inflight", type=int, default=2, help="c4: plan_batch calls kept in flight (host threads)")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
     ap.add_argument("--connect-steps", type=int, default=8, help="c4: connect-walk steps validated per lock-step round")
     ap.add_argument("--plan-time", type=float, default=0.5,
                     help="c4: OMPL `time` budget in seconds.  The reference arm gives EVERY query 1.0 s on its own host thread "
-                         "(Planner.plan's default); the batched call applies its budget to the whole lock-step batch.  0.5 s is "
-                         "the default because it already solves more of the queries than the reference does with 1.0 s per query "
-                         "(solve_rate is printed in both lines); 1.0 and 0.25 are recorded under profiles/")
+                         "(Planner.plan's default); the batched call applies its budget to the whole lock-step batch")
     return ap.parse_args()
-
-
-def workload_config(args):
-    from tests import workloads as WL
-
-    return WL.get(args.workload, args.batch)
 
 
 class ClockSampler:
@@ -94,108 +98,412 @@ class ClockSampler:
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+        busy = [x for x in sm if x >= 0.5 * max(mx)] if mx else sm  # samples taken while a kernel ran
+        return {"sm_mhz": float(np.median(busy if busy else sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_leg(desc, q, threads, budget_s, chunk):
-    """Time the oracle on successive chunks of q until ~budget_s of wall time is spent."""
+# ------------------------------------------------------------------------------------------------- CPU legs (oracle/)
+def cpu_leg(desc, q, threads, budget_s, accel):
+    """Time the hierarchical CPU restatement on successive chunks of q until ~budget_s of wall time is spent."""
     from oracle import oracle as O
 
     tw = time.perf_counter()
-    O.collide_batch(desc, q[:1000], threads=threads)  # warm-up (page-in, OpenMP pool); also sizes the chunks
+    O.collide_batch(desc, q[:256 * threads], threads=threads, accel=accel)  # warm-up (page-in, OpenMP pool); also sizes the chunks
     tw = max(time.perf_counter() - tw, 1e-6)
-    chunk = int(max(1000, min(chunk, 1000 * budget_s / tw / 4)))  # at most about a quarter of the budget per chunk
+    chunk = int(max(256 * threads, min(q.shape[0], 256 * threads * budget_s / tw / 4)))  # about a quarter of the budget per chunk
     done, t0 = 0, time.perf_counter()
     while done < q.shape[0] and time.perf_counter() - t0 < budget_s:
         m = min(chunk, q.shape[0] - done)
-        O.collide_batch(desc, q[done:done + m], threads=threads)
+        O.collide_batch(desc, q[done:done + m], threads=threads, accel=accel)
         done += m
     dt = time.perf_counter() - t0
     return done / dt, done, dt
 
 
-PLAN_METRIC = "panda_rrtconnect_plans_per_sec"
-PLAN_UNIT = "plans/s"
-
-
-def run_c4_reference(args):
-    """Reference arm of configs[3]: the oracle's RRTConnect restatement (OMPL semantics, one query per host thread,
-    `time` = 1 s per query as Planner.plan passes) on a bounded sample of the same seeded queries."""
+def cpu_baseline_checks(wl, threads, budget_s):
     from oracle import oracle as O
-    from mplib_b200.pymp import OMPLPlanner
-    from tests import workloads as WL
 
-    wl = WL.get("c4", args.batch)
+    desc = wl["desc"]
+    accel = O.Accel(desc)
+    qs = wl["make_q"](0, 1 << 18).astype(np.float64)
+    v, n, dt = cpu_leg(desc, qs, threads, budget_s, accel)
+    return {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "algorithm": "bvh",
+            "sample": f"first {n} states of the seeded workload in {dt:.1f} s; oracle.c hierarchical leg (AABB-tree descent of "
+                      f"meshes / octrees with early exit, edge-walking hull support), OpenMP x{threads}"}
+
+
+def cpu_plans(wl, threads, n_q, seed_base, steps, time_limit=1.0):
+    """The oracle's RRTConnect restatement (OMPL semantics, `time` = 1 s per query as Planner.plan passes), one query per
+    host thread at a time, hierarchical validity checker."""
+    from mplib_b200 import workloads as WL
+    from mplib_b200.pymp import OMPLPlanner
+    from oracle import oracle as O
+
     desc, w = wl["desc"], wl["world"]
-    threads = os.cpu_count() or 1
+    accel = O.Accel(desc)
     pl = OMPLPlanner(w)
     lo, hi = pl.lower_joint_limits, pl.upper_joint_limits
-    n_q = max(threads * 2, 16)
-    checker = lambda q: O.collide_batch(desc, q, threads=threads)[0]
-    per_step, solved_tot = [], 0
-    for s in range(args.warmup + args.steps):
-        starts, goals = WL.c4_queries(n_q, 5 + 104729 * s, checker)
+    checker = lambda q: O.collide_batch(desc, q, threads=threads, accel=accel)[0]
+    per_step = []
+    for s in range(steps):
+        starts, goals = WL.c4_queries(n_q, seed_base + 104729 * s, checker)
         t0 = time.perf_counter()
-        st, paths, gc, sc = O.rrtconnect_batch(desc, lo, hi, starts, goals, range_=0.1, time_limit=1.0, seed=s, threads=threads)
-        dt = time.perf_counter() - t0
-        if s >= args.warmup:
-            per_step.append((int((st == 1).sum()), dt, n_q))
-    n_solved = sum(a for a, _, _ in per_step)
-    t_tot = sum(b for _, b, _ in per_step)
-    val = n_solved / t_tot
-    line = {
-        "impl": "reference", "metric": PLAN_METRIC, "value": val, "unit": PLAN_UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / max(len(per_step), 1), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl["config"],
-        "solve_rate": n_solved / max(sum(c for _, _, c in per_step), 1),
-        "cpu_baseline": {"value": val, "unit": PLAN_UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{n_q} queries/step of the same seeded workload, one query per thread, OpenMP x{threads}, "
-                                   "time limit 1 s per query"},
-        "e2e": {"value": val, "unit": PLAN_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    print(json.dumps(line))
+        st, paths, gc, sc = O.rrtconnect_batch(desc, lo, hi, starts, goals, range_=0.1, time_limit=time_limit, seed=s, threads=threads,
+                                               accel=accel)
+        per_step.append((int((st == 1).sum()), time.perf_counter() - t0, n_q))
+    return per_step
 
 
-def run_c4(args):
-    """configs[3]: plans/s of lock-step RRTConnect.  `value` = solved queries / device time of mpb_rrtconnect_batch
-    (CUDA events inside the call); `e2e` = solved / wall time of OMPLPlanner.plan_batch (start/goal validity checks, goal
-    images, H2D of the queries, D2H of status + paths)."""
+# ------------------------------------------------------------------------------------------------- distributed context
+class Ctx:
+    def __init__(self):
+        import torch
+
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+
+    def barrier(self):
+        import torch
+
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(self, vals, op="max"):
+        import torch
+
+        if self.world == 1:
+            return [float(v) for v in vals]
+        import torch.distributed as dist
+
+        t = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+        return [float(x) for x in t.tolist()]
+
+    def close(self):
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.destroy_process_group()
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def ncu_capture(workload):
+    """Per-kernel DRAM bytes and executed FP32 flops per launch from the committed `ncu --set full` capture of this
+    workload (profiles/r02_ncu_full_<w>_raw.csv; scripts/ncu_export.sh writes it), or {} when there is none."""
+    import csv
+
+    for rnd in ("r02", "r01_final"):
+        path = os.path.join(ROOT, "profiles", f"{rnd}_ncu_full_{workload}_raw.csv")
+        if not os.path.exists(path):
+            continue
+        try:
+            rows = list(csv.reader(open(path)))
+            hdr, units = rows[0], rows[1]
+            col = {c: i for i, c in enumerate(hdr)}
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            out = {}
+            for r in rows[2:]:
+                name = r[col["Kernel Name"]].split("(")[0].split("<")[0]
+                b = sum(float(r[col[c]]) * scale.get(units[col[c]], 1.0) for c in ("dram__bytes_read.sum", "dram__bytes_write.sum") if c in col)
+                fl = None
+                ops = ["smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
+                       "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"]
+                if all(o in col for o in ops):
+                    fl = float(r[col[ops[0]]]) + float(r[col[ops[1]]]) + 2.0 * float(r[col[ops[2]]])
+                e = out.setdefault(name, {"launches": 0, "dram_bytes": 0.0, "fp32_flop": 0.0 if fl is not None else None})
+                e["launches"] += 1
+                e["dram_bytes"] += b
+                if fl is not None and e["fp32_flop"] is not None:
+                    e["fp32_flop"] += fl
+            return {"source": os.path.relpath(path, ROOT), "kernels": out}
+        except Exception:
+            continue
+    return {}
+
+
+# ------------------------------------------------------------------------------------------------- collision workloads
+def parity_sample(wl, dev, n_sample):
+    """GPU verdicts / pair flags of the first n_sample states of the seeded workload against the exhaustive oracle."""
+    from oracle import oracle as O
+
+    desc = dev.desc
+    q = wl["make_q"](0, n_sample)
+    v, ph, st = dev.collide(q, want_pairs=True, stats=True)
+    vh, hits = dev.collide_hits(q)
+    dense_from_hits = np.zeros_like(ph)
+    dense_from_hits[hits[:, 0], hits[:, 1]] = True
+    threads = os.cpu_count() or 1
+    ov, oph = O.collide_batch(desc, q.astype(np.float32).astype(np.float64), threads=threads)
+    mism = np.argwhere(ph != oph)
+    in_band = 0
+    for i, p in mism[:256]:
+        sd = O.pair_signed_distance(desc, q[i].astype(np.float32).astype(np.float64), int(p))
+        in_band += int(np.isfinite(sd) and abs(sd) < BAND)
+    return {"states_checked": int(n_sample), "pairs_checked": int(ph.size), "pair_mismatches": int(len(mism)),
+            "mismatches_in_1e-4_band": int(in_band), "mismatches_out_of_band": int(min(len(mism), 256) - in_band),
+            "verdict_mismatches": int((v != ov).sum()), "hit_list_equals_dense_mask": bool((dense_from_hits == ph).all() and (vh == v).all()),
+            "narrow_capped": int(st["narrow_capped"]), "oracle": "oracle.c exhaustive leaf tests, float64, same float32-rounded inputs"}
+
+
+def latency_record(wl, dev, world_obj):
+    """Host-to-host latency of small mpb_collide_batch(MPB_HOST) calls and the cost of scene edits (item: legacy single-state
+    callers and CollisionObject.set_transformation / update_point_cloud users)."""
+    from mplib_b200 import _lib
+
+    out = {}
+    lib = _lib.load()
+    import ctypes as C
+
+    for n in (1, 32, 1024):
+        q = np.ascontiguousarray(wl["make_q"](3, n).astype(np.float32))
+        vb = np.zeros((n + 31) // 32, dtype=np.uint32)
+        ts = []
+        for it in range(220):
+            t0 = time.perf_counter()
+            rc = lib.mpb_collide_batch(dev._h, q.ctypes.data, n, vb.ctypes.data, None, None, _lib.MPB_HOST, None)
+            ts.append(time.perf_counter() - t0)
+            assert rc == 0
+        out[f"collide_host_n{n}_us"] = float(np.median(ts[20:]) * 1e6)
+    if world_obj is not None:
+        try:
+            w = world_obj
+            c = w._sync()
+            name = next(n for n in w.normal_objects if n not in w.attached_bodies and w.normal_objects[n].geometry.gtype in (1, 2, 3, 4))
+            obj = w.normal_objects[name]
+            ts = []
+            for it in range(12):
+                pose = np.concatenate([obj.T[:3, 3] + np.array([0.0, 0.0, 0.001]), [1.0, 0.0, 0.0, 0.0]])
+                t0 = time.perf_counter()
+                obj.set_transformation(pose)
+                w._sync()
+                ts.append(time.perf_counter() - t0)
+            out["obstacle_move_resync_ms"] = float(np.median(ts[2:]) * 1e3)
+            if "cloud" in w.normal_objects:
+                from mplib_b200.workloads import box_surface_points
+
+                rng = np.random.Generator(np.random.PCG64(99))
+                pts = box_surface_points(rng, 100000, (0.8, 0.8, 0.05), (0.56, 0, -0.025))
+                t0 = time.perf_counter()
+                w.remove_normal_object("cloud")
+                w.add_point_cloud("cloud", pts, 0.01)
+                w._sync()
+                out["replace_100k_point_cloud_resync_ms"] = float((time.perf_counter() - t0) * 1e3)
+        except Exception as e:  # a scene without such an object: report, do not fail the bench
+            out["scene_edit_error"] = repr(e)
+    return out
+
+
+def run_checks(name, args, ctx, batch, steps, warmup, headline):
+    """One collision workload -> record (rank 0) or None."""
     import torch
     import torch.distributed as dist
 
     from mplib_b200 import _lib
-    from mplib_b200.pymp import OMPLPlanner
-    from tests import workloads as WL
+    from mplib_b200 import workloads as WL
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if _lib.load().mpb_device_count() == 0:
-        raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    world, rank, local = ctx.world, ctx.rank, ctx.local
+    t_setup = time.perf_counter()
+    wl = WL.get(name, batch)
+    desc, N, D = wl["desc"], wl["batch"], wl["desc"].state_dim
+    dev = _lib.DeviceScene(desc, local)
+    t_setup = time.perf_counter() - t_setup
+    K, Wm = steps, warmup
+    vwords = (N + 31) // 32
+    hit_cap = int(N * wl.get("hit_cap_per_state", 2))
+    # rotating pool of input batches larger than L2 (126 MB) so no step re-reads cached q
+    n_pool = min(max(2, int(np.ceil(160e6 / (N * D * 4)))), 16)
+    pool_h = [torch.from_numpy(wl["make_q"](rank * 1000 + k, N).astype(np.float32)).pin_memory() for k in range(n_pool)]
+    pool_d = [t.cuda(non_blocking=True) for t in pool_h]
+    verdict_d = torch.zeros((K, vwords), dtype=torch.int32, device="cuda")
+    hits_d = torch.zeros((hit_cap, 2), dtype=torch.int32, device="cuda")
+    nhits_d = torch.zeros(K + Wm + 8, dtype=torch.int32, device="cuda")
+    gathered = torch.zeros((world, K, vwords), dtype=torch.int32, device="cuda") if world > 1 else None
+    stream = torch.cuda.Stream()
+    torch.cuda.synchronize()
+
+    def enqueue(k, slot):
+        return dev.collide_hits_raw(pool_d[k % n_pool], N, verdict_d[slot % K], hits_d, hit_cap, nhits_d[slot:slot + 1], _lib.MPB_DEVICE,
+                                    stream.cuda_stream)
+
+    with torch.cuda.stream(stream):
+        st0 = enqueue(0, K + Wm)  # first device-pointer call on the scene: blocking, calibrates the pass size
+        for k in range(Wm):
+            enqueue(k, K + k)
+        dev.poll(wait=True)
+        ctx.barrier()
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_host0 = time.perf_counter()
+        e0.record(stream)
+        for k in range(K):
+            enqueue(Wm + k, k)
+        t_enq = time.perf_counter() - t_host0
+        if world > 1:  # the only inter-GPU traffic of the path: ONE gather of the packed verdict words of the region
+            dist.all_gather_into_tensor(gathered, verdict_d)
+        e1.record(stream)
+    ctx.barrier()
+    ms = e0.elapsed_time(e1)
+    agg, done, failed = dev.poll(wait=True)
+    assert failed == 0
+    nh = nhits_d[:K].cpu().numpy().astype(np.int64)
+    # per-kernel split: a short leg of the same steps with the per-pass CUDA events switched on (still in the sampled region)
+    dev.set_async_timing(True)
+    Ks = min(K, 3)
+    with torch.cuda.stream(stream):
+        for k in range(Ks):
+            enqueue(Wm + K + k, K + k)
+    split, _, _ = dev.poll(wait=True)
+    dev.set_async_timing(False)
+    clocks = sampler.stop() if rank == 0 else None
+    (ms,) = ctx.reduce([ms], "max")
+    tot = ctx.reduce([agg["narrow_iterations"], agg["kernel_launches"], agg["pairs_after_cull"], agg["pairs_after_spheres"],
+                      agg["narrow_capped"], float(nh.sum())], "sum")
+
+    # end to end through the C-ABI with pinned host buffers: H2D of q, kernels, D2H of verdict words + sparse hit list
+    verdict_h = torch.zeros(vwords, dtype=torch.int32).pin_memory()
+    hits_h = torch.zeros((hit_cap, 2), dtype=torch.int32).pin_memory()
+    nh_h = np.zeros(1, dtype=np.uint32)
+    e2e_hits = []
+
+    def host_step(k):
+        dev.collide_hits_raw(pool_h[k % n_pool], N, verdict_h, hits_h, hit_cap, nh_h, _lib.MPB_HOST, None)
+        e2e_hits.append(int(nh_h[0]))
+
+    for k in range(min(Wm, 2)):
+        host_step(k)
+    e2e_hits.clear()
+    ctx.barrier()
+    t0 = time.perf_counter()
+    for k in range(K):
+        host_step(Wm + k)
+    e2e_s = time.perf_counter() - t0
+    (e2e_s,) = ctx.reduce([e2e_s], "max")
+
+    rec = None
+    if rank == 0:
+        total_checks = float(N) * world * K
+        value = total_checks / (ms * 1e-3)
+        f = wl["flop_model"]
+        iters_per_step = tot[0] / K / world
+        F_step = N * (f["F_fk"] + 12.0 * desc.n_pairs) + iters_per_step * (2.0 * (5.0 * f["V_mean"] + 33.0) + 150.0)
+        step_ms = ms / K
+        peak_probe = _lib.fp32_peak_tflops(local)
+        props = torch.cuda.get_device_properties(local)
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        peak_formula = props.multi_processor_count * 128 * 2 * sm_mhz * 1e6 / 1e12
+        achieved = F_step / (step_ms * 1e-3) / 1e12
+        peaks = load_peaks()
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        B_alg = 4.0 * D + 4.0
+        fk_ms = split["gpu_ms_fk"] / Ks
+        cull_ms, narrow_ms = split["gpu_ms_cull"] / Ks, split["gpu_ms_narrow"] / Ks
+        fk_bytes = split["fk_bytes_per_state"]
+        ncu = ncu_capture(name)
+        kern = ncu.get("kernels", {})
+        dram_step = sum(v["dram_bytes"] for v in kern.values()) if kern else None
+        flop_exec = sum(v["fp32_flop"] for v in kern.values()) if kern and all(v["fp32_flop"] is not None for v in kern.values()) else None
+        fk_tr = kern.get("fk_table_kernel")
+        d2h = int(vwords * 4 + 4 + 8 * (np.mean(e2e_hits) if e2e_hits else 0))
+        rec = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": wl["config"],
+            "e2e": {"value": total_checks / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(N * D * 4), "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1e3 * e2e_s / K, "calls_in_flight": 1,
+                    "pcie_gbs_per_gpu": {"h2d": N * D * 4 / (e2e_s / K) / 1e9, "d2h": d2h / (e2e_s / K) / 1e9}},
+            "calls_in_flight": 1, "host_enqueue_ms_per_step": 1e3 * t_enq / K,
+            "gpu_launches": int(tot[1]),
+            "clocks": clocks,
+            "roofline": {
+                "bound": "fp32", "scope": "all kernels of one step (fk_table, sphere, dense, scan, scatter, narrow [, expand, scan, scatter, narrow])",
+                "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
+                "peak_source": "in-run FFMA probe (mpb_fp32_peak); formula SMs*128*2*f_sampled = %.1f" % peak_formula,
+                "flop_per_check": F_step / N, "traffic": dram_step,
+                "executed_fp32_flop_per_step": flop_exec, "ncu_source": ncu.get("source"),
+                "dominant_kernel": "fk_table+sphere+dense" if cull_ms >= narrow_ms else "narrow(+expand)",
+                "kernel_ms_per_step": {"fk_table+sphere+dense+scan+scatter": cull_ms, "narrow(+expand)": narrow_ms,
+                                       "measured": "leg of %d steps with per-pass CUDA events on the launching stream" % Ks},
+                "hbm": {"achieved": N * B_alg / (step_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": N * B_alg / (step_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_check": B_alg,
+                        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                # the one HBM-bound kernel of the pass, timed alone with CUDA events on the launching stream inside the C-ABI call
+                "fk_table_kernel": {"bound": "hbm", "achieved": N * fk_bytes / (fk_ms * 1e-3) / 1e9 if fk_ms > 0 else None,
+                                    "peak": hbm_peak, "unit": "GB/s",
+                                    "frac": N * fk_bytes / (fk_ms * 1e-3) / 1e9 / hbm_peak if fk_ms > 0 else None,
+                                    "bytes_per_state": fk_bytes, "ms_per_step": fk_ms,
+                                    "traffic": (fk_tr["dram_bytes"] / max(fk_tr["launches"], 1)) if fk_tr else None,
+                                    "share_of_step": fk_ms / max(cull_ms + narrow_ms, 1e-9)},
+            },
+            "stats_per_step": {"pairs_after_spheres": tot[3] / K / world, "pairs_after_cull": tot[2] / K / world, "support_evals": iters_per_step,
+                               "capped": tot[4] / K / world, "hits": tot[5] / K / world},
+            "setup_s": {"world_compile_and_scene_create": t_setup, "first_call_blocking_ms": st0.get("host_ms_total")},
+        }
+        if not args.no_parity:
+            rec["parity"] = parity_sample(wl, dev, 4096 if name == "c3" else 8192)
+        if headline and not args.no_latency and world == 1:
+            rec["latency"] = latency_record(wl, dev, None)
+        if not args.no_cpu_baseline and world == 1:
+            rec["cpu_baseline"] = cpu_baseline_checks(wl, 1, 6.0)
+    del pool_d, verdict_d, hits_d, gathered
+    dev.close()
+    if rank == 0 and headline and not args.no_latency and world == 1:
+        # scene-edit costs on a fresh PlanningWorld of the same workload (the product's host layer drives the C-ABI)
+        try:
+            w = wl["world"]
+            w.device = local
+            rec["latency"].update(latency_record(wl, w._sync()["dev"], w))
+            w._cache["dev"].close()
+        except Exception as e:
+            rec["latency"]["scene_edit_error"] = repr(e)
+    torch.cuda.empty_cache()
+    return rec
+
+
+# ------------------------------------------------------------------------------------------------- planning workload
+def run_c4(args, ctx, batch, steps, warmup):
+    """configs[3]: plans/s of lock-step RRTConnect.  `value` = solved queries / device time of mpb_rrtconnect_batch
+    (CUDA events inside the call); `e2e` = solved / wall time of OMPLPlanner.plan_batch (start/goal validity checks, goal
+    images, H2D of the queries, D2H of status + paths)."""
+    import torch
+
+    from mplib_b200 import _lib
+    from mplib_b200 import workloads as WL
+    from mplib_b200.pymp import OMPLPlanner
+
+    world, rank, local = ctx.world, ctx.rank, ctx.local
     # F plan_batch calls in flight (F host threads, each with its own world / scene handle): a lock-step round is a
     # chain of small kernels, so the rounds of independent query batches interleave on the GPU.
-    F = max(1, args.inflight)
-    wls = [WL.get("c4", args.batch) for _ in range(F)]
+    F = max(1, args.plan_inflight)
+    wls = [WL.get("c4", batch) for _ in range(F)]
     wl = wls[0]
     desc, Q = wl["desc"], wl["batch"]
     pls = []
     for x in wls:
         x["world"].device = local  # the world compiles its scene image on this rank's GPU
         pls.append(OMPLPlanner(x["world"]))
-    n_sets = min(args.warmup + args.steps, 4)
+    n_sets = min(warmup + steps, 4)
     sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, wl["world"].collide_batch) for k in range(n_sets)]
     kw = dict(range=0.1, time=args.plan_time, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048,
               connect_steps=args.connect_steps)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    keep = {}
 
     def run(k0, k1):
         out, errors = {}, []
@@ -204,7 +512,9 @@ def run_c4(args):
             try:
                 torch.cuda.set_device(local)
                 for k in range(k0 + t, k1, F):
-                    out[k] = pls[t].plan_batch(*sets[k % n_sets], seed=k, **kw)[2]
+                    status, paths, st = pls[t].plan_batch(*sets[k % n_sets], seed=k, **kw)
+                    out[k] = st
+                    keep[k] = (status, paths)
             except BaseException as e:
                 errors.append(e)
 
@@ -217,38 +527,34 @@ def run_c4(args):
             raise errors[0]
         return out
 
-    run(0, max(args.warmup, F))
-    barrier()
+    run(0, max(warmup, F))
+    ctx.barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     solved = launches = rounds = states = 0
     t0 = time.perf_counter()
-    res = run(args.warmup, args.warmup + args.steps)
+    res = run(warmup, warmup + steps)
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
     # device time of the region: the calls of one host thread run back to back, the threads run concurrently
-    gpu_ms = max(sum(st["gpu_ms"] for k, st in res.items() if (k - args.warmup) % F == t) for t in range(F))
+    gpu_ms = max(sum(st["gpu_ms"] for k, st in res.items() if (k - warmup) % F == t) for t in range(F))
     for st in res.values():
         solved += st["n_solved"]; launches += st["kernel_launches"]; rounds += st["rounds"]; states += st["states_checked"]
-    barrier()
+    ctx.barrier()
     clocks = sampler.stop() if rank == 0 else None
-    if world > 1:
-        t = torch.tensor([gpu_ms, wall], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        gpu_ms, wall = float(t[0]), float(t[1])
-        c = torch.tensor([solved, launches, states], device="cuda", dtype=torch.float64)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        solved, launches, states = float(c[0]), float(c[1]), float(c[2])
+    gpu_ms, wall = ctx.reduce([gpu_ms, wall], "max")
+    solved, launches, states = ctx.reduce([solved, launches, states], "sum")
+    rec = None
     if rank == 0:
-        K = args.steps
+        K = steps
         f = wl["flop_model"]
         peak_probe = _lib.fp32_peak_tflops(local)
         F_state = f["F_fk"] + 12.0 * desc.n_pairs  # FK + sphere cull per checked state (narrowphase not counted here)
         achieved = states * F_state / (gpu_ms * 1e-3) / 1e12
-        line = {
+        rec = {
             "metric": PLAN_METRIC, "value": solved / (gpu_ms * 1e-3), "unit": PLAN_UNIT, "n_gpus": world, "steps": K,
-            "warmup": args.warmup, "ms_per_step": gpu_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": warmup, "ms_per_step": gpu_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": wl["config"],
             "solve_rate": solved / (float(Q) * world * K), "plan_time_budget_s": args.plan_time, "calls_in_flight": F,
             "e2e": {"value": solved / wall, "unit": PLAN_UNIT, "h2d_bytes_per_step": int(Q * 2 * desc.state_dim * 4 + Q * 4),
@@ -258,303 +564,141 @@ def run_c4(args):
                          "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
                          "traffic": None, "states_checked_per_step": states / K / world, "rounds_per_step": rounds / K},
         }
-        print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+        if not args.no_parity:  # every path returned by the first timed step re-validated by the oracle's motion validator
+            from oracle import oracle as O
+
+            pl = pls[0]
+            status, paths = keep[warmup]
+            a = [p[:-1] for p in paths if len(p) > 1]
+            b = [p[1:] for p in paths if len(p) > 1]
+            n_paths = len(a)
+            bad = 0
+            if n_paths:
+                cnt = np.array([len(x) for x in a])
+                valid, _ = O.check_motion_batch(desc, pl.lower_joint_limits, pl.upper_joint_limits, np.concatenate(a), np.concatenate(b),
+                                                threads=os.cpu_count() or 1)
+                owner = np.repeat(np.arange(n_paths), cnt)
+                bad = int(len(set(owner[~valid].tolist())))
+            starts, goals = sets[warmup % n_sets]
+            ends_ok = sum(1 for i, p in enumerate(paths) if len(p) > 1 and np.allclose(p[0], starts[i], atol=1e-6) and np.allclose(p[-1], goals[i], atol=1e-6))
+            rec["parity"] = {"paths_returned": n_paths, "paths_valid": n_paths - bad, "paths_start_goal_ok": int(ends_ok),
+                             "oracle": "DiscreteMotionValidator restatement (oracle.c, float64, exhaustive leaf tests) over every edge of every path of one step"}
+        if not args.no_cpu_baseline and world == 1:
+            per = cpu_plans(wl, 1, 8, 5, 1)
+            ns, dt = sum(a for a, _, _ in per), sum(b for _, b, _ in per)
+            rec["cpu_baseline"] = {"value": ns / dt, "unit": PLAN_UNIT, "cores": 1, "kind": "port", "algorithm": "bvh",
+                                   "solve_rate": ns / sum(c for _, _, c in per),
+                                   "sample": "8 queries of the same seeded workload one after the other on one thread, time limit 1 s per query"}
+    for x in wls:
+        c = x["world"]._cache
+        if c is not None:
+            c["dev"].close()
+    torch.cuda.empty_cache()
+    return rec
 
 
-def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
-    if args.workload == "c4":
-        return run_c4_reference(args)
-    wl = workload_config(args)
+# ------------------------------------------------------------------------------------------------- reference arm
+def reference_checks(name, args, batch, steps, warmup, budget_s):
+    from mplib_b200 import workloads as WL
+    from oracle import oracle as O
+
+    wl = WL.get(name, batch)
     desc = wl["desc"]
     threads = os.cpu_count() or 1
+    accel = O.Accel(desc)
     q = wl["make_q"](0, min(wl["batch"], 1 << 18)).astype(np.float64)
     per_step = []
-    for s in range(args.warmup + args.steps):
-        v, n, dt = cpu_leg(desc, q, threads, budget_s=3.0, chunk=q.shape[0])
-        if s >= args.warmup:
+    for s in range(warmup + steps):
+        v, n, dt = cpu_leg(desc, q, threads, budget_s, accel)
+        if s >= warmup:
             per_step.append((n, dt))
-    n_tot = sum(n for n, _ in per_step)
-    t_tot = sum(dt for _, dt in per_step)
+    n_tot, t_tot = sum(n for n, _ in per_step), sum(dt for _, dt in per_step)
     val = n_tot / t_tot
-    line = {
-        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / max(len(per_step), 1), "higher_is_better": True, "scaling": "weak",
+    return {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": 1e3 * t_tot / max(len(per_step), 1), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl["config"],
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{per_step[0][0] if per_step else 0} states/step of the same seeded workload, OpenMP x{threads}"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "algorithm": "bvh",
+                         "sample": f"{per_step[0][0] if per_step else 0} states/step of the same seeded workload; oracle.c hierarchical leg "
+                                   f"(AABB-tree descent with early exit, edge-walking hull support), OpenMP x{threads}"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+
+
+def reference_c4(args, batch, steps, warmup):
+    from mplib_b200 import workloads as WL
+
+    wl = WL.get("c4", batch)
+    threads = os.cpu_count() or 1
+    n_q = max(threads * 2, 16)
+    per = cpu_plans(wl, threads, n_q, 5, warmup + steps)[warmup:]
+    ns, dt = sum(a for a, _, _ in per), sum(b for _, b, _ in per)
+    val = ns / dt
+    return {
+        "impl": "reference", "metric": PLAN_METRIC, "value": val, "unit": PLAN_UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": 1e3 * dt / max(len(per), 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl["config"],
+        "solve_rate": ns / max(sum(c for _, _, c in per), 1),
+        "cpu_baseline": {"value": val, "unit": PLAN_UNIT, "cores": threads, "kind": "port", "algorithm": "bvh",
+                         "sample": f"{n_q} queries/step of the same seeded workload, one query per thread, OpenMP x{threads}, "
+                                   "time limit 1 s per query"},
+        "e2e": {"value": val, "unit": PLAN_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def also_list(args):
+    if args.also.strip().lower() in ("", "none"):
+        return []
+    return [x for x in (y.strip() for y in args.also.split(",")) if x and x != args.workload]
+
+
+def run_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    head = args.workload
+    if head == "c4":
+        line = reference_c4(args, args.batch, args.steps, args.warmup)
+    else:
+        line = reference_checks(head, args, args.batch, args.steps, args.warmup, 1.0)
+    also = {}
+    for name in also_list(args):
+        if name == "c4":
+            also[name] = reference_c4(args, 0, 2, 1)
+        else:
+            also[name] = reference_checks(name, args, 0, 3, 1, 1.0)
+    if also:
+        line["also"] = also
     print(json.dumps(line))
-
-
-def ncu_traffic(workload, kernel):
-    """DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of `kernel` from the committed
-    `ncu --set full` capture of this workload (profiles/r01_final_ncu_full_<w>_raw.csv), or None."""
-    import csv
-    path = os.path.join(ROOT, "profiles", "r01_final_ncu_full_%s_raw.csv" % workload)
-    try:
-        rows = list(csv.reader(open(path)))
-        hdr, units = rows[0], rows[1]
-        ik, ir, iw, ig = (hdr.index(c) for c in ("Kernel Name", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__grid_size"))
-        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-        for r in rows[2:]:
-            if kernel in r[ik]:
-                b = float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
-                states = int(float(r[ig])) * 128
-                return {"dram_bytes_per_launch": b, "states_per_launch": states, "dram_bytes_per_state": b / states,
-                        "source": os.path.relpath(path, ROOT)}
-    except Exception:
-        pass
-    return None
 
 
 def main():
     args = parse()
     if args.impl == "reference":
         return run_reference(args)
-    if args.workload == "c4":
-        return run_c4(args)
-
-    import torch
-    import torch.distributed as dist
 
     from mplib_b200 import _lib
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
     if _lib.load().mpb_device_count() == 0:
         raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    wl = workload_config(args)
-    desc, N, D = wl["desc"], wl["batch"], wl["desc"].state_dim
-    dev = _lib.DeviceScene(desc, local)
-    W = dev.pair_words
-    stream = torch.cuda.current_stream()
-    # rotating pool of input batches larger than L2 (126 MB) so no step re-reads cached q
-    n_pool = max(2, int(np.ceil(160e6 / (N * D * 4))))
-    n_pool = min(n_pool, 16)
-    pool_h = [torch.from_numpy(wl["make_q"](rank * 1000 + k, N).astype(np.float32)).pin_memory() for k in range(n_pool)]
-    pool_d = [t.cuda(non_blocking=True) for t in pool_h]
-    vwords = (N + 31) // 32
-    # F calls in flight (F host threads, each with its own scene handle, stream and result set), the way a caller
-    # pipelines a blocking API: while one call synchronises to read its counters and the host enqueues its next pass,
-    # the other call's kernels keep the GPU busy.  The verdict gather of step k (NCCL, side stream, issued in step
-    # order by the main thread) overlaps the kernels of the following steps.  --inflight 1 is the strictly serial figure.
-    F = max(1, args.inflight)
-    devs_d = [dev] + [_lib.DeviceScene(desc, local) for _ in range(F - 1)]
-    streams = [torch.cuda.Stream() for _ in range(F)]
-    # verdict gather (NCCL): one all_gather per G steps of a call slot (G x 131 KB for C2), two buffers per slot, so a
-    # worker only waits for the gather issued two of its groups ago
-    G = 4 if world > 1 else 1
-    verdict_d = [[torch.zeros((G, vwords), dtype=torch.int32, device="cuda") for _ in range(2)] for _ in range(F)]
-    pairs_d = [[torch.zeros((N, max(W, 1)), dtype=torch.int32, device="cuda") for _ in range(2)] for _ in range(F)]
-    gathered = [[torch.zeros((world, G, vwords), dtype=torch.int32, device="cuda") for _ in range(2)] for _ in range(F)] if world > 1 else None
-    comm = torch.cuda.Stream() if world > 1 else None
-    ev_done = [[torch.cuda.Event() for _ in range(2)] for _ in range(F)]
-    ev_gathered = [[torch.cuda.Event() for _ in range(2)] for _ in range(F)]
-    verdict_h = torch.zeros(vwords, dtype=torch.int32).pin_memory()
-    pairs_h = torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()
-    torch.cuda.synchronize()
-
-    def run_device(k0, k1, start_event=None, F=F):
-        """Steps k0..k1-1 with F calls in flight; returns the per-step stats in step order."""
-        n_of = [len(range(k0 + t, k1, F)) for t in range(F)]      # steps of worker t
-        groups = [(n_of[t] + G - 1) // G for t in range(F)]         # gather groups of worker t
-        done = {(t, g): threading.Event() for t in range(F) for g in range(groups[t])}
-        issued = {(t, g): threading.Event() for t in range(F) for g in range(groups[t])}
-        stats = {}
-        errors = []
-
-        def worker(t):
-            try:
-                torch.cuda.set_device(local)
-                if start_event is not None:
-                    streams[t].wait_event(start_event)
-                for j, k in enumerate(range(k0 + t, k1, F)):
-                    g, r = j // G, j % G
-                    b = g & 1
-                    if world > 1 and r == 0 and g >= 2:
-                        issued[(t, g - 2)].wait()
-                        streams[t].wait_event(ev_gathered[t][b])  # the gather that read this buffer two groups ago
-                    stats[k] = devs_d[t].collide_raw(pool_d[k % n_pool], N, verdict_d[t][b][r], pairs_d[t][b], _lib.MPB_DEVICE,
-                                                     streams[t].cuda_stream)
-                    if r == G - 1 or j == n_of[t] - 1:
-                        ev_done[t][b].record(streams[t])
-                        done[(t, g)].set()
-            except BaseException as e:  # surface worker failures instead of hanging the main thread
-                errors.append(e)
-                for ev in list(done.values()) + list(issued.values()):
-                    ev.set()
-
-        th = [threading.Thread(target=worker, args=(t,)) for t in range(F)]
-        for x in th:
-            x.start()
-        if world > 1:
-            for g in range(max(groups)):
-                for t in range(F):
-                    if g >= groups[t] or errors:
-                        continue
-                    done[(t, g)].wait()
-                    if errors:
-                        break
-                    b = g & 1
-                    with torch.cuda.stream(comm):
-                        comm.wait_event(ev_done[t][b])
-                        dist.all_gather_into_tensor(gathered[t][b], verdict_d[t][b])  # the only inter-GPU traffic: verdict words
-                        ev_gathered[t][b].record(comm)
-                    issued[(t, g)].set()
-        for x in th:
-            x.join()
-        if errors:
-            raise errors[0]
-        for t in range(F):
-            stream.wait_stream(streams[t])
-        if world > 1:
-            stream.wait_stream(comm)  # the last gathers are inside the timed region
-        return [stats[k] for k in range(k0, k1)]
-
-    def step_host(k):
-        return dev.collide_raw(pool_h[k % n_pool], N, verdict_h, pairs_h, _lib.MPB_HOST, stream.cuda_stream)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    run_device(0, args.warmup)
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    agg = {"gpu_ms_cull": 0.0, "gpu_ms_narrow": 0.0, "gpu_ms_fk": 0.0, "pairs_after_cull": 0, "pairs_after_spheres": 0, "narrow_iterations": 0, "narrow_capped": 0,
-           "kernel_launches": 0}
-    e0.record(stream)
-    per_step = run_device(args.warmup, args.warmup + args.steps, start_event=e0)
-    e1.record(stream)  # the worker streams and the gather stream have been joined into this one
-    barrier()
-    ms = e0.elapsed_time(e1)
-    # per-kernel durations: with several calls in flight the kernels of different calls share the SMs and each call's
-    # event intervals stretch, so the kernel split (and the fk_table_kernel roofline) comes from a short serial leg
-    # of the same steps, one call in flight, still inside the clock-sampled region
-    if F > 1:
-        per_step_serial = run_device(args.warmup + args.steps, args.warmup + args.steps + min(args.steps, 5), F=1)
+    ctx = Ctx()
+    head = args.workload
+    if head == "c4":
+        line = run_c4(args, ctx, args.batch, args.steps, args.warmup)
     else:
-        per_step_serial = per_step
-    clocks = sampler.stop() if rank == 0 else None
-    Ks = len(per_step_serial)
-    for st in per_step_serial:
-        for key in ("gpu_ms_cull", "gpu_ms_narrow", "gpu_ms_fk"):
-            agg[key] += st[key] * args.steps / Ks  # scaled to K steps so the per-step divisions below stay uniform
-    for st in per_step:
-        for key in ("pairs_after_cull", "pairs_after_spheres", "narrow_iterations", "narrow_capped", "kernel_launches"):
-            agg[key] += st[key]
-        fk_bytes = st["fk_bytes_per_state"]
-    if world > 1:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-
-    # end-to-end through the C-ABI with pinned host buffers.  Two calls are kept in flight (two host threads, each
-    # with its own scene handle, streams and pinned result buffers), the way a caller pipelines a blocking API: the
-    # H2D copy of one call runs under the kernels of the other.  --e2e-inflight 1 gives the strictly serial figure.
-    n_fl = max(1, args.e2e_inflight)
-    devs = (devs_d + [_lib.DeviceScene(desc, local) for _ in range(max(0, n_fl - len(devs_d)))])[:n_fl]
-    outs = [(verdict_h, pairs_h)] + [(torch.zeros(vwords, dtype=torch.int32).pin_memory(),
-                                      torch.zeros((N, max(W, 1)), dtype=torch.int32).pin_memory()) for _ in range(n_fl - 1)]
-
-    def host_worker(t, k0, k1):
-        for k in range(k0 + t, k1, n_fl):
-            devs[t].collide_raw(pool_h[k % n_pool], N, outs[t][0], outs[t][1], _lib.MPB_HOST, None)
-
-    def run_host(k0, k1):
-        th = [threading.Thread(target=host_worker, args=(t, k0, k1)) for t in range(n_fl)]
-        for x in th:
-            x.start()
-        for x in th:
-            x.join()
-
-    run_host(0, max(min(args.warmup, 3), n_fl))
-    barrier()
-    t0 = time.perf_counter()
-    run_host(args.warmup, args.warmup + args.steps)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-
-    if rank == 0:
-        K = args.steps
-        total_checks = float(N) * world * K
-        value = total_checks / (ms * 1e-3)
-        # algorithmic flop model of SURVEY 8(d)
-        f = wl["flop_model"]
-        iters_per_step = agg["narrow_iterations"] / K
-        F_step = N * (f["F_fk"] + 12.0 * desc.n_pairs) + iters_per_step * (2.0 * (5.0 * f["V_mean"] + 33.0) + 150.0)
-        kernels_ms = ms / K  # the whole device-timed step (with calls in flight the per-call kernel intervals overlap)
-        peak_probe = _lib.fp32_peak_tflops(local)
-        props = torch.cuda.get_device_properties(local)
-        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-        peak_formula = props.multi_processor_count * 128 * 2 * sm_mhz * 1e6 / 1e12
-        achieved = F_step / (kernels_ms * 1e-3) / 1e12
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        B_alg = 4.0 * D + 4.0
-        hbm_achieved = N * B_alg / (kernels_ms * 1e-3) / 1e9
-        dominant = "fk_table+sphere+dense" if agg["gpu_ms_cull"] >= agg["gpu_ms_narrow"] else "narrow(+expand)"
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": wl["config"],
-            "e2e": {"value": total_checks / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(N * D * 4),
-                    "d2h_bytes_per_step": int(vwords * 4 + N * max(W, 1) * 4), "calls_in_flight": n_fl},
-            "calls_in_flight": F,
-            "gpu_launches": int(agg["kernel_launches"]),
-            "clocks": clocks,
-            "roofline": {
-                "bound": "fp32", "scope": "all kernels of one step (fk_table, sphere, dense, scan, scatter, narrow [, expand, scan, scatter, narrow])",
-                "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
-                "peak_source": "in-run FFMA probe (mpb_fp32_peak); formula SMs*128*2*f_sampled = %.1f" % peak_formula,
-                "flop_per_check": F_step / N, "traffic": None, "dominant_kernel": dominant,
-                "kernel_ms_per_step": {"fk_table+sphere+dense+scan+scatter": agg["gpu_ms_cull"] / K, "narrow(+expand)": agg["gpu_ms_narrow"] / K,
-                                       "measured": "serial leg of %d steps, one call in flight" % Ks},
-                "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
-                        "bytes_per_check": B_alg, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
-                # the one HBM-bound kernel of the pass, timed alone with CUDA events on its own stream inside the C-ABI call
-                "fk_table_kernel": {"bound": "hbm", "achieved": N * fk_bytes / (agg["gpu_ms_fk"] / K * 1e-3) / 1e9 if agg["gpu_ms_fk"] > 0 else None,
-                                    "peak": hbm_peak, "unit": "GB/s",
-                                    "frac": N * fk_bytes / (agg["gpu_ms_fk"] / K * 1e-3) / 1e9 / hbm_peak if agg["gpu_ms_fk"] > 0 else None,
-                                    "bytes_per_state": fk_bytes, "ms_per_step": agg["gpu_ms_fk"] / K,
-                                    "traffic": ncu_traffic(args.workload, "fk_table_kernel"),
-                                    "share_of_step": agg["gpu_ms_fk"] / max(agg["gpu_ms_cull"] + agg["gpu_ms_narrow"], 1e-9)},
-            },
-            "stats_per_step": {"pairs_after_spheres": agg["pairs_after_spheres"] / K, "pairs_after_cull": agg["pairs_after_cull"] / K, "support_evals": iters_per_step,
-                               "capped": agg["narrow_capped"] / K},
-        }
-        if not args.no_cpu_baseline and world == 1:
-            qs = wl["make_q"](0, min(N, 1 << 20)).astype(np.float64)
-            v, n, dt = cpu_leg(desc, qs, 1, budget_s=12.0, chunk=50000)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-                                    "sample": f"first {n} states of the seeded workload, oracle.c single thread, {dt:.1f}s"}
+        line = run_checks(head, args, ctx, args.batch, args.steps, args.warmup, True)
+    also = {}
+    for name in also_list(args):
+        if name == "c4":
+            also[name] = run_c4(args, ctx, 0, 4, 2)
+        else:
+            also[name] = run_checks(name, args, ctx, 0, min(args.steps, 20), min(args.warmup, 3), False)
+    if ctx.rank == 0:
+        if also:
+            line["also"] = also
         print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    ctx.close()
 
 
 if __name__ == "__main__":

@@ -124,6 +124,7 @@ typedef struct mpb_stats {
   float host_ms_total;       /* host wall time of the call, including the final synchronisation */
   float gpu_ms_fk;           /* fk_table_kernel alone (device-resident input; 0 when the input is streamed from the host) */
   int32_t fk_bytes_per_state; /* algorithmic bytes fk_table_kernel moves per state: 4*state_dim read + sphere and OBB table rows written */
+  int32_t async_pending;     /* 1: the call returned after enqueueing; its counters arrive through mpb_scene_poll */
 } mpb_stats;
 
 /* Thread-local message of the last failing call on this thread. */
@@ -143,6 +144,13 @@ int mpb_scene_set_q_base(mpb_scene *scene, const double *q_base, int32_t nq_full
 /* Replace the admitted pair list (after an ACM edit, src/collision_matrix.cpp:34-138). */
 int mpb_scene_set_pairs(mpb_scene *scene, int32_t n_pairs, const int32_t *pair_a, const int32_t *pair_b);
 
+/* Update objects of the compiled scene in place: the pose of a world-fixed object (CollisionObject::setTransformation,
+ * python/pybind_fcl.hpp:254-259), the pose of an attached body on its link (src/attached_body.h:48-54) and / or the
+ * parameters of a primitive.  Geometry type and hull / mesh / octree stay what they were; nothing is re-compiled.
+ *   obj_idx [n]   obj_local [n][12] nullable (as mpb_scene_desc::obj_local)   obj_param [n][4] nullable */
+int mpb_scene_update_objects(mpb_scene *scene, int32_t n, const int32_t *obj_idx, const double *obj_local,
+                             const double *obj_param);
+
 /* Batched PinocchioModelTpl::computeForwardKinematics + getLinkPose for every link
  * (src/pinocchio_model.cpp:271-312).  q: [n][state_dim] float32; poses: [n][n_links][7] float32. */
 int mpb_fk_batch(mpb_scene *scene, const float *q, int64_t n, float *poses, int space, void *stream);
@@ -152,10 +160,36 @@ int mpb_fk_batch(mpb_scene *scene, const float *q, int64_t n, float *poses, int 
  *   q            [n][state_dim] float32
  *   verdict_bits [ceil(n/32)] uint32, bit (i&31) of word i>>5 set iff state i collides
  *   pair_bits    nullable, [n][ceil(n_pairs/32)] uint32, bit p set iff admitted pair p collides
- * `stream` is a cudaStream_t (NULL = the scene's own stream).  With MPB_HOST the call returns
- * after the results are in the host buffers; with MPB_DEVICE it returns after enqueueing. */
+ * `stream` is a cudaStream_t (NULL = the scene's own stream).
+ * MPB_HOST: the call returns after the results are in the host buffers.  Batches of at most 4096 states on the
+ *   scene's own stream are replayed as one CUDA graph (copies + kernels) through pinned staging buffers, so a legacy
+ *   single-state query costs one graph launch.
+ * MPB_DEVICE: the call returns after ENQUEUEING on `stream` (stats->async_pending = 1); nothing synchronises.  The
+ *   passes are sized from the last blocking call on the scene, so the first device-pointer call after
+ *   mpb_scene_create / mpb_scene_set_pairs / mpb_scene_update_objects runs the blocking protocol once (it returns
+ *   with the stream idle and full stats).  If a later call still overflows the bounded work queues its outputs are
+ *   incomplete; that is never silent: mpb_scene_poll (and through it the caller) learns it as MPB_ERR_CAPACITY,
+ *   and the next call re-calibrates. */
 int mpb_collide_batch(mpb_scene *scene, const float *q, int64_t n, uint32_t *verdict_bits,
                       uint32_t *pair_bits, mpb_stats *stats, int space, void *stream);
+
+/* mpb_collide_batch with the per-pair result as a SPARSE list instead of the dense mask: entry k of `hits` is
+ * (configuration index, admitted pair index) of a colliding pair -- the content of the WorldCollisionResult list of
+ * PlanningWorldTpl::collideFull (src/planning_world.cpp:483-490), which also holds colliding pairs only.  Order is
+ * unspecified.  hits [hit_cap][2] uint32, n_hits [1] uint32 (same space as the other buffers); *n_hits may exceed
+ * hit_cap, in which case the list is truncated to hit_cap entries.  The dense mask stays in device memory. */
+int mpb_collide_batch_hits(mpb_scene *scene, const float *q, int64_t n, uint32_t *verdict_bits, uint32_t *hits,
+                           int64_t hit_cap, uint32_t *n_hits, mpb_stats *stats, int space, void *stream);
+
+/* Harvest the device-pointer calls that have finished (wait != 0: wait for all of them first).
+ *   sum              nullable; counters and times summed over the calls harvested since the previous poll
+ *                    (gpu_ms* only when mpb_scene_set_async_timing is on)
+ *   calls_completed  nullable; how many calls that is        calls_failed  nullable; how many of them overflowed
+ * Returns MPB_ERR_CAPACITY when calls_failed > 0 (the outputs of those calls are incomplete). */
+int mpb_scene_poll(mpb_scene *scene, int wait, mpb_stats *sum, int64_t *calls_completed, int64_t *calls_failed);
+
+/* Record per-pass CUDA timing events for device-pointer calls too (off by default: five events per pass). */
+int mpb_scene_set_async_timing(mpb_scene *scene, int on);
 
 /* Batched ValidityCheckerTpl::clearance = setQposAll + distanceFull (src/ompl_planner.h:69-72,
  * src/planning_world.cpp:492-720) with the default DistanceRequest (python/pybind_fcl.hpp:311-315):

@@ -56,7 +56,8 @@ SYMBOLS = [
     "mpb_last_error", "mpb_device_count", "mpb_scene_create", "mpb_scene_destroy", "mpb_scene_set_q_base",
     "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
     "mpb_check_motion_batch", "mpb_rrtconnect_batch", "mpb_distance_batch", "mpb_ik_clik_batch",
-    "mpb_link_jacobian_batch",
+    "mpb_link_jacobian_batch", "mpb_collide_batch_hits", "mpb_scene_poll", "mpb_scene_set_async_timing",
+    "mpb_scene_update_objects",
 ]
 
 _lib = None
@@ -86,6 +87,11 @@ def load():
     lib.mpb_fk_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p]
     lib.mpb_collide_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.POINTER(MpbStats), C.c_int, C.c_void_p]
+    lib.mpb_collide_batch_hits.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                           C.POINTER(MpbStats), C.c_int, C.c_void_p]
+    lib.mpb_scene_poll.argtypes = [C.c_void_p, C.c_int, C.POINTER(MpbStats), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.mpb_scene_set_async_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.mpb_scene_update_objects.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpb_scene_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int32)] * 5
     lib.mpb_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_float)]
     lib.mpb_distance_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(MpbStats), C.c_int,
@@ -156,6 +162,47 @@ class DeviceScene:
         self.n_pairs = int(a.shape[0])
         self.pair_words = (self.n_pairs + 31) // 32
 
+    def update_objects(self, idx, obj_local=None, obj_param=None):
+        """In-place pose (row-major 3x4 per object) / primitive-parameter update of compiled objects."""
+        idx = np.ascontiguousarray(np.asarray(idx, dtype=np.int32).reshape(-1))
+        loc = None if obj_local is None else np.ascontiguousarray(np.asarray(obj_local, dtype=np.float64).reshape(-1, 12))
+        par = None if obj_param is None else np.ascontiguousarray(np.asarray(obj_param, dtype=np.float64).reshape(-1, 4))
+        _check(load().mpb_scene_update_objects(self._h, idx.shape[0], _ptr(idx), _ptr(loc), _ptr(par)))
+        self.desc = self.desc.with_objects(idx, loc, par)
+
+    def poll(self, wait=True):
+        """Harvest finished device-pointer calls -> (summed stats dict, calls completed, calls failed).  Raises MpbError
+        when a harvested call overflowed the work queues."""
+        st = MpbStats()
+        done, failed = C.c_int64(0), C.c_int64(0)
+        _check(load().mpb_scene_poll(self._h, 1 if wait else 0, C.byref(st), C.byref(done), C.byref(failed)))
+        return st.as_dict(), int(done.value), int(failed.value)
+
+    def set_async_timing(self, on=True):
+        _check(load().mpb_scene_set_async_timing(self._h, 1 if on else 0))
+
+    def collide_hits(self, q, hit_cap=None, stats=False):
+        """q [n, D] host -> (verdict bool[n], hits int64[k, 2] = (configuration, pair) sorted[, stats]): the sparse form
+        of ``collide(want_pairs=True)``."""
+        q = np.ascontiguousarray(np.asarray(q, dtype=np.float32))
+        if q.ndim != 2 or q.shape[1] != self.state_dim:
+            raise RuntimeError(f"State dimension is not correct: expected [n,{self.state_dim}], got {q.shape}")
+        n = q.shape[0]
+        cap = int(hit_cap) if hit_cap is not None else max(1024, 4 * n)
+        st = MpbStats()
+        while True:
+            vb = np.zeros((n + 31) // 32, dtype=np.uint32)
+            hits = np.zeros((max(cap, 1), 2), dtype=np.uint32)
+            nh = np.zeros(1, dtype=np.uint32)
+            _check(load().mpb_collide_batch_hits(self._h, _ptr(q), n, _ptr(vb), _ptr(hits), cap, _ptr(nh), C.byref(st), MPB_HOST, None))
+            if int(nh[0]) <= cap or hit_cap is not None:
+                break
+            cap = int(nh[0])  # the list was truncated: repeat with the reported size
+        verdict = np.unpackbits(vb.view(np.uint8), bitorder="little")[:n].astype(bool)
+        h = hits[: min(int(nh[0]), cap)].astype(np.int64)
+        h = h[np.lexsort((h[:, 1], h[:, 0]))]
+        return (verdict, h, st.as_dict()) if stats else (verdict, h)
+
     # -- host-buffer entry points -------------------------------------------------------------
     def collide(self, q, want_pairs=True, stats=False):
         """q: [n, state_dim] (any float dtype, host).  -> (verdict bool[n], pair_hit bool[n,P] | None[, stats])"""
@@ -178,6 +225,13 @@ class DeviceScene:
         st = MpbStats()
         _check(load().mpb_collide_batch(self._h, _ptr(q_ptr), int(n), _ptr(verdict_ptr), _ptr(pair_ptr), C.byref(st),
                                         space, _ptr(stream)))
+        return st.as_dict()
+
+    def collide_hits_raw(self, q_ptr, n, verdict_ptr, hits_ptr, hit_cap, n_hits_ptr, space=MPB_HOST, stream=None):
+        """Pointer-level mpb_collide_batch_hits (pinned host or device memory); returns the stats dict."""
+        st = MpbStats()
+        _check(load().mpb_collide_batch_hits(self._h, _ptr(q_ptr), int(n), _ptr(verdict_ptr), _ptr(hits_ptr), int(hit_cap),
+                                             _ptr(n_hits_ptr), C.byref(st), space, _ptr(stream)))
         return st.as_dict()
 
     def fk(self, q):

@@ -11,6 +11,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -29,6 +30,40 @@ static int fail(int code, const std::string &msg) {
       return fail(MPB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                  \
   } while (0)
 
+#define MPB_ASYNC_SLOTS 16
+struct AsyncSlot {
+  unsigned *h = nullptr;          // pinned: totals[8] | counters[4] (64-bit)
+  cudaEvent_t done = nullptr;
+  std::vector<cudaEvent_t> ev;    // timing events, 5 per pass (only with mpb_scene_set_async_timing)
+  size_t n_ev = 0;
+  bool pending = false;
+  long long n = 0, launches = 0;
+  float host_ms = 0.f;
+};
+struct SmallGraph {
+  long long n = 0;
+  int mode = 0;                   // 0 verdicts, 1 + dense pair mask, 2 + hit list
+  unsigned hit_cap = 0;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  long long launches = 0;
+  // what the captured nodes point at; a graph is dropped when any of these moved
+  const void *d_q = nullptr, *d_v = nullptr, *d_p = nullptr, *d_h = nullptr, *h_base = nullptr;
+  long long chunk_at = 0;
+  unsigned long long img_version = 0;
+};
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per-function state shared by every scene of the process: only ever
+// raise it (a second scene with a smaller hull pool must not lower the limit under a scene that needs more).
+static cudaError_t raise_dyn_smem(const void *func, int device, int slot, size_t bytes) {
+  static int limit[2][64] = {{0}};
+  if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+  if ((int)bytes <= limit[slot][device]) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e == cudaSuccess) limit[slot][device] = (int)bytes;
+  return e;
+}
+
 struct mpb_scene {
   int device = 0;
   int num_sms = 0;
@@ -41,7 +76,10 @@ struct mpb_scene {
   // double-precision copy of the kinematic model for the IK entry point
   std::vector<double> h_jP64, h_jax64, h_qbase64, h_linkL64;
   std::vector<int> h_jtype, h_jparent, h_linkJoint;
-  std::vector<int> obj_key;
+  std::vector<int> obj_key, h_dynlist, h_objLink;
+  std::vector<float4> h_cobb;
+  std::vector<int32_t> h_pair_a, h_pair_b;  // the admitted pair list as given (build_pairs re-orders BVH pairs)
+  size_t work_P = 0;                        // pair count the work queues were sized for
   int nq_full = 0;
   // device image
   DevJoint *d_joints = nullptr;
@@ -98,7 +136,29 @@ struct mpb_scene {
   // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
   // buffers cost more than a thousand planning rounds)
   std::vector<std::pair<void *, size_t>> pool;
+  // blocking calls read their queue counters through this pinned block
+  unsigned *h_status = nullptr;  // [32]
+  // sparse hit list of host-buffer calls: [0] = counter, [1..] = (configuration, pair) entries
+  uint2 *d_hits = nullptr;
+  size_t d_hits_cap = 0;
+  // device-pointer calls in flight (see collide_enqueue)
+  AsyncSlot slots[MPB_ASYNC_SLOTS];
+  unsigned *h_slots = nullptr;  // pinned, 32 words per slot
+  int slot_head = 0;
+  mpb_stats async_acc{};
+  long long async_completed = 0, async_failed = 0;
+  bool calibrated = false, async_timing = false;
+  long long good_chunk = 0;
+  // small host batches replayed as CUDA graphs (see collide_small)
+  std::vector<SmallGraph> small_graphs;
+  unsigned char *h_small = nullptr;
+  size_t h_small_cap = 0;
+  unsigned long long img_version = 0;  // bumped whenever a by-value kernel parameter of the image changes
+  float *d_qconst = nullptr;           // [n_joints] value of the joints the batch state does not write (q_base)
 };
+
+static void drop_small_graphs(mpb_scene *s);
+static int harvest(mpb_scene *s, bool wait);
 
 extern "C" const char *mpb_last_error(void) { return g_err.c_str(); }
 
@@ -308,7 +368,23 @@ static std::vector<CellBox> merge_cells(const int32_t *cells, int n) {
 // planar quad on the cube (directions need not be unit length), so that maximum sits at one of its four corners.
 // Checking the condition against all j gives a superset of the exact set; the quad is widened by `margin` so that
 // the device's float arithmetic may place a boundary direction in either neighbouring cell.
+static void build_cell_table_uncached(const double *V, int nv, std::vector<unsigned char> &out);
+// Process-wide cache keyed by the vertex bytes: re-compiling a scene after an object was added or removed (or compiling a
+// second scene for the same robot) does not redo the O(cells x nv^2) table of geometry it has seen.
 static void build_cell_table(const double *V, int nv, std::vector<unsigned char> &out) {
+  static std::mutex mu;
+  static std::map<std::string, std::vector<unsigned char>> cache;
+  const std::string key(reinterpret_cast<const char *>(V), (size_t)nv * 3 * sizeof(double));
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { out = it->second; return; }
+  }
+  build_cell_table_uncached(V, nv, out);
+  std::lock_guard<std::mutex> lk(mu);
+  if (cache.size() < 4096) cache[key] = out;
+}
+static void build_cell_table_uncached(const double *V, int nv, std::vector<unsigned char> &out) {
   const int G = MPB_CELL_G;
   const double margin = 1e-3;
   double scale = 0;
@@ -348,6 +424,71 @@ static void build_cell_table(const double *V, int nv, std::vector<unsigned char>
   memcpy(out.data() + 2 * (MPB_CELL_COUNT + 1), cand.data(), cand.size());
 }
 
+// parameters, OBB, bounding sphere and inscribed ball of a primitive (object frame); p = obj_param of include/mpb.h
+static void primitive_bounds(DevObject &O, const double *p) {
+  switch (O.type) {
+    case MPB_GEOM_SPHERE:
+      O.prm[0] = (float)p[0];
+      bound_box(p[0], p[0], p[0], O);
+      O.br = (float)(p[0] + 1e-6);
+      O.rin = O.prm[0];
+      break;
+    case MPB_GEOM_BOX:
+      O.prm[0] = (float)(0.5 * p[0]); O.prm[1] = (float)(0.5 * p[1]); O.prm[2] = (float)(0.5 * p[2]);
+      bound_box(0.5 * p[0], 0.5 * p[1], 0.5 * p[2], O);
+      O.rin = std::min(O.prm[0], std::min(O.prm[1], O.prm[2]));
+      break;
+    case MPB_GEOM_CAPSULE:
+      O.prm[0] = (float)p[0]; O.prm[1] = (float)(0.5 * p[1]);
+      bound_box(p[0], p[0], 0.5 * p[1] + p[0], O);
+      O.br = (float)(p[0] + 0.5 * p[1] + 1e-6);
+      O.rin = O.prm[0];
+      break;
+    case MPB_GEOM_CYLINDER:
+      O.prm[0] = (float)p[0]; O.prm[1] = (float)(0.5 * p[1]);
+      bound_box(p[0], p[0], 0.5 * p[1], O);
+      O.rin = std::min(O.prm[0], O.prm[1]);
+      break;
+    default: break;
+  }
+}
+
+// Everything of an object that depends on its pose L: sphere centres in the world / owner-joint frame, the cull
+// record (MPB_COBB_WORDS float4, see dense_kernel) and, for a moving object, its record in fk_table_kernel's table.
+static void object_derived(mpb_scene *s, int o) {
+  DevObject &O = s->h_objs[o];
+  for (int r = 0; r < 3; r++)
+    O.bcw[r] = O.bcj[r] = O.L[4 * r] * O.bc[0] + O.L[4 * r + 1] * O.bc[1] + O.L[4 * r + 2] * O.bc[2] + O.L[4 * r + 3];
+  double Lm[12], E[12], Ei[12], M[12];
+  for (int k = 0; k < 12; k++) Lm[k] = O.L[k];
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 3; c++) { E[4 * r + c] = O.oR[3 * r + c]; Ei[4 * r + c] = O.oR[3 * c + r]; }
+    E[4 * r + 3] = O.oc[r];
+  }
+  for (int r = 0; r < 3; r++) Ei[4 * r + 3] = -(Ei[4 * r] * O.oc[0] + Ei[4 * r + 1] * O.oc[1] + Ei[4 * r + 2] * O.oc[2]);
+  mul12(Lm, E, M);
+  float4 *rec = s->h_cobb.data() + (size_t)MPB_COBB_WORDS * o;
+  for (int r = 0; r < 3; r++) {
+    rec[r] = make_float4((float)M[4 * r], (float)M[4 * r + 1], (float)M[4 * r + 2], (float)M[4 * r + 3]);
+    rec[5 + r] = make_float4((float)E[4 * r], (float)E[4 * r + 1], (float)E[4 * r + 2], (float)E[4 * r + 3]);
+    rec[8 + r] = make_float4((float)Ei[4 * r], (float)Ei[4 * r + 1], (float)Ei[4 * r + 2], (float)Ei[4 * r + 3]);
+  }
+  rec[3] = make_float4(O.oh[0], O.oh[1], O.oh[2], O.type >= MPB_GEOM_MESH ? 0.f : O.rin);
+  float co[3];  // inscribed-ball centre in the OBB frame
+  for (int r = 0; r < 3; r++) co[r] = (float)(Ei[4 * r] * O.ctr[0] + Ei[4 * r + 1] * O.ctr[1] + Ei[4 * r + 2] * O.ctr[2] + Ei[4 * r + 3]);
+  int dyn = O.dyn;
+  float df;
+  memcpy(&df, &dyn, sizeof(float));
+  rec[4] = make_float4(co[0], co[1], co[2], df);
+  if (O.dyn >= 0)
+    for (size_t e = 0; e < s->h_dynlist.size(); e++)
+      if (s->h_dynlist[e] == o) {
+        FkObjC &F = s->fk_tab.o[e];
+        for (int r = 0; r < 3; r++) { F.rec[r] = rec[r]; F.bcj[r] = O.bcj[r]; }
+        F.dyn = O.dyn;
+      }
+}
+
 static inline float __int_as_float_host(int v) { float f; memcpy(&f, &v, sizeof f); return f; }
 
 static int geom_key(int type, int geom) { return type == MPB_GEOM_CONVEX ? 16 + geom : type; }
@@ -355,6 +496,7 @@ static int geom_key(int type, int geom) { return type == MPB_GEOM_CONVEX ? 16 + 
 static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32_t *pb) {
   const int no = (int)s->h_objs.size();
   std::map<std::pair<int, int>, int> bins, bins2;
+  if (pa != s->h_pair_a.data()) { s->h_pair_a.assign(pa, pa + n_pairs); s->h_pair_b.assign(pb, pb + n_pairs); }
   s->h_pairs.resize(n_pairs);
   s->h_pair_bin2.assign(n_pairs, -1);
   int expand_bin = -1, expand2_bin = -1;
@@ -388,7 +530,7 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
   }
   // cull table: entries sorted by (moving object, partner kind, pair index); see sphere_kernel
   {
-    struct Ent { int m1, kind, p, m2; float c[3]; float rr2; };
+    struct Ent { int m1, kind, p, m2; float c[3]; float rr2; int fixed_verdict; };
     std::vector<Ent> ents((size_t)n_pairs);
     for (int p = 0; p < n_pairs; p++) {
       const DevPair &pr = s->h_pairs[p];
@@ -399,10 +541,12 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
       if (A.dyn >= 0 && B.dyn >= 0) { e.m1 = A.dyn; e.m2 = B.dyn; e.kind = 1; }
       else if (A.dyn >= 0) { e.m1 = A.dyn; e.m2 = -1; e.kind = 0; for (int k = 0; k < 3; k++) e.c[k] = B.bcw[k]; }
       else if (B.dyn >= 0) { e.m1 = B.dyn; e.m2 = -1; e.kind = 0; for (int k = 0; k < 3; k++) e.c[k] = A.bcw[k]; }
-      else {  // both world-fixed: the sphere verdict is a constant (the moving centre reads as the origin)
+      else {  // both world-fixed: the moving centre reads as the origin, so the "partner centre" is the difference of the two
+        // centres.  Distance mode gets the true bounds from it; the collide mode keeps a constant verdict (expanded form below)
         e.m1 = -1; e.m2 = -1; e.kind = 0;
-        const float dx = A.bcw[0] - B.bcw[0], dy = A.bcw[1] - B.bcw[1], dz = A.bcw[2] - B.bcw[2];
-        e.rr2 = (dx * dx + dy * dy + dz * dz <= pr.rr * pr.rr) ? FLT_MAX : -1.f;
+        for (int k = 0; k < 3; k++) e.c[k] = B.bcw[k] - A.bcw[k];
+        const float d2 = e.c[0] * e.c[0] + e.c[1] * e.c[1] + e.c[2] * e.c[2];
+        e.fixed_verdict = d2 <= pr.rr * pr.rr ? 1 : -1;
       }
       ents[p] = e;
     }
@@ -423,8 +567,8 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
         const double c2 = (double)e.c[0] * e.c[0] + (double)e.c[1] * e.c[1] + (double)e.c[2] * e.c[2];
         const double rr2 = e.rr2;
         double w;
-        if (e.rr2 >= FLT_MAX) w = -FLT_MAX;
-        else if (e.rr2 < 0.f) w = c2 + 1.0;
+        if (e.fixed_verdict > 0) w = -FLT_MAX;      // with the moving centre at the origin the test reads  w <= 0
+        else if (e.fixed_verdict < 0) w = 1.0;
         else w = c2 - rr2 - 2e-6 * std::max(c2, rr2) - 1e-9;
         s->h_cullq[k] = make_float4(-2.f * e.c[0], -2.f * e.c[1], -2.f * e.c[2], (float)w);
       }
@@ -493,7 +637,6 @@ static int upload_pairs(mpb_scene *s) {
   s->img.cullq = s->d_cullq;
   s->img.cullm = s->d_cullm;
   s->img.runs = s->d_runs;
-  s->chunk = 0;  // queue sizing depends on the pair count
   return MPB_OK;
 }
 
@@ -666,22 +809,10 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     const double *p = d->obj_param + 4 * o;
     switch (O.type) {
       case MPB_GEOM_SPHERE:
-        O.prm[0] = (float)p[0];
-        bound_box(p[0], p[0], p[0], O);
-        O.br = (float)(p[0] + 1e-6);
-        break;
       case MPB_GEOM_BOX:
-        O.prm[0] = (float)(0.5 * p[0]); O.prm[1] = (float)(0.5 * p[1]); O.prm[2] = (float)(0.5 * p[2]);
-        bound_box(0.5 * p[0], 0.5 * p[1], 0.5 * p[2], O);
-        break;
       case MPB_GEOM_CAPSULE:
-        O.prm[0] = (float)p[0]; O.prm[1] = (float)(0.5 * p[1]);
-        bound_box(p[0], p[0], 0.5 * p[1] + p[0], O);
-        O.br = (float)(p[0] + 0.5 * p[1] + 1e-6);
-        break;
       case MPB_GEOM_CYLINDER:
-        O.prm[0] = (float)p[0]; O.prm[1] = (float)(0.5 * p[1]);
-        bound_box(p[0], p[0], 0.5 * p[1], O);
+        primitive_bounds(O, p);
         break;
       case MPB_GEOM_CONVEX: {
         int h = O.geom;
@@ -724,10 +855,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
         return fail(MPB_ERR_INVALID, "unknown geometry type");
     }
     switch (O.type) {  // ball around ctr contained in the shape (0 disables the sufficient-hit test)
-      case MPB_GEOM_SPHERE: O.rin = O.prm[0]; break;
-      case MPB_GEOM_BOX: O.rin = std::min(O.prm[0], std::min(O.prm[1], O.prm[2])); break;
-      case MPB_GEOM_CAPSULE: O.rin = O.prm[0]; break;
-      case MPB_GEOM_CYLINDER: O.rin = std::min(O.prm[0], O.prm[1]); break;
+      case MPB_GEOM_SPHERE: case MPB_GEOM_BOX: case MPB_GEOM_CAPSULE: case MPB_GEOM_CYLINDER: break;  // primitive_bounds
       case MPB_GEOM_CONVEX: {
         const int h = O.geom;
         const double *V = d->hull_verts + 3 * (size_t)d->hull_vert_off[h];
@@ -765,50 +893,18 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     if (P.jslot < 0) P.jslot = n_jslots++;
     s->h_joints[j].pjslot = P.jslot;
   }
-  for (int o = 0; o < d->n_objects; o++) {
-    DevObject &O = s->h_objs[o];
-    for (int r = 0; r < 3; r++)
-      O.bcw[r] = O.bcj[r] = O.L[4 * r] * O.bc[0] + O.L[4 * r + 1] * O.bc[1] + O.L[4 * r + 2] * O.bc[2] + O.L[4 * r + 3];
-    O.jslot = O.joint > 0 ? s->h_joints[O.joint - 1].jslot : -1;
-  }
+  for (int o = 0; o < d->n_objects; o++) s->h_objs[o].jslot = s->h_objs[o].joint > 0 ? s->h_joints[s->h_objs[o].joint - 1].jslot : -1;
   s->img.n_dyn = ndyn;
   s->img.n_jslots = n_jslots;
   s->img.w_sphere = 0;
   s->img.w_joint = ndyn * 3;
-  // cull records (MPB_COBB_WORDS float4 per object), see dense_kernel
-  std::vector<float4> cobb((size_t)d->n_objects * MPB_COBB_WORDS);
-  for (int o = 0; o < d->n_objects; o++) {
-    const DevObject &O = s->h_objs[o];
-    double Lm[12], E[12], Ei[12], M[12];
-    for (int k = 0; k < 12; k++) Lm[k] = O.L[k];
-    for (int r = 0; r < 3; r++) {
-      for (int c = 0; c < 3; c++) { E[4 * r + c] = O.oR[3 * r + c]; Ei[4 * r + c] = O.oR[3 * c + r]; }
-      E[4 * r + 3] = O.oc[r];
-    }
-    for (int r = 0; r < 3; r++) Ei[4 * r + 3] = -(Ei[4 * r] * O.oc[0] + Ei[4 * r + 1] * O.oc[1] + Ei[4 * r + 2] * O.oc[2]);
-    mul12(Lm, E, M);
-    float4 *rec = cobb.data() + (size_t)MPB_COBB_WORDS * o;
-    for (int r = 0; r < 3; r++) {
-      rec[r] = make_float4((float)M[4 * r], (float)M[4 * r + 1], (float)M[4 * r + 2], (float)M[4 * r + 3]);
-      rec[5 + r] = make_float4((float)E[4 * r], (float)E[4 * r + 1], (float)E[4 * r + 2], (float)E[4 * r + 3]);
-      rec[8 + r] = make_float4((float)Ei[4 * r], (float)Ei[4 * r + 1], (float)Ei[4 * r + 2], (float)Ei[4 * r + 3]);
-    }
-    rec[3] = make_float4(O.oh[0], O.oh[1], O.oh[2], O.type >= MPB_GEOM_MESH ? 0.f : O.rin);
-    float co[3];  // inscribed-ball centre in the OBB frame
-    for (int r = 0; r < 3; r++) co[r] = (float)(Ei[4 * r] * O.ctr[0] + Ei[4 * r + 1] * O.ctr[1] + Ei[4 * r + 2] * O.ctr[2] + Ei[4 * r + 3]);
-    int dyn = O.dyn;
-    float df;
-    memcpy(&df, &dyn, sizeof(float));
-    rec[4] = make_float4(co[0], co[1], co[2], df);
-  }
-  // fk_table_kernel's parameter-space tables: joints, and the moving objects grouped by owner joint
+  // cull records, sphere centres and fk_table_kernel's parameter-space tables (joints; moving objects grouped by owner joint)
+  s->h_dynlist = dynlist;
+  s->h_cobb.assign((size_t)d->n_objects * MPB_COBB_WORDS, make_float4(0.f, 0.f, 0.f, 0.f));
   for (int j = 0; j < d->n_joints; j++) s->fk_tab.j[j] = s->h_joints[j];
-  for (size_t e = 0; e < dynlist.size(); e++) {
-    const int o = dynlist[e];
-    FkObjC &F = s->fk_tab.o[e];
-    for (int r = 0; r < 3; r++) { F.rec[r] = cobb[(size_t)MPB_COBB_WORDS * o + r]; F.bcj[r] = s->h_objs[o].bcj[r]; }
-    F.dyn = s->h_objs[o].dyn;
-  }
+  for (int o = 0; o < d->n_objects; o++) object_derived(s, o);
+  s->h_objLink.assign(d->obj_link, d->obj_link + d->n_objects);
+  std::vector<float4> &cobb = s->h_cobb;
 
   s->img.n_joints = d->n_joints;
   s->img.n_objects = d->n_objects;
@@ -848,13 +944,19 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   s->img.linkJoint = s->d_linkJoint;
   rc = upload_pairs(s);
   if (rc != MPB_OK) { mpb_scene_destroy(s); return rc; }
+  CU(cudaHostAlloc((void **)&s->h_status, 32 * sizeof(unsigned), cudaHostAllocDefault));
+  {
+    std::vector<float> qc(std::max(d->n_joints, 1), 0.f);
+    for (int j = 0; j < d->n_joints; j++) qc[j] = s->h_joints[j].qconst;
+    CU(up((void **)&s->d_qconst, qc.data(), qc.size() * sizeof(float)));
+  }
 
   // narrowphase launch shape: hull pool in shared memory when it fits
   const size_t vbytes = verts.size() * sizeof(float4);
   s->smem_verts = vbytes <= 200 * 1024;
   int per_sm = 0;
   if (s->smem_verts) {
-    CU(cudaFuncSetAttribute(narrow_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vbytes, 16)));
+    CU(raise_dyn_smem((const void *)narrow_kernel<true>, device, 0, std::max<size_t>(vbytes, 16)));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<true>, 256, vbytes));
   } else {
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<false>, 256, 0));
@@ -884,6 +986,17 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
                   s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
   for (void *p : ptrs)
     if (p) cudaFree(p);
+  cudaDeviceSynchronize();  // device-pointer calls may still be in flight on caller streams
+  drop_small_graphs(s);
+  if (s->h_small) cudaFreeHost(s->h_small);
+  if (s->h_status) cudaFreeHost(s->h_status);
+  if (s->h_slots) cudaFreeHost(s->h_slots);
+  if (s->d_hits) cudaFree(s->d_hits);
+  if (s->d_qconst) cudaFree(s->d_qconst);
+  for (auto &sl : s->slots) {
+    if (sl.done) cudaEventDestroy(sl.done);
+    for (auto e : sl.ev) cudaEventDestroy(e);
+  }
   for (auto &b : s->pool) cudaFree(b.first);
   for (auto e : s->events) cudaEventDestroy(e);
   for (auto e : s->sync_events) cudaEventDestroy(e);
@@ -908,21 +1021,74 @@ extern "C" int mpb_scene_set_q_base(mpb_scene *s, const double *q_base, int32_t 
   if (!s || !q_base) return fail(MPB_ERR_INVALID, "null argument");
   if (nq_full != s->nq_full) return fail(MPB_ERR_INVALID, "q_base length does not match the scene");
   CU(cudaSetDevice(s->device));
-  for (size_t j = 0; j < s->h_joints.size(); j++) s->h_joints[j].qconst = (float)q_base[s->joint_qidx[j]];
-  for (size_t j = 0; j < s->h_joints.size(); j++) s->fk_tab.j[j].qconst = s->h_joints[j].qconst;
   s->h_qbase64.assign(q_base, q_base + nq_full);
+  // only joints the batch state does not write read q_base on the device: the legacy single-state calls change the
+  // articulation's qpos before every query, but rarely the joints outside the move group
+  bool changed = false;
+  for (size_t j = 0; j < s->h_joints.size(); j++) {
+    const float v = (float)q_base[s->joint_qidx[j]];
+    if (s->h_joints[j].slot < 0 && v != s->h_joints[j].qconst) changed = true;
+    s->h_joints[j].qconst = v;
+    s->fk_tab.j[j].qconst = v;
+  }
+  if (!changed || s->h_joints.empty()) return MPB_OK;
+  int rc = harvest(s, true);
+  if (rc != MPB_OK) return rc;
   CU(cudaStreamSynchronize(s->stream));
-  if (!s->h_joints.empty())
-    CU(cudaMemcpy(s->d_joints, s->h_joints.data(), s->h_joints.size() * sizeof(DevJoint), cudaMemcpyHostToDevice));
+  std::vector<float> qc(s->h_joints.size());
+  for (size_t j = 0; j < qc.size(); j++) qc[j] = s->h_joints[j].qconst;
+  CU(cudaMemcpy(s->d_qconst, qc.data(), qc.size() * sizeof(float), cudaMemcpyHostToDevice));  // kernels read it through this table
+  CU(cudaMemcpy(s->d_joints, s->h_joints.data(), s->h_joints.size() * sizeof(DevJoint), cudaMemcpyHostToDevice));
   return MPB_OK;
 }
 
 extern "C" int mpb_scene_set_pairs(mpb_scene *s, int32_t n_pairs, const int32_t *pa, const int32_t *pb) {
   if (!s || n_pairs < 0 || (n_pairs && (!pa || !pb))) return fail(MPB_ERR_INVALID, "bad pair list");
   CU(cudaSetDevice(s->device));
-  CU(cudaStreamSynchronize(s->stream));
-  int rc = build_pairs(s, n_pairs, pa, pb);
+  int rc = harvest(s, true);
   if (rc != MPB_OK) return rc;
+  CU(cudaDeviceSynchronize());
+  rc = build_pairs(s, n_pairs, pa, pb);
+  if (rc != MPB_OK) return rc;
+  s->img_version++;
+  s->calibrated = false;
+  return upload_pairs(s);
+}
+
+// In-place update of objects of a compiled scene.  Geometry (type, hull / mesh / octree) stays; what may change is the
+// pose of a world-fixed object (CollisionObject::setTransformation, python/pybind_fcl.hpp:254-259, used in place by
+// mplib/sapien_utils/conversion.py:176-178), the pose of an attached body on its link (AttachedBodyTpl::setPose,
+// src/attached_body.h) and the parameters of a primitive.  Only the records derived from those are recomputed.
+extern "C" int mpb_scene_update_objects(mpb_scene *s, int32_t n, const int32_t *obj_idx, const double *obj_local, const double *obj_param) {
+  if (!s || n < 0 || (n > 0 && (!obj_idx || (!obj_local && !obj_param)))) return fail(MPB_ERR_INVALID, "bad object update");
+  if (n == 0) return MPB_OK;
+  const int no = (int)s->h_objs.size();
+  for (int k = 0; k < n; k++)
+    if (obj_idx[k] < 0 || obj_idx[k] >= no) return fail(MPB_ERR_INVALID, "object index out of range");
+  CU(cudaSetDevice(s->device));
+  int rc = harvest(s, true);
+  if (rc != MPB_OK) return rc;
+  CU(cudaDeviceSynchronize());
+  for (int k = 0; k < n; k++) {
+    const int o = obj_idx[k];
+    DevObject &O = s->h_objs[o];
+    if (obj_param && O.type >= MPB_GEOM_SPHERE && O.type <= MPB_GEOM_CYLINDER) primitive_bounds(O, obj_param + 4 * (size_t)k);
+    if (obj_local) {
+      double L[12];
+      const int link = s->h_objLink[o];
+      if (link >= 0) mul12(s->h_linkL64.data() + 12 * (size_t)link, obj_local + 12 * (size_t)k, L);
+      else memcpy(L, obj_local + 12 * (size_t)k, sizeof(L));
+      for (int i = 0; i < 12; i++) O.L[i] = (float)L[i];
+    }
+    object_derived(s, o);
+  }
+  // the cull table holds sphere centres and radius sums of the pairs: rebuild it (O(pairs), no geometry work)
+  rc = build_pairs(s, (int)s->h_pair_a.size(), s->h_pair_a.data(), s->h_pair_b.data());
+  if (rc != MPB_OK) return rc;
+  CU(cudaMemcpy(s->d_objs, s->h_objs.data(), s->h_objs.size() * sizeof(DevObject), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(s->d_cobb, s->h_cobb.data(), s->h_cobb.size() * sizeof(float4), cudaMemcpyHostToDevice));
+  s->img_version++;
+  s->calibrated = false;
   return upload_pairs(s);
 }
 
@@ -942,11 +1108,22 @@ static const long long kMaxChunk = 1ll << 20;       // configurations per pass
 static const size_t kMaxItems = (size_t)48 << 20;   // work-queue capacity bound (x56 B = 2.6 GiB)
 static const size_t kMaxSurvivors = (size_t)192 << 20;  // survivor-queue capacity bound (x8 B = 1.5 GiB)
 
+// Largest pass whose queue counters (32-bit: survivor slots, staged items) cannot wrap even if every admitted pair of
+// every configuration survives.
+static long long max_chunk_for(const mpb_scene *s) {
+  const long long P = std::max(s->img.n_pairs, 1);
+  const long long lim = ((1ll << 31) / P) / 32 * 32;
+  return std::max<long long>(32, std::min<long long>(kMaxChunk, lim));
+}
+
 static int prepare_work(mpb_scene *s, long long chunk) {
   // grow-only: buffers sized for a larger pass serve a smaller one (collide calls of different sizes and planning
   // rounds alternate on one scene; re-allocating GBs of queues between them would dominate small calls)
-  if (chunk <= s->chunk && s->wq.itf) return MPB_OK;
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
+  if (chunk <= s->chunk && s->wq.itf && P <= s->work_P && (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1) <= s->bins_cap) return MPB_OK;
+  CU(cudaDeviceSynchronize());  // calls in flight (device-pointer mode) still use the old buffers
+  chunk = std::max(chunk, s->chunk);
+  s->work_P = P;
   // staging may hold up to one unused half-chunk per reservation: worst case 2 x items + one chunk per warp
   // plus one partly used reservation per warp of dense_kernel / expand_kernel
   size_t cap = std::min((size_t)chunk * P * 2 + (size_t)s->num_sms * 8 * 4 * MPB_STAGE_CHUNK, kMaxItems);
@@ -1006,21 +1183,36 @@ static cudaEvent_t get_sync_event(mpb_scene *s, size_t i) {
   return s->sync_events[i];
 }
 
+// Result sink of one pass (see HitOut): `hits` / `n_hits` are call-wide, `cfg0` is the pass's offset in the call.
+struct PassOut {
+  uint32_t *dv = nullptr, *dp = nullptr;
+  uint2 *hits = nullptr;
+  unsigned *n_hits = nullptr;
+  unsigned hit_cap = 0, cfg0 = 0;
+};
+
+// Timing events of one pass: [0] start, [1] FK + cull done, [2] narrowphase done, [3], [4] around fk_table_kernel.
+struct PassEvents {
+  cudaEvent_t e[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool on = false;
+};
+
 // Kernels of one pass over m configurations.  hq == nullptr: q already sits at dq.  Otherwise the pass's q is
 // copied from the host pointer hq in sub-ranges on stream_h2d and FK + cull runs per sub-range as it lands, all
 // appending to the same staging queue; binning and narrowphase then run once over the whole pass.
-static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, uint32_t *dv, uint32_t *dp, cudaStream_t st,
-                       size_t *ev, long long *launches, const float *hq, size_t *sync_ev) {
+static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, const PassOut &po, cudaStream_t st,
+                       const PassEvents &pe, long long *launches, const float *hq, size_t *sync_ev) {
   const int D = s->img.state_dim, W = s->img.pair_words, nb = std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
   const size_t vwords = (size_t)(m + 31) / 32;
+  uint32_t *dv = po.dv, *dp = po.dp;
+  HitOut out;
+  out.verdict = dv; out.pair_bits = dp; out.hits = po.hits; out.n_hits = po.n_hits; out.hit_cap = po.hit_cap; out.cfg0 = po.cfg0;
+  out.pair_words = W;
   CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
   if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
-  CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
-  CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
-  CU(cudaMemsetAsync(s->wq.totals + 6, 0, sizeof(unsigned), st));
-  cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;  // ev == nullptr: no timing events (graph capture)
-  cudaEvent_t f0 = nullptr, f1 = nullptr;                // around fk_table_kernel (device-resident input only)
-  if (ev) { e0 = get_event(s, (*ev)++); e1 = get_event(s, (*ev)++); e2 = get_event(s, (*ev)++); f0 = get_event(s, (*ev)++); f1 = get_event(s, (*ev)++); }
+  pass_reset_kernel<<<1, 256, 0, st>>>(s->wq, nb);
+  const bool ev = pe.on;
+  cudaEvent_t e0 = pe.e[0], e1 = pe.e[1], e2 = pe.e[2], f0 = pe.e[3], f1 = pe.e[4];
   if (ev) CU(cudaEventRecord(e0, st));
   if (ev && hq) { CU(cudaEventRecord(f0, st)); CU(cudaEventRecord(f1, st)); }
   const long long sub = hq ? std::max<long long>(s->host_chunk, 64) : m;
@@ -1035,7 +1227,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((mm + 127) / 128);
       if (ev && !hq) CU(cudaEventRecord(f0, st));
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, s->d_qconst, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
       if (ev && !hq) CU(cudaEventRecord(f1, st));
       const int sblocks = std::min(cblocks, s->sphere_blocks[0]);  // persistent warps: survivor-queue chunks carry over between tiles
       if (s->cull_tier == 1)
@@ -1050,6 +1242,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       *launches += 2;
     }
   }
+  *launches += 1;
   if (s->img.n_pairs == 0) {
     if (ev) {
       if (!hq) { CU(cudaEventRecord(f0, st)); CU(cudaEventRecord(f1, st)); }
@@ -1058,7 +1251,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     return MPB_OK;
   }
-  dense_kernel<0><<<s->dense_blocks[0], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, dv, dp);
+  dense_kernel<0><<<s->dense_blocks[0], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out);
   *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
@@ -1066,46 +1259,94 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
-  if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
-  else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins, 0);
+  if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
+  else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
   *launches += 3;
   if (s->img.expand2_bin >= 0) {  // mesh x mesh / mesh x octree pairs: exact leaf tests inside the descent
-    expand2_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
+    expand2_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, out);
     *launches += 1;
   }
   if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
-    CU(cudaMemsetAsync(s->wq.totals, 0, sizeof(unsigned), st));
-    CU(cudaMemsetAsync(s->wq.bin_count, 0, (size_t)nb * sizeof(unsigned), st));
-    expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dv, dp);
+    pass_reset_kernel<<<1, 256, 0, st>>>(s->wq, nb);
+    expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, out);
     scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, n_warps, s->sq_cap);
     scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1);
-    if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
-    else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, dv, dp, s->img.n_bins2, 1);
-    *launches += 4;
+    if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);
+    else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);
+    *launches += 5;
   }
   if (ev) CU(cudaEventRecord(e2, st));
   CU(cudaGetLastError());
   return MPB_OK;
 }
 
-// One attempt over the whole batch with a given chunk size.  Returns MPB_OK and sets *overflow.
+// What a caller wants back per (configuration, pair): nothing, the dense mask, or the sparse hit list.
+struct CollideOut {
+  uint32_t *verdict = nullptr;
+  uint32_t *pair_bits = nullptr;
+  uint32_t *hits = nullptr;      // [hit_cap][2]
+  int64_t hit_cap = 0;
+  uint32_t *n_hits = nullptr;    // [1], same space as hits
+};
+
+static void fill_stats(mpb_scene *s, mpb_stats *stats, long long n, const unsigned long long *counters, long long launches) {
+  stats->n_states = n;
+  stats->pairs_admitted = n * (long long)s->img.n_pairs;
+  stats->pairs_after_cull = (long long)counters[0];
+  stats->pairs_after_spheres = (long long)counters[3];
+  stats->narrow_iterations = (long long)counters[1];
+  stats->narrow_capped = (long long)counters[2];
+  stats->kernel_launches = launches;
+  stats->fk_bytes_per_state = (int32_t)(4 * s->img.state_dim + 4 * (s->img.n_jslots * 12 + s->img.n_dyn * 3) + 32 * s->img.n_dyn);
+}
+
+static void add_pass_times(const cudaEvent_t *e, float *cull, float *narrow, float *fk) {
+  float a = 0.f, b = 0.f, c = 0.f;
+  cudaEventElapsedTime(&a, e[0], e[1]);
+  cudaEventElapsedTime(&b, e[1], e[2]);
+  cudaEventElapsedTime(&c, e[3], e[4]);
+  *cull += a;
+  *narrow += b;
+  *fk += c;
+}
+
+// One blocking attempt over the whole batch with a given chunk size.  Returns MPB_OK and sets *overflow.
 // Host buffers: chunk c uses device buffer set c & 1; its H2D runs on stream_h2d, its kernels on `st`, its D2H on
 // stream_d2h, so the copies of neighbouring chunks overlap the kernels (PCIe is full duplex).
-static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *verdict, uint32_t *pair_bits, int space,
+static int collide_attempt(mpb_scene *s, const float *q, long long n, const CollideOut &co, int space,
                            cudaStream_t st, long long chunk, bool *overflow, mpb_stats *stats) {
   const auto t_begin = std::chrono::steady_clock::now();
   int rc = prepare_work(s, chunk);
   if (rc != MPB_OK) return rc;
   const int D = s->img.state_dim, W = s->img.pair_words;
   const bool host = space == MPB_HOST;
+  const bool want_hits = co.hits != nullptr && co.n_hits != nullptr;
+  const bool want_mask = co.pair_bits != nullptr || want_hits;
   if (host) {
     for (int b = 0; b < 2; b++) {
       CU(ensure(&s->d_q[b], &s->d_q_cap[b], (size_t)chunk * std::max(D, 1)));
       CU(ensure(&s->d_verdict[b], &s->d_verdict_cap[b], (size_t)(chunk + 31) / 32));
-      if (pair_bits) CU(ensure(&s->d_pairbits[b], &s->d_pairbits_cap[b], (size_t)chunk * std::max(W, 1)));
+      if (want_mask) CU(ensure(&s->d_pairbits[b], &s->d_pairbits_cap[b], (size_t)chunk * std::max(W, 1)));
     }
     if (!s->stream_h2d) CU(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
     if (!s->stream_d2h) CU(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
+  } else if (want_hits) {
+    CU(ensure(&s->d_pairbits[0], &s->d_pairbits_cap[0], (size_t)chunk * std::max(W, 1)));  // the dense mask stays on the device
+  }
+  uint2 *d_hits = nullptr;
+  unsigned *d_nhits = nullptr;
+  unsigned hit_cap = 0;
+  if (want_hits) {
+    hit_cap = (unsigned)std::min<int64_t>(std::max<int64_t>(co.hit_cap, 0), (int64_t)1 << 30);
+    if (host) {
+      CU(ensure(&s->d_hits, &s->d_hits_cap, (size_t)hit_cap + 2));
+      d_hits = s->d_hits + 1;                                  // [0] holds the counter
+      d_nhits = reinterpret_cast<unsigned *>(s->d_hits);
+    } else {
+      d_hits = reinterpret_cast<uint2 *>(co.hits);
+      d_nhits = co.n_hits;
+    }
+    CU(cudaMemsetAsync(d_nhits, 0, sizeof(unsigned), st));
   }
   CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
   CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
@@ -1120,9 +1361,15 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
   for (long long off = 0; off < n; off += chunk, c++) {
     const long long m = std::min(chunk, n - off);
     const size_t vwords = (size_t)(m + 31) / 32;
+    PassEvents pe;
+    pe.on = true;
+    for (int k = 0; k < 5; k++) pe.e[k] = get_event(s, ev++);
+    PassOut po;
+    po.hits = d_hits; po.n_hits = d_nhits; po.hit_cap = hit_cap; po.cfg0 = (unsigned)off;
     if (!host) {
-      rc = launch_pass(s, nullptr, q + off * D, m, verdict + off / 32, pair_bits ? pair_bits + (size_t)off * W : nullptr, st, &ev,
-                       &launches, nullptr, &sync_ev);
+      po.dv = co.verdict + off / 32;
+      po.dp = co.pair_bits ? co.pair_bits + (size_t)off * W : (want_hits ? s->d_pairbits[0] : nullptr);
+      rc = launch_pass(s, nullptr, q + off * D, m, po, st, pe, &launches, nullptr, &sync_ev);
       if (rc != MPB_OK) return rc;
       continue;
     }
@@ -1131,47 +1378,44 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
       CU(cudaStreamWaitEvent(s->stream_h2d, ev_k[c - 2], 0));  // kernels of pass c-2 read d_q[b]
       CU(cudaStreamWaitEvent(st, ev_out[c - 2], 0));           // D2H of pass c-2 read the result buffers
     }
-    uint32_t *dv = s->d_verdict[b], *dp = pair_bits ? s->d_pairbits[b] : nullptr;
-    rc = launch_pass(s, s->d_q[b], s->d_q[b], m, dv, dp, st, &ev, &launches, q + off * D, &sync_ev);
+    po.dv = s->d_verdict[b];
+    po.dp = want_mask ? s->d_pairbits[b] : nullptr;
+    rc = launch_pass(s, s->d_q[b], s->d_q[b], m, po, st, pe, &launches, q + off * D, &sync_ev);
     if (rc != MPB_OK) return rc;
     ev_k.push_back(get_sync_event(s, sync_ev++));
     ev_out.push_back(get_sync_event(s, sync_ev++));
     CU(cudaEventRecord(ev_k[c], st));
     CU(cudaStreamWaitEvent(s->stream_d2h, ev_k[c], 0));
-    CU(cudaMemcpyAsync(verdict + off / 32, dv, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
-    if (pair_bits)
-      CU(cudaMemcpyAsync(pair_bits + (size_t)off * W, dp, (size_t)m * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
+    CU(cudaMemcpyAsync(co.verdict + off / 32, po.dv, vwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
+    if (co.pair_bits)
+      CU(cudaMemcpyAsync(co.pair_bits + (size_t)off * W, po.dp, (size_t)m * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
     CU(cudaEventRecord(ev_out[c], s->stream_d2h));
   }
   const auto t_enq = std::chrono::steady_clock::now();
-  unsigned totals[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  unsigned long long counters[4] = {0, 0, 0, 0};
-  CU(cudaMemcpyAsync(totals, s->wq.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(counters, s->wq.counters, sizeof(counters), cudaMemcpyDeviceToHost, st));
+  unsigned *totals = s->h_status;                                                        // pinned
+  unsigned long long *counters = reinterpret_cast<unsigned long long *>(s->h_status + 8);
+  CU(cudaMemcpyAsync(totals, s->wq.totals, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(counters, s->wq.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  if (want_hits && host) CU(cudaMemcpyAsync(s->h_status + 16, d_nhits, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   if (host) CU(cudaStreamSynchronize(s->stream_d2h));
-  const auto t_end = std::chrono::steady_clock::now();
   *overflow = totals[2] != 0;
+  if (want_hits && host && !*overflow) {
+    const unsigned nh = s->h_status[16];
+    *co.n_hits = nh;
+    const unsigned ncopy = std::min(nh, hit_cap);
+    if (ncopy) CU(cudaMemcpy(co.hits, d_hits, (size_t)ncopy * sizeof(uint2), cudaMemcpyDeviceToHost));
+  }
+  const auto t_end = std::chrono::steady_clock::now();
+  if (!*overflow) {  // what the device-pointer fast path sizes its passes from
+    s->calibrated = true;
+    s->good_chunk = chunk;
+  }
   if (stats) {
-    stats->n_states = n;
-    stats->pairs_admitted = n * (long long)s->img.n_pairs;
-    stats->pairs_after_cull = (long long)counters[0];
-    stats->pairs_after_spheres = (long long)counters[3];
-    stats->narrow_iterations = (long long)counters[1];
-    stats->narrow_capped = (long long)counters[2];
-    stats->kernel_launches = launches;
+    fill_stats(s, stats, n, counters, launches);
     float cull = 0.f, narrow = 0.f, fk = 0.f;
-    for (size_t i = 0; i + 5 <= ev; i += 5) {
-      float a = 0.f, b = 0.f, c = 0.f;
-      cudaEventElapsedTime(&a, s->events[i], s->events[i + 1]);
-      cudaEventElapsedTime(&b, s->events[i + 1], s->events[i + 2]);
-      cudaEventElapsedTime(&c, s->events[i + 3], s->events[i + 4]);
-      cull += a;
-      narrow += b;
-      fk += c;
-    }
+    for (size_t i = 0; i + 5 <= ev; i += 5) add_pass_times(&s->events[i], &cull, &narrow, &fk);
     stats->gpu_ms_fk = fk;
-    stats->fk_bytes_per_state = (int32_t)(4 * s->img.state_dim + 4 * (s->img.n_jslots * 12 + s->img.n_dyn * 3) + 32 * s->img.n_dyn);
     stats->gpu_ms_cull = cull;
     stats->gpu_ms_narrow = narrow;
     stats->gpu_ms = cull + narrow;
@@ -1181,28 +1425,321 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, uint32_t *
   return MPB_OK;
 }
 
-extern "C" int mpb_collide_batch(mpb_scene *s, const float *q, int64_t n, uint32_t *verdict_bits, uint32_t *pair_bits,
-                                 mpb_stats *stats, int space, void *stream) {
+// ---- device-pointer calls that return after enqueueing -------------------------------------------------------------
+// The queue counters of a call are snapshotted by an in-stream copy into a pinned slot of a small ring; a later call
+// (or mpb_scene_poll) harvests the finished slots: statistics are accumulated, an overflowed call is recorded as
+// failed.  The passes are sized from the last blocking call on the scene (the calibration), which is why the first
+// device-pointer call after a scene / pair-list change runs through the blocking protocol.
+static void harvest_slot(mpb_scene *s, AsyncSlot &sl) {
+  const unsigned *totals = sl.h;
+  const unsigned long long *counters = reinterpret_cast<const unsigned long long *>(sl.h + 8);
+  mpb_stats st;
+  memset(&st, 0, sizeof(st));
+  fill_stats(s, &st, sl.n, counters, sl.launches);
+  for (size_t i = 0; i + 5 <= sl.n_ev; i += 5) add_pass_times(&sl.ev[i], &st.gpu_ms_cull, &st.gpu_ms_narrow, &st.gpu_ms_fk);
+  st.gpu_ms = st.gpu_ms_cull + st.gpu_ms_narrow;
+  mpb_stats &a = s->async_acc;
+  a.n_states += st.n_states; a.pairs_admitted += st.pairs_admitted; a.pairs_after_cull += st.pairs_after_cull;
+  a.pairs_after_spheres += st.pairs_after_spheres; a.narrow_iterations += st.narrow_iterations; a.narrow_capped += st.narrow_capped;
+  a.kernel_launches += st.kernel_launches; a.gpu_ms += st.gpu_ms; a.gpu_ms_cull += st.gpu_ms_cull; a.gpu_ms_narrow += st.gpu_ms_narrow;
+  a.gpu_ms_fk += st.gpu_ms_fk; a.host_ms_enqueue += sl.host_ms; a.host_ms_total += sl.host_ms; a.fk_bytes_per_state = st.fk_bytes_per_state;
+  s->async_completed++;
+  if (totals[2]) { s->async_failed++; s->calibrated = false; }  // the next call re-calibrates through the blocking protocol
+  sl.pending = false;
+}
+
+static int harvest(mpb_scene *s, bool wait) {
+  for (int k = 0; k < MPB_ASYNC_SLOTS; k++) {
+    AsyncSlot &sl = s->slots[(s->slot_head + k) % MPB_ASYNC_SLOTS];  // oldest first
+    if (!sl.pending) continue;
+    if (wait) CU(cudaEventSynchronize(sl.done));
+    else {
+      cudaError_t e = cudaEventQuery(sl.done);
+      if (e == cudaErrorNotReady) break;  // slots complete in order
+      if (e != cudaSuccess) return fail(MPB_ERR_CUDA, std::string("cudaEventQuery: ") + cudaGetErrorString(e));
+    }
+    harvest_slot(s, sl);
+  }
+  return MPB_OK;
+}
+
+static int collide_enqueue(mpb_scene *s, const float *q, long long n, const CollideOut &co, cudaStream_t st, mpb_stats *stats) {
+  const auto t_begin = std::chrono::steady_clock::now();
+  const int D = s->img.state_dim, W = s->img.pair_words;
+  const long long chunk = std::min<long long>(s->good_chunk, (n + 31) / 32 * 32);
+  int rc = prepare_work(s, chunk);
+  if (rc != MPB_OK) return rc;
+  const bool want_hits = co.hits != nullptr && co.n_hits != nullptr;
+  if (want_hits && !co.pair_bits) CU(ensure(&s->d_pairbits[0], &s->d_pairbits_cap[0], (size_t)chunk * std::max(W, 1)));
+  if (!s->h_slots) {
+    CU(cudaHostAlloc((void **)&s->h_slots, (size_t)MPB_ASYNC_SLOTS * 32 * sizeof(unsigned), cudaHostAllocDefault));
+    for (int k = 0; k < MPB_ASYNC_SLOTS; k++) {
+      s->slots[k].h = s->h_slots + 32 * k;
+      CU(cudaEventCreateWithFlags(&s->slots[k].done, cudaEventDisableTiming));
+    }
+  }
+  AsyncSlot &sl = s->slots[s->slot_head];
+  if (sl.pending) {  // ring full: wait for the oldest call
+    CU(cudaEventSynchronize(sl.done));
+    harvest_slot(s, sl);
+  }
+  s->slot_head = (s->slot_head + 1) % MPB_ASYNC_SLOTS;
+  unsigned hit_cap = 0;
+  if (want_hits) {
+    hit_cap = (unsigned)std::min<int64_t>(std::max<int64_t>(co.hit_cap, 0), (int64_t)1 << 30);
+    CU(cudaMemsetAsync(co.n_hits, 0, sizeof(unsigned), st));
+  }
+  CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
+  CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
+  const bool timing = s->async_timing;
+  size_t ev = 0, sync_ev = 0;
+  long long launches = 0;
+  for (long long off = 0; off < n; off += chunk) {
+    const long long m = std::min(chunk, n - off);
+    PassEvents pe;
+    pe.on = timing;
+    if (timing) {
+      while (sl.ev.size() < ev + 5) { cudaEvent_t e; CU(cudaEventCreate(&e)); sl.ev.push_back(e); }
+      for (int k = 0; k < 5; k++) pe.e[k] = sl.ev[ev++];
+    }
+    PassOut po;
+    po.dv = co.verdict + off / 32;
+    po.dp = co.pair_bits ? co.pair_bits + (size_t)off * W : (want_hits ? s->d_pairbits[0] : nullptr);
+    po.hits = reinterpret_cast<uint2 *>(co.hits); po.n_hits = co.n_hits; po.hit_cap = hit_cap; po.cfg0 = (unsigned)off;
+    rc = launch_pass(s, nullptr, q + off * D, m, po, st, pe, &launches, nullptr, &sync_ev);
+    if (rc != MPB_OK) return rc;
+  }
+  CU(cudaMemcpyAsync(sl.h, s->wq.totals, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(sl.h + 8, s->wq.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(sl.done, st));
+  sl.pending = true;
+  sl.n = n;
+  sl.launches = launches;
+  sl.n_ev = ev;
+  sl.host_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+  if (stats) {
+    stats->n_states = n;
+    stats->pairs_admitted = n * (long long)s->img.n_pairs;
+    stats->kernel_launches = launches;
+    stats->host_ms_enqueue = stats->host_ms_total = sl.host_ms;
+    stats->async_pending = 1;
+  }
+  return MPB_OK;
+}
+
+extern "C" int mpb_scene_poll(mpb_scene *s, int wait, mpb_stats *sum, int64_t *calls_completed, int64_t *calls_failed) {
   if (!s) return fail(MPB_ERR_INVALID, "null scene");
-  if (n < 0 || (n > 0 && (!verdict_bits || (!q && s->img.state_dim > 0)))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  CU(cudaSetDevice(s->device));
+  int rc = harvest(s, wait != 0);
+  if (rc != MPB_OK) return rc;
+  if (sum) *sum = s->async_acc;
+  if (calls_completed) *calls_completed = s->async_completed;
+  if (calls_failed) *calls_failed = s->async_failed;
+  const long long failed = s->async_failed;
+  memset(&s->async_acc, 0, sizeof(s->async_acc));
+  s->async_completed = 0;
+  s->async_failed = 0;
+  if (failed) return fail(MPB_ERR_CAPACITY, std::to_string(failed) + " device-pointer call(s) overflowed the work queues: their outputs are incomplete, repeat them");
+  return MPB_OK;
+}
+
+extern "C" int mpb_scene_set_async_timing(mpb_scene *s, int on) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  s->async_timing = on != 0;
+  return MPB_OK;
+}
+
+// ---- small host batches: the whole call (H2D, kernels, D2H) replayed as one CUDA graph -----------------------------
+// A legacy single-state query (collide(), Planner.check_for_*_collision, the isValid stub of INTEGRATION.md) is a batch
+// of one: a dozen launches and copies whose enqueue cost, not their execution, sets the latency.  Calls of at most
+// kSmallBatch states go through pinned staging buffers and a graph cached per (n, outputs) shape.
+static const long long kSmallBatch = 4096;
+
+static void drop_small_graphs(mpb_scene *s) {
+  for (auto &g : s->small_graphs) {
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+  }
+  s->small_graphs.clear();
+}
+
+static int collide_small(mpb_scene *s, const float *q, long long n, const CollideOut &co, bool *overflow, mpb_stats *stats) {
+  const auto t_begin = std::chrono::steady_clock::now();
+  const int D = s->img.state_dim, W = s->img.pair_words;
+  const bool want_hits = co.hits != nullptr && co.n_hits != nullptr;
+  const int mode = want_hits ? 2 : (co.pair_bits ? 1 : 0);
+  const long long chunk = (n + 31) / 32 * 32;
+  cudaStream_t st = s->stream;
+  int rc = prepare_work(s, chunk);
+  if (rc != MPB_OK) return rc;
+  const size_t vwords = (size_t)(n + 31) / 32;
+  const size_t q_bytes = (size_t)n * std::max(D, 1) * sizeof(float), v_bytes = vwords * 4, p_bytes = (size_t)n * std::max(W, 1) * 4;
+  const unsigned hit_cap = want_hits ? (unsigned)std::min<int64_t>(std::max<int64_t>(co.hit_cap, 0), (int64_t)n * std::max(s->img.n_pairs, 1)) : 0;
+  const size_t h_bytes = (size_t)hit_cap * sizeof(uint2);
+  SmallGraph *g = nullptr;
+  for (auto &x : s->small_graphs)
+    if (x.n == n && x.mode == mode && x.hit_cap == hit_cap) g = &x;
+  if (!g) {
+    if (s->small_graphs.size() >= 8) {
+      CU(cudaStreamSynchronize(st));
+      SmallGraph &old = s->small_graphs.front();
+      if (old.exec) cudaGraphExecDestroy(old.exec);
+      if (old.graph) cudaGraphDestroy(old.graph);
+      s->small_graphs.erase(s->small_graphs.begin());
+    }
+    // staging: pinned q | verdict | pair mask or hit list | status words; device mirrors from the host-call buffers
+    const size_t need = q_bytes + v_bytes + std::max(p_bytes, h_bytes) + 256;
+    if (need > s->h_small_cap) {
+      CU(cudaStreamSynchronize(st));
+      drop_small_graphs(s);  // they point into the old staging block
+      if (s->h_small) cudaFreeHost(s->h_small);
+      s->h_small = nullptr;
+      s->h_small_cap = 0;
+      CU(cudaHostAlloc((void **)&s->h_small, need * 2, cudaHostAllocDefault));
+      s->h_small_cap = need * 2;
+    }
+    CU(ensure(&s->d_q[0], &s->d_q_cap[0], (size_t)chunk * std::max(D, 1)));
+    CU(ensure(&s->d_verdict[0], &s->d_verdict_cap[0], (size_t)(chunk + 31) / 32));
+    if (mode) CU(ensure(&s->d_pairbits[0], &s->d_pairbits_cap[0], (size_t)chunk * std::max(W, 1)));
+    if (want_hits) CU(ensure(&s->d_hits, &s->d_hits_cap, (size_t)hit_cap + 2));
+    s->small_graphs.push_back(SmallGraph{});
+    g = &s->small_graphs.back();
+    g->n = n; g->mode = mode; g->hit_cap = hit_cap;
+    g->d_q = s->d_q[0]; g->d_v = s->d_verdict[0]; g->d_p = s->d_pairbits[0]; g->d_h = s->d_hits; g->h_base = s->h_small; g->chunk_at = s->chunk; g->img_version = s->img_version;
+    unsigned char *hb = s->h_small;
+    float *h_q = reinterpret_cast<float *>(hb);
+    uint32_t *h_v = reinterpret_cast<uint32_t *>(hb + q_bytes);
+    unsigned char *h_p = hb + q_bytes + v_bytes;
+    unsigned *h_st = reinterpret_cast<unsigned *>(hb + q_bytes + v_bytes + (std::max(p_bytes, h_bytes) + 15) / 16 * 16);
+    CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    rc = MPB_OK;
+    cudaError_t ce = cudaSuccess;
+    do {
+      if (D > 0 && (ce = cudaMemcpyAsync(s->d_q[0], h_q, (size_t)n * D * sizeof(float), cudaMemcpyHostToDevice, st)) != cudaSuccess) break;
+      if ((ce = cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st)) != cudaSuccess) break;
+      if ((ce = cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st)) != cudaSuccess) break;
+      PassOut po;
+      po.dv = s->d_verdict[0];
+      po.dp = mode ? s->d_pairbits[0] : nullptr;
+      if (want_hits) {
+        po.hits = s->d_hits + 1; po.n_hits = reinterpret_cast<unsigned *>(s->d_hits); po.hit_cap = hit_cap;
+        if ((ce = cudaMemsetAsync(po.n_hits, 0, sizeof(unsigned), st)) != cudaSuccess) break;
+      }
+      size_t sync_ev = 0;
+      long long launches = 0;
+      rc = launch_pass(s, nullptr, s->d_q[0], n, po, st, PassEvents{}, &launches, nullptr, &sync_ev);
+      g->launches = launches;
+      if (rc != MPB_OK) break;
+      if ((ce = cudaMemcpyAsync(h_v, po.dv, v_bytes, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+      if (mode == 1 && (ce = cudaMemcpyAsync(h_p, po.dp, (size_t)n * W * 4, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+      if (mode == 2 && hit_cap && (ce = cudaMemcpyAsync(h_p, po.hits, h_bytes, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+      if (mode == 2 && (ce = cudaMemcpyAsync(h_st + 16, po.n_hits, sizeof(unsigned), cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+      if ((ce = cudaMemcpyAsync(h_st, s->wq.totals, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+      ce = cudaMemcpyAsync(h_st + 8, s->wq.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+    } while (0);
+    cudaError_t ee = cudaStreamEndCapture(st, &g->graph);
+    if (rc == MPB_OK && ce == cudaSuccess && ee == cudaSuccess) ee = cudaGraphInstantiate(&g->exec, g->graph, 0);
+    if (rc != MPB_OK || ce != cudaSuccess || ee != cudaSuccess) {
+      if (g->graph) cudaGraphDestroy(g->graph);
+      s->small_graphs.pop_back();
+      cudaGetLastError();
+      if (rc != MPB_OK) return rc;
+      return fail(MPB_ERR_CUDA, std::string("graph capture of the small-batch call: ") + cudaGetErrorString(ce != cudaSuccess ? ce : ee));
+    }
+  }
+  unsigned char *hb = s->h_small;
+  uint32_t *h_v = reinterpret_cast<uint32_t *>(hb + q_bytes);
+  unsigned char *h_p = hb + q_bytes + v_bytes;
+  unsigned *h_st = reinterpret_cast<unsigned *>(hb + q_bytes + v_bytes + (std::max(p_bytes, h_bytes) + 15) / 16 * 16);
+  if (D > 0) memcpy(hb, q, (size_t)n * D * sizeof(float));
+  CU(cudaGraphLaunch(g->exec, st));
+  CU(cudaStreamSynchronize(st));
+  *overflow = h_st[2] != 0;
+  if (!*overflow) {
+    memcpy(co.verdict, h_v, v_bytes);
+    if (mode == 1) memcpy(co.pair_bits, h_p, (size_t)n * W * 4);
+    if (mode == 2) {
+      const unsigned nh = h_st[16];
+      *co.n_hits = nh;
+      memcpy(co.hits, h_p, (size_t)std::min(nh, hit_cap) * sizeof(uint2));
+    }
+  }
+  if (stats) {
+    fill_stats(s, stats, n, reinterpret_cast<unsigned long long *>(h_st + 8), g->launches);
+    stats->host_ms_enqueue = stats->host_ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+  }
+  return MPB_OK;
+}
+
+static bool small_graphs_valid(mpb_scene *s) {
+  for (auto &g : s->small_graphs)
+    if (g.d_q != s->d_q[0] || g.d_v != s->d_verdict[0] || (g.mode && g.d_p != s->d_pairbits[0]) || (g.mode == 2 && g.d_h != s->d_hits) ||
+        g.h_base != s->h_small || g.chunk_at != s->chunk || g.img_version != s->img_version)
+      return false;
+  return true;
+}
+
+static int collide_common(mpb_scene *s, const float *q, int64_t n, const CollideOut &co, mpb_stats *stats, int space, void *stream,
+                          bool may_async) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!co.verdict || (!q && s->img.state_dim > 0)))) return fail(MPB_ERR_INVALID, "null batch pointer");
   if (space != MPB_HOST && space != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
+  if (co.hits && (!co.n_hits || co.hit_cap < 0)) return fail(MPB_ERR_INVALID, "hit list without a counter / negative capacity");
   if (stats) memset(stats, 0, sizeof(*stats));
-  if (n == 0) return MPB_OK;
+  if (n == 0) {
+    if (co.hits && space == MPB_HOST) *co.n_hits = 0;
+    return MPB_OK;
+  }
   CU(cudaSetDevice(s->device));
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  long long chunk = std::min<long long>(kMaxChunk, (n + 31) / 32 * 32);
   if (s->host_chunk == 0) {  // host buffers: H2D sub-range size (FK + cull of one sub-range overlaps the next copy)
     const char *e = getenv("MPB_HOST_CHUNK");
     s->host_chunk = e ? std::max<long long>(64, atoll(e) / 64 * 64) : (1ll << 17);
   }
+  int rc = harvest(s, false);
+  if (rc != MPB_OK) return rc;
+  if (space == MPB_DEVICE && may_async && s->calibrated) return collide_enqueue(s, q, n, co, st, stats);
+  // every blocking protocol below owns the work queues: calls still in flight finish first
+  rc = harvest(s, true);
+  if (rc != MPB_OK) return rc;
+  static const bool small_on = !(getenv("MPB_NO_SMALL_GRAPH") && atoi(getenv("MPB_NO_SMALL_GRAPH")));
+  if (space == MPB_HOST && n <= kSmallBatch && !stream && small_on) {
+    rc = prepare_work(s, (n + 31) / 32 * 32);
+    if (rc != MPB_OK) return rc;
+    if (!small_graphs_valid(s)) { CU(cudaStreamSynchronize(s->stream)); drop_small_graphs(s); }
+    bool overflow = false;
+    rc = collide_small(s, q, n, co, &overflow, stats);
+    if (rc != MPB_OK) return rc;
+    if (!overflow) return MPB_OK;
+  }
+  long long chunk = std::min<long long>(max_chunk_for(s), (n + 31) / 32 * 32);
   for (int attempt = 0; attempt < 12; attempt++) {
     bool overflow = false;
-    int rc = collide_attempt(s, q, n, verdict_bits, pair_bits, space, st, chunk, &overflow, stats);
+    rc = collide_attempt(s, q, n, co, space, st, chunk, &overflow, stats);
     if (rc != MPB_OK) return rc;
     if (!overflow) return MPB_OK;
     chunk = std::max<long long>(32, (chunk / 4 + 31) / 32 * 32);  // queue overflowed: smaller passes, exact redo
   }
   return fail(MPB_ERR_CAPACITY, "work queue overflow persists at the minimum chunk size");
+}
+
+extern "C" int mpb_collide_batch(mpb_scene *s, const float *q, int64_t n, uint32_t *verdict_bits, uint32_t *pair_bits,
+                                 mpb_stats *stats, int space, void *stream) {
+  CollideOut co;
+  co.verdict = verdict_bits;
+  co.pair_bits = pair_bits;
+  return collide_common(s, q, n, co, stats, space, stream, true);
+}
+
+extern "C" int mpb_collide_batch_hits(mpb_scene *s, const float *q, int64_t n, uint32_t *verdict_bits, uint32_t *hits, int64_t hit_cap,
+                                      uint32_t *n_hits, mpb_stats *stats, int space, void *stream) {
+  if (!hits || !n_hits) return fail(MPB_ERR_INVALID, "null hit list / counter");
+  CollideOut co;
+  co.verdict = verdict_bits;
+  co.hits = hits;
+  co.hit_cap = hit_cap;
+  co.n_hits = n_hits;
+  return collide_common(s, q, n, co, stats, space, stream, true);
 }
 
 extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *poses, int space, void *stream) {
@@ -1406,7 +1943,11 @@ extern "C" int mpb_check_motion_batch(mpb_scene *s, const mpb_space_desc *space,
   fill_valid_bits_kernel<<<(int)((vwords + 255) / 256), 256, 0, st>>>(dvalid, n_edges);
   CU(cudaGetLastError());
   mpb_stats inner;
-  rc = mpb_collide_batch(s, d_states, (int64_t)total, d_verdict, nullptr, &inner, MPB_DEVICE, (void *)st);
+  {
+    CollideOut co;
+    co.verdict = d_verdict;
+    rc = collide_common(s, d_states, (int64_t)total, co, &inner, MPB_DEVICE, (void *)st, false);  // blocking: overflow is redone
+  }
   if (rc != MPB_OK) return rc;
   motion_reduce_kernel<<<(int)((total + 255u) / 256u), 256, 0, st>>>(d_verdict, d_owner, total, dvalid);
   CU(cudaGetLastError());
@@ -1431,6 +1972,7 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   if (n_queries > (1 << 20)) return fail(MPB_ERR_CAPACITY, "too many queries in one call");
   const auto t_begin = std::chrono::steady_clock::now();
   CU(cudaSetDevice(s->device));
+  if (int hrc = harvest(s, true)) return hrc;  // device-pointer collide calls in flight share the work queues
   cudaStream_t st = s->stream;
   DevBufs bufs(s);
   DevSpace dsp;
@@ -1510,7 +2052,9 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
     rrt_advance_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
     motion_expand_kernel<<<(Q * S + 255) / 256, 256, 0, st>>>(dsp.sp, r.edge_a, r.edge_b, (long long)Q * S, nullptr, nullptr, smax, d_states, nullptr);
     *launches += 2;
-    return launch_pass(s, nullptr, d_states, n_states, d_verdict, nullptr, st, nullptr, launches, nullptr, &sync_ev);
+    PassOut po;
+    po.dv = d_verdict;
+    return launch_pass(s, nullptr, d_states, n_states, po, st, PassEvents{}, launches, nullptr, &sync_ev);
   };
   // the round has fixed launch shapes: capture it once, replay it
   cudaGraph_t graph = nullptr;
@@ -1607,17 +2151,13 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
   if (s->img.expand_bin >= 0 || s->img.expand2_bin >= 0)
     return fail(MPB_ERR_UNSUPPORTED, "distance to mesh / octree objects is not supported by this build yet");
   CU(cudaSetDevice(s->device));
+  if (int hrc = harvest(s, true)) return hrc;
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   const auto t_begin = std::chrono::steady_clock::now();
   const int D = s->img.state_dim;
   const bool host = space == MPB_HOST;
-  static bool attr_set = false;
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
-  if (!attr_set && s->smem_verts) {
-    CU(cudaFuncSetAttribute(distance_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vsm, 16)));
-    attr_set = true;
-  }
-  if (s->smem_verts) CU(cudaFuncSetAttribute(distance_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(vsm, 16)));
+  if (s->smem_verts) CU(raise_dyn_smem((const void *)distance_kernel<true>, s->device, 1, std::max<size_t>(vsm, 16)));
   int per_sm = 0;
   if (s->smem_verts) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, distance_kernel<true>, 256, vsm));
   else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, distance_kernel<false>, 256, 0));
@@ -1658,9 +2198,9 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
     CU(cudaEventRecord(e0, st));
     if (s->img.n_pairs > 0) {
       const int cblocks = (int)((m + 127) / 128);
-      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, dq, m, s->d_pose, s->pose_ld, s->d_obb);
+      fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, s->d_qconst, dq, m, s->d_pose, s->pose_ld, s->d_obb);
       sphere_kernel<1, 0, 0><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
-      dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, nullptr, nullptr);
+      dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, HitOut{});
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, -1, (unsigned)dblocks * 8u, s->sq_cap);
       scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));

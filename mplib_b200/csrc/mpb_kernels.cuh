@@ -67,9 +67,37 @@ struct WorkQ {
   unsigned int cap;
 };
 
+// Where the kernels of one pass report a colliding (configuration, pair): the verdict word, optionally the dense pair
+// mask of the pass, optionally the call-wide sparse hit list (the first setter of a mask bit appends the entry, so
+// several leaf items of one pair give one entry).
+struct HitOut {
+  unsigned int *verdict;    // [ceil(m / 32)] words of this pass
+  unsigned int *pair_bits;  // [m][pair_words] of this pass, or nullptr
+  uint2 *hits;              // (configuration index within the call, pair) entries, or nullptr (needs pair_bits)
+  unsigned int *n_hits;     // entries appended so far (may run past hit_cap: the list is then truncated)
+  unsigned int hit_cap;
+  unsigned int cfg0;        // index of this pass's first configuration within the call
+  int pair_words;
+};
+__device__ __forceinline__ void report_hit(const HitOut &o, unsigned cfg, int p) {
+  atomicOr(&o.verdict[cfg >> 5], 1u << (cfg & 31));
+  if (o.pair_bits) {
+    const unsigned bit = 1u << (p & 31);
+    const unsigned old = atomicOr(&o.pair_bits[(size_t)cfg * o.pair_words + (p >> 5)], bit);
+    if (o.hits && !(old & bit)) {
+      const unsigned k = atomicAdd(o.n_hits, 1u);
+      if (k < o.hit_cap) o.hits[k] = make_uint2(o.cfg0 + cfg, (unsigned)p);
+    }
+  }
+}
+// this (configuration, pair) -- or, without a pair mask, this configuration -- is already known to collide
+__device__ __forceinline__ bool hit_known(const HitOut &o, unsigned cfg, int p) {
+  return o.pair_bits ? ((o.pair_bits[(size_t)cfg * o.pair_words + (p >> 5)] >> (p & 31)) & 1u) : ((o.verdict[cfg >> 5] >> (cfg & 31)) & 1u);
+}
+
 #define MPB_EPS FLT_EPSILON
 #define MPB_MPR_TOL 1e-6f
-#define MPB_MPR_MAX_ITERS 96
+#define MPB_MPR_MAX_ITERS 500  // libccd: GJKSolver_libccd::max_collision_iterations [upstream]
 #define MPB_UNIT_ITEMS 128   // most items a warp owns at a time in the narrowphase (scan_bins_kernel picks 2..128)
 #define MPB_COOP_MAX 10      // busy lanes at or below which a warp evaluates hull supports cooperatively
 #define MPB_STAGE_CHUNK 256  // staging slots a warp reserves per atomic (>= 32)
@@ -266,7 +294,7 @@ struct FkTab {
   FkObjC o[MPB_MAX_DYN];
 };
 __global__ void __launch_bounds__(128) fk_table_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
-                                                       const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
+                                                       const float *__restrict__ qconst, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
                                                        float4 *__restrict__ obb) {
   // per warp: one object's 32 OBB rows, transposed for full-sector stores.  Quaternions at float4 [0, 32), translations
   // at [36, 68): the 4-word shift puts the two halves of a quarter-warp's interleaved read on disjoint banks
@@ -282,7 +310,8 @@ __global__ void __launch_bounds__(128) fk_table_kernel(const __grid_constant__ S
   const float *qrow = q + ic * img.state_dim;
   for (int j = 0; j < img.n_joints; j++) {
     const DevJoint &J = tab.j[j];
-    const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
+    const float qj = J.slot >= 0 ? qrow[J.slot] : __ldg(qconst + j);  // q_base values live in a device table: changing them
+                                                                      // leaves the by-value records (and captured graphs) alone
     if (J.parent == 0) cur = joint_step(J, nullptr, qj);
     else if (J.pjslot >= 0) { const Xf par = pose_joint(pose, ld, jbase + J.pjslot * 12, i); cur = joint_step(J, &par, qj); }
     else cur = joint_step(J, &cur, qj);
@@ -566,8 +595,7 @@ __global__ void __launch_bounds__(128) sphere_blk_kernel(const __grid_constant__
 
 template <int MODE>
 __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
-                                                    unsigned sq_cap, WorkQ wq, unsigned int *__restrict__ verdict_bits,
-                                                    unsigned int *__restrict__ pair_bits) {
+                                                    unsigned sq_cap, WorkQ wq, HitOut out) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
   __shared__ unsigned s_bins[MPB_SMEM_BINS];  // per-block bin counts, flushed once at the end
@@ -627,8 +655,7 @@ __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *
           const float rs = 0.999f * (ha.w + hb.w);
           if (fmaf(e0, e0, fmaf(e1, e1, e2 * e2)) < rs * rs) {
             keep = false;
-            atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
-            if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
+            report_hit(out, cfg, p);
           }
         }
       }
@@ -681,6 +708,12 @@ __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *
       if (s_bins[b]) atomicAdd(&wq.bin_count[b], s_bins[b]);
 }
 #undef POSE
+
+// start of a pass (or of its second narrowphase round): bin counts, staged-item and survivor counters back to zero
+__global__ void pass_reset_kernel(WorkQ wq, int n_bins) {
+  for (int b = threadIdx.x; b < n_bins; b += blockDim.x) wq.bin_count[b] = 0;
+  if (threadIdx.x == 0) { wq.totals[0] = 0; wq.totals[6] = 0; }
+}
 
 __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bin2, unsigned n_warps, unsigned sq_cap) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -901,8 +934,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 // ccdMPRIntersect [upstream libccd v2.1 mpr.c] in the frame of shape A; B sits at (R, t).
 // Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
 template <bool SMEM>
-__global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
-                                                     unsigned int *__restrict__ pair_bits, int n_bins, int round) {
+__global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
@@ -986,9 +1018,7 @@ __global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, 
               cBl = v3((a.x + b.x + c.x) * (1.f / 3.f), (a.y + b.y + c.y) * (1.f / 3.f), (a.z + b.z + c.z) * (1.f / 3.f));
             } else cBl = v3(a.x, a.y, a.z);
             // early exit: this (configuration, pair) is already known to collide
-            const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
-                                         : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
-            busy_ok = !known;
+            busy_ok = !hit_known(out, (unsigned)cfg, p);
           }
           v0 = cA - (rot(R, cBl) + t);
           if (is_zero(v0.x) && is_zero(v0.y) && is_zero(v0.z)) v0.x += 10.f * MPB_EPS;
@@ -1093,10 +1123,7 @@ __global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, 
       if (done) {
         busy = false;
         it_sum += (unsigned)iters;
-        if (hit) {
-          atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
-          if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
-        }
+        if (hit) report_hit(out, (unsigned)cfg, p);
       }
     }
   }
@@ -1164,8 +1191,7 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fm
 // lets the lanes that hold surviving leaves test / emit their primitives.  No divergence inside the 15-axis test and
 // a short critical path even for small batches (a planning round); when the stack runs nearly full the warp pops
 // one node per trip (depth-first), which bounds the growth by the tree depth.
-__global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
-                                                     unsigned int *__restrict__ pair_bits) {
+__global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, HitOut out) {
   __shared__ int s_stack[4][MPB_EXP_STACK];
   const int eb = img.expand_bin;
   if (eb < 0) return;
@@ -1184,8 +1210,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
     if (lane < 4 && it0 + lane < end) {
       my_cfg = wq.icfg[it0 + lane];
       my_p = wq.ipair[it0 + lane];
-      my_known = pair_bits ? ((pair_bits[(size_t)my_cfg * img.pair_words + (my_p >> 5)] >> (my_p & 31)) & 1u)
-                           : ((verdict_bits[my_cfg >> 5] >> (my_cfg & 31)) & 1u);
+      my_known = hit_known(out, (unsigned)my_cfg, my_p);
     }
     for (int sub = 0; sub < 4; sub++) {
     const unsigned it = it0 + sub;
@@ -1235,7 +1260,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
     int sp = 1;
     if (lane == 0) stack[0] = B.voff;
     __syncwarp();
-    bool hit = false;
+    bool hit = false, dropped = false;
     while (sp > 0) {
       const int take = sp > MPB_EXP_STACK - 64 ? 1 : min(sp, 32);
       int node = -1;
@@ -1255,7 +1280,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
       if (inner) {
         const int pos = sp + 2 * __popc(im & ((1u << lane) - 1u));
         if (pos + 1 < MPB_EXP_STACK) { stack[pos] = nd.left; stack[pos + 1] = nd.right; }
-        else atomicAdd(&wq.counters[2], 1ull);  // dropped subtree: reported as a capped item, never silent
+        else { atomicAdd(&wq.counters[2], 1ull); dropped = true; }  // dropped subtree: counted, and the item reads as colliding
       }
       sp = min(sp + 2 * __popc(im), MPB_EXP_STACK);  // (a frontier beyond the stack would need a tree deeper than ~60)
       __syncwarp();
@@ -1307,12 +1332,9 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
           }
         }
       }
-      if (__any_sync(FULL, lhit)) { hit = true; break; }
+      if (__any_sync(FULL, lhit || dropped)) { hit = true; break; }  // a subtree that could not be held: conservative verdict
     }
-    if (hit && lane == 0) {
-      atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
-      if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
-    }
+    if (hit && lane == 0) report_hit(out, (unsigned)cfg, p);
     __syncwarp();
     }  // sub-items of the ticket
   }
@@ -1374,8 +1396,7 @@ __device__ __forceinline__ bool box_tri_hit(V3 c, V3 h, V3 p0, V3 p1, V3 p2) {
   return true;
 }
 
-__global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, unsigned int *__restrict__ verdict_bits,
-                                                      unsigned int *__restrict__ pair_bits) {
+__global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, HitOut out) {
   __shared__ int2 s_stack[4][MPB_EXP2_STACK];
   const int eb = img.expand2_bin;
   if (eb < 0) return;
@@ -1389,9 +1410,7 @@ __global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, un
     it = first + __shfl_sync(FULL, it, 0);
     if (it >= end) break;
     const int cfg = wq.icfg[it], p = wq.ipair[it];
-    const bool known = pair_bits ? ((pair_bits[(size_t)cfg * img.pair_words + (p >> 5)] >> (p & 31)) & 1u)
-                                 : ((verdict_bits[cfg >> 5] >> (cfg & 31)) & 1u);
-    if (known) continue;
+    if (hit_known(out, (unsigned)cfg, p)) continue;
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // mesh
     const DevObject &B = img.objs[pr.b];  // mesh or octree
@@ -1404,7 +1423,7 @@ __global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, un
     int sp = 1;
     if (lane == 0) stack[0] = make_int2(A.voff, B.voff);
     __syncwarp();
-    bool hit = false;
+    bool hit = false, dropped = false;
     while (sp > 0) {
       const int take = sp > MPB_EXP2_STACK - 64 ? 1 : min(sp, 32);
       int2 np = make_int2(-1, -1);
@@ -1433,7 +1452,7 @@ __global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, un
         if (pos + 1 < MPB_EXP2_STACK) {
           stack[pos] = split_a ? make_int2(na.left, np.y) : make_int2(np.x, nb.left);
           stack[pos + 1] = split_a ? make_int2(na.right, np.y) : make_int2(np.x, nb.right);
-        } else atomicAdd(&wq.counters[2], 1ull);  // dropped subtree pair: reported as a capped item, never silent
+        } else { atomicAdd(&wq.counters[2], 1ull); dropped = true; }  // dropped subtree pair: counted, and the item reads as colliding
       }
       sp = min(sp + 2 * __popc(im), MPB_EXP2_STACK);
       __syncwarp();
@@ -1457,12 +1476,9 @@ __global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, un
           }
         }
       }
-      if (__any_sync(FULL, lhit)) { hit = true; break; }
+      if (__any_sync(FULL, lhit || dropped)) { hit = true; break; }
     }
-    if (hit && lane == 0) {
-      atomicOr(&verdict_bits[cfg >> 5], 1u << (cfg & 31));
-      if (pair_bits) atomicOr(&pair_bits[(size_t)cfg * img.pair_words + (p >> 5)], 1u << (p & 31));
-    }
+    if (hit && lane == 0) report_hit(out, (unsigned)cfg, p);
     __syncwarp();
   }
 }

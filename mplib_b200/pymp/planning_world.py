@@ -273,10 +273,20 @@ class PlanningWorld:
         return gt, geom._param(), -1
 
     def _structure_sig(self):
+        """What forces a re-compile: the set of articulations / objects / attachments and their geometry.  Poses are not
+        part of it (``_pose_sig``): a moved obstacle or a re-posed attached body is an in-place update."""
         arts = tuple((n, id(a), a.version, n in self.planned) for n, a in sorted(self.articulations.items()))
-        objs = tuple((n, id(o), o.T.tobytes()) for n, o in self.normal_objects.items())
-        att = tuple((n, id(bd.attached_articulation), bd.attached_link_id, bd.pose.tobytes()) for n, bd in self.attached_bodies.items())
+        objs = tuple((n, id(o), id(o.geometry), self._geom_sig(o.geometry)) for n, o in self.normal_objects.items())
+        att = tuple((n, id(bd.attached_articulation), bd.attached_link_id) for n, bd in self.attached_bodies.items())
         return (self._version, arts, objs, att)
+
+    @staticmethod
+    def _geom_sig(g):
+        return tuple(np.asarray(g._param(), dtype=np.float64).tolist()) if 0 < g.gtype < GEOM_MESH else ()
+
+    def _pose_sig(self):
+        return tuple((n, (self.attached_bodies[n].pose if n in self.attached_bodies else o.T).tobytes())
+                     for n, o in self.normal_objects.items())
 
     def compile(self):
         """Flatten the world (see SceneBuilder).  Returns (SceneDesc, candidate pairs with metadata)."""
@@ -352,6 +362,8 @@ class PlanningWorld:
                                  fm2.collision_link_names[j]))
             for sn, so in scene_obj.items():
                 cand.append((bo, so, "others", "attach_sceneobject", bn, sn, bn, sn))
+        self._obj_index = dict(scene_obj)
+        self._obj_index.update(att_obj)
         return b, cand
 
     def _admitted(self, cand):
@@ -372,11 +384,23 @@ class PlanningWorld:
                 b.add_pair(p[0], p[1], p[3])
             desc = b.finish()
             self._cache = c = {"sig": sig, "dev": DeviceScene(desc, self.device), "cand": cand, "pairs": pairs,
-                               "acm": self.acm.version, "q": self._q_sig()}
+                               "acm": self.acm.version, "q": self._q_sig(), "pose": self._pose_sig(), "obj_index": self._obj_index}
         elif c["acm"] != self.acm.version:
             pairs = self._admitted(c["cand"])
             c["dev"].set_pairs([p[0] for p in pairs], [p[1] for p in pairs], [p[3] for p in pairs])
             c["pairs"], c["acm"] = pairs, self.acm.version
+        ps = self._pose_sig()
+        if c["pose"] != ps:  # CollisionObject.set_transformation / a re-posed attached body: in-place update, no re-compile
+            old = dict(c["pose"])
+            idx, loc = [], []
+            for n, t in ps:
+                if old.get(n) != t:
+                    T = self.attached_bodies[n].pose if n in self.attached_bodies else self.normal_objects[n].T
+                    idx.append(c["obj_index"][n])
+                    loc.append(np.asarray(T, dtype=np.float64)[:3, :4].reshape(12))
+            if idx:
+                c["dev"].update_objects(idx, np.stack(loc))
+            c["pose"] = ps
         if c["q"] != self._q_sig():
             qb = [self.articulations[n].q_model_order() for n in sorted(self.articulations)]
             c["dev"].set_q_base(np.concatenate(qb) if qb else np.zeros(0))

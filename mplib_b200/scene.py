@@ -74,6 +74,7 @@ class MpbStats(C.Structure):
         ("host_ms_total", C.c_float),
         ("gpu_ms_fk", C.c_float),
         ("fk_bytes_per_state", C.c_int32),
+        ("async_pending", C.c_int32),
     ]
 
     def as_dict(self):
@@ -144,6 +145,20 @@ class SceneDesc:
         kw = {k: getattr(self, k) for k in self._ARRAYS}
         kw.update(q_base=np.asarray(q_base, dtype=np.float64), link_names=self.link_names,
                   object_names=self.object_names, pair_kinds=self.pair_kinds)
+        return SceneDesc(**kw)
+
+    def with_objects(self, idx, obj_local=None, obj_param=None):
+        """Copy with the pose (row-major 3x4) / parameters of the objects ``idx`` replaced (mpb_scene_update_objects)."""
+        kw = {k: getattr(self, k) for k in self._ARRAYS}
+        if obj_local is not None:
+            loc = self.obj_local.reshape(-1, 12).copy()
+            loc[np.asarray(idx, dtype=np.int64)] = np.asarray(obj_local, dtype=np.float64).reshape(-1, 12)
+            kw["obj_local"] = loc
+        if obj_param is not None:
+            par = self.obj_param.reshape(-1, 4).copy()
+            par[np.asarray(idx, dtype=np.int64)] = np.asarray(obj_param, dtype=np.float64).reshape(-1, 4)
+            kw["obj_param"] = par
+        kw.update(link_names=self.link_names, object_names=self.object_names, pair_kinds=self.pair_kinds)
         return SceneDesc(**kw)
 
     def _ptr(self, name, ctype):

@@ -180,6 +180,7 @@ typedef struct {
   xf_t T;            /* world pose */
   double a, b, c;    /* sphere r | box half sides | capsule/cylinder r, half height */
   const double *verts; int nverts; /* convex */
+  const int *nbr;                  /* convex, accelerated leg only: vertex adjacency (CSR: off[nverts + 1], then neighbours) */
   double center_local[3];          /* convex interior point (vertex mean), fcl::Convex ctor [upstream] */
   double tri[9];                   /* triangle vertices in the frame T */
 } shape_t;
@@ -233,7 +234,28 @@ static void shape_support(const shape_t *s, const double *dir_w, double *out_w) 
     } break;
     case MPB_GEOM_CONVEX: {
       int best = 0; double bd = dot3(s->verts, dir);
-      for (int i = 1; i < s->nverts; i++) { double t = dot3(s->verts + 3 * i, dir); if (t > bd) { bd = t; best = i; } }
+      if (s->nbr && s->nverts > 32) {
+        /* [upstream FCL 0.7.0 geometry/shape/convex-inl.h] Convex::findExtremeVertex on hulls with more than 32 vertices:
+         * start at vertex 0, walk to any not-yet-visited neighbour that is at least as extreme, until none is.  On a
+         * convex hull this ends on a global maximum (same vertex as the scan above except on exact ties). */
+        static __thread unsigned *stamp = NULL; static __thread int stamp_n = 0; static __thread unsigned cur = 0;
+        if (stamp_n < s->nverts) { free(stamp); stamp_n = s->nverts; stamp = (unsigned *)calloc((size_t)stamp_n, sizeof(unsigned)); cur = 0; }
+        if (++cur == 0) { memset(stamp, 0, sizeof(unsigned) * (size_t)stamp_n); cur = 1; }
+        stamp[0] = cur;
+        int keep = 1;
+        while (keep) {
+          keep = 0;
+          const int n0 = s->nbr[best], n1 = s->nbr[best + 1];
+          for (int k = n0; k < n1; k++) {
+            const int j = s->nbr[s->nverts + 1 + k];
+            if (stamp[j] == cur) continue;
+            stamp[j] = cur;
+            const double t = dot3(s->verts + 3 * j, dir);
+            if (t >= bd) { keep = 1; best = j; bd = t; }
+          }
+        }
+      } else
+        for (int i = 1; i < s->nverts; i++) { double t = dot3(s->verts + 3 * i, dir); if (t > bd) { bd = t; best = i; } }
       copy3(v, s->verts + 3 * best);
     } break;
     case ORC_TRI: {
@@ -694,7 +716,229 @@ static int octree_mesh(const mpb_scene_desc *d, int oo, const xf_t *To, int om, 
   return 0;
 }
 
+/* ------------------------------------------------------------------ hierarchical leg (the TIMED CPU baseline)
+ * FCL does not test every leaf: ::fcl::collide descends a BVHModel<OBBRSS> (load_mesh_as_BVH, src/urdf_utils.cpp:135-154)
+ * or the octree (addPointCloud, src/planning_world.cpp:101-110) and stops at the first hit (num_max_contacts = 1), and
+ * fcl::Convex finds its support vertex by walking the hull's edges.  The functions below do that work: an AABB tree per
+ * mesh / per occupied-voxel set (median split, one primitive per leaf), node-vs-shape-OBB overlap for the descent
+ * (role of OBBRSS::overlap / OcTreeSolver's obb1.overlap(obb2)), the SAME leaf tests as the exhaustive functions above,
+ * early exit.  A pruned leaf cannot intersect (the bounds are conservative, padded by ORC_PRUNE_PAD), so the verdict of
+ * every pair equals the exhaustive leg's -- tests/test_oracle_accel.py checks that bit for bit.  The exhaustive leg
+ * stays the CHECKER; this one is what bench.py times. */
+#define ORC_PRUNE_PAD 1e-6
+typedef struct { double c[3], h[3]; int left, right; } orc_node; /* inner: children; leaf: left = ~primitive, right = 1 */
+typedef struct { orc_node *nodes; int n_nodes, cap; } orc_bvh;
+typedef struct orc_accel {
+  int n_meshes, n_octrees, n_hulls;
+  orc_bvh *mesh, *oct;
+  int **hull_nbr;        /* per hull: CSR adjacency, NULL for hulls of <= 32 vertices */
+  double *hull_box;      /* per hull: centre[3], half[3] of the vertex AABB (hull frame) */
+} orc_accel;
+
+typedef struct { double lo[3], hi[3]; int prim; } orc_prim_box;
+static int g_sort_axis;
+static int cmp_prim_box(const void *a, const void *b) {
+  const orc_prim_box *x = (const orc_prim_box *)a, *y = (const orc_prim_box *)b;
+  double cx = x->lo[g_sort_axis] + x->hi[g_sort_axis], cy = y->lo[g_sort_axis] + y->hi[g_sort_axis];
+  return cx < cy ? -1 : (cx > cy ? 1 : (x->prim - y->prim));
+}
+static int bvh_build(orc_bvh *t, orc_prim_box *pb, int first, int count) {
+  if (t->n_nodes == t->cap) { t->cap = t->cap ? 2 * t->cap : 1024; t->nodes = (orc_node *)realloc(t->nodes, sizeof(orc_node) * (size_t)t->cap); }
+  int me = t->n_nodes++;
+  double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX}, clo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, chi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+  for (int i = first; i < first + count; i++) for (int a = 0; a < 3; a++) {
+    if (pb[i].lo[a] < lo[a]) lo[a] = pb[i].lo[a];
+    if (pb[i].hi[a] > hi[a]) hi[a] = pb[i].hi[a];
+    double cc = 0.5 * (pb[i].lo[a] + pb[i].hi[a]); if (cc < clo[a]) clo[a] = cc; if (cc > chi[a]) chi[a] = cc;
+  }
+  for (int a = 0; a < 3; a++) { t->nodes[me].c[a] = 0.5 * (lo[a] + hi[a]); t->nodes[me].h[a] = 0.5 * (hi[a] - lo[a]) + ORC_PRUNE_PAD; }
+  if (count == 1) { t->nodes[me].left = ~pb[first].prim; t->nodes[me].right = 1; return me; }
+  int ax = 0; if (chi[1] - clo[1] > chi[ax] - clo[ax]) ax = 1; if (chi[2] - clo[2] > chi[ax] - clo[ax]) ax = 2;
+  g_sort_axis = ax;
+  qsort(pb + first, (size_t)count, sizeof(orc_prim_box), cmp_prim_box);
+  int mid = count / 2;
+  int l = bvh_build(t, pb, first, mid);
+  int r = bvh_build(t, pb, first + mid, count - mid);
+  t->nodes[me].left = l; t->nodes[me].right = r;
+  return me;
+}
+
+void orc_accel_destroy(orc_accel *ac) {
+  if (!ac) return;
+  for (int m = 0; m < ac->n_meshes; m++) free(ac->mesh[m].nodes);
+  for (int t = 0; t < ac->n_octrees; t++) free(ac->oct[t].nodes);
+  for (int h = 0; h < ac->n_hulls; h++) free(ac->hull_nbr[h]);
+  free(ac->mesh); free(ac->oct); free(ac->hull_nbr); free(ac->hull_box); free(ac);
+}
+
+orc_accel *orc_accel_create(const mpb_scene_desc *d) {
+  orc_accel *ac = (orc_accel *)calloc(1, sizeof(orc_accel));
+  ac->n_meshes = d->n_meshes; ac->n_octrees = d->n_octrees; ac->n_hulls = d->n_hulls;
+  ac->mesh = (orc_bvh *)calloc((size_t)(d->n_meshes > 0 ? d->n_meshes : 1), sizeof(orc_bvh));
+  ac->oct = (orc_bvh *)calloc((size_t)(d->n_octrees > 0 ? d->n_octrees : 1), sizeof(orc_bvh));
+  ac->hull_nbr = (int **)calloc((size_t)(d->n_hulls > 0 ? d->n_hulls : 1), sizeof(int *));
+  ac->hull_box = (double *)calloc((size_t)(d->n_hulls > 0 ? d->n_hulls : 1) * 6, sizeof(double));
+  for (int m = 0; m < d->n_meshes; m++) {
+    const double *V = d->mesh_verts + 3 * d->mesh_vert_off[m];
+    const int32_t *Tr = d->mesh_tris + 3 * d->mesh_tri_off[m];
+    int nt = d->mesh_tri_off[m + 1] - d->mesh_tri_off[m];
+    if (nt <= 0) continue;
+    orc_prim_box *pb = (orc_prim_box *)malloc(sizeof(orc_prim_box) * (size_t)nt);
+    for (int t = 0; t < nt; t++) {
+      pb[t].prim = t;
+      for (int a = 0; a < 3; a++) {
+        double x0 = V[3 * Tr[3 * t] + a], x1 = V[3 * Tr[3 * t + 1] + a], x2 = V[3 * Tr[3 * t + 2] + a];
+        pb[t].lo[a] = fmin(x0, fmin(x1, x2)); pb[t].hi[a] = fmax(x0, fmax(x1, x2));
+      }
+    }
+    bvh_build(&ac->mesh[m], pb, 0, nt);
+    free(pb);
+  }
+  for (int t = 0; t < d->n_octrees; t++) {
+    double res = d->oct_res[t];
+    const int32_t *C = d->oct_cells + 3 * d->oct_cell_off[t];
+    int nc = d->oct_cell_off[t + 1] - d->oct_cell_off[t];
+    if (nc <= 0) continue;
+    orc_prim_box *pb = (orc_prim_box *)malloc(sizeof(orc_prim_box) * (size_t)nc);
+    for (int i = 0; i < nc; i++) { pb[i].prim = i; for (int a = 0; a < 3; a++) { pb[i].lo[a] = C[3 * i + a] * res; pb[i].hi[a] = (C[3 * i + a] + 1) * res; } }
+    bvh_build(&ac->oct[t], pb, 0, nc);
+    free(pb);
+  }
+  for (int h = 0; h < d->n_hulls; h++) {
+    int v0 = d->hull_vert_off[h], nv = d->hull_vert_off[h + 1] - v0;
+    const double *V = d->hull_verts + 3 * v0;
+    double lo[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, hi[3] = {-DBL_MAX, -DBL_MAX, -DBL_MAX};
+    for (int i = 0; i < nv; i++) for (int a = 0; a < 3; a++) { if (V[3 * i + a] < lo[a]) lo[a] = V[3 * i + a]; if (V[3 * i + a] > hi[a]) hi[a] = V[3 * i + a]; }
+    for (int a = 0; a < 3; a++) { ac->hull_box[6 * h + a] = 0.5 * (lo[a] + hi[a]); ac->hull_box[6 * h + 3 + a] = 0.5 * (hi[a] - lo[a]); }
+    if (nv <= 32) continue;
+    /* adjacency from the triangle faces (each edge listed once per endpoint) */
+    const int32_t *F = d->hull_faces + 3 * d->hull_face_off[h];
+    int nf = d->hull_face_off[h + 1] - d->hull_face_off[h];
+    unsigned char *adj = (unsigned char *)calloc((size_t)nv * (size_t)nv, 1);
+    for (int f = 0; f < nf; f++) for (int e = 0; e < 3; e++) { int i = F[3 * f + e], j = F[3 * f + (e + 1) % 3]; if (i >= 0 && i < nv && j >= 0 && j < nv && i != j) { adj[(size_t)i * nv + j] = 1; adj[(size_t)j * nv + i] = 1; } }
+    int total = 0; for (size_t k = 0; k < (size_t)nv * nv; k++) total += adj[k];
+    int *nbr = (int *)malloc(sizeof(int) * (size_t)(nv + 1 + total));
+    int off = 0, connected = 1;
+    for (int i = 0; i < nv; i++) {
+      nbr[i] = off;
+      for (int j = 0; j < nv; j++) if (adj[(size_t)i * nv + j]) nbr[nv + 1 + off++] = j;
+      if (off == nbr[i]) connected = 0; /* a vertex no face references: the walk could miss it -> keep the scan */
+    }
+    nbr[nv] = off;
+    free(adj);
+    if (connected) ac->hull_nbr[h] = nbr; else free(nbr);
+  }
+  return ac;
+}
+
+/* the shape's OBB in its own frame: centre + half extents (primitives: FCL computeBV<OBB>; convex: vertex AABB) */
+static void shape_local_box(const mpb_scene_desc *d, const orc_accel *ac, int o, double *c, double *h) {
+  const double *p = d->obj_param + 4 * o;
+  c[0] = c[1] = c[2] = 0;
+  switch (d->obj_type[o]) {
+    case MPB_GEOM_SPHERE: h[0] = h[1] = h[2] = p[0]; break;
+    case MPB_GEOM_BOX: h[0] = 0.5 * p[0]; h[1] = 0.5 * p[1]; h[2] = 0.5 * p[2]; break;
+    case MPB_GEOM_CAPSULE: h[0] = h[1] = p[0]; h[2] = 0.5 * p[1] + p[0]; break;
+    case MPB_GEOM_CYLINDER: h[0] = h[1] = p[0]; h[2] = 0.5 * p[1]; break;
+    case MPB_GEOM_CONVEX: { const double *b = ac->hull_box + 6 * d->obj_geom[o]; copy3(c, b); copy3(h, b + 3); } break;
+    default: h[0] = h[1] = h[2] = 1e30; break;
+  }
+}
+/* box A (axis-aligned in its frame, centre ca, half ha) vs box B (axes = columns of R, centre cb in A's frame, half hb) */
+static int boxes_disjoint(const double *ca, const double *ha, const double *R, const double *cb, const double *hb) {
+  double t[3] = {cb[0] - ca[0], cb[1] - ca[1], cb[2] - ca[2]}, Q[9];
+  for (int i = 0; i < 9; i++) Q[i] = fabs(R[i]) + 1e-12;
+  for (int i = 0; i < 3; i++) if (fabs(t[i]) > ha[i] + hb[0] * Q[3 * i] + hb[1] * Q[3 * i + 1] + hb[2] * Q[3 * i + 2]) return 1;
+  for (int j = 0; j < 3; j++) {
+    double tj = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
+    if (fabs(tj) > hb[j] + ha[0] * Q[j] + ha[1] * Q[3 + j] + ha[2] * Q[6 + j]) return 1;
+  }
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    double lhs = fabs(t[i2] * R[3 * i1 + j] - t[i1] * R[3 * i2 + j]);
+    double rhs = ha[i1] * Q[3 * i2 + j] + ha[i2] * Q[3 * i1 + j] + hb[j1] * Q[3 * i + j2] + hb[j2] * Q[3 * i + j1];
+    if (lhs > rhs) return 1;
+  }
+  return 0;
+}
+static void xf_inv_mul_(xf_t *o, const xf_t *a, const xf_t *b) { /* a^-1 b */
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { double v = 0; for (int k = 0; k < 3; k++) v += a->R[3 * k + i] * b->R[3 * k + j]; o->R[3 * i + j] = v; }
+  double dd[3]; sub3(dd, b->p, a->p); xf_rot_t(o->p, a, dd);
+}
+#define ORC_STACK 256
+/* shape (object os at Ts) against the tree of object ob (mesh or octree) at Tb */
+static int tree_shape_h(const mpb_scene_desc *d, const orc_accel *ac, int ob, const xf_t *Tb, int os, const xf_t *Ts) {
+  const int is_oct = d->obj_type[ob] == MPB_GEOM_OCTREE;
+  const int g = d->obj_geom[ob];
+  const orc_bvh *t = is_oct ? &ac->oct[g] : &ac->mesh[g];
+  if (t->n_nodes == 0) return 0;
+  shape_t S; shape_from_object(d, os, Ts, &S);
+  if (S.type == MPB_GEOM_CONVEX) S.nbr = ac->hull_nbr[d->obj_geom[os]];
+  xf_t rel; xf_inv_mul_(&rel, Tb, Ts); /* shape in the tree's frame */
+  double cl[3], hb[3], cb[3]; shape_local_box(d, ac, os, cl, hb); xf_apply(cb, &rel, cl);
+  for (int a = 0; a < 3; a++) hb[a] += ORC_PRUNE_PAD;
+  double res = is_oct ? d->oct_res[g] : 0;
+  const int32_t *C = is_oct ? d->oct_cells + 3 * d->oct_cell_off[g] : NULL;
+  const double *V = is_oct ? NULL : d->mesh_verts + 3 * d->mesh_vert_off[g];
+  const int32_t *Tr = is_oct ? NULL : d->mesh_tris + 3 * d->mesh_tri_off[g];
+  shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+  int stack[ORC_STACK], sp = 0; stack[sp++] = 0;
+  while (sp > 0) {
+    const orc_node *nd = &t->nodes[stack[--sp]];
+    if (boxes_disjoint(nd->c, nd->h, rel.R, cb, hb)) continue;
+    if (nd->left >= 0) { if (sp + 2 > ORC_STACK) return -1; stack[sp++] = nd->right; stack[sp++] = nd->left; continue; }
+    const int prim = ~nd->left;
+    if (is_oct) {
+      double c[3] = {(C[3 * prim] + 0.5) * res, (C[3 * prim + 1] + 0.5) * res, (C[3 * prim + 2] + 0.5) * res};
+      bx.T = *Tb; xf_apply(bx.T.p, Tb, c);
+      if (shape_intersect(&bx, &S)) return 1;
+    } else if (shape_triangle(&S, V + 3 * Tr[3 * prim], V + 3 * Tr[3 * prim + 1], V + 3 * Tr[3 * prim + 2], Tb)) return 1;
+  }
+  return 0;
+}
+/* mesh oa at Ta against mesh / octree ob at Tb: simultaneous descent of both trees */
+static int tree_tree_h(const mpb_scene_desc *d, const orc_accel *ac, int oa, const xf_t *Ta, int ob, const xf_t *Tb) {
+  const int ma = d->obj_geom[oa], gb = d->obj_geom[ob];
+  const int b_oct = d->obj_type[ob] == MPB_GEOM_OCTREE;
+  const orc_bvh *ta = &ac->mesh[ma], *tb = b_oct ? &ac->oct[gb] : &ac->mesh[gb];
+  if (ta->n_nodes == 0 || tb->n_nodes == 0) return 0;
+  xf_t rel; xf_inv_mul_(&rel, Ta, Tb); /* B in A */
+  const double *Va = d->mesh_verts + 3 * d->mesh_vert_off[ma];
+  const int32_t *Ia = d->mesh_tris + 3 * d->mesh_tri_off[ma];
+  const double *Vb = b_oct ? NULL : d->mesh_verts + 3 * d->mesh_vert_off[gb];
+  const int32_t *Ib = b_oct ? NULL : d->mesh_tris + 3 * d->mesh_tri_off[gb];
+  double res = b_oct ? d->oct_res[gb] : 0;
+  const int32_t *C = b_oct ? d->oct_cells + 3 * d->oct_cell_off[gb] : NULL;
+  shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+  int stack[2 * ORC_STACK], sp = 0; stack[sp++] = 0; stack[sp++] = 0;
+  while (sp > 0) {
+    const int ib = stack[--sp], ia = stack[--sp];
+    const orc_node *na = &ta->nodes[ia], *nb = &tb->nodes[ib];
+    double cb[3]; xf_apply(cb, &rel, nb->c);
+    if (boxes_disjoint(na->c, na->h, rel.R, cb, nb->h)) continue;
+    if (na->left < 0 && nb->left < 0) {
+      const int pa = ~na->left, pb = ~nb->left;
+      if (b_oct) {
+        double c[3] = {(C[3 * pb] + 0.5) * res, (C[3 * pb + 1] + 0.5) * res, (C[3 * pb + 2] + 0.5) * res};
+        bx.T = *Tb; xf_apply(bx.T.p, Tb, c);
+        if (shape_triangle(&bx, Va + 3 * Ia[3 * pa], Va + 3 * Ia[3 * pa + 1], Va + 3 * Ia[3 * pa + 2], Ta)) return 1;
+      } else {
+        double A[9], B[9];
+        for (int k = 0; k < 3; k++) { xf_apply(A + 3 * k, Ta, Va + 3 * Ia[3 * pa + k]); xf_apply(B + 3 * k, Tb, Vb + 3 * Ib[3 * pb + k]); }
+        if (tri_tri(A, B)) return 1;
+      }
+      continue;
+    }
+    if (sp + 4 > 2 * ORC_STACK) return -1;
+    const double sa = na->h[0] + na->h[1] + na->h[2], sb = nb->h[0] + nb->h[1] + nb->h[2];
+    if (nb->left < 0 || (na->left >= 0 && sa >= sb)) { stack[sp++] = na->right; stack[sp++] = ib; stack[sp++] = na->left; stack[sp++] = ib; }
+    else { stack[sp++] = ia; stack[sp++] = nb->right; stack[sp++] = ia; stack[sp++] = nb->left; }
+  }
+  return 0;
+}
+
 /* ::fcl::collide(o1, o2) as a boolean for the geometry types on the hot path */
+static int object_collide_ac(const mpb_scene_desc *d, const orc_accel *ac, int a, const xf_t *Ta, int b, const xf_t *Tb);
 static int object_collide(const mpb_scene_desc *d, int a, const xf_t *Ta, int b, const xf_t *Tb) {
   int ta = d->obj_type[a], tb = d->obj_type[b];
   if (ta == MPB_GEOM_OCTREE && tb == MPB_GEOM_OCTREE) return 0; /* not produced by the path */
@@ -705,6 +949,23 @@ static int object_collide(const mpb_scene_desc *d, int a, const xf_t *Ta, int b,
   if (tb == MPB_GEOM_MESH) return mesh_shape(d, b, Tb, a, Ta, 0);
   shape_t A, B; shape_from_object(d, a, Ta, &A); shape_from_object(d, b, Tb, &B);
   return shape_intersect(&A, &B);
+}
+
+/* the same dispatch through the hierarchies (ac != NULL); a traversal that outgrows its stack falls back to the exhaustive test */
+static int object_collide_ac(const mpb_scene_desc *d, const orc_accel *ac, int a, const xf_t *Ta, int b, const xf_t *Tb) {
+  if (!ac) return object_collide(d, a, Ta, b, Tb);
+  int ta = d->obj_type[a], tb = d->obj_type[b], r;
+  if (ta == MPB_GEOM_OCTREE && tb == MPB_GEOM_OCTREE) return 0;
+  if (ta >= MPB_GEOM_MESH && tb >= MPB_GEOM_MESH) r = ta == MPB_GEOM_MESH ? tree_tree_h(d, ac, a, Ta, b, Tb) : tree_tree_h(d, ac, b, Tb, a, Ta);
+  else if (ta >= MPB_GEOM_MESH) r = tree_shape_h(d, ac, a, Ta, b, Tb);
+  else if (tb >= MPB_GEOM_MESH) r = tree_shape_h(d, ac, b, Tb, a, Ta);
+  else {
+    shape_t A, B; shape_from_object(d, a, Ta, &A); shape_from_object(d, b, Tb, &B);
+    if (A.type == MPB_GEOM_CONVEX) A.nbr = ac->hull_nbr[d->obj_geom[a]];
+    if (B.type == MPB_GEOM_CONVEX) B.nbr = ac->hull_nbr[d->obj_geom[b]];
+    return shape_intersect(&A, &B);
+  }
+  return r < 0 ? object_collide(d, a, Ta, b, Tb) : r;
 }
 
 /* ------------------------------------------------------------------ exported API */
@@ -742,7 +1003,7 @@ int orc_object_poses(const mpb_scene_desc *d, const double *states, int64_t n, d
 /* ValidityCheckerTpl::isValid for a batch (src/ompl_planner.h:59-62): per state, every admitted pair
  * is tested (no early exit, src/planning_world.h:248-250).  pair_hit: [n][n_pairs] bytes (nullable),
  * verdict: [n] bytes (nullable).  Returns total support evaluations through *iters (nullable). */
-static int64_t collide_range(const mpb_scene_desc *d, const double *states, int64_t i0, int64_t i1, uint8_t *pair_hit, uint8_t *verdict) {
+static int64_t collide_range(const mpb_scene_desc *d, const orc_accel *ac, const double *states, int64_t i0, int64_t i1, uint8_t *pair_hit, uint8_t *verdict) {
   xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
   xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
   double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
@@ -754,7 +1015,7 @@ static int64_t collide_range(const mpb_scene_desc *d, const double *states, int6
     int any = 0;
     for (int p = 0; p < d->n_pairs; p++) {
       int a = d->pair_a[p], b = d->pair_b[p];
-      int hit = object_collide(d, a, &objT[a], b, &objT[b]);
+      int hit = object_collide_ac(d, ac, a, &objT[a], b, &objT[b]);
       if (pair_hit) pair_hit[i * d->n_pairs + p] = (uint8_t)hit;
       any |= hit;
     }
@@ -764,22 +1025,31 @@ static int64_t collide_range(const mpb_scene_desc *d, const double *states, int6
   return g_cnt.iters;
 }
 int orc_collide_batch(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters) {
-  int64_t it = collide_range(d, states, 0, n, pair_hit, verdict);
+  int64_t it = collide_range(d, NULL, states, 0, n, pair_hit, verdict);
   if (iters) *iters = it;
   return 0;
 }
 /* All-host-core variant: the stateful reference can only use more than one core as independent world
  * clones, one per thread; each thread owns its scratch and a contiguous slice. */
-int orc_collide_batch_mt(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters, int nthreads) {
+static int collide_batch_mt(const mpb_scene_desc *d, const orc_accel *ac, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters, int nthreads) {
   int64_t total = 0;
   if (nthreads < 1) nthreads = 1;
-#pragma omp parallel for num_threads(nthreads) schedule(static) reduction(+ : total)
-  for (int t = 0; t < nthreads; t++) {
-    int64_t i0 = n * t / nthreads, i1 = n * (t + 1) / nthreads;
-    total += collide_range(d, states, i0, i1, pair_hit, verdict);
+  /* slices of 256 states handed out dynamically: states near obstacles cost far more than free ones */
+  const int64_t slice = 256, n_slices = (n + slice - 1) / slice;
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 1) reduction(+ : total)
+  for (int64_t k = 0; k < n_slices; k++) {
+    int64_t i0 = k * slice, i1 = i0 + slice < n ? i0 + slice : n;
+    total += collide_range(d, ac, states, i0, i1, pair_hit, verdict);
   }
   if (iters) *iters = total;
   return 0;
+}
+int orc_collide_batch_mt(const mpb_scene_desc *d, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters, int nthreads) {
+  return collide_batch_mt(d, NULL, states, n, pair_hit, verdict, iters, nthreads);
+}
+/* the timed baseline: same loop through the hierarchies of `ac` (orc_accel_create) */
+int orc_collide_batch_accel(const mpb_scene_desc *d, const orc_accel *ac, const double *states, int64_t n, uint8_t *pair_hit, uint8_t *verdict, int64_t *iters, int nthreads) {
+  return collide_batch_mt(d, ac, states, n, pair_hit, verdict, iters, nthreads);
 }
 
 /* Band classifier for one (state, pair): signed distance estimate.  > 0: GJK separation distance;
@@ -976,9 +1246,9 @@ static int ss_segment_count(int D, const double *seg, const uint8_t *so2, const 
   return nd;
 }
 
-typedef struct { const mpb_scene_desc *d; xf_t *oMi; xf_t *objT; double *qf; int64_t checks; } orc_checker;
+typedef struct { const mpb_scene_desc *d; const orc_accel *ac; xf_t *oMi; xf_t *objT; double *qf; int64_t checks; } orc_checker;
 static void checker_init(orc_checker *c, const mpb_scene_desc *d) {
-  c->d = d; c->checks = 0;
+  c->d = d; c->checks = 0; c->ac = NULL;
   c->oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
   c->objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
   c->qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
@@ -990,7 +1260,7 @@ static int checker_is_valid(orc_checker *c, const double *state) {
   const mpb_scene_desc *d = c->d;
   scatter_state(d, state, c->qf); fk_joints(d, c->qf, c->oMi); object_transforms(d, c->oMi, c->objT, NULL);
   int any = 0;
-  for (int p = 0; p < d->n_pairs; p++) { int a = d->pair_a[p], b = d->pair_b[p]; any |= object_collide(d, a, &c->objT[a], b, &c->objT[b]); }
+  for (int p = 0; p < d->n_pairs; p++) { int a = d->pair_a[p], b = d->pair_b[p]; any |= object_collide_ac(d, c->ac, a, &c->objT[a], b, &c->objT[b]); }
   c->checks++;
   return !any;
 }
@@ -1069,11 +1339,11 @@ static int grow_tree(orc_rrt_ctx *c, orc_tree *tree, int is_start, const double 
 
 /* Returns 1 = "Exact solution", 0 = timeout / iteration budget exhausted, 3 = no valid goal.
  * path_out: [max_path][D]; *path_len = 0 unless solved and it fits. */
-int orc_rrtconnect(const mpb_scene_desc *d, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
+static int rrtconnect_ac(const mpb_scene_desc *d, const orc_accel *ac, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
                    const double *start, const double *goals, int n_goals, double range, int64_t max_grow_calls, double time_limit_s,
                    uint64_t seed, double *path_out, int max_path, int *path_len, int64_t *grow_calls, int64_t *state_checks) {
   if (D != d->state_dim) return MPB_ERR_INVALID;
-  orc_checker chk; checker_init(&chk, d);
+  orc_checker chk; checker_init(&chk, d); chk.ac = ac;
   orc_rrt_ctx c; c.D = D; c.lo = lo; c.hi = hi; c.seg = seg; c.so2 = so2; c.range = range; c.chk = &chk;
   c.xstate = (double *)malloc(sizeof(double) * (size_t)D); c.xmotion = -1;
   if (!(range > 1e-6)) { double ext = 0; for (int j = 0; j < D; j++) ext += (so2 && so2[j]) ? ORC_PI : hi[j] - lo[j]; c.range = 0.2 * ext; }
@@ -1127,7 +1397,32 @@ int orc_rrtconnect(const mpb_scene_desc *d, int D, const double *lo, const doubl
   return status;
 }
 
-/* Q independent queries, one per OpenMP thread at a time (the all-host-core CPU baseline of BASELINE.md 3). */
+int orc_rrtconnect(const mpb_scene_desc *d, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
+                   const double *start, const double *goals, int n_goals, double range, int64_t max_grow_calls, double time_limit_s,
+                   uint64_t seed, double *path_out, int max_path, int *path_len, int64_t *grow_calls, int64_t *state_checks) {
+  return rrtconnect_ac(d, NULL, D, lo, hi, seg, so2, start, goals, n_goals, range, max_grow_calls, time_limit_s, seed, path_out, max_path, path_len,
+                       grow_calls, state_checks);
+}
+
+/* Q independent queries, one per OpenMP thread at a time (the all-host-core CPU baseline of BASELINE.md 3).
+ * ac: NULL = exhaustive leaf tests, else the hierarchies of orc_accel_create (the timed baseline). */
+int orc_rrtconnect_batch_accel(const mpb_scene_desc *d, const orc_accel *ac, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
+                         const double *starts, const double *goals, const int32_t *n_goals, int max_goals, int64_t n_queries, double range,
+                         int64_t max_grow_calls, double time_limit_s, uint64_t seed, int32_t *status, int32_t *path_len, double *paths,
+                         int max_path, int64_t *grow_calls, int64_t *state_checks, int nthreads) {
+  int64_t gc = 0, sc = 0;
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 1) reduction(+ : gc, sc)
+  for (int64_t q = 0; q < n_queries; q++) {
+    int pl = 0; int64_t g1 = 0, s1 = 0;
+    status[q] = rrtconnect_ac(d, ac, D, lo, hi, seg, so2, starts + q * D, goals + (size_t)q * max_goals * D, n_goals[q], range, max_grow_calls,
+                              time_limit_s, seed + 7919ull * (uint64_t)q, paths + (size_t)q * max_path * D, max_path, &pl, &g1, &s1);
+    path_len[q] = pl; gc += g1; sc += s1;
+  }
+  if (grow_calls) *grow_calls = gc;
+  if (state_checks) *state_checks = sc;
+  return 0;
+}
 int orc_rrtconnect_batch(const mpb_scene_desc *d, int D, const double *lo, const double *hi, const double *seg, const uint8_t *so2,
                          const double *starts, const double *goals, const int32_t *n_goals, int max_goals, int64_t n_queries, double range,
                          int64_t max_grow_calls, double time_limit_s, uint64_t seed, int32_t *status, int32_t *path_len, double *paths,

@@ -53,14 +53,36 @@ def object_poses(desc, states):
     return out.reshape(s.shape[0], desc.n_objects, 3, 4)
 
 
-def collide_batch(desc, states, return_iters=False, threads=1):
+class Accel:
+    """Hierarchies of the TIMED baseline leg (orc_accel_create): AABB trees over mesh triangles / occupied voxels and
+    hull adjacency for the edge-walking support.  Holds the description it was built from."""
+
+    def __init__(self, desc):
+        self.desc = desc
+        lib().orc_accel_create.restype = C.c_void_p
+        self.h = C.c_void_p(lib().orc_accel_create(C.byref(desc.as_struct())))
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.orc_accel_destroy.argtypes = [C.c_void_p]
+            _lib.orc_accel_destroy(self.h)
+            self.h = None
+
+
+def collide_batch(desc, states, return_iters=False, threads=1, accel=None):
+    """Exhaustive checker (accel=None) or, with ``accel=Accel(desc)``, the hierarchical leg that bench.py times."""
     s = _states(desc, states)
     n = s.shape[0]
     ph = np.zeros((n, max(desc.n_pairs, 1)), dtype=np.uint8)
     vd = np.zeros(n, dtype=np.uint8)
     it = C.c_int64(0)
-    lib().orc_collide_batch_mt(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(ph.ctypes.data),
-                               C.c_void_p(vd.ctypes.data), C.byref(it), C.c_int(int(threads)))
+    if accel is not None:
+        assert accel.desc is desc, "the accelerator belongs to another scene description"
+        lib().orc_collide_batch_accel(C.byref(desc.as_struct()), accel.h, C.c_void_p(s.ctypes.data), C.c_int64(n),
+                                      C.c_void_p(ph.ctypes.data), C.c_void_p(vd.ctypes.data), C.byref(it), C.c_int(int(threads)))
+    else:
+        lib().orc_collide_batch_mt(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(ph.ctypes.data),
+                                   C.c_void_p(vd.ctypes.data), C.byref(it), C.c_int(int(threads)))
     ph = ph[:, : desc.n_pairs].astype(bool)
     if return_iters:
         return vd.astype(bool), ph, it.value
@@ -145,7 +167,7 @@ def check_motion_batch(desc, lo, hi, a, b, so2=None, threads=8):
 
 
 def rrtconnect_batch(desc, lo, hi, starts, goals, n_goals=None, so2=None, range_=0.1, max_grow_calls=1 << 20, time_limit=1.0, seed=0,
-                     max_path=4096, threads=1):
+                     max_path=4096, threads=1, accel=None):
     """CPU RRTConnect restatement for Q queries (one per thread at a time).
     -> (status int32[Q], list of paths, grow calls, state checks)"""
     lo, hi, seg, so2 = _space_args(lo, hi, so2)
@@ -161,7 +183,8 @@ def rrtconnect_batch(desc, lo, hi, starts, goals, n_goals=None, so2=None, range_
     plen = np.zeros(Q, dtype=np.int32)
     paths = np.zeros((Q, max_path, D), dtype=np.float64)
     gc, sc = C.c_int64(0), C.c_int64(0)
-    lib().orc_rrtconnect_batch(C.byref(desc.as_struct()), C.c_int(D), C.c_void_p(lo.ctypes.data), C.c_void_p(hi.ctypes.data),
+    lib().orc_rrtconnect_batch_accel(C.byref(desc.as_struct()), accel.h if accel is not None else None,
+                               C.c_int(D), C.c_void_p(lo.ctypes.data), C.c_void_p(hi.ctypes.data),
                                C.c_void_p(seg.ctypes.data), C.c_void_p(so2.ctypes.data), C.c_void_p(starts.ctypes.data),
                                C.c_void_p(goals.ctypes.data), C.c_void_p(ng.ctypes.data), C.c_int(G), C.c_int64(Q), C.c_double(range_),
                                C.c_int64(int(max_grow_calls)), C.c_double(time_limit), C.c_uint64(int(seed)), C.c_void_p(status.ctypes.data),
