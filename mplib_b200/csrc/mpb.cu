@@ -31,6 +31,7 @@ static int fail(int code, const std::string &msg) {
   } while (0)
 
 #define MPB_ASYNC_SLOTS 16
+static const long long kMaxHitPasses = 4096;
 struct AsyncSlot {
   unsigned *h = nullptr;          // pinned: totals[8] | counters[4] (64-bit)
   cudaEvent_t done = nullptr;
@@ -138,6 +139,7 @@ struct mpb_scene {
   std::vector<std::pair<void *, size_t>> pool;
   // blocking calls read their queue counters through this pinned block
   unsigned *h_status = nullptr;  // [32]
+  unsigned *h_hitcnt = nullptr;  // [kMaxHitPasses] hit-list length after each pass of a host-buffer call (same pinned block)
   // sparse hit list of host-buffer calls: [0] = counter, [1..] = (configuration, pair) entries
   uint2 *d_hits = nullptr;
   size_t d_hits_cap = 0;
@@ -148,11 +150,11 @@ struct mpb_scene {
   mpb_stats async_acc{};
   long long async_completed = 0, async_failed = 0;
   bool calibrated = false, async_timing = false;
-  long long good_chunk = 0;
+  long long good_chunk = 0, cap_chunk = 1ll << 40;  // largest pass size that fitted / smallest that is still allowed
   // small host batches replayed as CUDA graphs (see collide_small)
   std::vector<SmallGraph> small_graphs;
-  unsigned char *h_small = nullptr;
-  size_t h_small_cap = 0;
+  unsigned char *h_small = nullptr, *d_small = nullptr;  // pinned staging / device output block
+  size_t h_small_cap = 0, d_small_cap = 0;
   unsigned long long img_version = 0;  // bumped whenever a by-value kernel parameter of the image changes
   float *d_qconst = nullptr;           // [n_joints] value of the joints the batch state does not write (q_base)
 };
@@ -944,7 +946,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   s->img.linkJoint = s->d_linkJoint;
   rc = upload_pairs(s);
   if (rc != MPB_OK) { mpb_scene_destroy(s); return rc; }
-  CU(cudaHostAlloc((void **)&s->h_status, 32 * sizeof(unsigned), cudaHostAllocDefault));
+  CU(cudaHostAlloc((void **)&s->h_status, (32 + kMaxHitPasses) * sizeof(unsigned), cudaHostAllocDefault));
+  s->h_hitcnt = s->h_status + 32;
   {
     std::vector<float> qc(std::max(d->n_joints, 1), 0.f);
     for (int j = 0; j < d->n_joints; j++) qc[j] = s->h_joints[j].qconst;
@@ -983,7 +986,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals, s->wq.counters};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   cudaDeviceSynchronize();  // device-pointer calls may still be in flight on caller streams
@@ -992,6 +995,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   if (s->h_status) cudaFreeHost(s->h_status);
   if (s->h_slots) cudaFreeHost(s->h_slots);
   if (s->d_hits) cudaFree(s->d_hits);
+  if (s->d_small) cudaFree(s->d_small);
   if (s->d_qconst) cudaFree(s->d_qconst);
   for (auto &sl : s->slots) {
     if (sl.done) cudaEventDestroy(sl.done);
@@ -1052,6 +1056,8 @@ extern "C" int mpb_scene_set_pairs(mpb_scene *s, int32_t n_pairs, const int32_t 
   if (rc != MPB_OK) return rc;
   s->img_version++;
   s->calibrated = false;
+  s->good_chunk = 0;
+  s->cap_chunk = 1ll << 40;
   return upload_pairs(s);
 }
 
@@ -1089,6 +1095,8 @@ extern "C" int mpb_scene_update_objects(mpb_scene *s, int32_t n, const int32_t *
   CU(cudaMemcpy(s->d_cobb, s->h_cobb.data(), s->h_cobb.size() * sizeof(float4), cudaMemcpyHostToDevice));
   s->img_version++;
   s->calibrated = false;
+  s->good_chunk = 0;
+  s->cap_chunk = 1ll << 40;
   return upload_pairs(s);
 }
 
@@ -1105,6 +1113,7 @@ static cudaError_t ensure(T **p, size_t *cap, size_t need) {
 }
 
 static const long long kMaxChunk = 1ll << 20;       // configurations per pass
+static const long long kSmallBatch = 4096;          // host batches up to this size replay a CUDA graph (collide_small)
 static const size_t kMaxItems = (size_t)48 << 20;   // work-queue capacity bound (x56 B = 2.6 GiB)
 static const size_t kMaxSurvivors = (size_t)192 << 20;  // survivor-queue capacity bound (x8 B = 1.5 GiB)
 
@@ -1159,8 +1168,10 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   s->wq.bin_cursor = s->wq.bin_count + nb;
   s->wq.bin_start = s->wq.bin_cursor + nb;
   s->wq.unit_start = s->wq.bin_start + nb + 1;
-  if (!s->wq.totals) CU(cudaMalloc((void **)&s->wq.totals, 8 * sizeof(unsigned)));
-  if (!s->wq.counters) CU(cudaMalloc((void **)&s->wq.counters, 4 * sizeof(unsigned long long)));
+  if (!s->wq.totals) {  // totals[8] and counters[4] share one 64-byte block: one D2H copy brings both
+    CU(cudaMalloc((void **)&s->wq.totals, 8 * sizeof(unsigned) + 4 * sizeof(unsigned long long)));
+    s->wq.counters = reinterpret_cast<unsigned long long *>(s->wq.totals + 8);
+  }
   s->chunk = chunk;
   return MPB_OK;
 }
@@ -1189,6 +1200,7 @@ struct PassOut {
   uint2 *hits = nullptr;
   unsigned *n_hits = nullptr;
   unsigned hit_cap = 0, cfg0 = 0;
+  bool reset_call = false;  // small passes: the fused reset also zeroes the call's counters (first pass of a graph-captured call)
 };
 
 // Timing events of one pass: [0] start, [1] FK + cull done, [2] narrowphase done, [3], [4] around fk_table_kernel.
@@ -1206,11 +1218,22 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   const size_t vwords = (size_t)(m + 31) / 32;
   uint32_t *dv = po.dv, *dp = po.dp;
   HitOut out;
-  out.verdict = dv; out.pair_bits = dp; out.hits = po.hits; out.n_hits = po.n_hits; out.hit_cap = po.hit_cap; out.cfg0 = po.cfg0;
+  out.verdict = dv; out.pair_bits = dp;
   out.pair_words = W;
-  CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
-  if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
-  pass_reset_kernel<<<1, 256, 0, st>>>(s->wq, nb);
+  const bool small = m <= kSmallBatch;
+  // upper bound of the items any queue of this pass can hold: sizes the grids of small passes (every kernel below is
+  // grid-stride or ticket-driven, so a smaller grid is only less parallel, never wrong)
+  const long long work = m * (long long)std::max(s->img.n_pairs, 1);
+  auto grid_for = [&](int full, long long per_block) { return small ? (int)std::max<long long>(1, std::min<long long>(full, (work + per_block - 1) / per_block)) : full; };
+  if (small) {
+    const unsigned pw = dp ? (unsigned)(m * W) : 0u;
+    const int rb = (int)std::max<size_t>(1, std::min<size_t>(64, ((size_t)pw + vwords + 4095) / 4096));
+    small_reset_kernel<<<rb, 256, 0, st>>>(s->wq, nb, dv, (unsigned)vwords, dp, pw, po.n_hits, po.reset_call ? 1 : 0);
+  } else {
+    CU(cudaMemsetAsync(dv, 0, vwords * sizeof(uint32_t), st));
+    if (dp) CU(cudaMemsetAsync(dp, 0, (size_t)m * W * sizeof(uint32_t), st));
+    pass_reset_kernel<<<1, 256, 0, st>>>(s->wq, nb);
+  }
   const bool ev = pe.on;
   cudaEvent_t e0 = pe.e[0], e1 = pe.e[1], e2 = pe.e[2], f0 = pe.e[3], f1 = pe.e[4];
   if (ev) CU(cudaEventRecord(e0, st));
@@ -1251,29 +1274,36 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     return MPB_OK;
   }
-  dense_kernel<0><<<s->dense_blocks[0], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out);
+  dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out);
   *launches += 1;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
-  const unsigned n_warps = (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor);
+  const int nblocks = grid_for(s->narrow_blocks, 64);  // narrowphase: a block of 8 warps per 64 possible items of a small pass
+  const unsigned n_warps = (unsigned)std::max(1.0, nblocks * 8.0 * unit_factor);
   scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, n_warps, s->sq_cap);
-  scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
+  scatter_kernel<<<grid_for(s->num_sms * 2, 1024), 1024, 0, st>>>(s->img, s->wq, 0);
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
-  if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
-  else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
+  if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
+  else narrow_kernel<false><<<nblocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
   *launches += 3;
   if (s->img.expand2_bin >= 0) {  // mesh x mesh / mesh x octree pairs: exact leaf tests inside the descent
-    expand2_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, out);
+    expand2_kernel<<<grid_for(s->num_sms * 8, 4), 128, 0, st>>>(s->img, s->wq, out);
     *launches += 1;
   }
   if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
     pass_reset_kernel<<<1, 256, 0, st>>>(s->wq, nb);
-    expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, out);
-    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, n_warps, s->sq_cap);
+    expand_kernel<<<grid_for(s->num_sms * 8, 16), 128, 0, st>>>(s->img, s->wq, out);
+    scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor), s->sq_cap);
     scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1);
     if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);
     *launches += 5;
+  }
+  if (po.hits && dp && W > 0) {  // sparse hit list: compacted out of the pass's dense mask
+    const long long n_words = m * (long long)W;
+    const int blocks = (int)std::max<long long>(1, std::min<long long>((n_words + 1023) / 1024, (long long)s->num_sms * 8));
+    hits_compact_kernel<<<blocks, 256, 0, st>>>(dp, n_words, W, po.cfg0, po.hits, po.n_hits, po.hit_cap);
+    *launches += 1;
   }
   if (ev) CU(cudaEventRecord(e2, st));
   CU(cudaGetLastError());
@@ -1289,7 +1319,7 @@ struct CollideOut {
   uint32_t *n_hits = nullptr;    // [1], same space as hits
 };
 
-static void fill_stats(mpb_scene *s, mpb_stats *stats, long long n, const unsigned long long *counters, long long launches) {
+static void fill_stats(const mpb_scene *s, mpb_stats *stats, long long n, const unsigned long long *counters, long long launches) {
   stats->n_states = n;
   stats->pairs_admitted = n * (long long)s->img.n_pairs;
   stats->pairs_after_cull = (long long)counters[0];
@@ -1357,7 +1387,8 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, const Coll
     CU(cudaEventRecord(start, st));
     CU(cudaStreamWaitEvent(s->stream_h2d, start, 0));
   }
-  std::vector<cudaEvent_t> ev_k, ev_out;  // per pass: kernels done, results copied out
+  std::vector<cudaEvent_t> ev_k, ev_out, ev_cnt;  // per pass: kernels done, results copied out, hit count known
+  unsigned hits_copied = 0;
   for (long long off = 0; off < n; off += chunk, c++) {
     const long long m = std::min(chunk, n - off);
     const size_t vwords = (size_t)(m + 31) / 32;
@@ -1390,26 +1421,43 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, const Coll
     if (co.pair_bits)
       CU(cudaMemcpyAsync(co.pair_bits + (size_t)off * W, po.dp, (size_t)m * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream_d2h));
     CU(cudaEventRecord(ev_out[c], s->stream_d2h));
+    if (want_hits && c < kMaxHitPasses) {
+      // hit list: the counter after this pass lands in a pinned slot; once the PREVIOUS pass's count is known (this pass
+      // is already queued behind it, so the GPU stays busy) its share of the list is copied out under this pass's kernels
+      CU(cudaMemcpyAsync(s->h_hitcnt + c, d_nhits, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+      ev_cnt.push_back(get_sync_event(s, sync_ev++));
+      CU(cudaEventRecord(ev_cnt[c], st));
+      if (c >= 1) {
+        CU(cudaEventSynchronize(ev_cnt[c - 1]));
+        const unsigned upto = std::min(s->h_hitcnt[c - 1], hit_cap);
+        if (upto > hits_copied) {
+          CU(cudaMemcpyAsync(co.hits + 2 * (size_t)hits_copied, d_hits + hits_copied, (size_t)(upto - hits_copied) * sizeof(uint2), cudaMemcpyDeviceToHost, s->stream_d2h));
+          hits_copied = upto;
+        }
+      }
+    }
   }
   const auto t_enq = std::chrono::steady_clock::now();
   unsigned *totals = s->h_status;                                                        // pinned
   unsigned long long *counters = reinterpret_cast<unsigned long long *>(s->h_status + 8);
-  CU(cudaMemcpyAsync(totals, s->wq.totals, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(counters, s->wq.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(totals, s->wq.totals, 8 * sizeof(unsigned) + 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
   if (want_hits && host) CU(cudaMemcpyAsync(s->h_status + 16, d_nhits, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  if (host) CU(cudaStreamSynchronize(s->stream_d2h));
   *overflow = totals[2] != 0;
   if (want_hits && host && !*overflow) {
     const unsigned nh = s->h_status[16];
     *co.n_hits = nh;
-    const unsigned ncopy = std::min(nh, hit_cap);
-    if (ncopy) CU(cudaMemcpy(co.hits, d_hits, (size_t)ncopy * sizeof(uint2), cudaMemcpyDeviceToHost));
+    const unsigned upto = std::min(nh, hit_cap);
+    if (upto > hits_copied)
+      CU(cudaMemcpyAsync(co.hits + 2 * (size_t)hits_copied, d_hits + hits_copied, (size_t)(upto - hits_copied) * sizeof(uint2), cudaMemcpyDeviceToHost, s->stream_d2h));
   }
+  if (host) CU(cudaStreamSynchronize(s->stream_d2h));
   const auto t_end = std::chrono::steady_clock::now();
-  if (!*overflow) {  // what the device-pointer fast path sizes its passes from
+  if (!*overflow) {  // what the device-pointer fast path sizes its passes from: the largest pass size known to fit
+    s->good_chunk = s->calibrated ? std::max(s->good_chunk, chunk) : chunk;
     s->calibrated = true;
-    s->good_chunk = chunk;
+  } else {
+    s->cap_chunk = std::min(s->cap_chunk, std::max<long long>(32, (chunk / 4 + 31) / 32 * 32));  // passes of this size overflow
   }
   if (stats) {
     fill_stats(s, stats, n, counters, launches);
@@ -1444,7 +1492,7 @@ static void harvest_slot(mpb_scene *s, AsyncSlot &sl) {
   a.kernel_launches += st.kernel_launches; a.gpu_ms += st.gpu_ms; a.gpu_ms_cull += st.gpu_ms_cull; a.gpu_ms_narrow += st.gpu_ms_narrow;
   a.gpu_ms_fk += st.gpu_ms_fk; a.host_ms_enqueue += sl.host_ms; a.host_ms_total += sl.host_ms; a.fk_bytes_per_state = st.fk_bytes_per_state;
   s->async_completed++;
-  if (totals[2]) { s->async_failed++; s->calibrated = false; }  // the next call re-calibrates through the blocking protocol
+  if (totals[2]) { s->async_failed++; s->calibrated = false; s->good_chunk = 0; }  // the next call re-calibrates through the blocking protocol
   sl.pending = false;
 }
 
@@ -1466,7 +1514,7 @@ static int harvest(mpb_scene *s, bool wait) {
 static int collide_enqueue(mpb_scene *s, const float *q, long long n, const CollideOut &co, cudaStream_t st, mpb_stats *stats) {
   const auto t_begin = std::chrono::steady_clock::now();
   const int D = s->img.state_dim, W = s->img.pair_words;
-  const long long chunk = std::min<long long>(s->good_chunk, (n + 31) / 32 * 32);
+  const long long chunk = std::min<long long>(std::min<long long>(max_chunk_for(s), s->cap_chunk), (n + 31) / 32 * 32);
   int rc = prepare_work(s, chunk);
   if (rc != MPB_OK) return rc;
   const bool want_hits = co.hits != nullptr && co.n_hits != nullptr;
@@ -1553,7 +1601,6 @@ extern "C" int mpb_scene_set_async_timing(mpb_scene *s, int on) {
 // A legacy single-state query (collide(), Planner.check_for_*_collision, the isValid stub of INTEGRATION.md) is a batch
 // of one: a dozen launches and copies whose enqueue cost, not their execution, sets the latency.  Calls of at most
 // kSmallBatch states go through pinned staging buffers and a graph cached per (n, outputs) shape.
-static const long long kSmallBatch = 4096;
 
 static void drop_small_graphs(mpb_scene *s) {
   for (auto &g : s->small_graphs) {
@@ -1570,12 +1617,17 @@ static int collide_small(mpb_scene *s, const float *q, long long n, const Collid
   const int mode = want_hits ? 2 : (co.pair_bits ? 1 : 0);
   const long long chunk = (n + 31) / 32 * 32;
   cudaStream_t st = s->stream;
-  int rc = prepare_work(s, chunk);
-  if (rc != MPB_OK) return rc;
   const size_t vwords = (size_t)(n + 31) / 32;
-  const size_t q_bytes = (size_t)n * std::max(D, 1) * sizeof(float), v_bytes = vwords * 4, p_bytes = (size_t)n * std::max(W, 1) * 4;
-  const unsigned hit_cap = want_hits ? (unsigned)std::min<int64_t>(std::max<int64_t>(co.hit_cap, 0), (int64_t)n * std::max(s->img.n_pairs, 1)) : 0;
-  const size_t h_bytes = (size_t)hit_cap * sizeof(uint2);
+  // the graph copies a bounded hit list; a call that produces more goes through the chunked path
+  const unsigned user_cap = want_hits ? (unsigned)std::min<int64_t>(std::max<int64_t>(co.hit_cap, 0), (int64_t)1 << 30) : 0;
+  const unsigned hit_cap = std::min(user_cap, 65536u);
+  // output block, same layout on the device and in the pinned staging buffer:
+  //   [n_hits, pad to 16 B | verdict words, padded to 16 B | dense mask (mode 1) or hit list (mode 2)]
+  const size_t q_bytes = ((size_t)n * std::max(D, 1) * sizeof(float) + 15) / 16 * 16;
+  const size_t v_off = 16, v_bytes = (vwords * 4 + 15) / 16 * 16;
+  const size_t p_off = v_off + v_bytes;
+  const size_t p_bytes = mode == 1 ? (size_t)n * std::max(W, 1) * 4 : (mode == 2 ? (size_t)hit_cap * sizeof(uint2) : 0);
+  const size_t out_bytes = (p_off + p_bytes + 15) / 16 * 16;
   SmallGraph *g = nullptr;
   for (auto &x : s->small_graphs)
     if (x.n == n && x.mode == mode && x.hit_cap == hit_cap) g = &x;
@@ -1587,55 +1639,45 @@ static int collide_small(mpb_scene *s, const float *q, long long n, const Collid
       if (old.graph) cudaGraphDestroy(old.graph);
       s->small_graphs.erase(s->small_graphs.begin());
     }
-    // staging: pinned q | verdict | pair mask or hit list | status words; device mirrors from the host-call buffers
-    const size_t need = q_bytes + v_bytes + std::max(p_bytes, h_bytes) + 256;
-    if (need > s->h_small_cap) {
+    const size_t need = q_bytes + out_bytes + 64;
+    if (need > s->h_small_cap || out_bytes > s->d_small_cap) {
       CU(cudaStreamSynchronize(st));
-      drop_small_graphs(s);  // they point into the old staging block
-      if (s->h_small) cudaFreeHost(s->h_small);
-      s->h_small = nullptr;
-      s->h_small_cap = 0;
-      CU(cudaHostAlloc((void **)&s->h_small, need * 2, cudaHostAllocDefault));
-      s->h_small_cap = need * 2;
+      drop_small_graphs(s);  // they point into the old staging blocks
+      if (need > s->h_small_cap) {
+        if (s->h_small) cudaFreeHost(s->h_small);
+        s->h_small = nullptr;
+        s->h_small_cap = 0;
+        CU(cudaHostAlloc((void **)&s->h_small, need * 2, cudaHostAllocDefault));
+        s->h_small_cap = need * 2;
+      }
+      CU(ensure(&s->d_small, &s->d_small_cap, out_bytes * 2));
     }
     CU(ensure(&s->d_q[0], &s->d_q_cap[0], (size_t)chunk * std::max(D, 1)));
-    CU(ensure(&s->d_verdict[0], &s->d_verdict_cap[0], (size_t)(chunk + 31) / 32));
-    if (mode) CU(ensure(&s->d_pairbits[0], &s->d_pairbits_cap[0], (size_t)chunk * std::max(W, 1)));
-    if (want_hits) CU(ensure(&s->d_hits, &s->d_hits_cap, (size_t)hit_cap + 2));
+    if (mode == 2) CU(ensure(&s->d_pairbits[0], &s->d_pairbits_cap[0], (size_t)chunk * std::max(W, 1)));  // dense scratch of the compaction
     s->small_graphs.push_back(SmallGraph{});
     g = &s->small_graphs.back();
     g->n = n; g->mode = mode; g->hit_cap = hit_cap;
-    g->d_q = s->d_q[0]; g->d_v = s->d_verdict[0]; g->d_p = s->d_pairbits[0]; g->d_h = s->d_hits; g->h_base = s->h_small; g->chunk_at = s->chunk; g->img_version = s->img_version;
-    unsigned char *hb = s->h_small;
-    float *h_q = reinterpret_cast<float *>(hb);
-    uint32_t *h_v = reinterpret_cast<uint32_t *>(hb + q_bytes);
-    unsigned char *h_p = hb + q_bytes + v_bytes;
-    unsigned *h_st = reinterpret_cast<unsigned *>(hb + q_bytes + v_bytes + (std::max(p_bytes, h_bytes) + 15) / 16 * 16);
+    g->d_q = s->d_q[0]; g->d_v = s->d_small; g->d_p = mode == 2 ? s->d_pairbits[0] : nullptr; g->h_base = s->h_small; g->chunk_at = s->chunk;
+    g->img_version = s->img_version;
+    unsigned char *hb = s->h_small, *db = s->d_small;
     CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    rc = MPB_OK;
+    int rc = MPB_OK;
     cudaError_t ce = cudaSuccess;
     do {
-      if (D > 0 && (ce = cudaMemcpyAsync(s->d_q[0], h_q, (size_t)n * D * sizeof(float), cudaMemcpyHostToDevice, st)) != cudaSuccess) break;
-      if ((ce = cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st)) != cudaSuccess) break;
-      if ((ce = cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st)) != cudaSuccess) break;
+      if (D > 0 && (ce = cudaMemcpyAsync(s->d_q[0], hb, (size_t)n * D * sizeof(float), cudaMemcpyHostToDevice, st)) != cudaSuccess) break;
       PassOut po;
-      po.dv = s->d_verdict[0];
-      po.dp = mode ? s->d_pairbits[0] : nullptr;
-      if (want_hits) {
-        po.hits = s->d_hits + 1; po.n_hits = reinterpret_cast<unsigned *>(s->d_hits); po.hit_cap = hit_cap;
-        if ((ce = cudaMemsetAsync(po.n_hits, 0, sizeof(unsigned), st)) != cudaSuccess) break;
-      }
+      po.dv = reinterpret_cast<uint32_t *>(db + v_off);
+      po.dp = mode == 1 ? reinterpret_cast<uint32_t *>(db + p_off) : (mode == 2 ? s->d_pairbits[0] : nullptr);
+      po.reset_call = true;
+      po.n_hits = reinterpret_cast<unsigned *>(db);
+      if (mode == 2) { po.hits = reinterpret_cast<uint2 *>(db + p_off); po.hit_cap = hit_cap; }
       size_t sync_ev = 0;
       long long launches = 0;
       rc = launch_pass(s, nullptr, s->d_q[0], n, po, st, PassEvents{}, &launches, nullptr, &sync_ev);
       g->launches = launches;
       if (rc != MPB_OK) break;
-      if ((ce = cudaMemcpyAsync(h_v, po.dv, v_bytes, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
-      if (mode == 1 && (ce = cudaMemcpyAsync(h_p, po.dp, (size_t)n * W * 4, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
-      if (mode == 2 && hit_cap && (ce = cudaMemcpyAsync(h_p, po.hits, h_bytes, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
-      if (mode == 2 && (ce = cudaMemcpyAsync(h_st + 16, po.n_hits, sizeof(unsigned), cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
-      if ((ce = cudaMemcpyAsync(h_st, s->wq.totals, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
-      ce = cudaMemcpyAsync(h_st + 8, s->wq.counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+      if ((ce = cudaMemcpyAsync(hb + q_bytes, db, out_bytes, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+      ce = cudaMemcpyAsync(hb + q_bytes + out_bytes, s->wq.totals, 64, cudaMemcpyDeviceToHost, st);
     } while (0);
     cudaError_t ee = cudaStreamEndCapture(st, &g->graph);
     if (rc == MPB_OK && ce == cudaSuccess && ee == cudaSuccess) ee = cudaGraphInstantiate(&g->exec, g->graph, 0);
@@ -1648,24 +1690,26 @@ static int collide_small(mpb_scene *s, const float *q, long long n, const Collid
     }
   }
   unsigned char *hb = s->h_small;
-  uint32_t *h_v = reinterpret_cast<uint32_t *>(hb + q_bytes);
-  unsigned char *h_p = hb + q_bytes + v_bytes;
-  unsigned *h_st = reinterpret_cast<unsigned *>(hb + q_bytes + v_bytes + (std::max(p_bytes, h_bytes) + 15) / 16 * 16);
+  const unsigned char *ho = hb + q_bytes;
+  const unsigned *h_st = reinterpret_cast<const unsigned *>(ho + out_bytes);
   if (D > 0) memcpy(hb, q, (size_t)n * D * sizeof(float));
   CU(cudaGraphLaunch(g->exec, st));
   CU(cudaStreamSynchronize(st));
   *overflow = h_st[2] != 0;
-  if (!*overflow) {
-    memcpy(co.verdict, h_v, v_bytes);
-    if (mode == 1) memcpy(co.pair_bits, h_p, (size_t)n * W * 4);
-    if (mode == 2) {
-      const unsigned nh = h_st[16];
+  if (mode == 2 && !*overflow) {
+    const unsigned nh = *reinterpret_cast<const unsigned *>(ho);
+    if (nh > hit_cap && user_cap > hit_cap) *overflow = true;  // more hits than the graph copies: chunked path
+    else {
       *co.n_hits = nh;
-      memcpy(co.hits, h_p, (size_t)std::min(nh, hit_cap) * sizeof(uint2));
+      memcpy(co.hits, ho + p_off, (size_t)std::min(nh, hit_cap) * sizeof(uint2));
     }
   }
+  if (!*overflow) {
+    memcpy(co.verdict, ho + v_off, vwords * 4);
+    if (mode == 1) memcpy(co.pair_bits, ho + p_off, (size_t)n * W * 4);
+  }
   if (stats) {
-    fill_stats(s, stats, n, reinterpret_cast<unsigned long long *>(h_st + 8), g->launches);
+    fill_stats(s, stats, n, reinterpret_cast<const unsigned long long *>(h_st + 8), g->launches);
     stats->host_ms_enqueue = stats->host_ms_total = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
   }
   return MPB_OK;
@@ -1673,8 +1717,8 @@ static int collide_small(mpb_scene *s, const float *q, long long n, const Collid
 
 static bool small_graphs_valid(mpb_scene *s) {
   for (auto &g : s->small_graphs)
-    if (g.d_q != s->d_q[0] || g.d_v != s->d_verdict[0] || (g.mode && g.d_p != s->d_pairbits[0]) || (g.mode == 2 && g.d_h != s->d_hits) ||
-        g.h_base != s->h_small || g.chunk_at != s->chunk || g.img_version != s->img_version)
+    if (g.d_q != s->d_q[0] || g.d_v != s->d_small || (g.mode == 2 && g.d_p != s->d_pairbits[0]) || g.h_base != s->h_small ||
+        g.chunk_at != s->chunk || g.img_version != s->img_version)
       return false;
   return true;
 }
@@ -1698,7 +1742,9 @@ static int collide_common(mpb_scene *s, const float *q, int64_t n, const Collide
   }
   int rc = harvest(s, false);
   if (rc != MPB_OK) return rc;
-  if (space == MPB_DEVICE && may_async && s->calibrated) return collide_enqueue(s, q, n, co, st, stats);
+  // a pass size at most as large as one that already went through the blocking protocol without overflow
+  const long long want = std::min<long long>(std::min<long long>(max_chunk_for(s), s->cap_chunk), (n + 31) / 32 * 32);
+  if (space == MPB_DEVICE && may_async && s->calibrated && s->good_chunk >= want) return collide_enqueue(s, q, n, co, st, stats);
   // every blocking protocol below owns the work queues: calls still in flight finish first
   rc = harvest(s, true);
   if (rc != MPB_OK) return rc;
@@ -1712,7 +1758,7 @@ static int collide_common(mpb_scene *s, const float *q, int64_t n, const Collide
     if (rc != MPB_OK) return rc;
     if (!overflow) return MPB_OK;
   }
-  long long chunk = std::min<long long>(max_chunk_for(s), (n + 31) / 32 * 32);
+  long long chunk = want;
   for (int attempt = 0; attempt < 12; attempt++) {
     bool overflow = false;
     rc = collide_attempt(s, q, n, co, space, st, chunk, &overflow, stats);

@@ -67,32 +67,79 @@ struct WorkQ {
   unsigned int cap;
 };
 
-// Where the kernels of one pass report a colliding (configuration, pair): the verdict word, optionally the dense pair
-// mask of the pass, optionally the call-wide sparse hit list (the first setter of a mask bit appends the entry, so
-// several leaf items of one pair give one entry).
+// Where the kernels of one pass report a colliding (configuration, pair): the verdict word and, optionally, the dense
+// pair mask of the pass.  (The sparse hit list of mpb_collide_batch_hits is compacted out of the mask after the pass by
+// hits_compact_kernel: a list appended to from inside the narrowphase costs one same-address atomic per hit, which
+// at ~10 hits per configuration in the C3 scene slowed the whole pass by 40 %.)
 struct HitOut {
   unsigned int *verdict;    // [ceil(m / 32)] words of this pass
   unsigned int *pair_bits;  // [m][pair_words] of this pass, or nullptr
-  uint2 *hits;              // (configuration index within the call, pair) entries, or nullptr (needs pair_bits)
-  unsigned int *n_hits;     // entries appended so far (may run past hit_cap: the list is then truncated)
-  unsigned int hit_cap;
-  unsigned int cfg0;        // index of this pass's first configuration within the call
   int pair_words;
 };
 __device__ __forceinline__ void report_hit(const HitOut &o, unsigned cfg, int p) {
   atomicOr(&o.verdict[cfg >> 5], 1u << (cfg & 31));
-  if (o.pair_bits) {
-    const unsigned bit = 1u << (p & 31);
-    const unsigned old = atomicOr(&o.pair_bits[(size_t)cfg * o.pair_words + (p >> 5)], bit);
-    if (o.hits && !(old & bit)) {
-      const unsigned k = atomicAdd(o.n_hits, 1u);
-      if (k < o.hit_cap) o.hits[k] = make_uint2(o.cfg0 + cfg, (unsigned)p);
-    }
-  }
+  if (o.pair_bits) atomicOr(&o.pair_bits[(size_t)cfg * o.pair_words + (p >> 5)], 1u << (p & 31));
 }
 // this (configuration, pair) -- or, without a pair mask, this configuration -- is already known to collide
 __device__ __forceinline__ bool hit_known(const HitOut &o, unsigned cfg, int p) {
   return o.pair_bits ? ((o.pair_bits[(size_t)cfg * o.pair_words + (p >> 5)] >> (p & 31)) & 1u) : ((o.verdict[cfg >> 5] >> (cfg & 31)) & 1u);
+}
+
+// Dense pair mask of a pass -> (configuration, pair) entries appended to the call-wide list.  A block compacts tiles of
+// 1024 mask words (one 16-byte load per thread): popcounts, warp + block prefix sums, ONE atomic per tile for the
+// slots, then every thread writes the entries of its four words.  Entries are ordered by configuration within a tile;
+// the reservation order of the tiles is the only nondeterminism.
+__global__ void __launch_bounds__(256) hits_compact_kernel(const unsigned int *__restrict__ pair_bits, long long n_words, int pair_words,
+                                                           unsigned cfg0, uint2 *__restrict__ hits, unsigned int *__restrict__ n_hits,
+                                                           unsigned hit_cap) {
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ unsigned s_warp[8], s_base;
+  const long long n_quads = (n_words + 3) / 4, n_tiles = (n_quads + 255) / 256;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long qd = tile * 256 + threadIdx.x;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (qd * 4 + 3 < n_words) v = __ldg(reinterpret_cast<const uint4 *>(pair_bits) + qd);
+    else if (qd * 4 < n_words) {
+      v.x = pair_bits[qd * 4];
+      if (qd * 4 + 1 < n_words) v.y = pair_bits[qd * 4 + 1];
+      if (qd * 4 + 2 < n_words) v.z = pair_bits[qd * 4 + 2];
+    }
+    const unsigned c = __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+    unsigned incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(FULL, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned tot = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) { const unsigned t = s_warp[k]; s_warp[k] = tot; tot += t; }
+      s_base = tot ? atomicAdd(n_hits, tot) : 0u;
+    }
+    __syncthreads();
+    unsigned pos = s_base + s_warp[warp] + incl - c;
+    __syncthreads();  // s_warp / s_base are rewritten by the next tile
+    if (c) {
+      const unsigned words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        unsigned bits = words[j];
+        if (!bits) continue;
+        const long long w = qd * 4 + j;
+        const unsigned cfg = cfg0 + (unsigned)(w / pair_words), p0 = (unsigned)(w % pair_words) * 32u;
+        while (bits) {
+          const int k = __ffs(bits) - 1;
+          bits &= bits - 1;
+          if (pos < hit_cap) hits[pos] = make_uint2(cfg, p0 + (unsigned)k);
+          pos++;
+        }
+      }
+    }
+  }
 }
 
 #define MPB_EPS FLT_EPSILON
@@ -715,6 +762,23 @@ __global__ void pass_reset_kernel(WorkQ wq, int n_bins) {
   if (threadIdx.x == 0) { wq.totals[0] = 0; wq.totals[6] = 0; }
 }
 
+// the same for a small pass, plus the zeroing of its outputs (and, at the start of a call, of the call's counters): one
+// launch instead of a reset kernel and up to five memsets -- a legacy single-state query is bounded by its node count
+__global__ void __launch_bounds__(256) small_reset_kernel(WorkQ wq, int n_bins, unsigned *__restrict__ verdict, unsigned v_words,
+                                                          unsigned *__restrict__ pair_bits, unsigned p_words, unsigned *__restrict__ n_hits,
+                                                          int reset_call) {
+  if (blockIdx.x == 0) {
+    for (int b = threadIdx.x; b < n_bins; b += blockDim.x) wq.bin_count[b] = 0;
+    if (threadIdx.x < 8 && (reset_call || threadIdx.x == 0 || threadIdx.x == 6)) wq.totals[threadIdx.x] = 0;
+    if (reset_call && threadIdx.x < 4) wq.counters[threadIdx.x] = 0;
+    if (reset_call && n_hits && threadIdx.x == 0) *n_hits = 0;
+  }
+  const unsigned stride = gridDim.x * blockDim.x, i0 = blockIdx.x * blockDim.x + threadIdx.x;
+  for (unsigned i = i0; i < v_words; i += stride) verdict[i] = 0;
+  if (pair_bits)
+    for (unsigned i = i0; i < p_words; i += stride) pair_bits[i] = 0;
+}
+
 __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bin2, unsigned n_warps, unsigned sq_cap) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned items = 0, units = 0;
@@ -1028,7 +1092,12 @@ __global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, 
           busy = !(round == 1 && !busy_ok);
         }
         next += __popc(need);
-        if (__ballot_sync(FULL, busy) == 0) break;  // slice exhausted and every lane finished
+        if (__ballot_sync(FULL, busy) == 0) {
+          // no lane has work: either the slice is exhausted, or every item just fetched was skipped as already known
+          // (second round: the leaf items of one (configuration, pair) sit next to each other) -- then fetch again
+          if (next >= end) break;
+          continue;
+        }
       }
       // ---- one Minkowski support for every lane: sA(dir) - (R sB(R^T(-dir)) + t)
       const unsigned bm = __ballot_sync(FULL, busy);

@@ -29,6 +29,8 @@ def test_hit_list_equals_dense_mask():
         dense[hits[:, 0], hits[:, 1]] = True
         assert np.array_equal(dense, ph)
         assert len(np.unique(hits, axis=0)) == len(hits)  # one entry per (configuration, pair)
+        v2, ph2 = dev.collide(q, want_pairs=True)
+        assert np.array_equal(ph, ph2), "two calls on the same input must agree bit for bit"
     # a capacity that is too small truncates the list and reports the full count
     q = random_q(3000, 9)
     _, full = dev.collide_hits(q)
@@ -50,7 +52,6 @@ def test_device_pointer_calls_are_async_and_polled():
     dev = w._sync()["dev"]
     n = 50000
     qs = [random_q(n, 500 + k).astype(np.float32) for k in range(4)]
-    ref = [dev.collide(q, want_pairs=True) for q in qs]
     qd = [torch.from_numpy(q).cuda() for q in qs]
     W = dev.pair_words
     vd = [torch.zeros((n + 31) // 32, dtype=torch.int32, device="cuda") for _ in qs]
@@ -62,6 +63,13 @@ def test_device_pointer_calls_are_async_and_polled():
     acc, done, failed = dev.poll(wait=True)
     assert done == 3 and failed == 0 and acc["n_states"] == 3 * n and acc["narrow_iterations"] > 0
     torch.cuda.synchronize()
+    ref = [dev.collide(q, want_pairs=True) for q in qs]
+    # a larger batch than any calibrated one goes through the blocking protocol again, a smaller one does not
+    big = torch.from_numpy(random_q(2 * n, 1).astype(np.float32)).cuda()
+    vb = torch.zeros((2 * n + 31) // 32, dtype=torch.int32, device="cuda")
+    assert dev.collide_raw(big, 2 * n, vb, None, _lib.MPB_DEVICE, stream.cuda_stream)["async_pending"] == 0
+    assert dev.collide_raw(big, n // 2, vb, None, _lib.MPB_DEVICE, stream.cuda_stream)["async_pending"] == 1
+    dev.poll(wait=True)
     for k in range(4):
         v = np.unpackbits(vd[k].cpu().numpy().view(np.uint8), bitorder="little")[:n].astype(bool)
         p = np.unpackbits(pd[k].cpu().numpy().view(np.uint8), axis=1, bitorder="little")[:, : dev.n_pairs].astype(bool)
