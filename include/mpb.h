@@ -196,7 +196,9 @@ int mpb_scene_set_async_timing(mpb_scene *scene, int on);
  *   min_dist [n] float32   minimum over the ACM-admitted pairs of ::fcl::distance: the separation distance, or -1 when
  *                          some admitted pair touches / intersects; FLT_MAX when no pair is admitted
  *   argmin   [n] int32     nullable; index of the pair attaining it (first such pair in list order), -1 if none
- * Pairs involving a mesh or an octree return MPB_ERR_UNSUPPORTED in this build. */
+ * Pairs that involve a mesh (BVHModel) or an octree give the minimum over their leaf primitives, by branch and bound
+ * over the object's tree (the role of the Mesh... / OcTree... distance traversal nodes of FCL); overlapping triangles of a
+ * mesh x mesh pair give 0 (FCL's triDistance), every other touching / intersecting leaf -1. */
 int mpb_distance_batch(mpb_scene *scene, const float *q, int64_t n, float *min_dist, int32_t *argmin, mpb_stats *stats,
                        int space, void *stream);
 

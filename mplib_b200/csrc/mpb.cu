@@ -843,7 +843,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
         if (oct_root[t] < 0) {  // empty tree: a far-away zero box that never survives the cull
           bound_box(0, 0, 0, O);
           O.oc[0] = O.bc[0] = 1e6f;
-          O.voff = 0; O.vcnt = MPB_GEOM_VBOX;
+          O.voff = -1; O.vcnt = MPB_GEOM_VBOX;  // no tree: the traversal kernels skip the object
           break;
         }
         const auto &bb = oct_bounds[t];
@@ -1253,7 +1253,10 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, s->d_qconst, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);
       if (ev && !hq) CU(cudaEventRecord(f1, st));
       const int sblocks = std::min(cblocks, s->sphere_blocks[0]);  // persistent warps: survivor-queue chunks carry over between tiles
-      if (s->cull_tier == 1)
+      if (small)
+        sphere_pairs_kernel<<<(int)std::max<long long>(1, std::min<long long>((mm * (long long)s->img.n_pairs + 255) / 256, (long long)s->num_sms * 16)), 256, 0, st>>>(
+            s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
+      else if (s->cull_tier == 1)
         sphere_kernel<0, 256, 64><<<std::min(cblocks, s->sphere_blocks_ct[0]), 128, (size_t)s->img.n_dyn * 3 * 128 * sizeof(float), st>>>(s->img, s->ct_small, s->d_pose + off, s->pose_ld, mm, off, s->d_sq,
                                                                                               s->sq_cap, s->wq.totals);
       else if (s->sphere_cb == 2)
@@ -2194,8 +2197,6 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
   if (space != MPB_HOST && space != MPB_DEVICE) return fail(MPB_ERR_INVALID, "space must be MPB_HOST or MPB_DEVICE");
   if (stats) memset(stats, 0, sizeof(*stats));
   if (n == 0) return MPB_OK;
-  if (s->img.expand_bin >= 0 || s->img.expand2_bin >= 0)
-    return fail(MPB_ERR_UNSUPPORTED, "distance to mesh / octree objects is not supported by this build yet");
   CU(cudaSetDevice(s->device));
   if (int hrc = harvest(s, true)) return hrc;
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
@@ -2247,12 +2248,15 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, s->d_qconst, dq, m, s->d_pose, s->pose_ld, s->d_obb);
       sphere_kernel<1, 0, 0><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
       dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, HitOut{});
-      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, -1, -1, (unsigned)dblocks * 8u, s->sq_cap);
+      scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, (unsigned)dblocks * 8u, s->sq_cap);
       scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
       CU(cudaEventRecord(e1, st));
       if (s->smem_verts) distance_kernel<true><<<dblocks, 256, vsm, st>>>(s->img, s->wq, dbest, s->img.n_bins);
       else distance_kernel<false><<<dblocks, 256, 0, st>>>(s->img, s->wq, dbest, s->img.n_bins);
       launches += 4;
+      // mesh / octree pairs last: branch and bound against the minimum the convex / primitive pairs left in dbest
+      if (s->img.expand_bin >= 0) { distance_expand_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dbest); launches += 1; }
+      if (s->img.expand2_bin >= 0) { distance_expand2_kernel<<<s->num_sms * 8, 128, 0, st>>>(s->img, s->wq, dbest); launches += 1; }
     } else CU(cudaEventRecord(e1, st));
     distance_unpack_kernel<<<(int)((m + 255) / 256), 256, 0, st>>>(dbest, m, omin, oarg);
     launches += 1;

@@ -200,6 +200,307 @@ __global__ void __launch_bounds__(256) distance_kernel(SceneImg img, WorkQ wq, u
   if (lane == 0 && cap_sum) atomicAdd(&wq.counters[2], cap_sum);
 }
 
+// ---------------------------------------------------------------------------------------------- BVH distance
+// ::fcl::distance for pairs that involve a BVHModel or an OcTree (src/planning_world.cpp:492-712 reach them through
+// distanceSelf for `convex=False` links and distanceOthers for mesh obstacles / the point-cloud octree): the minimum over
+// the leaf primitives of the leaf distance, found by branch and bound over the object's AABB tree -- the role of
+// MeshShapeDistanceTraversalNodeOBBRSS / OcTreeSolver::OcTreeShapeDistanceRecurse / MeshDistanceTraversalNodeOBBRSS /
+// OcTreeMeshDistanceRecurse [upstream FCL 0.7.0].  A node is pruned when a lower bound of its distance exceeds the
+// smallest distance known for the configuration (from ANY admitted pair: best[cfg] is re-read every trip), so the
+// convex / primitive pairs, which run first, already cut most of the tree.
+
+// One GJK run per LANE (leaf primitives differ per lane; the loop is divergent by nature).  Same iteration as
+// distance_kernel.  Returns the separation distance, or -1 when the two shapes touch or intersect.
+__device__ __forceinline__ float gjk_lane(DevShape A, DevShape B, const float *R, V3 t, V3 cA, V3 cBl, const float4 *__restrict__ verts,
+                                          const float4 *__restrict__ prims, const unsigned char *__restrict__ cells, int &iters, bool &capped) {
+  float margin = 0.f;
+  if (A.type == MPB_GEOM_SPHERE || A.type == MPB_GEOM_CAPSULE) { margin += A.p0; A.p0 = 0.f; }
+  if (B.type == MPB_GEOM_SPHERE || B.type == MPB_GEOM_CAPSULE) { margin += B.p0; B.p0 = 0.f; }
+  V3 v = cA - (rot(R, cBl) + t);
+  if (dot(v, v) < 1e-20f) v = v3(1.f, 0.f, 0.f);
+  GjkSimplex S;
+  S.n = 0;
+  bool have = false;
+  float dist = -1.f;
+  for (;;) {
+    const V3 dir = normalized(v) * -1.f;
+    const V3 sa = support_local<false>(A, dir, verts, prims, cells);
+    const V3 sb = support_local<false>(B, rot_t(R, dir * -1.f), verts, prims, cells);
+    const V3 w = sa - (rot(R, sb) + t);
+    iters++;
+    if (have) {
+      const float vl = sqrtf(dot(v, v));
+      const float lb = -dot(w, dir);
+      bool dup = false;
+      for (int i = 0; i < S.n; i++) {
+        const V3 e = S.p[i] - w;
+        dup |= dot(e, e) <= 1e-14f;
+      }
+      if (vl - lb <= MPB_GJK_TOL || dup) { dist = vl; break; }
+    }
+    S.p[S.n++] = w;
+    if (!gjk_closest(S, v)) { dist = -1.f; break; }
+    have = true;
+    if (dot(v, v) < 1e-12f) { dist = -1.f; break; }
+    if (iters >= MPB_GJK_MAX_ITERS) { dist = sqrtf(dot(v, v)); capped = true; break; }
+  }
+  if (dist >= 0.f) { dist -= margin; if (dist <= 0.f) dist = -1.f; }
+  return dist;
+}
+
+__device__ __forceinline__ float best_distance(const unsigned long long *best, int cfg) {  // smallest distance known so far
+  const unsigned long long b = *reinterpret_cast<const volatile unsigned long long *>(best + cfg);
+  if (b == ~0ull) return FLT_MAX;
+  const unsigned key = (unsigned)(b >> 32);
+  return key == 0u ? -1.f : __uint_as_float(key & 0x7fffffffu);
+}
+__device__ __forceinline__ float gap3(float d0, float d1, float d2) {  // length of the positive parts
+  d0 = fmaxf(d0, 0.f); d1 = fmaxf(d1, 0.f); d2 = fmaxf(d2, 0.f);
+  return sqrtf(fmaf(d0, d0, fmaf(d1, d1, d2 * d2)));
+}
+// bounds of a leaf primitive in its object's frame: centre, half extents
+__device__ __forceinline__ void prim_box(const float4 *__restrict__ prims, int prim, int leaf_type, float *pc, float *ph) {
+  const float4 a = __ldg(prims + 3 * prim), b = __ldg(prims + 3 * prim + 1);
+  if (leaf_type == MPB_GEOM_VBOX) { pc[0] = a.x; pc[1] = a.y; pc[2] = a.z; ph[0] = b.x; ph[1] = b.y; ph[2] = b.z; return; }
+  const float4 c = __ldg(prims + 3 * prim + 2);
+  const float lo0 = fminf(a.x, fminf(b.x, c.x)), hi0 = fmaxf(a.x, fmaxf(b.x, c.x));
+  const float lo1 = fminf(a.y, fminf(b.y, c.y)), hi1 = fmaxf(a.y, fmaxf(b.y, c.y));
+  const float lo2 = fminf(a.z, fminf(b.z, c.z)), hi2 = fmaxf(a.z, fmaxf(b.z, c.z));
+  pc[0] = 0.5f * (lo0 + hi0); pc[1] = 0.5f * (lo1 + hi1); pc[2] = 0.5f * (lo2 + hi2);
+  ph[0] = 0.5f * (hi0 - lo0); ph[1] = 0.5f * (hi1 - lo1); ph[2] = 0.5f * (hi2 - lo2);
+}
+__device__ __forceinline__ V3 prim_centre(const float4 *__restrict__ prims, int prim, int leaf_type) {  // centerTriangle / box pose
+  const float4 a = __ldg(prims + 3 * prim);
+  if (leaf_type != MPB_GEOM_TRI) return v3(a.x, a.y, a.z);
+  const float4 b = __ldg(prims + 3 * prim + 1), c = __ldg(prims + 3 * prim + 2);
+  return v3((a.x + b.x + c.x) * (1.f / 3.f), (a.y + b.y + c.y) * (1.f / 3.f), (a.z + b.z + c.z) * (1.f / 3.f));
+}
+#define MPB_LB_SLACK 1e-6f  // fp32 rounding of the bounds: a node is kept unless its bound clears the best distance by this
+
+// warp per (configuration, shape x BVH object) item of the expand bin
+__global__ void __launch_bounds__(128) distance_expand_kernel(SceneImg img, WorkQ wq, unsigned long long *__restrict__ best) {
+  __shared__ int s_stack[4][MPB_EXP_STACK];
+  const int eb = img.expand_bin;
+  if (eb < 0) return;
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int *stack = s_stack[warp];
+  const unsigned char *cells = reinterpret_cast<const unsigned char *>(img.verts + img.n_verts);
+  const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
+  unsigned long long it_sum = 0, cap_sum = 0;
+  for (;;) {
+    unsigned it = 0;
+    if (lane == 0) it = atomicAdd(&wq.totals[5], 1u);
+    it = first + __shfl_sync(FULL, it, 0);
+    if (it >= end) break;
+    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    float ub = best_distance(best, cfg);
+    if (ub < 0.f) continue;  // some pair of this configuration already intersects: nothing can be smaller
+    const DevPair pr = img.pairs[p];
+    const DevObject &A = img.objs[pr.a];  // the shape
+    const DevObject &B = img.objs[pr.b];  // the BVH object
+    if (B.voff < 0) continue;             // empty octree: no leaf, no distance
+    float R[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
+    const V3 t = v3(wq.itf[(size_t)9 * wq.cap + it], wq.itf[(size_t)10 * wq.cap + it], wq.itf[(size_t)11 * wq.cap + it]);
+    // the shape seen from the object's frame:  x_B = R^T (x_A - t)
+    const V3 cs = rot_t(R, v3(A.bc[0], A.bc[1], A.bc[2]) - t);   // bounding-sphere centre
+    const V3 co = rot_t(R, v3(A.oc[0], A.oc[1], A.oc[2]) - t);   // OBB centre
+    float bh[3];  // axis-aligned bounds of the shape's OBB in the object's frame
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+      float acc = 0.f;
+#pragma unroll
+      for (int c = 0; c < 3; c++) {
+        const float m = fmaf(R[r], A.oR[c], fmaf(R[3 + r], A.oR[3 + c], R[6 + r] * A.oR[6 + c]));  // (R^T oR)[r][c]
+        acc = fmaf(fabsf(m), A.oh[c], acc);
+      }
+      bh[r] = acc;
+    }
+    const int leaf_type = B.vcnt;
+    DevShape SA = shape_of(A), SB;
+    SB.type = leaf_type; SB.voff = 0; SB.vcnt = 0; SB.cell = -1; SB.p0 = SB.p1 = SB.p2 = 0.f;
+    const V3 cA = v3(A.ctr[0], A.ctr[1], A.ctr[2]);
+    float local = FLT_MAX;
+    int sp = 1;
+    if (lane == 0) stack[0] = B.voff;
+    __syncwarp();
+    while (sp > 0) {
+      ub = fminf(ub, best_distance(best, cfg));
+      if (ub < 0.f) break;
+      const int take = sp > MPB_EXP_STACK - 64 ? 1 : min(sp, 32);
+      int node = -1;
+      if ((int)lane < take) node = stack[sp - 1 - (int)lane];
+      sp -= take;
+      __syncwarp();
+      bool pass = false;
+      DevBvhNode nd;
+      nd.left = 0; nd.right = 0;
+      if (node >= 0) {
+        nd = img.nodes[node];
+        const float lb1 = gap3(fabsf(nd.c[0] - cs.x) - nd.h[0], fabsf(nd.c[1] - cs.y) - nd.h[1], fabsf(nd.c[2] - cs.z) - nd.h[2]) - A.br;
+        const float lb2 = gap3(fabsf(nd.c[0] - co.x) - nd.h[0] - bh[0], fabsf(nd.c[1] - co.y) - nd.h[1] - bh[1], fabsf(nd.c[2] - co.z) - nd.h[2] - bh[2]);
+        pass = fmaxf(lb1, lb2) <= ub + MPB_LB_SLACK;
+      }
+      const bool inner = pass && nd.left >= 0;
+      const unsigned im = __ballot_sync(FULL, inner);
+      bool dropped = false;
+      if (inner) {
+        const int pos = sp + 2 * __popc(im & ((1u << lane) - 1u));
+        if (pos + 1 < MPB_EXP_STACK) { stack[pos] = nd.left; stack[pos + 1] = nd.right; }
+        else dropped = true;
+      }
+      sp = min(sp + 2 * __popc(im), MPB_EXP_STACK);
+      __syncwarp();
+      if (__any_sync(FULL, dropped)) cap_sum++;  // a subtree that could not be held: counted (narrow_capped), the minimum may miss it
+      float dmin = FLT_MAX;
+      if (pass && nd.left < 0) {
+        const int pfirst = ~nd.left;
+        for (int k = 0; k < nd.right; k++) {
+          const int prim = pfirst + k;
+          float pc[3], ph[3];
+          prim_box(img.prims, prim, leaf_type, pc, ph);
+          const float lb1 = gap3(fabsf(pc[0] - cs.x) - ph[0], fabsf(pc[1] - cs.y) - ph[1], fabsf(pc[2] - cs.z) - ph[2]) - A.br;
+          const float lb2 = gap3(fabsf(pc[0] - co.x) - ph[0] - bh[0], fabsf(pc[1] - co.y) - ph[1] - bh[1], fabsf(pc[2] - co.z) - ph[2] - bh[2]);
+          if (fmaxf(lb1, lb2) > fminf(ub, dmin) + MPB_LB_SLACK) continue;
+          SB.voff = prim;
+          int iters = 0;
+          bool capped = false;
+          const float d = gjk_lane(SA, SB, R, t, cA, prim_centre(img.prims, prim, leaf_type), img.verts, img.prims, cells, iters, capped);
+          it_sum += (unsigned)iters;
+          cap_sum += capped ? 1u : 0u;
+          dmin = fminf(dmin, d);
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dmin = fminf(dmin, __shfl_xor_sync(FULL, dmin, o));
+      if (dmin < local) local = dmin;
+      ub = fminf(ub, dmin);
+      if (ub < 0.f) break;
+    }
+    if (lane == 0 && local < FLT_MAX) {
+      const unsigned key = local < 0.f ? 0u : (__float_as_uint(local) | 0x80000000u);
+      atomicMin(&best[cfg], ((unsigned long long)key << 32) | (unsigned)p);
+    }
+    __syncwarp();
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    it_sum += __shfl_xor_sync(FULL, it_sum, o);
+    cap_sum += __shfl_xor_sync(FULL, cap_sum, o);
+  }
+  if (lane == 0 && it_sum) atomicAdd(&wq.counters[1], it_sum);
+  if (lane == 0 && cap_sum) atomicAdd(&wq.counters[2], cap_sum);
+}
+
+// warp per (configuration, mesh x mesh | mesh x octree) item of the expand2 bin; A = mesh, B = mesh or octree
+__global__ void __launch_bounds__(128) distance_expand2_kernel(SceneImg img, WorkQ wq, unsigned long long *__restrict__ best) {
+  __shared__ int2 s_stack[4][MPB_EXP2_STACK];
+  const int eb = img.expand2_bin;
+  if (eb < 0) return;
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int2 *stack = s_stack[warp];
+  const unsigned char *cells = reinterpret_cast<const unsigned char *>(img.verts + img.n_verts);
+  const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
+  unsigned long long it_sum = 0, cap_sum = 0;
+  for (;;) {
+    unsigned it = 0;
+    if (lane == 0) it = atomicAdd(&wq.totals[7], 1u);
+    it = first + __shfl_sync(FULL, it, 0);
+    if (it >= end) break;
+    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    float ub = best_distance(best, cfg);
+    if (ub < 0.f) continue;
+    const DevPair pr = img.pairs[p];
+    const DevObject &A = img.objs[pr.a];
+    const DevObject &B = img.objs[pr.b];
+    if (B.voff < 0) continue;
+    float R[9];  // B in A
+#pragma unroll
+    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
+    const V3 t = v3(wq.itf[(size_t)9 * wq.cap + it], wq.itf[(size_t)10 * wq.cap + it], wq.itf[(size_t)11 * wq.cap + it]);
+    const int leaf_b = B.vcnt;
+    DevShape SA, SB;
+    SA.type = MPB_GEOM_TRI; SA.voff = 0; SA.vcnt = 0; SA.cell = -1; SA.p0 = SA.p1 = SA.p2 = 0.f;
+    SB = SA;
+    SB.type = leaf_b;
+    float local = FLT_MAX;
+    int sp = 1;
+    if (lane == 0) stack[0] = make_int2(A.voff, B.voff);
+    __syncwarp();
+    while (sp > 0) {
+      ub = fminf(ub, best_distance(best, cfg));
+      if (ub < 0.f) break;
+      const int take = sp > MPB_EXP2_STACK - 64 ? 1 : min(sp, 32);
+      int2 np = make_int2(-1, -1);
+      if ((int)lane < take) np = stack[sp - 1 - (int)lane];
+      sp -= take;
+      __syncwarp();
+      bool pass = false;
+      DevBvhNode na, nb;
+      na.left = nb.left = 0; na.right = nb.right = 0;
+      if (np.x >= 0) {
+        na = img.nodes[np.x];
+        nb = img.nodes[np.y];
+        const V3 cb = rot(R, v3(nb.c[0], nb.c[1], nb.c[2])) + t;  // B node centre in A's frame; its box lies inside the sphere |h|
+        const float rb = sqrtf(fmaf(nb.h[0], nb.h[0], fmaf(nb.h[1], nb.h[1], nb.h[2] * nb.h[2])));
+        const float lb = gap3(fabsf(cb.x - na.c[0]) - na.h[0], fabsf(cb.y - na.c[1]) - na.h[1], fabsf(cb.z - na.c[2]) - na.h[2]) - rb;
+        pass = lb <= ub + MPB_LB_SLACK;
+      }
+      const bool both_leaf = na.left < 0 && nb.left < 0;
+      const bool inner = pass && !both_leaf;
+      const unsigned im = __ballot_sync(FULL, inner);
+      bool dropped = false;
+      if (inner) {
+        const float sa = na.h[0] + na.h[1] + na.h[2], sb = nb.h[0] + nb.h[1] + nb.h[2];
+        const bool split_a = nb.left < 0 || (na.left >= 0 && sa >= sb);
+        const int pos = sp + 2 * __popc(im & ((1u << lane) - 1u));
+        if (pos + 1 < MPB_EXP2_STACK) {
+          stack[pos] = split_a ? make_int2(na.left, np.y) : make_int2(np.x, nb.left);
+          stack[pos + 1] = split_a ? make_int2(na.right, np.y) : make_int2(np.x, nb.right);
+        } else dropped = true;
+      }
+      sp = min(sp + 2 * __popc(im), MPB_EXP2_STACK);
+      __syncwarp();
+      if (__any_sync(FULL, dropped)) cap_sum++;
+      float dmin = FLT_MAX;
+      if (pass && both_leaf) {
+        const int fa = ~na.left, fb = ~nb.left;
+        for (int i = 0; i < na.right; i++)
+          for (int j = 0; j < nb.right; j++) {
+            SA.voff = fa + i;
+            SB.voff = fb + j;
+            int iters = 0;
+            bool capped = false;
+            float d = gjk_lane(SA, SB, R, t, prim_centre(img.prims, fa + i, MPB_GEOM_TRI), prim_centre(img.prims, fb + j, leaf_b), img.verts, img.prims,
+                               cells, iters, capped);
+            if (d < 0.f && leaf_b == MPB_GEOM_TRI) d = 0.f;  // [upstream] TriangleDistance::triDistance returns 0 for overlapping triangles
+            it_sum += (unsigned)iters;
+            cap_sum += capped ? 1u : 0u;
+            dmin = fminf(dmin, d);
+          }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dmin = fminf(dmin, __shfl_xor_sync(FULL, dmin, o));
+      if (dmin < local) local = dmin;
+      ub = fminf(ub, dmin);
+      if (ub < 0.f) break;
+    }
+    if (lane == 0 && local < FLT_MAX) {
+      const unsigned key = local < 0.f ? 0u : (__float_as_uint(local) | 0x80000000u);
+      atomicMin(&best[cfg], ((unsigned long long)key << 32) | (unsigned)p);
+    }
+    __syncwarp();
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    it_sum += __shfl_xor_sync(FULL, it_sum, o);
+    cap_sum += __shfl_xor_sync(FULL, cap_sum, o);
+  }
+  if (lane == 0 && it_sum) atomicAdd(&wq.counters[1], it_sum);
+  if (lane == 0 && cap_sum) atomicAdd(&wq.counters[2], cap_sum);
+}
+
 // best[] -> (min_distance, argmin pair); a configuration with no admitted pair keeps FLT_MAX / -1
 __global__ void distance_unpack_kernel(const unsigned long long *__restrict__ best, long long n, float *__restrict__ min_dist,
                                        int *__restrict__ argmin) {

@@ -640,6 +640,50 @@ __global__ void __launch_bounds__(128) sphere_blk_kernel(const __grid_constant__
 }
 #undef POSE
 
+// sphere phase of a SMALL pass (a legacy single-state query, a few thousand states): thread per (configuration, cull-table
+// entry) instead of thread per configuration -- one warp walking the 1587 entries of the C3 table for a single state
+// took 0.21 ms, all of it load latency.  Same tests as sphere_kernel<0> (expanded form for world-fixed partners).
+#define POSE(w, i) pose[(size_t)(w) * ld + (i)]
+__global__ void __launch_bounds__(256) sphere_pairs_kernel(const __grid_constant__ SceneImg img, const float *__restrict__ pose, size_t ld,
+                                                           long long n, long long cfg_base, uint2 *__restrict__ sq, unsigned sq_cap,
+                                                           unsigned *__restrict__ totals) {
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31;
+  const int cbase = img.w_sphere, P = img.n_pairs;
+  const long long total = n * (long long)P, total_r = (total + 31) / 32 * 32;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total_r; idx += (long long)gridDim.x * blockDim.x) {
+    bool pass = false;
+    long long i = 0;
+    int k = 0;
+    if (idx < total) {
+      i = idx / P;
+      k = (int)(idx - i * P);
+      const int mm = __ldg(&img.cullm[k].y);
+      const int m1 = mm & 0xffff, m2 = mm >> 16;  // biased by one; 0 = none
+      float ax = 0.f, ay = 0.f, az = 0.f;
+      if (m1) { ax = POSE(cbase + (m1 - 1) * 3, i); ay = POSE(cbase + (m1 - 1) * 3 + 1, i); az = POSE(cbase + (m1 - 1) * 3 + 2, i); }
+      if (m2) {
+        const float rr2 = __ldg(&img.cullc[k].w);
+        const float dx = ax - POSE(cbase + (m2 - 1) * 3, i), dy = ay - POSE(cbase + (m2 - 1) * 3 + 1, i), dz = az - POSE(cbase + (m2 - 1) * 3 + 2, i);
+        pass = fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= rr2;
+      } else {
+        const float4 c = __ldg(img.cullq + k);
+        pass = fmaf(ax, c.x, fmaf(ay, c.y, fmaf(az, c.z, c.w))) <= -fmaf(ax, ax, fmaf(ay, ay, az * az));
+      }
+    }
+    const unsigned bm = __ballot_sync(FULL, pass);
+    if (!bm) continue;
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(&totals[6], (unsigned)__popc(bm));
+    base = __shfl_sync(FULL, base, 0);
+    if (pass) {
+      const unsigned pos = base + __popc(bm & ((1u << lane) - 1u));
+      if (pos < sq_cap) sq[pos] = make_uint2((unsigned)(cfg_base + i), (unsigned)k);
+    }
+  }
+}
+#undef POSE
+
 template <int MODE>
 __global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
                                                     unsigned sq_cap, WorkQ wq, HitOut out) {
@@ -780,24 +824,39 @@ __global__ void __launch_bounds__(256) small_reset_kernel(WorkQ wq, int n_bins, 
 }
 
 __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bin2, unsigned n_warps, unsigned sq_cap) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    unsigned items = 0, units = 0;
-    // unit = slice of one bin a warp owns: as large as possible (persistent lanes keep all 32 lanes busy across the
-    // spread of MPR run lengths; the tail of a slice runs in the cooperative mode) while still feeding n_warps
-    unsigned all = 0;
-    for (int b = 0; b < n_bins; b++)
-      if (b != skip_bin && b != skip_bin2) all += wq.bin_count[b];
-    unsigned unit = MPB_UNIT_ITEMS;
-    while (unit > 2u && all / unit < n_warps - n_warps / 4) unit >>= 1;  // few items (a planning round): short slices -> cooperative supports
-    wq.totals[4] = unit;
-    for (int b = 0; b < n_bins; b++) {
-      wq.bin_start[b] = items;
-      wq.unit_start[b] = units;
-      const unsigned c = wq.bin_count[b];
-      items += c;
-      if (b != skip_bin && b != skip_bin2) units += (c + unit - 1u) / unit;  // BVH pairs go to expand_kernel / expand2_kernel instead
+  // one warp: bins in groups of 32 (count -> warp prefix sums), the running totals carried in registers
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+  // unit = slice of one bin a warp owns: as large as possible (persistent lanes keep all 32 lanes busy across the
+  // spread of MPR run lengths; the tail of a slice runs in the cooperative mode) while still feeding n_warps
+  unsigned all = 0;
+  for (int b = lane; b < n_bins; b += 32)
+    if (b != skip_bin && b != skip_bin2) all += wq.bin_count[b];
+  all = __reduce_add_sync(FULL, all);
+  unsigned unit = MPB_UNIT_ITEMS;
+  while (unit > 2u && all / unit < n_warps - n_warps / 4) unit >>= 1;  // few items (a planning round): short slices -> cooperative supports
+  unsigned items = 0, units = 0;
+  for (int b0 = 0; b0 < n_bins; b0 += 32) {
+    const int b = b0 + lane;
+    const unsigned c = b < n_bins ? wq.bin_count[b] : 0u;
+    const unsigned u = (b < n_bins && b != skip_bin && b != skip_bin2) ? (c + unit - 1u) / unit : 0u;  // BVH pairs go to expand_kernel / expand2_kernel instead
+    unsigned ic = c, iu = u;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t1 = __shfl_up_sync(FULL, ic, o), t2 = __shfl_up_sync(FULL, iu, o);
+      if (lane >= o) { ic += t1; iu += t2; }
+    }
+    if (b < n_bins) {
+      wq.bin_start[b] = items + ic - c;
+      wq.unit_start[b] = units + iu - u;
       wq.bin_cursor[b] = 0;
     }
+    items += __shfl_sync(FULL, ic, 31);
+    units += __shfl_sync(FULL, iu, 31);
+  }
+  if (lane == 0) {
+    wq.totals[4] = unit;
     wq.bin_start[n_bins] = items;
     wq.unit_start[n_bins] = units;
     wq.totals[1] = units;
@@ -1288,6 +1347,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // the shape
     const DevObject &B = img.objs[pr.b];  // the BVH object
+    if (B.voff < 0) continue;             // empty octree
     float R[9], t[3];
 #pragma unroll
     for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
@@ -1418,27 +1478,31 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
 // intersects", which is what FCL returns with num_max_contacts = 1.
 #define MPB_EXP2_STACK 768
 
-// segment pq pierces triangle abc (closed sets)
-__device__ __forceinline__ bool seg_tri_hit(V3 p, V3 q, V3 a, V3 b, V3 c) {
-  const V3 ab = b - a, ac = c - a, n = cross(ab, ac), pq = q - p, ap = p - a;
-  const float dn = dot(n, pq);
-  if (dn == 0.f) return false;
-  const float t = -dot(n, ap) / dn;
-  if (t < 0.f || t > 1.f) return false;
-  const V3 x = v3(fmaf(t, pq.x, p.x) - a.x, fmaf(t, pq.y, p.y) - a.y, fmaf(t, pq.z, p.z) - a.z);
-  const float d00 = dot(ab, ab), d01 = dot(ab, ac), d11 = dot(ac, ac), d20 = dot(x, ab), d21 = dot(x, ac);
-  const float den = d00 * d11 - d01 * d01;
-  if (den == 0.f) return false;
-  const float v = (d11 * d20 - d01 * d21) / den, w = (d00 * d21 - d01 * d20) / den;
-  return v >= 0.f && w >= 0.f && v + w <= 1.f;
+// triangle x triangle [upstream FCL Intersect::intersect_Triangle = PQP TriContact]: 17-axis separating-axis test (two
+// normals, nine edge x edge products, six in-plane edge normals, which decide coplanar triangles); touching = hit
+__device__ __forceinline__ bool tri_axis_overlap(V3 ax, V3 p2, V3 p3, V3 q1, V3 q2, V3 q3) {  // p1 is the origin
+  const float P2 = dot(ax, p2), P3 = dot(ax, p3), Q1 = dot(ax, q1), Q2 = dot(ax, q2), Q3 = dot(ax, q3);
+  const float mx1 = fmaxf(0.f, fmaxf(P2, P3)), mn1 = fminf(0.f, fminf(P2, P3)), mx2 = fmaxf(Q1, fmaxf(Q2, Q3)), mn2 = fminf(Q1, fminf(Q2, Q3));
+  return !(mn1 > mx2 || mn2 > mx1);
 }
 __device__ __forceinline__ bool tri_tri_hit(const V3 *A, const V3 *B) {
+  const V3 p2 = A[1] - A[0], p3 = A[2] - A[0], q1 = B[0] - A[0], q2 = B[1] - A[0], q3 = B[2] - A[0];
+  const V3 e[3] = {p2, p3 - p2, p3 * -1.f}, f[3] = {q2 - q1, q3 - q2, q1 - q3};
+  const V3 n1 = cross(e[0], e[1]), m1 = cross(f[0], f[1]);
+  if (!tri_axis_overlap(n1, p2, p3, q1, q2, q3)) return false;
+  if (!tri_axis_overlap(m1, p2, p3, q1, q2, q3)) return false;
 #pragma unroll
-  for (int e = 0; e < 3; e++) {
-    if (seg_tri_hit(A[e], A[(e + 1) % 3], B[0], B[1], B[2])) return true;
-    if (seg_tri_hit(B[e], B[(e + 1) % 3], A[0], A[1], A[2])) return true;
-  }
-  return false;
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+      if (!tri_axis_overlap(cross(e[i], f[j]), p2, p3, q1, q2, q3)) return false;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+    if (!tri_axis_overlap(cross(e[i], n1), p2, p3, q1, q2, q3)) return false;
+#pragma unroll
+  for (int j = 0; j < 3; j++)
+    if (!tri_axis_overlap(cross(f[j], m1), p2, p3, q1, q2, q3)) return false;
+  return true;
 }
 // axis-aligned box (centre c, half h) vs triangle, 13-axis SAT (closed sets touch = hit)
 __device__ __forceinline__ bool box_tri_hit(V3 c, V3 h, V3 p0, V3 p1, V3 p2) {
@@ -1483,6 +1547,7 @@ __global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, Hi
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // mesh
     const DevObject &B = img.objs[pr.b];  // mesh or octree
+    if (B.voff < 0) continue;             // empty octree
     float R[9], t[3];  // B in A
 #pragma unroll
     for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];

@@ -635,26 +635,30 @@ static int mesh_shape(const mpb_scene_desc *d, int om, const xf_t *Tm, int os, c
   }
   return 0;
 }
-/* triangle-triangle intersection (role of FCL Intersect::intersect_Triangle): exact segment/triangle
- * piercing tests both ways plus the coplanar-overlap fallback via MPR on the two triangles. */
-static int seg_tri(const double *p, const double *q, const double *a, const double *b, const double *c) {
-  double ab[3], ac[3], n[3], pq[3], ap[3];
-  sub3(ab, b, a); sub3(ac, c, a); cross3(n, ab, ac); sub3(pq, q, p); sub3(ap, p, a);
-  double dn = dot3(n, pq), t = -dot3(n, ap);
-  if (dn == 0) return 0;
-  t /= dn; if (t < 0 || t > 1) return 0;
-  double x[3] = {p[0] + t * pq[0] - a[0], p[1] + t * pq[1] - a[1], p[2] + t * pq[2] - a[2]};
-  double d00 = dot3(ab, ab), d01 = dot3(ab, ac), d11 = dot3(ac, ac), d20 = dot3(x, ab), d21 = dot3(x, ac);
-  double den = d00 * d11 - d01 * d01; if (den == 0) return 0;
-  double v = (d11 * d20 - d01 * d21) / den, w = (d00 * d21 - d01 * d20) / den;
-  return v >= 0 && w >= 0 && v + w <= 1;
+/* triangle-triangle intersection [upstream FCL 0.7.0 Intersect::intersect_Triangle = PQP TriContact]: separating-axis
+ * test over 17 axes -- the two normals, the nine edge x edge products and the six in-plane edge normals (edge x own
+ * normal), which are the ones that decide COPLANAR triangles.  Closed sets: touching counts as intersecting
+ * (project6 separates only on a strict gap). */
+static int project6(const double *ax, const double *p1, const double *p2, const double *p3, const double *q1, const double *q2, const double *q3) {
+  double P1 = dot3(ax, p1), P2 = dot3(ax, p2), P3 = dot3(ax, p3), Q1 = dot3(ax, q1), Q2 = dot3(ax, q2), Q3 = dot3(ax, q3);
+  double mx1 = fmax(P1, fmax(P2, P3)), mn1 = fmin(P1, fmin(P2, P3)), mx2 = fmax(Q1, fmax(Q2, Q3)), mn2 = fmin(Q1, fmin(Q2, Q3));
+  if (mn1 > mx2) return 0;
+  if (mn2 > mx1) return 0;
+  return 1;
 }
 static int tri_tri(const double *A, const double *B) {
-  for (int e = 0; e < 3; e++) {
-    if (seg_tri(A + 3 * e, A + 3 * ((e + 1) % 3), B, B + 3, B + 6)) return 1;
-    if (seg_tri(B + 3 * e, B + 3 * ((e + 1) % 3), A, A + 3, A + 6)) return 1;
-  }
-  return 0;
+  double p1[3] = {0, 0, 0}, p2[3], p3[3], q1[3], q2[3], q3[3];
+  sub3(p2, A + 3, A); sub3(p3, A + 6, A); sub3(q1, B, A); sub3(q2, B + 3, A); sub3(q3, B + 6, A);
+  double e[3][3], f[3][3], n1[3], m1[3], ax[3];
+  sub3(e[0], p2, p1); sub3(e[1], p3, p2); sub3(e[2], p1, p3);
+  sub3(f[0], q2, q1); sub3(f[1], q3, q2); sub3(f[2], q1, q3);
+  cross3(n1, e[0], e[1]); cross3(m1, f[0], f[1]);
+  if (!project6(n1, p1, p2, p3, q1, q2, q3)) return 0;
+  if (!project6(m1, p1, p2, p3, q1, q2, q3)) return 0;
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { cross3(ax, e[i], f[j]); if (!project6(ax, p1, p2, p3, q1, q2, q3)) return 0; }
+  for (int i = 0; i < 3; i++) { cross3(ax, e[i], n1); if (!project6(ax, p1, p2, p3, q1, q2, q3)) return 0; }
+  for (int j = 0; j < 3; j++) { cross3(ax, f[j], m1); if (!project6(ax, p1, p2, p3, q1, q2, q3)) return 0; }
+  return 1;
 }
 static int mesh_mesh(const mpb_scene_desc *d, int oa, const xf_t *Ta, int ob, const xf_t *Tb) {
   int ma = d->obj_geom[oa], mb = d->obj_geom[ob];
@@ -1113,27 +1117,213 @@ int orc_pair_signed_distance(const mpb_scene_desc *d, const double *state, int p
   return 0;
 }
 
-/* min over admitted pairs of ::fcl::distance (distanceFull, src/planning_world.cpp:714-720) for
- * shape/shape pairs; -1 for touching/penetrating pairs as FCL returns with signed distance disabled. */
-int orc_distance_batch(const mpb_scene_desc *d, const double *states, int64_t n, double *min_dist, int32_t *argmin_pair) {
-  xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
-  xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
-  double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
-  int rc = 0;
-  for (int64_t i = 0; i < n; i++) {
-    scatter_state(d, states + i * d->state_dim, qf); fk_joints(d, qf, oMi); object_transforms(d, oMi, objT, NULL);
-    double best = DBL_MAX; int bi = -1; /* WorldDistanceResult::min_distance starts at max (src/planning_world.h:30-41) */
-    for (int p = 0; p < d->n_pairs; p++) {
-      int a = d->pair_a[p], b = d->pair_b[p];
-      if (d->obj_type[a] >= MPB_GEOM_MESH || d->obj_type[b] >= MPB_GEOM_MESH) { rc = MPB_ERR_UNSUPPORTED; continue; }
-      shape_t A, B; shape_from_object(d, a, &objT[a], &A); shape_from_object(d, b, &objT[b], &B);
-      double g = gjk_distance(&A, &B);
-      if (g < best) { best = g; bi = p; }
+/* ---- ::fcl::distance for pairs that involve a BVHModel or an OcTree (distance column): the minimum over
+ * the leaf primitives of the leaf distance -- what MeshShapeDistanceTraversalNode / OcTreeSolver::OcTree*DistanceRecurse /
+ * MeshDistanceTraversalNode compute with their bounding-volume pruning [upstream FCL 0.7.0].  Leaf distances:
+ *   shape x triangle, box(voxel) x shape, box(voxel) x triangle : GJK (shapeTriangleDistance / shapeDistance), -1 when
+ *                                                                touching or intersecting (signed distance disabled)
+ *   triangle x triangle (mesh x mesh)                          : TriangleDistance::triDistance, which returns 0 for
+ *                                                                overlapping triangles (not -1)
+ * Exhaustive over the leaves; a leaf is skipped only when a bounding-sphere lower bound already exceeds the running
+ * minimum (cannot change the result). */
+static void tri_shape(shape_t *t, const xf_t *T, const double *P0, const double *P1, const double *P2) {
+  memset(t, 0, sizeof(*t)); t->type = ORC_TRI; t->T = *T;
+  copy3(t->tri, P0); copy3(t->tri + 3, P1); copy3(t->tri + 6, P2);
+}
+static double tri_bound(const double *a, const double *b, const double *c, double *ctr) {
+  for (int k = 0; k < 3; k++) ctr[k] = (a[k] + b[k] + c[k]) / 3.0;
+  double d[3], r = 0, l;
+  sub3(d, a, ctr); l = len2_3(d); if (l > r) r = l;
+  sub3(d, b, ctr); l = len2_3(d); if (l > r) r = l;
+  sub3(d, c, ctr); l = len2_3(d); if (l > r) r = l;
+  return sqrt(r);
+}
+static double bvh_object_distance(const mpb_scene_desc *d, int a, const xf_t *Ta, int b, const xf_t *Tb) {
+  int ta = d->obj_type[a], tb = d->obj_type[b];
+  double best = DBL_MAX;
+  if (ta >= MPB_GEOM_MESH && tb >= MPB_GEOM_MESH) {
+    if (ta == MPB_GEOM_OCTREE && tb == MPB_GEOM_OCTREE) return DBL_MAX; /* not produced by the path */
+    if (ta == MPB_GEOM_OCTREE) { int t = a; a = b; b = t; const xf_t *T = Ta; Ta = Tb; Tb = T; tb = MPB_GEOM_OCTREE; }
+    /* a = mesh; b = mesh or octree */
+    int ma = d->obj_geom[a];
+    const double *Va = d->mesh_verts + 3 * d->mesh_vert_off[ma];
+    const int32_t *Ia = d->mesh_tris + 3 * d->mesh_tri_off[ma];
+    int na = d->mesh_tri_off[ma + 1] - d->mesh_tri_off[ma];
+    for (int i = 0; i < na; i++) {
+      double A[9], ca[3];
+      for (int k = 0; k < 3; k++) xf_apply(A + 3 * k, Ta, Va + 3 * Ia[3 * i + k]);
+      double ra = tri_bound(A, A + 3, A + 6, ca);
+      shape_t tA; xf_t I; xf_identity(&I); tri_shape(&tA, &I, A, A + 3, A + 6);
+      if (tb == MPB_GEOM_MESH) {
+        int mb = d->obj_geom[b];
+        const double *Vb = d->mesh_verts + 3 * d->mesh_vert_off[mb];
+        const int32_t *Ib = d->mesh_tris + 3 * d->mesh_tri_off[mb];
+        int nb = d->mesh_tri_off[mb + 1] - d->mesh_tri_off[mb];
+        for (int j = 0; j < nb; j++) {
+          double B[9], cb[3], dd[3];
+          for (int k = 0; k < 3; k++) xf_apply(B + 3 * k, Tb, Vb + 3 * Ib[3 * j + k]);
+          double rb = tri_bound(B, B + 3, B + 6, cb);
+          sub3(dd, ca, cb);
+          if (sqrt(len2_3(dd)) - ra - rb >= best) continue;
+          shape_t tB; tri_shape(&tB, &I, B, B + 3, B + 6);
+          double g = gjk_distance(&tA, &tB);
+          if (g < 0) g = 0.0; /* triDistance: overlapping triangles -> 0 */
+          if (g < best) best = g;
+        }
+      } else {
+        int t = d->obj_geom[b]; double res = d->oct_res[t];
+        const int32_t *C = d->oct_cells + 3 * d->oct_cell_off[t];
+        int nc = d->oct_cell_off[t + 1] - d->oct_cell_off[t];
+        shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+        double rb = 0.5 * res * sqrt(3.0);
+        for (int j = 0; j < nc; j++) {
+          double c[3] = {(C[3 * j] + 0.5) * res, (C[3 * j + 1] + 0.5) * res, (C[3 * j + 2] + 0.5) * res}, cw[3], dd[3];
+          xf_apply(cw, Tb, c); sub3(dd, ca, cw);
+          if (sqrt(len2_3(dd)) - ra - rb >= best && best >= 0) continue;
+          bx.T = *Tb; copy3(bx.T.p, cw);
+          double g = gjk_distance(&bx, &tA);
+          if (g < best) best = g;
+          if (best < 0) return -1.0;
+        }
+      }
     }
-    min_dist[i] = best; if (argmin_pair) argmin_pair[i] = bi;
+    return best;
   }
-  free(oMi); free(objT); free(qf);
-  return rc;
+  /* shape x mesh / octree */
+  int os = ta >= MPB_GEOM_MESH ? b : a, ob = ta >= MPB_GEOM_MESH ? a : b;
+  const xf_t *Ts = ta >= MPB_GEOM_MESH ? Tb : Ta, *To = ta >= MPB_GEOM_MESH ? Ta : Tb;
+  shape_t S; shape_from_object(d, os, Ts, &S);
+  double cl[3]; double rad = shape_bound_radius(d, os, cl);
+  if (d->obj_type[ob] == MPB_GEOM_OCTREE) {
+    int t = d->obj_geom[ob]; double res = d->oct_res[t];
+    const int32_t *C = d->oct_cells + 3 * d->oct_cell_off[t];
+    int nc = d->oct_cell_off[t + 1] - d->oct_cell_off[t];
+    shape_t bx; memset(&bx, 0, sizeof(bx)); bx.type = MPB_GEOM_BOX; bx.a = bx.b = bx.c = 0.5 * res;
+    double rb = 0.5 * res * sqrt(3.0);
+    for (int j = 0; j < nc; j++) {
+      double c[3] = {(C[3 * j] + 0.5) * res, (C[3 * j + 1] + 0.5) * res, (C[3 * j + 2] + 0.5) * res}, cw[3], dd[3];
+      xf_apply(cw, To, c); sub3(dd, Ts->p, cw);
+      if (sqrt(len2_3(dd)) - rad - rb >= best) continue;
+      bx.T = *To; copy3(bx.T.p, cw);
+      double g = gjk_distance(&bx, &S);
+      if (g < best) best = g;
+      if (best < 0) return -1.0;
+    }
+  } else {
+    int m = d->obj_geom[ob];
+    const double *V = d->mesh_verts + 3 * d->mesh_vert_off[m];
+    const int32_t *Tr = d->mesh_tris + 3 * d->mesh_tri_off[m];
+    int nt = d->mesh_tri_off[m + 1] - d->mesh_tri_off[m];
+    for (int t = 0; t < nt; t++) {
+      double A[9], ca[3], dd[3];
+      for (int k = 0; k < 3; k++) xf_apply(A + 3 * k, To, V + 3 * Tr[3 * t + k]);
+      double ra = tri_bound(A, A + 3, A + 6, ca);
+      sub3(dd, Ts->p, ca);
+      if (sqrt(len2_3(dd)) - rad - ra >= best) continue;
+      shape_t tri; tri_shape(&tri, To, V + 3 * Tr[3 * t], V + 3 * Tr[3 * t + 1], V + 3 * Tr[3 * t + 2]);
+      double g = gjk_distance(&S, &tri);
+      if (g < best) best = g;
+      if (best < 0) return -1.0;
+    }
+  }
+  return best;
+}
+
+/* closest distance between two segments (Ericson 5.1.9) and the closed-form triangle-triangle distance built from it
+ * (6 vertex-face + 9 edge-edge candidates; valid when the triangles are disjoint): an INDEPENDENT check of the GJK leaf
+ * distance above (tests/test_oracle_distance.py). */
+static double seg_seg_dist2(const double *p1, const double *q1, const double *p2, const double *q2) {
+  double d1[3], d2[3], r[3]; sub3(d1, q1, p1); sub3(d2, q2, p2); sub3(r, p1, p2);
+  double a = len2_3(d1), e = len2_3(d2), f = dot3(d2, r), s, t;
+  if (a <= 1e-300 && e <= 1e-300) return len2_3(r);
+  if (a <= 1e-300) { s = 0; t = f / e; t = t < 0 ? 0 : (t > 1 ? 1 : t); }
+  else {
+    double c = dot3(d1, r);
+    if (e <= 1e-300) { t = 0; s = -c / a; s = s < 0 ? 0 : (s > 1 ? 1 : s); }
+    else {
+      double b = dot3(d1, d2), den = a * e - b * b;
+      s = den != 0 ? (b * f - c * e) / den : 0; s = s < 0 ? 0 : (s > 1 ? 1 : s);
+      t = (b * s + f) / e;
+      if (t < 0) { t = 0; s = -c / a; s = s < 0 ? 0 : (s > 1 ? 1 : s); }
+      else if (t > 1) { t = 1; s = (b - c) / a; s = s < 0 ? 0 : (s > 1 ? 1 : s); }
+    }
+  }
+  double c1[3] = {p1[0] + d1[0] * s, p1[1] + d1[1] * s, p1[2] + d1[2] * s}, c2[3] = {p2[0] + d2[0] * t, p2[1] + d2[1] * t, p2[2] + d2[2] * t}, dd[3];
+  sub3(dd, c1, c2); return len2_3(dd);
+}
+double orc_tri_tri_distance_closed(const double *A, const double *B) {
+  double best = DBL_MAX;
+  for (int i = 0; i < 3; i++) {
+    double v = point_tri_dist2(A + 3 * i, B, B + 3, B + 6, NULL); if (v < best) best = v;
+    v = point_tri_dist2(B + 3 * i, A, A + 3, A + 6, NULL); if (v < best) best = v;
+    for (int j = 0; j < 3; j++) { v = seg_seg_dist2(A + 3 * i, A + 3 * ((i + 1) % 3), B + 3 * j, B + 3 * ((j + 1) % 3)); if (v < best) best = v; }
+  }
+  return sqrt(best);
+}
+double orc_tri_tri_distance_gjk(const double *A, const double *B) {
+  shape_t tA, tB; xf_t I; xf_identity(&I);
+  tri_shape(&tA, &I, A, A + 3, A + 6); tri_shape(&tB, &I, B, B + 3, B + 6);
+  return gjk_distance(&tA, &tB);
+}
+int orc_tri_tri_intersect(const double *A, const double *B) { return tri_tri(A, B); }
+/* INDEPENDENT intersection test (shares nothing with the SAT above): an edge of one triangle pierces the other
+ * (segment / plane intersection + barycentric containment), or -- coplanar and touching configurations -- one of the
+ * vertex-face / edge-edge distance candidates is zero. */
+static int seg_pierces_tri(const double *p, const double *q, const double *a, const double *b, const double *c) {
+  double ab[3], ac[3], n[3], pq[3], ap[3];
+  sub3(ab, b, a); sub3(ac, c, a); cross3(n, ab, ac); sub3(pq, q, p); sub3(ap, p, a);
+  double dn = dot3(n, pq), t = -dot3(n, ap);
+  if (dn == 0) return 0;
+  t /= dn; if (t < 0 || t > 1) return 0;
+  double x[3] = {p[0] + t * pq[0] - a[0], p[1] + t * pq[1] - a[1], p[2] + t * pq[2] - a[2]};
+  double d00 = dot3(ab, ab), d01 = dot3(ab, ac), d11 = dot3(ac, ac), d20 = dot3(x, ab), d21 = dot3(x, ac);
+  double den = d00 * d11 - d01 * d01; if (den == 0) return 0;
+  double v = (d11 * d20 - d01 * d21) / den, w = (d00 * d21 - d01 * d20) / den;
+  return v >= 0 && w >= 0 && v + w <= 1;
+}
+int orc_tri_tri_intersect_independent(const double *A, const double *B, double zero_tol) {
+  for (int e = 0; e < 3; e++) {
+    if (seg_pierces_tri(A + 3 * e, A + 3 * ((e + 1) % 3), B, B + 3, B + 6)) return 1;
+    if (seg_pierces_tri(B + 3 * e, B + 3 * ((e + 1) % 3), A, A + 3, A + 6)) return 1;
+  }
+  return orc_tri_tri_distance_closed(A, B) <= zero_tol;
+}
+
+/* ::fcl::distance of one admitted pair in world poses */
+static double object_distance(const mpb_scene_desc *d, int a, const xf_t *Ta, int b, const xf_t *Tb) {
+  if (d->obj_type[a] >= MPB_GEOM_MESH || d->obj_type[b] >= MPB_GEOM_MESH) return bvh_object_distance(d, a, Ta, b, Tb);
+  shape_t A, B; shape_from_object(d, a, Ta, &A); shape_from_object(d, b, Tb, &B);
+  return gjk_distance(&A, &B);
+}
+
+/* min over admitted pairs of ::fcl::distance (distanceFull, src/planning_world.cpp:714-720); -1 for touching /
+ * penetrating pairs as FCL returns with signed distance disabled (0 for overlapping mesh x mesh, see above).
+ * pair_dist: nullable [n][n_pairs], the distance of every pair. */
+int orc_distance_batch_ex(const mpb_scene_desc *d, const double *states, int64_t n, double *min_dist, int32_t *argmin_pair, double *pair_dist, int nthreads) {
+  if (nthreads < 1) nthreads = 1;
+#pragma omp parallel num_threads(nthreads)
+  {
+    xf_t *oMi = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_joints + 1));
+    xf_t *objT = (xf_t *)malloc(sizeof(xf_t) * (size_t)(d->n_objects > 0 ? d->n_objects : 1));
+    double *qf = (double *)malloc(sizeof(double) * (size_t)(d->nq_full > 0 ? d->nq_full : 1));
+#pragma omp for schedule(dynamic, 1)
+    for (int64_t i = 0; i < n; i++) {
+      scatter_state(d, states + i * d->state_dim, qf); fk_joints(d, qf, oMi); object_transforms(d, oMi, objT, NULL);
+      double best = DBL_MAX; int bi = -1; /* WorldDistanceResult::min_distance starts at max (src/planning_world.h:30-41) */
+      for (int p = 0; p < d->n_pairs; p++) {
+        int a = d->pair_a[p], b = d->pair_b[p];
+        double g = object_distance(d, a, &objT[a], b, &objT[b]);
+        if (pair_dist) pair_dist[i * d->n_pairs + p] = g;
+        if (g < best) { best = g; bi = p; }
+      }
+      min_dist[i] = best; if (argmin_pair) argmin_pair[i] = bi;
+    }
+    free(oMi); free(objT); free(qf);
+  }
+  return 0;
+}
+int orc_distance_batch(const mpb_scene_desc *d, const double *states, int64_t n, double *min_dist, int32_t *argmin_pair) {
+  return orc_distance_batch_ex(d, states, n, min_dist, argmin_pair, NULL, 1);
 }
 
 /* ------------------------------------------------------------------ independent exact check: SAT on polytopes

@@ -118,14 +118,37 @@ def sat_batch(desc, states, item_state, item_pair, threads=8):
     return out
 
 
-def distance_batch(desc, states):
+def distance_batch(desc, states, threads=1, return_pairs=False):
+    """min over the admitted pairs of ::fcl::distance (-1: some pair touches / intersects) + arg-min pair; mesh and
+    octree pairs by exhaustive leaf minimum.  return_pairs: also the [n, n_pairs] matrix of pair distances."""
     s = _states(desc, states)
     n = s.shape[0]
     md = np.zeros(n, dtype=np.float64)
     am = np.zeros(n, dtype=np.int32)
-    lib().orc_distance_batch(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(md.ctypes.data),
-                             C.c_void_p(am.ctypes.data))
+    pd = np.zeros((n, max(desc.n_pairs, 1)), dtype=np.float64) if return_pairs else None
+    lib().orc_distance_batch_ex(C.byref(desc.as_struct()), C.c_void_p(s.ctypes.data), C.c_int64(n), C.c_void_p(md.ctypes.data),
+                                C.c_void_p(am.ctypes.data), C.c_void_p(pd.ctypes.data if return_pairs else None), C.c_int(int(threads)))
+    if return_pairs:
+        return md, am, pd[:, : desc.n_pairs]
     return md, am
+
+
+def tri_tri_distance(A, B, closed=True):
+    """Distance of two triangles ([3, 3] each): closed form (vertex-face + edge-edge) or the GJK the oracle's leaves use."""
+    A = np.ascontiguousarray(np.asarray(A, dtype=np.float64).reshape(9))
+    B = np.ascontiguousarray(np.asarray(B, dtype=np.float64).reshape(9))
+    f = lib().orc_tri_tri_distance_closed if closed else lib().orc_tri_tri_distance_gjk
+    f.restype = C.c_double
+    return float(f(C.c_void_p(A.ctypes.data), C.c_void_p(B.ctypes.data)))
+
+
+def tri_tri_intersect(A, B, independent=False):
+    """SAT of FCL / PQP (default) or the independent edge-piercing + zero-distance-candidate test."""
+    A = np.ascontiguousarray(np.asarray(A, dtype=np.float64).reshape(9))
+    B = np.ascontiguousarray(np.asarray(B, dtype=np.float64).reshape(9))
+    if independent:
+        return bool(lib().orc_tri_tri_intersect_independent(C.c_void_p(A.ctypes.data), C.c_void_p(B.ctypes.data), C.c_double(1e-12)))
+    return bool(lib().orc_tri_tri_intersect(C.c_void_p(A.ctypes.data), C.c_void_p(B.ctypes.data)))
 
 
 def _T12(T):
