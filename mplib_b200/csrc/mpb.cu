@@ -132,6 +132,7 @@ struct mpb_scene {
   bool smem_verts = true;
   int narrow_blocks = 0;
   int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0}, sphere_blocks_blk[2] = {0, 0};
+  int expand_lane_blocks = 0;
   int sphere_cb = 4;         // tiles of 32 configurations per warp of sphere_blk_kernel (large cull tables)  // one resident wave of the static grid-stride kernels, per MODE
   std::vector<cudaEvent_t> events;
   // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
@@ -976,6 +977,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<1, 0, 0>, 128, 0)); s->sphere_blocks[1] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<0>, 128, 0)); s->dense_blocks[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<1>, 128, 0)); s->dense_blocks[1] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_lane_kernel, 128, 0)); s->expand_lane_blocks = s->num_sms * std::max(b, 1);
   }
   *out = s;
   return MPB_OK;
@@ -1295,7 +1297,9 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   }
   if (s->img.expand_bin >= 0) {  // shape x mesh / octree pairs: expand to leaf items, second narrowphase round
     pass_reset_kernel<<<1, 256, 0, st>>>(s->wq, nb);
-    expand_kernel<<<grid_for(s->num_sms * 8, 16), 128, 0, st>>>(s->img, s->wq, out);
+    static const int lane_on = !(getenv("MPB_EXPAND_WARP") && atoi(getenv("MPB_EXPAND_WARP")));
+    expand_kernel<<<grid_for(s->num_sms * 8, 16), 128, 0, st>>>(s->img, s->wq, out, small ? 0 : lane_on);
+    if (!small && lane_on) { expand_lane_kernel<<<s->expand_lane_blocks, 128, 0, st>>>(s->img, s->wq, out); *launches += 1; }
     scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor), s->sq_cap);
     scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1);
     if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);

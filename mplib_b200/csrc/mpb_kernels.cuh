@@ -1319,7 +1319,8 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fm
 // lets the lanes that hold surviving leaves test / emit their primitives.  No divergence inside the 15-axis test and
 // a short critical path even for small batches (a planning round); when the stack runs nearly full the warp pops
 // one node per trip (depth-first), which bounds the growth by the tree depth.
-__global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, HitOut out) {
+#define MPB_EXPL_MIN_ITEMS 32768u  // items in the bin from which expand_lane_kernel runs instead of expand_kernel
+__global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, HitOut out, int lane_variant_on) {
   __shared__ int s_stack[4][MPB_EXP_STACK];
   const int eb = img.expand_bin;
   if (eb < 0) return;
@@ -1327,6 +1328,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int *stack = s_stack[warp];
   const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
+  if (lane_variant_on && end - first >= MPB_EXPL_MIN_ITEMS) return;  // expand_lane_kernel takes large bins
   for (;;) {
     // four items per ticket; lanes 0..3 fetch their (configuration, pair, already-known) in parallel
     unsigned it0 = 0;
@@ -1467,6 +1469,248 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
     __syncwarp();
     }  // sub-items of the ticket
   }
+}
+
+// Lane per item: the throughput variant of expand_kernel for passes with many items (a collide call over 10^5+
+// configurations).  A lane walks its own item's tree depth-first with a private stack in shared memory ([depth][thread],
+// conflict-free), one node per trip: pop a node whose bounds already passed and fetch + test its two children (two
+// independent loads in flight; the survivors are pushed, the one nearer to the shape's inscribed ball on top, so an item
+// that collides meets its decisive leaves first).  LEAVES are not tested by the lane that finds them: their
+// primitives go to a per-warp queue and are tested 32 at a time by the whole warp (exact OBB test, inscribed-ball
+// shortcut, emission of the leaf item), each lane reading the owner's item record from shared memory.  The first version
+// tested leaves in place and ran its leaf code -- 60 % of its instructions -- on two lanes of 32
+// (profiles/r02_ncu_expand_lane_v1_source.csv).  Lanes are persistent: idle lanes take the next items of the bin.
+// The warp-per-item kernel stays for small passes (planning rounds), where the critical path of a single traversal
+// matters more than throughput; both are launched, the item count of the bin decides which one runs.
+#define MPB_EXPL_DEPTH 40     // per-lane stack entries (the tree depth is ~17 for 10^5 leaves; DFS holds at most depth + 1)
+#define MPB_EXPL_QCAP 128     // leaf-primitive queue entries per warp
+#define MPB_EXPL_BINS 64      // second-round bins counted in shared memory
+#define MPB_EXPL_F 31         // floats of an item record: R 9, t 3, Ra 9, ca 3, cin 3, ah 3, rin2
+
+struct ExpShared {
+  int stack[MPB_EXPL_DEPTH][128];
+  float item[MPB_EXPL_F][128];  // [field][thread]: lanes of the warp read each other's record in the leaf phase
+  int meta[4][128];             // cfg, pair, leaf type, second-round bin
+  int hitflag[128];             // set by the leaf phase: this lane's item collides, stop its traversal
+  uint2 queue[4][MPB_EXPL_QCAP];  // per warp: (owner thread, primitive)
+  unsigned bins[MPB_EXPL_BINS];
+};
+
+// squared distance from point c to the box (centre, half extents) of a node
+__device__ __forceinline__ float exp_node_dist2(const DevBvhNode &nd, const float *c) {
+  const float d0 = fmaxf(fabsf(nd.c[0] - c[0]) - nd.h[0], 0.f), d1 = fmaxf(fabsf(nd.c[1] - c[1]) - nd.h[1], 0.f), d2 = fmaxf(fabsf(nd.c[2] - c[2]) - nd.h[2], 0.f);
+  return fmaf(d0, d0, fmaf(d1, d1, d2 * d2));
+}
+__device__ __forceinline__ bool exp_box_pass(const DevBvhNode &nd, const float *ca, const float *bh) {
+  return fabsf(nd.c[0] - ca[0]) <= nd.h[0] + bh[0] && fabsf(nd.c[1] - ca[1]) <= nd.h[1] + bh[1] && fabsf(nd.c[2] - ca[2]) <= nd.h[2] + bh[2];
+}
+
+// Warp-cooperative leaf phase: entries [q0, q0 + nb) of the warp's queue, one per lane.
+__device__ __forceinline__ void exp_leaf_batch(const SceneImg &img, const WorkQ &wq, const HitOut &out, ExpShared &S, const uint2 *q, int nb,
+                                               unsigned lane, bool smem_bins) {
+  const unsigned FULL = 0xffffffffu;
+  bool emit = false, hit = false;
+  int o = 0, prim = 0;
+  if ((int)lane < nb) {
+    const uint2 e = q[lane];
+    o = (int)e.x;
+    prim = (int)e.y;
+    if (!S.hitflag[o]) {
+      const int leaf_type = S.meta[2][o];
+      const float4 a = __ldg(img.prims + 3 * prim), b = __ldg(img.prims + 3 * prim + 1);
+      float pc[3], ph[3];
+      if (leaf_type == MPB_GEOM_VBOX) {
+        pc[0] = a.x; pc[1] = a.y; pc[2] = a.z; ph[0] = b.x; ph[1] = b.y; ph[2] = b.z;
+      } else {
+        const float4 c = __ldg(img.prims + 3 * prim + 2);
+        const float lo0 = fminf(a.x, fminf(b.x, c.x)), hi0 = fmaxf(a.x, fmaxf(b.x, c.x));
+        const float lo1 = fminf(a.y, fminf(b.y, c.y)), hi1 = fmaxf(a.y, fmaxf(b.y, c.y));
+        const float lo2 = fminf(a.z, fminf(b.z, c.z)), hi2 = fmaxf(a.z, fmaxf(b.z, c.z));
+        pc[0] = 0.5f * (lo0 + hi0); pc[1] = 0.5f * (lo1 + hi1); pc[2] = 0.5f * (lo2 + hi2);
+        ph[0] = 0.5f * (hi0 - lo0) + 1e-6f; ph[1] = 0.5f * (hi1 - lo1) + 1e-6f; ph[2] = 0.5f * (hi2 - lo2) + 1e-6f;
+      }
+      float Ra[9], ah[3], tr[3], Rrel[9];
+#pragma unroll
+      for (int k = 0; k < 9; k++) Ra[k] = S.item[12 + k][o];
+#pragma unroll
+      for (int k = 0; k < 3; k++) ah[k] = S.item[27 + k][o];
+      const float g0 = pc[0] - S.item[21][o], g1 = pc[1] - S.item[22][o], g2 = pc[2] - S.item[23][o];
+#pragma unroll
+      for (int r = 0; r < 3; r++) {
+        tr[r] = fmaf(Ra[r], g0, fmaf(Ra[3 + r], g1, Ra[6 + r] * g2));
+#pragma unroll
+        for (int c = 0; c < 3; c++) Rrel[3 * r + c] = Ra[3 * c + r];
+      }
+      if (!obb_disjoint(Rrel, tr, ah, ph)) {  // primitive-level reject: the exact OBB test
+        emit = true;
+        const float rin2 = S.item[30][o];
+        if (leaf_type == MPB_GEOM_VBOX && rin2 > 0.f) {  // sufficient test: cell touches the inscribed ball
+          const float c0 = S.item[24][o], c1 = S.item[25][o], c2 = S.item[26][o];
+          const float q0 = clampf(c0, pc[0] - ph[0], pc[0] + ph[0]) - c0;
+          const float q1 = clampf(c1, pc[1] - ph[1], pc[1] + ph[1]) - c1;
+          const float q2 = clampf(c2, pc[2] - ph[2], pc[2] + ph[2]) - c2;
+          if (fmaf(q0, q0, fmaf(q1, q1, q2 * q2)) < rin2) { hit = true; emit = false; }
+        }
+      }
+    }
+  }
+  if (hit) {
+    S.hitflag[o] = 1;
+    report_hit(out, (unsigned)S.meta[0][o], S.meta[1][o]);
+  }
+  const unsigned em = __ballot_sync(FULL, emit);
+  if (em) {
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(&wq.totals[0], (unsigned)__popc(em));
+    base = __shfl_sync(FULL, base, 0);
+    if (emit) {
+      const unsigned slot = base + __popc(em & ((1u << lane) - 1u));
+      if (slot < wq.cap) {
+#pragma unroll
+        for (int k2 = 0; k2 < 12; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = S.item[k2][o];
+        wq.scfg[slot] = S.meta[0][o];
+        wq.spair[slot] = S.meta[1][o];
+        wq.saux[slot] = prim;
+        const int bin2 = S.meta[3][o];
+        if (smem_bins) atomicAdd(&S.bins[bin2], 1u);
+        else atomicAdd(&wq.bin_count[bin2], 1u);
+      }
+    }
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(128) expand_lane_kernel(SceneImg img, WorkQ wq, HitOut out) {
+  __shared__ ExpShared S;
+  const int eb = img.expand_bin;
+  if (eb < 0) return;
+  const unsigned first = wq.bin_start[eb], end = min(wq.bin_start[eb + 1], wq.cap);
+  if (end - first < MPB_EXPL_MIN_ITEMS) return;  // expand_kernel (warp per item) handles small bins
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tid = threadIdx.x;
+  const bool smem_bins = img.n_bins2 <= MPB_EXPL_BINS;
+  for (int b = tid; b < MPB_EXPL_BINS; b += blockDim.x) S.bins[b] = 0;
+  S.hitflag[tid] = 0;
+  __syncthreads();
+  int *stack = &S.stack[0][tid];  // entry d at stack[d * 128]
+  uint2 *queue = S.queue[warp];
+  unsigned long long drop_sum = 0;
+  bool busy = false, drained = false;  // drained: the bin has no more items (warp-uniform)
+  int sp = 0, qn = 0;                  // qn: entries in the warp's leaf queue (warp-uniform)
+  float ca[3] = {0.f, 0.f, 0.f}, bh[3] = {0.f, 0.f, 0.f}, cin[3] = {0.f, 0.f, 0.f};
+  for (;;) {
+    if (busy && S.hitflag[tid]) { busy = false; sp = 0; }  // a leaf of this lane's item was an immediate hit
+    // ---- refill: idle lanes take the next items of the bin (one ticket per warp and refill; the refill block is long, so
+    // it runs only when a quarter of the warp is idle, or nobody has work)
+    const unsigned need = __ballot_sync(FULL, !busy);
+    if (!drained && (__popc(need) >= 8 || need == FULL)) {
+      // queued leaves refer to the records of their owner lanes: test them before any record is replaced
+      while (qn > 0) { const int nb = min(qn, 32); exp_leaf_batch(img, wq, out, S, queue + qn - nb, nb, lane, smem_bins); qn -= nb; }
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&wq.totals[5], (unsigned)__popc(need));
+      base = first + __shfl_sync(FULL, base, 0);
+      if (base + __popc(need) >= end) drained = true;
+      const unsigned my = base + __popc(need & ((1u << lane) - 1u));
+      if (!busy && my < end) {
+        const int cfg = wq.icfg[my], p = wq.ipair[my];
+        const DevPair pr = img.pairs[p];
+        const DevObject &A = img.objs[pr.a];  // the shape
+        const DevObject &B = img.objs[pr.b];  // the BVH object
+        if (B.voff >= 0 && !hit_known(out, (unsigned)cfg, p)) {
+          float R[9], t[3], Ra[9];
+#pragma unroll
+          for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + my];
+#pragma unroll
+          for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + my];
+          {  // shape OBB in the object frame B:  x_B = R^T (x_A - t)
+            const float d0 = A.oc[0] - t[0], d1 = A.oc[1] - t[1], d2 = A.oc[2] - t[2];
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+              ca[r] = fmaf(R[r], d0, fmaf(R[3 + r], d1, R[6 + r] * d2));
+#pragma unroll
+              for (int c = 0; c < 3; c++) Ra[3 * r + c] = fmaf(R[r], A.oR[c], fmaf(R[3 + r], A.oR[3 + c], R[6 + r] * A.oR[6 + c]));
+            }
+            const float e0 = A.ctr[0] - t[0], e1 = A.ctr[1] - t[1], e2 = A.ctr[2] - t[2];
+#pragma unroll
+            for (int r = 0; r < 3; r++) cin[r] = fmaf(R[r], e0, fmaf(R[3 + r], e1, R[6 + r] * e2));
+          }
+#pragma unroll
+          for (int r = 0; r < 3; r++)
+            bh[r] = fmaf(fabsf(Ra[3 * r]), A.oh[0], fmaf(fabsf(Ra[3 * r + 1]), A.oh[1], fabsf(Ra[3 * r + 2]) * A.oh[2])) + 1e-5f;
+          const DevBvhNode root = img.nodes[B.voff];
+          if (exp_box_pass(root, ca, bh)) {
+#pragma unroll
+            for (int k = 0; k < 9; k++) { S.item[k][tid] = R[k]; S.item[12 + k][tid] = Ra[k]; }
+#pragma unroll
+            for (int k = 0; k < 3; k++) { S.item[9 + k][tid] = t[k]; S.item[21 + k][tid] = ca[k]; S.item[24 + k][tid] = cin[k]; S.item[27 + k][tid] = A.oh[k]; }
+            S.item[30][tid] = A.rin * A.rin;
+            S.meta[0][tid] = cfg; S.meta[1][tid] = p; S.meta[2][tid] = B.vcnt; S.meta[3][tid] = img.pair_bin2[p];
+            S.hitflag[tid] = 0;
+            stack[0] = B.voff;
+            sp = 1;
+            busy = true;
+          }
+        }
+      }
+      __syncwarp();
+    }
+    if (__ballot_sync(FULL, busy) == 0) {
+      while (qn > 0) { const int nb = min(qn, 32); exp_leaf_batch(img, wq, out, S, queue + qn - nb, nb, lane, smem_bins); qn -= nb; }
+      if (drained) break;
+      continue;
+    }
+    // ---- one node of every busy lane's traversal
+    int n_leaf = 0, leaf_first = 0;
+    if (busy) {
+      const int node = stack[(sp - 1) * 128];
+      sp--;
+      const DevBvhNode nd = img.nodes[node];
+      if (nd.left >= 0) {
+        const DevBvhNode nl = img.nodes[nd.left], nr = img.nodes[nd.right];
+        const bool pl = exp_box_pass(nl, ca, bh), prt = exp_box_pass(nr, ca, bh);
+        if (sp + 2 > MPB_EXPL_DEPTH) {  // cannot happen for a tree of depth < MPB_EXPL_DEPTH; conservative if it does
+          drop_sum++;
+          S.hitflag[tid] = 1;
+          report_hit(out, (unsigned)S.meta[0][tid], S.meta[1][tid]);
+        } else {
+          const bool left_first = exp_node_dist2(nl, cin) <= exp_node_dist2(nr, cin);
+          const int c_far = left_first ? nd.right : nd.left, c_near = left_first ? nd.left : nd.right;
+          const bool p_far = left_first ? prt : pl, p_near = left_first ? pl : prt;
+          if (p_far) { stack[sp * 128] = c_far; sp++; }
+          if (p_near) { stack[sp * 128] = c_near; sp++; }
+        }
+      } else {
+        leaf_first = ~nd.left;
+        n_leaf = nd.right;
+      }
+      if (sp == 0) busy = false;  // its queued leaves are tested before the lane's record is replaced
+    }
+    // ---- leaf primitives -> the warp's queue (prefix sum of the per-lane counts)
+    unsigned incl = (unsigned)n_leaf;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned tt = __shfl_up_sync(FULL, incl, o);
+      if ((int)lane >= o) incl += tt;
+    }
+    const int tot = (int)__shfl_sync(FULL, incl, 31);
+    if (tot) {
+      if (qn + tot > MPB_EXPL_QCAP) {  // make room first (a trip adds at most 32 x leaf size entries)
+        while (qn > 0) { const int nb = min(qn, 32); exp_leaf_batch(img, wq, out, S, queue + qn - nb, nb, lane, smem_bins); qn -= nb; }
+      }
+      int pos = qn + (int)incl - n_leaf;
+      for (int k = 0; k < n_leaf; k++)
+        if (pos + k < MPB_EXPL_QCAP) queue[pos + k] = make_uint2((unsigned)tid, (unsigned)(leaf_first + k));
+      qn = min(qn + tot, MPB_EXPL_QCAP);
+      __syncwarp();
+      while (qn >= 32) { exp_leaf_batch(img, wq, out, S, queue + qn - 32, 32, lane, smem_bins); qn -= 32; }
+    }
+  }
+  if (drop_sum) atomicAdd(&wq.counters[2], drop_sum);
+  __syncthreads();
+  if (smem_bins)
+    for (int b = tid; b < img.n_bins2; b += blockDim.x)
+      if (S.bins[b]) atomicAdd(&wq.bin_count[b], S.bins[b]);
 }
 
 // ---------------------------------------------------------------------------------------------- BVH x BVH

@@ -262,3 +262,25 @@ def test_mesh_links_vs_mesh_octree_and_primitives():
     add_c3_primitives(w, 2)
     ov = _mesh_parity(w, random_q(300, 32), 12)
     assert ov.mean() > 0.05
+
+
+def test_expand_variants_agree_and_match_oracle():
+    """A large pass takes the lane-per-item expansion (expand_lane_kernel) and the thread-per-configuration sphere phase,
+    small passes the warp-per-item expansion and the thread-per-pair sphere phase: bit-identical pair masks, and the
+    large pass against the oracle."""
+    from oracle import oracle as O
+    from tests.workloads import c3_world
+
+    w = c3_world()
+    dev = w._sync()["dev"]
+    q = random_q(24000, 31)
+    v, ph, st = dev.collide(q, want_pairs=True, stats=True)
+    for k in range(0, 24000, 8000):
+        v2, ph2 = dev.collide(q[k:k + 2000], want_pairs=True)
+        assert np.array_equal(ph[k:k + 2000], ph2) and np.array_equal(v[k:k + 2000], v2)
+    qd = q[:6000].astype(np.float32).astype(np.float64)
+    ov, oph = O.collide_batch(dev.desc, qd, threads=8)
+    mism = np.argwhere(ph[:6000] != oph)
+    for i, p in mism:
+        assert abs(O.pair_signed_distance(dev.desc, qd[i], int(p))) < BAND
+    assert len(mism) <= 30 and st["narrow_capped"] == 0
