@@ -427,6 +427,83 @@ static void build_cell_table_uncached(const double *V, int nv, std::vector<unsig
   memcpy(out.data() + 2 * (MPB_CELL_COUNT + 1), cand.data(), cand.size());
 }
 
+// ---- inner balls: up to MPB_INNER_BALLS balls that lie inside a shape (object frame).  If a ball of A intersects B
+// (exactly, for a primitive B; or a ball of B otherwise) the two shapes intersect: scatter_kernel settles such items
+// without the narrowphase.  Radii are shrunk by 2 % so that fp32 rounding of the poses cannot turn "inside" into "outside".
+static void set_ball(DevObject &O, int k, double x, double y, double z, double r) {
+  O.ball[k] = make_float4((float)x, (float)y, (float)z, r > 0 ? (float)(0.98 * r) : 0.f);
+}
+static void primitive_balls(DevObject &O) {
+  for (int k = 0; k < MPB_INNER_BALLS; k++) O.ball[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  switch (O.type) {
+    case MPB_GEOM_SPHERE: set_ball(O, 0, 0, 0, 0, O.prm[0]); break;
+    case MPB_GEOM_BOX: {  // balls of the smallest half side along the longest axis
+      const double h[3] = {O.prm[0], O.prm[1], O.prm[2]};
+      int ax = 0;
+      if (h[1] > h[ax]) ax = 1;
+      if (h[2] > h[ax]) ax = 2;
+      const double r = std::min(h[0], std::min(h[1], h[2])), span = h[ax] - r;
+      for (int k = 0; k < MPB_INNER_BALLS; k++) {
+        double c[3] = {0, 0, 0};
+        c[ax] = MPB_INNER_BALLS > 1 ? -span + 2.0 * span * k / (MPB_INNER_BALLS - 1) : 0.0;
+        set_ball(O, k, c[0], c[1], c[2], r);
+      }
+    } break;
+    case MPB_GEOM_CAPSULE:
+      for (int k = 0; k < MPB_INNER_BALLS; k++) set_ball(O, k, 0, 0, -O.prm[1] + 2.0 * O.prm[1] * k / (MPB_INNER_BALLS - 1), O.prm[0]);
+      break;
+    case MPB_GEOM_CYLINDER: {
+      const double r = std::min(O.prm[0], O.prm[1]), span = O.prm[1] - r;
+      for (int k = 0; k < MPB_INNER_BALLS; k++) set_ball(O, k, 0, 0, -span + 2.0 * span * k / (MPB_INNER_BALLS - 1), r);
+    } break;
+    default: break;
+  }
+}
+// convex hull (vertices V, triangle faces F): the signed distance to the nearest face plane on a grid over the bounding box;
+// greedy choice of the largest ball, then of the largest balls whose centres lie outside the balls chosen so far
+static void hull_balls(const double *V, int nv, const int32_t *F, int nf, float4 *out) {
+  for (int k = 0; k < MPB_INNER_BALLS; k++) out[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (nv < 4 || nf < 4) return;
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, ctr[3] = {0, 0, 0};
+  for (int i = 0; i < nv; i++)
+    for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], V[3 * i + a]); hi[a] = std::max(hi[a], V[3 * i + a]); ctr[a] += V[3 * i + a] / nv; }
+  std::vector<std::array<double, 4>> planes;  // outward unit normal, offset: n.x <= d inside
+  for (int f = 0; f < nf; f++) {
+    const double *A0 = V + 3 * F[3 * f], *A1 = V + 3 * F[3 * f + 1], *A2 = V + 3 * F[3 * f + 2];
+    double e1[3], e2[3], n[3];
+    for (int a = 0; a < 3; a++) { e1[a] = A1[a] - A0[a]; e2[a] = A2[a] - A0[a]; }
+    n[0] = e1[1] * e2[2] - e1[2] * e2[1]; n[1] = e1[2] * e2[0] - e1[0] * e2[2]; n[2] = e1[0] * e2[1] - e1[1] * e2[0];
+    const double l = sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    if (l < 1e-14) continue;
+    for (int a = 0; a < 3; a++) n[a] /= l;
+    double d = n[0] * A0[0] + n[1] * A0[1] + n[2] * A0[2];
+    if (n[0] * ctr[0] + n[1] * ctr[1] + n[2] * ctr[2] > d) { for (int a = 0; a < 3; a++) n[a] = -n[a]; d = -d; }  // orient away from the interior point
+    planes.push_back({n[0], n[1], n[2], d});
+  }
+  const int G = 14;
+  std::vector<std::array<double, 4>> cand;
+  for (int ix = 0; ix < G; ix++)
+    for (int iy = 0; iy < G; iy++)
+      for (int iz = 0; iz < G; iz++) {
+        const double x[3] = {lo[0] + (hi[0] - lo[0]) * (ix + 0.5) / G, lo[1] + (hi[1] - lo[1]) * (iy + 0.5) / G, lo[2] + (hi[2] - lo[2]) * (iz + 0.5) / G};
+        double r = 1e300;
+        for (const auto &pl : planes) r = std::min(r, pl[3] - (pl[0] * x[0] + pl[1] * x[1] + pl[2] * x[2]));
+        if (r > 0) cand.push_back({x[0], x[1], x[2], r});
+      }
+  std::sort(cand.begin(), cand.end(), [](const std::array<double, 4> &a, const std::array<double, 4> &b) { return a[3] > b[3]; });
+  int n_out = 0;
+  for (const auto &c : cand) {
+    if (n_out == MPB_INNER_BALLS) break;
+    if (n_out > 0 && c[3] < 0.35 * out[0].w) break;  // small balls settle nothing the large ones do not
+    bool ok = true;
+    for (int k = 0; k < n_out && ok; k++) {
+      const double dx = c[0] - out[k].x, dy = c[1] - out[k].y, dz = c[2] - out[k].z;
+      ok = sqrt(dx * dx + dy * dy + dz * dz) >= 0.9 * out[k].w;
+    }
+    if (ok) out[n_out++] = make_float4((float)c[0], (float)c[1], (float)c[2], (float)(0.98 * c[3]));
+  }
+}
+
 // parameters, OBB, bounding sphere and inscribed ball of a primitive (object frame); p = obj_param of include/mpb.h
 static void primitive_bounds(DevObject &O, const double *p) {
   switch (O.type) {
@@ -454,6 +531,7 @@ static void primitive_bounds(DevObject &O, const double *p) {
       break;
     default: break;
   }
+  primitive_balls(O);
 }
 
 // Everything of an object that depends on its pose L: sphere centres in the world / owner-joint frame, the cull
@@ -874,6 +952,8 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
           rmin = std::min(rmin, dist);
         }
         O.rin = rmin < 1e299 ? (float)(0.98 * rmin) : 0.f;  // valid for a convex hull with the centre inside
+        hull_balls(V, d->hull_vert_off[h + 1] - d->hull_vert_off[h], d->hull_faces + 3 * (size_t)d->hull_face_off[h],
+                   d->hull_face_off[h + 1] - d->hull_face_off[h], O.ball);
       } break;
       default: O.rin = 0.f; break;
     }
@@ -1202,6 +1282,7 @@ struct PassOut {
   uint2 *hits = nullptr;
   unsigned *n_hits = nullptr;
   unsigned hit_cap = 0, cfg0 = 0;
+  bool whole_pass = false;  // host input: copy q of the pass in one piece (multi-pass calls)
   bool reset_call = false;  // small passes: the fused reset also zeroes the call's counters (first pass of a graph-captured call)
 };
 
@@ -1240,7 +1321,10 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   cudaEvent_t e0 = pe.e[0], e1 = pe.e[1], e2 = pe.e[2], f0 = pe.e[3], f1 = pe.e[4];
   if (ev) CU(cudaEventRecord(e0, st));
   if (ev && hq) { CU(cudaEventRecord(f0, st)); CU(cudaEventRecord(f1, st)); }
-  const long long sub = hq ? std::max<long long>(s->host_chunk, 64) : m;
+  // host input: q arrives in sub-ranges so that FK + cull of one overlaps the copy of the next.  A call of several passes
+  // already overlaps the copy of pass c+1 with the kernels of pass c (double buffering), so its passes take q whole:
+  // the thread-per-configuration cull kernels need ~10^6 configurations to fill the GPU
+  const long long sub = hq ? (po.whole_pass ? m : std::max<long long>(s->host_chunk, 64)) : m;
   for (long long off = 0; off < m; off += sub) {
     const long long mm = std::min(sub, m - off);
     if (hq) {
@@ -1281,15 +1365,17 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   }
   dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out);
   *launches += 1;
+  static const int refill_min = getenv("MPB_REFILL_MIN") ? atoi(getenv("MPB_REFILL_MIN")) : 8;
+  static const int presolve = !(getenv("MPB_NO_PRESOLVE") && atoi(getenv("MPB_NO_PRESOLVE")));
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const int nblocks = grid_for(s->narrow_blocks, 64);  // narrowphase: a block of 8 warps per 64 possible items of a small pass
   const unsigned n_warps = (unsigned)std::max(1.0, nblocks * 8.0 * unit_factor);
   scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, n_warps, s->sq_cap);
-  scatter_kernel<<<grid_for(s->num_sms * 2, 1024), 1024, 0, st>>>(s->img, s->wq, 0);
+  scatter_kernel<<<grid_for(s->num_sms * 4, 512), 512, 0, st>>>(s->img, s->wq, 0, out, presolve);
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
-  if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
-  else narrow_kernel<false><<<nblocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0);
+  if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
+  else narrow_kernel<false><<<nblocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
   *launches += 3;
   if (s->img.expand2_bin >= 0) {  // mesh x mesh / mesh x octree pairs: exact leaf tests inside the descent
     expand2_kernel<<<grid_for(s->num_sms * 8, 4), 128, 0, st>>>(s->img, s->wq, out);
@@ -1301,9 +1387,9 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     expand_kernel<<<grid_for(s->num_sms * 8, 16), 128, 0, st>>>(s->img, s->wq, out, small ? 0 : lane_on);
     if (!small && lane_on) { expand_lane_kernel<<<s->expand_lane_blocks, 128, 0, st>>>(s->img, s->wq, out); *launches += 1; }
     scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor), s->sq_cap);
-    scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1);
-    if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);
-    else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1);
+    scatter_kernel<<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 1, out, presolve);
+    if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
+    else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     *launches += 5;
   }
   if (po.hits && dp && W > 0) {  // sparse hit list: compacted out of the pass's dense mask
@@ -1418,6 +1504,7 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, const Coll
     }
     po.dv = s->d_verdict[b];
     po.dp = want_mask ? s->d_pairbits[b] : nullptr;
+    po.whole_pass = n > chunk;
     rc = launch_pass(s, s->d_q[b], s->d_q[b], m, po, st, pe, &launches, q + off * D, &sync_ev);
     if (rc != MPB_OK) return rc;
     ev_k.push_back(get_sync_event(s, sync_ev++));
@@ -2253,7 +2340,7 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
       sphere_kernel<1, 0, 0><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
       dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, HitOut{});
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, (unsigned)dblocks * 8u, s->sq_cap);
-      scatter_kernel<<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0);
+      scatter_kernel<<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 0, HitOut{}, 0);
       CU(cudaEventRecord(e1, st));
       if (s->smem_verts) distance_kernel<true><<<dblocks, 256, vsm, st>>>(s->img, s->wq, dbest, s->img.n_bins);
       else distance_kernel<false><<<dblocks, 256, 0, st>>>(s->img, s->wq, dbest, s->img.n_bins);

@@ -15,6 +15,7 @@
 #define MPB_MAX_JOINTS 32   // movable joints in the merged forest (two Pandas = 18)
 #define MPB_MAX_DYN 128     // objects that move with a joint (8-bit slot fields; fk_table_kernel's parameter table)
 #define MPB_ITEM_WORDS 14   // 12 floats relative transform + cfg + pair
+#define MPB_INNER_BALLS 4   // balls inscribed in every shape (sufficient-hit test in front of the narrowphase)
 
 struct alignas(16) DevJoint {
   float P[12];   // placement in the parent joint frame
@@ -51,6 +52,7 @@ struct alignas(16) DevObject {
   int jslot;        // joint-table slot of the owner joint, -1 if world-fixed
   float bcj[3];     // bounding-sphere centre in the owner joint frame (L * bc)
   int cell;         // convex hulls: byte offset of the support cell table behind the vertex pool, -1 = none
+  float4 ball[MPB_INNER_BALLS];  // balls inside the shape, object frame: centre xyz, radius w (0 = unused); sufficient-hit test
 };
 static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
 

@@ -142,6 +142,16 @@ __global__ void __launch_bounds__(256) hits_compact_kernel(const unsigned int *_
   }
 }
 
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+__device__ __forceinline__ V3 rot(const float *R, V3 v) {
+  return v3(fmaf(R[0], v.x, fmaf(R[1], v.y, R[2] * v.z)), fmaf(R[3], v.x, fmaf(R[4], v.y, R[5] * v.z)),
+            fmaf(R[6], v.x, fmaf(R[7], v.y, R[8] * v.z)));
+}
+__device__ __forceinline__ V3 rot_t(const float *R, V3 v) {
+  return v3(fmaf(R[0], v.x, fmaf(R[3], v.y, R[6] * v.z)), fmaf(R[1], v.x, fmaf(R[4], v.y, R[7] * v.z)),
+            fmaf(R[2], v.x, fmaf(R[5], v.y, R[8] * v.z)));
+}
+
 #define MPB_EPS FLT_EPSILON
 #define MPB_MPR_TOL 1e-6f
 #define MPB_MPR_MAX_ITERS 500  // libccd: GJKSolver_libccd::max_collision_iterations [upstream]
@@ -868,9 +878,86 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bi
   }
 }
 
+// ---- sufficient-hit test in front of the narrowphase.  Every object carries up to MPB_INNER_BALLS balls that lie inside
+// it (host: primitive_balls / hull_balls).  If a ball of one shape intersects the other shape -- exactly, by the closed
+// forms below, when that one is a primitive; a ball of it otherwise -- the shapes intersect, which is what MPR would
+// report after three or more support evaluations.  In the C3 scene most narrowphase items are such collisions.
+__device__ __forceinline__ bool ball_hits_primitive(int type, const float *prm, V3 c, float r) {  // c: ball centre in the primitive's frame
+  switch (type) {
+    case MPB_GEOM_SPHERE: { const float rr = r + prm[0]; return dot(c, c) < rr * rr; }
+    case MPB_GEOM_BOX: {
+      const float dx = c.x - clampf(c.x, -prm[0], prm[0]), dy = c.y - clampf(c.y, -prm[1], prm[1]), dz = c.z - clampf(c.z, -prm[2], prm[2]);
+      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < r * r;
+    }
+    case MPB_GEOM_CAPSULE: {
+      const float dz = c.z - clampf(c.z, -prm[1], prm[1]), rr = r + prm[0];
+      return fmaf(c.x, c.x, fmaf(c.y, c.y, dz * dz)) < rr * rr;
+    }
+    case MPB_GEOM_CYLINDER: {
+      const float dr = fmaxf(sqrtf(fmaf(c.x, c.x, c.y * c.y)) - prm[0], 0.f), dz = fmaxf(fabsf(c.z) - prm[1], 0.f);
+      return fmaf(dr, dr, dz * dz) < r * r;
+    }
+    default: return false;
+  }
+}
+// A, B: the two objects of the item; (R, t): B in A.  leaf >= 0: B is a BVH object and the item is its leaf primitive `leaf`.
+__device__ __forceinline__ bool sufficient_hit(const SceneImg &img, const DevObject &A, const DevObject &B, const float *R, V3 t, int leaf) {
+  if (leaf >= 0) {
+    if (B.vcnt != MPB_GEOM_VBOX) return false;  // triangles: left to the narrowphase
+    const float4 pc = __ldg(img.prims + 3 * leaf), ph = __ldg(img.prims + 3 * leaf + 1);
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 b = A.ball[k];
+      if (b.w <= 0.f) break;
+      const V3 c = rot_t(R, v3(b.x, b.y, b.z) - t);  // ball centre in the octree's frame
+      const float dx = c.x - clampf(c.x, pc.x - ph.x, pc.x + ph.x), dy = c.y - clampf(c.y, pc.y - ph.y, pc.y + ph.y),
+                  dz = c.z - clampf(c.z, pc.z - ph.z, pc.z + ph.z);
+      if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < b.w * b.w) return true;
+    }
+    return false;
+  }
+  const bool pa = A.type >= MPB_GEOM_SPHERE && A.type <= MPB_GEOM_CYLINDER, pb = B.type >= MPB_GEOM_SPHERE && B.type <= MPB_GEOM_CYLINDER;
+  if (pb) {  // balls of A against the primitive B, exactly
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 b = A.ball[k];
+      if (b.w <= 0.f) break;
+      if (ball_hits_primitive(B.type, B.prm, rot_t(R, v3(b.x, b.y, b.z) - t), b.w)) return true;
+    }
+    return false;
+  }
+  if (pa) {  // balls of B against the primitive A
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 b = B.ball[k];
+      if (b.w <= 0.f) break;
+      if (ball_hits_primitive(A.type, A.prm, rot(R, v3(b.x, b.y, b.z)) + t, b.w)) return true;
+    }
+    return false;
+  }
+  if (A.type != MPB_GEOM_CONVEX || B.type != MPB_GEOM_CONVEX) return false;
+#pragma unroll
+  for (int j = 0; j < MPB_INNER_BALLS; j++) {
+    const float4 bb = B.ball[j];
+    if (bb.w <= 0.f) break;
+    const V3 cb = rot(R, v3(bb.x, bb.y, bb.z)) + t;
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 ba = A.ball[k];
+      if (ba.w <= 0.f) break;
+      const V3 d = v3(ba.x, ba.y, ba.z) - cb;
+      const float rr = ba.w + bb.w;
+      if (dot(d, d) < rr * rr) return true;
+    }
+  }
+  return false;
+}
+
 // Staging queue -> binned queue.  A block ranks its items per bin in shared memory (the shared atomic returns the
-// rank), reserves one range per bin per trip in the global cursors, then moves the items.
-__global__ void __launch_bounds__(1024) scatter_kernel(SceneImg img, WorkQ wq, int round) {
+// rank), reserves one range per bin per trip in the global cursors, then moves the items.  The kernel is bound by its
+// dependent loads and leaves most issue slots idle, so the sufficient-hit test runs here (presolve != 0): an item it
+// settles sets its result bits and is not moved; bin_cursor[b] ends as the number of items bin b really holds.
+__global__ void __launch_bounds__(512, 2) scatter_kernel(SceneImg img, WorkQ wq, int round, HitOut out, int presolve) {
   __shared__ unsigned s_cnt[MPB_SMEM_BINS], s_base[MPB_SMEM_BINS];
   const unsigned n = min(wq.totals[0], wq.cap);
   const int n_bins = round == 0 ? img.n_bins : img.n_bins2;
@@ -878,9 +965,25 @@ __global__ void __launch_bounds__(1024) scatter_kernel(SceneImg img, WorkQ wq, i
   const unsigned n_round = (n + blockDim.x - 1) / blockDim.x * blockDim.x;
   const unsigned lane = threadIdx.x & 31;
   for (unsigned s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
-    const bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
+    bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
     const int p = valid ? wq.spair[s] : 0;
     int bin = valid ? (round == 0 ? (img.pairs[p].bin_dyn & 0xffff) : img.pair_bin2[p]) : -1;
+    float f[12];
+    int cfg = 0, aux = 0;
+    if (valid) {
+#pragma unroll
+      for (int k = 0; k < 12; k++) f[k] = wq.stf[(size_t)k * wq.cap + s];
+      cfg = wq.scfg[s];
+      aux = wq.saux[s];
+      if (presolve && !(round == 0 && (bin == img.expand_bin || bin == img.expand2_bin))) {
+        const DevPair pr = img.pairs[p];
+        if (sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], f, v3(f[9], f[10], f[11]), round == 0 ? -1 : aux)) {
+          report_hit(out, (unsigned)cfg, p);
+          valid = false;
+          bin = -1;
+        }
+      }
+    }
     unsigned dst = 0;
     if (smem_bins) {
       for (int b = threadIdx.x; b < n_bins; b += blockDim.x) s_cnt[b] = 0;
@@ -904,10 +1007,10 @@ __global__ void __launch_bounds__(1024) scatter_kernel(SceneImg img, WorkQ wq, i
     }
     if (valid) {
 #pragma unroll
-      for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = wq.stf[(size_t)k * wq.cap + s];
-      wq.icfg[dst] = wq.scfg[s];
+      for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = f[k];
+      wq.icfg[dst] = cfg;
       wq.ipair[dst] = p;
-      wq.iaux[dst] = wq.saux[s];
+      wq.iaux[dst] = aux;
     }
   }
 }
@@ -994,14 +1097,6 @@ __device__ __forceinline__ V3 support_local(const DevShape &s, V3 d, const float
   }
 }
 
-__device__ __forceinline__ V3 rot(const float *R, V3 v) {
-  return v3(fmaf(R[0], v.x, fmaf(R[1], v.y, R[2] * v.z)), fmaf(R[3], v.x, fmaf(R[4], v.y, R[5] * v.z)),
-            fmaf(R[6], v.x, fmaf(R[7], v.y, R[8] * v.z)));
-}
-__device__ __forceinline__ V3 rot_t(const float *R, V3 v) {
-  return v3(fmaf(R[0], v.x, fmaf(R[3], v.y, R[6] * v.z)), fmaf(R[1], v.x, fmaf(R[4], v.y, R[7] * v.z)),
-            fmaf(R[2], v.x, fmaf(R[5], v.y, R[8] * v.z)));
-}
 __device__ __forceinline__ bool is_zero(float v) { return fabsf(v) < MPB_EPS; }
 
 // Hull support evaluated by the whole warp for ONE query direction (same on every lane): lane-strided scan and a
@@ -1057,7 +1152,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 // ccdMPRIntersect [upstream libccd v2.1 mpr.c] in the frame of shape A; B sits at (R, t).
 // Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
 template <bool SMEM>
-__global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round) {
+__global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round, int refill_min) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
@@ -1095,7 +1190,9 @@ __global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, 
       if (wq.unit_start[mid] <= u) lo = mid; else hi = mid;
     }
     unsigned next = wq.bin_start[lo] + (u - wq.unit_start[lo]) * unit_items;
-    const unsigned end = min(min(wq.bin_start[lo + 1], next + unit_items), wq.cap);
+    // the bin holds bin_cursor items (the scatter's sufficient-hit test may have settled some of the counted ones)
+    const unsigned end = min(min(wq.bin_start[lo] + wq.bin_cursor[lo], next + unit_items), wq.cap);
+    if (next >= end) continue;
     const unsigned first = next;
 
     // per-lane item state
@@ -1116,8 +1213,10 @@ __global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, 
     }
     for (;;) {
       // ---- refill idle lanes from the slice
+      // the refill block is as long as a support evaluation: it runs when at least MPB_REFILL_MIN lanes are idle (or none has
+      // work), not every time one lane finishes
       const unsigned need = __ballot_sync(FULL, !busy);
-      if (need) {
+      if (need == FULL || (__popc(need) >= refill_min && next < end)) {
         const unsigned my = next + __popc(need & ((1u << lane) - 1u));
         if (!busy && my < end) {
           bool busy_ok = true;
@@ -1310,7 +1409,6 @@ __global__ void __launch_bounds__(128) fk_pose_kernel(SceneImg img, const float 
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
-__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
 #define MPB_EXP_STACK 1024  // node frontier per warp
 
