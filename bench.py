@@ -49,9 +49,12 @@ def parse():
     ap.add_argument("--plan-inflight", type=int, default=2, help="c4: plan_batch calls kept in flight (host threads)")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
     ap.add_argument("--connect-steps", type=int, default=8, help="c4: connect-walk steps validated per lock-step round")
-    ap.add_argument("--plan-time", type=float, default=0.5,
-                    help="c4: OMPL `time` budget in seconds.  The reference arm gives EVERY query 1.0 s on its own host thread "
-                         "(Planner.plan's default); the batched call applies its budget to the whole lock-step batch")
+    ap.add_argument("--plan-slots", type=int, default=2048, help="c4: concurrent searches per plan_batch call; a finished query's slot takes the next pending query")
+    ap.add_argument("--plan-rounds-per-query", type=int, default=1024,
+                    help="c4: the PER-QUERY budget in lock-step rounds (the role of OMPL's `time`; the reference arm gives every "
+                         "query 1.0 s of one host thread, Planner.plan's default).  Both arms print solve_rate and "
+                         "grow_calls_per_query so the budgets can be compared")
+    ap.add_argument("--plan-time", type=float, default=60.0, help="c4: wall-clock safety limit of one plan_batch call (not the budget)")
     return ap.parse_args()
 
 
@@ -151,7 +154,7 @@ def cpu_plans(wl, threads, n_q, seed_base, steps, time_limit=1.0):
         t0 = time.perf_counter()
         st, paths, gc, sc = O.rrtconnect_batch(desc, lo, hi, starts, goals, range_=0.1, time_limit=time_limit, seed=s, threads=threads,
                                                accel=accel)
-        per_step.append((int((st == 1).sum()), time.perf_counter() - t0, n_q))
+        per_step.append((int((st == 1).sum()), time.perf_counter() - t0, n_q, gc))
     return per_step
 
 
@@ -502,7 +505,7 @@ def run_c4(args, ctx, batch, steps, warmup):
     n_sets = min(warmup + steps, 4)
     sets = [WL.c4_queries(Q, 5 + 104729 * k + 1000003 * rank, wl["world"].collide_batch) for k in range(n_sets)]
     kw = dict(range=0.1, time=args.plan_time, max_rounds=args.max_rounds, tree_capacity=4096, max_path=2048,
-              connect_steps=args.connect_steps)
+              connect_steps=args.connect_steps, n_slots=args.plan_slots, max_rounds_per_query=args.plan_rounds_per_query)
     keep = {}
 
     def run(k0, k1):
@@ -532,7 +535,7 @@ def run_c4(args, ctx, batch, steps, warmup):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    solved = launches = rounds = states = 0
+    solved = launches = rounds = states = grow = 0
     t0 = time.perf_counter()
     res = run(warmup, warmup + steps)
     torch.cuda.synchronize()
@@ -541,10 +544,11 @@ def run_c4(args, ctx, batch, steps, warmup):
     gpu_ms = max(sum(st["gpu_ms"] for k, st in res.items() if (k - warmup) % F == t) for t in range(F))
     for st in res.values():
         solved += st["n_solved"]; launches += st["kernel_launches"]; rounds += st["rounds"]; states += st["states_checked"]
+        grow += st["grow_calls"]
     ctx.barrier()
     clocks = sampler.stop() if rank == 0 else None
     gpu_ms, wall = ctx.reduce([gpu_ms, wall], "max")
-    solved, launches, states = ctx.reduce([solved, launches, states], "sum")
+    solved, launches, states, grow = ctx.reduce([solved, launches, states, grow], "sum")
     rec = None
     if rank == 0:
         K = steps
@@ -556,7 +560,10 @@ def run_c4(args, ctx, batch, steps, warmup):
             "metric": PLAN_METRIC, "value": solved / (gpu_ms * 1e-3), "unit": PLAN_UNIT, "n_gpus": world, "steps": K,
             "warmup": warmup, "ms_per_step": gpu_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": wl["config"],
-            "solve_rate": solved / (float(Q) * world * K), "plan_time_budget_s": args.plan_time, "calls_in_flight": F,
+            "solve_rate": solved / (float(Q) * world * K), "calls_in_flight": F,
+            "budget": {"per_query_rounds": args.plan_rounds_per_query, "slots_per_call": min(args.plan_slots, Q),
+                       "grow_calls_per_query": grow / (float(Q) * world * K),
+                       "note": "per-query budget (a query that spends it ends as Timeout and frees its slot); no per-batch deadline"},
             "e2e": {"value": solved / wall, "unit": PLAN_UNIT, "h2d_bytes_per_step": int(Q * 2 * desc.state_dim * 4 + Q * 4),
                     "d2h_bytes_per_step": int(Q * 8 + Q * kw["max_path"] * desc.state_dim * 4)},
             "gpu_launches": int(launches), "clocks": clocks,
@@ -585,9 +592,9 @@ def run_c4(args, ctx, batch, steps, warmup):
                              "oracle": "DiscreteMotionValidator restatement (oracle.c, float64, exhaustive leaf tests) over every edge of every path of one step"}
         if not args.no_cpu_baseline and world == 1:
             per = cpu_plans(wl, 1, 8, 5, 1)
-            ns, dt = sum(a for a, _, _ in per), sum(b for _, b, _ in per)
+            ns, dt = sum(x[0] for x in per), sum(x[1] for x in per)
             rec["cpu_baseline"] = {"value": ns / dt, "unit": PLAN_UNIT, "cores": 1, "kind": "port", "algorithm": "bvh",
-                                   "solve_rate": ns / sum(c for _, _, c in per),
+                                   "solve_rate": ns / sum(x[2] for x in per), "grow_calls_per_query": sum(x[3] for x in per) / sum(x[2] for x in per),
                                    "sample": "8 queries of the same seeded workload one after the other on one thread, time limit 1 s per query"}
     for x in wls:
         c = x["world"]._cache
@@ -633,13 +640,14 @@ def reference_c4(args, batch, steps, warmup):
     threads = os.cpu_count() or 1
     n_q = max(threads * 2, 16)
     per = cpu_plans(wl, threads, n_q, 5, warmup + steps)[warmup:]
-    ns, dt = sum(a for a, _, _ in per), sum(b for _, b, _ in per)
+    ns, dt = sum(x[0] for x in per), sum(x[1] for x in per)
     val = ns / dt
     return {
         "impl": "reference", "metric": PLAN_METRIC, "value": val, "unit": PLAN_UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": 1e3 * dt / max(len(per), 1), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": wl["config"],
-        "solve_rate": ns / max(sum(c for _, _, c in per), 1),
+        "solve_rate": ns / max(sum(x[2] for x in per), 1),
+        "budget": {"per_query_time_s": 1.0, "grow_calls_per_query": sum(x[3] for x in per) / max(sum(x[2] for x in per), 1)},
         "cpu_baseline": {"value": val, "unit": PLAN_UNIT, "cores": threads, "kind": "port", "algorithm": "bvh",
                          "sample": f"{n_q} queries/step of the same seeded workload, one query per thread, OpenMP x{threads}, "
                                    "time limit 1 s per query"},

@@ -242,6 +242,10 @@ typedef struct mpb_rrt_params {
   uint64_t seed;
   int32_t check_every;    /* rounds between host checks of the active-query counter (<= 0: 16)        */
   int32_t connect_steps;  /* steps of the connect loop validated per round (<= 0: 8, at most 32)      */
+  int32_t n_slots;        /* concurrent searches (<= 0 or > n_queries: n_queries).  A slot whose query ends takes the
+                             next pending query, so a batch larger than n_slots flows through without idle slots */
+  int32_t max_rounds_per_query; /* the PER-QUERY budget (the role of OMPL's `time` for one query): rounds a query
+                             may occupy a slot before it ends as MPB_RRT_ACTIVE ("Timeout"); <= 0: none */
 } mpb_rrt_params;
 
 typedef struct mpb_rrt_stats {

@@ -18,7 +18,8 @@ class MpbSpaceDesc(C.Structure):
 
 class MpbRrtParams(C.Structure):
     _fields_ = [("range", C.c_float), ("max_rounds", C.c_int32), ("time_limit_s", C.c_float), ("tree_capacity", C.c_int32),
-                ("max_path", C.c_int32), ("seed", C.c_uint64), ("check_every", C.c_int32), ("connect_steps", C.c_int32)]
+                ("max_path", C.c_int32), ("seed", C.c_uint64), ("check_every", C.c_int32), ("connect_steps", C.c_int32),
+                ("n_slots", C.c_int32), ("max_rounds_per_query", C.c_int32)]
 
 
 class MpbRrtStats(C.Structure):
@@ -271,7 +272,7 @@ class DeviceScene:
         return (valid, st.as_dict()) if stats else valid
 
     def rrtconnect(self, space: Space, starts, goals, n_goals=None, range_=0.1, max_rounds=4096, time_limit=0.0,
-                   tree_capacity=2048, max_path=1024, seed=0, check_every=16, connect_steps=8):
+                   tree_capacity=2048, max_path=1024, seed=0, check_every=16, connect_steps=8, n_slots=0, max_rounds_per_query=0):
         """Lock-step RRTConnect for Q queries.  starts [Q, D]; goals [Q, G, D] (or [Q, D]); n_goals [Q].
         -> (status int32[Q], list of float64 paths ([n_i, D], empty if unsolved), stats dict)"""
         starts = np.ascontiguousarray(np.asarray(starts, dtype=np.float32))
@@ -284,7 +285,7 @@ class DeviceScene:
             raise RuntimeError("Length of start state and goal state should be equal")
         G = goals.shape[1]
         ng = np.ascontiguousarray(np.full(Q, G, np.int32) if n_goals is None else np.asarray(n_goals, dtype=np.int32))
-        prm = MpbRrtParams(float(range_), int(max_rounds), float(time_limit), int(tree_capacity), int(max_path), int(seed), int(check_every), int(connect_steps))
+        prm = MpbRrtParams(float(range_), int(max_rounds), float(time_limit), int(tree_capacity), int(max_path), int(seed), int(check_every), int(connect_steps), int(n_slots), int(max_rounds_per_query))
         status = np.zeros(Q, dtype=np.int32)
         plen = np.zeros(Q, dtype=np.int32)
         paths = np.empty((Q, max_path, D), dtype=np.float32)  # rows past path_len stay unwritten

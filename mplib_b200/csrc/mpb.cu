@@ -162,6 +162,19 @@ struct mpb_scene {
 
 static void drop_small_graphs(mpb_scene *s);
 static int harvest(mpb_scene *s, bool wait);
+// Wait for everything this scene has in flight (its own streams and the device-pointer calls on caller streams).  Never
+// cudaDeviceSynchronize: another host thread may be capturing a graph on another scene's stream.
+static cudaError_t sync_scene(mpb_scene *s);
+
+static cudaError_t sync_scene(mpb_scene *s) {
+  cudaError_t e = cudaSuccess;
+  for (auto &sl : s->slots)
+    if (sl.pending && sl.done && (e = cudaEventSynchronize(sl.done)) != cudaSuccess) return e;
+  if (s->stream && (e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return e;
+  if (s->stream_h2d && (e = cudaStreamSynchronize(s->stream_h2d)) != cudaSuccess) return e;
+  if (s->stream_d2h && (e = cudaStreamSynchronize(s->stream_d2h)) != cudaSuccess) return e;
+  return e;
+}
 
 extern "C" const char *mpb_last_error(void) { return g_err.c_str(); }
 
@@ -1071,7 +1084,8 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
                   s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals};
   for (void *p : ptrs)
     if (p) cudaFree(p);
-  cudaDeviceSynchronize();  // device-pointer calls may still be in flight on caller streams
+  harvest(s, true);  // device-pointer calls may still be in flight on caller streams
+  sync_scene(s);
   drop_small_graphs(s);
   if (s->h_small) cudaFreeHost(s->h_small);
   if (s->h_status) cudaFreeHost(s->h_status);
@@ -1133,7 +1147,7 @@ extern "C" int mpb_scene_set_pairs(mpb_scene *s, int32_t n_pairs, const int32_t 
   CU(cudaSetDevice(s->device));
   int rc = harvest(s, true);
   if (rc != MPB_OK) return rc;
-  CU(cudaDeviceSynchronize());
+  CU(sync_scene(s));
   rc = build_pairs(s, n_pairs, pa, pb);
   if (rc != MPB_OK) return rc;
   s->img_version++;
@@ -1156,7 +1170,7 @@ extern "C" int mpb_scene_update_objects(mpb_scene *s, int32_t n, const int32_t *
   CU(cudaSetDevice(s->device));
   int rc = harvest(s, true);
   if (rc != MPB_OK) return rc;
-  CU(cudaDeviceSynchronize());
+  CU(sync_scene(s));
   for (int k = 0; k < n; k++) {
     const int o = obj_idx[k];
     DevObject &O = s->h_objs[o];
@@ -1212,7 +1226,8 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   // rounds alternate on one scene; re-allocating GBs of queues between them would dominate small calls)
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
   if (chunk <= s->chunk && s->wq.itf && P <= s->work_P && (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1) <= s->bins_cap) return MPB_OK;
-  CU(cudaDeviceSynchronize());  // calls in flight (device-pointer mode) still use the old buffers
+  if (int hrc = harvest(s, true)) return hrc;  // calls in flight (device-pointer mode) still use the old buffers
+  CU(sync_scene(s));
   chunk = std::max(chunk, s->chunk);
   s->work_P = P;
   // staging may hold up to one unused half-chunk per reservation: worst case 2 x items + one chunk per warp
@@ -2121,6 +2136,7 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   int rc = upload_space(s, space, &dsp, d_space);
   if (rc != MPB_OK) return rc;
   const int D = s->img.state_dim, Q = (int)n_queries;
+  const int W = params->n_slots > 0 ? std::min(params->n_slots, Q) : Q;  // concurrent searches
   const int cap = std::max(params->tree_capacity, 2), max_path = std::max(params->max_path, 2);
   const int max_rounds = std::max(params->max_rounds, 1), check_every = params->check_every > 0 ? params->check_every : 16;
   float range = params->range;
@@ -2133,55 +2149,49 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   for (int j = 0; j < D; j++) smax = std::max(smax, (int)std::ceil((double)range / space->seg[j]) + 1);
   if (smax > 4096) return fail(MPB_ERR_CAPACITY, "range / validity resolution gives too many samples per edge");
   const int S = params->connect_steps > 0 ? std::min(std::max(params->connect_steps, 2), 32) : 8;
-  const long long n_states = (long long)Q * S * smax;
+  const long long n_states = (long long)W * S * smax;
   rc = prepare_work(s, (n_states + 31) / 32 * 32);
   if (rc != MPB_OK) return rc;
 
   RrtState r{};
-  r.n_queries = Q; r.cap = cap; r.dim = D; r.smax = smax; r.max_goals = max_goals; r.max_path = max_path;
+  r.n_queries = Q; r.n_slots = W; r.cap = cap; r.dim = D; r.smax = smax; r.max_goals = max_goals; r.max_path = max_path;
   r.S = S;
+  r.max_rounds_q = params->max_rounds_per_query;
   r.seed = params->seed;
-  float *d_start = nullptr, *d_goals = nullptr, *d_states = nullptr, *d_paths = nullptr;
-  int *d_ngoals = nullptr, *d_ints = nullptr, *d_pathlen = nullptr;
+  float *d_start = nullptr, *d_goals = nullptr, *d_states = nullptr;
+  int *d_ngoals = nullptr, *d_ints = nullptr, *d_qints = nullptr;
   uint32_t *d_verdict = nullptr;
-  CU(bufs.alloc(&r.nodes, (size_t)Q * 2 * cap * D));
-  CU(bufs.alloc(&r.parent, (size_t)Q * 2 * cap));
+  CU(bufs.alloc(&r.nodes, (size_t)W * 2 * cap * D));
+  CU(bufs.alloc(&r.parent, (size_t)W * 2 * cap));
   CU(bufs.alloc(&d_start, (size_t)Q * D));
   CU(bufs.alloc(&d_goals, (size_t)Q * max_goals * D));
   CU(bufs.alloc(&d_ngoals, (size_t)Q));
-  CU(bufs.alloc(&d_ints, (size_t)Q * 15 + 4));  // size[2] goals_used status phase flag tsel nearest reach added sol[2] iters n_steps nearest2
-  CU(bufs.alloc(&r.target, (size_t)Q * D));
-  CU(bufs.alloc(&r.edge_a, (size_t)Q * S * D));
-  CU(bufs.alloc(&r.edge_b, (size_t)Q * S * D));
+  CU(bufs.alloc(&d_ints, (size_t)W * 15 + 4));   // per slot: size[2] slot_query rounds_used goals_used phase flag tsel nearest nearest2 reach n_steps added iters | pending[2]
+  CU(bufs.alloc(&d_qints, (size_t)Q * 3));       // per query: status, path_len, iters
+  CU(bufs.alloc(&r.target, (size_t)W * D));
+  CU(bufs.alloc(&r.edge_a, (size_t)W * S * D));
+  CU(bufs.alloc(&r.edge_b, (size_t)W * S * D));
   CU(bufs.alloc(&d_states, (size_t)n_states * D));
   CU(bufs.alloc(&d_verdict, (size_t)(n_states + 31) / 32 + 1));
-  CU(bufs.alloc(&d_paths, (size_t)Q * max_path * D));
-  CU(bufs.alloc(&d_pathlen, (size_t)Q));
+  CU(bufs.alloc(&r.q_paths, (size_t)Q * max_path * D));
   r.size = d_ints;
-  r.goals_used = d_ints + 2 * Q; r.status = d_ints + 3 * Q; r.phase = d_ints + 4 * Q; r.flag_start = d_ints + 5 * Q;
-  r.tsel = d_ints + 6 * Q; r.nearest = d_ints + 7 * Q; r.reach = d_ints + 8 * Q; r.added = d_ints + 9 * Q;
-  r.sol = d_ints + 10 * Q; r.iters = d_ints + 12 * Q;
-  r.n_steps = d_ints + 13 * Q;
-  r.nearest2 = d_ints + 14 * Q;
-  r.n_active = reinterpret_cast<unsigned *>(d_ints + 15 * Q);
+  r.slot_query = d_ints + 2 * W; r.rounds_used = d_ints + 3 * W; r.goals_used = d_ints + 4 * W; r.phase = d_ints + 5 * W;
+  r.flag_start = d_ints + 6 * W; r.tsel = d_ints + 7 * W; r.nearest = d_ints + 8 * W; r.nearest2 = d_ints + 9 * W;
+  r.reach = d_ints + 10 * W; r.n_steps = d_ints + 11 * W; r.added = d_ints + 12 * W; r.iters = d_ints + 13 * W;
+  r.pending = reinterpret_cast<unsigned *>(d_ints + 15 * W);
+  r.q_status = d_qints; r.q_pathlen = d_qints + Q; r.q_iters = d_qints + 2 * Q;
   r.start = d_start; r.goals = d_goals; r.n_goals = d_ngoals;
   {
-    std::vector<int> h((size_t)Q * 15 + 4, 0);
-    for (int q = 0; q < Q; q++) {
-      h[2 * q] = 1;          // tStart_ holds the start state
-      h[5 * (size_t)Q + q] = 1;  // startTree_ = true
-    }
-    h[15 * (size_t)Q] = Q;
+    std::vector<int> h((size_t)W * 15 + 4, 0);
+    for (int w = 0; w < W; w++) h[2 * (size_t)W + w] = -1;  // every slot idle: the first round hands out the first W queries
     CU(cudaMemcpyAsync(d_ints, h.data(), h.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    CU(cudaMemsetAsync(r.parent, 0xff, (size_t)Q * 2 * cap * sizeof(int), st));
+    CU(cudaMemsetAsync(d_qints, 0, (size_t)Q * 3 * sizeof(int), st));  // status MPB_RRT_ACTIVE, no path
     CU(cudaMemcpyAsync(d_start, starts, (size_t)Q * D * sizeof(float), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_goals, goals, (size_t)Q * max_goals * D * sizeof(float), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_ngoals, n_goals, (size_t)Q * sizeof(int), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpy2DAsync(r.nodes, (size_t)2 * cap * D * sizeof(float), d_start, (size_t)D * sizeof(float), (size_t)D * sizeof(float), Q,
-                         cudaMemcpyDeviceToDevice, st));
     CU(cudaMemsetAsync(d_verdict, 0, ((size_t)(n_states + 31) / 32 + 1) * sizeof(uint32_t), st));
-    CU(cudaMemsetAsync(r.edge_a, 0, (size_t)Q * S * D * sizeof(float), st));
-    CU(cudaMemsetAsync(r.edge_b, 0, (size_t)Q * S * D * sizeof(float), st));
+    CU(cudaMemsetAsync(r.edge_a, 0xff, (size_t)W * S * D * sizeof(float), st));  // NaN: idle slots cost no narrowphase work
+    CU(cudaMemsetAsync(r.edge_b, 0xff, (size_t)W * S * D * sizeof(float), st));
     CU(cudaMemsetAsync(s->wq.totals, 0, 8 * sizeof(unsigned), st));
     CU(cudaMemsetAsync(s->wq.counters, 0, 4 * sizeof(unsigned long long), st));
     CU(cudaStreamSynchronize(st));  // h goes out of scope
@@ -2189,8 +2199,8 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   long long launches_per_round = 0;
   auto enqueue_round = [&](long long *launches) -> int {
     size_t sync_ev = 0;
-    rrt_advance_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
-    motion_expand_kernel<<<(Q * S + 255) / 256, 256, 0, st>>>(dsp.sp, r.edge_a, r.edge_b, (long long)Q * S, nullptr, nullptr, smax, d_states, nullptr);
+    rrt_advance_kernel<<<(W * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
+    motion_expand_kernel<<<(W * S + 255) / 256, 256, 0, st>>>(dsp.sp, r.edge_a, r.edge_b, (long long)W * S, nullptr, nullptr, smax, d_states, nullptr);
     *launches += 2;
     PassOut po;
     po.dv = d_verdict;
@@ -2213,16 +2223,16 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   cudaEvent_t e0 = get_event(s, 0), e1 = get_event(s, 1);
   CU(cudaEventRecord(e0, st));
   long long rounds = 0, launches = 0;
-  unsigned n_active = (unsigned)Q;
+  unsigned pending[2] = {0, 0};
   unsigned totals[8] = {0};
-  while (rounds < max_rounds && n_active > 0) {
+  while (rounds < max_rounds && pending[1] < (unsigned)Q) {
     const int k = (int)std::min<long long>(check_every, max_rounds - rounds);
     for (int i = 0; i < k; i++) {
       if (use_graph) { CU(cudaGraphLaunch(exec, st)); launches += launches_per_round; }
       else { rc = enqueue_round(&launches); if (rc != MPB_OK) return rc; }
     }
     rounds += k;
-    CU(cudaMemcpyAsync(&n_active, r.n_active, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(pending, r.pending, sizeof(pending), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(totals, s->wq.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     if (totals[2]) { rc = fail(MPB_ERR_CAPACITY, "work queue overflow inside the planning round"); break; }
@@ -2233,16 +2243,15 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
   if (graph) cudaGraphDestroy(graph);
   if (rc != MPB_OK) return rc;
   // one more advance so that the verdict of the last round is consumed (it may complete a query)
-  rrt_advance_kernel<<<(Q * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
-  r.max_path = max_path;
-  rrt_extract_kernel<<<(Q + 127) / 128, 128, 0, st>>>(r, d_paths, d_pathlen);
+  rrt_advance_kernel<<<(W * 32 + 255) / 256, 256, 0, st>>>(r, dsp.sp, range, d_verdict);
+  rrt_flush_kernel<<<(W + 127) / 128, 128, 0, st>>>(r);
   launches += 2;
   CU(cudaEventRecord(e1, st));
   CU(cudaGetLastError());
   std::vector<int> h_iters(Q);
-  CU(cudaMemcpyAsync(status, r.status, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(path_len, d_pathlen, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(h_iters.data(), r.iters, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(status, r.q_status, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(path_len, r.q_pathlen, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(h_iters.data(), r.q_iters, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   {  // waypoints: only the used rows cross PCIe (packed on the device, scattered into the caller's matrix here)
     std::vector<int> off((size_t)Q + 1, 0);
@@ -2254,7 +2263,7 @@ extern "C" int mpb_rrtconnect_batch(mpb_scene *s, const mpb_space_desc *space, c
       CU(bufs.alloc(&d_off, (size_t)Q + 1));
       CU(bufs.alloc(&d_packed, (size_t)total * D));
       CU(cudaMemcpyAsync(d_off, off.data(), ((size_t)Q + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
-      pack_paths_kernel<<<Q, 128, 0, st>>>(d_paths, d_off, D, max_path, d_packed);
+      pack_paths_kernel<<<Q, 128, 0, st>>>(r.q_paths, d_off, D, max_path, d_packed);
       launches += 1;
       std::vector<float> h_packed((size_t)total * D);
       CU(cudaMemcpyAsync(h_packed.data(), d_packed, h_packed.size() * sizeof(float), cudaMemcpyDeviceToHost, st));

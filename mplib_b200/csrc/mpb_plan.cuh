@@ -123,31 +123,41 @@ __global__ void fill_valid_bits_kernel(unsigned *__restrict__ valid_bits, long l
 }
 
 // ---------------------------------------------------------------------------------------------- RRTConnect, lock-step
+// Queries run in SLOTS (one warp each).  A slot whose query finishes -- solved, out of its per-query round budget, tree
+// full, no goal -- writes the query's result (status, path) at once and takes the next pending query in the following
+// round, so a batch of Q queries flows through n_slots <= Q concurrent searches and no slot idles while work is left.
 struct RrtState {
-  int n_queries, cap, dim, smax, max_goals, max_path;
-  int S;               // sub-edges a query may emit per round (connect steps validated speculatively)
-  float *nodes;        // [Q][2][cap][dim]   tree 0 = tStart_, tree 1 = tGoal_
-  int *parent;         // [Q][2][cap]        -1 = root
-  int *size;           // [Q][2]
+  int n_queries, n_slots, cap, dim, smax, max_goals, max_path;
+  int S;               // sub-edges a slot may emit per round (connect steps validated speculatively)
+  int max_rounds_q;    // rounds a query may occupy its slot (<= 0: unlimited); the per-query budget
+  // ---- per slot
+  float *nodes;        // [slots][2][cap][dim]   tree 0 = tStart_, tree 1 = tGoal_
+  int *parent;         // [slots][2][cap]        -1 = root
+  int *size;           // [slots][2]
+  int *slot_query;     // [slots]  query in the slot, -1 = idle
+  int *rounds_used;    // [slots]
+  int *goals_used;     // [slots]  pis_.getSampledGoalsCount()
+  int *phase;          // [slots]  0 = nothing pending, 3 = extend edge + first connect steps pending, 2 = further connect steps pending
+  int *flag_start;     // [slots]  startTree_
+  int *tsel;           // [slots]  tree the pending edges grow
+  int *nearest;        // [slots]  nmotion of the first pending edge
+  int *nearest2;       // [slots]  phase 3: nmotion of the first connect step (other tree)
+  int *reach;          // [slots]  the last pending edge ends on the target
+  int *n_steps;        // [slots]  pending sub-edges (1 .. S)
+  int *added;          // [slots]  addedMotion (index in tree 1 - tsel while connecting)
+  int *iters;          // [slots]  growTree calls consumed by the slot's query
+  float *target;       // [slots][dim]  rstate
+  float *edge_a;       // [slots][S][dim]  sub-edge k runs from edge_a[k] to edge_b[k]; edge_a[k] = edge_b[k-1]
+  float *edge_b;       // [slots][S][dim]
+  // ---- per query
   const float *start;  // [Q][dim]
   const float *goals;  // [Q][max_goals][dim]
   const int *n_goals;  // [Q]
-  int *goals_used;     // [Q]  pis_.getSampledGoalsCount()
-  int *status;         // [Q]  MPB_RRT_*
-  int *phase;          // [Q]  0 = nothing pending, 3 = extend edge + first connect steps pending, 2 = further connect steps pending
-  int *flag_start;     // [Q]  startTree_
-  int *tsel;           // [Q]  tree the pending edges grow
-  int *nearest;        // [Q]  nmotion of the first pending edge
-  int *nearest2;       // [Q]  phase 3: nmotion of the first connect step (other tree)
-  int *reach;          // [Q]  the last pending edge ends on the target
-  int *n_steps;        // [Q]  pending sub-edges (1 .. S)
-  int *added;          // [Q]  addedMotion (index in tree 1 - tsel while connecting)
-  float *target;       // [Q][dim]  rstate
-  float *edge_a;       // [Q][S][dim]  sub-edge k runs from edge_a[k] to edge_b[k]; edge_a[k] = edge_b[k-1]
-  float *edge_b;       // [Q][S][dim]
-  int *sol;            // [Q][2]   solution motions in tree 0 / tree 1
-  int *iters;          // [Q]      growTree calls consumed
-  unsigned *n_active;  // [1]
+  int *q_status;       // [Q]  MPB_RRT_*
+  int *q_pathlen;      // [Q]
+  int *q_iters;        // [Q]  growTree calls
+  float *q_paths;      // [Q][max_path][dim]
+  unsigned *pending;   // [0] next query to start   [1] queries finished
   unsigned long long seed;
 };
 
@@ -159,8 +169,8 @@ __device__ __forceinline__ float rrt_uniform(unsigned long long seed, unsigned q
   return (float)(z >> 40) * (1.0f / 16777216.0f);
 }
 
-// A query that has finished (or a speculative slot that is not used this round) must not cost narrowphase work:
-// its edge slots are set to NaN, which every bounding-sphere comparison of sphere_kernel rejects.
+// A slot that is idle (or a speculative sub-edge that is not used this round) must not cost narrowphase work:
+// its edge slots are set to NaN, which every bounding-sphere comparison of the sphere kernels rejects.
 __device__ __forceinline__ void rrt_blank_edges(float *ea, float *eb, int n, int lane) {
   const float nanv = __int_as_float(0x7fc00000);
   for (int i = lane; i < n; i += 32) { ea[i] = nanv; eb[i] = nanv; }
@@ -206,7 +216,40 @@ __device__ __forceinline__ int rrt_emit_walk(float *ea, float *eb, int slot0, in
   return ns;
 }
 
-// One warp per query.  A round consumes the verdicts of the query's pending sub-edges and emits the next ones.
+// The query of slot w ends with `status`: its result is written now (the slot's trees are about to be reused).
+// Solved: the path is the start chain (root first) followed by the goal chain (towards its root).
+__device__ __forceinline__ void rrt_finish(const RrtState &r, int w, int q, int status, int sol_s, int sol_g, int lane) {
+  const int D = r.dim;
+  int plen = 0;
+  if (status == MPB_RRT_SOLVED) {
+    const int *p0 = r.parent + ((size_t)w * 2 + 0) * r.cap, *p1 = r.parent + ((size_t)w * 2 + 1) * r.cap;
+    int ls = 0, lg = 0;
+    for (int i = sol_s; i >= 0; i = p0[i]) ls++;
+    for (int i = sol_g; i >= 0; i = p1[i]) lg++;
+    if (ls + lg > r.max_path) status = MPB_RRT_PATH_TOO_LONG;
+    else {
+      float *out = r.q_paths + (size_t)q * r.max_path * D;
+      const float *n0 = r.nodes + ((size_t)w * 2 + 0) * r.cap * D, *n1 = r.nodes + ((size_t)w * 2 + 1) * r.cap * D;
+      int k = ls - 1;
+      for (int i = sol_s; i >= 0; i = p0[i], k--)
+        for (int j = lane; j < D; j += 32) out[(size_t)k * D + j] = n0[(size_t)i * D + j];
+      k = ls;
+      for (int i = sol_g; i >= 0; i = p1[i], k++)
+        for (int j = lane; j < D; j += 32) out[(size_t)k * D + j] = n1[(size_t)i * D + j];
+      plen = ls + lg;
+    }
+  }
+  if (lane == 0) {
+    r.q_status[q] = status;
+    r.q_pathlen[q] = plen;
+    r.q_iters[q] = r.iters[w];
+    r.slot_query[w] = -1;
+    atomicAdd(&r.pending[1], 1u);
+  }
+  rrt_blank_edges(r.edge_a + (size_t)w * r.S * D, r.edge_b + (size_t)w * r.S * D, r.S * D, lane);
+}
+
+// One warp per slot.  A round consumes the verdicts of the slot's pending sub-edges and emits the next ones.
 // An iteration of RRTConnect::solve is  growTree(tree, rstate)  followed, unless TRAPPED, by the connect loop
 // `while (gsc == ADVANCED) gsc = growTree(otherTree, tgi, rmotion)`.  Both are emitted in ONE round (phase 3): slot 0
 // carries the extend edge; its end state q_new is known before it is validated, so slots 1.. carry the first steps
@@ -218,21 +261,44 @@ __device__ __forceinline__ int rrt_emit_walk(float *ea, float *eb, int slot0, in
 // continues in the following rounds (phase 2) with all S slots.
 __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc sp, float range, const unsigned *__restrict__ verdict_bits) {
   const unsigned FULL = 0xffffffffu;
-  const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int w = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   const int lane = threadIdx.x & 31;
-  if (q >= r.n_queries) return;
-  if (r.status[q] != MPB_RRT_ACTIVE) return;
+  if (w >= r.n_slots) return;
   const int D = r.dim, S = r.S;
-  float *ea = r.edge_a + (size_t)q * S * D, *eb = r.edge_b + (size_t)q * S * D, *tg = r.target + (size_t)q * D;
-  const int phase = r.phase[q];
-  int T = r.tsel[q];  // phase 3: the tree of the extend edge; phase 2: the connecting tree
+  float *ea = r.edge_a + (size_t)w * S * D, *eb = r.edge_b + (size_t)w * S * D, *tg = r.target + (size_t)w * D;
+  int q = r.slot_query[w];
+  if (q < 0) {
+    // ---- idle slot: take the next pending query (the trees restart from its start state)
+    unsigned nxt = 0;
+    if (lane == 0) nxt = r.pending[0] < (unsigned)r.n_queries ? atomicAdd(&r.pending[0], 1u) : 0xffffffffu;
+    nxt = __shfl_sync(FULL, nxt, 0);
+    if (nxt >= (unsigned)r.n_queries) return;  // nothing left: the slot stays idle (its edges are already blank)
+    q = (int)nxt;
+    float *root = r.nodes + ((size_t)w * 2 + 0) * r.cap * D;
+    for (int j = lane; j < D; j += 32) root[j] = r.start[(size_t)q * D + j];
+    if (lane == 0) {
+      r.parent[((size_t)w * 2 + 0) * r.cap] = -1;
+      r.size[w * 2] = 1; r.size[w * 2 + 1] = 0;   // tStart_ holds the start state
+      r.goals_used[w] = 0; r.phase[w] = 0; r.flag_start[w] = 1; r.iters[w] = 0; r.rounds_used[w] = 0;
+      r.slot_query[w] = q;
+    }
+    __syncwarp();
+  }
+  if (r.max_rounds_q > 0) {
+    const int used = r.rounds_used[w];
+    if (used >= r.max_rounds_q) { rrt_finish(r, w, q, MPB_RRT_ACTIVE, -1, -1, lane); return; }  // per-query budget spent: "Timeout"
+    __syncwarp();
+    if (lane == 0) r.rounds_used[w] = used + 1;
+  }
+  const int phase = r.phase[w];
+  int T = r.tsel[w];  // phase 3: the tree of the extend edge; phase 2: the connecting tree
   bool new_iter = phase == 0;
   if (phase != 0) {
     // ---- verdicts of the pending sub-edges: sub-edge k is invalid if any of its samples collides
-    const int ns_all = r.n_steps[q];
+    const int ns_all = r.n_steps[w];
     unsigned bad = 0;
     for (int k = lane; k < ns_all * r.smax; k += 32) {
-      const unsigned s = (unsigned)q * S * r.smax + k;
+      const unsigned s = (unsigned)w * S * r.smax + k;
       if ((verdict_bits[s >> 5] >> (s & 31)) & 1u) bad |= 1u << (k / r.smax);
     }
     bad = __reduce_or_sync(FULL, bad);
@@ -242,15 +308,11 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
       calls = 1;
       if (bad & 1u) { go = false; new_iter = true; }  // the extend is TRAPPED: the speculative connect steps are void
       else {
-        const int n = r.size[q * 2 + T];
-        if (n + 1 > r.cap) {
-          if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
-          rrt_blank_edges(ea, eb, S * D, lane);
-          return;
-        }
-        float *node = r.nodes + (((size_t)q * 2 + T) * r.cap + n) * D;
+        const int n = r.size[w * 2 + T];
+        if (n + 1 > r.cap) { rrt_finish(r, w, q, MPB_RRT_CAPACITY, -1, -1, lane); return; }
+        float *node = r.nodes + (((size_t)w * 2 + T) * r.cap + n) * D;
         for (int j = lane; j < D; j += 32) node[j] = eb[j];
-        if (lane == 0) { r.parent[((size_t)q * 2 + T) * r.cap + n] = r.nearest[q]; r.size[q * 2 + T] = n + 1; r.added[q] = n; }
+        if (lane == 0) { r.parent[((size_t)w * 2 + T) * r.cap + n] = r.nearest[w]; r.size[w * 2 + T] = n + 1; r.added[w] = n; }
         T = 1 - T;  // the connect loop grows the other tree
         first_slot = 1;
         bad >>= 1;
@@ -260,113 +322,81 @@ __global__ void __launch_bounds__(256) rrt_advance_kernel(RrtState r, SpaceDesc 
       const int ns = ns_all - first_slot;
       const int n_add = bad ? (__ffs(bad) - 1) : ns;  // valid prefix of the connect walk
       calls += n_add + (bad ? 1 : 0);
-      const int n = r.size[q * 2 + T];
-      if (n + n_add > r.cap) {
-        if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
-        rrt_blank_edges(ea, eb, S * D, lane);
-        return;
-      }
-      float *node = r.nodes + (((size_t)q * 2 + T) * r.cap + n) * D;
+      const int n = r.size[w * 2 + T];
+      if (n + n_add > r.cap) { rrt_finish(r, w, q, MPB_RRT_CAPACITY, -1, -1, lane); return; }
+      float *node = r.nodes + (((size_t)w * 2 + T) * r.cap + n) * D;
       for (int j = lane; j < n_add * D; j += 32) node[j] = eb[first_slot * D + j];
-      const int near_c = phase == 3 ? r.nearest2[q] : r.nearest[q];
-      for (int k = lane; k < n_add; k += 32) r.parent[((size_t)q * 2 + T) * r.cap + n + k] = k == 0 ? near_c : n + k - 1;
-      if (lane == 0 && n_add) r.size[q * 2 + T] = n + n_add;
+      const int near_c = phase == 3 ? r.nearest2[w] : r.nearest[w];
+      for (int k = lane; k < n_add; k += 32) r.parent[((size_t)w * 2 + T) * r.cap + n + k] = k == 0 ? near_c : n + k - 1;
+      if (lane == 0 && n_add) r.size[w * 2 + T] = n + n_add;
       __syncwarp();
-      if (n_add == ns && r.reach[q]) {  // REACHED: the trees meet
-        if (lane == 0) {
-          const int m_first = r.added[q], m_other = n + n_add - 1;  // first tree = 1 - T
-          int is = T == 0 ? m_other : m_first, ig = T == 0 ? m_first : m_other;
-          const int ps = r.parent[((size_t)q * 2 + 0) * r.cap + is];
-          if (ps >= 0) is = ps;  // one step back so the shared state is not duplicated on the path
-          else ig = r.parent[((size_t)q * 2 + 1) * r.cap + ig];
-          r.sol[q * 2] = is;
-          r.sol[q * 2 + 1] = ig;
-          r.status[q] = MPB_RRT_SOLVED;
-          r.iters[q] += calls;
-          atomicSub(r.n_active, 1u);
-        }
-        rrt_blank_edges(ea, eb, S * D, lane);
+      if (n_add == ns && r.reach[w]) {  // REACHED: the trees meet
+        const int m_first = r.added[w], m_other = n + n_add - 1;  // first tree = 1 - T
+        int is = T == 0 ? m_other : m_first, ig = T == 0 ? m_first : m_other;
+        const int ps = r.parent[((size_t)w * 2 + 0) * r.cap + is];
+        if (ps >= 0) is = ps;  // one step back so the shared state is not duplicated on the path
+        else ig = r.parent[((size_t)w * 2 + 1) * r.cap + ig];
+        if (lane == 0) r.iters[w] += calls;
+        __syncwarp();
+        rrt_finish(r, w, q, MPB_RRT_SOLVED, is, ig, lane);
         return;
       }
       if (n_add < ns) new_iter = true;  // ADVANCED n_add times, then TRAPPED
     }
-    if (lane == 0) r.iters[q] += calls;
+    if (lane == 0) r.iters[w] += calls;
     __syncwarp();  // the sampling counter below reads it
   }
   if (new_iter) {
     // ---- head of the solve loop: pick the tree, maybe admit another goal, sample
-    const int fs = r.flag_start[q];
+    const int fs = r.flag_start[w];
     T = fs ? 0 : 1;
-    const int gsz = r.size[q * 2 + 1], used = r.goals_used[q];
+    const int gsz = r.size[w * 2 + 1], used = r.goals_used[w];
     if ((gsz == 0 || used < gsz / 2) && used < r.n_goals[q]) {
-      if (gsz >= r.cap) {
-        if (lane == 0) { r.status[q] = MPB_RRT_CAPACITY; atomicSub(r.n_active, 1u); }
-        rrt_blank_edges(ea, eb, S * D, lane);
-        return;
-      }
-      float *node = r.nodes + (((size_t)q * 2 + 1) * r.cap + gsz) * D;
+      if (gsz >= r.cap) { rrt_finish(r, w, q, MPB_RRT_CAPACITY, -1, -1, lane); return; }
+      float *node = r.nodes + (((size_t)w * 2 + 1) * r.cap + gsz) * D;
       const float *g = r.goals + ((size_t)q * r.max_goals + used) * D;
       for (int j = lane; j < D; j += 32) node[j] = g[j];
-      if (lane == 0) { r.parent[((size_t)q * 2 + 1) * r.cap + gsz] = -1; r.size[q * 2 + 1] = gsz + 1; r.goals_used[q] = used + 1; }
-    } else if (gsz == 0) {
-      if (lane == 0) { r.status[q] = MPB_RRT_INVALID_GOAL; atomicSub(r.n_active, 1u); }
-      rrt_blank_edges(ea, eb, S * D, lane);
-      return;
-    }
-    const unsigned ctr = (unsigned)r.iters[q];
+      if (lane == 0) { r.parent[((size_t)w * 2 + 1) * r.cap + gsz] = -1; r.size[w * 2 + 1] = gsz + 1; r.goals_used[w] = used + 1; }
+    } else if (gsz == 0) { rrt_finish(r, w, q, MPB_RRT_INVALID_GOAL, -1, -1, lane); return; }
+    const unsigned ctr = (unsigned)r.iters[w];
     for (int j = lane; j < D; j += 32) tg[j] = fmaf(sp.hi[j] - sp.lo[j], rrt_uniform(r.seed, (unsigned)q, ctr, (unsigned)j), sp.lo[j]);
     __syncwarp();
     // ---- growTree(tree, rstate): the extend edge into slot 0 ...
-    const float *base = r.nodes + ((size_t)q * 2 + T) * r.cap * D;
+    const float *base = r.nodes + ((size_t)w * 2 + T) * r.cap * D;
     float best;
-    const int bi = rrt_nearest(base, r.size[q * 2 + T], D, tg, sp, lane, &best);
+    const int bi = rrt_nearest(base, r.size[w * 2 + T], D, tg, sp, lane, &best);
     bool reach0;
     rrt_emit_walk(ea, eb, 0, 1, 1, base + (size_t)bi * D, best, tg, range, D, sp, lane, &reach0);
     __syncwarp();
     for (int j = lane; j < D; j += 32) tg[j] = eb[j];  // q_new: the target of the connect loop
     __syncwarp();
     // ---- ... and the first steps of the connect walk of the other tree towards q_new into slots 1..
-    const float *base2 = r.nodes + ((size_t)q * 2 + (1 - T)) * r.cap * D;
+    const float *base2 = r.nodes + ((size_t)w * 2 + (1 - T)) * r.cap * D;
     float best2;
-    const int bi2 = rrt_nearest(base2, r.size[q * 2 + (1 - T)], D, tg, sp, lane, &best2);
+    const int bi2 = rrt_nearest(base2, r.size[w * 2 + (1 - T)], D, tg, sp, lane, &best2);
     bool reach2;
     const int ns2 = rrt_emit_walk(ea, eb, 1, S, S - 1, base2 + (size_t)bi2 * D, best2, tg, range, D, sp, lane, &reach2);
     if (lane == 0) {
-      r.flag_start[q] = !fs; r.tsel[q] = T; r.phase[q] = 3;
-      r.nearest[q] = bi; r.nearest2[q] = bi2; r.reach[q] = reach2 ? 1 : 0; r.n_steps[q] = 1 + ns2;
+      r.flag_start[w] = !fs; r.tsel[w] = T; r.phase[w] = 3;
+      r.nearest[w] = bi; r.nearest2[w] = bi2; r.reach[w] = reach2 ? 1 : 0; r.n_steps[w] = 1 + ns2;
     }
     return;
   }
   // ---- the connect walk continues (phase 2): nearest neighbour of the connecting tree and the next S steps
-  const float *base = r.nodes + ((size_t)q * 2 + T) * r.cap * D;
+  const float *base = r.nodes + ((size_t)w * 2 + T) * r.cap * D;
   float best;
-  const int bi = rrt_nearest(base, r.size[q * 2 + T], D, tg, sp, lane, &best);
+  const int bi = rrt_nearest(base, r.size[w * 2 + T], D, tg, sp, lane, &best);
   bool reach;
   const int ns = rrt_emit_walk(ea, eb, 0, S, S, base + (size_t)bi * D, best, tg, range, D, sp, lane, &reach);
-  if (lane == 0) { r.tsel[q] = T; r.phase[q] = 2; r.nearest[q] = bi; r.reach[q] = reach ? 1 : 0; r.n_steps[q] = ns; }
+  if (lane == 0) { r.tsel[w] = T; r.phase[w] = 2; r.nearest[w] = bi; r.reach[w] = reach ? 1 : 0; r.n_steps[w] = ns; }
 }
 
-// Solution path of every solved query: start chain (root first) then goal chain (towards its root).
-__global__ void rrt_extract_kernel(RrtState r, float *__restrict__ paths, int *__restrict__ path_len) {
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= r.n_queries) return;
-  path_len[q] = 0;
-  if (r.status[q] != MPB_RRT_SOLVED) return;
-  const int D = r.dim;
-  const int *p0 = r.parent + ((size_t)q * 2 + 0) * r.cap, *p1 = r.parent + ((size_t)q * 2 + 1) * r.cap;
-  int ls = 0, lg = 0;
-  for (int i = r.sol[q * 2]; i >= 0; i = p0[i]) ls++;
-  for (int i = r.sol[q * 2 + 1]; i >= 0; i = p1[i]) lg++;
-  if (ls + lg > r.max_path) { r.status[q] = MPB_RRT_PATH_TOO_LONG; return; }
-  float *out = paths + (size_t)q * r.max_path * D;
-  const float *n0 = r.nodes + ((size_t)q * 2 + 0) * r.cap * D, *n1 = r.nodes + ((size_t)q * 2 + 1) * r.cap * D;
-  int k = ls - 1;
-  for (int i = r.sol[q * 2]; i >= 0; i = p0[i], k--)
-    for (int j = 0; j < D; j++) out[(size_t)k * D + j] = n0[(size_t)i * D + j];
-  k = ls;
-  for (int i = r.sol[q * 2 + 1]; i >= 0; i = p1[i], k++)
-    for (int j = 0; j < D; j++) out[(size_t)k * D + j] = n1[(size_t)i * D + j];
-  path_len[q] = ls + lg;
+// End of the call: queries still in a slot keep status MPB_RRT_ACTIVE ("Timeout"); their growTree count is recorded.
+__global__ void rrt_flush_kernel(RrtState r) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= r.n_slots) return;
+  const int q = r.slot_query[w];
+  if (q >= 0) r.q_iters[q] = r.iters[w];
 }
 
 // [Q][max_path][D] -> packed rows: query q owns rows off[q] .. off[q+1] of `packed`

@@ -117,9 +117,13 @@ class OMPLPlanner:
         return status[0], paths[0]
 
     def plan_batch(self, start_states, goal_states, planner_name="RRTConnect", time=1.0, range=0.0, verbose=False,
-                   max_rounds=8192, tree_capacity=4096, max_path=2048, seed=None, check_every=16, connect_steps=8):
+                   max_rounds=8192, tree_capacity=4096, max_path=2048, seed=None, check_every=16, connect_steps=8, n_slots=0,
+                   max_rounds_per_query=0):
         """Q independent queries.  start_states [Q, dim]; goal_states: per query a list of goal states (or an array
-        [Q, dim] for one goal each).  -> (list of status strings, list of float64 paths [n_i, dim], stats)"""
+        [Q, dim] for one goal each).  -> (list of status strings, list of float64 paths [n_i, dim], stats)
+        ``time`` bounds the whole call; ``max_rounds_per_query`` is the per-query budget (the role ``time`` plays for the
+        reference's one query per call); ``n_slots`` < Q runs the queries through that many concurrent searches, a
+        finished query's slot taking the next pending one."""
         if planner_name != "RRTConnect":
             if planner_name in ("RRT", "PRMstar", "LazyPRMstar", "RRTstar", "RRTsharp", "RRTXstatic", "InformedRRTstar"):
                 raise NotImplementedError(f"{planner_name} is outside the accelerated path (only RRTConnect is ported)")
@@ -164,7 +168,7 @@ class OMPLPlanner:
         seed = int(_global_rng.randint(0, 2 ** 31 - 1)) if seed is None else int(seed)
         st, paths, stats = dev.rrtconnect(self.space, starts, goals, ng, range_=range, max_rounds=max_rounds, time_limit=time,
                                           tree_capacity=tree_capacity, max_path=max_path, seed=seed, check_every=check_every,
-                                          connect_steps=connect_steps)
+                                          connect_steps=connect_steps, n_slots=n_slots, max_rounds_per_query=max_rounds_per_query)
         status, out = [], []
         for i in builtins.range(Q):  # `range` is the reference's argument name
             s = _STATUS.get(int(st[i]), "Unknown")

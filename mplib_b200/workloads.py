@@ -312,13 +312,13 @@ def c1_q(n=10000):
 
 def c4(batch=0):
     """configs[3]: RRTConnect plan_qpos queries in the C4 scene.  ``batch`` = planning queries per GPU per step."""
-    n = batch or 1024
+    n = batch or 4096
     w = c4_world()
     desc = compile_desc(w)
     return {
         "world": w, "desc": desc, "batch": n,
         "config": {"workload": "configs[3]: RRTConnect plan_qpos, C4 scene (Panda + grasped box vs 16 boxes + 50k-point table "
-                               f"octree), {n} independent (start, goal) queries per GPU per step (seed 5), range 0.1, validity "
+                               f"octree), {n} independent (start, goal) queries per GPU per step (seed 5) through concurrent search slots, range 0.1, validity "
                                "resolution 1 %, one goal per query, every state of every edge checked (DiscreteMotionValidator)",
                    "queries_per_gpu": n, "state_dim": desc.state_dim, "pairs": desc.n_pairs,
                    "outputs": "status + waypoint matrix per query",

@@ -121,3 +121,32 @@ def test_rrtconnect_c4_scene_and_plan_api():
         pl.plan(starts[0][:6], [goals[0][:6]])
     with pytest.raises(RuntimeError, match="Planner Not implemented"):
         pl.plan(starts[0], [goals[0]], planner_name="Nope")
+
+
+def test_rrtconnect_slots_retire_and_refill():
+    """Q queries through fewer concurrent slots: a slot whose query ends takes the next pending one.  The per-query
+    result does not depend on the slot schedule (random numbers are keyed by the query, trees are per query), and the
+    per-query round budget turns long searches into "Timeout" without touching the others."""
+    from mplib_b200.pymp import OMPLPlanner
+    from tests.workloads import c4_world, free_states
+
+    w = c4_world(cloud_points=20000)
+    pl = OMPLPlanner(w)
+    pts = free_states(w, 192, 54, w.collide_batch)
+    starts, goals = pts[:96], pts[96:]
+    kw = dict(range=0.1, time=60.0, seed=11, max_rounds=200000, tree_capacity=4096)
+    s_all, p_all, st_all = pl.plan_batch(starts, goals, **kw)
+    s_16, p_16, st_16 = pl.plan_batch(starts, goals, n_slots=16, **kw)
+    assert s_all == s_16
+    assert all(np.array_equal(a, b) for a, b in zip(p_all, p_16))
+    assert st_16["n_solved"] == st_all["n_solved"] >= 85 and st_16["rounds"] > st_all["rounds"]
+    n = _validate_paths(w._sync()["dev"].desc, pl, starts, goals, s_16, p_16, 0.1)
+    assert n == st_16["n_solved"]
+    # per-query budget: the queries that needed more rounds end as "Timeout", the others are unchanged
+    s_b, p_b, st_b = pl.plan_batch(starts, goals, n_slots=16, max_rounds_per_query=40, **kw)
+    assert 0 < st_b["n_solved"] < st_all["n_solved"]
+    for i, s in enumerate(s_b):
+        if s == "Exact solution":
+            assert s_all[i] == s and np.array_equal(p_b[i], p_all[i])
+        else:
+            assert s == "Timeout" and p_b[i].shape == (0, 7)
