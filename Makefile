@@ -5,11 +5,19 @@ LIB = mplib_b200/libmpb.so
 SRC = mplib_b200/csrc/mpb.cu
 HDR = $(wildcard mplib_b200/csrc/*.cuh) include/mpb.h
 
-all: $(LIB) oracle
+all: $(LIB) native oracle
 
 $(LIB): $(SRC) $(HDR)
 	mkdir -p build
 	$(NVCC) $(NVCCFLAGS) -Xptxas -v -o $@ $(SRC) 2> build/ptxas.log || (cat build/ptxas.log; false)
+
+# pybind11 host module over the C-ABI (per-call path): g++ only, Python.h + pybind11 headers from the interpreter on PATH
+PYEXT := $(shell python -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
+PYINC := $(shell python -c "import sysconfig, pybind11; print('-I' + sysconfig.get_paths()['include'] + ' -I' + pybind11.get_include())")
+NATIVE = mplib_b200/_native$(PYEXT)
+native: $(NATIVE)
+$(NATIVE): mplib_b200/csrc/pymp_native.cpp include/mpb.h $(LIB)
+	g++ -O2 -std=c++17 -fPIC -shared -fvisibility=hidden -Wall $(PYINC) -o $@ mplib_b200/csrc/pymp_native.cpp -Lmplib_b200 -lmpb -Wl,-rpath,'$$ORIGIN'
 
 oracle: oracle/_build/liboracle.so
 oracle/_build/liboracle.so: oracle/oracle.c include/mpb.h
@@ -17,6 +25,6 @@ oracle/_build/liboracle.so: oracle/oracle.c include/mpb.h
 	gcc -O3 -fopenmp -fPIC -shared -Wall -Wextra -o $@ oracle/oracle.c -lm
 
 clean:
-	rm -f $(LIB) oracle/_build/liboracle.so
+	rm -f $(LIB) $(NATIVE) oracle/_build/liboracle.so
 
-.PHONY: all oracle clean
+.PHONY: all native oracle clean

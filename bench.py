@@ -49,8 +49,8 @@ def parse():
     ap.add_argument("--plan-inflight", type=int, default=2, help="c4: plan_batch calls kept in flight (host threads)")
     ap.add_argument("--max-rounds", type=int, default=20000, help="c4: cap on lock-step RRTConnect rounds per step")
     ap.add_argument("--connect-steps", type=int, default=8, help="c4: connect-walk steps validated per lock-step round")
-    ap.add_argument("--plan-slots", type=int, default=2048, help="c4: concurrent searches per plan_batch call; a finished query's slot takes the next pending query")
-    ap.add_argument("--plan-rounds-per-query", type=int, default=1024,
+    ap.add_argument("--plan-slots", type=int, default=4096, help="c4: concurrent searches per plan_batch call; a finished query's slot takes the next pending query")
+    ap.add_argument("--plan-rounds-per-query", type=int, default=4096,
                     help="c4: the PER-QUERY budget in lock-step rounds (the role of OMPL's `time`; the reference arm gives every "
                          "query 1.0 s of one host thread, Planner.plan's default).  Both arms print solve_rate and "
                          "grow_calls_per_query so the budgets can be compared")
@@ -563,7 +563,9 @@ def run_c4(args, ctx, batch, steps, warmup):
             "solve_rate": solved / (float(Q) * world * K), "calls_in_flight": F,
             "budget": {"per_query_rounds": args.plan_rounds_per_query, "slots_per_call": min(args.plan_slots, Q),
                        "grow_calls_per_query": grow / (float(Q) * world * K),
-                       "note": "per-query budget (a query that spends it ends as Timeout and frees its slot); no per-batch deadline"},
+                       "per_query_wall_s": args.plan_rounds_per_query * (gpu_ms / max(rounds / F, 1)) * 1e-3,
+                       "note": "per-query budget (a query that spends it ends as Timeout and frees its slot); no per-batch deadline; "
+                               "per_query_wall_s = budget x measured time per round, to set beside the reference arm's 1.0 s per query"},
             "e2e": {"value": solved / wall, "unit": PLAN_UNIT, "h2d_bytes_per_step": int(Q * 2 * desc.state_dim * 4 + Q * 4),
                     "d2h_bytes_per_step": int(Q * 8 + Q * kw["max_path"] * desc.state_dim * 4)},
             "gpu_launches": int(launches), "clocks": clocks,

@@ -68,6 +68,29 @@ class MpbError(RuntimeError):
     pass
 
 
+# The pybind11 host module (csrc/pymp_native.cpp) carries the per-call path when it is built: numpy buffers in, C-ABI
+# call with the GIL released, result words unpacked in C++.  The ctypes binding below stays as the fallback BINDING
+# (never a compute path) and serves the pointer-level calls.
+try:
+    if os.environ.get("MPB_NO_NATIVE"):
+        raise ImportError("disabled by MPB_NO_NATIVE")
+    from . import _native
+except ImportError:
+    _native = None
+
+
+def _nat(f, *a, **k):
+    """Call into the native module with the binding's exception types (MpbError for non-argument failures)."""
+    try:
+        return f(*a, **k)
+    except ValueError:
+        raise
+    except RuntimeError as e:
+        if isinstance(e, MpbError) or str(e).startswith("State dimension"):
+            raise
+        raise MpbError(str(e)) from None
+
+
 def load():
     global _lib
     if _lib is not None:
@@ -135,16 +158,25 @@ class DeviceScene:
         lib = load()
         self.desc = desc
         self.device = device
-        h = C.c_void_p()
-        _check(lib.mpb_scene_create(C.byref(desc.as_struct()), device, C.byref(h)))
-        self._h = h
+        self._n = None
+        if _native is not None:
+            self._n = _nat(_native.Scene, {k: getattr(desc, k) for k in desc._ARRAYS}, device)
+            self._h = C.c_void_p(self._n.handle)  # the same handle serves the pointer-level ctypes calls
+        else:
+            h = C.c_void_p()
+            _check(lib.mpb_scene_create(C.byref(desc.as_struct()), device, C.byref(h)))
+            self._h = h
         self.n_pairs = desc.n_pairs
         self.pair_words = (desc.n_pairs + 31) // 32
         self.state_dim = desc.state_dim
         self.n_links = desc.n_links
 
     def close(self):
-        if getattr(self, "_h", None) and _lib is not None:  # _lib is None during interpreter shutdown
+        if getattr(self, "_n", None) is not None:
+            self._n.close()
+            self._n = None
+            self._h = None
+        elif getattr(self, "_h", None) and _lib is not None:  # _lib is None during interpreter shutdown
             _lib.mpb_scene_destroy(self._h)
             self._h = None
 
@@ -152,13 +184,19 @@ class DeviceScene:
 
     def set_q_base(self, q_base):
         q = np.ascontiguousarray(np.asarray(q_base, dtype=np.float64))
-        _check(load().mpb_scene_set_q_base(self._h, q.ctypes.data, q.shape[0]))
+        if self._n is not None:
+            _nat(self._n.set_q_base, q)
+        else:
+            _check(load().mpb_scene_set_q_base(self._h, q.ctypes.data, q.shape[0]))
         self.desc = self.desc.with_q_base(q)
 
     def set_pairs(self, pair_a, pair_b, pair_kinds=()):
         a = np.ascontiguousarray(np.asarray(pair_a, dtype=np.int32))
         b = np.ascontiguousarray(np.asarray(pair_b, dtype=np.int32))
-        _check(load().mpb_scene_set_pairs(self._h, a.shape[0], a.ctypes.data, b.ctypes.data))
+        if self._n is not None:
+            _nat(self._n.set_pairs, a, b)
+        else:
+            _check(load().mpb_scene_set_pairs(self._h, a.shape[0], a.ctypes.data, b.ctypes.data))
         self.desc = self.desc.with_pairs(a, b, pair_kinds)
         self.n_pairs = int(a.shape[0])
         self.pair_words = (self.n_pairs + 31) // 32
@@ -168,12 +206,18 @@ class DeviceScene:
         idx = np.ascontiguousarray(np.asarray(idx, dtype=np.int32).reshape(-1))
         loc = None if obj_local is None else np.ascontiguousarray(np.asarray(obj_local, dtype=np.float64).reshape(-1, 12))
         par = None if obj_param is None else np.ascontiguousarray(np.asarray(obj_param, dtype=np.float64).reshape(-1, 4))
-        _check(load().mpb_scene_update_objects(self._h, idx.shape[0], _ptr(idx), _ptr(loc), _ptr(par)))
+        if self._n is not None:
+            _nat(self._n.update_objects, idx, loc, par)
+        else:
+            _check(load().mpb_scene_update_objects(self._h, idx.shape[0], _ptr(idx), _ptr(loc), _ptr(par)))
         self.desc = self.desc.with_objects(idx, loc, par)
 
     def poll(self, wait=True):
         """Harvest finished device-pointer calls -> (summed stats dict, calls completed, calls failed).  Raises MpbError
         when a harvested call overflowed the work queues."""
+        if self._n is not None:
+            st, done, failed = _nat(self._n.poll, bool(wait))
+            return st, int(done), int(failed)
         st = MpbStats()
         done, failed = C.c_int64(0), C.c_int64(0)
         _check(load().mpb_scene_poll(self._h, 1 if wait else 0, C.byref(st), C.byref(done), C.byref(failed)))
@@ -189,6 +233,9 @@ class DeviceScene:
         if q.ndim != 2 or q.shape[1] != self.state_dim:
             raise RuntimeError(f"State dimension is not correct: expected [n,{self.state_dim}], got {q.shape}")
         n = q.shape[0]
+        if self._n is not None:
+            verdict, h, st = _nat(self._n.collide_hits, q, int(hit_cap) if hit_cap is not None else 0)
+            return (verdict, h, st) if stats else (verdict, h)
         cap = int(hit_cap) if hit_cap is not None else max(1024, 4 * n)
         st = MpbStats()
         while True:
@@ -211,6 +258,9 @@ class DeviceScene:
         if q.ndim != 2 or q.shape[1] != self.state_dim:
             raise RuntimeError(f"State dimension is not correct: expected [n,{self.state_dim}], got {q.shape}")
         n = q.shape[0]
+        if self._n is not None:
+            verdict, pairs, st = _nat(self._n.collide, q, bool(want_pairs), bool(stats))
+            return (verdict, pairs, st) if stats else (verdict, pairs)
         vb = np.zeros((n + 31) // 32, dtype=np.uint32)
         pb = np.zeros((n, max(self.pair_words, 1)), dtype=np.uint32) if want_pairs else None
         st = MpbStats()
@@ -239,6 +289,8 @@ class DeviceScene:
         q = np.ascontiguousarray(np.asarray(q, dtype=np.float32))
         if q.ndim != 2 or q.shape[1] != self.state_dim:
             raise RuntimeError(f"State dimension is not correct: expected [n,{self.state_dim}], got {q.shape}")
+        if self._n is not None:
+            return _nat(self._n.fk, q)
         out = np.zeros((q.shape[0], self.n_links, 7), dtype=np.float32)
         _check(load().mpb_fk_batch(self._h, _ptr(q), q.shape[0], _ptr(out), MPB_HOST, None))
         return out
@@ -250,6 +302,9 @@ class DeviceScene:
         if q.ndim != 2 or q.shape[1] != self.state_dim:
             raise RuntimeError(f"State dimension is not correct: expected [n,{self.state_dim}], got {q.shape}")
         n = q.shape[0]
+        if self._n is not None:
+            out, am, st = _nat(self._n.distance, q)
+            return (out, am, st) if stats else (out, am)
         md = np.zeros(n, dtype=np.float32)
         am = np.zeros(n, dtype=np.int32)
         st = MpbStats()

@@ -312,7 +312,7 @@ def c1_q(n=10000):
 
 def c4(batch=0):
     """configs[3]: RRTConnect plan_qpos queries in the C4 scene.  ``batch`` = planning queries per GPU per step."""
-    n = batch or 4096
+    n = batch or 8192
     w = c4_world()
     desc = compile_desc(w)
     return {

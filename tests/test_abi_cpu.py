@@ -156,3 +156,17 @@ def test_two_articulations_state_split_in_name_order():
     for k in desc.pair_kinds:
         kinds[k] = kinds.get(k, 0) + 1
     assert kinds == {"self": 38, "self_articulation": 121}
+
+
+def test_native_host_module_builds_and_fails_loudly_without_gpu():
+    """The pybind11 host module (csrc/pymp_native.cpp) is what the per-call path runs through; it must import, expose the
+    scene class, and -- like the C-ABI under it -- refuse to work without a CUDA device instead of falling back."""
+    from mplib_b200 import _lib
+    from tests.common import compile_desc, make_panda_world
+
+    assert _lib._native is not None, "mplib_b200/_native*.so is missing: run `make`"
+    for name in ("collide", "collide_hits", "fk", "distance", "poll", "set_q_base", "set_pairs", "update_objects", "close", "handle"):
+        assert hasattr(_lib._native.Scene, name)
+    if _lib.load().mpb_device_count() == 0:
+        with pytest.raises(_lib.MpbError, match="no CUDA device"):
+            _lib.DeviceScene(compile_desc(make_panda_world()), 0)

@@ -257,3 +257,31 @@ def test_unplanned_articulation_and_two_attached_bodies():
     hit = np.argwhere(oph[:, k == "attach_attach"].any(axis=1)).ravel()
     w.set_qpos_all(q[hit[0]])
     assert any(r.collision_type == "attach_attach" for r in w.collide_full())
+
+
+def test_native_module_and_ctypes_binding_agree(monkeypatch):
+    """The per-call path through the pybind11 module (default) and through the ctypes fallback binding: same results."""
+    from mplib_b200 import _lib
+
+    assert _lib._native is not None
+    w = _c3_small_world(n_each=4)
+    desc = w._sync()["dev"].desc
+    q = random_q(3000, 5)
+    nat = _lib.DeviceScene(desc, 0)
+    assert nat._n is not None
+    monkeypatch.setattr(_lib, "_native", None)
+    ct = _lib.DeviceScene(desc, 0)
+    assert ct._n is None
+    for n in (1, 3000):
+        a, b = nat.collide(q[:n], stats=True), ct.collide(q[:n], stats=True)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2]["n_states"] == b[2]["n_states"] == n
+        a, b = nat.collide_hits(q[:n]), ct.collide_hits(q[:n])
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+        assert np.array_equal(nat.fk(q[:n]), ct.fk(q[:n]))
+        a, b = nat.distance(q[:n]), ct.distance(q[:n])
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    v, _ = nat.collide(q[:10], want_pairs=False)
+    assert _ is None and v.dtype == bool
+    with pytest.raises(RuntimeError, match="State dimension"):
+        nat.collide(np.zeros((3, 5)))
+    nat.close(); ct.close()
