@@ -248,11 +248,21 @@ __device__ __forceinline__ float gjk_lane(DevShape A, DevShape B, const float *R
   return dist;
 }
 
-__device__ __forceinline__ float best_distance(const unsigned long long *best, int cfg) {  // smallest distance known so far
+// Smallest distance known so far for the configuration, as a pruning bound for pair p.  An intersecting pair (-1) found
+// by a pair of HIGHER index does not end the search: the arg-min is the first intersecting pair in list order
+// (the reference keeps the first pair that attains the minimum), so p must still find out whether it intersects --
+// the bound is then 0 (only overlapping nodes survive).  -> false: a pair of lower index already intersects, p cannot matter.
+__device__ __forceinline__ bool best_bound(const unsigned long long *best, int cfg, int p, float &ub) {
   const unsigned long long b = *reinterpret_cast<const volatile unsigned long long *>(best + cfg);
-  if (b == ~0ull) return FLT_MAX;
+  if (b == ~0ull) return true;
   const unsigned key = (unsigned)(b >> 32);
-  return key == 0u ? -1.f : __uint_as_float(key & 0x7fffffffu);
+  if (key == 0u) {
+    if ((unsigned)(b & 0xffffffffu) < (unsigned)p) return false;
+    ub = fminf(ub, 0.f);
+    return true;
+  }
+  ub = fminf(ub, __uint_as_float(key & 0x7fffffffu));
+  return true;
 }
 __device__ __forceinline__ float gap3(float d0, float d1, float d2) {  // length of the positive parts
   d0 = fmaxf(d0, 0.f); d1 = fmaxf(d1, 0.f); d2 = fmaxf(d2, 0.f);
@@ -294,8 +304,8 @@ __global__ void __launch_bounds__(128) distance_expand_kernel(SceneImg img, Work
     it = first + __shfl_sync(FULL, it, 0);
     if (it >= end) break;
     const int cfg = wq.icfg[it], p = wq.ipair[it];
-    float ub = best_distance(best, cfg);
-    if (ub < 0.f) continue;  // some pair of this configuration already intersects: nothing can be smaller
+    float ub = FLT_MAX;
+    if (!best_bound(best, cfg, p, ub)) continue;  // a pair of lower index already intersects: this one cannot change the result
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // the shape
     const DevObject &B = img.objs[pr.b];  // the BVH object
@@ -327,8 +337,7 @@ __global__ void __launch_bounds__(128) distance_expand_kernel(SceneImg img, Work
     if (lane == 0) stack[0] = B.voff;
     __syncwarp();
     while (sp > 0) {
-      ub = fminf(ub, best_distance(best, cfg));
-      if (ub < 0.f) break;
+      if (!best_bound(best, cfg, p, ub)) break;
       const int take = sp > MPB_EXP_STACK - 64 ? 1 : min(sp, 32);
       int node = -1;
       if ((int)lane < take) node = stack[sp - 1 - (int)lane];
@@ -376,8 +385,8 @@ __global__ void __launch_bounds__(128) distance_expand_kernel(SceneImg img, Work
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) dmin = fminf(dmin, __shfl_xor_sync(FULL, dmin, o));
       if (dmin < local) local = dmin;
+      if (dmin < 0.f) break;  // this pair intersects: nothing smaller to find
       ub = fminf(ub, dmin);
-      if (ub < 0.f) break;
     }
     if (lane == 0 && local < FLT_MAX) {
       const unsigned key = local < 0.f ? 0u : (__float_as_uint(local) | 0x80000000u);
@@ -410,8 +419,8 @@ __global__ void __launch_bounds__(128) distance_expand2_kernel(SceneImg img, Wor
     it = first + __shfl_sync(FULL, it, 0);
     if (it >= end) break;
     const int cfg = wq.icfg[it], p = wq.ipair[it];
-    float ub = best_distance(best, cfg);
-    if (ub < 0.f) continue;
+    float ub = FLT_MAX;
+    if (!best_bound(best, cfg, p, ub)) continue;
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];
     const DevObject &B = img.objs[pr.b];
@@ -430,8 +439,7 @@ __global__ void __launch_bounds__(128) distance_expand2_kernel(SceneImg img, Wor
     if (lane == 0) stack[0] = make_int2(A.voff, B.voff);
     __syncwarp();
     while (sp > 0) {
-      ub = fminf(ub, best_distance(best, cfg));
-      if (ub < 0.f) break;
+      if (!best_bound(best, cfg, p, ub)) break;
       const int take = sp > MPB_EXP2_STACK - 64 ? 1 : min(sp, 32);
       int2 np = make_int2(-1, -1);
       if ((int)lane < take) np = stack[sp - 1 - (int)lane];
@@ -484,8 +492,8 @@ __global__ void __launch_bounds__(128) distance_expand2_kernel(SceneImg img, Wor
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) dmin = fminf(dmin, __shfl_xor_sync(FULL, dmin, o));
       if (dmin < local) local = dmin;
+      if (dmin <= 0.f) break;  // this pair intersects (0: overlapping triangles of two meshes): nothing smaller to find
       ub = fminf(ub, dmin);
-      if (ub < 0.f) break;
     }
     if (lane == 0 && local < FLT_MAX) {
       const unsigned key = local < 0.f ? 0u : (__float_as_uint(local) | 0x80000000u);

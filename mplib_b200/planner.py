@@ -9,6 +9,7 @@ from this image; `plan_qpos` returns the waypoint matrix under "position" exactl
 from __future__ import annotations
 
 import os
+import pathlib
 import xml.etree.ElementTree as ET
 from xml.dom import minidom
 
@@ -51,17 +52,16 @@ class Planner:
         self.move_group_link_id = self.link_name_2_idx[self.move_group]
 
     def replace_package_keyword(self, package_keyword_replacement):
-        """mplib/planner.py:99-116"""
-        rtn_urdf = self.urdf
-        with open(self.urdf, "r") as in_f:
-            content = in_f.read()
-            if "package://" in content:
-                rtn_urdf = self.urdf.replace(".urdf", "_package_keyword_replaced.urdf")
-                content = content.replace("package://", package_keyword_replacement)
-                if not os.path.exists(rtn_urdf):
-                    with open(rtn_urdf, "w") as out_f:
-                        out_f.write(content)
-        return rtn_urdf
+        """Behaviour of mplib/planner.py:99-116: a URDF that refers to ``package://`` resources is written once, next to the
+        original, with that prefix replaced; the path of the file to load is returned."""
+        text = pathlib.Path(self.urdf).read_text()
+        if "package://" not in text:
+            return self.urdf
+        stem, ext = os.path.splitext(self.urdf)
+        patched = pathlib.Path(stem + "_package_keyword_replaced" + (ext or ".urdf"))
+        if not patched.exists():
+            patched.write_text(text.replace("package://", package_keyword_replacement))
+        return str(patched)
 
     # ------------------------------------------------------------------ SRDF auto-generation (SURVEY 8f rank 2)
     def always_colliding_pairs(self, sample_time=1 << 20, seed=None, batch=1 << 18):
@@ -139,22 +139,25 @@ class Planner:
         return True
 
     def check_for_collision(self, collision_function, state=None):
-        """mplib/planner.py:194-224"""
-        planned = self.planning_world.get_planned_articulations()
-        assert len(planned) == 1, "Only support 1 planned articulation now"
-        articulation = planned[0]
-        old_qpos = articulation.get_qpos()
-        if state is None:
-            state = old_qpos
-        state = np.asarray(state, dtype=np.float64)
-        if len(state) == len(self.move_group_joint_indices):
-            tmp = old_qpos.copy()
-            tmp[: len(state)] = state
-            state = tmp
-        articulation.set_qpos(state, True)
-        collisions = collision_function()
-        articulation.set_qpos(old_qpos, True)
-        return collisions
+        """Behaviour of mplib/planner.py:194-224: run ``collision_function`` with the (single) planned articulation
+        placed at ``state`` -- a full qpos or just the move-group joints, default: where it is -- and put it back."""
+        arts = self.planning_world.get_planned_articulations()
+        if len(arts) != 1:
+            raise AssertionError("Only support 1 planned articulation now")
+        art = arts[0]
+        saved = art.get_qpos()
+        q = saved.copy()
+        if state is not None:
+            given = np.asarray(state, dtype=np.float64).reshape(-1)
+            if given.shape[0] == len(self.move_group_joint_indices):
+                q[: given.shape[0]] = given  # move-group joints come first in the user joint order
+            else:
+                q = given
+        art.set_qpos(q, True)
+        try:
+            return collision_function()
+        finally:
+            art.set_qpos(saved, True)
 
     def check_for_self_collision(self, qpos=None):
         """mplib/planner.py:226-240"""
