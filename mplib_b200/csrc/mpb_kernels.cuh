@@ -694,8 +694,11 @@ __global__ void __launch_bounds__(256) sphere_pairs_kernel(const __grid_constant
 }
 #undef POSE
 
+#ifndef MPB_DENSE_MINB
+#define MPB_DENSE_MINB 6  // 80 registers: six blocks of 128 threads per SM (measured best of 1 / 6: cull leg 13.6 -> 12.6 ms on C3)
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(128) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
+__global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
                                                     unsigned sq_cap, WorkQ wq, HitOut out) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
@@ -1151,8 +1154,11 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 // ---------------------------------------------------------------------------------------------- narrowphase
 // ccdMPRIntersect [upstream libccd v2.1 mpr.c] in the frame of shape A; B sits at (R, t).
 // Phases: 1 = v1, 2 = v2, 3 = v3 search (discoverPortal), 4 = refinePortal.  One support per trip.
+#ifndef MPB_NARROW_MINB
+#define MPB_NARROW_MINB 3
+#endif
 template <bool SMEM>
-__global__ void __launch_bounds__(256, 3) narrow_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round, int refill_min) {
+__global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round, int refill_min) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
@@ -1678,7 +1684,10 @@ __device__ __forceinline__ void exp_leaf_batch(const SceneImg &img, const WorkQ 
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(128) expand_lane_kernel(SceneImg img, WorkQ wq, HitOut out) {
+#ifndef MPB_EXPL_MINB
+#define MPB_EXPL_MINB 1
+#endif
+__global__ void __launch_bounds__(128, MPB_EXPL_MINB) expand_lane_kernel(SceneImg img, WorkQ wq, HitOut out) {
   __shared__ ExpShared S;
   const int eb = img.expand_bin;
   if (eb < 0) return;
