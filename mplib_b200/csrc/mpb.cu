@@ -133,6 +133,7 @@ struct mpb_scene {
   int narrow_blocks = 0;
   int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0}, sphere_blocks_blk[2] = {0, 0};
   int expand_lane_blocks = 0;
+  bool has_primitives = false;  // some object is a sphere / box / capsule / cylinder or an octree (sufficient-hit test worthwhile)
   int sphere_cb = 4;         // tiles of 32 configurations per warp of sphere_blk_kernel (large cull tables)  // one resident wave of the static grid-stride kernels, per MODE
   std::vector<cudaEvent_t> events;
   // scratch blocks of the planning / distance entry points, kept between calls (cudaMalloc + cudaFree of the tree
@@ -971,6 +972,7 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
       default: O.rin = 0.f; break;
     }
     s->obj_key[o] = geom_key(O.type, O.geom);
+    if ((O.type >= MPB_GEOM_SPHERE && O.type <= MPB_GEOM_CYLINDER) || O.type == MPB_GEOM_OCTREE) s->has_primitives = true;
   }
   if (ndyn > MPB_MAX_DYN) { delete s; return fail(MPB_ERR_CAPACITY, "too many moving collision objects (MPB_MAX_DYN = 128)"); }
   std::vector<int> dynlist;
@@ -1378,15 +1380,18 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     }
     return MPB_OK;
   }
-  dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out);
+  // the sufficient-hit test pays where collisions are common and deep: scenes with primitive obstacles / octrees; hull x hull
+  // pairs of a robot against itself (C2, C5) seldom overlap by more than a few millimetres
+  static const int presolve_env = !(getenv("MPB_NO_PRESOLVE") && atoi(getenv("MPB_NO_PRESOLVE")));
+  const int presolve = presolve_env && s->has_primitives;
+  dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out, presolve);
   *launches += 1;
   static const int refill_min = getenv("MPB_REFILL_MIN") ? atoi(getenv("MPB_REFILL_MIN")) : 8;
-  static const int presolve = !(getenv("MPB_NO_PRESOLVE") && atoi(getenv("MPB_NO_PRESOLVE")));
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
   const int nblocks = grid_for(s->narrow_blocks, 64);  // narrowphase: a block of 8 warps per 64 possible items of a small pass
   const unsigned n_warps = (unsigned)std::max(1.0, nblocks * 8.0 * unit_factor);
   scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, n_warps, s->sq_cap);
-  scatter_kernel<<<grid_for(s->num_sms * 4, 512), 512, 0, st>>>(s->img, s->wq, 0, out, presolve);
+  scatter_kernel<false><<<grid_for(s->num_sms * 2, 1024), 1024, 0, st>>>(s->img, s->wq, 0, out);  // round 0: dense_kernel ran the sufficient test
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
   if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
@@ -1402,7 +1407,8 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     expand_kernel<<<grid_for(s->num_sms * 8, 16), 128, 0, st>>>(s->img, s->wq, out, small ? 0 : lane_on);
     if (!small && lane_on) { expand_lane_kernel<<<s->expand_lane_blocks, 128, 0, st>>>(s->img, s->wq, out); *launches += 1; }
     scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor), s->sq_cap);
-    scatter_kernel<<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 1, out, presolve);
+    if (presolve) scatter_kernel<true><<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 1, out);
+    else scatter_kernel<false><<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1, out);
     if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     *launches += 5;
@@ -2347,9 +2353,9 @@ extern "C" int mpb_distance_batch(mpb_scene *s, const float *q, int64_t n, float
       const int cblocks = (int)((m + 127) / 128);
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, s->d_qconst, dq, m, s->d_pose, s->pose_ld, s->d_obb);
       sphere_kernel<1, 0, 0><<<std::min(cblocks, s->sphere_blocks[1]), 128, 0, st>>>(s->img, CullTabC<0, 0>{}, s->d_pose, s->pose_ld, m, 0, s->d_sq, s->sq_cap, s->wq.totals);
-      dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, HitOut{});
+      dense_kernel<1><<<s->dense_blocks[1], 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, HitOut{}, 0);
       scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins, s->img.expand_bin, s->img.expand2_bin, (unsigned)dblocks * 8u, s->sq_cap);
-      scatter_kernel<<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 0, HitOut{}, 0);
+      scatter_kernel<false><<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 0, HitOut{});
       CU(cudaEventRecord(e1, st));
       if (s->smem_verts) distance_kernel<true><<<dblocks, 256, vsm, st>>>(s->img, s->wq, dbest, s->img.n_bins);
       else distance_kernel<false><<<dblocks, 256, 0, st>>>(s->img, s->wq, dbest, s->img.n_bins);

@@ -650,6 +650,81 @@ __global__ void __launch_bounds__(128) sphere_blk_kernel(const __grid_constant__
 }
 #undef POSE
 
+// ---- sufficient-hit test in front of the narrowphase.  Every object carries up to MPB_INNER_BALLS balls that lie inside
+// it (host: primitive_balls / hull_balls).  If a ball of one shape intersects the other shape -- exactly, by the closed
+// forms below, when that one is a primitive; a ball of it otherwise -- the shapes intersect, which is what MPR would
+// report after three or more support evaluations.  In the C3 scene most narrowphase items are such collisions.
+__device__ __forceinline__ bool ball_hits_primitive(int type, const float *prm, V3 c, float r) {  // c: ball centre in the primitive's frame
+  switch (type) {
+    case MPB_GEOM_SPHERE: { const float rr = r + prm[0]; return dot(c, c) < rr * rr; }
+    case MPB_GEOM_BOX: {
+      const float dx = c.x - clampf(c.x, -prm[0], prm[0]), dy = c.y - clampf(c.y, -prm[1], prm[1]), dz = c.z - clampf(c.z, -prm[2], prm[2]);
+      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < r * r;
+    }
+    case MPB_GEOM_CAPSULE: {
+      const float dz = c.z - clampf(c.z, -prm[1], prm[1]), rr = r + prm[0];
+      return fmaf(c.x, c.x, fmaf(c.y, c.y, dz * dz)) < rr * rr;
+    }
+    case MPB_GEOM_CYLINDER: {
+      const float dr = fmaxf(sqrtf(fmaf(c.x, c.x, c.y * c.y)) - prm[0], 0.f), dz = fmaxf(fabsf(c.z) - prm[1], 0.f);
+      return fmaf(dr, dr, dz * dz) < r * r;
+    }
+    default: return false;
+  }
+}
+// A, B: the two objects of the item; (R, t): B in A.  leaf >= 0: B is a BVH object and the item is its leaf primitive `leaf`.
+__device__ __forceinline__ bool sufficient_hit(const SceneImg &img, const DevObject &A, const DevObject &B, const float *R, V3 t, int leaf) {
+  if (leaf >= 0) {
+    if (B.vcnt != MPB_GEOM_VBOX) return false;  // triangles: left to the narrowphase
+    const float4 pc = __ldg(img.prims + 3 * leaf), ph = __ldg(img.prims + 3 * leaf + 1);
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 b = A.ball[k];
+      if (b.w <= 0.f) break;
+      const V3 c = rot_t(R, v3(b.x, b.y, b.z) - t);  // ball centre in the octree's frame
+      const float dx = c.x - clampf(c.x, pc.x - ph.x, pc.x + ph.x), dy = c.y - clampf(c.y, pc.y - ph.y, pc.y + ph.y),
+                  dz = c.z - clampf(c.z, pc.z - ph.z, pc.z + ph.z);
+      if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < b.w * b.w) return true;
+    }
+    return false;
+  }
+  const bool pa = A.type >= MPB_GEOM_SPHERE && A.type <= MPB_GEOM_CYLINDER, pb = B.type >= MPB_GEOM_SPHERE && B.type <= MPB_GEOM_CYLINDER;
+  if (pb) {  // balls of A against the primitive B, exactly
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 b = A.ball[k];
+      if (b.w <= 0.f) break;
+      if (ball_hits_primitive(B.type, B.prm, rot_t(R, v3(b.x, b.y, b.z) - t), b.w)) return true;
+    }
+    return false;
+  }
+  if (pa) {  // balls of B against the primitive A
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 b = B.ball[k];
+      if (b.w <= 0.f) break;
+      if (ball_hits_primitive(A.type, A.prm, rot(R, v3(b.x, b.y, b.z)) + t, b.w)) return true;
+    }
+    return false;
+  }
+  if (A.type != MPB_GEOM_CONVEX || B.type != MPB_GEOM_CONVEX) return false;
+#pragma unroll
+  for (int j = 0; j < MPB_INNER_BALLS; j++) {
+    const float4 bb = B.ball[j];
+    if (bb.w <= 0.f) break;
+    const V3 cb = rot(R, v3(bb.x, bb.y, bb.z)) + t;
+#pragma unroll
+    for (int k = 0; k < MPB_INNER_BALLS; k++) {
+      const float4 ba = A.ball[k];
+      if (ba.w <= 0.f) break;
+      const V3 d = v3(ba.x, ba.y, ba.z) - cb;
+      const float rr = ba.w + bb.w;
+      if (dot(d, d) < rr * rr) return true;
+    }
+  }
+  return false;
+}
+
 // sphere phase of a SMALL pass (a legacy single-state query, a few thousand states): thread per (configuration, cull-table
 // entry) instead of thread per configuration -- one warp walking the 1587 entries of the C3 table for a single state
 // took 0.21 ms, all of it load latency.  Same tests as sphere_kernel<0> (expanded form for world-fixed partners).
@@ -699,7 +774,7 @@ __global__ void __launch_bounds__(256) sphere_pairs_kernel(const __grid_constant
 #endif
 template <int MODE>
 __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
-                                                    unsigned sq_cap, WorkQ wq, HitOut out) {
+                                                    unsigned sq_cap, WorkQ wq, HitOut out, int presolve) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
   __shared__ unsigned s_bins[MPB_SMEM_BINS];  // per-block bin counts, flushed once at the end
@@ -767,6 +842,14 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
         const Xf Xa = xf_rows(__ldg(ca + 5), __ldg(ca + 6), __ldg(ca + 7));
         const Xf Xbi = xf_rows(__ldg(cb + 8), __ldg(cb + 9), __ldg(cb + 10));
         rel = xf_mul(xf_mul(Xa, Rt), Xbi);
+        // sufficient test with the inner balls (exact closed forms against a primitive partner): an item it settles is
+        // never staged, binned or sent to the narrowphase.  Survivors of one configuration sit next to each other in the
+        // queue and the partners of a run come in blocks of one geometry type, so the type switch rarely diverges.
+        if (MODE == 0 && presolve && (pr.bin_dyn & 0xffff) != img.expand_bin && (pr.bin_dyn & 0xffff) != img.expand2_bin &&
+            sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], rel.r, v3(rel.p[0], rel.p[1], rel.p[2]), -1)) {
+          keep = false;
+          report_hit(out, cfg, p);
+        }
       }
     }
     const unsigned km = __ballot_sync(FULL, keep);
@@ -881,86 +964,14 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bi
   }
 }
 
-// ---- sufficient-hit test in front of the narrowphase.  Every object carries up to MPB_INNER_BALLS balls that lie inside
-// it (host: primitive_balls / hull_balls).  If a ball of one shape intersects the other shape -- exactly, by the closed
-// forms below, when that one is a primitive; a ball of it otherwise -- the shapes intersect, which is what MPR would
-// report after three or more support evaluations.  In the C3 scene most narrowphase items are such collisions.
-__device__ __forceinline__ bool ball_hits_primitive(int type, const float *prm, V3 c, float r) {  // c: ball centre in the primitive's frame
-  switch (type) {
-    case MPB_GEOM_SPHERE: { const float rr = r + prm[0]; return dot(c, c) < rr * rr; }
-    case MPB_GEOM_BOX: {
-      const float dx = c.x - clampf(c.x, -prm[0], prm[0]), dy = c.y - clampf(c.y, -prm[1], prm[1]), dz = c.z - clampf(c.z, -prm[2], prm[2]);
-      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < r * r;
-    }
-    case MPB_GEOM_CAPSULE: {
-      const float dz = c.z - clampf(c.z, -prm[1], prm[1]), rr = r + prm[0];
-      return fmaf(c.x, c.x, fmaf(c.y, c.y, dz * dz)) < rr * rr;
-    }
-    case MPB_GEOM_CYLINDER: {
-      const float dr = fmaxf(sqrtf(fmaf(c.x, c.x, c.y * c.y)) - prm[0], 0.f), dz = fmaxf(fabsf(c.z) - prm[1], 0.f);
-      return fmaf(dr, dr, dz * dz) < r * r;
-    }
-    default: return false;
-  }
-}
-// A, B: the two objects of the item; (R, t): B in A.  leaf >= 0: B is a BVH object and the item is its leaf primitive `leaf`.
-__device__ __forceinline__ bool sufficient_hit(const SceneImg &img, const DevObject &A, const DevObject &B, const float *R, V3 t, int leaf) {
-  if (leaf >= 0) {
-    if (B.vcnt != MPB_GEOM_VBOX) return false;  // triangles: left to the narrowphase
-    const float4 pc = __ldg(img.prims + 3 * leaf), ph = __ldg(img.prims + 3 * leaf + 1);
-#pragma unroll
-    for (int k = 0; k < MPB_INNER_BALLS; k++) {
-      const float4 b = A.ball[k];
-      if (b.w <= 0.f) break;
-      const V3 c = rot_t(R, v3(b.x, b.y, b.z) - t);  // ball centre in the octree's frame
-      const float dx = c.x - clampf(c.x, pc.x - ph.x, pc.x + ph.x), dy = c.y - clampf(c.y, pc.y - ph.y, pc.y + ph.y),
-                  dz = c.z - clampf(c.z, pc.z - ph.z, pc.z + ph.z);
-      if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < b.w * b.w) return true;
-    }
-    return false;
-  }
-  const bool pa = A.type >= MPB_GEOM_SPHERE && A.type <= MPB_GEOM_CYLINDER, pb = B.type >= MPB_GEOM_SPHERE && B.type <= MPB_GEOM_CYLINDER;
-  if (pb) {  // balls of A against the primitive B, exactly
-#pragma unroll
-    for (int k = 0; k < MPB_INNER_BALLS; k++) {
-      const float4 b = A.ball[k];
-      if (b.w <= 0.f) break;
-      if (ball_hits_primitive(B.type, B.prm, rot_t(R, v3(b.x, b.y, b.z) - t), b.w)) return true;
-    }
-    return false;
-  }
-  if (pa) {  // balls of B against the primitive A
-#pragma unroll
-    for (int k = 0; k < MPB_INNER_BALLS; k++) {
-      const float4 b = B.ball[k];
-      if (b.w <= 0.f) break;
-      if (ball_hits_primitive(A.type, A.prm, rot(R, v3(b.x, b.y, b.z)) + t, b.w)) return true;
-    }
-    return false;
-  }
-  if (A.type != MPB_GEOM_CONVEX || B.type != MPB_GEOM_CONVEX) return false;
-#pragma unroll
-  for (int j = 0; j < MPB_INNER_BALLS; j++) {
-    const float4 bb = B.ball[j];
-    if (bb.w <= 0.f) break;
-    const V3 cb = rot(R, v3(bb.x, bb.y, bb.z)) + t;
-#pragma unroll
-    for (int k = 0; k < MPB_INNER_BALLS; k++) {
-      const float4 ba = A.ball[k];
-      if (ba.w <= 0.f) break;
-      const V3 d = v3(ba.x, ba.y, ba.z) - cb;
-      const float rr = ba.w + bb.w;
-      if (dot(d, d) < rr * rr) return true;
-    }
-  }
-  return false;
-}
-
 // Staging queue -> binned queue.  A block ranks its items per bin in shared memory (the shared atomic returns the
 // rank), reserves one range per bin per trip in the global cursors, then moves the items.  The kernel is bound by its
-// dependent loads and leaves most issue slots idle, so the sufficient-hit test runs here (presolve != 0): an item it
-// settles sets its result bits and is not moved; bin_cursor[b] ends as the number of items bin b really holds.
-__global__ void __launch_bounds__(512, 2) scatter_kernel(SceneImg img, WorkQ wq, int round, HitOut out, int presolve) {
+// dependent loads and leaves most issue slots idle, so the sufficient-hit test of the SECOND round (leaf items: inner balls
+// of the shape against a voxel box) runs here (PRESOLVE): an item it settles sets its result bits and is not moved;
+// bin_cursor[b] ends as the number of items bin b really holds.  (First-round items are tested in dense_kernel, before
+// they are staged at all.)
+template <bool PRESOLVE>
+__global__ void __launch_bounds__(PRESOLVE ? 512 : 1024, 2) scatter_kernel(SceneImg img, WorkQ wq, int round, HitOut out) {
   __shared__ unsigned s_cnt[MPB_SMEM_BINS], s_base[MPB_SMEM_BINS];
   const unsigned n = min(wq.totals[0], wq.cap);
   const int n_bins = round == 0 ? img.n_bins : img.n_bins2;
@@ -971,17 +982,14 @@ __global__ void __launch_bounds__(512, 2) scatter_kernel(SceneImg img, WorkQ wq,
     bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
     const int p = valid ? wq.spair[s] : 0;
     int bin = valid ? (round == 0 ? (img.pairs[p].bin_dyn & 0xffff) : img.pair_bin2[p]) : -1;
-    float f[12];
-    int cfg = 0, aux = 0;
-    if (valid) {
+    if constexpr (PRESOLVE) {
+      if (valid && !(round == 0 && (bin == img.expand_bin || bin == img.expand2_bin))) {
+        float f[12];
 #pragma unroll
-      for (int k = 0; k < 12; k++) f[k] = wq.stf[(size_t)k * wq.cap + s];
-      cfg = wq.scfg[s];
-      aux = wq.saux[s];
-      if (presolve && !(round == 0 && (bin == img.expand_bin || bin == img.expand2_bin))) {
+        for (int k = 0; k < 12; k++) f[k] = wq.stf[(size_t)k * wq.cap + s];
         const DevPair pr = img.pairs[p];
-        if (sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], f, v3(f[9], f[10], f[11]), round == 0 ? -1 : aux)) {
-          report_hit(out, (unsigned)cfg, p);
+        if (sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], f, v3(f[9], f[10], f[11]), round == 0 ? -1 : wq.saux[s])) {
+          report_hit(out, (unsigned)wq.scfg[s], p);
           valid = false;
           bin = -1;
         }
@@ -1008,12 +1016,12 @@ __global__ void __launch_bounds__(512, 2) scatter_kernel(SceneImg img, WorkQ wq,
       base = __shfl_sync(0xffffffffu, base, leader);
       if (valid) dst = wq.bin_start[bin] + base + __popc(grp & ((1u << lane) - 1u));
     }
-    if (valid) {
+    if (valid) {  // the payload is (re)read here: holding it across the ranking would cost the lean variant its occupancy
 #pragma unroll
-      for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = f[k];
-      wq.icfg[dst] = cfg;
+      for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = wq.stf[(size_t)k * wq.cap + s];
+      wq.icfg[dst] = wq.scfg[s];
       wq.ipair[dst] = p;
-      wq.iaux[dst] = aux;
+      wq.iaux[dst] = wq.saux[s];
     }
   }
 }
