@@ -57,7 +57,7 @@ struct SmallGraph {
 // cudaFuncAttributeMaxDynamicSharedMemorySize is per-function state shared by every scene of the process: only ever
 // raise it (a second scene with a smaller hull pool must not lower the limit under a scene that needs more).
 static cudaError_t raise_dyn_smem(const void *func, int device, int slot, size_t bytes) {
-  static int limit[2][64] = {{0}};
+  static int limit[4][64] = {{0}};
   if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
   if ((int)bytes <= limit[slot][device]) return cudaSuccess;
   cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
@@ -133,6 +133,8 @@ struct mpb_scene {
   int narrow_blocks = 0;
   int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0}, sphere_blocks_blk[2] = {0, 0};
   int expand_lane_blocks = 0;
+  size_t narrow2_smem = 0;
+  int narrow2_blocks = 0;
   bool has_primitives = false;  // some object is a sphere / box / capsule / cylinder or an octree (sufficient-hit test worthwhile)
   int sphere_cb = 4;         // tiles of 32 configurations per warp of sphere_blk_kernel (large cull tables)  // one resident wave of the static grid-stride kernels, per MODE
   std::vector<cudaEvent_t> events;
@@ -1060,6 +1062,18 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   } else {
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, narrow_kernel<false>, 256, 0));
   }
+  {  // phase-split variant: hull pool (padded to 128 B) + one survivor buffer per warp
+    s->narrow2_smem = (s->smem_verts ? (vbytes + 127) / 128 * 128 : 0) + (size_t)8 * (MPB_SURV_F + 1) * MPB_SURV_CAP * sizeof(float);
+    int b2 = 0;
+    if (s->smem_verts) {
+      CU(raise_dyn_smem((const void *)narrow2_kernel<true>, device, 2, s->narrow2_smem));
+      CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, narrow2_kernel<true>, 256, s->narrow2_smem));
+    } else {
+      CU(raise_dyn_smem((const void *)narrow2_kernel<false>, device, 3, s->narrow2_smem));
+      CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, narrow2_kernel<false>, 256, s->narrow2_smem));
+    }
+    s->narrow2_blocks = s->num_sms * std::max(b2, 1);
+  }
   s->narrow_blocks = s->num_sms * std::max(per_sm, 1);
   {  // sphere_kernel / dense_kernel split their range statically over the grid: exactly one resident wave, or the
      // blocks beyond it run as a second, mostly empty wave
@@ -1394,7 +1408,12 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   scatter_kernel<false><<<grid_for(s->num_sms * 2, 1024), 1024, 0, st>>>(s->img, s->wq, 0, out);  // round 0: dense_kernel ran the sufficient test
   if (ev) CU(cudaEventRecord(e1, st));
   const size_t vsm = s->smem_verts ? (size_t)s->img.pool_bytes : 0;
-  if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
+  static const int narrow_v2 = !(getenv("MPB_NARROW_V1") && atoi(getenv("MPB_NARROW_V1")));
+  const int nblocks2 = grid_for(s->narrow2_blocks, 64);
+  if (narrow_v2) {
+    if (s->smem_verts) narrow2_kernel<true><<<nblocks2, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
+    else narrow2_kernel<false><<<nblocks2, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
+  } else if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
   else narrow_kernel<false><<<nblocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
   *launches += 3;
   if (s->img.expand2_bin >= 0) {  // mesh x mesh / mesh x octree pairs: exact leaf tests inside the descent
@@ -1409,7 +1428,10 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor), s->sq_cap);
     if (presolve) scatter_kernel<true><<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 1, out);
     else scatter_kernel<false><<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1, out);
-    if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
+    if (narrow_v2) {
+      if (s->smem_verts) narrow2_kernel<true><<<s->narrow2_blocks, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
+      else narrow2_kernel<false><<<s->narrow2_blocks, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
+    } else if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     *launches += 5;
   }

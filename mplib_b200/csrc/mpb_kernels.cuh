@@ -1376,6 +1376,261 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow_kernel(SceneImg i
   if (lane == 0 && cap_sum) atomicAdd(&wq.counters[2], cap_sum);
 }
 
+// ---------------------------------------------------------------------------------------------- narrowphase, phase-split
+// narrow_kernel runs the four MPR phases as one per-lane state machine; ncu showed 15 of 32 lanes active per instruction
+// (profiles/r02_ncu_full_c3_pre_expand_lane_raw.csv): the phase bodies serialise, and the long item-fetch block runs for
+// the few lanes that just finished.  Here a warp alternates between two CONVERGED regions over its slice of a bin:
+//   A  prologue: 32 fresh items, one per lane -- fetch, v0, the first two supports (v1, v2) and their exits.  More
+//      than half of the items that do not collide end here; what is left has a triangle (v0, v1, v2) to search from.
+//   B  portal loop over the survivors of A (kept in a per-warp buffer in shared memory: 13 floats + item index):
+//      discoverPortal's v3 search and refinePortal, one support per trip, lanes refilled from the buffer.
+// The arithmetic is that of narrow_kernel (libccd's mpr.c order); only the schedule differs.
+#define MPB_SURV_CAP 64
+#define MPB_SURV_F 13  // v0 v1 v2 dir (12 floats) + iteration count
+
+struct MprItem {  // what a lane needs of its item for a support evaluation
+  float R[9];
+  V3 t;
+  int cfg, p;
+};
+
+template <bool SMEM>
+__device__ __forceinline__ V3 mink_support(const DevShape &A, const DevShape &B, const MprItem &I, V3 dir, const float4 *verts,
+                                           const float4 *prims, const unsigned char *cells) {
+  const V3 sa = support_local<SMEM>(A, dir, verts, prims, cells);
+  const V3 sb = support_local<SMEM>(B, rot_t(I.R, dir * -1.f), verts, prims, cells);
+  return sa - (rot(I.R, sb) + I.t);
+}
+
+// item `my` of the binned queue -> lane state; false: nothing to do (already known to collide)
+__device__ __forceinline__ bool mpr_fetch(const SceneImg &img, const WorkQ &wq, const HitOut &out, unsigned my, int round, DevShape &A, DevShape &B,
+                                          MprItem &I, V3 &cA, V3 &cBl) {
+#pragma unroll
+  for (int k = 0; k < 9; k++) I.R[k] = wq.itf[(size_t)k * wq.cap + my];
+  I.t = v3(wq.itf[(size_t)9 * wq.cap + my], wq.itf[(size_t)10 * wq.cap + my], wq.itf[(size_t)11 * wq.cap + my]);
+  I.cfg = wq.icfg[my];
+  I.p = wq.ipair[my];
+  const DevPair pr = img.pairs[I.p];
+  const DevObject &OA = img.objs[pr.a];
+  const DevObject &OB = img.objs[pr.b];
+  A.p0 = OA.prm[0]; A.p1 = OA.prm[1]; A.p2 = OA.prm[2];  // primitive parameters differ per item
+  B.p0 = OB.prm[0]; B.p1 = OB.prm[1]; B.p2 = OB.prm[2];
+  cA = v3(OA.ctr[0], OA.ctr[1], OA.ctr[2]);
+  cBl = v3(OB.ctr[0], OB.ctr[1], OB.ctr[2]);
+  if (round == 1) {  // [upstream] centerTriangle = centroid; voxel Box centre = its pose
+    B.voff = wq.iaux[my];
+    const float4 a = __ldg(img.prims + 3 * B.voff);
+    if (B.type == MPB_GEOM_TRI) {
+      const float4 b = __ldg(img.prims + 3 * B.voff + 1), c = __ldg(img.prims + 3 * B.voff + 2);
+      cBl = v3((a.x + b.x + c.x) * (1.f / 3.f), (a.y + b.y + c.y) * (1.f / 3.f), (a.z + b.z + c.z) * (1.f / 3.f));
+    } else cBl = v3(a.x, a.y, a.z);
+    return !hit_known(out, (unsigned)I.cfg, I.p);  // early exit: this (configuration, pair) is already known to collide
+  }
+  return true;
+}
+
+template <bool SMEM>
+__global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow2_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round, int refill_min) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) unsigned long long bar;
+  const float4 *verts = img.verts;
+  const unsigned pool = ((unsigned)img.pool_bytes + 127u) & ~127u;
+  if (SMEM) {
+    const unsigned total = (unsigned)img.pool_bytes;
+    if (threadIdx.x == 0) {
+      mbar_init(&bar, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && total > 0) {
+      mbar_expect_tx(&bar, total);
+      for (unsigned off = 0; off < total; off += 32768u) tma_bulk_g2s(smem_raw + off, reinterpret_cast<const unsigned char *>(img.verts) + off, min(32768u, total - off), &bar);
+    }
+    if (total > 0) mbar_wait(&bar, 0);
+    verts = reinterpret_cast<const float4 *>(smem_raw);
+  }
+  const unsigned char *cells = reinterpret_cast<const unsigned char *>(verts + img.n_verts);
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // survivor buffer of this warp: [field][slot] floats, then [slot] item indices
+  float *sv = reinterpret_cast<float *>(smem_raw + (SMEM ? pool : 0u)) + (size_t)warp * (MPB_SURV_F + 1) * MPB_SURV_CAP;
+  unsigned *sv_item = reinterpret_cast<unsigned *>(sv + MPB_SURV_F * MPB_SURV_CAP);
+  const unsigned n_units = wq.totals[1], unit_items = wq.totals[4];
+  unsigned long long it_sum = 0, cap_sum = 0;
+  for (;;) {
+    unsigned u = 0;
+    if (lane == 0) u = atomicAdd(&wq.totals[3], 1u);
+    u = __shfl_sync(FULL, u, 0);
+    if (u >= n_units) break;
+    int lo = 0, hi = n_bins;  // bin of this unit: largest b with unit_start[b] <= u
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (wq.unit_start[mid] <= u) lo = mid; else hi = mid;
+    }
+    unsigned next = wq.bin_start[lo] + (u - wq.unit_start[lo]) * unit_items;
+    const unsigned end = min(min(wq.bin_start[lo] + wq.bin_cursor[lo], next + unit_items), wq.cap);
+    if (next >= end) continue;
+    DevShape A, B;
+    {  // shapes are uniform over the bin: read them once from the first item of the slice
+      const DevPair pr0 = img.pairs[wq.ipair[next]];
+      A = shape_of(img.objs[pr0.a]);
+      B = shape_of(img.objs[pr0.b]);
+      if (round == 1) B.type = img.objs[pr0.b].vcnt;  // leaf primitives of a BVH object: MPB_GEOM_TRI / MPB_GEOM_VBOX
+    }
+    int cnt = 0;  // survivors in the buffer (warp-uniform)
+    for (;;) {
+      // ---------------- region A: prologue batches until the buffer holds a warp's worth of survivors
+      while (cnt <= MPB_SURV_CAP - 32 && next < end) {
+        const unsigned my = next + lane;
+        next += 32;
+        MprItem I;
+        V3 cA = v3(0.f, 0.f, 0.f), cBl = cA;
+        bool act = false;
+        if (my < end) act = mpr_fetch(img, wq, out, my, round, A, B, I, cA, cBl);
+        else {
+#pragma unroll
+          for (int k = 0; k < 9; k++) I.R[k] = (k % 4 == 0) ? 1.f : 0.f;
+          I.t = cA; I.cfg = 0; I.p = 0;
+          if (round == 1) B.voff = 0;
+        }
+        V3 v0 = cA - (rot(I.R, cBl) + I.t);
+        if (is_zero(v0.x) && is_zero(v0.y) && is_zero(v0.z)) v0.x += 10.f * MPB_EPS;
+        V3 dir = normalized(v0 * -1.f);
+        bool hit = false;
+        int iters = 0;
+        const V3 v1 = mink_support<SMEM>(A, B, I, dir, verts, img.prims, cells);
+        V3 v2 = v1;
+        if (act) {
+          iters = 1;
+          const float dv = dot(v1, dir);
+          if (is_zero(dv) || dv < 0.f) act = false;
+          else {
+            dir = cross(v0, v1);
+            // libccd tests |v0 x v1|^2 against DBL_EPSILON (effectively exact zero); in fp32 the test must be
+            // relative to the operand lengths or centimetre-sized shapes alias to "origin on the segment"
+            if (dot(dir, dir) <= 1e-12f * dot(v0, v0) * dot(v1, v1)) { act = false; hit = true; }
+            else dir = normalized(dir);
+          }
+        }
+        V3 w1 = v1;
+        if (__any_sync(FULL, act)) {
+          v2 = mink_support<SMEM>(A, B, I, dir, verts, img.prims, cells);
+          if (act) {
+            iters = 2;
+            const float dv = dot(v2, dir);
+            if (is_zero(dv) || dv < 0.f) act = false;
+            else {
+              dir = normalized(cross(v1 - v0, v2 - v0));
+              if (dot(dir, v0) > 0.f) { w1 = v2; v2 = v1; dir = dir * -1.f; }
+            }
+          }
+        }
+        if (hit) report_hit(out, (unsigned)I.cfg, I.p);
+        if (!act) it_sum += (unsigned)iters;
+        const unsigned sm = __ballot_sync(FULL, act);
+        if (act) {
+          const int slot = cnt + __popc(sm & ((1u << lane) - 1u));
+          sv[0 * MPB_SURV_CAP + slot] = v0.x; sv[1 * MPB_SURV_CAP + slot] = v0.y; sv[2 * MPB_SURV_CAP + slot] = v0.z;
+          sv[3 * MPB_SURV_CAP + slot] = w1.x; sv[4 * MPB_SURV_CAP + slot] = w1.y; sv[5 * MPB_SURV_CAP + slot] = w1.z;
+          sv[6 * MPB_SURV_CAP + slot] = v2.x; sv[7 * MPB_SURV_CAP + slot] = v2.y; sv[8 * MPB_SURV_CAP + slot] = v2.z;
+          sv[9 * MPB_SURV_CAP + slot] = dir.x; sv[10 * MPB_SURV_CAP + slot] = dir.y; sv[11 * MPB_SURV_CAP + slot] = dir.z;
+          sv[12 * MPB_SURV_CAP + slot] = __int_as_float(iters);
+          sv_item[slot] = my;
+        }
+        cnt += __popc(sm);
+        __syncwarp();
+      }
+      if (cnt == 0) break;  // slice exhausted (the loop above ran out of items) and nothing to refine
+      // ---------------- region B: portal search / refinement over the buffered survivors
+      bool busy = false;
+      MprItem I;
+      V3 v0 = v3(0.f, 0.f, 0.f), v1 = v0, v2 = v0, v3p = v0, dir = v3(1.f, 0.f, 0.f);
+      int phase = 3, iters = 0;
+#pragma unroll
+      for (int k = 0; k < 9; k++) I.R[k] = (k % 4 == 0) ? 1.f : 0.f;
+      I.t = v0; I.cfg = 0; I.p = 0;
+      for (;;) {
+        const unsigned idle = __ballot_sync(FULL, !busy);
+        if (cnt > 0 && (idle == FULL || __popc(idle) >= refill_min)) {
+          const int take = min(cnt, __popc(idle));
+          const int rank = __popc(idle & ((1u << lane) - 1u));
+          if (!busy && rank < take) {
+            const int slot = cnt - 1 - rank;
+            v0 = v3(sv[0 * MPB_SURV_CAP + slot], sv[1 * MPB_SURV_CAP + slot], sv[2 * MPB_SURV_CAP + slot]);
+            v1 = v3(sv[3 * MPB_SURV_CAP + slot], sv[4 * MPB_SURV_CAP + slot], sv[5 * MPB_SURV_CAP + slot]);
+            v2 = v3(sv[6 * MPB_SURV_CAP + slot], sv[7 * MPB_SURV_CAP + slot], sv[8 * MPB_SURV_CAP + slot]);
+            dir = v3(sv[9 * MPB_SURV_CAP + slot], sv[10 * MPB_SURV_CAP + slot], sv[11 * MPB_SURV_CAP + slot]);
+            iters = __float_as_int(sv[12 * MPB_SURV_CAP + slot]);
+            V3 cA, cBl;
+            mpr_fetch(img, wq, out, sv_item[slot], round, A, B, I, cA, cBl);
+            phase = 3;
+            busy = true;
+          }
+          cnt -= take;
+          __syncwarp();
+        }
+        if (__ballot_sync(FULL, busy) == 0) break;  // buffer empty (or it would have refilled) and every lane finished
+        const V3 v = mink_support<SMEM>(A, B, I, dir, verts, img.prims, cells);
+        if (!busy) continue;
+        iters++;
+        bool done = false, hit = false;
+        const float dv = dot(v, dir);
+        if (phase == 3) {
+          v3p = v;
+          if (is_zero(dv) || dv < 0.f) done = true;
+          else {
+            bool cont = false;
+            const float d1 = dot(cross(v1, v3p), v0);
+            if (d1 < 0.f) { v2 = v3p; cont = true; }  // triple products: exact sign (DBL_EPSILON-scale zero band upstream)
+            if (!cont) {
+              const float d2 = dot(cross(v3p, v2), v0);
+              if (d2 < 0.f) { v1 = v3p; cont = true; }
+            }
+            if (cont) dir = normalized(cross(v1 - v0, v2 - v0));
+            else {
+              phase = 4;
+              dir = normalized(cross(v2 - v1, v3p - v1));
+              const float de = dot(dir, v1);
+              if (is_zero(de) || de > 0.f) { done = true; hit = true; }
+            }
+          }
+        } else {
+          // refinePortal: can v4 expand the portal past the origin, and is there still progress?
+          if (!(is_zero(dv) || dv > 0.f)) done = true;
+          else {
+            const float m = fminf(dv - dot(v1, dir), fminf(dv - dot(v2, dir), dv - dot(v3p, dir)));
+            if (m <= MPB_MPR_TOL) done = true;
+            else {
+              const V3 v4v0 = cross(v, v0);
+              if (dot(v1, v4v0) > 0.f) {
+                if (dot(v2, v4v0) > 0.f) v1 = v; else v3p = v;
+              } else {
+                if (dot(v3p, v4v0) > 0.f) v2 = v; else v1 = v;
+              }
+              dir = normalized(cross(v2 - v1, v3p - v1));
+              const float de = dot(dir, v1);
+              if (is_zero(de) || de > 0.f) { done = true; hit = true; }
+            }
+          }
+        }
+        if (!done && iters >= MPB_MPR_MAX_ITERS) { done = true; cap_sum++; }
+        if (done) {
+          busy = false;
+          it_sum += (unsigned)iters;
+          if (hit) report_hit(out, (unsigned)I.cfg, I.p);
+        }
+      }
+      if (next >= end && cnt == 0) break;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    it_sum += __shfl_xor_sync(FULL, it_sum, o);
+    cap_sum += __shfl_xor_sync(FULL, cap_sum, o);
+  }
+  if (lane == 0 && it_sum) atomicAdd(&wq.counters[1], it_sum);
+  if (lane == 0 && cap_sum) atomicAdd(&wq.counters[2], cap_sum);
+}
+
 // ---------------------------------------------------------------------------------------------- FK-only API
 __device__ __forceinline__ void mat_to_quat(const float *R, float *q) {  // Eigen branches, (w,x,y,z)
   float t = R[0] + R[4] + R[8];
