@@ -207,37 +207,42 @@ def load_peaks():
 
 
 def ncu_capture(workload):
-    """Per-kernel DRAM bytes and executed FP32 flops per launch from the committed `ncu --set full` capture of this
-    workload (profiles/r02_ncu_full_<w>_raw.csv; scripts/ncu_export.sh writes it), or {} when there is none."""
+    """DRAM bytes and executed FP32 flops PER STATE, per kernel and in total, from the committed `ncu --set full` capture of
+    this workload (profiles/r02_ncu_full_<w>_raw.csv: the kernels of whole passes; scripts/gpu_evidence.sh makes it,
+    scripts/collect_evidence.sh exports it), or {} when there is none.  States in the capture = fk_table_kernel's threads."""
     import csv
 
-    for rnd in ("r02", "r01_final"):
-        path = os.path.join(ROOT, "profiles", f"{rnd}_ncu_full_{workload}_raw.csv")
-        if not os.path.exists(path):
-            continue
-        try:
-            rows = list(csv.reader(open(path)))
-            hdr, units = rows[0], rows[1]
-            col = {c: i for i, c in enumerate(hdr)}
-            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-            out = {}
-            for r in rows[2:]:
-                name = r[col["Kernel Name"]].split("(")[0].split("<")[0]
-                b = sum(float(r[col[c]]) * scale.get(units[col[c]], 1.0) for c in ("dram__bytes_read.sum", "dram__bytes_write.sum") if c in col)
-                fl = None
-                ops = ["smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
-                       "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"]
-                if all(o in col for o in ops):
-                    fl = float(r[col[ops[0]]]) + float(r[col[ops[1]]]) + 2.0 * float(r[col[ops[2]]])
-                e = out.setdefault(name, {"launches": 0, "dram_bytes": 0.0, "fp32_flop": 0.0 if fl is not None else None})
-                e["launches"] += 1
-                e["dram_bytes"] += b
-                if fl is not None and e["fp32_flop"] is not None:
-                    e["fp32_flop"] += fl
-            return {"source": os.path.relpath(path, ROOT), "kernels": out}
-        except Exception:
-            continue
-    return {}
+    path = os.path.join(ROOT, "profiles", f"r02_ncu_full_{workload}_raw.csv")
+    if not os.path.exists(path):
+        return {}
+    try:
+        rows = list(csv.reader(open(path)))
+        hdr, units = rows[0], rows[1]
+        col = {c: i for i, c in enumerate(hdr)}
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        ops = ["smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
+               "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"]
+        have_ops = all(o in col for o in ops)
+        out, states = {}, 0
+        for r in rows[2:]:
+            name = r[col["Kernel Name"]].split("(")[0].split("<")[0].replace("void ", "").strip()
+            b = sum(float(r[col[c]]) * scale.get(units[col[c]], 1.0) for c in ("dram__bytes_read.sum", "dram__bytes_write.sum") if c in col)
+            e = out.setdefault(name, {"launches": 0, "dram_bytes": 0.0, "fp32_flop": 0.0 if have_ops else None})
+            e["launches"] += 1
+            e["dram_bytes"] += b
+            if have_ops:
+                e["fp32_flop"] += float(r[col[ops[0]]]) + float(r[col[ops[1]]]) + 2.0 * float(r[col[ops[2]]])
+            if name == "fk_table_kernel":
+                states += int(float(r[col["launch__grid_size"]])) * 128
+        first = rows[2][col["Kernel Name"]] if len(rows) > 2 else ""
+        if not states or out["fk_table_kernel"]["launches"] != 1 or "fk_table_kernel" not in first:
+            return {}  # the capture must be the kernels of exactly one pass, FK first
+        return {"source": os.path.relpath(path, ROOT), "states_in_capture": states, "kernels": out,
+                "dram_bytes_per_state": sum(v["dram_bytes"] for v in out.values()) / states,
+                "fp32_flop_per_state": (sum(v["fp32_flop"] for v in out.values()) / states) if have_ops else None,
+                "fk_table_dram_bytes_per_state": out["fk_table_kernel"]["dram_bytes"] / states}
+    except Exception:
+        return {}
 
 
 # ------------------------------------------------------------------------------------------------- collision workloads
@@ -420,10 +425,9 @@ def run_checks(name, args, ctx, batch, steps, warmup, headline):
         cull_ms, narrow_ms = split["gpu_ms_cull"] / Ks, split["gpu_ms_narrow"] / Ks
         fk_bytes = split["fk_bytes_per_state"]
         ncu = ncu_capture(name)
-        kern = ncu.get("kernels", {})
-        dram_step = sum(v["dram_bytes"] for v in kern.values()) if kern else None
-        flop_exec = sum(v["fp32_flop"] for v in kern.values()) if kern and all(v["fp32_flop"] is not None for v in kern.values()) else None
-        fk_tr = kern.get("fk_table_kernel")
+        dram_step = ncu["dram_bytes_per_state"] * N if ncu else None
+        flop_exec = ncu["fp32_flop_per_state"] * N if ncu and ncu.get("fp32_flop_per_state") is not None else None
+        fk_tr = ncu["fk_table_dram_bytes_per_state"] * N if ncu else None
         d2h = int(vwords * 4 + 4 + 8 * (np.mean(e2e_hits) if e2e_hits else 0))
         rec = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
@@ -440,7 +444,8 @@ def run_checks(name, args, ctx, batch, steps, warmup, headline):
                 "achieved": achieved, "peak": peak_probe, "unit": "TFLOP/s", "frac": achieved / peak_probe if peak_probe else None,
                 "peak_source": "in-run FFMA probe (mpb_fp32_peak); formula SMs*128*2*f_sampled = %.1f" % peak_formula,
                 "flop_per_check": F_step / N, "traffic": dram_step,
-                "executed_fp32_flop_per_step": flop_exec, "ncu_source": ncu.get("source"),
+                "executed_fp32_flop_per_step": flop_exec, "executed_over_algorithmic": (flop_exec / F_step) if flop_exec else None,
+                "ncu_source": ncu.get("source"),
                 "dominant_kernel": "fk_table+sphere+dense" if cull_ms >= narrow_ms else "narrow(+expand)",
                 "kernel_ms_per_step": {"fk_table+sphere+dense+scan+scatter": cull_ms, "narrow(+expand)": narrow_ms,
                                        "measured": "leg of %d steps with per-pass CUDA events on the launching stream" % Ks},
@@ -452,7 +457,7 @@ def run_checks(name, args, ctx, batch, steps, warmup, headline):
                                     "peak": hbm_peak, "unit": "GB/s",
                                     "frac": N * fk_bytes / (fk_ms * 1e-3) / 1e9 / hbm_peak if fk_ms > 0 else None,
                                     "bytes_per_state": fk_bytes, "ms_per_step": fk_ms,
-                                    "traffic": (fk_tr["dram_bytes"] / max(fk_tr["launches"], 1)) if fk_tr else None,
+                                    "traffic": fk_tr,
                                     "share_of_step": fk_ms / max(cull_ms + narrow_ms, 1e-9)},
             },
             "stats_per_step": {"pairs_after_spheres": tot[3] / K / world, "pairs_after_cull": tot[2] / K / world, "support_evals": iters_per_step,

@@ -22,7 +22,7 @@ case $mode in
          CMD="python bench.py --workload $w --also none --steps 1 --warmup 1 --no-cpu-baseline --no-parity --no-latency $*"
          $CMD > gpurun_out/plain_$w.log 2>&1 &&
          ncu --set full --metrics smsp__sass_thread_inst_executed_op_fadd_pred_on.sum,smsp__sass_thread_inst_executed_op_fmul_pred_on.sum,smsp__sass_thread_inst_executed_op_ffma_pred_on.sum \
-             --clock-control none --import-source on -k regex:'fk_table|sphere|dense|narrow|expand|scatter|scan|distance' -s ${NCU_SKIP:-14} -c ${NCU_COUNT:-14} \
+             --clock-control none --import-source on -k regex:'fk_table|sphere|dense|narrow|expand|scatter|scan_bins|hits_compact' -s ${NCU_SKIP:-0} -c ${NCU_COUNT:-40} \
              -o gpurun_out/prof_$w -f $CMD > gpurun_out/ncu_full_$w.log 2>&1
          echo "rc=$?"; tail -3 gpurun_out/ncu_full_$w.log ;;
   multi) n=$1; shift
