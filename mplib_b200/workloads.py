@@ -240,8 +240,10 @@ def prefixed_panda_files(prefix, xyz, yaw):
     sr = re.sub(r'((?:link1|link2|link|parent_link|child_link|joint)\s*=\s*")', r"\g<1>" + prefix, sr)
     for path, txt in ((urdf_out, u), (srdf_out, sr)):
         if not os.path.exists(path) or open(path).read() != txt:
-            with open(path, "w") as f:
+            tmp = f"{path}.{os.getpid()}.tmp"  # written aside and renamed: the ranks of a multi-GPU run generate it concurrently
+            with open(tmp, "w") as f:
                 f.write(txt)
+            os.replace(tmp, path)
     return urdf_out, srdf_out
 
 
