@@ -132,7 +132,14 @@ struct mpb_scene {
   bool smem_verts = true;
   int narrow_blocks = 0;
   int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0}, sphere_blocks_blk[2] = {0, 0};
-  int expand_lane_blocks = 0;
+  int expand_lane_blocks = 0, dense2_blocks = 0;
+  // broadphase grid over world-fixed partners (sphere_grid_kernel), built lazily before the first large pass
+  bool grid_dirty = true, grid_on = false;
+  int *d_grid_start = nullptr;
+  unsigned short *d_grid_list = nullptr;
+  int2 *d_grid_run = nullptr;
+  size_t grid_start_cap = 0, grid_list_cap = 0, grid_run_cap = 0;
+  int sphere_blocks_grid = 0;
   size_t narrow2_smem = 0;
   int narrow2_blocks = 0;
   bool has_primitives = false;  // some object is a sphere / box / capsule / cylinder or an octree (sufficient-hit test worthwhile)
@@ -690,6 +697,7 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
       if (ct_on && n_pairs <= 256 && s->h_runs.size() <= 64 && s->img.n_dyn <= 30) { fill(s->ct_small.q, s->ct_small.runs); s->cull_tier = 1; }
     }
   }
+  s->grid_dirty = true;
   s->img.n_pairs = n_pairs;
   s->img.n_bins = (int)bins.size();
   s->img.n_bins2 = (int)bins2.size();
@@ -1086,7 +1094,9 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_kernel<1, 0, 0>, 128, 0)); s->sphere_blocks[1] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<0>, 128, 0)); s->dense_blocks[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<1>, 128, 0)); s->dense_blocks[1] = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense2_kernel, 128, 0)); s->dense2_blocks = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_lane_kernel, 128, 0)); s->expand_lane_blocks = s->num_sms * std::max(b, 1);
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_grid_kernel, 128, 0)); s->sphere_blocks_grid = s->num_sms * std::max(b, 1);
   }
   *out = s;
   return MPB_OK;
@@ -1108,6 +1118,9 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   if (s->h_slots) cudaFreeHost(s->h_slots);
   if (s->d_hits) cudaFree(s->d_hits);
   if (s->d_small) cudaFree(s->d_small);
+  if (s->d_grid_start) cudaFree(s->d_grid_start);
+  if (s->d_grid_list) cudaFree(s->d_grid_list);
+  if (s->d_grid_run) cudaFree(s->d_grid_run);
   if (s->d_qconst) cudaFree(s->d_qconst);
   for (auto &sl : s->slots) {
     if (sl.done) cudaEventDestroy(sl.done);
@@ -1237,9 +1250,96 @@ static long long max_chunk_for(const mpb_scene *s) {
   return std::max<long long>(32, std::min<long long>(kMaxChunk, lim));
 }
 
+// Broadphase grid of sphere_grid_kernel: per run of world-fixed partners, every partner's sphere (radius = sum of the two
+// bounding radii, as in the cull table) rasterised into a uniform grid; cell -> list of cull-table entries.  Built lazily
+// (a few ms for the C3 scene) so that a scene edit followed by small queries does not pay for it.
+static int ensure_grid(mpb_scene *s) {
+  if (!s->grid_dirty) return MPB_OK;
+  s->grid_dirty = false;
+  s->grid_on = false;
+  static const bool enabled = !(getenv("MPB_NO_GRID") && atoi(getenv("MPB_NO_GRID")));
+  const size_t n_runs = s->h_runs.size();  // incl. the sentinel
+  std::vector<int2> grun(n_runs, make_int2(-1, 0));
+  size_t fixed_entries = 0;
+  for (const int4 &r : s->h_runs)
+    if (r.w == 0) fixed_entries += (size_t)r.z;
+  if (!enabled || s->cull_tier != 0 || fixed_entries < 256) return MPB_OK;  // small tables: the parameter-space / direct kernels
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (const int4 &r : s->h_runs) {
+    if (r.w != 0) continue;
+    for (int k = r.y; k < r.y + r.z; k++) {
+      const float4 c = s->h_cullc[k];
+      const double rr = std::sqrt((double)c.w);
+      const double cc[3] = {c.x, c.y, c.z};
+      for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], cc[a] - rr); hi[a] = std::max(hi[a], cc[a] + rr); }
+    }
+  }
+  double ext = 0;
+  for (int a = 0; a < 3; a++) ext = std::max(ext, hi[a] - lo[a]);
+  if (!(ext > 0) || !(ext < 1e6)) return MPB_OK;
+  const double h = std::max(ext / 32.0, 0.02);
+  int gn[3];
+  for (int a = 0; a < 3; a++) gn[a] = std::max(1, std::min(40, (int)std::ceil((hi[a] - lo[a]) / h)));
+  const size_t cells = (size_t)gn[0] * gn[1] * gn[2];
+  std::vector<int> start;
+  std::vector<unsigned short> list;
+  const double pad = 1e-4;  // fp32 rounding of the moving centre near a cell face
+  for (size_t ri = 0; ri < n_runs; ri++) {
+    const int4 r = s->h_runs[ri];
+    if (r.w != 0 || r.z == 0 || r.z > 65535) continue;
+    std::vector<int> cnt(cells + 1, 0);
+    std::vector<std::pair<int, unsigned short>> ins;  // (cell, entry)
+    for (int e = 0; e < r.z; e++) {
+      const float4 c = s->h_cullc[r.y + e];
+      const double rr = std::sqrt((double)c.w) + pad;
+      const double cc[3] = {c.x, c.y, c.z};
+      int c0[3], c1[3];
+      for (int a = 0; a < 3; a++) {
+        c0[a] = std::max(0, (int)std::floor((cc[a] - rr - lo[a]) / h));
+        c1[a] = std::min(gn[a] - 1, (int)std::floor((cc[a] + rr - lo[a]) / h));
+      }
+      for (int z = c0[2]; z <= c1[2]; z++)
+        for (int y = c0[1]; y <= c1[1]; y++)
+          for (int x = c0[0]; x <= c1[0]; x++) {
+            const int idx[3] = {x, y, z};
+            double d2 = 0;
+            for (int a = 0; a < 3; a++) {
+              const double b0 = lo[a] + idx[a] * h, b1 = b0 + h;
+              const double d = cc[a] < b0 ? b0 - cc[a] : (cc[a] > b1 ? cc[a] - b1 : 0.0);
+              d2 += d * d;
+            }
+            if (d2 <= rr * rr) ins.push_back(std::make_pair((z * gn[1] + y) * gn[0] + x, (unsigned short)e));
+          }
+    }
+    for (const auto &p : ins) cnt[(size_t)p.first + 1]++;
+    for (size_t c = 0; c < cells; c++) cnt[c + 1] = cnt[c] + (cnt[c + 1] + 3) / 4 * 4;  // lists padded to multiples of four entries
+    grun[ri] = make_int2((int)start.size(), (int)list.size());
+    const size_t l0 = list.size();
+    list.resize(l0 + (size_t)cnt[cells], (unsigned short)0xffff);
+    std::vector<int> cur(cnt.begin(), cnt.end() - 1);
+    for (const auto &p : ins) list[l0 + (size_t)cur[(size_t)p.first]++] = p.second;  // entries ascending within a cell (insertion order)
+    start.insert(start.end(), cnt.begin(), cnt.end());
+  }
+  if (start.empty()) return MPB_OK;
+  CU(ensure(&s->d_grid_start, &s->grid_start_cap, start.size()));
+  CU(ensure(&s->d_grid_list, &s->grid_list_cap, std::max<size_t>(list.size(), 1)));
+  CU(ensure(&s->d_grid_run, &s->grid_run_cap, grun.size()));
+  CU(cudaMemcpy(s->d_grid_start, start.data(), start.size() * sizeof(int), cudaMemcpyHostToDevice));
+  if (!list.empty()) CU(cudaMemcpy(s->d_grid_list, list.data(), list.size() * sizeof(unsigned short), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(s->d_grid_run, grun.data(), grun.size() * sizeof(int2), cudaMemcpyHostToDevice));
+  s->img.grid_start = s->d_grid_start;
+  s->img.grid_list = s->d_grid_list;
+  s->img.grid_run = s->d_grid_run;
+  for (int a = 0; a < 3; a++) { s->img.grid_o[a] = (float)lo[a]; s->img.grid_n[a] = gn[a]; }
+  s->img.grid_inv_h = (float)(1.0 / h);
+  s->grid_on = true;
+  return MPB_OK;
+}
+
 static int prepare_work(mpb_scene *s, long long chunk) {
   // grow-only: buffers sized for a larger pass serve a smaller one (collide calls of different sizes and planning
   // rounds alternate on one scene; re-allocating GBs of queues between them would dominate small calls)
+  if (int grc = ensure_grid(s)) return grc;
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
   if (chunk <= s->chunk && s->wq.itf && P <= s->work_P && (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1) <= s->bins_cap) return MPB_OK;
   if (int hrc = harvest(s, true)) return hrc;  // calls in flight (device-pointer mode) still use the old buffers
@@ -1259,7 +1359,7 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   if (s->d_obb) { cudaFree(s->d_obb); s->d_obb = nullptr; }
   CU(cudaMalloc((void **)&s->d_obb, std::max<size_t>((size_t)s->img.n_dyn * 2 * s->pose_ld, 1) * sizeof(float4)));
   // survivors of the sphere phase: every admitted pair of every configuration at worst, bounded like the work queue
-  const size_t sq_cap = std::max<size_t>(std::min((size_t)chunk * P + (size_t)s->num_sms * 64 * MPB_SQ_CHUNK, kMaxSurvivors), 4096);
+  const size_t sq_cap = std::max<size_t>(std::min((size_t)chunk * P + (size_t)s->num_sms * 64 * MPB_SQ_CHUNK_GRID, kMaxSurvivors), 4096);
   CU(cudaMalloc((void **)&s->d_sq, sq_cap * sizeof(uint2)));
   s->sq_cap = (unsigned)sq_cap;
   // one slab: staging [12 f + cfg + pair][cap], then binned [12 f + cfg + pair][cap]
@@ -1373,6 +1473,8 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       if (small)
         sphere_pairs_kernel<<<(int)std::max<long long>(1, std::min<long long>((mm * (long long)s->img.n_pairs + 255) / 256, (long long)s->num_sms * 16)), 256, 0, st>>>(
             s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
+      else if (s->grid_on)
+        sphere_grid_kernel<<<std::min(cblocks, s->sphere_blocks_grid), 128, 0, st>>>(s->img, s->d_pose + off, s->pose_ld, mm, off, s->d_sq, s->sq_cap, s->wq.totals);
       else if (s->cull_tier == 1)
         sphere_kernel<0, 256, 64><<<std::min(cblocks, s->sphere_blocks_ct[0]), 128, (size_t)s->img.n_dyn * 3 * 128 * sizeof(float), st>>>(s->img, s->ct_small, s->d_pose + off, s->pose_ld, mm, off, s->d_sq,
                                                                                               s->sq_cap, s->wq.totals);
@@ -1398,7 +1500,9 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   // pairs of a robot against itself (C2, C5) seldom overlap by more than a few millimetres
   static const int presolve_env = !(getenv("MPB_NO_PRESOLVE") && atoi(getenv("MPB_NO_PRESOLVE")));
   const int presolve = presolve_env && s->has_primitives;
-  dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out, presolve);
+  static const int dense_v2 = getenv("MPB_DENSE_V2") && atoi(getenv("MPB_DENSE_V2"));  // two-phase variant: measured slower (it reloads the OBB rows), kept behind the switch
+  if (dense_v2) dense2_kernel<<<grid_for(s->dense2_blocks, 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out, presolve);
+  else dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out, presolve);
   *launches += 1;
   static const int refill_min = getenv("MPB_REFILL_MIN") ? atoi(getenv("MPB_REFILL_MIN")) : 8;
   static const double unit_factor = getenv("MPB_UNIT_FACTOR") ? atof(getenv("MPB_UNIT_FACTOR")) : 1.0;
@@ -1411,8 +1515,8 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   static const int narrow_v2 = !(getenv("MPB_NARROW_V1") && atoi(getenv("MPB_NARROW_V1")));
   const int nblocks2 = grid_for(s->narrow2_blocks, 64);
   if (narrow_v2) {
-    if (s->smem_verts) narrow2_kernel<true><<<nblocks2, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
-    else narrow2_kernel<false><<<nblocks2, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
+    if (s->smem_verts) narrow2_kernel<true><<<nblocks2, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min, 0);
+    else narrow2_kernel<false><<<nblocks2, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min, 0);
   } else if (s->smem_verts) narrow_kernel<true><<<nblocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
   else narrow_kernel<false><<<nblocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins, 0, refill_min);
   *launches += 3;
@@ -1426,11 +1530,11 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
     expand_kernel<<<grid_for(s->num_sms * 8, 16), 128, 0, st>>>(s->img, s->wq, out, small ? 0 : lane_on);
     if (!small && lane_on) { expand_lane_kernel<<<s->expand_lane_blocks, 128, 0, st>>>(s->img, s->wq, out); *launches += 1; }
     scan_bins_kernel<<<1, 32, 0, st>>>(s->wq, s->img.n_bins2, -1, -1, (unsigned)std::max(1.0, s->narrow_blocks * 8.0 * unit_factor), s->sq_cap);
-    if (presolve) scatter_kernel<true><<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 1, out);
+    if (presolve) scatter_kernel<true><<<s->num_sms * 4, 512, 0, st>>>(s->img, s->wq, 1, out);  // leaf items: inner balls vs voxel box
     else scatter_kernel<false><<<s->num_sms * 2, 1024, 0, st>>>(s->img, s->wq, 1, out);
     if (narrow_v2) {
-      if (s->smem_verts) narrow2_kernel<true><<<s->narrow2_blocks, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
-      else narrow2_kernel<false><<<s->narrow2_blocks, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
+      if (s->smem_verts) narrow2_kernel<true><<<s->narrow2_blocks, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min, 0);
+      else narrow2_kernel<false><<<s->narrow2_blocks, 256, s->narrow2_smem, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min, 0);
     } else if (s->smem_verts) narrow_kernel<true><<<s->narrow_blocks, 256, vsm, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     else narrow_kernel<false><<<s->narrow_blocks, 256, 0, st>>>(s->img, s->wq, out, s->img.n_bins2, 1, refill_min);
     *launches += 5;

@@ -42,6 +42,12 @@ struct SceneImg {
   const float4 *cullq;      // [n_pairs] world-fixed partners in expanded form: (-2c, |c|^2 - (R1 + R2)^2 - slack), see sphere_kernel
   const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}
   const int4 *runs;         // cull-table runs: {moving slot or -1, first entry, count, partner kind (0 fixed, 1 moving)}
+  // broadphase grid over the world-fixed partners (sphere_grid_kernel): one cell table per run of fixed partners
+  const int *grid_start;    // [n_grid_runs][gx * gy * gz + 1] offsets into grid_list (relative to the run's block)
+  const unsigned short *grid_list;  // cull-table entries (relative to the run's first entry) per cell
+  const int2 *grid_run;     // [n_runs] {offset of the run's cell table in grid_start or -1, offset of its lists in grid_list}
+  float grid_o[3], grid_inv_h; // grid origin, 1 / cell size
+  int grid_n[3];            // cells per axis
   const int *pair_bin2;     // [n_pairs] bin of the leaf-level items a BVH pair expands into (-1: not a BVH pair)
   int expand_bin;           // first-round bin that collects the shape x BVH pairs (-1: none)
   int expand2_bin;          // first-round bin that collects the BVH x BVH pairs (-1: none)
@@ -548,6 +554,112 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
     if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
 }
 
+// sphere phase through a broadphase GRID for large cull tables whose partners are world-fixed (C3: 12 moving objects x 130
+// obstacles).  sphere_blk_kernel tests every admitted pair of every configuration, 1587 tests of which 2.6 % pass; here
+// the host rasterises, per run (= moving object), every partner's sphere inflated by the object's radius into a uniform
+// grid, and a configuration tests only the partners listed in the cell that holds the moving object's centre (mean 7,
+// warp maximum ~11 per object instead of 130).  The survivors are exactly those of the full loop (the cell lists are
+// conservative), in a different order.  Runs of moving partners (self pairs) keep the direct loop.
+#define POSE(w, i) pose[(size_t)(w) * ld + (i)]
+#define MPB_SQ_CHUNK_GRID 1024  // survivor-queue slots a warp of sphere_grid_kernel reserves per atomic: a trip pushes up to 128 entries,
+                               // and what is left of a chunk when the next push does not fit is padding dense_kernel has to skip
+__global__ void __launch_bounds__(128) sphere_grid_kernel(const __grid_constant__ SceneImg img, const float *__restrict__ pose, size_t ld, long long n,
+                                                          long long cfg_base, uint2 *__restrict__ sq, unsigned sq_cap, unsigned *__restrict__ totals) {
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31;
+  const int cbase = img.w_sphere;
+  unsigned wbase = 0, wused = 0, wcap = 0;  // warp-uniform survivor-queue chunk, kept across the warp's tiles
+  const long long n_tiles = (n + 31) / 32;
+  const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
+  const int cells = img.grid_n[0] * img.grid_n[1] * img.grid_n[2];
+  for (long long tile = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < n_tiles; tile += warp_stride) {
+    const long long i = tile * 32 + lane;
+    const bool valid = i < n;
+    const long long ic = valid ? i : n - 1;
+    const unsigned cfg = (unsigned)(cfg_base + i);
+    for (int r = 0;; r++) {
+      const int4 run = __ldg(img.runs + r);  // {moving slot or -1, first, count, partner kind}
+      if (run.z == 0) break;                  // sentinel
+      float ax = 0.f, ay = 0.f, az = 0.f;
+      if (run.x >= 0) { ax = POSE(cbase + run.x * 3, ic); ay = POSE(cbase + run.x * 3 + 1, ic); az = POSE(cbase + run.x * 3 + 2, ic); }
+      const int2 gr = __ldg(img.grid_run + r);
+      int j0 = 0, j1 = 0;  // this lane's slice of candidate slots
+      const unsigned short *list = nullptr;
+      if (gr.x >= 0) {
+        const int cx = (int)floorf((ax - img.grid_o[0]) * img.grid_inv_h), cy = (int)floorf((ay - img.grid_o[1]) * img.grid_inv_h),
+                  cz = (int)floorf((az - img.grid_o[2]) * img.grid_inv_h);
+        if (valid && cx >= 0 && cy >= 0 && cz >= 0 && cx < img.grid_n[0] && cy < img.grid_n[1] && cz < img.grid_n[2]) {
+          const int cell = (cz * img.grid_n[1] + cy) * img.grid_n[0] + cx;
+          j0 = __ldg(img.grid_start + gr.x + cell);
+          j1 = __ldg(img.grid_start + gr.x + cell + 1);
+        }
+        list = img.grid_list + gr.y;
+      } else if (valid) j1 = run.z;  // no grid for this run (moving partners): every entry is a candidate
+      (void)cells;
+      // four candidates per trip: the cell lists are padded to multiples of four entries (0xffff = none), so one aligned
+      // 8-byte load brings four entry numbers and the four partner records are fetched independently -- the kernel is
+      // bound by its chain of dependent loads, not by instructions
+      const int len = __reduce_max_sync(FULL, j1 - j0);
+      for (int t = 0; t < len; t += 4) {
+        unsigned pmask = 0;
+        int kk[4] = {0, 0, 0, 0};
+        if (j0 + t < j1) {
+          if (list) {
+            const uint2 pk = __ldg(reinterpret_cast<const uint2 *>(list + j0 + t));
+            kk[0] = (int)(pk.x & 0xffffu); kk[1] = (int)(pk.x >> 16); kk[2] = (int)(pk.y & 0xffffu); kk[3] = (int)(pk.y >> 16);
+          } else {
+#pragma unroll
+            for (int u = 0; u < 4; u++) kk[u] = t + u < j1 ? t + u : 0xffff;
+          }
+          float4 c[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) c[u] = __ldg(img.cullc + run.y + (kk[u] == 0xffff ? 0 : kk[u]));
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            if (kk[u] == 0xffff) continue;
+            float bx = c[u].x, by = c[u].y, bz = c[u].z;
+            if (run.w == 1) {  // moving partner
+              const int m2 = (__ldg(&img.cullm[run.y + kk[u]].y) >> 16) - 1;
+              bx = POSE(cbase + m2 * 3, ic); by = POSE(cbase + m2 * 3 + 1, ic); bz = POSE(cbase + m2 * 3 + 2, ic);
+            }
+            const float dx = ax - bx, dy = ay - by, dz = az - bz;
+            if (fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= c[u].w) pmask |= 1u << u;
+          }
+        }
+        if (!__any_sync(FULL, pmask != 0)) continue;
+        const unsigned cntl = __popc(pmask);
+        unsigned incl = cntl;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const unsigned tt = __shfl_up_sync(FULL, incl, o);
+          if ((int)lane >= o) incl += tt;
+        }
+        const unsigned cnt = __shfl_sync(FULL, incl, 31);
+        if (wused + cnt > wcap) {
+          for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+            if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);  // unused tail of the old chunk
+          unsigned nb = 0;
+          if (lane == 0) nb = atomicAdd(&totals[6], (unsigned)MPB_SQ_CHUNK_GRID);
+          wbase = __shfl_sync(FULL, nb, 0);
+          wused = 0;
+          wcap = MPB_SQ_CHUNK_GRID;
+        }
+        unsigned pos = wbase + wused + incl - cntl;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (pmask & (1u << u)) {
+            if (pos < sq_cap) sq[pos] = make_uint2(cfg, (unsigned)(run.y + kk[u]));
+            pos++;
+          }
+        wused += cnt;
+      }
+    }
+  }
+  for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+    if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
+}
+#undef POSE
+
 // sphere_kernel<0> for cull tables too large for the parameter space (C3: 1587 entries), register-blocked over CB
 // tiles of 32 configurations: an entry fetched with a per-lane LDG.128 writes 512 B back through the LSU (4 cycles per
 // SM) although every lane reads the same address, which is more than the ~8 instructions of its test cost to issue;
@@ -655,22 +767,19 @@ __global__ void __launch_bounds__(128) sphere_blk_kernel(const __grid_constant__
 // forms below, when that one is a primitive; a ball of it otherwise -- the shapes intersect, which is what MPR would
 // report after three or more support evaluations.  In the C3 scene most narrowphase items are such collisions.
 __device__ __forceinline__ bool ball_hits_primitive(int type, const float *prm, V3 c, float r) {  // c: ball centre in the primitive's frame
-  switch (type) {
-    case MPB_GEOM_SPHERE: { const float rr = r + prm[0]; return dot(c, c) < rr * rr; }
-    case MPB_GEOM_BOX: {
-      const float dx = c.x - clampf(c.x, -prm[0], prm[0]), dy = c.y - clampf(c.y, -prm[1], prm[1]), dz = c.z - clampf(c.z, -prm[2], prm[2]);
-      return fmaf(dx, dx, fmaf(dy, dy, dz * dz)) < r * r;
-    }
-    case MPB_GEOM_CAPSULE: {
-      const float dz = c.z - clampf(c.z, -prm[1], prm[1]), rr = r + prm[0];
-      return fmaf(c.x, c.x, fmaf(c.y, c.y, dz * dz)) < rr * rr;
-    }
-    case MPB_GEOM_CYLINDER: {
-      const float dr = fmaxf(sqrtf(fmaf(c.x, c.x, c.y * c.y)) - prm[0], 0.f), dz = fmaxf(fabsf(c.z) - prm[1], 0.f);
-      return fmaf(dr, dr, dz * dz) < r * r;
-    }
-    default: return false;
-  }
+  // all four closed forms, selected at the end: the lanes of a warp meet different partner types, and a switch would run
+  // each case for a handful of lanes
+  const float rp = r + prm[0];
+  const float d_sph = dot(c, c) - rp * rp;                                         // sphere: |c| < r + R
+  const float bx = c.x - clampf(c.x, -prm[0], prm[0]), by = c.y - clampf(c.y, -prm[1], prm[1]), bz = c.z - clampf(c.z, -prm[2], prm[2]);
+  const float d_box = fmaf(bx, bx, fmaf(by, by, bz * bz)) - r * r;                 // box: point-box distance < r
+  const float cz = c.z - clampf(c.z, -prm[1], prm[1]);
+  const float rad2 = fmaf(c.x, c.x, c.y * c.y);
+  const float d_cap = rad2 + cz * cz - rp * rp;                                    // capsule: point-segment distance < r + R
+  const float dr = fmaxf(sqrtf(rad2) - prm[0], 0.f), dz = fmaxf(fabsf(c.z) - prm[1], 0.f);
+  const float d_cyl = fmaf(dr, dr, dz * dz) - r * r;                               // cylinder: radial / axial excess < r
+  const float d = type == MPB_GEOM_SPHERE ? d_sph : (type == MPB_GEOM_BOX ? d_box : (type == MPB_GEOM_CAPSULE ? d_cap : d_cyl));
+  return type >= MPB_GEOM_SPHERE && type <= MPB_GEOM_CYLINDER && d < 0.f;
 }
 // A, B: the two objects of the item; (R, t): B in A.  leaf >= 0: B is a BVH object and the item is its leaf primitive `leaf`.
 __device__ __forceinline__ bool sufficient_hit(const SceneImg &img, const DevObject &A, const DevObject &B, const float *R, V3 t, int leaf) {
@@ -689,14 +798,14 @@ __device__ __forceinline__ bool sufficient_hit(const SceneImg &img, const DevObj
     return false;
   }
   const bool pa = A.type >= MPB_GEOM_SPHERE && A.type <= MPB_GEOM_CYLINDER, pb = B.type >= MPB_GEOM_SPHERE && B.type <= MPB_GEOM_CYLINDER;
-  if (pb) {  // balls of A against the primitive B, exactly
+  if (pb) {  // balls of A against the primitive B, exactly (an unused ball has radius 0 and a far centre: it cannot hit)
+    bool hit = false;
 #pragma unroll
     for (int k = 0; k < MPB_INNER_BALLS; k++) {
       const float4 b = A.ball[k];
-      if (b.w <= 0.f) break;
-      if (ball_hits_primitive(B.type, B.prm, rot_t(R, v3(b.x, b.y, b.z) - t), b.w)) return true;
+      hit |= b.w > 0.f && ball_hits_primitive(B.type, B.prm, rot_t(R, v3(b.x, b.y, b.z) - t), b.w);
     }
-    return false;
+    return hit;
   }
   if (pa) {  // balls of B against the primitive A
 #pragma unroll
@@ -843,8 +952,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
         const Xf Xbi = xf_rows(__ldg(cb + 8), __ldg(cb + 9), __ldg(cb + 10));
         rel = xf_mul(xf_mul(Xa, Rt), Xbi);
         // sufficient test with the inner balls (exact closed forms against a primitive partner): an item it settles is
-        // never staged, binned or sent to the narrowphase.  Survivors of one configuration sit next to each other in the
-        // queue and the partners of a run come in blocks of one geometry type, so the type switch rarely diverges.
+        // never staged, binned or sent to the narrowphase (what matters: the narrowphase's prologue costs per ITEM)
         if (MODE == 0 && presolve && (pr.bin_dyn & 0xffff) != img.expand_bin && (pr.bin_dyn & 0xffff) != img.expand2_bin &&
             sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], rel.r, v3(rel.p[0], rel.p[1], rel.p[2]), -1)) {
           keep = false;
@@ -895,6 +1003,182 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
       if (s_bins[b]) atomicAdd(&wq.bin_count[b], s_bins[b]);
 }
 #undef POSE
+
+// ---------------------------------------------------------------------------------------------- dense cull, two phases
+// dense_kernel<0> does everything for a survivor in one go: SAT, relative pose, staging (and, for a while, the
+// sufficient-hit test).  ncu showed 11.5 of 32 lanes per instruction: half of a warp's survivors fail the SAT and idle
+// through the rest, and the sufficient test's geometry switch ran on 2-4 lanes (profiles/r02_ncu_dense_presolve_source.csv).
+// Here a warp runs PHASE 1 (frames, SAT, inscribed-ball test) on 32 survivors and appends what is kept, as
+// (configuration, pair), to one of five per-warp buffers in shared memory by the partner's geometry type; whenever a buffer
+// holds 32 entries, PHASE 2 runs on them with all lanes on one type: frames again (the rows are still in L1), relative
+// pose of the object frames, the sufficient-hit test, staging of what is left.
+#define MPB_D2_TYPES 5   // partner is a sphere / box / capsule / cylinder / anything else
+#define MPB_D2_CAP 64    // entries per buffer: phase 2 runs at 32, a phase-1 trip adds at most 32
+
+struct DensePair {  // frames of a (configuration, pair): what both phases derive first
+  Xf Rt;            // OBB frame of B in the OBB frame of A
+  float4 ha, hb, ia, ib;
+  const float4 *ca, *cb;
+};
+__device__ __forceinline__ void dense_frames(const SceneImg &img, const float4 *__restrict__ obb, size_t ld, unsigned cfg, const DevPair &pr, DensePair &D) {
+  // cull records (MPB_COBB_WORDS float4 per object): [0..2] OBB frame (world frame if the object is fixed,
+  // owner-joint frame if it moves), [3] half extents + inscribed radius, [4] inscribed-ball centre in the OBB frame
+  // + moving slot, [5..7] OBB frame in the object frame, [8..10] its inverse
+  D.ca = img.cobb + MPB_COBB_WORDS * pr.a;
+  D.cb = img.cobb + MPB_COBB_WORDS * pr.b;
+  D.ha = __ldg(D.ca + 3); D.hb = __ldg(D.cb + 3); D.ia = __ldg(D.ca + 4); D.ib = __ldg(D.cb + 4);
+  const int da = __float_as_int(D.ia.w), db = __float_as_int(D.ib.w);
+  // moving: this configuration's row of the OBB table (quaternion, translation); fixed: the record's world frame
+  Xf Ea, Eb;
+  if (da >= 0) { const float4 *pa = obb + ((size_t)da * ld + cfg) * 2; Ea = quat_rows(pa[0], pa[1]); }
+  else Ea = xf_rows(__ldg(D.ca), __ldg(D.ca + 1), __ldg(D.ca + 2));
+  if (db >= 0) { const float4 *pb = obb + ((size_t)db * ld + cfg) * 2; Eb = quat_rows(pb[0], pb[1]); }
+  else Eb = xf_rows(__ldg(D.cb), __ldg(D.cb + 1), __ldg(D.cb + 2));
+  const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
+#pragma unroll
+  for (int rr = 0; rr < 3; rr++) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) D.Rt.r[3 * rr + c] = fmaf(Ea.r[rr], Eb.r[c], fmaf(Ea.r[3 + rr], Eb.r[3 + c], Ea.r[6 + rr] * Eb.r[6 + c]));
+    D.Rt.p[rr] = fmaf(Ea.r[rr], d0, fmaf(Ea.r[3 + rr], d1, Ea.r[6 + rr] * d2));
+  }
+}
+
+__global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
+                                                                      unsigned sq_cap, WorkQ wq, HitOut out, int presolve) {
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ unsigned s_bins[MPB_SMEM_BINS];  // per-block bin counts, flushed once at the end
+  __shared__ uint2 s_buf[4][MPB_D2_TYPES][MPB_D2_CAP];
+  const bool smem_bins = img.n_bins <= MPB_SMEM_BINS;
+  for (int b = threadIdx.x; b < MPB_SMEM_BINS; b += blockDim.x) s_bins[b] = 0;
+  __syncthreads();
+  unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
+  int cnt[MPB_D2_TYPES];
+#pragma unroll
+  for (int c = 0; c < MPB_D2_TYPES; c++) cnt[c] = 0;
+  const unsigned total = min(wq.totals[6], sq_cap);
+  const unsigned total_r = (total + 31u) & ~31u;
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&wq.counters[3], (unsigned long long)total);  // incl. chunk padding
+
+  // phase 2 on `nb` entries of buffer `c` (the top ones)
+  auto phase2 = [&](int c, int nb) {
+    bool keep = false;
+    unsigned cfg = 0;
+    int p = 0;
+    Xf rel;
+    if ((int)lane < nb) {
+      const uint2 e = s_buf[warp][c][cnt[c] - nb + (int)lane];
+      cfg = e.x;
+      p = (int)e.y;
+      const DevPair pr = img.pairs[p];
+      DensePair D;
+      dense_frames(img, obb, ld, cfg, pr, D);
+      // relative pose of the two OBJECT frames for the narrowphase: Xa (A_obb^-1 B_obb) Xb^-1
+      const Xf Xa = xf_rows(__ldg(D.ca + 5), __ldg(D.ca + 6), __ldg(D.ca + 7));
+      const Xf Xbi = xf_rows(__ldg(D.cb + 8), __ldg(D.cb + 9), __ldg(D.cb + 10));
+      rel = xf_mul(xf_mul(Xa, D.Rt), Xbi);
+      keep = true;
+      const int bin = pr.bin_dyn & 0xffff;
+      if (presolve && bin != img.expand_bin && bin != img.expand2_bin &&
+          sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], rel.r, v3(rel.p[0], rel.p[1], rel.p[2]), -1)) {
+        keep = false;
+        report_hit(out, cfg, p);
+      }
+    }
+    const unsigned km = __ballot_sync(FULL, keep);
+    if (km) {
+      // warp-private chunk of staging slots: one same-address atomic per MPB_STAGE_CHUNK items
+      const unsigned cntk = (unsigned)__popc(km);
+      if (wused + cntk > MPB_STAGE_CHUNK) {
+        if (wbase != 0xffffffffu)
+          for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
+            if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;  // unused tail of the old chunk
+        unsigned nbs = 0;
+        if (lane == 0) nbs = atomicAdd(&wq.totals[0], (unsigned)MPB_STAGE_CHUNK);
+        wbase = __shfl_sync(FULL, nbs, 0);
+        wused = 0;
+      }
+      if (keep) {
+        const unsigned slot = wbase + wused + __popc(km & ((1u << lane) - 1u));
+        if (slot < wq.cap) {
+#pragma unroll
+          for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = rel.r[k2];
+#pragma unroll
+          for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = rel.p[k2];
+          wq.scfg[slot] = (int)cfg;
+          wq.spair[slot] = p;
+          wq.saux[slot] = 0;
+          const int bin = img.pairs[p].bin_dyn & 0xffff;
+          if (smem_bins) atomicAdd(&s_bins[bin], 1u);
+          else atomicAdd(&wq.bin_count[bin], 1u);
+        }
+      }
+      wused += cntk;
+    }
+    cnt[c] -= nb;
+    __syncwarp();
+  };
+
+  const unsigned e_first = blockIdx.x * blockDim.x + threadIdx.x, e_stride = gridDim.x * blockDim.x;
+  uint2 ent_next = make_uint2(0xffffffffu, 0u);  // the survivor record of the next trip is fetched one trip ahead
+  if (e_first < total) ent_next = sq[e_first];
+  for (unsigned e = e_first; e < total_r; e += e_stride) {
+    // ---- phase 1: frames, SAT, inscribed balls
+    bool keep = false;
+    int p = 0, cls = MPB_D2_TYPES - 1;
+    unsigned cfg = 0;
+    const uint2 ent = ent_next;
+    ent_next = make_uint2(0xffffffffu, 0u);
+    if (e + e_stride < total) ent_next = sq[e + e_stride];
+    if (ent.x != 0xffffffffu) {
+      cfg = ent.x;
+      p = __ldg(&img.cullm[ent.y].x);
+      const DevPair pr = img.pairs[p];
+      DensePair D;
+      dense_frames(img, obb, ld, cfg, pr, D);
+      const float ah[3] = {D.ha.x, D.ha.y, D.ha.z}, bh[3] = {D.hb.x, D.hb.y, D.hb.z};
+      keep = !obb_disjoint(D.Rt.r, D.Rt.p, ah, bh);
+      if (keep && D.ha.w > 0.f && D.hb.w > 0.f) {
+        // sufficient test: balls inscribed in the two shapes overlap -> the pair collides, no narrowphase needed
+        const float ib3[3] = {D.ib.x, D.ib.y, D.ib.z};
+        float icb[3];
+        xf_point(D.Rt, ib3, icb);  // B's ball centre in A's OBB frame
+        const float e0 = D.ia.x - icb[0], e1 = D.ia.y - icb[1], e2 = D.ia.z - icb[2];
+        const float rs = 0.999f * (D.ha.w + D.hb.w);
+        if (fmaf(e0, e0, fmaf(e1, e1, e2 * e2)) < rs * rs) {
+          keep = false;
+          report_hit(out, cfg, p);
+        }
+      }
+      if (keep) {
+        const int tb = img.objs[pr.b].type;
+        cls = (tb >= MPB_GEOM_SPHERE && tb <= MPB_GEOM_CYLINDER) ? tb - MPB_GEOM_SPHERE : MPB_D2_TYPES - 1;
+      }
+    }
+    // ---- kept survivors -> the buffer of their partner type; a buffer that reaches 32 entries runs phase 2
+#pragma unroll
+    for (int c = 0; c < MPB_D2_TYPES; c++) {
+      const unsigned m = __ballot_sync(FULL, keep && cls == c);
+      if (!m) continue;
+      if (keep && cls == c) s_buf[warp][c][cnt[c] + __popc(m & ((1u << lane) - 1u))] = make_uint2(cfg, (unsigned)p);
+      cnt[c] += __popc(m);
+      __syncwarp();
+      if (cnt[c] >= 32) phase2(c, 32);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < MPB_D2_TYPES; c++)
+    while (cnt[c] > 0) phase2(c, min(cnt[c], 32));
+  // invalidate the unused tail of the last chunk
+  if (wbase != 0xffffffffu) {
+    for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
+      if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;
+  }
+  __syncthreads();
+  if (smem_bins)
+    for (int b = threadIdx.x; b < img.n_bins; b += blockDim.x)
+      if (s_bins[b]) atomicAdd(&wq.bin_count[b], s_bins[b]);
+}
 
 // start of a pass (or of its second narrowphase round): bin counts, staged-item and survivor counters back to zero
 __global__ void pass_reset_kernel(WorkQ wq, int n_bins) {
@@ -1404,13 +1688,14 @@ __device__ __forceinline__ V3 mink_support(const DevShape &A, const DevShape &B,
 
 // item `my` of the binned queue -> lane state; false: nothing to do (already known to collide)
 __device__ __forceinline__ bool mpr_fetch(const SceneImg &img, const WorkQ &wq, const HitOut &out, unsigned my, int round, DevShape &A, DevShape &B,
-                                          MprItem &I, V3 &cA, V3 &cBl) {
+                                          MprItem &I, V3 &cA, V3 &cBl, int2 *objs = nullptr) {
 #pragma unroll
   for (int k = 0; k < 9; k++) I.R[k] = wq.itf[(size_t)k * wq.cap + my];
   I.t = v3(wq.itf[(size_t)9 * wq.cap + my], wq.itf[(size_t)10 * wq.cap + my], wq.itf[(size_t)11 * wq.cap + my]);
   I.cfg = wq.icfg[my];
   I.p = wq.ipair[my];
   const DevPair pr = img.pairs[I.p];
+  if (objs) *objs = make_int2(pr.a, pr.b);
   const DevObject &OA = img.objs[pr.a];
   const DevObject &OB = img.objs[pr.b];
   A.p0 = OA.prm[0]; A.p1 = OA.prm[1]; A.p2 = OA.prm[2];  // primitive parameters differ per item
@@ -1430,7 +1715,7 @@ __device__ __forceinline__ bool mpr_fetch(const SceneImg &img, const WorkQ &wq, 
 }
 
 template <bool SMEM>
-__global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow2_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round, int refill_min) {
+__global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow2_kernel(SceneImg img, WorkQ wq, HitOut out, int n_bins, int round, int refill_min, int presolve) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bar;
   const float4 *verts = img.verts;
@@ -1485,9 +1770,15 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow2_kernel(SceneImg 
         next += 32;
         MprItem I;
         V3 cA = v3(0.f, 0.f, 0.f), cBl = cA;
-        bool act = false;
-        if (my < end) act = mpr_fetch(img, wq, out, my, round, A, B, I, cA, cBl);
-        else {
+        bool act = false, hit = false;
+        if (my < end) {
+          int2 ob;
+          act = mpr_fetch(img, wq, out, my, round, A, B, I, cA, cBl, &ob);
+          // sufficient test with the inner balls (exact closed forms against a primitive partner; leaf items: against the voxel
+          // box): here the lanes are converged and the geometry types are those of the bin, so the type switch is uniform.
+          // (Inside dense_kernel, on unsorted survivors, the same code ran on 2-4 lanes of 32: profiles/r02_ncu_dense_presolve_source.csv.)
+          if (act && presolve && sufficient_hit(img, img.objs[ob.x], img.objs[ob.y], I.R, I.t, round == 1 ? B.voff : -1)) { act = false; hit = true; }
+        } else {
 #pragma unroll
           for (int k = 0; k < 9; k++) I.R[k] = (k % 4 == 0) ? 1.f : 0.f;
           I.t = cA; I.cfg = 0; I.p = 0;
@@ -1496,7 +1787,6 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow2_kernel(SceneImg 
         V3 v0 = cA - (rot(I.R, cBl) + I.t);
         if (is_zero(v0.x) && is_zero(v0.y) && is_zero(v0.z)) v0.x += 10.f * MPB_EPS;
         V3 dir = normalized(v0 * -1.f);
-        bool hit = false;
         int iters = 0;
         const V3 v1 = mink_support<SMEM>(A, B, I, dir, verts, img.prims, cells);
         V3 v2 = v1;
