@@ -1500,7 +1500,7 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   // pairs of a robot against itself (C2, C5) seldom overlap by more than a few millimetres
   static const int presolve_env = !(getenv("MPB_NO_PRESOLVE") && atoi(getenv("MPB_NO_PRESOLVE")));
   const int presolve = presolve_env && s->has_primitives;
-  static const int dense_v2 = getenv("MPB_DENSE_V2") && atoi(getenv("MPB_DENSE_V2"));  // two-phase variant: measured slower (it reloads the OBB rows), kept behind the switch
+  static const int dense_v2 = !(getenv("MPB_DENSE_V1") && atoi(getenv("MPB_DENSE_V1")));
   if (dense_v2) dense2_kernel<<<grid_for(s->dense2_blocks, 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out, presolve);
   else dense_kernel<0><<<grid_for(s->dense_blocks[0], 128), 128, 0, st>>>(s->img, s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq, out, presolve);
   *launches += 1;

@@ -1005,78 +1005,54 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
 #undef POSE
 
 // ---------------------------------------------------------------------------------------------- dense cull, two phases
-// dense_kernel<0> does everything for a survivor in one go: SAT, relative pose, staging (and, for a while, the
-// sufficient-hit test).  ncu showed 11.5 of 32 lanes per instruction: half of a warp's survivors fail the SAT and idle
-// through the rest, and the sufficient test's geometry switch ran on 2-4 lanes (profiles/r02_ncu_dense_presolve_source.csv).
-// Here a warp runs PHASE 1 (frames, SAT, inscribed-ball test) on 32 survivors and appends what is kept, as
-// (configuration, pair), to one of five per-warp buffers in shared memory by the partner's geometry type; whenever a buffer
-// holds 32 entries, PHASE 2 runs on them with all lanes on one type: frames again (the rows are still in L1), relative
-// pose of the object frames, the sufficient-hit test, staging of what is left.
-#define MPB_D2_TYPES 5   // partner is a sphere / box / capsule / cylinder / anything else
-#define MPB_D2_CAP 64    // entries per buffer: phase 2 runs at 32, a phase-1 trip adds at most 32
-
-struct DensePair {  // frames of a (configuration, pair): what both phases derive first
-  Xf Rt;            // OBB frame of B in the OBB frame of A
-  float4 ha, hb, ia, ib;
-  const float4 *ca, *cb;
-};
-__device__ __forceinline__ void dense_frames(const SceneImg &img, const float4 *__restrict__ obb, size_t ld, unsigned cfg, const DevPair &pr, DensePair &D) {
-  // cull records (MPB_COBB_WORDS float4 per object): [0..2] OBB frame (world frame if the object is fixed,
-  // owner-joint frame if it moves), [3] half extents + inscribed radius, [4] inscribed-ball centre in the OBB frame
-  // + moving slot, [5..7] OBB frame in the object frame, [8..10] its inverse
-  D.ca = img.cobb + MPB_COBB_WORDS * pr.a;
-  D.cb = img.cobb + MPB_COBB_WORDS * pr.b;
-  D.ha = __ldg(D.ca + 3); D.hb = __ldg(D.cb + 3); D.ia = __ldg(D.ca + 4); D.ib = __ldg(D.cb + 4);
-  const int da = __float_as_int(D.ia.w), db = __float_as_int(D.ib.w);
-  // moving: this configuration's row of the OBB table (quaternion, translation); fixed: the record's world frame
-  Xf Ea, Eb;
-  if (da >= 0) { const float4 *pa = obb + ((size_t)da * ld + cfg) * 2; Ea = quat_rows(pa[0], pa[1]); }
-  else Ea = xf_rows(__ldg(D.ca), __ldg(D.ca + 1), __ldg(D.ca + 2));
-  if (db >= 0) { const float4 *pb = obb + ((size_t)db * ld + cfg) * 2; Eb = quat_rows(pb[0], pb[1]); }
-  else Eb = xf_rows(__ldg(D.cb), __ldg(D.cb + 1), __ldg(D.cb + 2));
-  const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
-#pragma unroll
-  for (int rr = 0; rr < 3; rr++) {
-#pragma unroll
-    for (int c = 0; c < 3; c++) D.Rt.r[3 * rr + c] = fmaf(Ea.r[rr], Eb.r[c], fmaf(Ea.r[3 + rr], Eb.r[3 + c], Ea.r[6 + rr] * Eb.r[6 + c]));
-    D.Rt.p[rr] = fmaf(Ea.r[rr], d0, fmaf(Ea.r[3 + rr], d1, Ea.r[6 + rr] * d2));
-  }
-}
+// dense_kernel<0> does everything for a survivor in one go: SAT, relative pose, sufficient-hit test, staging.  ncu showed
+// 11-14 of 32 lanes per instruction: half of a warp's survivors fail the SAT and idle through the longer second half
+// (profiles/r02_ncu_dense_presolve_source.csv).  Here a warp runs PHASE 1 (frames, SAT, inscribed-ball test) on 32
+// survivors and appends what is kept -- the relative OBB frame Rt, configuration and pair, 14 words -- to a per-warp
+// buffer in shared memory; whenever the buffer holds 32 entries, PHASE 2 runs on them with all lanes busy: relative
+// pose of the object frames, the (branch-free) sufficient-hit test, staging of what is left.  Nothing is loaded twice.
+// (A first version buffered only (configuration, pair) and re-derived the frames in phase 2: the OBB rows are random
+// 32-byte reads, and fetching them twice cost more than the idle lanes had.)
+#define MPB_D2_CAP 64    // buffer entries per warp: phase 2 runs at 32, a phase-1 trip adds at most 32
+#define MPB_D2_F 14      // Rt (12 floats), configuration, pair
 
 __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
                                                                       unsigned sq_cap, WorkQ wq, HitOut out, int presolve) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ unsigned s_bins[MPB_SMEM_BINS];  // per-block bin counts, flushed once at the end
-  __shared__ uint2 s_buf[4][MPB_D2_TYPES][MPB_D2_CAP];
+  __shared__ float s_buf[4][MPB_D2_F][MPB_D2_CAP];
   const bool smem_bins = img.n_bins <= MPB_SMEM_BINS;
   for (int b = threadIdx.x; b < MPB_SMEM_BINS; b += blockDim.x) s_bins[b] = 0;
   __syncthreads();
+  float (*buf)[MPB_D2_CAP] = s_buf[warp];
   unsigned wbase = 0xffffffffu, wused = MPB_STAGE_CHUNK;  // warp-uniform staging chunk state
-  int cnt[MPB_D2_TYPES];
-#pragma unroll
-  for (int c = 0; c < MPB_D2_TYPES; c++) cnt[c] = 0;
+  int cnt = 0;                                             // entries in the warp's buffer (warp-uniform)
   const unsigned total = min(wq.totals[6], sq_cap);
   const unsigned total_r = (total + 31u) & ~31u;
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&wq.counters[3], (unsigned long long)total);  // incl. chunk padding
 
-  // phase 2 on `nb` entries of buffer `c` (the top ones)
-  auto phase2 = [&](int c, int nb) {
+  // phase 2 on the top `nb` entries of the buffer
+  auto phase2 = [&](int nb) {
     bool keep = false;
     unsigned cfg = 0;
     int p = 0;
     Xf rel;
     if ((int)lane < nb) {
-      const uint2 e = s_buf[warp][c][cnt[c] - nb + (int)lane];
-      cfg = e.x;
-      p = (int)e.y;
+      const int e = cnt - nb + (int)lane;
+      Xf Rt;
+#pragma unroll
+      for (int k = 0; k < 9; k++) Rt.r[k] = buf[k][e];
+#pragma unroll
+      for (int k = 0; k < 3; k++) Rt.p[k] = buf[9 + k][e];
+      cfg = __float_as_uint(buf[12][e]);
+      p = __float_as_int(buf[13][e]);
       const DevPair pr = img.pairs[p];
-      DensePair D;
-      dense_frames(img, obb, ld, cfg, pr, D);
+      const float4 *ca = img.cobb + MPB_COBB_WORDS * pr.a, *cb = img.cobb + MPB_COBB_WORDS * pr.b;
       // relative pose of the two OBJECT frames for the narrowphase: Xa (A_obb^-1 B_obb) Xb^-1
-      const Xf Xa = xf_rows(__ldg(D.ca + 5), __ldg(D.ca + 6), __ldg(D.ca + 7));
-      const Xf Xbi = xf_rows(__ldg(D.cb + 8), __ldg(D.cb + 9), __ldg(D.cb + 10));
-      rel = xf_mul(xf_mul(Xa, D.Rt), Xbi);
+      const Xf Xa = xf_rows(__ldg(ca + 5), __ldg(ca + 6), __ldg(ca + 7));
+      const Xf Xbi = xf_rows(__ldg(cb + 8), __ldg(cb + 9), __ldg(cb + 10));
+      rel = xf_mul(xf_mul(Xa, Rt), Xbi);
       keep = true;
       const int bin = pr.bin_dyn & 0xffff;
       if (presolve && bin != img.expand_bin && bin != img.expand2_bin &&
@@ -1115,7 +1091,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
       }
       wused += cntk;
     }
-    cnt[c] -= nb;
+    cnt -= nb;
     __syncwarp();
   };
 
@@ -1125,8 +1101,9 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
   for (unsigned e = e_first; e < total_r; e += e_stride) {
     // ---- phase 1: frames, SAT, inscribed balls
     bool keep = false;
-    int p = 0, cls = MPB_D2_TYPES - 1;
+    int p = 0;
     unsigned cfg = 0;
+    Xf Rt;
     const uint2 ent = ent_next;
     ent_next = make_uint2(0xffffffffu, 0u);
     if (e + e_stride < total) ent_next = sq[e + e_stride];
@@ -1134,41 +1111,58 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
       cfg = ent.x;
       p = __ldg(&img.cullm[ent.y].x);
       const DevPair pr = img.pairs[p];
-      DensePair D;
-      dense_frames(img, obb, ld, cfg, pr, D);
-      const float ah[3] = {D.ha.x, D.ha.y, D.ha.z}, bh[3] = {D.hb.x, D.hb.y, D.hb.z};
-      keep = !obb_disjoint(D.Rt.r, D.Rt.p, ah, bh);
-      if (keep && D.ha.w > 0.f && D.hb.w > 0.f) {
+      // cull records (MPB_COBB_WORDS float4 per object): [0..2] OBB frame (world frame if the object is fixed,
+      // owner-joint frame if it moves), [3] half extents + inscribed radius, [4] inscribed-ball centre in the OBB frame
+      // + moving slot, [5..7] OBB frame in the object frame, [8..10] its inverse
+      const float4 *ca = img.cobb + MPB_COBB_WORDS * pr.a, *cb = img.cobb + MPB_COBB_WORDS * pr.b;
+      const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
+      const int da = __float_as_int(ia.w), db = __float_as_int(ib.w);
+      // moving: this configuration's row of the OBB table (quaternion, translation); fixed: the record's world frame
+      Xf Ea, Eb;
+      if (da >= 0) { const float4 *pa = obb + ((size_t)da * ld + cfg) * 2; Ea = quat_rows(pa[0], pa[1]); }
+      else Ea = xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2));
+      if (db >= 0) { const float4 *pb = obb + ((size_t)db * ld + cfg) * 2; Eb = quat_rows(pb[0], pb[1]); }
+      else Eb = xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
+      // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)  ==  (OBB frame A)^-1 (OBB frame B)
+      const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
+#pragma unroll
+      for (int rr = 0; rr < 3; rr++) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) Rt.r[3 * rr + c] = fmaf(Ea.r[rr], Eb.r[c], fmaf(Ea.r[3 + rr], Eb.r[3 + c], Ea.r[6 + rr] * Eb.r[6 + c]));
+        Rt.p[rr] = fmaf(Ea.r[rr], d0, fmaf(Ea.r[3 + rr], d1, Ea.r[6 + rr] * d2));
+      }
+      const float ah[3] = {ha.x, ha.y, ha.z}, bh[3] = {hb.x, hb.y, hb.z};
+      keep = !obb_disjoint(Rt.r, Rt.p, ah, bh);
+      if (keep && ha.w > 0.f && hb.w > 0.f) {
         // sufficient test: balls inscribed in the two shapes overlap -> the pair collides, no narrowphase needed
-        const float ib3[3] = {D.ib.x, D.ib.y, D.ib.z};
+        const float ib3[3] = {ib.x, ib.y, ib.z};
         float icb[3];
-        xf_point(D.Rt, ib3, icb);  // B's ball centre in A's OBB frame
-        const float e0 = D.ia.x - icb[0], e1 = D.ia.y - icb[1], e2 = D.ia.z - icb[2];
-        const float rs = 0.999f * (D.ha.w + D.hb.w);
+        xf_point(Rt, ib3, icb);  // B's ball centre in A's OBB frame
+        const float e0 = ia.x - icb[0], e1 = ia.y - icb[1], e2 = ia.z - icb[2];
+        const float rs = 0.999f * (ha.w + hb.w);
         if (fmaf(e0, e0, fmaf(e1, e1, e2 * e2)) < rs * rs) {
           keep = false;
           report_hit(out, cfg, p);
         }
       }
-      if (keep) {
-        const int tb = img.objs[pr.b].type;
-        cls = (tb >= MPB_GEOM_SPHERE && tb <= MPB_GEOM_CYLINDER) ? tb - MPB_GEOM_SPHERE : MPB_D2_TYPES - 1;
-      }
     }
-    // ---- kept survivors -> the buffer of their partner type; a buffer that reaches 32 entries runs phase 2
+    // ---- kept survivors -> the warp's buffer; 32 entries run phase 2
+    const unsigned m = __ballot_sync(FULL, keep);
+    if (!m) continue;
+    if (keep) {
+      const int e2 = cnt + __popc(m & ((1u << lane) - 1u));
 #pragma unroll
-    for (int c = 0; c < MPB_D2_TYPES; c++) {
-      const unsigned m = __ballot_sync(FULL, keep && cls == c);
-      if (!m) continue;
-      if (keep && cls == c) s_buf[warp][c][cnt[c] + __popc(m & ((1u << lane) - 1u))] = make_uint2(cfg, (unsigned)p);
-      cnt[c] += __popc(m);
-      __syncwarp();
-      if (cnt[c] >= 32) phase2(c, 32);
+      for (int k = 0; k < 9; k++) buf[k][e2] = Rt.r[k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) buf[9 + k][e2] = Rt.p[k];
+      buf[12][e2] = __uint_as_float(cfg);
+      buf[13][e2] = __int_as_float(p);
     }
+    cnt += __popc(m);
+    __syncwarp();
+    if (cnt >= 32) phase2(32);
   }
-#pragma unroll
-  for (int c = 0; c < MPB_D2_TYPES; c++)
-    while (cnt[c] > 0) phase2(c, min(cnt[c], 32));
+  while (cnt > 0) phase2(min(cnt, 32));
   // invalidate the unused tail of the last chunk
   if (wbase != 0xffffffffu) {
     for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
