@@ -839,8 +839,31 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
   std::vector<int> mesh_root(std::max(d->n_meshes, 0), -1), oct_root(std::max(d->n_octrees, 0), -1);
   auto finish_tree = [&](std::vector<HostPrim> &hp) -> int {
     if (hp.empty()) return -1;
-    std::vector<DevBvhNode> local;
-    build_bvh(hp, 0, (int)hp.size(), local);
+    std::vector<DevBvhNode> built;
+    build_bvh(hp, 0, (int)hp.size(), built);
+    // Breadth-first re-layout with siblings adjacent at an even index (right == left + 1, 64-byte aligned pair): a
+    // traversal that keeps "first child of a passing inner node" on its stack reads both children with one access
+    // (expand_lane_kernel).  Slot 1 pads the root to a pair; nothing points at it.
+    std::vector<DevBvhNode> local(2);
+    local[0] = built[0];
+    local[1] = DevBvhNode{};
+    local[1].left = ~0; local[1].right = 0;
+    for (int a = 0; a < 3; a++) { local[1].c[a] = 0.f; local[1].h[a] = -1.f; }
+    {
+      std::vector<std::pair<int, int>> fifo{{0, 0}};
+      for (size_t qi = 0; qi < fifo.size(); qi++) {
+        const int was = fifo[qi].first, now = fifo[qi].second;
+        if (built[was].left < 0) continue;
+        const int at = (int)local.size();
+        local.push_back(built[built[was].left]);
+        local.push_back(built[built[was].right]);
+        fifo.push_back({built[was].left, at});
+        fifo.push_back({built[was].right, at + 1});
+        local[now].left = at;
+        local[now].right = at + 1;
+      }
+    }
+    if (nodes.size() & 1) nodes.push_back(local[1]);
     const int node0 = (int)nodes.size(), prim0 = (int)(prims.size() / 3);
     for (DevBvhNode nd : local) {
       if (nd.left >= 0) { nd.left += node0; nd.right += node0; }

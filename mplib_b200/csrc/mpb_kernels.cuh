@@ -2124,9 +2124,12 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
 
 // Lane per item: the throughput variant of expand_kernel for passes with many items (a collide call over 10^5+
 // configurations).  A lane walks its own item's tree depth-first with a private stack in shared memory ([depth][thread],
-// conflict-free), one node per trip: pop a node whose bounds already passed and fetch + test its two children (two
-// independent loads in flight; the survivors are pushed, the one nearer to the shape's inscribed ball on top, so an item
-// that collides meets its decisive leaves first).  LEAVES are not tested by the lane that finds them: their
+// conflict-free), one sibling pair per trip: the stack holds the first-child index of inner nodes whose bounds already
+// passed; siblings are adjacent in the pool (host re-layout in mpb_scene_create), so one dependent 64-byte access
+// brings both children's boxes (the first version popped a node, read it, then read its children: two dependent accesses
+// per trip, and leaves cost a trip of their own).  Passing inner children are pushed, the one nearer to the shape's
+// inscribed ball on top, so an item that collides meets its decisive leaves first; passing leaf children hand their
+// primitives over in the same trip.  LEAVES are not tested by the lane that finds them: their
 // primitives go to a per-warp queue and are tested 32 at a time by the whole warp (exact OBB test, inscribed-ball
 // shortcut, emission of the leaf item), each lane reading the owner's item record from shared memory.  The first version
 // tested leaves in place and ran its leaf code -- 60 % of its instructions -- on two lanes of 32
@@ -2255,6 +2258,7 @@ __global__ void __launch_bounds__(128, MPB_EXPL_MINB) expand_lane_kernel(SceneIm
   float ca[3] = {0.f, 0.f, 0.f}, bh[3] = {0.f, 0.f, 0.f}, cin[3] = {0.f, 0.f, 0.f};
   for (;;) {
     if (busy && S.hitflag[tid]) { busy = false; sp = 0; }  // a leaf of this lane's item was an immediate hit
+    int n_leaf = 0, leaf_first = 0;
     // ---- refill: idle lanes take the next items of the bin (one ticket per warp and refill; the refill block is long, so
     // it runs only when a quarter of the warp is idle, or nobody has work)
     const unsigned need = __ballot_sync(FULL, !busy);
@@ -2301,42 +2305,48 @@ __global__ void __launch_bounds__(128, MPB_EXPL_MINB) expand_lane_kernel(SceneIm
             S.item[30][tid] = A.rin * A.rin;
             S.meta[0][tid] = cfg; S.meta[1][tid] = p; S.meta[2][tid] = B.vcnt; S.meta[3][tid] = img.pair_bin2[p];
             S.hitflag[tid] = 0;
-            stack[0] = B.voff;
-            sp = 1;
-            busy = true;
+            if (root.left >= 0) {
+              stack[0] = root.left;  // the stack holds sibling pairs: index of the first child of a passing inner node
+              sp = 1;
+              busy = true;
+            } else {  // one-leaf tree: its primitives go to the queue in this trip; the record stays until the next refill
+              leaf_first = ~root.left;
+              n_leaf = root.right;
+            }
           }
         }
       }
       __syncwarp();
     }
-    if (__ballot_sync(FULL, busy) == 0) {
+    if (__ballot_sync(FULL, busy || n_leaf > 0) == 0) {
       while (qn > 0) { const int nb = min(qn, 32); exp_leaf_batch(img, wq, out, S, queue + qn - nb, nb, lane, smem_bins); qn -= nb; }
       if (drained) break;
       continue;
     }
-    // ---- one node of every busy lane's traversal
-    int n_leaf = 0, leaf_first = 0;
+    // ---- one sibling pair of every busy lane's traversal (siblings are adjacent: one 64-byte access reads both boxes)
     if (busy) {
-      const int node = stack[(sp - 1) * 128];
+      const int pair = stack[(sp - 1) * 128];
       sp--;
-      const DevBvhNode nd = img.nodes[node];
-      if (nd.left >= 0) {
-        const DevBvhNode nl = img.nodes[nd.left], nr = img.nodes[nd.right];
-        const bool pl = exp_box_pass(nl, ca, bh), prt = exp_box_pass(nr, ca, bh);
-        if (sp + 2 > MPB_EXPL_DEPTH) {  // cannot happen for a tree of depth < MPB_EXPL_DEPTH; conservative if it does
-          drop_sum++;
-          S.hitflag[tid] = 1;
-          report_hit(out, (unsigned)S.meta[0][tid], S.meta[1][tid]);
-        } else {
-          const bool left_first = exp_node_dist2(nl, cin) <= exp_node_dist2(nr, cin);
-          const int c_far = left_first ? nd.right : nd.left, c_near = left_first ? nd.left : nd.right;
-          const bool p_far = left_first ? prt : pl, p_near = left_first ? pl : prt;
-          if (p_far) { stack[sp * 128] = c_far; sp++; }
-          if (p_near) { stack[sp * 128] = c_near; sp++; }
-        }
+      const DevBvhNode nl = img.nodes[pair], nr = img.nodes[pair + 1];
+      const bool pl = exp_box_pass(nl, ca, bh), prt = exp_box_pass(nr, ca, bh);
+      const bool il = pl && nl.left >= 0, ir = prt && nr.left >= 0;   // inner children to descend into
+      const bool ll = pl && nl.left < 0, lr = prt && nr.left < 0;     // leaf children: primitives to the queue
+      if (sp + 2 > MPB_EXPL_DEPTH) {  // cannot happen for a tree of depth < MPB_EXPL_DEPTH; conservative if it does
+        drop_sum++;
+        S.hitflag[tid] = 1;
+        report_hit(out, (unsigned)S.meta[0][tid], S.meta[1][tid]);
       } else {
-        leaf_first = ~nd.left;
-        n_leaf = nd.right;
+        const bool left_first = exp_node_dist2(nl, cin) <= exp_node_dist2(nr, cin);
+        const int c_far = left_first ? nr.left : nl.left, c_near = left_first ? nl.left : nr.left;
+        const bool p_far = left_first ? ir : il, p_near = left_first ? il : ir;
+        if (p_far) { stack[sp * 128] = c_far; sp++; }
+        if (p_near) { stack[sp * 128] = c_near; sp++; }
+        // sibling leaves cover adjacent primitive ranges (build_bvh splits [first, mid) | [mid, end)): one range when both pass
+        if (ll) { leaf_first = ~nl.left; n_leaf = nl.right; }
+        if (lr) {
+          if (!ll) leaf_first = ~nr.left;
+          n_leaf += nr.right;
+        }
       }
       if (sp == 0) busy = false;  // its queued leaves are tested before the lane's record is replaced
     }
@@ -2349,7 +2359,7 @@ __global__ void __launch_bounds__(128, MPB_EXPL_MINB) expand_lane_kernel(SceneIm
     }
     const int tot = (int)__shfl_sync(FULL, incl, 31);
     if (tot) {
-      if (qn + tot > MPB_EXPL_QCAP) {  // make room first (a trip adds at most 32 x leaf size entries)
+      if (qn + tot > MPB_EXPL_QCAP) {  // make room first (a trip adds at most 32 lanes x 2 leaves x 2 primitives = MPB_EXPL_QCAP entries)
         while (qn > 0) { const int nb = min(qn, 32); exp_leaf_batch(img, wq, out, S, queue + qn - nb, nb, lane, smem_bins); qn -= nb; }
       }
       int pos = qn + (int)incl - n_leaf;
