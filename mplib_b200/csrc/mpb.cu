@@ -697,6 +697,7 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
       if (ct_on && n_pairs <= 256 && s->h_runs.size() <= 64 && s->img.n_dyn <= 30) { fill(s->ct_small.q, s->ct_small.runs); s->cull_tier = 1; }
     }
   }
+  if (bins.size() >= 0xffffu || bins2.size() >= 0xffffu) return fail(MPB_ERR_CAPACITY, "more than 65534 geometry classes among the pairs");  // 16-bit bin keys
   s->grid_dirty = true;
   s->img.n_pairs = n_pairs;
   s->img.n_bins = (int)bins.size();
@@ -1130,7 +1131,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   cudaSetDevice(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
   void *ptrs[] = {s->d_joints, s->d_objs, s->d_pairs, s->d_verts, s->d_linkL, s->d_linkJoint, s->d_q[0], s->d_q[1], s->d_verdict[0],
-                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.stf, s->wq.bin_count, s->wq.totals};
+                  s->d_verdict[1], s->d_pairbits[0], s->d_pairbits[1], s->d_poses, s->d_dynlist, s->d_nodes, s->d_prims, s->d_pair_bin2, s->d_pose, s->d_obb, s->d_sq, s->d_cobb, s->d_cullc, s->d_cullq, s->d_cullm, s->d_runs, s->wq.rec[0], s->wq.bin_count, s->wq.totals};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   harvest(s, true);  // device-pointer calls may still be in flight on caller streams
@@ -1364,7 +1365,7 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   // rounds alternate on one scene; re-allocating GBs of queues between them would dominate small calls)
   if (int grc = ensure_grid(s)) return grc;
   const size_t P = (size_t)std::max(s->img.n_pairs, 1);
-  if (chunk <= s->chunk && s->wq.itf && P <= s->work_P && (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1) <= s->bins_cap) return MPB_OK;
+  if (chunk <= s->chunk && s->wq.rec[0] && P <= s->work_P && (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1) <= s->bins_cap) return MPB_OK;
   if (int hrc = harvest(s, true)) return hrc;  // calls in flight (device-pointer mode) still use the old buffers
   CU(sync_scene(s));
   chunk = std::max(chunk, s->chunk);
@@ -1373,7 +1374,7 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   // plus one partly used reservation per warp of dense_kernel / expand_kernel
   size_t cap = std::min((size_t)chunk * P * 2 + (size_t)s->num_sms * 8 * 4 * MPB_STAGE_CHUNK, kMaxItems);
   cap = std::max<size_t>(cap, 4096);
-  if (s->wq.stf) { cudaFree(s->wq.stf); s->wq.stf = nullptr; s->wq.itf = nullptr; }
+  if (s->wq.rec[0]) { cudaFree(s->wq.rec[0]); s->wq.rec[0] = s->wq.rec[1] = nullptr; }
   if (s->d_pose) { cudaFree(s->d_pose); s->d_pose = nullptr; }
   if (s->d_sq) { cudaFree(s->d_sq); s->d_sq = nullptr; }
   s->pose_ld = (size_t)(chunk + 31) / 32 * 32;
@@ -1385,15 +1386,11 @@ static int prepare_work(mpb_scene *s, long long chunk) {
   const size_t sq_cap = std::max<size_t>(std::min((size_t)chunk * P + (size_t)s->num_sms * 64 * MPB_SQ_CHUNK_GRID, kMaxSurvivors), 4096);
   CU(cudaMalloc((void **)&s->d_sq, sq_cap * sizeof(uint2)));
   s->sq_cap = (unsigned)sq_cap;
-  // one slab: staging [12 f + cfg + pair][cap], then binned [12 f + cfg + pair][cap]
-  CU(cudaMalloc((void **)&s->wq.stf, cap * 30 * sizeof(float)));
-  s->wq.scfg = reinterpret_cast<int *>(s->wq.stf + cap * 12);
-  s->wq.spair = s->wq.scfg + cap;
-  s->wq.saux = s->wq.spair + cap;
-  s->wq.itf = reinterpret_cast<float *>(s->wq.saux + cap);
-  s->wq.icfg = reinterpret_cast<int *>(s->wq.itf + cap * 12);
-  s->wq.ipair = s->wq.icfg + cap;
-  s->wq.iaux = s->wq.ipair + cap;
+  // one slab: item records of the two rounds (64 bytes each), binned order, bin keys
+  CU(cudaMalloc((void **)&s->wq.rec[0], cap * (2 * 64 + sizeof(unsigned) + sizeof(unsigned short))));
+  s->wq.rec[1] = s->wq.rec[0] + cap * 4;
+  s->wq.order = reinterpret_cast<unsigned *>(s->wq.rec[1] + cap * 4);
+  s->wq.skey = reinterpret_cast<unsigned short *>(s->wq.order + cap);
   s->wq.cap = (unsigned)cap;
   const size_t nb = (size_t)std::max(std::max(s->img.n_bins, s->img.n_bins2), 1);
   if (nb > s->bins_cap || !s->wq.bin_count) {

@@ -133,10 +133,12 @@ __global__ void __launch_bounds__(256) distance_kernel(SceneImg img, WorkQ wq, u
       bool busy = my < end;
       const unsigned src = busy ? my : first;  // idle lanes shadow a real item so the hull scans stay uniform
       float R[9];
-#pragma unroll
-      for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + src];
-      const V3 t = v3(wq.itf[(size_t)9 * wq.cap + src], wq.itf[(size_t)10 * wq.cap + src], wq.itf[(size_t)11 * wq.cap + src]);
-      const int cfg = wq.icfg[src], p = wq.ipair[src];
+      const float4 *rc = item_rec(wq, 0, src);
+      float t3[3];
+      int cfg, p, aux_;
+      item_pose(rc, R, t3);
+      item_ids(rc, cfg, p, aux_);
+      const V3 t = v3(t3[0], t3[1], t3[2]);
       const DevPair pr = img.pairs[p];
       const DevObject &OA = img.objs[pr.a];
       const DevObject &OB = img.objs[pr.b];
@@ -303,17 +305,18 @@ __global__ void __launch_bounds__(128) distance_expand_kernel(SceneImg img, Work
     if (lane == 0) it = atomicAdd(&wq.totals[5], 1u);
     it = first + __shfl_sync(FULL, it, 0);
     if (it >= end) break;
-    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    const float4 *rc = item_rec(wq, 0, it);
+    int cfg, p, aux_;
+    item_ids(rc, cfg, p, aux_);
     float ub = FLT_MAX;
     if (!best_bound(best, cfg, p, ub)) continue;  // a pair of lower index already intersects: this one cannot change the result
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // the shape
     const DevObject &B = img.objs[pr.b];  // the BVH object
     if (B.voff < 0) continue;             // empty octree: no leaf, no distance
-    float R[9];
-#pragma unroll
-    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
-    const V3 t = v3(wq.itf[(size_t)9 * wq.cap + it], wq.itf[(size_t)10 * wq.cap + it], wq.itf[(size_t)11 * wq.cap + it]);
+    float R[9], t3[3];
+    item_pose(rc, R, t3);
+    const V3 t = v3(t3[0], t3[1], t3[2]);
     // the shape seen from the object's frame:  x_B = R^T (x_A - t)
     const V3 cs = rot_t(R, v3(A.bc[0], A.bc[1], A.bc[2]) - t);   // bounding-sphere centre
     const V3 co = rot_t(R, v3(A.oc[0], A.oc[1], A.oc[2]) - t);   // OBB centre
@@ -418,17 +421,18 @@ __global__ void __launch_bounds__(128) distance_expand2_kernel(SceneImg img, Wor
     if (lane == 0) it = atomicAdd(&wq.totals[7], 1u);
     it = first + __shfl_sync(FULL, it, 0);
     if (it >= end) break;
-    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    const float4 *rc = item_rec(wq, 0, it);
+    int cfg, p, aux_;
+    item_ids(rc, cfg, p, aux_);
     float ub = FLT_MAX;
     if (!best_bound(best, cfg, p, ub)) continue;
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];
     const DevObject &B = img.objs[pr.b];
     if (B.voff < 0) continue;
-    float R[9];  // B in A
-#pragma unroll
-    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
-    const V3 t = v3(wq.itf[(size_t)9 * wq.cap + it], wq.itf[(size_t)10 * wq.cap + it], wq.itf[(size_t)11 * wq.cap + it]);
+    float R[9], t3[3];  // B in A
+    item_pose(rc, R, t3);
+    const V3 t = v3(t3[0], t3[1], t3[2]);
     const int leaf_b = B.vcnt;
     DevShape SA, SB;
     SA.type = MPB_GEOM_TRI; SA.voff = 0; SA.vcnt = 0; SA.cell = -1; SA.p0 = SA.p1 = SA.p2 = 0.f;

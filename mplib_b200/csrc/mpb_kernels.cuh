@@ -59,11 +59,13 @@ struct SceneImg {
   int w_sphere, w_joint;  // sphere-table word offsets: [n_dyn][3] sphere centres, then [n_jslots][12] branch joints
 };
 
+#define MPB_KEY_HOLE 0xffffu
 struct WorkQ {
-  float *stf;            // staging: [12][cap] relative transform B in A (SoA)
-  int *scfg, *spair, *saux;     // staging: [cap]
-  float *itf;            // binned:  [12][cap]
-  int *icfg, *ipair, *iaux;     // binned:  [cap]   aux = leaf primitive index (second round), else 0
+  float4 *rec[2];        // item records, 64 bytes each, in the order they were produced: [0] first round (dense cull),
+                         // [1] leaf items of the second round (BVH expansion).  R (9), t (3): B in A; cfg, pair, aux
+                         // (leaf primitive index in the second round, else 0)
+  unsigned short *skey;  // [cap] bin of the record in slot s of the round being binned; MPB_KEY_HOLE = unused chunk tail
+  unsigned int *order;   // [cap] binned order: order[k] = slot of the k-th item (bins are ranges of k)
   unsigned int *bin_count;   // [n_bins]
   unsigned int *bin_cursor;  // [n_bins]
   unsigned int *bin_start;   // [n_bins+1]
@@ -72,6 +74,30 @@ struct WorkQ {
   unsigned long long *counters;  // [0]=items after cull [1]=support evaluations [2]=capped items
   unsigned int cap;
 };
+
+// Items are SORTED BY INDEX, not moved: the producer writes one 64-byte record per item (full sectors) and a 2-byte bin
+// key; scatter_kernel ranks the keys and writes order[]; the consumers read order[k] and gather the record (two full
+// sectors).  The first layout (structure of arrays, staged, then copied to its binned position by scatter_kernel) moved
+// 112 bytes per item through the scatter and made it 11 % of a C3 pass.
+__device__ __forceinline__ void item_store(const WorkQ &wq, int round, unsigned slot, const float *R, const float *t, int cfg, int pair, int aux, int bin) {
+  float4 *r = wq.rec[round] + 4 * (size_t)slot;
+  r[0] = make_float4(R[0], R[1], R[2], R[3]);
+  r[1] = make_float4(R[4], R[5], R[6], R[7]);
+  r[2] = make_float4(R[8], t[0], t[1], t[2]);
+  r[3] = make_float4(__int_as_float(cfg), __int_as_float(pair), __int_as_float(aux), 0.f);
+  wq.skey[slot] = (unsigned short)bin;
+}
+// record of the k-th binned item
+__device__ __forceinline__ const float4 *item_rec(const WorkQ &wq, int round, unsigned k) { return wq.rec[round] + 4 * (size_t)wq.order[k]; }
+__device__ __forceinline__ void item_ids(const float4 *r, int &cfg, int &pair, int &aux) {
+  const float4 d = __ldg(r + 3);
+  cfg = __float_as_int(d.x); pair = __float_as_int(d.y); aux = __float_as_int(d.z);
+}
+__device__ __forceinline__ void item_pose(const float4 *r, float *R, float *t) {
+  const float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2);
+  R[0] = a.x; R[1] = a.y; R[2] = a.z; R[3] = a.w; R[4] = b.x; R[5] = b.y; R[6] = b.z; R[7] = b.w; R[8] = c.x;
+  t[0] = c.y; t[1] = c.z; t[2] = c.w;
+}
 
 // Where the kernels of one pass report a colliding (configuration, pair): the verdict word and, optionally, the dense
 // pair mask of the pass.  (The sparse hit list of mpb_collide_batch_hits is compacted out of the mask after the pass by
@@ -967,7 +993,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
     if (wused + cntk > MPB_STAGE_CHUNK) {
       if (wbase != 0xffffffffu)
         for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
-          if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;  // unused tail of the old chunk
+          if (wbase + k < wq.cap) wq.skey[wbase + k] = MPB_KEY_HOLE;  // unused tail of the old chunk
       unsigned nb = 0;
       if (lane == 0) nb = atomicAdd(&wq.totals[0], (unsigned)MPB_STAGE_CHUNK);
       wbase = __shfl_sync(FULL, nb, 0);
@@ -977,13 +1003,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
       const unsigned slot = wbase + wused + __popc(km & ((1u << lane) - 1u));
       const int bin = img.pairs[p].bin_dyn & 0xffff;
       if (slot < wq.cap) {
-#pragma unroll
-        for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = rel.r[k2];
-#pragma unroll
-        for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = rel.p[k2];
-        wq.scfg[slot] = (int)cfg;
-        wq.spair[slot] = p;
-        wq.saux[slot] = 0;
+        item_store(wq, 0, slot, rel.r, rel.p, (int)cfg, p, 0, bin);
       }
       if (slot < wq.cap) {
         if (smem_bins) atomicAdd(&s_bins[bin], 1u);
@@ -995,7 +1015,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
   // invalidate the unused tail of the last chunk
   if (wbase != 0xffffffffu) {
     for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
-      if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;
+      if (wbase + k < wq.cap) wq.skey[wbase + k] = MPB_KEY_HOLE;
   }
   __syncthreads();
   if (smem_bins)
@@ -1068,7 +1088,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
       if (wused + cntk > MPB_STAGE_CHUNK) {
         if (wbase != 0xffffffffu)
           for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
-            if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;  // unused tail of the old chunk
+            if (wbase + k < wq.cap) wq.skey[wbase + k] = MPB_KEY_HOLE;  // unused tail of the old chunk
         unsigned nbs = 0;
         if (lane == 0) nbs = atomicAdd(&wq.totals[0], (unsigned)MPB_STAGE_CHUNK);
         wbase = __shfl_sync(FULL, nbs, 0);
@@ -1077,14 +1097,8 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
       if (keep) {
         const unsigned slot = wbase + wused + __popc(km & ((1u << lane) - 1u));
         if (slot < wq.cap) {
-#pragma unroll
-          for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = rel.r[k2];
-#pragma unroll
-          for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = rel.p[k2];
-          wq.scfg[slot] = (int)cfg;
-          wq.spair[slot] = p;
-          wq.saux[slot] = 0;
           const int bin = img.pairs[p].bin_dyn & 0xffff;
+          item_store(wq, 0, slot, rel.r, rel.p, (int)cfg, p, 0, bin);
           if (smem_bins) atomicAdd(&s_bins[bin], 1u);
           else atomicAdd(&wq.bin_count[bin], 1u);
         }
@@ -1166,7 +1180,7 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
   // invalidate the unused tail of the last chunk
   if (wbase != 0xffffffffu) {
     for (unsigned k = wused + lane; k < MPB_STAGE_CHUNK; k += 32)
-      if (wbase + k < wq.cap) wq.scfg[wbase + k] = -1;
+      if (wbase + k < wq.cap) wq.skey[wbase + k] = MPB_KEY_HOLE;
   }
   __syncthreads();
   if (smem_bins)
@@ -1242,12 +1256,12 @@ __global__ void scan_bins_kernel(WorkQ wq, int n_bins, int skip_bin, int skip_bi
   }
 }
 
-// Staging queue -> binned queue.  A block ranks its items per bin in shared memory (the shared atomic returns the
-// rank), reserves one range per bin per trip in the global cursors, then moves the items.  The kernel is bound by its
-// dependent loads and leaves most issue slots idle, so the sufficient-hit test of the SECOND round (leaf items: inner balls
-// of the shape against a voxel box) runs here (PRESOLVE): an item it settles sets its result bits and is not moved;
-// bin_cursor[b] ends as the number of items bin b really holds.  (First-round items are tested in dense_kernel, before
-// they are staged at all.)
+// Produced order -> binned order.  A block ranks the bin keys of its slots in shared memory (the shared atomic returns the
+// rank), reserves one range per bin per trip in the global cursors, then writes order[position] = slot: six bytes per
+// item.  The sufficient-hit test of the SECOND round (leaf items: inner balls of the shape against a voxel box) runs here
+// (PRESOLVE), on the record read in produced order: an item it settles sets its result bits and gets no position;
+// bin_cursor[b] ends as the number of items bin b really holds.  (First-round items are tested in the dense cull, before
+// they are recorded at all.)
 template <bool PRESOLVE>
 __global__ void __launch_bounds__(PRESOLVE ? 512 : 1024, 2) scatter_kernel(SceneImg img, WorkQ wq, int round, HitOut out) {
   __shared__ unsigned s_cnt[MPB_SMEM_BINS], s_base[MPB_SMEM_BINS];
@@ -1257,17 +1271,19 @@ __global__ void __launch_bounds__(PRESOLVE ? 512 : 1024, 2) scatter_kernel(Scene
   const unsigned n_round = (n + blockDim.x - 1) / blockDim.x * blockDim.x;
   const unsigned lane = threadIdx.x & 31;
   for (unsigned s = blockIdx.x * blockDim.x + threadIdx.x; s < n_round; s += gridDim.x * blockDim.x) {
-    bool valid = s < n && wq.scfg[s] >= 0;  // holes are the unused tails of warp chunks
-    const int p = valid ? wq.spair[s] : 0;
-    int bin = valid ? (round == 0 ? (img.pairs[p].bin_dyn & 0xffff) : img.pair_bin2[p]) : -1;
+    int bin = s < n ? (int)wq.skey[s] : (int)MPB_KEY_HOLE;  // holes are the unused tails of warp chunks
+    bool valid = bin != (int)MPB_KEY_HOLE;
+    if (!valid) bin = -1;
     if constexpr (PRESOLVE) {
       if (valid && !(round == 0 && (bin == img.expand_bin || bin == img.expand2_bin))) {
-        float f[12];
-#pragma unroll
-        for (int k = 0; k < 12; k++) f[k] = wq.stf[(size_t)k * wq.cap + s];
+        const float4 *r = wq.rec[round] + 4 * (size_t)s;
+        float R[9], t3[3];
+        int cfg, p, aux;
+        item_pose(r, R, t3);
+        item_ids(r, cfg, p, aux);
         const DevPair pr = img.pairs[p];
-        if (sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], f, v3(f[9], f[10], f[11]), round == 0 ? -1 : wq.saux[s])) {
-          report_hit(out, (unsigned)wq.scfg[s], p);
+        if (sufficient_hit(img, img.objs[pr.a], img.objs[pr.b], R, v3(t3[0], t3[1], t3[2]), round == 0 ? -1 : aux)) {
+          report_hit(out, (unsigned)cfg, p);
           valid = false;
           bin = -1;
         }
@@ -1294,13 +1310,7 @@ __global__ void __launch_bounds__(PRESOLVE ? 512 : 1024, 2) scatter_kernel(Scene
       base = __shfl_sync(0xffffffffu, base, leader);
       if (valid) dst = wq.bin_start[bin] + base + __popc(grp & ((1u << lane) - 1u));
     }
-    if (valid) {  // the payload is (re)read here: holding it across the ranking would cost the lean variant its occupancy
-#pragma unroll
-      for (int k = 0; k < 12; k++) wq.itf[(size_t)k * wq.cap + dst] = wq.stf[(size_t)k * wq.cap + s];
-      wq.icfg[dst] = wq.scfg[s];
-      wq.ipair[dst] = p;
-      wq.iaux[dst] = wq.saux[s];
-    }
+    if (valid) wq.order[dst] = s;
   }
 }
 
@@ -1495,7 +1505,9 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow_kernel(SceneImg i
     int cfg = 0, p = 0, phase = 1, iters = 0;
     {
       // shapes are uniform over the bin: read them once from the first item of the slice
-      const DevPair pr0 = img.pairs[wq.ipair[first]];
+      int c0_, p0_, a0_;
+      item_ids(item_rec(wq, round, first), c0_, p0_, a0_);
+      const DevPair pr0 = img.pairs[p0_];
       const DevObject &OA = img.objs[pr0.a];
       const DevObject &OB = img.objs[pr0.b];
       A = shape_of(OA); B = shape_of(OB);
@@ -1512,11 +1524,12 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow_kernel(SceneImg i
         const unsigned my = next + __popc(need & ((1u << lane) - 1u));
         if (!busy && my < end) {
           bool busy_ok = true;
-#pragma unroll
-          for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + my];
-          t = v3(wq.itf[(size_t)9 * wq.cap + my], wq.itf[(size_t)10 * wq.cap + my], wq.itf[(size_t)11 * wq.cap + my]);
-          cfg = wq.icfg[my];
-          p = wq.ipair[my];
+          const float4 *rc = item_rec(wq, round, my);
+          float t3[3];
+          int aux;
+          item_pose(rc, R, t3);
+          item_ids(rc, cfg, p, aux);
+          t = v3(t3[0], t3[1], t3[2]);
           const DevPair pr = img.pairs[p];
           const DevObject &OA = img.objs[pr.a];
           const DevObject &OB = img.objs[pr.b];
@@ -1525,7 +1538,7 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow_kernel(SceneImg i
           cA = v3(OA.ctr[0], OA.ctr[1], OA.ctr[2]);
           cBl = v3(OB.ctr[0], OB.ctr[1], OB.ctr[2]);
           if (round == 1) {  // [upstream] centerTriangle = centroid; voxel Box centre = its pose
-            B.voff = wq.iaux[my];
+            B.voff = aux;
             const float4 a = __ldg(img.prims + 3 * B.voff);
             if (B.type == MPB_GEOM_TRI) {
               const float4 b = __ldg(img.prims + 3 * B.voff + 1), c = __ldg(img.prims + 3 * B.voff + 2);
@@ -1683,11 +1696,12 @@ __device__ __forceinline__ V3 mink_support(const DevShape &A, const DevShape &B,
 // item `my` of the binned queue -> lane state; false: nothing to do (already known to collide)
 __device__ __forceinline__ bool mpr_fetch(const SceneImg &img, const WorkQ &wq, const HitOut &out, unsigned my, int round, DevShape &A, DevShape &B,
                                           MprItem &I, V3 &cA, V3 &cBl, int2 *objs = nullptr) {
-#pragma unroll
-  for (int k = 0; k < 9; k++) I.R[k] = wq.itf[(size_t)k * wq.cap + my];
-  I.t = v3(wq.itf[(size_t)9 * wq.cap + my], wq.itf[(size_t)10 * wq.cap + my], wq.itf[(size_t)11 * wq.cap + my]);
-  I.cfg = wq.icfg[my];
-  I.p = wq.ipair[my];
+  const float4 *rc = item_rec(wq, round, my);
+  float t3[3];
+  int aux;
+  item_pose(rc, I.R, t3);
+  item_ids(rc, I.cfg, I.p, aux);
+  I.t = v3(t3[0], t3[1], t3[2]);
   const DevPair pr = img.pairs[I.p];
   if (objs) *objs = make_int2(pr.a, pr.b);
   const DevObject &OA = img.objs[pr.a];
@@ -1697,7 +1711,7 @@ __device__ __forceinline__ bool mpr_fetch(const SceneImg &img, const WorkQ &wq, 
   cA = v3(OA.ctr[0], OA.ctr[1], OA.ctr[2]);
   cBl = v3(OB.ctr[0], OB.ctr[1], OB.ctr[2]);
   if (round == 1) {  // [upstream] centerTriangle = centroid; voxel Box centre = its pose
-    B.voff = wq.iaux[my];
+    B.voff = aux;
     const float4 a = __ldg(img.prims + 3 * B.voff);
     if (B.type == MPB_GEOM_TRI) {
       const float4 b = __ldg(img.prims + 3 * B.voff + 1), c = __ldg(img.prims + 3 * B.voff + 2);
@@ -1751,7 +1765,9 @@ __global__ void __launch_bounds__(256, MPB_NARROW_MINB) narrow2_kernel(SceneImg 
     if (next >= end) continue;
     DevShape A, B;
     {  // shapes are uniform over the bin: read them once from the first item of the slice
-      const DevPair pr0 = img.pairs[wq.ipair[next]];
+      int c0_, p0_, a0_;
+      item_ids(item_rec(wq, round, next), c0_, p0_, a0_);
+      const DevPair pr0 = img.pairs[p0_];
       A = shape_of(img.objs[pr0.a]);
       B = shape_of(img.objs[pr0.b]);
       if (round == 1) B.type = img.objs[pr0.b].vcnt;  // leaf primitives of a BVH object: MPB_GEOM_TRI / MPB_GEOM_VBOX
@@ -1989,8 +2005,8 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
     int my_cfg = 0, my_p = 0;
     bool my_known = true;
     if (lane < 4 && it0 + lane < end) {
-      my_cfg = wq.icfg[it0 + lane];
-      my_p = wq.ipair[it0 + lane];
+      int aux_;
+      item_ids(item_rec(wq, 0, it0 + lane), my_cfg, my_p, aux_);
       my_known = hit_known(out, (unsigned)my_cfg, my_p);
     }
     for (int sub = 0; sub < 4; sub++) {
@@ -2002,10 +2018,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
     const DevObject &B = img.objs[pr.b];  // the BVH object
     if (B.voff < 0) continue;             // empty octree
     float R[9], t[3];
-#pragma unroll
-    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
-#pragma unroll
-    for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + it];
+    item_pose(item_rec(wq, 0, it), R, t);
     // shape OBB expressed in the object frame B:  x_B = R^T (x_A - t)
     float Ra[9], ca[3];  // OBB axes (columns) and centre in B
     {
@@ -2103,13 +2116,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
           base = g.shfl(base, 0);
           const unsigned slot = base + g.thread_rank();
           if (slot < wq.cap) {
-#pragma unroll
-            for (int k2 = 0; k2 < 9; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = R[k2];
-#pragma unroll
-            for (int k2 = 0; k2 < 3; k2++) wq.stf[(size_t)(9 + k2) * wq.cap + slot] = t[k2];
-            wq.scfg[slot] = cfg;
-            wq.spair[slot] = p;
-            wq.saux[slot] = prim;
+            item_store(wq, 1, slot, R, t, cfg, p, prim, bin2);
             atomicAdd(&wq.bin_count[bin2], 1u);
           }
         }
@@ -2220,12 +2227,13 @@ __device__ __forceinline__ void exp_leaf_batch(const SceneImg &img, const WorkQ 
     if (emit) {
       const unsigned slot = base + __popc(em & ((1u << lane) - 1u));
       if (slot < wq.cap) {
+        float R9[9], t3[3];
 #pragma unroll
-        for (int k2 = 0; k2 < 12; k2++) wq.stf[(size_t)k2 * wq.cap + slot] = S.item[k2][o];
-        wq.scfg[slot] = S.meta[0][o];
-        wq.spair[slot] = S.meta[1][o];
-        wq.saux[slot] = prim;
+        for (int k2 = 0; k2 < 9; k2++) R9[k2] = S.item[k2][o];
+#pragma unroll
+        for (int k2 = 0; k2 < 3; k2++) t3[k2] = S.item[9 + k2][o];
         const int bin2 = S.meta[3][o];
+        item_store(wq, 1, slot, R9, t3, S.meta[0][o], S.meta[1][o], prim, bin2);
         if (smem_bins) atomicAdd(&S.bins[bin2], 1u);
         else atomicAdd(&wq.bin_count[bin2], 1u);
       }
@@ -2271,16 +2279,15 @@ __global__ void __launch_bounds__(128, MPB_EXPL_MINB) expand_lane_kernel(SceneIm
       if (base + __popc(need) >= end) drained = true;
       const unsigned my = base + __popc(need & ((1u << lane) - 1u));
       if (!busy && my < end) {
-        const int cfg = wq.icfg[my], p = wq.ipair[my];
+        const float4 *rc = item_rec(wq, 0, my);
+        int cfg, p, aux_;
+        item_ids(rc, cfg, p, aux_);
         const DevPair pr = img.pairs[p];
         const DevObject &A = img.objs[pr.a];  // the shape
         const DevObject &B = img.objs[pr.b];  // the BVH object
         if (B.voff >= 0 && !hit_known(out, (unsigned)cfg, p)) {
           float R[9], t[3], Ra[9];
-#pragma unroll
-          for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + my];
-#pragma unroll
-          for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + my];
+          item_pose(rc, R, t);
           {  // shape OBB in the object frame B:  x_B = R^T (x_A - t)
             const float d0 = A.oc[0] - t[0], d1 = A.oc[1] - t[1], d2 = A.oc[2] - t[2];
 #pragma unroll
@@ -2450,17 +2457,16 @@ __global__ void __launch_bounds__(128) expand2_kernel(SceneImg img, WorkQ wq, Hi
     if (lane == 0) it = atomicAdd(&wq.totals[7], 1u);
     it = first + __shfl_sync(FULL, it, 0);
     if (it >= end) break;
-    const int cfg = wq.icfg[it], p = wq.ipair[it];
+    const float4 *rc = item_rec(wq, 0, it);
+    int cfg, p, aux_;
+    item_ids(rc, cfg, p, aux_);
     if (hit_known(out, (unsigned)cfg, p)) continue;
     const DevPair pr = img.pairs[p];
     const DevObject &A = img.objs[pr.a];  // mesh
     const DevObject &B = img.objs[pr.b];  // mesh or octree
     if (B.voff < 0) continue;             // empty octree
     float R[9], t[3];  // B in A
-#pragma unroll
-    for (int k = 0; k < 9; k++) R[k] = wq.itf[(size_t)k * wq.cap + it];
-#pragma unroll
-    for (int k = 0; k < 3; k++) t[k] = wq.itf[(size_t)(9 + k) * wq.cap + it];
+    item_pose(rc, R, t);
     const int leaf_b = B.vcnt;  // MPB_GEOM_TRI or MPB_GEOM_VBOX (A's leaves are triangles)
     int sp = 1;
     if (lane == 0) stack[0] = make_int2(A.voff, B.voff);
