@@ -155,6 +155,19 @@ int mpb_scene_update_objects(mpb_scene *scene, int32_t n, const int32_t *obj_idx
  * (src/pinocchio_model.cpp:271-312).  q: [n][state_dim] float32; poses: [n][n_links][7] float32. */
 int mpb_fk_batch(mpb_scene *scene, const float *q, int64_t n, float *poses, int space, void *stream);
 
+/* mpb_fk_batch for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Calls no cudaMalloc / cudaFree / allocating routine: the joint-frame table of the batch lives in a fixed array of
+ * MPB_NOALLOC_SCRATCH_BYTES inside the library image (held by every GPU that loads the library, until exit).
+ *   q_dev [n][state_dim] float32 and poses_dev [n][n_links][7] float32 are DEVICE pointers; the call returns after the
+ *   enqueue on `stream` (NULL: the scene's stream) and the caller synchronises.
+ *   n x (joints + 1) x 48 bytes must fit the array (Panda: 34 944 configurations per call); more: MPB_ERR_CAPACITY.
+ * All calls on one GPU share the array: calls that overlap on the GPU (different streams) race; calls on one stream do
+ * not.  The array keeps the last call's contents; nothing in it needs clearing (every word is written before it is read).
+ * Same arithmetic as mpb_fk_batch: the results are identical. */
+#define MPB_NOALLOC_SCRATCH_BYTES (16u << 20)
+int mpb_fk_batch_noalloc(mpb_scene *scene, const float *q_dev, int64_t n, float *poses_dev, void *stream);
+
 /* Batched ValidityCheckerTpl::isValid = setQposAll + collideFull (src/ompl_planner.h:59-62,
  * src/planning_world.cpp:249-262, 483-490).
  *   q            [n][state_dim] float32

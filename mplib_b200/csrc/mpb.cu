@@ -2081,6 +2081,88 @@ extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *pose
   return MPB_OK;
 }
 
+// ------------------------------------------------------------------------------------------ FK without allocation
+// mpb_fk_batch_noalloc: the FK-only call for callers that may not allocate (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// fk_pose_kernel keeps the joint-frame table T[] of a configuration in per-thread local memory (the driver's own scratch
+// allocation); this variant keeps it in a fixed array of the library image, word-major [joint * 12 + word][configuration]
+// (coalesced), so the call needs nothing but the caller's input and output buffers.  Every GPU that loads the library
+// holds MPB_NOALLOC_SCRATCH_BYTES until exit.  All calls on a device share the array: calls that overlap on the GPU
+// (two streams) race.  Nothing in it has to start at zero -- a thread reads only words it wrote in the same launch.
+static __device__ __align__(256) float g_fk_scratch[MPB_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+__global__ void __launch_bounds__(128) fk_pose_scratch_kernel(SceneImg img, const float *__restrict__ q, long long n, float *__restrict__ poses,
+                                                              float *scratch, size_t ld) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float *T = scratch + i;  // word w of joint frame j: T[(j * 12 + w) * ld]
+  auto put = [&](int j, const Xf &x) {
+#pragma unroll
+    for (int k = 0; k < 9; k++) T[(size_t)(j * 12 + k) * ld] = x.r[k];
+#pragma unroll
+    for (int k = 0; k < 3; k++) T[(size_t)(j * 12 + 9 + k) * ld] = x.p[k];
+  };
+  auto get = [&](int j) {
+    Xf x;
+#pragma unroll
+    for (int k = 0; k < 9; k++) x.r[k] = T[(size_t)(j * 12 + k) * ld];
+#pragma unroll
+    for (int k = 0; k < 3; k++) x.p[k] = T[(size_t)(j * 12 + 9 + k) * ld];
+    return x;
+  };
+  const float *qrow = q + i * img.state_dim;
+  put(0, xf_identity());
+  for (int j = 0; j < img.n_joints; j++) {  // the arithmetic of fk_joints, term by term
+    const DevJoint &J = img.joints[j];
+    const float qj = J.slot >= 0 ? qrow[J.slot] : J.qconst;
+    const Xf li = xf_mul(load_xf12(J.P), joint_motion(J, qj));
+    put(j + 1, xf_mul(get(J.parent), li));
+  }
+  for (int l = 0; l < img.n_links; l++) {
+    const Xf w = xf_mul(get(img.linkJoint[l]), load_xf12(img.linkL + 12 * l));
+    float *o = poses + ((size_t)i * img.n_links + l) * 7;
+    float qt[4];
+    mat_to_quat(w.r, qt);
+    o[0] = w.p[0]; o[1] = w.p[1]; o[2] = w.p[2]; o[3] = qt[0]; o[4] = qt[1]; o[5] = qt[2]; o[6] = qt[3];
+  }
+}
+
+// Device address of g_fk_scratch on `device` (which must be current): in host code the array's name is only a handle for
+// the runtime, not a device pointer.  Resolved once per device.
+static int fk_scratch_address(int device, float **ptr) {
+  static std::mutex mu;
+  static float *addr[64] = {};
+  if (device < 0 || device >= 64) return fail(MPB_ERR_INVALID, "device index out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device]) {
+    void *p = nullptr;
+    CU(cudaGetSymbolAddress(&p, g_fk_scratch));
+    addr[device] = static_cast<float *>(p);
+  }
+  *ptr = addr[device];
+  return MPB_OK;
+}
+
+extern "C" int mpb_fk_batch_noalloc(mpb_scene *s, const float *q_dev, int64_t n, float *poses_dev, void *stream) {
+  if (!s) return fail(MPB_ERR_INVALID, "null scene");
+  if (n < 0 || (n > 0 && (!poses_dev || (!q_dev && s->img.state_dim > 0)))) return fail(MPB_ERR_INVALID, "null batch pointer");
+  if (n == 0 || s->img.n_links == 0) return MPB_OK;
+  const size_t ld = ((size_t)n + 31) / 32 * 32;
+  const size_t words = (size_t)(s->img.n_joints + 1) * 12;
+  const size_t max_n = MPB_NOALLOC_SCRATCH_BYTES / sizeof(float) / words / 32 * 32;
+  if (ld > max_n)
+    return fail(MPB_ERR_CAPACITY, "mpb_fk_batch_noalloc: n = " + std::to_string(n) + " exceeds the fixed scratch array (" +
+                                      std::to_string(MPB_NOALLOC_SCRATCH_BYTES) + " bytes = at most " + std::to_string(max_n) +
+                                      " configurations of this scene per call); split the batch or use mpb_fk_batch");
+  CU(cudaSetDevice(s->device));
+  float *scratch = nullptr;
+  if (int rc = fk_scratch_address(s->device, &scratch)) return rc;
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  fk_pose_scratch_kernel<<<(int)((n + 127) / 128), 128, 0, st>>>(s->img, q_dev, n, poses_dev, scratch, ld);
+  CU(cudaGetLastError());
+  return MPB_OK;
+}
+
 // ------------------------------------------------------------------------------------------ FP32 peak probe
 __global__ void __launch_bounds__(256) fma_probe_kernel(float *out, int iters) {
   float a[8];
