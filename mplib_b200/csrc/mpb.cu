@@ -133,6 +133,10 @@ struct mpb_scene {
   int narrow_blocks = 0;
   int sphere_blocks[2] = {0, 0}, dense_blocks[2] = {0, 0}, sphere_blocks_ct[1] = {0}, sphere_blocks_blk[2] = {0, 0};
   int expand_lane_blocks = 0, dense2_blocks = 0;
+  // fk_sphere_kernel (FK + sphere phase fused, OBB rows on demand): branch-point joint slots kept on chip
+  unsigned jneed = 0;
+  size_t fk_sphere_smem = 0;
+  int fk_sphere_blocks = 0;
   // broadphase grid over world-fixed partners (sphere_grid_kernel), built lazily before the first large pass
   bool grid_dirty = true, grid_on = false;
   int *d_grid_start = nullptr;
@@ -1119,6 +1123,16 @@ extern "C" int mpb_scene_create(const mpb_scene_desc *d, int device, mpb_scene *
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<0>, 128, 0)); s->dense_blocks[0] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense_kernel<1>, 128, 0)); s->dense_blocks[1] = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, dense2_kernel, 128, 0)); s->dense2_blocks = s->num_sms * std::max(b, 1);
+    {  // fk_sphere_kernel: the joint-table slots some joint names as its parent stay in shared memory
+      s->jneed = 0;
+      for (const DevJoint &J : s->h_joints)
+        if (J.pjslot >= 0) s->jneed |= 1u << J.pjslot;
+      s->fk_sphere_smem = ((size_t)s->img.n_dyn * 3 + 12 * (size_t)__builtin_popcount(s->jneed)) * 128 * sizeof(float);
+      if (s->fk_sphere_smem <= 48 * 1024) {
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, fk_sphere_kernel, 128, s->fk_sphere_smem));
+        s->fk_sphere_blocks = s->num_sms * std::max(b, 1);
+      }
+    }
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_lane_kernel, 128, 0)); s->expand_lane_blocks = s->num_sms * std::max(b, 1);
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, sphere_grid_kernel, 128, 0)); s->sphere_blocks_grid = s->num_sms * std::max(b, 1);
   }
@@ -1475,6 +1489,11 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
   // host input: q arrives in sub-ranges so that FK + cull of one overlaps the copy of the next.  A call of several passes
   // already overlaps the copy of pass c+1 with the kernels of pass c (double buffering), so its passes take q whole:
   // the thread-per-configuration cull kernels need ~10^6 configurations to fill the GPU
+  // fk_sphere_kernel cuts the DRAM traffic of a C2 pass from ~790 MB to ~290 MB but FK is issue-bound (fk_table_kernel runs at
+  // 74 % issue-active), and the second walk of the chain costs more than the writes it saves: C2 0.365 -> 0.377 ms, C5 3.92 ->
+  // 4.57 ms per step.  Off unless asked for.
+  static const int lazy_env = getenv("MPB_LAZY_FK") && atoi(getenv("MPB_LAZY_FK"));
+  const bool lazy = lazy_env && !small && s->cull_tier == 1 && s->fk_sphere_blocks > 0;
   const long long sub = hq ? (po.whole_pass ? m : std::max<long long>(s->host_chunk, 64)) : m;
   for (long long off = 0; off < m; off += sub) {
     const long long mm = std::min(sub, m - off);
@@ -1484,7 +1503,14 @@ static int launch_pass(mpb_scene *s, float *dq_w, const float *dq, long long m, 
       CU(cudaEventRecord(landed, s->stream_h2d));
       CU(cudaStreamWaitEvent(st, landed, 0));
     }
-    if (s->img.n_pairs > 0) {
+    if (s->img.n_pairs > 0 && lazy) {
+      // parameter-space tier: FK + sphere phase fused, no sphere table, OBB rows only for objects that survivors name
+      const int cblocks = (int)((mm + 127) / 128);
+      if (ev && !hq) { CU(cudaEventRecord(f0, st)); CU(cudaEventRecord(f1, st)); }
+      fk_sphere_kernel<<<std::min(cblocks, s->fk_sphere_blocks), 128, s->fk_sphere_smem, st>>>(s->img, s->fk_tab, s->ct_small, s->d_qconst, dq + off * D, mm, off, s->jneed,
+                                                                                              s->d_obb, s->pose_ld, s->d_sq, s->sq_cap, s->wq.totals);
+      *launches += 1;
+    } else if (s->img.n_pairs > 0) {
       const int cblocks = (int)((mm + 127) / 128);
       if (ev && !hq) CU(cudaEventRecord(f0, st));
       fk_table_kernel<<<cblocks, 128, 0, st>>>(s->img, s->fk_tab, s->d_qconst, dq + off * D, mm, s->d_pose + off, s->pose_ld, s->d_obb + (size_t)off * 2);

@@ -580,6 +580,173 @@ __global__ void __launch_bounds__(128) sphere_kernel(const __grid_constant__ Sce
     if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
 }
 
+// FK + sphere phase in one kernel, for scenes of the parameter-space tier (a robot against itself: C2's 19 pairs, C5's
+// 150): thread per configuration, the joint chain in registers, the sphere centres of the thread's configuration in the
+// warp's [word][lane] block of shared memory -- and NO sphere table, and OBB rows ON DEMAND: fk_table_kernel writes 352 B
+// of OBB rows per Panda configuration of which the ~1.6 survivors per configuration read < 10 % (80 % of the DRAM traffic of
+// a C2 pass).  Here a thread collects, while it tests the pairs, the set of moving objects its survivors name, then walks
+// the joint chain a second time (arithmetic is cheap next to the HBM writes it replaces) and writes the rows of those
+// objects only; the dense cull reads them where it always did.  A first version re-derived the frames per survivor inside
+// the dense cull (two divergent chains per survivor, 110 registers): C2 0.375 -> 0.400 ms, C5 3.9 -> 5.2 ms, dropped.
+// MEASURED (profiles/r02_ncu_c2_fk_sphere.txt): DRAM traffic of a C2 pass 790 -> 290 MB, but 186 us against 109 + 65 us for
+// fk_table_kernel + sphere_kernel -- FK is bound by issue slots (fk_table_kernel: 74 % issue-active), not by its writes, and
+// the second walk costs more instructions than the stores it replaces.  Kept behind MPB_LAZY_FK=1, off by default.
+// Branch-point joint frames (pjslot) that a later child reads stay in shared memory (`jneed`: bit per joint-table slot
+// that some joint names as its parent).  Same arithmetic as fk_table_kernel + sphere_kernel<0, 256, 64>: identical
+// survivors and rows.
+__global__ void __launch_bounds__(128) fk_sphere_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
+                                                        const __grid_constant__ CullTabC<256, 64> ct, const float *__restrict__ qconst,
+                                                        const float *__restrict__ q, long long n, long long cfg_base, unsigned jneed,
+                                                        float4 *__restrict__ obb, size_t ld, uint2 *__restrict__ sq, unsigned sq_cap,
+                                                        unsigned *__restrict__ totals) {
+  const unsigned FULL = 0xffffffffu;
+  const unsigned lane = threadIdx.x & 31;
+  extern __shared__ float s_ctr[];  // [warp][n_dyn * 3 + 12 * popc(jneed)][32]
+  const int n_need = __popc(jneed);
+  float *ctr = s_ctr + (size_t)(threadIdx.x >> 5) * ((img.n_dyn * 3 + n_need * 12) * 32) + lane;
+  float *jt = ctr + img.n_dyn * 3 * 32;
+  unsigned wbase = 0, wused = 0, wcap = 0;  // warp-uniform survivor-queue chunk, kept across the warp's tiles
+  const long long n_tiles = (n + 31) / 32;
+  const long long warp_stride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long tile = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < n_tiles; tile += warp_stride) {
+    const long long i = tile * 32 + lane;  // whole warps run; lanes past n push nothing
+    const bool valid = i < n;
+    const long long ic = valid ? i : n - 1;
+    {  // forward kinematics down the forest (fk_table_kernel's loop; the frames stay on chip)
+      Xf cur = xf_identity();
+      const float *qrow = q + ic * img.state_dim;
+      for (int j = 0; j < img.n_joints; j++) {
+        const DevJoint &J = tab.j[j];
+        const float qj = J.slot >= 0 ? qrow[J.slot] : __ldg(qconst + j);
+        if (J.parent == 0) cur = joint_step(J, nullptr, qj);
+        else if (J.pjslot >= 0) {
+          const float *src = jt + __popc(jneed & ((1u << J.pjslot) - 1u)) * (12 * 32);
+          Xf par;
+#pragma unroll
+          for (int k = 0; k < 9; k++) par.r[k] = src[k * 32];
+#pragma unroll
+          for (int k = 0; k < 3; k++) par.p[k] = src[(9 + k) * 32];
+          cur = joint_step(J, &par, qj);
+        } else cur = joint_step(J, &cur, qj);
+        if (J.jslot >= 0 && ((jneed >> J.jslot) & 1u)) {
+          float *dst = jt + __popc(jneed & ((1u << J.jslot) - 1u)) * (12 * 32);
+#pragma unroll
+          for (int k = 0; k < 9; k++) dst[k * 32] = cur.r[k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) dst[(9 + k) * 32] = cur.p[k];
+        }
+        for (int e = 0; e < J.dyn_count; e++) {
+          const FkObjC &O = tab.o[J.dyn_first + e];
+          float c[3];
+          xf_point(cur, O.bcj, c);  // bounding-sphere centre in the joint frame -> world
+#pragma unroll
+          for (int k = 0; k < 3; k++) ctr[(O.dyn * 3 + k) * 32] = c[k];
+        }
+      }
+    }
+    int r = 0;          // run cursor
+    unsigned need = 0;  // moving objects (slots) named by this configuration's survivors
+    for (int gbase = 0; gbase < img.n_pairs; gbase += 32) {
+      const int gend = min(gbase + 32, img.n_pairs);
+      unsigned mask = 0;
+      int k = gbase;
+      while (k < gend) {
+        const int4 run = ct.runs[r];  // {moving slot or -1, first, count, partner kind}
+        const int rlast = run.y + run.z;
+        const int rend = min(rlast, gend);
+        float ax = 0.f, ay = 0.f, az = 0.f;
+        const unsigned before = mask;
+        if (run.x >= 0) { ax = ctr[run.x * 96]; ay = ctr[run.x * 96 + 32]; az = ctr[run.x * 96 + 64]; }
+        if (run.w == 0) {
+          const float na2 = -fmaf(ax, ax, fmaf(ay, ay, az * az));
+#pragma unroll 8
+          for (; k < rend; k++) {
+            const float4 c = ct.q[k];
+            mask |= (unsigned)(fmaf(ax, c.x, fmaf(ay, c.y, fmaf(az, c.z, c.w))) <= na2) << (k - gbase);
+          }
+        } else {
+#pragma unroll 4
+          for (; k < rend; k++) {
+            const float4 c = ct.q[k];
+            const int m2 = __float_as_int(c.x);
+            const float dx = ax - ctr[m2 * 96], dy = ay - ctr[m2 * 96 + 32], dz = az - ctr[m2 * 96 + 64];
+            const unsigned hit = (unsigned)(fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= c.w);
+            mask |= hit << (k - gbase);
+            need |= hit << m2;
+          }
+        }
+        if (mask != before && run.x >= 0) need |= 1u << run.x;  // the segment's bits are new ones: any hit changes the mask
+        if (rend == rlast) r++;
+      }
+      if (!valid) mask = 0;
+      if (!__any_sync(FULL, mask != 0)) continue;
+      // push (configuration, entry) survivors: warp prefix sum into the warp's chunk of the survivor queue
+      const unsigned c = __popc(mask);
+      unsigned incl = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned t = __shfl_up_sync(FULL, incl, o);
+        if ((int)lane >= o) incl += t;
+      }
+      const unsigned wtot = __shfl_sync(FULL, incl, 31);
+      if (wused + wtot > wcap) {
+        for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+          if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);  // unused tail of the old chunk
+        const unsigned want = max((unsigned)MPB_SQ_CHUNK, wtot);
+        unsigned nb = 0;
+        if (lane == 0) nb = atomicAdd(&totals[6], want);
+        wbase = __shfl_sync(FULL, nb, 0);
+        wused = 0;
+        wcap = want;
+      }
+      unsigned pos = wbase + wused + incl - c;
+      const unsigned cfg = (unsigned)(cfg_base + i);
+      while (mask) {
+        const int kk = __ffs(mask) - 1;
+        mask &= mask - 1;
+        if (pos < sq_cap) sq[pos] = make_uint2(cfg, (unsigned)(gbase + kk));
+        pos++;
+      }
+      wused += wtot;
+    }
+    // ---- OBB rows of the objects the survivors name: the chain once more, rows written where dense2_kernel reads them
+    if (!valid) need = 0;
+    unsigned wneed = need;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wneed |= __shfl_xor_sync(FULL, wneed, o);
+    if (wneed) {
+      Xf cur = xf_identity();
+      const float *qrow = q + ic * img.state_dim;
+      for (int j = 0; j < img.n_joints; j++) {
+        const DevJoint &J = tab.j[j];
+        const float qj = J.slot >= 0 ? qrow[J.slot] : __ldg(qconst + j);
+        if (J.parent == 0) cur = joint_step(J, nullptr, qj);
+        else if (J.pjslot >= 0) {  // stored by the first walk
+          const float *src = jt + __popc(jneed & ((1u << J.pjslot) - 1u)) * (12 * 32);
+          Xf par;
+#pragma unroll
+          for (int k = 0; k < 9; k++) par.r[k] = src[k * 32];
+#pragma unroll
+          for (int k = 0; k < 3; k++) par.p[k] = src[(9 + k) * 32];
+          cur = joint_step(J, &par, qj);
+        } else cur = joint_step(J, &cur, qj);
+        for (int e = 0; e < J.dyn_count; e++) {
+          const FkObjC &O = tab.o[J.dyn_first + e];
+          if (!((wneed >> O.dyn) & 1u)) continue;  // warp-uniform
+          const Xf E = xf_mul(cur, xf_rows(O.rec[0], O.rec[1], O.rec[2]));  // OBB frame in the joint frame -> world
+          if ((need >> O.dyn) & 1u) {
+            float4 *dst = obb + ((size_t)O.dyn * ld + (size_t)(cfg_base + i)) * 2;
+            dst[0] = rot_to_quat(E.r);
+            dst[1] = make_float4(E.p[0], E.p[1], E.p[2], 0.f);
+          }
+        }
+      }
+    }
+  }  // tiles
+  for (unsigned k2 = wused + lane; k2 < wcap; k2 += 32)
+    if (wbase + k2 < sq_cap) sq[wbase + k2] = make_uint2(0xffffffffu, 0u);
+}
+
 // sphere phase through a broadphase GRID for large cull tables whose partners are world-fixed (C3: 12 moving objects x 130
 // obstacles).  sphere_blk_kernel tests every admitted pair of every configuration, 1587 tests of which 2.6 % pass; here
 // the host rasterises, per run (= moving object), every partner's sphere inflated by the object's radius into a uniform
