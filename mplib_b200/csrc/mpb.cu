@@ -1296,6 +1296,7 @@ static int ensure_grid(mpb_scene *s) {
   s->grid_dirty = false;
   s->grid_on = false;
   static const bool enabled = !(getenv("MPB_NO_GRID") && atoi(getenv("MPB_NO_GRID")));
+  static const double grid_div = getenv("MPB_GRID_DIV") ? atof(getenv("MPB_GRID_DIV")) : 32.0;
   const size_t n_runs = s->h_runs.size();  // incl. the sentinel
   std::vector<int2> grun(n_runs, make_int2(-1, 0));
   size_t fixed_entries = 0;
@@ -1315,13 +1316,14 @@ static int ensure_grid(mpb_scene *s) {
   double ext = 0;
   for (int a = 0; a < 3; a++) ext = std::max(ext, hi[a] - lo[a]);
   if (!(ext > 0) || !(ext < 1e6)) return MPB_OK;
-  const double h = std::max(ext / 32.0, 0.02);
+  const double h = std::max(ext / grid_div, 0.02);
   int gn[3];
-  for (int a = 0; a < 3; a++) gn[a] = std::max(1, std::min(40, (int)std::ceil((hi[a] - lo[a]) / h)));
+  for (int a = 0; a < 3; a++) gn[a] = std::max(1, std::min((int)(grid_div * 1.25), (int)std::ceil((hi[a] - lo[a]) / h)));
   const size_t cells = (size_t)gn[0] * gn[1] * gn[2];
   std::vector<int> start;
   std::vector<unsigned short> list;
   const double pad = 1e-4;  // fp32 rounding of the moving centre near a cell face
+  static const bool obb_filter = !(getenv("MPB_GRID_NO_OBB") && atoi(getenv("MPB_GRID_NO_OBB")));
   for (size_t ri = 0; ri < n_runs; ri++) {
     const int4 r = s->h_runs[ri];
     if (r.w != 0 || r.z == 0 || r.z > 65535) continue;
@@ -1331,6 +1333,13 @@ static int ensure_grid(mpb_scene *s) {
       const float4 c = s->h_cullc[r.y + e];
       const double rr = std::sqrt((double)c.w) + pad;
       const double cc[3] = {c.x, c.y, c.z};
+      // the partner's oriented box (world frame): the moving object lies inside the ball (its sphere centre, rm), so the pair
+      // can only touch when that centre is within rm of the box -- for a long capsule or a flat box a much smaller region than
+      // the ball around the partner's bounding sphere.  Tested at the cell centre with the cell's half diagonal as slack.
+      const DevPair &pr = s->h_pairs[s->h_cullm[r.y + e].x];
+      const int fo = s->h_objs[pr.a].dyn < 0 ? pr.a : pr.b;
+      const float4 *box = s->h_cobb.data() + (size_t)MPB_COBB_WORDS * fo;
+      const double rm = rr - (double)s->h_objs[fo].br + 0.5 * 1.7320508075688772 * h + 1e-4;
       int c0[3], c1[3];
       for (int a = 0; a < 3; a++) {
         c0[a] = std::max(0, (int)std::floor((cc[a] - rr - lo[a]) / h));
@@ -1346,7 +1355,16 @@ static int ensure_grid(mpb_scene *s) {
               const double d = cc[a] < b0 ? b0 - cc[a] : (cc[a] > b1 ? cc[a] - b1 : 0.0);
               d2 += d * d;
             }
-            if (d2 <= rr * rr) ins.push_back(std::make_pair((z * gn[1] + y) * gn[0] + x, (unsigned short)e));
+            if (d2 > rr * rr) continue;
+            if (obb_filter) {
+              const double g[3] = {lo[0] + (x + 0.5) * h, lo[1] + (y + 0.5) * h, lo[2] + (z + 0.5) * h};
+              const double d0 = g[0] - box[0].w, d1 = g[1] - box[1].w, d2g = g[2] - box[2].w;
+              const double l0 = box[0].x * d0 + box[1].x * d1 + box[2].x * d2g, l1 = box[0].y * d0 + box[1].y * d1 + box[2].y * d2g,
+                           l2 = box[0].z * d0 + box[1].z * d1 + box[2].z * d2g;
+              const double e0 = std::max(std::fabs(l0) - box[3].x, 0.0), e1 = std::max(std::fabs(l1) - box[3].y, 0.0), e2 = std::max(std::fabs(l2) - box[3].z, 0.0);
+              if (e0 * e0 + e1 * e1 + e2 * e2 > rm * rm) continue;
+            }
+            ins.push_back(std::make_pair((z * gn[1] + y) * gn[0] + x, (unsigned short)e));
           }
     }
     for (const auto &p : ins) cnt[(size_t)p.first + 1]++;

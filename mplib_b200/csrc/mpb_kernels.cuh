@@ -2310,7 +2310,7 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
 // (profiles/r02_ncu_expand_lane_v1_source.csv).  Lanes are persistent: idle lanes take the next items of the bin.
 // The warp-per-item kernel stays for small passes (planning rounds), where the critical path of a single traversal
 // matters more than throughput; both are launched, the item count of the bin decides which one runs.
-#define MPB_EXPL_DEPTH 40     // per-lane stack entries (the tree depth is ~17 for 10^5 leaves; DFS holds at most depth + 1)
+#define MPB_EXPL_DEPTH 28     // per-lane stack entries: the walk holds at most one sibling pair per level (tree depth ~17 for 10^5 leaves; 28 covers 2^28)
 #define MPB_EXPL_QCAP 128     // leaf-primitive queue entries per warp
 #define MPB_EXPL_BINS 64      // second-round bins counted in shared memory
 #define MPB_EXPL_F 31         // floats of an item record: R 9, t 3, Ra 9, ca 3, cin 3, ah 3, rin2
