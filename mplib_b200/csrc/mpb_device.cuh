@@ -39,22 +39,23 @@ struct alignas(16) DevObject {
   int type;         // MPB_GEOM_*
   int geom;         // hull / mesh / octree index
   int dyn;          // slot in the per-thread dynamic-object table, -1 if world-fixed
+  // bytes 64..96, one 32-byte sector: what the narrowphase reads per item besides the item record
   float prm[4];     // sphere r | box half sides | capsule, cylinder: r, half height
+  float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
+  float rin;        // radius of a ball around ctr that lies inside the shape (sufficient-hit test)
   float bc[3];      // bounding-sphere centre, object frame
   float br;         // bounding-sphere radius
   float oc[3];      // OBB centre, object frame
   float oh[3];      // OBB half extents
   float oR[9];      // OBB axes as columns of a rotation (object frame)
-  float ctr[3];     // MPR centre: hull interior point (vertex mean) or 0
   int voff, vcnt;   // hull vertices in the pool
   float bcw[3];     // world-fixed objects: bounding-sphere centre in the world frame
-  float rin;        // radius of a ball around ctr that lies inside the shape (sufficient-hit test)
   int jslot;        // joint-table slot of the owner joint, -1 if world-fixed
   float bcj[3];     // bounding-sphere centre in the owner joint frame (L * bc)
   int cell;         // convex hulls: byte offset of the support cell table behind the vertex pool, -1 = none
   float4 ball[MPB_INNER_BALLS];  // balls inside the shape, object frame: centre xyz, radius w (0 = unused); sufficient-hit test
 };
-static_assert(sizeof(DevObject) % 16 == 0, "DevObject must keep 16-byte alignment");
+static_assert(sizeof(DevObject) % 32 == 0, "DevObject records must start on 32-byte sectors");
 
 // Support cell table of a convex hull: the directions of a cube map (MPB_CELL_G x MPB_CELL_G cells per face) -> the
 // vertices that can be extreme for SOME direction of the cell (a conservative superset, built on the host), so the

@@ -119,14 +119,17 @@ __device__ __forceinline__ bool hit_known(const HitOut &o, unsigned cfg, int p) 
 
 // Dense pair mask of a pass -> (configuration, pair) entries appended to the call-wide list.  A block compacts tiles of
 // 1024 mask words (one 16-byte load per thread): popcounts, warp + block prefix sums, ONE atomic per tile for the
-// slots, then every thread writes the entries of its four words.  Entries are ordered by configuration within a tile;
-// the reservation order of the tiles is the only nondeterminism.
+// slots; the threads expand their set bits into a shared-memory stage at their rank within the tile, and the block
+// copies the stage out with consecutive 8-byte stores (a tile with more hits than the stage holds writes directly).
+// Entries are ordered by configuration within a tile; the reservation order of the tiles is the only nondeterminism.
+#define MPB_HC_STAGE 2048
 __global__ void __launch_bounds__(256) hits_compact_kernel(const unsigned int *__restrict__ pair_bits, long long n_words, int pair_words,
                                                            unsigned cfg0, uint2 *__restrict__ hits, unsigned int *__restrict__ n_hits,
                                                            unsigned hit_cap) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __shared__ unsigned s_warp[8], s_base;
+  __shared__ unsigned s_warp[8], s_base, s_tot;
+  __shared__ uint2 s_stage[MPB_HC_STAGE];
   const long long n_quads = (n_words + 3) / 4, n_tiles = (n_quads + 255) / 256;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long qd = tile * 256 + threadIdx.x;
@@ -150,27 +153,38 @@ __global__ void __launch_bounds__(256) hits_compact_kernel(const unsigned int *_
       unsigned tot = 0;
 #pragma unroll
       for (int k = 0; k < 8; k++) { const unsigned t = s_warp[k]; s_warp[k] = tot; tot += t; }
+      s_tot = tot;
       s_base = tot ? atomicAdd(n_hits, tot) : 0u;
     }
     __syncthreads();
-    unsigned pos = s_base + s_warp[warp] + incl - c;
-    __syncthreads();  // s_warp / s_base are rewritten by the next tile
+    const unsigned tot = s_tot, base = s_base;
+    const bool staged = tot <= MPB_HC_STAGE;
+    unsigned pos = s_warp[warp] + incl - c;  // rank within the tile
     if (c) {
+      // (configuration, first pair) of the thread's first word: one division per thread, then counted forward
+      const long long w0 = qd * 4;
+      unsigned cfg = cfg0 + (unsigned)(w0 / pair_words), pw = (unsigned)(w0 % pair_words);
       const unsigned words[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         unsigned bits = words[j];
-        if (!bits) continue;
-        const long long w = qd * 4 + j;
-        const unsigned cfg = cfg0 + (unsigned)(w / pair_words), p0 = (unsigned)(w % pair_words) * 32u;
+        const unsigned p0 = pw * 32u;
         while (bits) {
           const int k = __ffs(bits) - 1;
           bits &= bits - 1;
-          if (pos < hit_cap) hits[pos] = make_uint2(cfg, p0 + (unsigned)k);
+          const uint2 ent = make_uint2(cfg, p0 + (unsigned)k);
+          if (staged) s_stage[pos] = ent;
+          else if (base + pos < hit_cap) hits[base + pos] = ent;
           pos++;
         }
+        if (++pw == (unsigned)pair_words) { pw = 0; cfg++; }
       }
     }
+    __syncthreads();  // the stage is complete; s_warp / s_base / s_tot may be rewritten after this point
+    if (staged)
+      for (unsigned k = threadIdx.x; k < tot; k += blockDim.x)
+        if (base + k < hit_cap) hits[base + k] = s_stage[k];
+    // (the next tile writes the stage only after its own two barriers, which every thread reaches after this copy)
   }
 }
 
