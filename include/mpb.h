@@ -289,6 +289,12 @@ int mpb_scene_info(const mpb_scene *scene, int32_t *n_pairs, int32_t *state_dim,
  * (the in-run confirmation of SMs x 128 x 2 x f that BASELINE.md 2 asks for; no reference counterpart). */
 int mpb_fp32_peak(int device, float *tflops);
 
+/* Diagnostics (no reference counterpart): the support cell table the scene compiler builds for a convex hull of <= 255
+ * vertices -- uint16 first[6 G G + 1] (G = 8 cells per cube-map face edge), then uint8 candidate vertex indices per cell.
+ * The hull support on the device scans only the candidates of the direction's cell; tests check on the host that the
+ * arg-max vertex of any direction is among them.  Needs no GPU.  out may be NULL (size query). */
+int mpb_debug_cell_table(const double *verts, int32_t n_verts, uint8_t *out, int64_t cap, int64_t *n_bytes);
+
 /* PinocchioModelTpl::computeIKCLIK (src/pinocchio_model.cpp:377-432) for n independent problems, double precision:
  * damped least squares on the 6 x nv joint Jacobian of `link`'s parent joint until |log6 error| < eps or max_iter.
  * The unknowns are the scene's batch state (state_dim joints); joints outside it keep their q_base value.

@@ -58,7 +58,7 @@ SYMBOLS = [
     "mpb_scene_set_pairs", "mpb_fk_batch", "mpb_collide_batch", "mpb_scene_info", "mpb_fp32_peak",
     "mpb_check_motion_batch", "mpb_rrtconnect_batch", "mpb_distance_batch", "mpb_ik_clik_batch",
     "mpb_link_jacobian_batch", "mpb_collide_batch_hits", "mpb_scene_poll", "mpb_scene_set_async_timing",
-    "mpb_scene_update_objects", "mpb_fk_batch_noalloc",
+    "mpb_scene_update_objects", "mpb_fk_batch_noalloc", "mpb_debug_cell_table",
 ]
 
 _lib = None
@@ -109,6 +109,7 @@ def load():
     lib.mpb_scene_set_q_base.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
     lib.mpb_scene_set_pairs.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     lib.mpb_fk_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p]
+    lib.mpb_debug_cell_table.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
     lib.mpb_fk_batch_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.mpb_collide_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                       C.POINTER(MpbStats), C.c_int, C.c_void_p]
@@ -387,6 +388,17 @@ class DeviceScene:
     def fk_noalloc_raw(self, q_dev_ptr, n, poses_dev_ptr, stream=None):
         """mpb_fk_batch_noalloc: device pointers, no allocation inside the call, returns after the enqueue."""
         _check(load().mpb_fk_batch_noalloc(self._h, _ptr(q_dev_ptr), int(n), _ptr(poses_dev_ptr), _ptr(stream)))
+
+
+def debug_cell_table(verts):
+    """Support cell table of a hull (diagnostics): -> (first uint16[6*G*G+1], candidates uint8[...])."""
+    v = np.ascontiguousarray(np.asarray(verts, dtype=np.float64))
+    nb = C.c_int64(0)
+    _check(load().mpb_debug_cell_table(v.ctypes.data, v.shape[0], None, 0, C.byref(nb)))
+    buf = np.zeros(nb.value, dtype=np.uint8)
+    _check(load().mpb_debug_cell_table(v.ctypes.data, v.shape[0], buf.ctypes.data, buf.size, C.byref(nb)))
+    n_first = 6 * 8 * 8 + 1
+    return buf[:2 * n_first].view(np.uint16).copy(), buf[2 * n_first:].copy()
 
 
 def fp32_peak_tflops(device=0):

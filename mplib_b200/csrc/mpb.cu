@@ -414,40 +414,57 @@ static void build_cell_table(const double *V, int nv, std::vector<unsigned char>
   std::lock_guard<std::mutex> lk(mu);
   if (cache.size() < 4096) cache[key] = out;
 }
+// Candidates of a cell = the vertices whose NORMAL CONE meets the cell: vertex i is the support point for a direction d iff
+// d . (v_i - v_j) >= 0 for every j.  On a cube-map face d = (+-1, u, v) (permuted), so every j is a half-plane in (u, v)
+// and the question is whether the cell's rectangle, clipped by all of them, stays non-empty (Sutherland-Hodgman on a
+// polygon of a handful of vertices).  The first version kept i when, for every j, SOME corner of the cell preferred i to
+// j -- necessary, far from sufficient: ~35 candidates per cell for the Panda's hulls where the cones give ~4, and the
+// candidate loop was a third of the narrowphase's instructions.  The half-planes are relaxed by 1e-6 (relative), so a
+// vertex that loses to the winner by less than fp32 rounding is still listed and ties resolve as in the full scan.
 static void build_cell_table_uncached(const double *V, int nv, std::vector<unsigned char> &out) {
   const int G = MPB_CELL_G;
   const double margin = 1e-3;
-  double scale = 0;
-  for (int i = 0; i < 3 * nv; i++) scale = std::max(scale, std::fabs(V[i]));
-  const double eps = 1e-9 * std::max(scale, 1e-9);
   std::vector<unsigned short> first(MPB_CELL_COUNT + 1, 0);
   std::vector<unsigned char> cand;
-  for (int face = 0; face < 6; face++)
+  std::vector<std::array<double, 2>> poly, next;
+  for (int face = 0; face < 6; face++) {
+    const double sgn = (face & 1) ? -1.0 : 1.0;
+    const int am = face < 2 ? 0 : (face < 4 ? 1 : 2);          // dominant axis
+    const int au = face < 2 ? 1 : 0, av = face < 4 ? 2 : 1;    // axes of u, v (mpb_cube_cell)
     for (int iv = 0; iv < G; iv++)
       for (int iu = 0; iu < G; iu++) {
         const double u0 = -1.0 + 2.0 * iu / G - margin, u1 = -1.0 + 2.0 * (iu + 1) / G + margin;
         const double v0 = -1.0 + 2.0 * iv / G - margin, v1 = -1.0 + 2.0 * (iv + 1) / G + margin;
-        double c[4][3];
-        const double uu[4] = {u0, u1, u0, u1}, vv[4] = {v0, v0, v1, v1};
-        for (int k = 0; k < 4; k++) {
-          const double sgn = (face & 1) ? -1.0 : 1.0;
-          if (face < 2) { c[k][0] = sgn; c[k][1] = uu[k]; c[k][2] = vv[k]; }
-          else if (face < 4) { c[k][0] = uu[k]; c[k][1] = sgn; c[k][2] = vv[k]; }
-          else { c[k][0] = uu[k]; c[k][1] = vv[k]; c[k][2] = sgn; }
-        }
         first[(face * G + iv) * G + iu] = (unsigned short)cand.size();
         for (int i = 0; i < nv; i++) {
-          bool ok = true;
-          for (int j = 0; j < nv && ok; j++) {
+          poly = {{u0, v0}, {u1, v0}, {u1, v1}, {u0, v1}};
+          for (int j = 0; j < nv && !poly.empty(); j++) {
             if (j == i) continue;
             const double w[3] = {V[3 * i] - V[3 * j], V[3 * i + 1] - V[3 * j + 1], V[3 * i + 2] - V[3 * j + 2]};
-            double best = -1e300;
-            for (int k = 0; k < 4; k++) best = std::max(best, c[k][0] * w[0] + c[k][1] * w[1] + c[k][2] * w[2]);
-            ok = best >= -eps;
+            const double a = w[au], b = w[av], c = sgn * w[am];
+            const double tol = 1e-6 * (std::fabs(a) + std::fabs(b) + std::fabs(c)) + 1e-300;
+            // keep the part of the polygon with a u + b v + c >= -tol
+            next.clear();
+            const size_t n = poly.size();
+            for (size_t k = 0; k < n; k++) {
+              const auto &P = poly[k], &Q = poly[(k + 1) % n];
+              const double fp = a * P[0] + b * P[1] + c + tol, fq = a * Q[0] + b * Q[1] + c + tol;
+              if (fp >= 0) next.push_back(P);
+              if ((fp >= 0) != (fq >= 0)) {
+                const double t = fp / (fp - fq);
+                next.push_back({P[0] + t * (Q[0] - P[0]), P[1] + t * (Q[1] - P[1])});
+              }
+            }
+            poly.swap(next);
           }
-          if (ok) cand.push_back((unsigned char)i);
+          if (!poly.empty()) cand.push_back((unsigned char)i);
         }
+        // some vertex is extreme for every direction, so a cell is never empty -- unless the input is degenerate (duplicated
+        // vertices exclude each other only through the tolerance): then the cell falls back to the full scan
+        if (cand.size() == first[(face * G + iv) * G + iu])
+          for (int i = 0; i < nv; i++) cand.push_back((unsigned char)i);
       }
+  }
   first[MPB_CELL_COUNT] = (unsigned short)cand.size();
   out.resize(2 * (MPB_CELL_COUNT + 1) + cand.size());
   memcpy(out.data(), first.data(), 2 * (MPB_CELL_COUNT + 1));
@@ -2122,6 +2139,16 @@ extern "C" int mpb_fk_batch(mpb_scene *s, const float *q, int64_t n, float *pose
       CU(cudaMemcpyAsync(poses + (size_t)off * L * 7, dp, (size_t)m * L * 7 * sizeof(float), cudaMemcpyDeviceToHost, st));
   }
   if (space == MPB_HOST) CU(cudaStreamSynchronize(st));
+  return MPB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ diagnostics: support cell table
+extern "C" int mpb_debug_cell_table(const double *verts, int32_t n_verts, uint8_t *out, int64_t cap, int64_t *n_bytes) {
+  if (!verts || n_verts < 1 || n_verts > 255 || !n_bytes) return fail(MPB_ERR_INVALID, "mpb_debug_cell_table: 1..255 vertices");
+  std::vector<unsigned char> t;
+  build_cell_table_uncached(verts, n_verts, t);
+  *n_bytes = (int64_t)t.size();
+  if (out && cap >= (int64_t)t.size()) memcpy(out, t.data(), t.size());
   return MPB_OK;
 }
 
