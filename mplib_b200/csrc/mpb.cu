@@ -98,10 +98,12 @@ struct mpb_scene {
   // cull table (sphere_kernel): pairs re-ordered into runs that share their moving object
   std::vector<float4> h_cullc, h_cullq;
   std::vector<int2> h_cullm;
+  std::vector<int4> h_cullp;  // per cull entry: {pair, object a, object b, (slot a + 1) | (slot b + 1) << 16}: one load for the dense cull
   std::vector<int4> h_runs;
   float4 *d_cobb = nullptr;
   float4 *d_cullc = nullptr, *d_cullq = nullptr;
   int2 *d_cullm = nullptr;
+  int4 *d_cullp = nullptr;
   int4 *d_runs = nullptr;
   size_t cull_cap = 0;
   SceneImg img{};
@@ -694,6 +696,7 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
     s->h_cullc.resize(n_pairs);
     s->h_cullq.resize(n_pairs);
     s->h_cullm.resize(n_pairs);
+    s->h_cullp.resize(n_pairs);
     s->h_runs.clear();
     for (int k = 0; k < n_pairs; k++) {
       const Ent &e = ents[k];
@@ -709,6 +712,10 @@ static int build_pairs(mpb_scene *s, int n_pairs, const int32_t *pa, const int32
         s->h_cullq[k] = make_float4(-2.f * e.c[0], -2.f * e.c[1], -2.f * e.c[2], (float)w);
       }
       s->h_cullm[k] = make_int2(e.p, (e.m1 + 1) | ((e.m2 + 1) << 16));
+      {
+        const DevPair &pr = s->h_pairs[e.p];
+        s->h_cullp[k] = make_int4(e.p, pr.a, pr.b, (s->h_objs[pr.a].dyn + 1) | ((s->h_objs[pr.b].dyn + 1) << 16));
+      }
       if (s->h_runs.empty() || s->h_runs.back().x != e.m1 || s->h_runs.back().w != e.kind)
         s->h_runs.push_back(make_int4(e.m1, k, 1, e.kind));
       else
@@ -760,20 +767,24 @@ static int upload_pairs(mpb_scene *s) {
     if (s->d_cullc) cudaFree(s->d_cullc);
     if (s->d_cullq) cudaFree(s->d_cullq);
     if (s->d_cullm) cudaFree(s->d_cullm);
+    if (s->d_cullp) cudaFree(s->d_cullp);
     if (s->d_runs) cudaFree(s->d_runs);
     s->cull_cap = std::max<size_t>(n + 1, 64);
     CU(cudaMalloc(&s->d_cullc, s->cull_cap * sizeof(float4)));
     CU(cudaMalloc(&s->d_cullq, s->cull_cap * sizeof(float4)));
     CU(cudaMalloc(&s->d_cullm, s->cull_cap * sizeof(int2)));
+    CU(cudaMalloc(&s->d_cullp, s->cull_cap * sizeof(int4)));
     CU(cudaMalloc(&s->d_runs, s->cull_cap * sizeof(int4)));
   }
   if (n) CU(cudaMemcpy(s->d_cullc, s->h_cullc.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
   if (n) CU(cudaMemcpy(s->d_cullq, s->h_cullq.data(), n * sizeof(float4), cudaMemcpyHostToDevice));
   if (n) CU(cudaMemcpy(s->d_cullm, s->h_cullm.data(), n * sizeof(int2), cudaMemcpyHostToDevice));
+  if (n) CU(cudaMemcpy(s->d_cullp, s->h_cullp.data(), n * sizeof(int4), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(s->d_runs, s->h_runs.data(), s->h_runs.size() * sizeof(int4), cudaMemcpyHostToDevice));
   s->img.cullc = s->d_cullc;
   s->img.cullq = s->d_cullq;
   s->img.cullm = s->d_cullm;
+  s->img.cullp = s->d_cullp;
   s->img.runs = s->d_runs;
   return MPB_OK;
 }

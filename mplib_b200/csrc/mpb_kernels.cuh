@@ -40,6 +40,7 @@ struct SceneImg {
   const float4 *cobb;       // [n_objects][MPB_COBB_WORDS] cull records (see dense_kernel)
   const float4 *cullc;      // [n_pairs] cull table: world-fixed partner's sphere centre (xyz), (R1 + R2 + margin)^2 (w)
   const float4 *cullq;      // [n_pairs] world-fixed partners in expanded form: (-2c, |c|^2 - (R1 + R2)^2 - slack), see sphere_kernel
+  const int4 *cullp;        // [n_pairs] cull table: {pair index, object a, object b, (slot a + 1) | (slot b + 1) << 16}
   const int2 *cullm;        // [n_pairs] cull table: {pair index, (moving slot 1 + 1) | (moving slot 2 + 1) << 16}
   const int4 *runs;         // cull-table runs: {moving slot or -1, first entry, count, partner kind (0 fixed, 1 moving)}
   // broadphase grid over the world-fixed partners (sphere_grid_kernel): one cell table per run of fixed partners
@@ -1304,20 +1305,24 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg im
     if (e + e_stride < total) ent_next = sq[e + e_stride];
     if (ent.x != 0xffffffffu) {
       cfg = ent.x;
-      p = __ldg(&img.cullm[ent.y].x);
-      const DevPair pr = img.pairs[p];
+      // one 16-byte load names the pair, its objects and their moving slots: the OBB rows (random 32-byte reads, the long
+      // latency of this kernel) are requested together with the cull records instead of two dependent loads later
+      const int4 cp = __ldg(img.cullp + ent.y);
+      p = cp.x;
+      const int da = (cp.w & 0xffff) - 1, db = (cp.w >> 16) - 1;
       // cull records (MPB_COBB_WORDS float4 per object): [0..2] OBB frame (world frame if the object is fixed,
       // owner-joint frame if it moves), [3] half extents + inscribed radius, [4] inscribed-ball centre in the OBB frame
       // + moving slot, [5..7] OBB frame in the object frame, [8..10] its inverse
-      const float4 *ca = img.cobb + MPB_COBB_WORDS * pr.a, *cb = img.cobb + MPB_COBB_WORDS * pr.b;
-      const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
-      const int da = __float_as_int(ia.w), db = __float_as_int(ib.w);
+      const float4 *ca = img.cobb + MPB_COBB_WORDS * cp.y, *cb = img.cobb + MPB_COBB_WORDS * cp.z;
       // moving: this configuration's row of the OBB table (quaternion, translation); fixed: the record's world frame
+      const float4 *pa = da >= 0 ? obb + ((size_t)da * ld + cfg) * 2 : ca, *pb = db >= 0 ? obb + ((size_t)db * ld + cfg) * 2 : cb;
+      const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
+      const float4 ha = __ldg(ca + 3), hb = __ldg(cb + 3), ia = __ldg(ca + 4), ib = __ldg(cb + 4);
       Xf Ea, Eb;
-      if (da >= 0) { const float4 *pa = obb + ((size_t)da * ld + cfg) * 2; Ea = quat_rows(pa[0], pa[1]); }
-      else Ea = xf_rows(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2));
-      if (db >= 0) { const float4 *pb = obb + ((size_t)db * ld + cfg) * 2; Eb = quat_rows(pb[0], pb[1]); }
-      else Eb = xf_rows(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2));
+      if (da >= 0) Ea = quat_rows(a0, a1);
+      else Ea = xf_rows(a0, a1, __ldg(ca + 2));
+      if (db >= 0) Eb = quat_rows(b0, b1);
+      else Eb = xf_rows(b0, b1, __ldg(cb + 2));
       // box B in box A's frame:  Ra^T Rb,  Ra^T (cb - ca)  ==  (OBB frame A)^-1 (OBB frame B)
       const float d0 = Eb.p[0] - Ea.p[0], d1 = Eb.p[1] - Ea.p[1], d2 = Eb.p[2] - Ea.p[2];
 #pragma unroll
