@@ -129,6 +129,7 @@ struct mpb_scene {
   float *d_poses = nullptr;
   size_t d_q_cap[2] = {0, 0}, d_verdict_cap[2] = {0, 0}, d_pairbits_cap[2] = {0, 0}, d_poses_cap = 0, bins_cap = 0;
   cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
+  cudaStream_t stream_hits = nullptr;  // hit-list shares: not ordered behind stream_d2h's wait for the NEXT pass's kernels
   std::vector<cudaEvent_t> sync_events;
   long long host_chunk = 0;
   bool smem_verts = true;
@@ -189,6 +190,7 @@ static cudaError_t sync_scene(mpb_scene *s) {
   if (s->stream && (e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return e;
   if (s->stream_h2d && (e = cudaStreamSynchronize(s->stream_h2d)) != cudaSuccess) return e;
   if (s->stream_d2h && (e = cudaStreamSynchronize(s->stream_d2h)) != cudaSuccess) return e;
+  if (s->stream_hits && (e = cudaStreamSynchronize(s->stream_hits)) != cudaSuccess) return e;
   return e;
 }
 
@@ -1208,6 +1210,7 @@ extern "C" void mpb_scene_destroy(mpb_scene *s) {
   for (auto e : s->sync_events) cudaEventDestroy(e);
   if (s->stream_h2d) cudaStreamDestroy(s->stream_h2d);
   if (s->stream_d2h) cudaStreamDestroy(s->stream_d2h);
+  if (s->stream_hits) cudaStreamDestroy(s->stream_hits);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
 }
@@ -1703,6 +1706,7 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, const Coll
     }
     if (!s->stream_h2d) CU(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
     if (!s->stream_d2h) CU(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
+    if (!s->stream_hits) CU(cudaStreamCreateWithFlags(&s->stream_hits, cudaStreamNonBlocking));
   } else if (want_hits) {
     CU(ensure(&s->d_pairbits[0], &s->d_pairbits_cap[0], (size_t)chunk * std::max(W, 1)));  // the dense mask stays on the device
   }
@@ -1775,7 +1779,8 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, const Coll
         CU(cudaEventSynchronize(ev_cnt[c - 1]));
         const unsigned upto = std::min(s->h_hitcnt[c - 1], hit_cap);
         if (upto > hits_copied) {
-          CU(cudaMemcpyAsync(co.hits + 2 * (size_t)hits_copied, d_hits + hits_copied, (size_t)(upto - hits_copied) * sizeof(uint2), cudaMemcpyDeviceToHost, s->stream_d2h));
+          // its own stream: stream_d2h already waits for THIS pass's kernels, and the share would be copied a pass late
+          CU(cudaMemcpyAsync(co.hits + 2 * (size_t)hits_copied, d_hits + hits_copied, (size_t)(upto - hits_copied) * sizeof(uint2), cudaMemcpyDeviceToHost, s->stream_hits));
           hits_copied = upto;
         }
       }
@@ -1793,9 +1798,10 @@ static int collide_attempt(mpb_scene *s, const float *q, long long n, const Coll
     *co.n_hits = nh;
     const unsigned upto = std::min(nh, hit_cap);
     if (upto > hits_copied)
-      CU(cudaMemcpyAsync(co.hits + 2 * (size_t)hits_copied, d_hits + hits_copied, (size_t)(upto - hits_copied) * sizeof(uint2), cudaMemcpyDeviceToHost, s->stream_d2h));
+      CU(cudaMemcpyAsync(co.hits + 2 * (size_t)hits_copied, d_hits + hits_copied, (size_t)(upto - hits_copied) * sizeof(uint2), cudaMemcpyDeviceToHost, s->stream_hits));
   }
   if (host) CU(cudaStreamSynchronize(s->stream_d2h));
+  if (host && want_hits) CU(cudaStreamSynchronize(s->stream_hits));
   const auto t_end = std::chrono::steady_clock::now();
   if (!*overflow) {  // what the device-pointer fast path sizes its passes from: the largest pass size known to fit
     s->good_chunk = s->calibrated ? std::max(s->good_chunk, chunk) : chunk;

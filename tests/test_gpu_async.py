@@ -285,3 +285,21 @@ def test_native_module_and_ctypes_binding_agree(monkeypatch):
     with pytest.raises(RuntimeError, match="State dimension"):
         nat.collide(np.zeros((3, 5)))
     nat.close(); ct.close()
+
+
+def test_multi_pass_host_call_matches_single_pass_calls(panda_world):
+    """A host-buffer call larger than one pass (2^20 configurations) double-buffers its passes and copies every pass's share
+    of the hit list out on a stream of its own under the next pass's kernels: same verdicts, pair masks and hit list as the
+    same configurations sent in single-pass calls."""
+    dev = panda_world._sync()["dev"]
+    n = (1 << 20) + 70001
+    q = random_q(n, 77)
+    v, ph = dev.collide(q, want_pairs=True)
+    for lo, hi in ((0, 300000), (700000, 1000000), (n - 200000, n)):
+        v2, ph2 = dev.collide(q[lo:hi], want_pairs=True)
+        assert np.array_equal(v[lo:hi], v2) and np.array_equal(ph[lo:hi], ph2)
+    vh, hits = dev.collide_hits(q)
+    assert np.array_equal(vh, v)
+    got = np.zeros_like(ph)
+    got[hits[:, 0], hits[:, 1]] = True
+    assert np.array_equal(got, ph) and len(hits) == int(ph.sum())
