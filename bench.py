@@ -405,6 +405,21 @@ def run_checks(name, args, ctx, batch, steps, warmup, headline):
     e2e_s = time.perf_counter() - t0
     (e2e_s,) = ctx.reduce([e2e_s], "max")
 
+    # for information: the same steps asking for the verdict bit only -- what ValidityCheckerTpl::isValid consumes
+    # (src/ompl_planner.h:59-62); the kernels then skip pairs of configurations already known to collide
+    Kv = min(K, 5)
+    with torch.cuda.stream(stream):
+        dev.collide_raw(pool_d[0], N, verdict_d[0], None, _lib.MPB_DEVICE, stream.cuda_stream)
+        dev.poll(wait=True)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for k in range(Kv):
+            dev.collide_raw(pool_d[(Wm + k) % n_pool], N, verdict_d[k % K], None, _lib.MPB_DEVICE, stream.cuda_stream)
+        ev1.record(stream)
+    dev.poll(wait=True)
+    torch.cuda.synchronize()
+    (ms_v,) = ctx.reduce([ev0.elapsed_time(ev1)], "max")
+
     rec = None
     if rank == 0:
         total_checks = float(N) * world * K
@@ -437,6 +452,8 @@ def run_checks(name, args, ctx, batch, steps, warmup, headline):
                     "ms_per_step": 1e3 * e2e_s / K, "calls_in_flight": 1,
                     "pcie_gbs_per_gpu": {"h2d": N * D * 4 / (e2e_s / K) / 1e9, "d2h": d2h / (e2e_s / K) / 1e9}},
             "calls_in_flight": 1, "host_enqueue_ms_per_step": 1e3 * t_enq / K,
+            "verdict_only": {"value": float(N) * world * Kv / (ms_v * 1e-3), "unit": UNIT, "ms_per_step": ms_v / Kv, "steps": Kv,
+                             "note": "same steps, verdict bit only (no pair mask / hit list): what isValid needs; not the headline"},
             "gpu_launches": int(tot[1]),
             "clocks": clocks,
             "roofline": {
