@@ -397,7 +397,10 @@ struct FkTab {
   DevJoint j[MPB_MAX_JOINTS];  // dyn_first indexes o[] (objects grouped by owner joint)
   FkObjC o[MPB_MAX_DYN];
 };
-__global__ void __launch_bounds__(128) fk_table_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
+#ifndef MPB_FK_MINB
+#define MPB_FK_MINB 1
+#endif
+__global__ void __launch_bounds__(128, MPB_FK_MINB) fk_table_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
                                                        const float *__restrict__ qconst, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
                                                        float4 *__restrict__ obb) {
   // per warp: one object's 32 OBB rows, transposed for full-sector stores.  Quaternions at float4 [0, 32), translations
@@ -771,7 +774,10 @@ __global__ void __launch_bounds__(128) fk_sphere_kernel(const __grid_constant__ 
 #define POSE(w, i) pose[(size_t)(w) * ld + (i)]
 #define MPB_SQ_CHUNK_GRID 1024  // survivor-queue slots a warp of sphere_grid_kernel reserves per atomic: a trip pushes up to 128 entries,
                                // and what is left of a chunk when the next push does not fit is padding dense_kernel has to skip
-__global__ void __launch_bounds__(128) sphere_grid_kernel(const __grid_constant__ SceneImg img, const float *__restrict__ pose, size_t ld, long long n,
+#ifndef MPB_GRID_MINB
+#define MPB_GRID_MINB 10  // 48 registers (16 bytes of spills): ten blocks per SM; cull leg of a C3 step 7.58 -> 7.33 ms against 56 registers
+#endif
+__global__ void __launch_bounds__(128, MPB_GRID_MINB) sphere_grid_kernel(const __grid_constant__ SceneImg img, const float *__restrict__ pose, size_t ld, long long n,
                                                           long long cfg_base, uint2 *__restrict__ sq, unsigned sq_cap, unsigned *__restrict__ totals) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31;
@@ -1218,7 +1224,10 @@ __global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense_kernel(SceneImg img
 #define MPB_D2_CAP 64    // buffer entries per warp: phase 2 runs at 32, a phase-1 trip adds at most 32
 #define MPB_D2_F 14      // Rt (12 floats), configuration, pair
 
-__global__ void __launch_bounds__(128, MPB_DENSE_MINB) dense2_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
+#ifndef MPB_DENSE2_MINB
+#define MPB_DENSE2_MINB 8  // 64 registers, no spills: eight blocks per SM (cull leg of a C3 step 7.40 -> 7.22 ms against six blocks at 72 registers)
+#endif
+__global__ void __launch_bounds__(128, MPB_DENSE2_MINB) dense2_kernel(SceneImg img, const float4 *__restrict__ obb, size_t ld, const uint2 *__restrict__ sq,
                                                                       unsigned sq_cap, WorkQ wq, HitOut out, int presolve) {
   const unsigned FULL = 0xffffffffu;
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
