@@ -204,7 +204,9 @@ __device__ __forceinline__ V3 rot_t(const float *R, V3 v) {
 #define MPB_MPR_MAX_ITERS 500  // libccd: GJKSolver_libccd::max_collision_iterations [upstream]
 #define MPB_UNIT_ITEMS 128   // most items a warp owns at a time in the narrowphase (scan_bins_kernel picks 2..128)
 #define MPB_COOP_MAX 10      // busy lanes at or below which a warp evaluates hull supports cooperatively
+#ifndef MPB_STAGE_CHUNK
 #define MPB_STAGE_CHUNK 256  // staging slots a warp reserves per atomic (>= 32)
+#endif
 #define MPB_SMEM_BINS 1024    // bins a block can count in shared memory (more: global atomics)
 
 // ---------------------------------------------------------------------------------------------- FK
@@ -772,8 +774,10 @@ __global__ void __launch_bounds__(128) fk_sphere_kernel(const __grid_constant__ 
 // warp maximum ~11 per object instead of 130).  The survivors are exactly those of the full loop (the cell lists are
 // conservative), in a different order.  Runs of moving partners (self pairs) keep the direct loop.
 #define POSE(w, i) pose[(size_t)(w) * ld + (i)]
+#ifndef MPB_SQ_CHUNK_GRID
 #define MPB_SQ_CHUNK_GRID 1024  // survivor-queue slots a warp of sphere_grid_kernel reserves per atomic: a trip pushes up to 128 entries,
-                               // and what is left of a chunk when the next push does not fit is padding dense_kernel has to skip
+                                // and what is left of a chunk when the next push does not fit is padding dense_kernel has to skip
+#endif
 #ifndef MPB_GRID_MINB
 #define MPB_GRID_MINB 10  // 48 registers (16 bytes of spills): ten blocks per SM; cull leg of a C3 step 7.58 -> 7.33 ms against 56 registers
 #endif
@@ -2339,6 +2343,9 @@ __global__ void __launch_bounds__(128, 8) expand_kernel(SceneImg img, WorkQ wq, 
 // The warp-per-item kernel stays for small passes (planning rounds), where the critical path of a single traversal
 // matters more than throughput; both are launched, the item count of the bin decides which one runs.
 #define MPB_EXPL_DEPTH 28     // per-lane stack entries: the walk holds at most one sibling pair per level (tree depth ~17 for 10^5 leaves; 28 covers 2^28)
+#ifndef MPB_EXPL_REFILL
+#define MPB_EXPL_REFILL 16    // idle lanes that trigger a refill (the refill block is long): 4: +0.65 ms per C3 step, 8: 0, 16: -0.18, 24: +0.05, 32: +4
+#endif
 #define MPB_EXPL_QCAP 128     // leaf-primitive queue entries per warp
 #define MPB_EXPL_BINS 64      // second-round bins counted in shared memory
 #define MPB_EXPL_F 31         // floats of an item record: R 9, t 3, Ra 9, ca 3, cin 3, ah 3, rin2
@@ -2465,7 +2472,7 @@ __global__ void __launch_bounds__(128, MPB_EXPL_MINB) expand_lane_kernel(SceneIm
     // ---- refill: idle lanes take the next items of the bin (one ticket per warp and refill; the refill block is long, so
     // it runs only when a quarter of the warp is idle, or nobody has work)
     const unsigned need = __ballot_sync(FULL, !busy);
-    if (!drained && (__popc(need) >= 8 || need == FULL)) {
+    if (!drained && (__popc(need) >= MPB_EXPL_REFILL || need == FULL)) {
       // queued leaves refer to the records of their owner lanes: test them before any record is replaced
       while (qn > 0) { const int nb = min(qn, 32); exp_leaf_batch(img, wq, out, S, queue + qn - nb, nb, lane, smem_bins); qn -= nb; }
       unsigned base = 0;
