@@ -399,10 +399,8 @@ struct FkTab {
   DevJoint j[MPB_MAX_JOINTS];  // dyn_first indexes o[] (objects grouped by owner joint)
   FkObjC o[MPB_MAX_DYN];
 };
-#ifndef MPB_FK_MINB
-#define MPB_FK_MINB 1
-#endif
-__global__ void __launch_bounds__(128, MPB_FK_MINB) fk_table_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
+// (no minimum-blocks hint: with one, ptxas spends 72 registers instead of 56 and the kernel loses a fifth of its occupancy)
+__global__ void __launch_bounds__(128) fk_table_kernel(const __grid_constant__ SceneImg img, const __grid_constant__ FkTab tab,
                                                        const float *__restrict__ qconst, const float *__restrict__ q, long long n, float *__restrict__ pose, size_t ld,
                                                        float4 *__restrict__ obb) {
   // per warp: one object's 32 OBB rows, transposed for full-sector stores.  Quaternions at float4 [0, 32), translations
