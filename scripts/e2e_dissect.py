@@ -1,3 +1,7 @@
+#!/usr/bin/env python
+"""Where the end-to-end time of a C3 host-buffer call goes: verdict only / full hit list / truncated hit list (no list copy),
+each with the library's own gpu / enqueue / total times, and the box's pinned copy rates.  Run on a GPU box:
+PYTHONPATH=. python scripts/e2e_dissect.py   (this is what showed the hit-list shares queued behind the next pass's kernels)"""
 import time, numpy as np, torch
 from mplib_b200 import _lib
 from mplib_b200 import workloads as W
