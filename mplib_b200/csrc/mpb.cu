@@ -1398,7 +1398,7 @@ static int ensure_grid(mpb_scene *s) {
               d2 += d * d;
             }
             if (d2 > rr * rr) continue;
-            if (obb_filter) {
+            if (obb_filter && r.x >= 0) {  // (a run of fixed x fixed pairs lives in difference coordinates: no box filter there)
               const double g[3] = {lo[0] + (x + 0.5) * h, lo[1] + (y + 0.5) * h, lo[2] + (z + 0.5) * h};
               const double d0 = g[0] - box[0].w, d1 = g[1] - box[1].w, d2g = g[2] - box[2].w;
               const double l0 = box[0].x * d0 + box[1].x * d1 + box[2].x * d2g, l1 = box[0].y * d0 + box[1].y * d1 + box[2].y * d2g,

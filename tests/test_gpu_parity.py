@@ -284,3 +284,41 @@ def test_expand_variants_agree_and_match_oracle():
     for i, p in mism:
         assert abs(O.pair_signed_distance(dev.desc, qd[i], int(p))) < BAND
     assert len(mism) <= 30 and st["narrow_capped"] == 0
+
+
+def _base_ring_world():
+    """C3 primitives (grid scene: > 256 world-fixed partners) plus a ring of small spheres at the surface of the
+    world-fixed base link: fixed x fixed pairs whose verdict must not depend on the broadphase grid."""
+    from mplib_b200.pymp import fcl
+    from tests.workloads import c3_world
+
+    w = c3_world(n_each=32, mesh=False, cloud_points=0)
+    k = 0
+    for r in (0.07, 0.10, 0.13, 0.16):
+        for az in np.linspace(0.0, 2.0 * np.pi, 8, endpoint=False):
+            for z in (0.03, 0.09):
+                pos = [-0.04 + r * np.cos(az), r * np.sin(az), z]
+                w.add_normal_object(f"ring_{k}", fcl.CollisionObject(fcl.Sphere(0.03), pos, [1, 0, 0, 0]))
+                k += 1
+    return w
+
+
+def test_world_fixed_link_against_obstacles_in_a_grid_scene():
+    from oracle import oracle as O
+
+    w = _base_ring_world()
+    dev = w._sync()["dev"]
+    desc = dev.desc
+    q = random_q(6000, 41)  # > 4096: the thread-per-configuration kernels (sphere_grid_kernel)
+    v, ph = dev.collide(q, want_pairs=True)
+    qd = q[:64].astype(np.float32).astype(np.float64)
+    ov, oph = O.collide_batch(desc, qd, threads=8)
+    world_fixed = np.array([l < 0 or desc.link_joint[l] == 0 for l in desc.obj_link])  # obstacles, and links welded to the world
+    fixed = world_fixed[np.asarray(desc.pair_a)] & world_fixed[np.asarray(desc.pair_b)]
+    assert fixed.sum() >= 64  # base link x (primitives + ring)
+    # fixed x fixed verdicts are the same for every configuration, and equal to the oracle's
+    assert np.all(ph[:, fixed] == ph[0, fixed])
+    assert np.array_equal(ph[0, fixed], oph[0, fixed])
+    assert 4 <= int(ph[0, fixed].sum()) < int(fixed.sum())  # some of the ring touches the base, some does not
+    n_mis, _ = _check_pairs(desc, qd, ph[:64], oph)
+    assert n_mis <= 5
