@@ -8,20 +8,26 @@
 //                      src/pinocchio_model.cpp:271-312, src/fcl_model.cpp:138-148, src/attached_body.h:48-54.)
 //   sphere_kernel      thread per configuration over the cull table (admitted pairs in runs that share their moving
 //   sphere_blk_kernel  object): bounding-sphere test, 32 entries per mask word, survivors pushed into warp-private
-//                      chunks of the survivor queue.  Small tables ride in the parameter space with the tile's
-//                      sphere centres staged in shared memory; large ones are applied to four tiles per fetch.
-//   dense_kernel       thread per survivor: 15-axis OBB SAT from the two OBB rows, inscribed-ball sufficient test,
-//                      relative pose of what is left -> staging queue (one atomic per warp and 256 slots).
-//   scan_bins_kernel   prefix sums of the per-bin counts -> binned queue offsets.
-//   scatter_kernel     staging queue -> binned queue (bin = (geometry A, geometry B) class).
-//   narrow_kernel      lane per work item with PERSISTENT lanes: a warp owns a slice of ONE bin, so all
-//                      lanes walk the same hulls and the vertex loop is a broadcast LDS.128 + 3 FFMA per
-//                      vertex for 32 items at once; a lane that finishes its item pulls the next one of the
-//                      slice, so short and long MPR runs do not wait for each other.  Hull pool staged in
-//                      shared memory by TMA bulk copies (cp.async.bulk + mbarrier).  MPR (replaces
+//   sphere_grid_kernel chunks of the survivor queue.  Small tables ride in the parameter space with the tile's
+//   sphere_pairs_kernel sphere centres staged in shared memory; large ones with world-fixed partners go through a uniform
+//                      grid per moving object (a handful of candidates instead of the whole run); small passes use a
+//                      thread per (configuration, entry).
+//   dense2_kernel      thread per survivor, two converged phases: 15-axis OBB SAT from the two OBB rows + inscribed-ball
+//   (dense_kernel)     test; then the relative pose of what is left, the sufficient-hit test with the inner balls, and one
+//                      64-byte ITEM RECORD + 2-byte bin key per item (warp-private chunks of 256 slots).
+//   scan_bins_kernel   prefix sums of the per-bin counts -> offsets of the binned order.
+//   scatter_kernel     ranks the bin keys and writes order[]: the items are sorted by INDEX, the records never move
+//                      (bin = (geometry A, geometry B) class).
+//   narrow2_kernel     lane per work item, a warp owns a slice of ONE bin (so all lanes walk the same hulls): a converged
+//   (narrow_kernel)    prologue over 32 fresh items (fetch through order[], first two supports and their exits), survivors
+//                      buffered in shared memory, then the portal loop over full warps of survivors.  Hull pool + support
+//                      cell tables staged in shared memory by TMA bulk copies (cp.async.bulk + mbarrier).  MPR (replaces
 //                      ::fcl::collide -> ccdMPRIntersect on the pairs of FCLModelTpl::collideFull /
 //                      PlanningWorldTpl::selfCollide / collideWithOthers, src/fcl_model.cpp:181-193,
-//                      src/planning_world.cpp:276-481) is a state machine with a single support call site.
+//                      src/planning_world.cpp:276-481).
+//   expand_kernel      shape x BVH object (mesh / octree): AABB-tree descent against the shape's box, leaf items for a
+//   expand_lane_kernel second narrowphase round; expand2_kernel: mesh x mesh / mesh x octree with exact leaf tests in place.
+//   hits_compact_kernel dense pair mask of a pass -> (configuration, pair) list.
 //   fk_pose_kernel     FK-only API: link poses as [x,y,z,qw,qx,qy,qz].
 #pragma once
 #include <float.h>
@@ -71,7 +77,7 @@ struct WorkQ {
   unsigned int *bin_cursor;  // [n_bins]
   unsigned int *bin_start;   // [n_bins+1]
   unsigned int *unit_start;  // [n_bins+1]   units of MPB_UNIT_ITEMS items
-  unsigned int *totals;      // [0]=staged items [1]=units [2]=overflow flag [3]=unit ticket [4]=items per unit
+  unsigned int *totals;      // [0]=record slots handed out (holes included) [1]=units [2]=overflow flag [3]=unit ticket [4]=items per unit
   unsigned long long *counters;  // [0]=items after cull [1]=support evaluations [2]=capped items
   unsigned int cap;
 };
